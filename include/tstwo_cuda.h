@@ -1,0 +1,126 @@
+/*
+ * tstwo_cuda.h -- C ABI of libtstwo_cuda.so, the B200 (sm_100a) CudaBackend for TStwo.
+ *
+ * Drop-in boundary: these entry points are what a `bun:ffi` (or ctypes / cgo) binding of the reference's
+ * backend interfaces binds for the LDE + Blake2s-commit hot path.  Each function cites the reference interface
+ * it replaces (paths relative to packages/core/src of teddyjfpender/tstwo).  See INTEGRATION.md for the
+ * TypeScript-side stub.
+ *
+ * Conventions
+ *  - Every function returns 0 on success or a negative tstwo_status; tstwo_last_error() gives the message of
+ *    the last failure on the calling thread (the reference throws `Error(msg)`).
+ *  - Device memory is addressed by plain 64-bit device addresses (tstwo_dptr).  They may come from
+ *    tstwo_malloc() or from any other allocator in the same process (e.g. a torch tensor's data_ptr()).
+ *  - Field elements are canonical little-endian u32 in [0, 2^31-1).  A SecureField (QM31) column is four
+ *    coordinate columns (SecureColumnByCoords, fields/secure_columns.ts:124-217); a QM31 scalar is u32[4] in
+ *    to_m31_array order (fields/qm31.ts:139-141).  Hashes are 32 raw bytes.
+ *  - Calls are issued from one host thread and are asynchronous on the library stream unless they return
+ *    host-visible data (those synchronise before returning).  tstwo_sync() waits for everything.
+ *  - Arrays of column addresses (`const tstwo_dptr *cols`) are HOST arrays of device addresses.
+ */
+#ifndef TSTWO_CUDA_H
+#define TSTWO_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef uint64_t tstwo_dptr;      /* device address */
+typedef uint64_t tstwo_twiddles;  /* opaque TwiddleTree handle (poly/twiddles.ts:14-29) */
+
+enum tstwo_status {
+    TSTWO_OK = 0,
+    TSTWO_ERR_BAD_ARG = -1,
+    TSTWO_ERR_SIZE_MISMATCH = -2,     /* e.g. "fold_circle_into_line: Length mismatch ..." (fri.ts:167-169) */
+    TSTWO_ERR_TWIDDLE_MISMATCH = -3,  /* "twiddle tree mismatch" (backend/cpu/circle.ts:90,141) */
+    TSTWO_ERR_CUDA = -4,
+    TSTWO_ERR_OOM = -5,
+    TSTWO_ERR_NOT_POW2 = -6,          /* "length is not power of two" (backend/cpu/index.ts:65) */
+    TSTWO_ERR_NOT_INIT = -7
+};
+
+/* flags */
+#define TSTWO_FLAG_QUIRKS 1u /* reproduce CpuBackend's log_size==3 swap of values[5]<->values[7]
+                                (backend/cpu/circle.ts:127-131,147-151) */
+
+/* ---- lifecycle ------------------------------------------------------------------------------------------- */
+int tstwo_init(int device);                 /* select device, create the library stream; idempotent */
+int tstwo_shutdown(void);
+const char *tstwo_last_error(void);
+int tstwo_set_stream(void *cuda_stream);    /* run on a caller-owned cudaStream_t (NULL = library stream) */
+int tstwo_sync(void);
+int tstwo_device_info(int *sm_count, int *cc_major, int *cc_minor, uint64_t *total_mem);
+uint64_t tstwo_launch_count(void);          /* number of kernels this library has launched (for bench.py) */
+
+/* ---- Column<T> / ColumnOps  (backend/index.ts:53-74, :12-14; impl backend/cpu/index.ts:18-53,85-157) ------ */
+int tstwo_malloc(uint64_t bytes, tstwo_dptr *out);                       /* Column.zeros/uninitialized */
+int tstwo_free(tstwo_dptr p);
+int tstwo_memset_zero(tstwo_dptr p, uint64_t bytes);
+int tstwo_upload(tstwo_dptr dst, const void *host, uint64_t bytes);      /* createBaseFieldColumn(data) */
+int tstwo_download(void *host, tstwo_dptr src, uint64_t bytes);          /* Column.toCpu() / at(i) */
+int tstwo_copy(tstwo_dptr dst, tstwo_dptr src, uint64_t bytes);
+int tstwo_bit_reverse(tstwo_dptr col, uint64_t len);                     /* ColumnOps.bitReverseColumn; len = #u32 */
+
+/* ---- PolyOps  (poly/circle/ops.ts:20-66; impl backend/cpu/circle.ts:17-239) -------------------------------- */
+/* precomputeTwiddles(coset): backend/cpu/circle.ts:210-239.  The tree holds 2^log words of twiddles+itwiddles. */
+int tstwo_twiddles_precompute(uint32_t coset_initial_index, int coset_log_size, tstwo_twiddles *out);
+int tstwo_twiddles_free(tstwo_twiddles tw);
+int tstwo_twiddles_info(tstwo_twiddles tw, uint32_t *root_initial_index, int *root_log_size,
+                        tstwo_dptr *twiddles, tstwo_dptr *itwiddles);
+/* interpolateColumns / CpuCirclePoly.interpolate (circle.ts:136-207): n_cols evaluations (bit-reversed order) on
+ * the circle domain with half coset (half_coset_initial_index, log_size-1) -> coefficients.  evals[i] may equal
+ * coeffs[i] (in place). */
+int tstwo_interpolate_columns(const tstwo_dptr *evals, const tstwo_dptr *coeffs, int n_cols, int log_size,
+                              uint32_t half_coset_initial_index, tstwo_twiddles tw, uint32_t flags);
+/* evaluatePolynomials / CpuCirclePoly.evaluate with extend (circle.ts:71-134): coefficient vectors of 2^poly_log
+ * words -> 2^domain_log evaluations on the domain with half coset (half_coset_initial_index, domain_log-1). */
+int tstwo_evaluate_columns(const tstwo_dptr *coeffs, int poly_log, const tstwo_dptr *evals, int n_cols,
+                           int domain_log, uint32_t half_coset_initial_index, tstwo_twiddles tw, uint32_t flags);
+/* CpuCirclePoly.eval_at_point (circle.ts:52-69): point = CirclePoint<SecureField>. */
+int tstwo_eval_at_point(tstwo_dptr coeffs, int log_size, const uint32_t px[4], const uint32_t py[4], uint32_t out[4]);
+
+/* ---- MerkleOps<Blake2sHash>  (vcs/ops.ts:16-26; vcs/blake2_merkle.ts:9-24; backend/cpu/blake2.ts:98-127) --- */
+/* commitOnLayer(logSize, prevLayer, columns): out_layer = 2^log_size hashes (32 B each); prev_layer = 0 or the
+ * 2^(log_size+1) hashes of the layer below.  node_i = blake2s(prev[2i] || prev[2i+1] || LE32(col_0[i]) || ...). */
+int tstwo_merkle_commit_layer(int log_size, tstwo_dptr prev_layer, const tstwo_dptr *cols, int n_cols,
+                              tstwo_dptr out_layer);
+/* MerkleProver.commit (vcs/prover.ts:13-30): all layers, root first: layer k (2^k hashes) at byte offset
+ * 32*(2^k-1) of `layers` ((2^(max_log+1)-1)*32 bytes).  root[32] is copied to the host (synchronises). */
+int tstwo_merkle_commit(const tstwo_dptr *cols, const int *col_logs, int n_cols, tstwo_dptr layers, uint8_t root[32]);
+
+/* ---- FriOps  (fri.ts:93-110, :120-192; impl backend/cpu/fri.ts:23-164) -------------------------------------- */
+/* tw may be 0: the twiddles are then derived from the coset on the fly. */
+int tstwo_fold_line(const tstwo_dptr src[4], int log_size, uint32_t coset_initial_index, const uint32_t alpha[4],
+                    const tstwo_dptr dst[4], tstwo_twiddles tw);
+int tstwo_fold_circle_into_line(const tstwo_dptr dst[4], const tstwo_dptr src[4], int log_size,
+                                uint32_t half_coset_initial_index, const uint32_t alpha[4], tstwo_twiddles tw);
+int tstwo_fri_decompose(const tstwo_dptr src[4], int log_size, const tstwo_dptr g[4], uint32_t lambda[4]);
+
+/* ---- AccumulationOps / QuotientOps  (backend/cpu/accumulation.ts:38-63, backend/cpu/quotients.ts:52-178) ---- */
+int tstwo_accumulate(const tstwo_dptr dst[4], const tstwo_dptr src[4], uint64_t len);
+/* Sample batches are flattened: batch b has point (px[4], py[4]) at points[8b..8b+8) and entries
+ * [batch_offsets[b], batch_offsets[b+1]) of (col_index[j], values[4j..4j+4)).  Host arrays. */
+int tstwo_accumulate_quotients(int log_size, uint32_t half_coset_initial_index, const tstwo_dptr *cols, int n_cols,
+                               const uint32_t random_coeff[4], int n_batches, const uint32_t *points,
+                               const int *batch_offsets, const int *col_index, const uint32_t *values,
+                               const tstwo_dptr out[4]);
+
+/* ---- the metric path in one call: Stwo's CommitmentTreeProver::new (quoted at pcs/prover.ts:215-235) -------- */
+/* interpolate n_cols trace columns on CanonicCoset(log_size), evaluate on CanonicCoset(log_size+log_blowup),
+ * Blake2s Merkle commit.  trace/coeffs/evals are contiguous column-major blocks (column c at base + c*len).
+ * coeffs may be 0 (coefficients are then not kept).  tw must cover half_odds(log_size+log_blowup-1). */
+int tstwo_lde_commit(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
+                     tstwo_dptr coeffs, tstwo_dptr evals, tstwo_dptr layers, uint8_t root[32], uint32_t flags);
+/* Same, but the trace lives in HOST memory (pinned or pageable): host->device copies are pipelined with the
+ * kernels inside the call; only the root comes back. */
+int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
+                          tstwo_dptr trace_staging, tstwo_dptr coeffs, tstwo_dptr evals, tstwo_dptr layers,
+                          uint8_t root[32], uint32_t flags);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TSTWO_CUDA_H */

@@ -1,0 +1,57 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/tstwo_cuda.h declares, fails loudly
+without a GPU (no CPU fallback), and the host index arithmetic mirrors the reference (vs the oracle)."""
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_header_symbol():
+    import __graft_entry__ as g
+    if not os.path.exists(os.path.join(ROOT, "tstwo_b200", "libtstwo_cuda.so")):
+        g.build()
+    from tstwo_b200 import _lib
+    lib = _lib.load()
+    hdr = open(os.path.join(ROOT, "include", "tstwo_cuda.h")).read()
+    names = set(re.findall(r"\b(tstwo_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 28
+    for n in names:
+        assert hasattr(lib, n), n
+        assert n in _lib.SIGNATURES, n
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from tstwo_b200 import _lib, CudaColumn
+    with pytest.raises(_lib.TstwoError, match="no CUDA device|CUDA"):
+        CudaColumn.zeros(4)
+
+
+def test_product_does_not_import_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "tstwo_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in src and "tstwo_oracle" not in src, f
+
+
+def test_host_circle_mirror(orc):
+    from tstwo_b200 import CanonicCoset, CirclePointIndex, Coset
+    for log in range(1, 12):
+        cc = CanonicCoset.new(log)
+        hc = cc.half_coset()
+        assert (hc.initial_index.value, hc.log_size) == orc.canonic_half_coset(log)
+        dom = cc.circleDomain()
+        assert dom.isCanonic()
+        for i in [0, 1, dom.size() // 2, dom.size() - 1]:
+            assert dom.at(i) == orc.domain_point(hc.initial_index.value, hc.log_size, i)
+    big = Coset.half_odds(10)
+    assert Coset.half_odds(6).is_doubling_of(big) and not Coset.half_odds(6).shift(CirclePointIndex(2)).is_doubling_of(big)
+    assert not big.is_doubling_of(Coset.half_odds(6))
+    assert CirclePointIndex(1).to_point() == (2, 1268011823)
+    with pytest.raises(ValueError):
+        CanonicCoset.new(0)

@@ -1,0 +1,95 @@
+"""The metric path (tstwo_lde_commit / CommitmentTreeProver.from_trace) against the oracle at sizes the oracle
+finishes in seconds, and through size-independent properties at BASELINE.json's config-2 size."""
+import ctypes as C
+import hashlib
+import struct
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+P = 2147483647
+
+
+@pytest.fixture(scope="module")
+def tb():
+    import tstwo_b200
+    return tstwo_b200
+
+
+@pytest.mark.parametrize("log,blow,n_cols,keep", [(4, 1, 3, True), (10, 2, 5, True), (14, 1, 24, True), (14, 1, 9, False),
+                                                 (15, 2, 16, False), (16, 1, 64, True)])
+def test_lde_commit_vs_oracle(tb, orc, log, blow, n_cols, keep):
+    rng = np.random.default_rng(log * 100 + n_cols)
+    trace = rng.integers(0, P, (n_cols, 1 << log), dtype=np.uint32)
+    root_coset = tb.CanonicCoset.new(log + blow).half_coset()
+    tw = tb.CudaBackend.precomputeTwiddles(root_coset)
+    tree = tb.CommitmentTreeProver.from_trace(tb.CudaColumn.from_cpu(trace.reshape(-1)), n_cols, log, blow, tw, keep_coeffs=keep)
+    otw, oitw = orc.precompute_twiddles(root_coset.initial_index.value, root_coset.log_size)
+    coeffs, evals, layers = orc.lde_commit(trace, blow, otw, oitw, want_coeffs=True)
+    for c in range(n_cols):
+        if keep:
+            assert (tree.polynomials[c].coeffs.toCpu() == coeffs[c]).all()
+        assert (tree.evaluations[c].values.toCpu() == evals[c]).all()
+    assert tree.root() == layers[0][0].tobytes()
+    for k in (0, 1, log + blow - 1, log + blow):
+        assert (tree.commitment.layer_bytes(k) == layers[k]).all()
+
+
+def test_lde_commit_host_matches_device(tb, orc):
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    log, blow, n_cols = 14, 1, 40
+    rng = np.random.default_rng(5)
+    trace = rng.integers(0, P, (n_cols, 1 << log), dtype=np.uint32)
+    tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(log + blow).half_coset())
+    ref = tb.CommitmentTreeProver.from_trace(tb.CudaColumn.from_cpu(trace.reshape(-1)), n_cols, log, blow, tw)
+    stage = tb.CudaColumn.uninitialized(trace.size)
+    evals = tb.CudaColumn.uninitialized(trace.size << blow)
+    layers = tb.CudaColumn.uninitialized(8 * ((2 << (log + blow)) - 1))
+    root = (C.c_uint8 * 32)()
+    _lib.check(L.tstwo_lde_commit_host(trace.ctypes.data, n_cols, log, blow, tw.handle, stage.ptr, 0, evals.ptr, layers.ptr, root, 1))
+    assert bytes(root) == ref.root()
+
+
+def test_config2_properties(tb, orc):
+    """BASELINE config 2: wide-Fibonacci 256 columns, log 20, blowup 2.  Too big for an element-wise oracle compare in
+    the test budget, so: (a) the first and last column are compared with the oracle in full, (b) a Merkle
+    authentication path of a random leaf is re-hashed with hashlib up to the root, (c) interpolating the extended
+    evaluation gives back the coefficients padded with zeros (round trip), (d) root is reproducible."""
+    log, blow, n_cols = 20, 1, 256
+    n = 1 << log
+    # wide Fibonacci (examples/fibonacci.ts:245-258 a=1, b=row; c = a^2 + b^2), natural row order
+    a = np.ones(n, dtype=np.uint64); b = np.arange(n, dtype=np.uint64) % P
+    cols = np.empty((n_cols, n), dtype=np.uint32)
+    cols[0], cols[1] = a, b
+    for k in range(2, n_cols):
+        a, b = b, (a * a % P + b * b % P) % P
+        cols[k] = b
+    root_coset = tb.CanonicCoset.new(log + blow).half_coset()
+    tw = tb.CudaBackend.precomputeTwiddles(root_coset)
+    tree = tb.CommitmentTreeProver.from_trace(tb.CudaColumn.from_cpu(cols.reshape(-1)), n_cols, log, blow, tw)
+    otw, oitw = orc.precompute_twiddles(root_coset.initial_index.value, root_coset.log_size)
+    for c in (0, n_cols - 1):
+        cf, ev, _ = orc.lde_commit(cols[c:c + 1], blow, otw, oitw, want_coeffs=True, want_layers=False)
+        assert (tree.polynomials[c].coeffs.toCpu() == cf[0]).all()
+        assert (tree.evaluations[c].values.toCpu() == ev[0]).all()
+    # (b) authentication path
+    ext = log + blow
+    leaf = 0x12345 % (1 << ext)
+    row = b"".join(struct.pack("<I", tree.evaluations[c].values.at(leaf)) for c in range(n_cols))
+    h = hashlib.blake2s(row).digest()
+    idx = leaf
+    for k in range(ext, 0, -1):
+        layer = tree.commitment.layers[k]
+        assert layer.slice(8 * idx, 8).toCpu().tobytes() == h
+        sib = layer.slice(8 * (idx ^ 1), 8).toCpu().tobytes()
+        h = hashlib.blake2s(h + sib if idx % 2 == 0 else sib + h).digest()
+        idx >>= 1
+    assert h == tree.root()
+    # (c) round trip on the big domain
+    back = tb.CudaBackend.interpolateColumns([tree.evaluations[7]], tw)[0].coeffs.toCpu()
+    assert (back[:n] == tree.polynomials[7].coeffs.toCpu()).all() and not back[n:].any()
+    # (d) determinism
+    again = tb.CommitmentTreeProver.from_trace(tb.CudaColumn.from_cpu(cols.reshape(-1)), n_cols, log, blow, tw, keep_coeffs=False)
+    assert again.root() == tree.root()

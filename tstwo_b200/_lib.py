@@ -1,0 +1,112 @@
+"""ctypes binding of libtstwo_cuda.so (include/tstwo_cuda.h).  No CPU fallback: importing works without a GPU
+(so the symbol table can be checked), but any compute call raises unless a B200 is present."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_DIR = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_DIR, "libtstwo_cuda.so")
+
+dptr = C.c_uint64
+u32p = C.POINTER(C.c_uint32)
+dptrp = C.POINTER(C.c_uint64)
+intp = C.POINTER(C.c_int)
+
+FLAG_QUIRKS = 1
+
+ERR_NAMES = {-1: "BAD_ARG", -2: "SIZE_MISMATCH", -3: "TWIDDLE_MISMATCH", -4: "CUDA", -5: "OOM", -6: "NOT_POW2", -7: "NOT_INIT"}
+
+
+class TstwoError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"[{ERR_NAMES.get(code, code)}] {msg}")
+        self.code = code
+        self.msg = msg
+
+
+class TwiddleMismatch(TstwoError):
+    pass
+
+
+# name -> (restype, argtypes); mirrors include/tstwo_cuda.h one to one
+SIGNATURES = {
+    "tstwo_init": (C.c_int, [C.c_int]),
+    "tstwo_shutdown": (C.c_int, []),
+    "tstwo_last_error": (C.c_char_p, []),
+    "tstwo_set_stream": (C.c_int, [C.c_void_p]),
+    "tstwo_sync": (C.c_int, []),
+    "tstwo_device_info": (C.c_int, [intp, intp, intp, C.POINTER(C.c_uint64)]),
+    "tstwo_launch_count": (C.c_uint64, []),
+    "tstwo_malloc": (C.c_int, [C.c_uint64, dptrp]),
+    "tstwo_free": (C.c_int, [dptr]),
+    "tstwo_memset_zero": (C.c_int, [dptr, C.c_uint64]),
+    "tstwo_upload": (C.c_int, [dptr, C.c_void_p, C.c_uint64]),
+    "tstwo_download": (C.c_int, [C.c_void_p, dptr, C.c_uint64]),
+    "tstwo_copy": (C.c_int, [dptr, dptr, C.c_uint64]),
+    "tstwo_bit_reverse": (C.c_int, [dptr, C.c_uint64]),
+    "tstwo_twiddles_precompute": (C.c_int, [C.c_uint32, C.c_int, dptrp]),
+    "tstwo_twiddles_free": (C.c_int, [C.c_uint64]),
+    "tstwo_twiddles_info": (C.c_int, [C.c_uint64, u32p, intp, dptrp, dptrp]),
+    "tstwo_interpolate_columns": (C.c_int, [dptrp, dptrp, C.c_int, C.c_int, C.c_uint32, C.c_uint64, C.c_uint32]),
+    "tstwo_evaluate_columns": (C.c_int, [dptrp, C.c_int, dptrp, C.c_int, C.c_int, C.c_uint32, C.c_uint64, C.c_uint32]),
+    "tstwo_eval_at_point": (C.c_int, [dptr, C.c_int, u32p, u32p, u32p]),
+    "tstwo_merkle_commit_layer": (C.c_int, [C.c_int, dptr, dptrp, C.c_int, dptr]),
+    "tstwo_merkle_commit": (C.c_int, [dptrp, intp, C.c_int, dptr, C.POINTER(C.c_uint8)]),
+    "tstwo_fold_line": (C.c_int, [dptrp, C.c_int, C.c_uint32, u32p, dptrp, C.c_uint64]),
+    "tstwo_fold_circle_into_line": (C.c_int, [dptrp, dptrp, C.c_int, C.c_uint32, u32p, C.c_uint64]),
+    "tstwo_fri_decompose": (C.c_int, [dptrp, C.c_int, dptrp, u32p]),
+    "tstwo_accumulate": (C.c_int, [dptrp, dptrp, C.c_uint64]),
+    "tstwo_accumulate_quotients": (C.c_int, [C.c_int, C.c_uint32, dptrp, C.c_int, u32p, C.c_int, u32p, intp, intp, u32p, dptrp]),
+    "tstwo_lde_commit": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptr, C.POINTER(C.c_uint8), C.c_uint32]),
+    "tstwo_lde_commit_host": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptr, dptr,
+                                        C.POINTER(C.c_uint8), C.c_uint32]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen the library and bind every symbol of the header.  Raises if the .so is missing (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise RuntimeError(f"{SO_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(tstwo_b200 has no CPU fallback)")
+        lib = C.CDLL(SO_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)   # AttributeError if the symbol is missing
+            fn.restype = res
+            fn.argtypes = args
+        lib.tstwo_debug_force_naive_fft.restype = C.c_int
+        lib.tstwo_debug_force_naive_fft.argtypes = [C.c_int]
+        _lib = lib
+    return _lib
+
+
+def check(rc: int):
+    if rc != 0:
+        msg = load().tstwo_last_error().decode(errors="replace")
+        if rc == -3:
+            raise TwiddleMismatch(rc, msg)
+        raise TstwoError(rc, msg)
+
+
+_inited = None
+
+
+def init(device: int = 0):
+    global _inited
+    lib = load()
+    if _inited != device:
+        check(lib.tstwo_init(device))
+        _inited = device
+    return lib
+
+
+def dptr_array(addrs):
+    return (C.c_uint64 * max(1, len(addrs)))(*addrs)
+
+
+def u32_array(vals):
+    return (C.c_uint32 * max(1, len(vals)))(*[int(v) for v in vals])

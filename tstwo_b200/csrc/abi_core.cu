@@ -1,0 +1,301 @@
+// libtstwo_cuda.so: lifecycle, column memory, bit-reverse and twiddle-tree entry points of include/tstwo_cuda.h.
+#include <cstdarg>
+#include <cstring>
+#include <mutex>
+#include <unordered_map>
+#include <vector>
+
+#include "common.cuh"
+#include "circle_dev.cuh"
+
+namespace tstwo {
+
+static thread_local char g_err[512] = "";
+static Context g_ctx;
+Context &ctx() { return g_ctx; }
+
+int fail(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+static const int PTR_SLOTS = 4;
+static const size_t PTR_SLOT_CAP = 4096;   // addresses per slot
+
+int make_colset(const tstwo_dptr *cols, int n_cols, int slot, ColSet *out)
+{
+    out->base = nullptr; out->stride = 0; out->table = nullptr;
+    if (n_cols <= 0) return 0;
+    if (!cols) return fail(TSTWO_ERR_BAD_ARG, "null column list");
+    bool uniform = true;
+    int64_t stride = n_cols > 1 ? (int64_t)(cols[1] - cols[0]) : 0;
+    for (int c = 1; c < n_cols && uniform; c++) uniform = (int64_t)(cols[c] - cols[c - 1]) == stride;
+    if (uniform && stride >= 0 && (stride % 4) == 0) {
+        out->base = reinterpret_cast<const uint32_t *>(cols[0]);
+        out->stride = (uint64_t)stride / 4;
+        return 0;
+    }
+    if ((size_t)n_cols > PTR_SLOT_CAP || slot >= PTR_SLOTS) return fail(TSTWO_ERR_BAD_ARG, "too many scattered columns (%d)", n_cols);
+    Context &c = ctx();
+    uint64_t *dst = c.d_ptr_table + (size_t)slot * PTR_SLOT_CAP;
+    TS_CUDA(cudaMemcpyAsync(dst, cols, sizeof(uint64_t) * (size_t)n_cols, cudaMemcpyHostToDevice, c.stream));
+    out->table = dst;
+    return 0;
+}
+
+// ---------------------------------------------------------------- bit reverse (backend/cpu/index.ts:62-79)
+__global__ void bit_reverse_kernel(uint32_t *a, int log_n)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >> log_n) return;
+    uint32_t j = m31::bitrev((uint32_t)i, log_n);
+    if (j > i) { uint32_t t = a[i]; a[i] = a[j]; a[j] = t; }
+}
+
+// ---------------------------------------------------------------- twiddles (backend/cpu/circle.ts:210-239)
+
+// One thread per entry e of the 2^log tree buffer.  Layer i holds bitrev(x of first half of the i-times doubled
+// coset); the last entry is the pad value 1.
+__global__ void twiddle_tree_kernel(uint32_t *tw, uint32_t *itw, uint32_t *tw2, uint32_t *itw2, uint32_t init, int log)
+{
+    uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t n = 1ull << log;
+    if (e >= n) return;
+    uint32_t x;
+    if (e == n - 1) x = 1;
+    else {
+        uint32_t r = (uint32_t)(n - e);              // 2 .. 2^log
+        int m = 31 - __clz(r - 1);                   // layer half-size = 2^m
+        uint32_t j = (1u << (m + 1)) - r;
+        int i = log - 1 - m;                         // layer number
+        uint32_t ci = (init << i) & 0x7fffffffu;     // init * 2^i mod 2^31
+        uint32_t step = 1u << (31 - (m + 1));
+        uint32_t idx = (ci + m31::bitrev(j, m) * step) & 0x7fffffffu;
+        x = index_to_point(idx).x;
+    }
+    uint32_t ix = m31::inv(x);
+    tw[e] = x; itw[e] = ix; tw2[e] = x + x; itw2[e] = ix + ix;
+}
+
+// out[i] = 2 / coord(init + bitrev(i, m) * step)  (pre-doubled inverse), i < 2^m; which: 0 = x, 1 = y
+__global__ void coset_inv_coord_kernel(uint32_t *out2, uint32_t init, uint32_t step, int m, int which)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >> m) return;
+    uint32_t idx = (init + m31::bitrev((uint32_t)i, m) * step) & 0x7fffffffu;
+    m31::Pt p = index_to_point(idx);
+    uint32_t v = m31::inv(which ? p.y : p.x);
+    out2[i] = v + v;
+}
+
+int launch_coset_points(uint32_t *out2, int which, uint32_t init, int step_log, int m)
+{
+    uint64_t n = 1ull << m;
+    uint32_t step = host::subgroup_gen(step_log);
+    TS_LAUNCH(coset_inv_coord_kernel, (unsigned)((n + 255) / 256), 256, 0, out2, init, step, m, which);
+    return 0;
+}
+
+static std::mutex g_tree_mu;
+static std::unordered_map<uint64_t, TwiddleTree *> g_trees;
+static uint64_t g_next_tree = 1;
+
+TwiddleTree *get_tree(tstwo_twiddles h)
+{
+    std::lock_guard<std::mutex> lk(g_tree_mu);
+    auto it = g_trees.find(h);
+    return it == g_trees.end() ? nullptr : it->second;
+}
+bool is_doubling_of(uint32_t init, int log, const TwiddleTree *t)
+{
+    if (log > t->root_log) return false;
+    uint32_t v = t->root_init & 0x7fffffffu;
+    for (int i = 0; i < t->root_log - log; i++) v = (v * 2u) & 0x7fffffffu;
+    return v == (init & 0x7fffffffu);
+}
+
+}  // namespace tstwo
+
+using namespace tstwo;
+
+extern "C" {
+
+int tstwo_init(int device)
+{
+    Context &c = ctx();
+    if (c.ready && c.device == device) return 0;
+    if (c.ready) tstwo_shutdown();
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(TSTWO_ERR_CUDA, "no CUDA device available (%s); libtstwo_cuda has no CPU fallback",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= n) return fail(TSTWO_ERR_BAD_ARG, "device %d out of range [0,%d)", device, n);
+    TS_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    TS_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(TSTWO_ERR_CUDA, "device is sm_%d%d; this library is built for sm_100a only", prop.major, prop.minor);
+    c.device = device;
+    c.sm_count = prop.multiProcessorCount;
+    TS_CUDA(cudaStreamCreateWithFlags(&c.own_stream, cudaStreamNonBlocking));
+    TS_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
+    c.stream = c.own_stream;
+    TS_CUDA(cudaMalloc(&c.d_ptr_table, sizeof(uint64_t) * PTR_SLOTS * PTR_SLOT_CAP));
+    TS_CUDA(upload_gen_table());
+    TS_CUDA(elementwise_init());
+    c.launches = 0;
+    c.ready = true;
+    return 0;
+}
+
+int tstwo_shutdown(void)
+{
+    Context &c = ctx();
+    if (!c.ready) return 0;
+    cudaDeviceSynchronize();
+    {
+        std::lock_guard<std::mutex> lk(g_tree_mu);
+        for (auto &kv : g_trees) {
+            cudaFree(kv.second->tw);
+            delete kv.second;
+        }
+        g_trees.clear();
+    }
+    cudaFree(c.d_ptr_table);
+    cudaStreamDestroy(c.own_stream);
+    cudaStreamDestroy(c.copy_stream);
+    c = Context();
+    return 0;
+}
+
+const char *tstwo_last_error(void) { return g_err; }
+
+int tstwo_set_stream(void *s)
+{
+    TS_REQUIRE_INIT();
+    ctx().stream = s ? (cudaStream_t)s : ctx().own_stream;
+    return 0;
+}
+int tstwo_sync(void)
+{
+    TS_REQUIRE_INIT();
+    TS_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+int tstwo_device_info(int *sm_count, int *cc_major, int *cc_minor, uint64_t *total_mem)
+{
+    TS_REQUIRE_INIT();
+    cudaDeviceProp prop;
+    TS_CUDA(cudaGetDeviceProperties(&prop, ctx().device));
+    if (sm_count) *sm_count = prop.multiProcessorCount;
+    if (cc_major) *cc_major = prop.major;
+    if (cc_minor) *cc_minor = prop.minor;
+    if (total_mem) *total_mem = prop.totalGlobalMem;
+    return 0;
+}
+uint64_t tstwo_launch_count(void) { return ctx().launches; }
+
+int tstwo_malloc(uint64_t bytes, tstwo_dptr *out)
+{
+    TS_REQUIRE_INIT();
+    if (!out) return fail(TSTWO_ERR_BAD_ARG, "null out");
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 4);
+    if (e == cudaErrorMemoryAllocation) { cudaGetLastError(); return fail(TSTWO_ERR_OOM, "cudaMalloc(%llu) out of memory", (unsigned long long)bytes); }
+    TS_CUDA(e);
+    *out = (tstwo_dptr)p;
+    return 0;
+}
+int tstwo_free(tstwo_dptr p)
+{
+    TS_REQUIRE_INIT();
+    TS_CUDA(cudaStreamSynchronize(ctx().stream));
+    TS_CUDA(cudaFree((void *)p));
+    return 0;
+}
+int tstwo_memset_zero(tstwo_dptr p, uint64_t bytes)
+{
+    TS_REQUIRE_INIT();
+    TS_CUDA(cudaMemsetAsync((void *)p, 0, bytes, ctx().stream));
+    return 0;
+}
+int tstwo_upload(tstwo_dptr dst, const void *host, uint64_t bytes)
+{
+    TS_REQUIRE_INIT();
+    TS_CUDA(cudaMemcpyAsync((void *)dst, host, bytes, cudaMemcpyHostToDevice, ctx().stream));
+    TS_CUDA(cudaStreamSynchronize(ctx().stream));   // host buffer is borrowed for the call only
+    return 0;
+}
+int tstwo_download(void *host, tstwo_dptr src, uint64_t bytes)
+{
+    TS_REQUIRE_INIT();
+    TS_CUDA(cudaMemcpyAsync(host, (const void *)src, bytes, cudaMemcpyDeviceToHost, ctx().stream));
+    TS_CUDA(cudaStreamSynchronize(ctx().stream));
+    return 0;
+}
+int tstwo_copy(tstwo_dptr dst, tstwo_dptr src, uint64_t bytes)
+{
+    TS_REQUIRE_INIT();
+    TS_CUDA(cudaMemcpyAsync((void *)dst, (const void *)src, bytes, cudaMemcpyDeviceToDevice, ctx().stream));
+    return 0;
+}
+int tstwo_bit_reverse(tstwo_dptr col, uint64_t len)
+{
+    TS_REQUIRE_INIT();
+    if (len == 0 || (len & (len - 1))) return fail(TSTWO_ERR_NOT_POW2, "length is not power of two");
+    int log_n = 0;
+    while ((1ull << log_n) < len) log_n++;
+    if (log_n > 31) return fail(TSTWO_ERR_BAD_ARG, "column too long");
+    TS_LAUNCH(bit_reverse_kernel, (unsigned)((len + 255) / 256), 256, 0, (uint32_t *)col, log_n);
+    return 0;
+}
+
+int tstwo_twiddles_precompute(uint32_t init, int log, tstwo_twiddles *out)
+{
+    TS_REQUIRE_INIT();
+    if (!out || log < 0 || log > 30) return fail(TSTWO_ERR_BAD_ARG, "bad twiddle request (log %d)", log);
+    uint64_t n = 1ull << log;
+    uint32_t *buf = nullptr;
+    cudaError_t e = cudaMalloc(&buf, n * 4 * 4);
+    if (e == cudaErrorMemoryAllocation) { cudaGetLastError(); return fail(TSTWO_ERR_OOM, "twiddle tree out of memory"); }
+    TS_CUDA(e);
+    TwiddleTree *t = new TwiddleTree{ init & 0x7fffffffu, log, buf, buf + n, buf + 2 * n, buf + 3 * n };
+    TS_LAUNCH(twiddle_tree_kernel, (unsigned)((n + 127) / 128), 128, 0, t->tw, t->itw, t->tw2, t->itw2, t->root_init, log);
+    std::lock_guard<std::mutex> lk(g_tree_mu);
+    uint64_t h = g_next_tree++;
+    g_trees[h] = t;
+    *out = h;
+    return 0;
+}
+int tstwo_twiddles_free(tstwo_twiddles h)
+{
+    TS_REQUIRE_INIT();
+    TwiddleTree *t = get_tree(h);
+    if (!t) return fail(TSTWO_ERR_BAD_ARG, "unknown twiddle tree handle");
+    TS_CUDA(cudaStreamSynchronize(ctx().stream));
+    TS_CUDA(cudaFree(t->tw));
+    {
+        std::lock_guard<std::mutex> lk(g_tree_mu);
+        g_trees.erase(h);
+    }
+    delete t;
+    return 0;
+}
+int tstwo_twiddles_info(tstwo_twiddles h, uint32_t *root_init, int *root_log, tstwo_dptr *tw, tstwo_dptr *itw)
+{
+    TS_REQUIRE_INIT();
+    TwiddleTree *t = get_tree(h);
+    if (!t) return fail(TSTWO_ERR_BAD_ARG, "unknown twiddle tree handle");
+    if (root_init) *root_init = t->root_init;
+    if (root_log) *root_log = t->root_log;
+    if (tw) *tw = (tstwo_dptr)t->tw;
+    if (itw) *itw = (tstwo_dptr)t->itw;
+    return 0;
+}
+
+}  // extern "C"

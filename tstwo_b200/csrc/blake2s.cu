@@ -1,0 +1,163 @@
+// Blake2s Merkle layers for sm_100a: MerkleOps.commitOnLayer / MerkleProver.commit of the reference
+// (packages/core/src/vcs/ops.ts:16-26, vcs/prover.ts:13-30) with Blake2sMerkleHasher.hashNode semantics
+// (vcs/blake2_merkle.ts:9-24): node_i = BLAKE2s-256( prev[2i] || prev[2i+1] || LE32(col_0[i]) || LE32(col_1[i]) ... ).
+// The hash itself is plain RFC 7693 BLAKE2s (the reference calls @noble/hashes 1.8.0, vcs/blake2_hash.ts:52-71).
+//
+// One thread per node.  The message words of a node come straight from column-major loads: for a fixed column
+// the 32 lanes of a warp read 32 consecutive rows (128 B, fully coalesced).  Rotations by 16/8 are PRMT, by
+// 12/7 funnel shifts; the ten rounds are fully unrolled with compile-time message schedules.
+#include <vector>
+
+#include "common.cuh"
+
+namespace tstwo {
+
+__device__ __forceinline__ uint32_t rotr16(uint32_t x) { return __byte_perm(x, x, 0x1032); }
+__device__ __forceinline__ uint32_t rotr8(uint32_t x) { return __byte_perm(x, x, 0x0321); }
+__device__ __forceinline__ uint32_t rotr12(uint32_t x) { return __funnelshift_r(x, x, 12); }
+__device__ __forceinline__ uint32_t rotr7(uint32_t x) { return __funnelshift_r(x, x, 7); }
+
+#define B2S_G(a, b, c, d, x, y)                                     \
+    do {                                                            \
+        a = a + b + (x); d = rotr16(d ^ a); c = c + d; b = rotr12(b ^ c); \
+        a = a + b + (y); d = rotr8(d ^ a);  c = c + d; b = rotr7(b ^ c);  \
+    } while (0)
+
+#define B2S_ROUND(s0, s1, s2, s3, s4, s5, s6, s7, s8, s9, s10, s11, s12, s13, s14, s15) \
+    do {                                                                                  \
+        B2S_G(v0, v4, v8, v12, m[s0], m[s1]);   B2S_G(v1, v5, v9, v13, m[s2], m[s3]);     \
+        B2S_G(v2, v6, v10, v14, m[s4], m[s5]);  B2S_G(v3, v7, v11, v15, m[s6], m[s7]);    \
+        B2S_G(v0, v5, v10, v15, m[s8], m[s9]);  B2S_G(v1, v6, v11, v12, m[s10], m[s11]);  \
+        B2S_G(v2, v7, v8, v13, m[s12], m[s13]); B2S_G(v3, v4, v9, v14, m[s14], m[s15]);   \
+    } while (0)
+
+// one compression; t = byte counter (< 2^32 on this path), last = final-block flag
+__device__ __forceinline__ void b2s_compress(uint32_t (&h)[8], const uint32_t (&m)[16], uint32_t t, bool last)
+{
+    uint32_t v0 = h[0], v1 = h[1], v2 = h[2], v3 = h[3], v4 = h[4], v5 = h[5], v6 = h[6], v7 = h[7];
+    uint32_t v8 = 0x6A09E667u, v9 = 0xBB67AE85u, v10 = 0x3C6EF372u, v11 = 0xA54FF53Au;
+    uint32_t v12 = 0x510E527Fu ^ t, v13 = 0x9B05688Cu, v14 = last ? ~0x1F83D9ABu : 0x1F83D9ABu, v15 = 0x5BE0CD19u;
+    B2S_ROUND(0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15);
+    B2S_ROUND(14, 10, 4, 8, 9, 15, 13, 6, 1, 12, 0, 2, 11, 7, 5, 3);
+    B2S_ROUND(11, 8, 12, 0, 5, 2, 15, 13, 10, 14, 3, 6, 7, 1, 9, 4);
+    B2S_ROUND(7, 9, 3, 1, 13, 12, 11, 14, 2, 6, 5, 10, 4, 0, 15, 8);
+    B2S_ROUND(9, 0, 5, 7, 2, 4, 10, 15, 14, 1, 11, 12, 6, 8, 3, 13);
+    B2S_ROUND(2, 12, 6, 10, 0, 11, 8, 3, 4, 13, 7, 5, 15, 14, 1, 9);
+    B2S_ROUND(12, 5, 1, 15, 14, 13, 4, 10, 0, 7, 6, 3, 9, 2, 8, 11);
+    B2S_ROUND(13, 11, 7, 14, 12, 1, 3, 9, 5, 0, 15, 4, 8, 6, 2, 10);
+    B2S_ROUND(6, 15, 14, 9, 11, 3, 0, 8, 12, 2, 13, 7, 1, 4, 10, 5);
+    B2S_ROUND(10, 2, 8, 4, 7, 6, 1, 5, 15, 11, 9, 14, 3, 12, 13, 0);
+    h[0] ^= v0 ^ v8;  h[1] ^= v1 ^ v9;  h[2] ^= v2 ^ v10; h[3] ^= v3 ^ v11;
+    h[4] ^= v4 ^ v12; h[5] ^= v5 ^ v13; h[6] ^= v6 ^ v14; h[7] ^= v7 ^ v15;
+}
+
+__device__ __forceinline__ void b2s_init(uint32_t (&h)[8])
+{
+    h[0] = 0x6A09E667u ^ 0x01010020u; h[1] = 0xBB67AE85u; h[2] = 0x3C6EF372u; h[3] = 0xA54FF53Au;
+    h[4] = 0x510E527Fu; h[5] = 0x9B05688Cu; h[6] = 0x1F83D9ABu; h[7] = 0x5BE0CD19u;
+}
+
+// HAS_PREV: the first 16 message words are the two child hashes.
+template <bool HAS_PREV>
+__global__ void __launch_bounds__(256) merkle_layer_kernel(const uint4 *__restrict__ prev, ColSet cols, int n_cols,
+                                                           uint64_t n_nodes, uint4 *__restrict__ out)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    uint32_t h[8], m[16];
+    b2s_init(h);
+    const uint32_t total_words = (HAS_PREV ? 16u : 0u) + (uint32_t)n_cols;
+    uint32_t done = 0;   // words consumed
+    if (HAS_PREV) {
+        const uint4 *p = prev + 4 * i;   // 64 bytes = children 2i, 2i+1
+        uint4 a = __ldcs(p), b = __ldcs(p + 1), c = __ldcs(p + 2), d = __ldcs(p + 3);
+        m[0] = a.x; m[1] = a.y; m[2] = a.z; m[3] = a.w; m[4] = b.x; m[5] = b.y; m[6] = b.z; m[7] = b.w;
+        m[8] = c.x; m[9] = c.y; m[10] = c.z; m[11] = c.w; m[12] = d.x; m[13] = d.y; m[14] = d.z; m[15] = d.w;
+        done = 16;
+        if (n_cols == 0) {
+            b2s_compress(h, m, 64u, true);
+        } else {
+            b2s_compress(h, m, 64u, false);
+        }
+    }
+    if (!HAS_PREV || n_cols > 0) {
+        int c = 0;
+        // full, non-final blocks of 16 columns
+        while (n_cols - c > 16) {
+#pragma unroll
+            for (int k = 0; k < 16; k++) m[k] = __ldcs(cols.col(c + k) + i);
+            c += 16; done += 16;
+            b2s_compress(h, m, done * 4u, false);
+        }
+        // final block: 0..16 remaining columns, zero padded
+#pragma unroll
+        for (int k = 0; k < 16; k++) m[k] = (c + k < n_cols) ? __ldcs(cols.col(c + k) + i) : 0u;
+        b2s_compress(h, m, total_words * 4u, true);
+    }
+    out[2 * i] = make_uint4(h[0], h[1], h[2], h[3]);
+    out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
+}
+
+int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, int n_cols, uint8_t *out)
+{
+    const uint64_t n = 1ull << log_size;
+    const unsigned block = 256;
+    const unsigned grid = (unsigned)((n + block - 1) / block);
+    if (prev) TS_LAUNCH((merkle_layer_kernel<true>), grid, block, 0, (const uint4 *)prev, cols, n_cols, n, (uint4 *)out);
+    else TS_LAUNCH((merkle_layer_kernel<false>), grid, block, 0, (const uint4 *)nullptr, cols, n_cols, n, (uint4 *)out);
+    return 0;
+}
+
+}  // namespace tstwo
+
+using namespace tstwo;
+
+extern "C" {
+
+int tstwo_merkle_commit_layer(int log_size, tstwo_dptr prev_layer, const tstwo_dptr *cols, int n_cols, tstwo_dptr out_layer)
+{
+    TS_REQUIRE_INIT();
+    if (log_size < 0 || log_size > 31 || n_cols < 0 || !out_layer) return fail(TSTWO_ERR_BAD_ARG, "bad commit_layer arguments");
+    ColSet cs;
+    int rc = make_colset(cols, n_cols, 0, &cs);
+    if (rc) return rc;
+    return merkle_commit_layer(log_size, (const uint8_t *)prev_layer, cs, n_cols, (uint8_t *)out_layer);
+}
+
+int tstwo_merkle_commit(const tstwo_dptr *cols, const int *col_logs, int n_cols, tstwo_dptr layers, uint8_t root[32])
+{
+    TS_REQUIRE_INIT();
+    if (n_cols < 0 || !layers) return fail(TSTWO_ERR_BAD_ARG, "bad merkle_commit arguments");
+    uint8_t *base = (uint8_t *)layers;
+    if (n_cols == 0) {
+        ColSet none = { nullptr, 0, nullptr };
+        int rc = merkle_commit_layer(0, nullptr, none, 0, base);   // vcs/prover.ts:17-19
+        if (rc) return rc;
+    } else {
+        int max_log = 0;
+        for (int c = 0; c < n_cols; c++) {
+            if (col_logs[c] < 0 || col_logs[c] > 31) return fail(TSTWO_ERR_NOT_POW2, "column length is not a power of two");
+            if (col_logs[c] > max_log) max_log = col_logs[c];
+        }
+        std::vector<tstwo_dptr> layer_cols((size_t)n_cols);
+        const uint8_t *prev = nullptr;
+        for (int log = max_log; log >= 0; log--) {
+            int k = 0;   // stable order among equal lengths (vcs/prover.ts:21,25)
+            for (int c = 0; c < n_cols; c++) if (col_logs[c] == log) layer_cols[k++] = cols[c];
+            ColSet cs;
+            int rc = make_colset(layer_cols.data(), k, (max_log - log) & 1, &cs);
+            if (rc) return rc;
+            uint8_t *dst = base + 32ull * ((1ull << log) - 1);
+            rc = merkle_commit_layer(log, prev, cs, k, dst);
+            if (rc) return rc;
+            prev = dst;
+        }
+    }
+    if (root) {
+        TS_CUDA(cudaMemcpyAsync(root, base, 32, cudaMemcpyDeviceToHost, ctx().stream));
+        TS_CUDA(cudaStreamSynchronize(ctx().stream));
+    }
+    return 0;
+}
+
+}  // extern "C"

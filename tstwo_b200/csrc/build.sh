@@ -1,0 +1,18 @@
+#!/bin/bash
+# Builds libtstwo_cuda.so for sm_100a in-tree (the .so travels to the GPU box with the snapshot).
+set -e
+cd "$(dirname "$0")"
+OUT=../libtstwo_cuda.so
+NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
+FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -ccbin /usr/bin/g++"
+mkdir -p _obj
+pids=()
+for f in abi_core fft blake2s elementwise pipeline; do
+  if [ ! -f _obj/$f.o ] || [ $f.cu -nt _obj/$f.o ] || [ -n "$(find . -maxdepth 1 \( -name '*.cuh' -o -name '*.h' \) -newer _obj/$f.o 2>/dev/null)" ] || [ ../../include/tstwo_cuda.h -nt _obj/$f.o ]; then
+    $NVCC $FLAGS -c $f.cu -o _obj/$f.o &
+    pids+=($!)
+  fi
+done
+for p in "${pids[@]}"; do wait $p; done
+$NVCC -gencode arch=compute_100a,code=sm_100a -shared -ccbin /usr/bin/g++ -o $OUT _obj/*.o -lcudart
+echo "built $OUT"

@@ -1,0 +1,87 @@
+// Shared host-side plumbing for libtstwo_cuda.so: context, error slot, launch accounting.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "../../include/tstwo_cuda.h"
+
+namespace tstwo {
+
+struct Context {
+    bool ready = false;
+    int device = -1;
+    int sm_count = 0;
+    cudaStream_t own_stream = nullptr;   // library stream
+    cudaStream_t stream = nullptr;       // stream in use (own_stream or caller's)
+    cudaStream_t copy_stream = nullptr;  // H2D pipeline for tstwo_lde_commit_host
+    uint64_t launches = 0;
+    // small device scratch for pointer tables / parameters
+    uint64_t *d_ptr_table = nullptr;
+    size_t ptr_table_cap = 0;
+};
+
+Context &ctx();
+int fail(int code, const char *fmt, ...);
+
+#define TS_CUDA(expr)                                                                              \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess)                                                                     \
+            return ::tstwo::fail(TSTWO_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), \
+                                 __FILE__, __LINE__);                                              \
+    } while (0)
+
+#define TS_REQUIRE_INIT()                                                                          \
+    do {                                                                                           \
+        if (!::tstwo::ctx().ready) return ::tstwo::fail(TSTWO_ERR_NOT_INIT, "tstwo_init() has not been called"); \
+    } while (0)
+
+// every kernel launch goes through this so tstwo_launch_count() is exact
+#define TS_LAUNCH(kernel, grid, block, smem, ...)                                                  \
+    do {                                                                                           \
+        kernel<<<(grid), (block), (smem), ::tstwo::ctx().stream>>>(__VA_ARGS__);                   \
+        ::tstwo::ctx().launches++;                                                                 \
+        cudaError_t _e = cudaGetLastError();                                                       \
+        if (_e != cudaSuccess)                                                                     \
+            return ::tstwo::fail(TSTWO_ERR_CUDA, "launch %s failed: %s (%s:%d)", #kernel,          \
+                                 cudaGetErrorString(_e), __FILE__, __LINE__);                      \
+    } while (0)
+
+// Column address list: either uniform stride (base + c*stride words) or a device table of addresses.
+struct ColSet {
+    const uint32_t *base;       // used when table == nullptr
+    uint64_t stride;            // words
+    const uint64_t *table;      // device array of addresses, or nullptr
+    __host__ __device__ __forceinline__ uint32_t *col(int c) const
+    {
+        return table ? reinterpret_cast<uint32_t *>(table[c]) : const_cast<uint32_t *>(base) + (uint64_t)c * stride;
+    }
+};
+// Builds a ColSet from a host array of device addresses; uploads a table only when the stride is not uniform.
+// `slot` selects one of several independent table regions (so src and dst sets can coexist in one launch).
+int make_colset(const tstwo_dptr *cols, int n_cols, int slot, ColSet *out);
+
+// ---- twiddle trees ----
+struct TwiddleTree {
+    uint32_t root_init;
+    int root_log;
+    uint32_t *tw, *itw;      // reference layout (backend/cpu/circle.ts:210-239), 2^root_log words each
+    uint32_t *tw2, *itw2;    // the same tables pre-doubled (2*t), consumed by the butterfly kernels
+};
+TwiddleTree *get_tree(tstwo_twiddles h);
+// is `half coset (init, log)` a repeated doubling of the tree root?  (circle.ts:264-266)
+bool is_doubling_of(uint32_t init, int log, const TwiddleTree *t);
+
+// kernels implemented in the other translation units (host launchers)
+// out2[i] = 2 / coord(init + bitrev(i, m) * subgroup_gen(step_log)), i < 2^m; which: 0 = x, 1 = y
+int launch_coset_points(uint32_t *out2, int which, uint32_t init, int step_log, int m);
+cudaError_t elementwise_init();   // per-TU constant tables of elementwise.cu
+int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int log_size, const TwiddleTree *t, uint32_t flags);
+int fft_evaluate(const ColSet &src, int poly_log, const ColSet &dst, int n_cols, int domain_log, const TwiddleTree *t,
+                 uint32_t flags);
+int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, int n_cols, uint8_t *out);
+
+}  // namespace tstwo

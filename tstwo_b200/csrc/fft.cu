@@ -1,0 +1,470 @@
+// Circle-domain FFT / iFFT over M31 for sm_100a: CpuCirclePoly.interpolate / evaluate of the reference
+// (packages/core/src/backend/cpu/circle.ts:84-207) as radix-2^11 tiled passes.
+//
+// Layer i of a domain of log size n pairs indices differing in bit i; block h = idx >> (i+1) uses twiddle
+//   T_i[h], T_i = tree[2^root_log - 2^(n-i) ..)  for i >= 1   (poly/utils.ts:78-99 slices from the END of the tree)
+//   circle layer 0: +-T_1[(h>>1)^1]  with sign = bit0(h ^ (h>>1))  (circle.ts:270-278: [y,-y,-x,x])
+// A pass loads a tile of 2^11 "rows" (index bits [lo, lo+11)) x 8 "lanes" into registers/shared memory and
+// runs up to 11 layers on it in three register-resident radix-16 stages (row bits 10..7, 6..3, 3..0), exchanging
+// through a padded shared-memory tile of uint4 units between stages.  Lanes are either 8 different columns
+// (contiguous pass, lo = 0) or the 8 lowest index bits of one column (strided pass, lo >= 3), so every twiddle a
+// thread loads is reused by 4 butterflies.  All twiddles are read pre-doubled (m31::mul2).
+#include "common.cuh"
+#include "host_m31.h"
+#include "m31.cuh"
+
+namespace tstwo {
+
+constexpr int W = 11;
+constexpr int TILE_ROWS = 1 << W;
+constexpr int PASS_THREADS = 256;
+constexpr int SMEM_UNITS = 2 * TILE_ROWS + 2 * (TILE_ROWS / 16);
+constexpr int SMEM_BYTES = SMEM_UNITS * 16;
+constexpr int FAST_MIN_LOG = 14;
+
+struct PassParams {
+    ColSet src, dst;
+    int n_cols;
+    int n;                 // log size of the index space of dst
+    uint32_t src_mask;     // src index = idx & src_mask (coset replication of zero-extended coefficients)
+    int lo;                // window = index bits [lo, lo+W)
+    int j_min;             // relative layers j in [j_min, W) are applied
+    const uint32_t *tw2;   // pre-doubled twiddle (or inverse twiddle) tree
+    uint32_t tree_len;     // 2^root_log
+    uint32_t scale2;       // 2/2^n after the last inverse layer, or 0
+};
+
+__device__ __forceinline__ void load_tw(const uint32_t *p, int cnt, uint32_t (&t)[8])
+{
+    if (cnt == 8) {
+        uint4 a = __ldg(reinterpret_cast<const uint4 *>(p)), b = __ldg(reinterpret_cast<const uint4 *>(p) + 1);
+        t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w;
+    } else if (cnt == 4) {
+        uint4 a = __ldg(reinterpret_cast<const uint4 *>(p));
+        t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w;
+    } else if (cnt == 2) {
+        uint2 a = __ldg(reinterpret_cast<const uint2 *>(p));
+        t[0] = a.x; t[1] = a.y;
+    } else t[0] = __ldg(p);
+}
+
+// One radix-16 stage on v[16][4]: digit bit k <-> row bit S+k, layers j = S+k for k in [0, NL).
+template <int S, int NL, bool INV>
+__device__ __forceinline__ void stage(uint32_t (&v)[16][4], const PassParams &p, uint32_t tile_hi, int rbase)
+{
+#pragma unroll
+    for (int kk = 0; kk < NL; kk++) {
+        const int k = INV ? kk : NL - 1 - kk;
+        const int j = S + k;
+        if (j < p.j_min) continue;                     // uniform across the grid
+        const int i = p.lo + j;                        // absolute layer
+        const int cnt = 8 >> k;
+        uint32_t t[8];
+        const uint32_t hb = (tile_hi << (W - 1 - j)) | ((uint32_t)rbase >> (j + 1));
+        if (i >= 1) {
+            load_tw(p.tw2 + (p.tree_len - (1u << (p.n - i))) + hb, cnt, t);
+        } else {
+            // circle layer: j == 0, k == 0, cnt == 8; T_1 entries hb/2 .. hb/2+3 = (x0, y0, x1, y1)
+            uint4 a = __ldg(reinterpret_cast<const uint4 *>(p.tw2 + (p.tree_len - (1u << (p.n - 1))) + (hb >> 1)));
+            const uint32_t P2 = 0xfffffffeu;
+            t[0] = a.y; t[1] = P2 - a.y; t[2] = P2 - a.x; t[3] = a.x;
+            t[4] = a.w; t[5] = P2 - a.w; t[6] = P2 - a.z; t[7] = a.z;
+        }
+#pragma unroll
+        for (int d = 0; d < 16; d++) {
+            if (d & (1 << k)) continue;
+            const uint32_t tw = t[d >> (k + 1)];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                if (INV) m31::ibutterfly(v[d][q], v[d | (1 << k)][q], tw);
+                else m31::butterfly(v[d][q], v[d | (1 << k)][q], tw);
+            }
+        }
+    }
+}
+
+enum { MAP_A = 0, MAP_B = 1, MAP_C = 2 };
+template <int MAP> __device__ __forceinline__ int map_rbase(int rg)
+{
+    return MAP == MAP_A ? rg : MAP == MAP_B ? ((rg >> 3) * 128 + (rg & 7)) : rg * 16;
+}
+template <int MAP> __device__ __forceinline__ int map_row(int rbase, int d)
+{
+    return MAP == MAP_A ? rbase + d * 128 : MAP == MAP_B ? rbase + d * 8 : rbase + d;
+}
+// shared-memory unit (16 B) of (row r, half): half + 2r + 2(r>>4); conflict-free for all three maps
+template <int MAP> __device__ __forceinline__ int map_unit0(int rg, int half)
+{
+    const int r = map_rbase<MAP>(rg);
+    return half + 2 * r + 2 * (r >> 4);
+}
+template <int MAP> __device__ __forceinline__ constexpr int map_unit_off(int d)
+{
+    return MAP == MAP_A ? d * 272 : MAP == MAP_B ? 16 * d + 2 * (d >> 1) : 2 * d;
+}
+template <int MAP> __device__ __forceinline__ void smem_store(uint4 *sm, int u0, const uint32_t (&v)[16][4])
+{
+#pragma unroll
+    for (int d = 0; d < 16; d++) sm[u0 + map_unit_off<MAP>(d)] = make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]);
+}
+template <int MAP> __device__ __forceinline__ void smem_load(const uint4 *sm, int u0, uint32_t (&v)[16][4])
+{
+#pragma unroll
+    for (int d = 0; d < 16; d++) {
+        uint4 a = sm[u0 + map_unit_off<MAP>(d)];
+        v[d][0] = a.x; v[d][1] = a.y; v[d][2] = a.z; v[d][3] = a.w;
+    }
+}
+
+// global I/O.  STRIDED: lanes = index bits [0,3) of one column (blockIdx.y); CONTIG: lanes = 8 columns.
+template <int MAP, bool STRIDED>
+__device__ __forceinline__ void gmem_load(const PassParams &p, uint32_t tile_hi, uint32_t mid, int rbase, int half,
+                                          uint32_t (&v)[16][4])
+{
+    if (STRIDED) {
+        const uint32_t *col = p.src.col(blockIdx.y);
+        const uint32_t fixed = (tile_hi << (p.lo + W)) | (mid << 3) | (half << 2);
+#pragma unroll
+        for (int d = 0; d < 16; d++) {
+            uint32_t idx = (fixed | ((uint32_t)map_row<MAP>(rbase, d) << p.lo)) & p.src_mask;
+            uint4 a = __ldcg(reinterpret_cast<const uint4 *>(col + idx));
+            v[d][0] = a.x; v[d][1] = a.y; v[d][2] = a.z; v[d][3] = a.w;
+        }
+    } else {
+        const int c0 = blockIdx.y * 8 + half * 4;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            if (c0 + q < p.n_cols) {
+                const uint32_t *col = p.src.col(c0 + q);
+                if (MAP == MAP_C) {
+                    const uint32_t idx = ((tile_hi << W) | (uint32_t)rbase) & p.src_mask;
+#pragma unroll
+                    for (int dd = 0; dd < 4; dd++) {
+                        uint4 a = __ldg(reinterpret_cast<const uint4 *>(col + idx + 4 * dd));
+                        v[4 * dd][q] = a.x; v[4 * dd + 1][q] = a.y; v[4 * dd + 2][q] = a.z; v[4 * dd + 3][q] = a.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int d = 0; d < 16; d++)
+                        v[d][q] = __ldcg(col + (((tile_hi << W) | (uint32_t)map_row<MAP>(rbase, d)) & p.src_mask));
+                }
+            } else {
+#pragma unroll
+                for (int d = 0; d < 16; d++) v[d][q] = 0;
+            }
+        }
+    }
+}
+template <int MAP, bool STRIDED>
+__device__ __forceinline__ void gmem_store(const PassParams &p, uint32_t tile_hi, uint32_t mid, int rbase, int half,
+                                           const uint32_t (&v)[16][4])
+{
+    if (STRIDED) {
+        uint32_t *col = p.dst.col(blockIdx.y);
+        const uint32_t fixed = (tile_hi << (p.lo + W)) | (mid << 3) | (half << 2);
+#pragma unroll
+        for (int d = 0; d < 16; d++) {
+            uint32_t idx = fixed | ((uint32_t)map_row<MAP>(rbase, d) << p.lo);
+            __stcg(reinterpret_cast<uint4 *>(col + idx), make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]));
+        }
+    } else {
+        const int c0 = blockIdx.y * 8 + half * 4;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            if (c0 + q < p.n_cols) {
+                uint32_t *col = p.dst.col(c0 + q);
+                if (MAP == MAP_C) {
+                    const uint32_t idx = (tile_hi << W) | (uint32_t)rbase;
+#pragma unroll
+                    for (int dd = 0; dd < 4; dd++)
+                        __stcg(reinterpret_cast<uint4 *>(col + idx + 4 * dd),
+                               make_uint4(v[4 * dd][q], v[4 * dd + 1][q], v[4 * dd + 2][q], v[4 * dd + 3][q]));
+                } else {
+#pragma unroll
+                    for (int d = 0; d < 16; d++) __stcg(col + ((tile_hi << W) | (uint32_t)map_row<MAP>(rbase, d)), v[d][q]);
+                }
+            }
+        }
+    }
+}
+
+template <bool INV, bool STRIDED>
+__global__ void __launch_bounds__(PASS_THREADS, 2) fft_pass_kernel(const PassParams p)
+{
+    extern __shared__ uint4 sm[];
+    const int tid = threadIdx.x, half = tid & 1, rg = tid >> 1;
+    uint32_t tile_hi, mid;
+    if (STRIDED) {
+        tile_hi = blockIdx.x >> (p.lo - 3);
+        mid = blockIdx.x & ((1u << (p.lo - 3)) - 1);
+    } else {
+        tile_hi = blockIdx.x;
+        mid = 0;
+    }
+    uint32_t v[16][4];
+    const int rA = map_rbase<MAP_A>(rg), rB = map_rbase<MAP_B>(rg), rC = map_rbase<MAP_C>(rg);
+    const int uA = map_unit0<MAP_A>(rg, half), uB = map_unit0<MAP_B>(rg, half), uC = map_unit0<MAP_C>(rg, half);
+    if (!INV) {
+        gmem_load<MAP_A, STRIDED>(p, tile_hi, mid, rA, half, v);
+        stage<7, 4, false>(v, p, tile_hi, rA);
+        smem_store<MAP_A>(sm, uA, v);
+        __syncthreads();
+        smem_load<MAP_B>(sm, uB, v);
+        stage<3, 4, false>(v, p, tile_hi, rB);
+        smem_store<MAP_B>(sm, uB, v);
+        __syncthreads();
+        smem_load<MAP_C>(sm, uC, v);
+        stage<0, 3, false>(v, p, tile_hi, rC);
+        gmem_store<MAP_C, STRIDED>(p, tile_hi, mid, rC, half, v);
+    } else {
+        gmem_load<MAP_C, STRIDED>(p, tile_hi, mid, rC, half, v);
+        stage<0, 3, true>(v, p, tile_hi, rC);
+        smem_store<MAP_C>(sm, uC, v);
+        __syncthreads();
+        smem_load<MAP_B>(sm, uB, v);
+        stage<3, 4, true>(v, p, tile_hi, rB);
+        smem_store<MAP_B>(sm, uB, v);
+        __syncthreads();
+        smem_load<MAP_A>(sm, uA, v);
+        stage<7, 4, true>(v, p, tile_hi, rA);
+        if (p.scale2) {
+#pragma unroll
+            for (int d = 0; d < 16; d++)
+#pragma unroll
+                for (int q = 0; q < 4; q++) v[d][q] = m31::mul2(v[d][q], p.scale2);
+        }
+        gmem_store<MAP_A, STRIDED>(p, tile_hi, mid, rA, half, v);
+    }
+}
+
+// ---------------------------------------------------------------- naive per-layer kernels (any size; used for
+// log sizes below FAST_MIN_LOG and as the on-device cross-check of the tiled passes)
+__global__ void fft_layer_kernel(ColSet cols, int n, int i, const uint32_t *tw2, uint32_t tree_len, int inverse)
+{
+    uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >> (n - 1)) return;
+    uint32_t *v = cols.col(blockIdx.y);
+    uint32_t h = (uint32_t)(b >> i), l = (uint32_t)b & ((1u << i) - 1);
+    uint32_t i0 = (h << (i + 1)) + l, i1 = i0 + (1u << i);
+    uint32_t t;
+    if (i >= 1) t = tw2[tree_len - (1u << (n - i)) + h];
+    else {
+        t = tw2[tree_len - (1u << (n - 1)) + ((h >> 1) ^ 1)];
+        if ((h ^ (h >> 1)) & 1) t = 0xfffffffeu - t;
+    }
+    uint32_t a = v[i0], c = v[i1];
+    if (inverse) m31::ibutterfly(a, c, t); else m31::butterfly(a, c, t);
+    v[i0] = a; v[i1] = c;
+}
+__global__ void scale_kernel(ColSet cols, int n, uint32_t scale2)
+{
+    uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >> n) return;
+    uint32_t *v = cols.col(blockIdx.y);
+    v[e] = m31::mul2(v[e], scale2);
+}
+// dst[e] = e < 2^poly_log ? src[e] : 0   (CpuCirclePoly.extend, circle.ts:71-82)
+__global__ void extend_kernel(ColSet src, ColSet dst, int poly_log, int n)
+{
+    uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >> n) return;
+    dst.col(blockIdx.y)[e] = (e >> poly_log) ? 0u : src.col(blockIdx.y)[e];
+}
+__global__ void copy_cols_kernel(ColSet src, ColSet dst, int n)
+{
+    uint64_t e = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >> n) return;
+    dst.col(blockIdx.y)[e] = src.col(blockIdx.y)[e];
+}
+__global__ void swap57_kernel(ColSet cols)
+{
+    uint32_t *v = cols.col(blockIdx.x);
+    uint32_t t = v[5]; v[5] = v[7]; v[7] = t;
+}
+// closed forms for log 1 and 2 (circle.ts:93-110, 153-185); x, y = half coset initial point, pre-doubled factors
+__global__ void small_eval_kernel(ColSet cols, int n, uint32_t x2, uint32_t y2, uint32_t ny2)
+{
+    uint32_t *v = cols.col(blockIdx.x);
+    if (n == 1) { uint32_t a = v[0], b = v[1]; m31::butterfly(a, b, y2); v[0] = a; v[1] = b; return; }
+    uint32_t v0 = v[0], v1 = v[1], v2 = v[2], v3 = v[3];
+    m31::butterfly(v0, v2, x2); m31::butterfly(v1, v3, x2);
+    m31::butterfly(v0, v1, y2); m31::butterfly(v2, v3, ny2);
+    v[0] = v0; v[1] = v1; v[2] = v2; v[3] = v3;
+}
+__global__ void small_interp_kernel(ColSet cols, int n, uint32_t xi2, uint32_t yi2, uint32_t nyi2, uint32_t ninv2)
+{
+    uint32_t *v = cols.col(blockIdx.x);
+    if (n == 1) {
+        uint32_t a = v[0], b = v[1];
+        m31::ibutterfly(a, b, yi2);
+        v[0] = m31::mul2(a, ninv2); v[1] = m31::mul2(b, ninv2);
+        return;
+    }
+    uint32_t v0 = v[0], v1 = v[1], v2 = v[2], v3 = v[3];
+    m31::ibutterfly(v0, v1, yi2); m31::ibutterfly(v2, v3, nyi2);
+    m31::ibutterfly(v0, v2, xi2); m31::ibutterfly(v1, v3, xi2);
+    v[0] = m31::mul2(v0, ninv2); v[1] = m31::mul2(v1, ninv2); v[2] = m31::mul2(v2, ninv2); v[3] = m31::mul2(v3, ninv2);
+}
+
+static bool g_force_naive = false;
+static bool g_smem_attr_set = false;
+
+static int ensure_smem_attr()
+{
+    if (g_smem_attr_set) return 0;
+    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    g_smem_attr_set = true;
+    return 0;
+}
+
+struct Pass { int lo, j_min; };
+// passes in ascending layer order for L real layers (see scripts/proto_fft.py)
+static int plan_passes(int L, Pass out[3])
+{
+    if (L <= 22) { out[0] = { 0, 0 }; out[1] = { L - W, 2 * W - L }; return 2; }
+    out[0] = { 0, 0 }; out[1] = { W, 0 }; out[2] = { L - W, 3 * W - L };
+    return 3;
+}
+
+static int launch_pass(bool inverse, const PassParams &p)
+{
+    if (p.lo == 0) {
+        dim3 grid(1u << (p.n - W), (unsigned)((p.n_cols + 7) / 8));
+        if (inverse) TS_LAUNCH((fft_pass_kernel<true, false>), grid, PASS_THREADS, SMEM_BYTES, p);
+        else TS_LAUNCH((fft_pass_kernel<false, false>), grid, PASS_THREADS, SMEM_BYTES, p);
+    } else {
+        dim3 grid(1u << (p.n - W - 3), (unsigned)p.n_cols);
+        if (inverse) TS_LAUNCH((fft_pass_kernel<true, true>), grid, PASS_THREADS, SMEM_BYTES, p);
+        else TS_LAUNCH((fft_pass_kernel<false, true>), grid, PASS_THREADS, SMEM_BYTES, p);
+    }
+    return 0;
+}
+
+static uint32_t dbl(uint32_t v) { return v + v; }
+
+int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int n, const TwiddleTree *t, uint32_t flags)
+{
+    if (n_cols <= 0) return 0;
+    const uint32_t tree_len = 1u << t->root_log;
+    const uint64_t N = 1ull << n;
+    const bool in_place = (src.base == dst.base && src.table == dst.table && src.stride == dst.stride);
+    const uint32_t inv_n2 = dbl(host::inv((uint32_t)(N % host::P)));
+    if (n >= FAST_MIN_LOG && !g_force_naive) {
+        int rc = ensure_smem_attr();
+        if (rc) return rc;
+        Pass ps[3];
+        int np = plan_passes(n, ps);
+        for (int k = 0; k < np; k++) {
+            PassParams p;
+            p.src = (k == 0) ? src : dst; p.dst = dst; p.n_cols = n_cols; p.n = n; p.src_mask = (uint32_t)(N - 1);
+            p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.tw2 = t->itw2; p.tree_len = tree_len;
+            p.scale2 = (k == np - 1) ? inv_n2 : 0;
+            rc = launch_pass(true, p);
+            if (rc) return rc;
+        }
+        return 0;
+    }
+    dim3 egrid((unsigned)((N + 255) / 256), (unsigned)n_cols);
+    if (!in_place) TS_LAUNCH(copy_cols_kernel, egrid, 256, 0, src, dst, n);
+    if ((flags & TSTWO_FLAG_QUIRKS) && n == 3) TS_LAUNCH(swap57_kernel, n_cols, 1, 0, dst);
+    if (n <= 2) {
+        // circle.ts:153-185
+        uint32_t half_init = (t->root_init << (t->root_log - (n - 1))) & 0x7fffffffu;
+        host::Pt ip = host::index_to_point(half_init);
+        uint32_t xi = n == 2 ? host::inv(ip.x) : 0, yi = host::inv(ip.y);
+        TS_LAUNCH(small_interp_kernel, n_cols, 1, 0, dst, n, dbl(xi), dbl(yi), dbl(host::neg(yi)), inv_n2);
+        return 0;
+    }
+    dim3 bgrid((unsigned)((N / 2 + 255) / 256), (unsigned)n_cols);
+    for (int i = 0; i < n; i++) TS_LAUNCH(fft_layer_kernel, bgrid, 256, 0, dst, n, i, t->itw2, tree_len, 1);
+    TS_LAUNCH(scale_kernel, egrid, 256, 0, dst, n, inv_n2);
+    return 0;
+}
+
+int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n, const TwiddleTree *t, uint32_t flags)
+{
+    if (n_cols <= 0) return 0;
+    const uint32_t tree_len = 1u << t->root_log;
+    const uint64_t N = 1ull << n;
+    if (L >= FAST_MIN_LOG && !g_force_naive) {
+        int rc = ensure_smem_attr();
+        if (rc) return rc;
+        Pass ps[3];
+        int np = plan_passes(L, ps);
+        for (int k = np - 1; k >= 0; k--) {
+            PassParams p;
+            const bool first = (k == np - 1);
+            p.src = first ? src : dst; p.dst = dst; p.n_cols = n_cols; p.n = n;
+            p.src_mask = first ? (uint32_t)((1ull << L) - 1) : (uint32_t)(N - 1);
+            p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.tw2 = t->tw2; p.tree_len = tree_len; p.scale2 = 0;
+            rc = launch_pass(false, p);
+            if (rc) return rc;
+        }
+        return 0;
+    }
+    dim3 egrid((unsigned)((N + 255) / 256), (unsigned)n_cols);
+    const bool in_place = (src.base == dst.base && src.table == dst.table && src.stride == dst.stride);
+    if (!(in_place && L == n)) TS_LAUNCH(extend_kernel, egrid, 256, 0, src, dst, L, n);
+    if (n <= 2) {
+        uint32_t half_init = (t->root_init << (t->root_log - (n - 1))) & 0x7fffffffu;
+        host::Pt ip = host::index_to_point(half_init);
+        TS_LAUNCH(small_eval_kernel, n_cols, 1, 0, dst, n, dbl(ip.x), dbl(ip.y), dbl(host::neg(ip.y)));
+        return 0;
+    }
+    dim3 bgrid((unsigned)((N / 2 + 255) / 256), (unsigned)n_cols);
+    for (int i = n - 1; i >= 0; i--) TS_LAUNCH(fft_layer_kernel, bgrid, 256, 0, dst, n, i, t->tw2, tree_len, 0);
+    if ((flags & TSTWO_FLAG_QUIRKS) && n == 3) TS_LAUNCH(swap57_kernel, n_cols, 1, 0, dst);
+    return 0;
+}
+
+}  // namespace tstwo
+
+using namespace tstwo;
+
+extern "C" {
+
+// test hook: force the per-layer kernels for every size (used by tests to cross-check the tiled passes on device)
+int tstwo_debug_force_naive_fft(int on) { g_force_naive = on != 0; return 0; }
+
+static int check_tree(tstwo_twiddles h, uint32_t half_init, int half_log, TwiddleTree **out)
+{
+    TwiddleTree *t = get_tree(h);
+    if (!t) return fail(TSTWO_ERR_BAD_ARG, "unknown twiddle tree handle");
+    if (!is_doubling_of(half_init, half_log, t)) return fail(TSTWO_ERR_TWIDDLE_MISMATCH, "twiddle tree mismatch");
+    *out = t;
+    return 0;
+}
+
+int tstwo_interpolate_columns(const tstwo_dptr *evals, const tstwo_dptr *coeffs, int n_cols, int log_size,
+                              uint32_t half_init, tstwo_twiddles tw, uint32_t flags)
+{
+    TS_REQUIRE_INIT();
+    if (log_size < 1 || log_size > 30 || n_cols < 0) return fail(TSTWO_ERR_BAD_ARG, "bad interpolate arguments");
+    TwiddleTree *t;
+    int rc = check_tree(tw, half_init, log_size - 1, &t);
+    if (rc) return rc;
+    ColSet s, d;
+    if ((rc = make_colset(evals, n_cols, 0, &s))) return rc;
+    if ((rc = make_colset(coeffs, n_cols, 1, &d))) return rc;
+    return fft_interpolate(s, d, n_cols, log_size, t, flags);
+}
+
+int tstwo_evaluate_columns(const tstwo_dptr *coeffs, int poly_log, const tstwo_dptr *evals, int n_cols, int domain_log,
+                           uint32_t half_init, tstwo_twiddles tw, uint32_t flags)
+{
+    TS_REQUIRE_INIT();
+    if (domain_log < 1 || domain_log > 30 || poly_log < 0 || n_cols < 0) return fail(TSTWO_ERR_BAD_ARG, "bad evaluate arguments");
+    if (poly_log > domain_log) return fail(TSTWO_ERR_SIZE_MISMATCH, "log size too small");   // circle.ts:72
+    TwiddleTree *t;
+    int rc = check_tree(tw, half_init, domain_log - 1, &t);
+    if (rc) return rc;
+    ColSet s, d;
+    if ((rc = make_colset(coeffs, n_cols, 0, &s))) return rc;
+    if ((rc = make_colset(evals, n_cols, 1, &d))) return rc;
+    return fft_evaluate(s, poly_log, d, n_cols, domain_log, t, flags);
+}
+
+}  // extern "C"

@@ -1,0 +1,124 @@
+// The metric path in one call: Stwo's CommitmentTreeProver::new as quoted in the reference at
+// packages/core/src/pcs/prover.ts:215-235 (interpolate -> evaluate on the blown-up canonic domain -> Merkle commit),
+// i.e. PolyOps.interpolateColumns + evaluatePolynomials (poly/circle/ops.ts:73-101) + MerkleProver.commit
+// (vcs/prover.ts:13-30) on device-resident columns.
+#include <vector>
+
+#include "common.cuh"
+#include "host_m31.h"
+
+using namespace tstwo;
+
+namespace {
+int lde_commit_device(const uint32_t *trace, int n_cols, int log_size, int log_blowup, TwiddleTree *t, uint32_t *coeffs,
+                      uint32_t *evals, uint8_t *layers, uint8_t *root, uint32_t flags, bool sync_root)
+{
+    const int ext = log_size + log_blowup;
+    const uint64_t n = 1ull << log_size, ne = 1ull << ext;
+    // coefficients either kept (coeffs) or staged in the low half of each evals column (needs blowup >= 1)
+    ColSet src = { trace, n, nullptr };
+    ColSet cf = coeffs ? ColSet{ coeffs, n, nullptr } : ColSet{ evals + (ne - n), ne, nullptr };
+    if (!coeffs && log_blowup == 0) cf = ColSet{ evals, ne, nullptr };
+    ColSet ev = { evals, ne, nullptr };
+    int rc = fft_interpolate(src, cf, n_cols, log_size, t, flags);
+    if (rc) return rc;
+    rc = fft_evaluate(cf, log_size, ev, n_cols, ext, t, flags);
+    if (rc) return rc;
+    if (layers) {
+        const uint8_t *prev = nullptr;
+        ColSet none = { nullptr, 0, nullptr };
+        for (int log = ext; log >= 0; log--) {
+            uint8_t *dst = layers + 32ull * ((1ull << log) - 1);
+            rc = merkle_commit_layer(log, prev, log == ext ? ev : none, log == ext ? n_cols : 0, dst);
+            if (rc) return rc;
+            prev = dst;
+        }
+        if (root) {
+            TS_CUDA(cudaMemcpyAsync(root, layers, 32, cudaMemcpyDeviceToHost, ctx().stream));
+            if (sync_root) TS_CUDA(cudaStreamSynchronize(ctx().stream));
+        }
+    }
+    return 0;
+}
+
+int check_args(int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, TwiddleTree **t)
+{
+    if (n_cols < 1 || log_size < 1 || log_blowup < 0 || log_size + log_blowup > 30)
+        return fail(TSTWO_ERR_BAD_ARG, "bad lde_commit arguments");
+    *t = get_tree(tw);
+    if (!*t) return fail(TSTWO_ERR_BAD_ARG, "unknown twiddle tree handle");
+    const int ext = log_size + log_blowup;
+    // CanonicCoset(k).half_coset() = half_odds(k-1): initial index 2^(31-(k-1)-2) (poly/circle/canonic.ts, circle.ts:232-234)
+    if (!is_doubling_of(host::subgroup_gen(ext - 1 + 2), ext - 1, *t) ||
+        !is_doubling_of(host::subgroup_gen(log_size - 1 + 2), log_size - 1, *t))
+        return fail(TSTWO_ERR_TWIDDLE_MISMATCH, "twiddle tree mismatch");
+    return 0;
+}
+}  // namespace
+
+extern "C" {
+
+int tstwo_lde_commit(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, tstwo_dptr coeffs,
+                     tstwo_dptr evals, tstwo_dptr layers, uint8_t root[32], uint32_t flags)
+{
+    TS_REQUIRE_INIT();
+    TwiddleTree *t;
+    int rc = check_args(n_cols, log_size, log_blowup, tw, &t);
+    if (rc) return rc;
+    if (!trace || !evals) return fail(TSTWO_ERR_BAD_ARG, "null trace/evals");
+    if (!coeffs && log_blowup == 0 && trace != evals)
+        ;   // coefficients are produced directly in evals, then evaluated in place
+    return lde_commit_device((const uint32_t *)trace, n_cols, log_size, log_blowup, t, (uint32_t *)coeffs, (uint32_t *)evals,
+                             (uint8_t *)layers, root, flags, true);
+}
+
+// Host-resident trace: the columns are copied in chunks on a copy stream while the previous chunk's interpolate /
+// evaluate kernels run; the Merkle commit runs once all columns are extended.
+int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
+                          tstwo_dptr trace_staging, tstwo_dptr coeffs, tstwo_dptr evals, tstwo_dptr layers,
+                          uint8_t root[32], uint32_t flags)
+{
+    TS_REQUIRE_INIT();
+    TwiddleTree *t;
+    int rc = check_args(n_cols, log_size, log_blowup, tw, &t);
+    if (rc) return rc;
+    if (!host_trace || !trace_staging || !evals) return fail(TSTWO_ERR_BAD_ARG, "null trace/staging/evals");
+    Context &c = ctx();
+    const int ext = log_size + log_blowup;
+    const uint64_t n = 1ull << log_size, ne = 1ull << ext;
+    const int chunk = 16;   // columns per H2D chunk (multiple of the 8-column FFT tile)
+    const int n_chunks = (n_cols + chunk - 1) / chunk;
+    std::vector<cudaEvent_t> ev((size_t)n_chunks);
+    uint32_t *stage = (uint32_t *)trace_staging;
+    for (int k = 0; k < n_chunks; k++) {
+        const int c0 = k * chunk, nc = (n_cols - c0 < chunk) ? n_cols - c0 : chunk;
+        TS_CUDA(cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming));
+        TS_CUDA(cudaMemcpyAsync(stage + (uint64_t)c0 * n, host_trace + (uint64_t)c0 * n, (uint64_t)nc * n * 4,
+                                cudaMemcpyHostToDevice, c.copy_stream));
+        TS_CUDA(cudaEventRecord(ev[k], c.copy_stream));
+    }
+    for (int k = 0; k < n_chunks; k++) {
+        const int c0 = k * chunk, nc = (n_cols - c0 < chunk) ? n_cols - c0 : chunk;
+        TS_CUDA(cudaStreamWaitEvent(c.stream, ev[k], 0));
+        uint32_t *cf = coeffs ? (uint32_t *)coeffs + (uint64_t)c0 * n : nullptr;
+        rc = lde_commit_device(stage + (uint64_t)c0 * n, nc, log_size, log_blowup, t, cf, (uint32_t *)evals + (uint64_t)c0 * ne,
+                               nullptr, nullptr, flags, false);
+        if (rc) return rc;
+    }
+    if (layers) {
+        const uint8_t *prev = nullptr;
+        ColSet evs = { (const uint32_t *)evals, ne, nullptr }, none = { nullptr, 0, nullptr };
+        for (int log = ext; log >= 0; log--) {
+            uint8_t *dst = (uint8_t *)layers + 32ull * ((1ull << log) - 1);
+            rc = merkle_commit_layer(log, prev, log == ext ? evs : none, log == ext ? n_cols : 0, dst);
+            if (rc) return rc;
+            prev = dst;
+        }
+        if (root) TS_CUDA(cudaMemcpyAsync(root, (const void *)layers, 32, cudaMemcpyDeviceToHost, c.stream));
+    }
+    TS_CUDA(cudaStreamSynchronize(c.stream));
+    for (auto e : ev) cudaEventDestroy(e);
+    return 0;
+}
+
+}  // extern "C"
