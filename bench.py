@@ -1,0 +1,340 @@
+#!/usr/bin/env python
+"""bench.py -- LDE + Blake2s-commit throughput (BASELINE.json metric) on N B200s of one node.
+
+A step = one pass of the hot path over one batch of synthetic input: interpolate 256 trace columns of 2^22 M31
+elements, evaluate them on the blow-up-2 canonic domain (2^23 rows), Blake2s Merkle commit, root on the host.
+  value : trace elements / s with the trace resident in HBM (CUDA events, max over ranks)
+  e2e   : the same through the C-ABI call a host makes (tstwo_lde_commit_host): trace in pinned HOST memory,
+          host->device copies inside the timed region, root read back
+N > 1 : columns are sharded by column for the LDE, an NCCL all-to-all re-shards by row range, every rank
+        hashes its leaves and builds its subtree, rank 0 finishes the top log2(N) layers.
+--impl reference : the CPU oracle (C restatement of TStwo's CpuBackend; the TypeScript reference cannot run here)
+        on all host cores, on a bounded sample of the same workload.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_COLS, LOG_SIZE, LOG_BLOWUP = 256, 22, 1
+METRIC = "lde_blake2s_commit_throughput"
+UNIT = "M31 trace elements/s"
+P = 2147483647
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--log-size", type=int, default=LOG_SIZE)
+    ap.add_argument("--cols", type=int, default=N_COLS)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-sample-cols", type=int, default=8)
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            pass
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            for k, nm in enumerate(names):
+                if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        # "under load": drop samples below half of the largest seen (idle ramp)
+        load = [s for s in sm if s >= 0.5 * sm[-1]] if sm else []
+        return {"sm_mhz": load[len(load) // 2] if load else None, "sm_max_mhz": mx[0] if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    import numpy as np
+    import oracle as orc
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    log, blow, cols = args.log_size, LOG_BLOWUP, args.cpu_sample_cols
+    root_init, root_log = orc.canonic_half_coset(log + blow)
+    tw, itw = orc.precompute_twiddles(root_init, root_log)
+    rng = np.random.default_rng(0x5EED0003)
+    trace = rng.integers(0, P, (cols, 1 << log), dtype=np.uint32)
+    for _ in range(min(args.warmup, 1)):
+        orc.lde_commit(trace, blow, tw, itw)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        orc.lde_commit(trace, blow, tw, itw)
+    dt = (time.perf_counter() - t0) / args.steps
+    val = cols * (1 << log) / dt
+    sample = f"{cols} of {args.cols} columns at log_size {log}, blowup 2 (interpolate + evaluate + Merkle commit of those columns)"
+    print(json.dumps({
+        "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32 (M31)",
+        "data": "synthetic", "impl": "reference",
+        "config": {"workload": f"{args.cols} cols x 2^{log}, blowup 2, Blake2s Merkle commit", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": orc.num_threads(), "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference = C restatement of TStwo CpuBackend (oracle/); the TypeScript reference needs bun/node, absent here",
+    }))
+
+
+# ------------------------------------------------------------------------------------------------ cuda arm
+def cpu_baseline(args):
+    import numpy as np
+    import oracle as orc
+    log, blow, cols = args.log_size, LOG_BLOWUP, args.cpu_sample_cols
+    root_init, root_log = orc.canonic_half_coset(log + blow)
+    tw, itw = orc.precompute_twiddles(root_init, root_log)
+    trace = np.random.default_rng(1).integers(0, P, (cols, 1 << log), dtype=np.uint32)
+    t0 = time.perf_counter()
+    reps = 0
+    while reps < 1 or (time.perf_counter() - t0 < 10 and reps < 4):
+        orc.lde_commit(trace, blow, tw, itw)
+        reps += 1
+    dt = (time.perf_counter() - t0) / reps
+    return {"value": cols * (1 << log) / dt, "unit": UNIT, "cores": orc.num_threads(), "kind": "port",
+            "sample": f"{cols} of {args.cols} columns at log_size {log}, blowup 2, {reps} rep(s), {dt:.2f} s each"}
+
+
+def run_cuda(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from tstwo_b200 import _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run for --gpus > 1")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    L = _lib.init(local)
+    chk = _lib.check
+    # a dedicated (non-default) stream shared by torch and the library, so torch.cuda.Event sees the library's kernels
+    stream = torch.cuda.Stream(device=local)
+    torch.cuda.set_stream(stream)
+    chk(L.tstwo_set_stream(C.c_void_p(stream.cuda_stream)))
+
+    log, blow, n_cols = args.log_size, LOG_BLOWUP, args.cols
+    ext = log + blow
+    n, ne = 1 << log, 1 << ext
+    assert n_cols % world == 0 and world & (world - 1) == 0
+    lc = n_cols // world                      # local columns
+    dev = torch.device("cuda", local)
+
+    tw = C.c_uint64()
+    chk(L.tstwo_twiddles_precompute(1 << (31 - (ext - 1) - 2), ext - 1, C.byref(tw)))
+
+    # synthetic trace: uniform random canonical M31, column c of the job uses stream c
+    g = torch.Generator(device=dev); g.manual_seed(0x5EED0003 + rank)
+    trace = torch.randint(0, P, (lc, n), dtype=torch.int32, device=dev, generator=g)
+    coeffs = torch.empty((lc, n), dtype=torch.int32, device=dev)
+    evals = torch.empty((lc, ne), dtype=torch.int32, device=dev)
+    root = (C.c_uint8 * 32)()
+
+    if world == 1:
+        layers = torch.empty(((2 << ext) - 1) * 8, dtype=torch.int32, device=dev)
+
+        def step():
+            chk(L.tstwo_lde_commit(trace.data_ptr(), n_cols, log, blow, tw.value, coeffs.data_ptr(), evals.data_ptr(),
+                                   layers.data_ptr(), root, 0))
+        launches_per_step = None
+    else:
+        sub = ext - (world.bit_length() - 1)      # log rows per rank
+        rows = 1 << sub
+        recv = torch.empty((n_cols, rows), dtype=torch.int32, device=dev)
+        layers = torch.empty(((2 << sub) - 1) * 8, dtype=torch.int32, device=dev)
+        roots = torch.empty((world, 8), dtype=torch.int32, device=dev)
+        top = torch.empty(((2 * world) - 1) * 8, dtype=torch.int32, device=dev)
+        col_ptrs = _lib.dptr_array([recv.data_ptr() + 4 * rows * c for c in range(n_cols)])
+        col_logs = (C.c_int * n_cols)(*([sub] * n_cols))
+
+        def step():
+            # column-sharded LDE; evals come out grouped by destination rank: [dest][local col][rows]
+            chk(L.tstwo_lde_columns_sharded(trace.data_ptr(), lc, log, blow, tw.value, coeffs.data_ptr(), evals.data_ptr(),
+                                            world, 0))
+            dist.all_to_all_single(recv.view(-1), evals.view(-1))          # NVLink all-to-all: recv = [src][local col][rows]
+            chk(L.tstwo_merkle_commit(col_ptrs, col_logs, n_cols, layers.data_ptr(), None))
+            dist.all_gather_into_tensor(roots.view(-1), layers[:8])
+            if rank == 0:
+                prev = roots.data_ptr()
+                for k in range(world.bit_length() - 2, -1, -1):
+                    dst = top.data_ptr() + 32 * ((1 << k) - 1)
+                    chk(L.tstwo_merkle_commit_layer(k, prev, None, 0, dst))
+                    prev = dst
+                chk(L.tstwo_download(root, top.data_ptr(), 32))
+            else:
+                chk(L.tstwo_sync())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = L.tstwo_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = int(L.tstwo_launch_count() - l0)
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    value = n_cols * n / (ms * 1e-3)
+    root_hex = bytes(root).hex()
+
+    # ---- per-kernel timing (1 GPU): the roofline of the dominant kernel, measured live with CUDA events
+    roof, kernels = None, None
+    if world == 1:
+        kernels = kernel_breakdown(L, chk, torch, stream, trace, coeffs, evals, layers, tw, n_cols, log, blow)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak, which = (peaks.get("hbm_gbs"), "measured (MEASURED_PEAKS.json hbm_gbs)") if peaks.get("hbm_gbs") else (6650.0, "fallback")
+        top_k = max(kernels, key=lambda k: kernels[k]["ms"])
+        kk = kernels[top_k]
+        roof = {"bound": "hbm", "kernel": top_k, "achieved": kk["gbs"], "peak": peak, "unit": "GB/s", "frac": kk["gbs"] / peak,
+                "traffic": None, "peak_source": which, "algorithmic_bytes_per_launch": kk["bytes"], "ms_per_launch": kk["ms"],
+                "note": "integer-issue bound, not HBM bound: see int_roofline and DESIGN.md"}
+
+    # ---- end to end through the C ABI with HOST buffers (1 GPU)
+    e2e = None
+    if world == 1 and not args.no_e2e:
+        host = torch.empty((n_cols, n), dtype=torch.int32, pin_memory=True)
+        host.copy_(trace.cpu())
+        stage = torch.empty((n_cols, n), dtype=torch.int32, device=dev)
+        root2 = (C.c_uint8 * 32)()
+
+        def e2e_step():
+            chk(L.tstwo_lde_commit_host(host.data_ptr(), n_cols, log, blow, tw.value, stage.data_ptr(), coeffs.data_ptr(),
+                                        evals.data_ptr(), layers.data_ptr(), root2, 0))
+        for _ in range(2):
+            e2e_step()
+        torch.cuda.synchronize()
+        k = max(3, min(args.steps, 5))
+        t0 = time.perf_counter()
+        for _ in range(k):
+            e2e_step()          # synchronises inside (root is host-visible on return)
+        dt = (time.perf_counter() - t0) / k
+        assert bytes(root2).hex() == root_hex, "e2e root differs from device-resident root"
+        e2e = {"value": n_cols * n / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "h2d_bytes_per_step": n_cols * n * 4,
+               "d2h_bytes_per_step": 32, "api": "tstwo_lde_commit_host (C ABI, pinned host trace -> root)"}
+
+    if rank == 0:
+        cpu = None if args.no_cpu or world > 1 else cpu_baseline(args)
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32 (M31)",
+            "data": "synthetic",
+            "config": {"workload": f"{n_cols} cols x 2^{log} M31, blowup 2 (2^{ext} rows), Blake2s Merkle commit",
+                       "n_cols": n_cols, "log_size": log, "log_blowup": blow,
+                       "l2": "inputs (%.1f GiB) and outputs exceed the 126 MB L2; no flush needed" % (n_cols * n * 4 / 2**30),
+                       "parallelism": "1 GPU" if world == 1 else f"column-sharded LDE -> NCCL all-to-all -> row-sharded Merkle x{world}"},
+            "gpu_launches": launches, "clocks": clocks, "root": root_hex,
+        }
+        if roof: out["roofline"] = roof
+        if kernels: out["kernels"] = kernels
+        if e2e: out["e2e"] = e2e
+        if cpu: out["cpu_baseline"] = cpu
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def kernel_breakdown(L, chk, torch, stream, trace, coeffs, evals, layers, tw, n_cols, log, blow):
+    """Times the three phases of the step separately (CUDA events on the launching stream)."""
+    from tstwo_b200 import _lib
+    ext = log + blow
+    n, ne = 1 << log, 1 << ext
+
+    def timed(fn, reps=5):
+        fn(); torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(reps):
+            fn()
+        b.record(stream); torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    tp = _lib.dptr_array([trace.data_ptr() + 4 * n * c for c in range(n_cols)])
+    cp = _lib.dptr_array([coeffs.data_ptr() + 4 * n * c for c in range(n_cols)])
+    ep = _lib.dptr_array([evals.data_ptr() + 4 * ne * c for c in range(n_cols)])
+    hi_small, hi_big = 1 << (31 - (log - 1) - 2), 1 << (31 - (ext - 1) - 2)
+    t_int = timed(lambda: chk(L.tstwo_interpolate_columns(tp, cp, n_cols, log, hi_small, tw.value, 0)))
+    t_ev = timed(lambda: chk(L.tstwo_evaluate_columns(cp, log, ep, n_cols, ext, hi_big, tw.value, 0)))
+    leaf = layers.data_ptr() + 32 * ((1 << ext) - 1)
+    t_leaf = timed(lambda: chk(L.tstwo_merkle_commit_layer(ext, 0, ep, n_cols, leaf)))
+    node = layers.data_ptr() + 32 * ((1 << (ext - 1)) - 1)
+    t_node = timed(lambda: chk(L.tstwo_merkle_commit_layer(ext - 1, leaf, None, 0, node)))
+    b_int, b_ev = 8 * n_cols * n, (4 + 4 * (1 << blow)) * n_cols * n
+    b_leaf, b_node = (4 * n_cols + 32) * ne, 96 * (ne // 2)
+    mk = lambda ms, by, launches: {"ms": ms, "bytes": by, "gbs": by / ms / 1e6, "launches": launches}
+    return {"interpolate (2 fft_pass launches)": mk(t_int, b_int, 2), "evaluate (2 fft_pass launches)": mk(t_ev, b_ev, 2),
+            "merkle_leaf_layer": mk(t_leaf, b_leaf, 1), "merkle_node_layer_top": mk(t_node, b_node, 1)}
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_cuda(a)

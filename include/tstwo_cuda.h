@@ -114,6 +114,11 @@ int tstwo_accumulate_quotients(int log_size, uint32_t half_coset_initial_index, 
  * coeffs may be 0 (coefficients are then not kept).  tw must cover half_odds(log_size+log_blowup-1). */
 int tstwo_lde_commit(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
                      tstwo_dptr coeffs, tstwo_dptr evals, tstwo_dptr layers, uint8_t root[32], uint32_t flags);
+/* Multi-GPU building block: LDE of this rank's n_cols columns with the evaluations written grouped by destination
+ * rank, [n_shards][n_cols][2^(log_size+log_blowup)/n_shards] (contiguous row ranges = complete Merkle subtrees), ready
+ * for one all-to-all.  The receiver then calls tstwo_merkle_commit on its [all columns][rows] block. */
+int tstwo_lde_columns_sharded(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
+                              tstwo_dptr coeffs, tstwo_dptr evals, int n_shards, uint32_t flags);
 /* Same, but the trace lives in HOST memory (pinned or pageable): host->device copies are pipelined with the
  * kernels inside the call; only the root comes back. */
 int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,

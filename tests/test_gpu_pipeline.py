@@ -93,3 +93,31 @@ def test_config2_properties(tb, orc):
     # (d) determinism
     again = tb.CommitmentTreeProver.from_trace(tb.CudaColumn.from_cpu(cols.reshape(-1)), n_cols, log, blow, tw, keep_coeffs=False)
     assert again.root() == tree.root()
+
+
+@pytest.mark.parametrize("n_shards", [2, 4, 8])
+def test_lde_columns_sharded_layout(tb, orc, n_shards):
+    """Multi-GPU building block: evaluations grouped by destination rank equal the plain LDE, re-laid out; hashing a
+    row shard gives the matching subtree of the full Merkle tree (top layers = hash of the shard roots)."""
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    log, blow, n_cols = 14, 1, 12
+    ext = log + blow
+    rng = np.random.default_rng(n_shards)
+    trace = rng.integers(0, P, (n_cols, 1 << log), dtype=np.uint32)
+    tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(ext).half_coset())
+    ref = tb.CommitmentTreeProver.from_trace(tb.CudaColumn.from_cpu(trace.reshape(-1)), n_cols, log, blow, tw)
+    full = np.stack([e.values.toCpu() for e in ref.evaluations])                     # (n_cols, 2^ext)
+    dtrace = tb.CudaColumn.from_cpu(trace.reshape(-1))
+    out = tb.CudaColumn.uninitialized(n_cols << ext)
+    _lib.check(L.tstwo_lde_columns_sharded(dtrace.ptr, n_cols, log, blow, tw.handle, 0, out.ptr, n_shards, 0))
+    rows = (1 << ext) // n_shards
+    got = out.toCpu().reshape(n_shards, n_cols, rows)
+    for s in range(n_shards):
+        assert (got[s] == full[:, s * rows:(s + 1) * rows]).all()
+    # subtree of shard 1 == the corresponding nodes of the full tree
+    sub = ext - (n_shards.bit_length() - 1)
+    shard = tb.CudaColumn.from_cpu(got[1].reshape(-1))
+    mp = tb.MerkleProver.commit(tb.CudaBackend.merkleOps, [shard.slice(c * rows, rows) for c in range(n_cols)])
+    k = n_shards.bit_length() - 1
+    assert mp.root() == ref.commitment.layer_bytes(k)[1].tobytes()

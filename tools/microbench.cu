@@ -27,6 +27,11 @@ __device__ __forceinline__ void op(uint32_t &a, uint32_t &b, uint32_t t)
     else if (V == 7) { a = __funnelshift_r(a, b, 7); b = __funnelshift_r(b, a, 12); } // SHF only (2 per op)
     else if (V == 8) { a = __byte_perm(a, b, 0x1032); b = __byte_perm(b, a, 0x0321); } // PRMT only (2 per op)
     else if (V == 9) { uint64_t p = (uint64_t)a * t + b; a = (uint32_t)p; b = (uint32_t)(p >> 32) ^ t; } // IMAD.WIDE + LOP
+    else if (V == 11) { uint64_t p = (uint64_t)a * t; a = (uint32_t)p ^ b; b = (uint32_t)(p >> 32) ^ a; }   // IMAD.WIDE + 2 LOP
+    else if (V == 12) { a = __umulhi(a, t) ^ b; b = __umulhi(b, t) ^ a; }                                   // IMAD.HI + LOP (x2)
+    else if (V == 13) { a = a * t + b; b = (b ^ a) & t; }                                                   // 1 IMAD + 1 LOP3
+    else if (V == 14) { uint32_t s = a + b; a = m31::csub(s); uint32_t d = a - b; b = __viaddmin_u32(d, m31::P, d); } // add+sub mod P (4)
+    else if (V == 15) { a = (a >> 1) + b; b = (b >> 1) + a; }                                               // LEA.HI-like x2
     else if (V == 10) {                                                              // Shoup-style: 3 IMAD-pipe + 1 ALU mul
         uint32_t q = __umulhi(b, t); uint32_t r = b * (t >> 1) - q * m31::P; uint32_t m = m31::csub(r);
         uint32_t x = a; a = m31::add(x, m); b = m31::sub(x, m);
@@ -73,6 +78,53 @@ __device__ __forceinline__ void compress(uint32_t (&h)[8], const uint32_t (&m)[1
     RND(6, 15, 14, 9, 11, 3, 0, 8, 12, 2, 13, 7, 1, 4, 10, 5); RND(10, 2, 8, 4, 7, 6, 1, 5, 15, 11, 9, 14, 3, 12, 13, 0);
     h[0] ^= v0 ^ v8; h[1] ^= v1 ^ v9; h[2] ^= v2 ^ v10; h[3] ^= v3 ^ v11; h[4] ^= v4 ^ v12; h[5] ^= v5 ^ v13; h[6] ^= v6 ^ v14; h[7] ^= v7 ^ v15;
 }
+// same compression with every addition forced onto the FMA pipe (x * one + y)
+#define GA(x, y) ((x) * one + (y))
+#define G2(a, b, c, d, x, y) do { a = GA(GA(a, b), (x)); d = rotr16(d ^ a); c = GA(c, d); b = rotr12(b ^ c); a = GA(GA(a, b), (y)); d = rotr8(d ^ a); c = GA(c, d); b = rotr7(b ^ c); } while (0)
+// only the two-input adds on the FMA pipe, a + b + m stays IADD3
+#define G3(a, b, c, d, x, y) do { a = a + b + (x); d = rotr16(d ^ a); c = GA(c, d); b = rotr12(b ^ c); a = a + b + (y); d = rotr8(d ^ a); c = GA(c, d); b = rotr7(b ^ c); } while (0)
+#define RNDX(GX, s0, s1, s2, s3, s4, s5, s6, s7, s8, s9, s10, s11, s12, s13, s14, s15) do { \
+    GX(v0, v4, v8, v12, m[s0], m[s1]); GX(v1, v5, v9, v13, m[s2], m[s3]); GX(v2, v6, v10, v14, m[s4], m[s5]); GX(v3, v7, v11, v15, m[s6], m[s7]); \
+    GX(v0, v5, v10, v15, m[s8], m[s9]); GX(v1, v6, v11, v12, m[s10], m[s11]); GX(v2, v7, v8, v13, m[s12], m[s13]); GX(v3, v4, v9, v14, m[s14], m[s15]); } while (0)
+template <int VAR>
+__device__ __forceinline__ void compress_v(uint32_t (&h)[8], const uint32_t (&m)[16], uint32_t t, uint32_t one)
+{
+    uint32_t v0 = h[0], v1 = h[1], v2 = h[2], v3 = h[3], v4 = h[4], v5 = h[5], v6 = h[6], v7 = h[7];
+    uint32_t v8 = 0x6A09E667u, v9 = 0xBB67AE85u, v10 = 0x3C6EF372u, v11 = 0xA54FF53Au, v12 = 0x510E527Fu ^ t, v13 = 0x9B05688Cu, v14 = 0x1F83D9ABu, v15 = 0x5BE0CD19u;
+#define ALLR(GX) RNDX(GX, 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15); RNDX(GX, 14, 10, 4, 8, 9, 15, 13, 6, 1, 12, 0, 2, 11, 7, 5, 3); \
+    RNDX(GX, 11, 8, 12, 0, 5, 2, 15, 13, 10, 14, 3, 6, 7, 1, 9, 4); RNDX(GX, 7, 9, 3, 1, 13, 12, 11, 14, 2, 6, 5, 10, 4, 0, 15, 8); \
+    RNDX(GX, 9, 0, 5, 7, 2, 4, 10, 15, 14, 1, 11, 12, 6, 8, 3, 13); RNDX(GX, 2, 12, 6, 10, 0, 11, 8, 3, 4, 13, 7, 5, 15, 14, 1, 9); \
+    RNDX(GX, 12, 5, 1, 15, 14, 13, 4, 10, 0, 7, 6, 3, 9, 2, 8, 11); RNDX(GX, 13, 11, 7, 14, 12, 1, 3, 9, 5, 0, 15, 4, 8, 6, 2, 10); \
+    RNDX(GX, 6, 15, 14, 9, 11, 3, 0, 8, 12, 2, 13, 7, 1, 4, 10, 5); RNDX(GX, 10, 2, 8, 4, 7, 6, 1, 5, 15, 11, 9, 14, 3, 12, 13, 0);
+    if (VAR == 0) { ALLR(G) } else if (VAR == 1) { ALLR(G2) } else { ALLR(G3) }
+    h[0] ^= v0 ^ v8; h[1] ^= v1 ^ v9; h[2] ^= v2 ^ v10; h[3] ^= v3 ^ v11; h[4] ^= v4 ^ v12; h[5] ^= v5 ^ v13; h[6] ^= v6 ^ v14; h[7] ^= v7 ^ v15;
+}
+template <int VAR>
+__global__ void __launch_bounds__(256) k_blake_v(uint32_t *out, int iters, uint32_t one)
+{
+    uint32_t h[8], m[16];
+    for (int i = 0; i < 8; i++) h[i] = threadIdx.x * 31 + i;
+    for (int i = 0; i < 16; i++) m[i] = threadIdx.x * 17 + i * 3 + blockIdx.x;
+    for (int it = 0; it < iters; it++) { compress_v<VAR>(h, m, it, one); m[it & 15] ^= h[0]; }
+    uint32_t s = 0;
+    for (int i = 0; i < 8; i++) s ^= h[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+template <int VAR> int run_blake(const char *name, int sms, uint32_t *out)
+{
+    for (int bps : {2, 4, 6}) {
+        int iters = 4096, grid = sms * bps;
+        cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+        k_blake_v<VAR><<<grid, 256>>>(out, 512, 1u); CK(cudaDeviceSynchronize());
+        CK(cudaEventRecord(e0)); k_blake_v<VAR><<<grid, 256>>>(out, iters, 1u); CK(cudaEventRecord(e1)); CK(cudaDeviceSynchronize());
+        float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+        double comp = (double)grid * 256 * iters;
+        printf("blake2s %-24s blocks/SM=%d  chip %7.2f Gcompress/s  => %.0f clk per warp-compress per SMSP @1965MHz (%.2f ms)\n",
+               name, bps, comp / ms / 1e6, 1.965e9 / (comp / (ms * 1e-3) / 32 / (sms * 4)), ms);
+    }
+    return 0;
+}
+
 __global__ void __launch_bounds__(256) k_blake(uint32_t *out, int iters, long long *cycles)
 {
     uint32_t h[8], m[16];
@@ -99,7 +151,7 @@ __global__ void k_copy(const uint4 *__restrict__ src, uint4 *__restrict__ dst, s
 
 template <int V> int run_ops(const char *name, int ops_per_call, int blocks_per_sm, int sms, uint32_t *out, long long *cyc)
 {
-    int iters = 4096, grid = sms * blocks_per_sm;
+    int iters = 65536, grid = sms * blocks_per_sm;
     cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     k_ops<V><<<grid, 256>>>(out, 64, cyc); CK(cudaDeviceSynchronize());
     CK(cudaEventRecord(e0)); k_ops<V><<<grid, 256>>>(out, iters, cyc); CK(cudaEventRecord(e1)); CK(cudaDeviceSynchronize());
@@ -107,8 +159,10 @@ template <int V> int run_ops(const char *name, int ops_per_call, int blocks_per_
     long long hc[1]; CK(cudaMemcpy(hc, cyc, 8, cudaMemcpyDeviceToHost));
     double calls = (double)grid * 256 * ILP * iters;
     double per_sm_clk = (double)blocks_per_sm * 256 * ILP * iters / (double)hc[0];
-    printf("%-28s blocks/SM=%d  calls/SM/clk=%6.2f  x%d instr => %7.1f instr/SM/clk   chip %8.1f Gcalls/s  (%.3f ms, %lld cyc, ~%.0f MHz)\n",
-           name, blocks_per_sm, per_sm_clk, ops_per_call, per_sm_clk * ops_per_call, calls / ms / 1e6, ms, hc[0], hc[0] / ms / 1e3);
+    (void)per_sm_clk;
+    double calls_per_sm_clk = calls / (ms * 1e-3) / sms / 1.965e9;   // wall-clock based, SM clock 1965 MHz (nvidia-smi)
+    printf("%-28s blocks/SM=%d  chip %8.1f Gcalls/s => %6.2f calls/SM/clk, x%d instr = %6.1f instr/SM/clk, %.2f clk per warp-call per SMSP (%.2f ms)\n",
+           name, blocks_per_sm, calls / ms / 1e6, calls_per_sm_clk, ops_per_call, calls_per_sm_clk * ops_per_call, 128.0 / calls_per_sm_clk, ms);
     return 0;
 }
 
@@ -119,7 +173,7 @@ int main()
     printf("device %s, %d SMs, clock %d kHz\n", prop.name, sms, prop.clockRate);
     uint32_t *out; long long *cyc;
     CK(cudaMalloc(&out, (size_t)sms * 8 * 256 * 4)); CK(cudaMalloc(&cyc, (size_t)sms * 8 * 8));
-    for (int bps : {2, 4, 8}) {
+    for (int bps : {2, 6}) {
         run_ops<0>("butterfly(7)", 7, bps, sms, out, cyc);
         run_ops<1>("ibutterfly(7)", 7, bps, sms, out, cyc);
         run_ops<2>("butterfly_min(10)", 10, bps, sms, out, cyc);
@@ -130,9 +184,17 @@ int main()
         run_ops<6>("lop3 x2", 2, bps, sms, out, cyc);
         run_ops<7>("shf x2", 2, bps, sms, out, cyc);
         run_ops<8>("prmt x2", 2, bps, sms, out, cyc);
-        run_ops<9>("imad.wide+lop", 2, bps, sms, out, cyc);
+        run_ops<9>("imad.wide(acc)+lop", 2, bps, sms, out, cyc);
+        run_ops<11>("imad.wide+2lop", 3, bps, sms, out, cyc);
+        run_ops<12>("(imad.hi+lop) x2", 4, bps, sms, out, cyc);
+        run_ops<13>("imad+lop3", 2, bps, sms, out, cyc);
+        run_ops<14>("add+sub modP (4)", 4, bps, sms, out, cyc);
+        run_ops<15>("lea.hi x2", 2, bps, sms, out, cyc);
     }
-    for (int bps : {2, 4, 8}) {
+    run_blake<0>("iadd3 adds (as compiled)", sms, out);
+    run_blake<1>("all adds IMAD*one", sms, out);
+    run_blake<2>("2-input adds IMAD*one", sms, out);
+    for (int bps : {8}) {
         int iters = 2048, grid = sms * bps;
         cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
         k_blake<<<grid, 256>>>(out, 16, cyc); CK(cudaDeviceSynchronize());

@@ -59,6 +59,7 @@ SIGNATURES = {
     "tstwo_accumulate": (C.c_int, [dptrp, dptrp, C.c_uint64]),
     "tstwo_accumulate_quotients": (C.c_int, [C.c_int, C.c_uint32, dptrp, C.c_int, u32p, C.c_int, u32p, intp, intp, u32p, dptrp]),
     "tstwo_lde_commit": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptr, C.POINTER(C.c_uint8), C.c_uint32]),
+    "tstwo_lde_columns_sharded": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, C.c_int, C.c_uint32]),
     "tstwo_lde_commit_host": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptr, dptr,
                                         C.POINTER(C.c_uint8), C.c_uint32]),
 }

@@ -17,10 +17,14 @@ __device__ __forceinline__ uint32_t rotr8(uint32_t x) { return __byte_perm(x, x,
 __device__ __forceinline__ uint32_t rotr12(uint32_t x) { return __funnelshift_r(x, x, 12); }
 __device__ __forceinline__ uint32_t rotr7(uint32_t x) { return __funnelshift_r(x, x, 7); }
 
+// Additions are issued as IMAD (x * one + y, `one` = 1 passed as a kernel argument so ptxas cannot fold it back
+// into IADD3): on sm_100 the xor/rotate work saturates the ALU pipe (64 lanes/clk/SM), the FMA pipe is idle, so
+// moving all 6 two-input adds of a G there cuts the ALU work per G from 10 to 8 instructions (profiles/r01).
+#define B2S_ADD(x, y) ((x) * one + (y))
 #define B2S_G(a, b, c, d, x, y)                                     \
     do {                                                            \
-        a = a + b + (x); d = rotr16(d ^ a); c = c + d; b = rotr12(b ^ c); \
-        a = a + b + (y); d = rotr8(d ^ a);  c = c + d; b = rotr7(b ^ c);  \
+        a = B2S_ADD(B2S_ADD(a, b), (x)); d = rotr16(d ^ a); c = B2S_ADD(c, d); b = rotr12(b ^ c); \
+        a = B2S_ADD(B2S_ADD(a, b), (y)); d = rotr8(d ^ a);  c = B2S_ADD(c, d); b = rotr7(b ^ c);  \
     } while (0)
 
 #define B2S_ROUND(s0, s1, s2, s3, s4, s5, s6, s7, s8, s9, s10, s11, s12, s13, s14, s15) \
@@ -32,7 +36,7 @@ __device__ __forceinline__ uint32_t rotr7(uint32_t x) { return __funnelshift_r(x
     } while (0)
 
 // one compression; t = byte counter (< 2^32 on this path), last = final-block flag
-__device__ __forceinline__ void b2s_compress(uint32_t (&h)[8], const uint32_t (&m)[16], uint32_t t, bool last)
+__device__ __forceinline__ void b2s_compress(uint32_t (&h)[8], const uint32_t (&m)[16], uint32_t t, bool last, uint32_t one)
 {
     uint32_t v0 = h[0], v1 = h[1], v2 = h[2], v3 = h[3], v4 = h[4], v5 = h[5], v6 = h[6], v7 = h[7];
     uint32_t v8 = 0x6A09E667u, v9 = 0xBB67AE85u, v10 = 0x3C6EF372u, v11 = 0xA54FF53Au;
@@ -57,43 +61,45 @@ __device__ __forceinline__ void b2s_init(uint32_t (&h)[8])
     h[4] = 0x510E527Fu; h[5] = 0x9B05688Cu; h[6] = 0x1F83D9ABu; h[7] = 0x5BE0CD19u;
 }
 
-// HAS_PREV: the first 16 message words are the two child hashes.
+// HAS_PREV: the first 16 message words are the two child hashes.  The next block's 16 message words are loaded
+// before the current block is compressed (software pipelining hides the column loads behind ~1200 instructions).
 template <bool HAS_PREV>
 __global__ void __launch_bounds__(256) merkle_layer_kernel(const uint4 *__restrict__ prev, ColSet cols, int n_cols,
-                                                           uint64_t n_nodes, uint4 *__restrict__ out)
+                                                           uint64_t n_nodes, uint4 *__restrict__ out, uint32_t one)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_nodes) return;
-    uint32_t h[8], m[16];
+    uint32_t h[8], m[16], nx[16];
     b2s_init(h);
     const uint32_t total_words = (HAS_PREV ? 16u : 0u) + (uint32_t)n_cols;
-    uint32_t done = 0;   // words consumed
-    if (HAS_PREV) {
-        const uint4 *p = prev + 4 * i;   // 64 bytes = children 2i, 2i+1
-        uint4 a = __ldcs(p), b = __ldcs(p + 1), c = __ldcs(p + 2), d = __ldcs(p + 3);
-        m[0] = a.x; m[1] = a.y; m[2] = a.z; m[3] = a.w; m[4] = b.x; m[5] = b.y; m[6] = b.z; m[7] = b.w;
-        m[8] = c.x; m[9] = c.y; m[10] = c.z; m[11] = c.w; m[12] = d.x; m[13] = d.y; m[14] = d.z; m[15] = d.w;
-        done = 16;
-        if (n_cols == 0) {
-            b2s_compress(h, m, 64u, true);
+    const uint32_t n_blocks = total_words == 0 ? 1u : (total_words + 15u) / 16u;
+    // block b covers message words [16b, 16b+16); word w is a child-hash word (w < 16, HAS_PREV) or column w - off
+    const int off = HAS_PREV ? 16 : 0;
+    auto load_block = [&](uint32_t b, uint32_t (&dst)[16]) {
+        if (HAS_PREV && b == 0) {
+            const uint4 *p = prev + 4 * i;   // 64 bytes = children 2i, 2i+1
+            uint4 x0 = __ldcs(p), x1 = __ldcs(p + 1), x2 = __ldcs(p + 2), x3 = __ldcs(p + 3);
+            dst[0] = x0.x; dst[1] = x0.y; dst[2] = x0.z; dst[3] = x0.w; dst[4] = x1.x; dst[5] = x1.y; dst[6] = x1.z; dst[7] = x1.w;
+            dst[8] = x2.x; dst[9] = x2.y; dst[10] = x2.z; dst[11] = x2.w; dst[12] = x3.x; dst[13] = x3.y; dst[14] = x3.z; dst[15] = x3.w;
         } else {
-            b2s_compress(h, m, 64u, false);
-        }
-    }
-    if (!HAS_PREV || n_cols > 0) {
-        int c = 0;
-        // full, non-final blocks of 16 columns
-        while (n_cols - c > 16) {
+            const int c0 = (int)(16 * b) - off;
+            if (c0 + 16 <= n_cols) {
 #pragma unroll
-            for (int k = 0; k < 16; k++) m[k] = __ldcs(cols.col(c + k) + i);
-            c += 16; done += 16;
-            b2s_compress(h, m, done * 4u, false);
-        }
-        // final block: 0..16 remaining columns, zero padded
+                for (int k = 0; k < 16; k++) dst[k] = __ldcs(cols.col(c0 + k) + i);
+            } else {
 #pragma unroll
-        for (int k = 0; k < 16; k++) m[k] = (c + k < n_cols) ? __ldcs(cols.col(c + k) + i) : 0u;
-        b2s_compress(h, m, total_words * 4u, true);
+                for (int k = 0; k < 16; k++) dst[k] = (c0 + k < n_cols) ? __ldcs(cols.col(c0 + k) + i) : 0u;
+            }
+        }
+    };
+    load_block(0, m);
+    for (uint32_t b = 0; b + 1 < n_blocks; b++) {
+        load_block(b + 1, nx);
+        b2s_compress(h, m, (b + 1) * 64u, false, one);
+#pragma unroll
+        for (int k = 0; k < 16; k++) m[k] = nx[k];
     }
+    b2s_compress(h, m, total_words * 4u, true, one);
     out[2 * i] = make_uint4(h[0], h[1], h[2], h[3]);
     out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
 }
@@ -103,8 +109,8 @@ int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, i
     const uint64_t n = 1ull << log_size;
     const unsigned block = 256;
     const unsigned grid = (unsigned)((n + block - 1) / block);
-    if (prev) TS_LAUNCH((merkle_layer_kernel<true>), grid, block, 0, (const uint4 *)prev, cols, n_cols, n, (uint4 *)out);
-    else TS_LAUNCH((merkle_layer_kernel<false>), grid, block, 0, (const uint4 *)nullptr, cols, n_cols, n, (uint4 *)out);
+    if (prev) TS_LAUNCH((merkle_layer_kernel<true>), grid, block, 0, (const uint4 *)prev, cols, n_cols, n, (uint4 *)out, 1u);
+    else TS_LAUNCH((merkle_layer_kernel<false>), grid, block, 0, (const uint4 *)nullptr, cols, n_cols, n, (uint4 *)out, 1u);
     return 0;
 }
 

@@ -55,10 +55,15 @@ struct ColSet {
     const uint32_t *base;       // used when table == nullptr
     uint64_t stride;            // words
     const uint64_t *table;      // device array of addresses, or nullptr
+    // Optional row-sharded layout [shard][column][rows]: element idx of column c lives at
+    // col(c) + idx + (idx >> shard_log) * shard_adj  (shard_log = 31 disables it: idx < 2^31).
+    int shard_log = 31;
+    uint64_t shard_adj = 0;
     __host__ __device__ __forceinline__ uint32_t *col(int c) const
     {
         return table ? reinterpret_cast<uint32_t *>(table[c]) : const_cast<uint32_t *>(base) + (uint64_t)c * stride;
     }
+    __host__ __device__ __forceinline__ uint64_t off(uint32_t idx) const { return idx + (uint64_t)(idx >> shard_log) * shard_adj; }
 };
 // Builds a ColSet from a host array of device addresses; uploads a table only when the stride is not uniform.
 // `slot` selects one of several independent table regions (so src and dst sets can coexist in one launch).

@@ -18,8 +18,9 @@ namespace tstwo {
 constexpr int W = 11;
 constexpr int TILE_ROWS = 1 << W;
 constexpr int PASS_THREADS = 256;
-constexpr int SMEM_UNITS = 2 * TILE_ROWS + 2 * (TILE_ROWS / 16);
-constexpr int SMEM_BYTES = SMEM_UNITS * 16;
+constexpr int HALF_UNITS = TILE_ROWS + TILE_ROWS / 16;       // uint4 units per half tile (1 pad unit per 16 rows)
+constexpr int TW_WORDS = TILE_ROWS;                          // twiddle heap: layer j at [2^(10-j), 2^(11-j))
+constexpr int SMEM_BYTES = 2 * HALF_UNITS * 16 + TW_WORDS * 4;
 constexpr int FAST_MIN_LOG = 14;
 
 struct PassParams {
@@ -34,38 +35,51 @@ struct PassParams {
     uint32_t scale2;       // 2/2^n after the last inverse layer, or 0
 };
 
-__device__ __forceinline__ void load_tw(const uint32_t *p, int cnt, uint32_t (&t)[8])
+// Stage all twiddles of the tile in shared memory as a heap: relative layer j (absolute i = lo + j) needs
+// T_i[(tile_hi << (10-j)) + r], r < 2^(10-j); it is stored at tws[2^(10-j) + r].  cp.async, 8 words per thread.
+__device__ __forceinline__ void tile_twiddles_async(uint32_t *tws, const PassParams &p, uint32_t tile_hi, int tid)
 {
-    if (cnt == 8) {
-        uint4 a = __ldg(reinterpret_cast<const uint4 *>(p)), b = __ldg(reinterpret_cast<const uint4 *>(p) + 1);
-        t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w;
-    } else if (cnt == 4) {
-        uint4 a = __ldg(reinterpret_cast<const uint4 *>(p));
-        t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w;
-    } else if (cnt == 2) {
-        uint2 a = __ldg(reinterpret_cast<const uint2 *>(p));
-        t[0] = a.x; t[1] = a.y;
-    } else t[0] = __ldg(p);
+#pragma unroll
+    for (int e = tid; e < TW_WORDS; e += PASS_THREADS) {
+        if (e == 0) continue;
+        const int lg = 31 - __clz(e);            // 10 - j
+        const int j = (W - 1) - lg;
+        const int i = p.lo + j;
+        if (j < p.j_min || i < 1) continue;      // the circle layer derives its twiddles from T_1
+        const uint32_t r = (uint32_t)e - (1u << lg);
+        const uint32_t *g = p.tw2 + (p.tree_len - (1u << (p.n - i))) + (tile_hi << lg) + r;
+        const uint32_t sa = (uint32_t)__cvta_generic_to_shared(tws + e);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
+    }
+    asm volatile("cp.async.commit_group;");
 }
 
 // One radix-16 stage on v[16][4]: digit bit k <-> row bit S+k, layers j = S+k for k in [0, NL).
 template <int S, int NL, bool INV>
-__device__ __forceinline__ void stage(uint32_t (&v)[16][4], const PassParams &p, uint32_t tile_hi, int rbase)
+__device__ __forceinline__ void stage(uint32_t (&v)[16][4], const PassParams &p, const uint32_t *tws, int rbase)
 {
 #pragma unroll
     for (int kk = 0; kk < NL; kk++) {
         const int k = INV ? kk : NL - 1 - kk;
         const int j = S + k;
         if (j < p.j_min) continue;                     // uniform across the grid
-        const int i = p.lo + j;                        // absolute layer
         const int cnt = 8 >> k;
         uint32_t t[8];
-        const uint32_t hb = (tile_hi << (W - 1 - j)) | ((uint32_t)rbase >> (j + 1));
-        if (i >= 1) {
-            load_tw(p.tw2 + (p.tree_len - (1u << (p.n - i))) + hb, cnt, t);
+        if (p.lo + j >= 1) {
+            const uint32_t *q = tws + (1 << (W - 1 - j)) + (rbase >> (j + 1));
+            if (cnt == 8) {
+                uint4 a = *reinterpret_cast<const uint4 *>(q), b = *reinterpret_cast<const uint4 *>(q + 4);
+                t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w;
+            } else if (cnt == 4) {
+                uint4 a = *reinterpret_cast<const uint4 *>(q);
+                t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w;
+            } else if (cnt == 2) {
+                uint2 a = *reinterpret_cast<const uint2 *>(q);
+                t[0] = a.x; t[1] = a.y;
+            } else t[0] = q[0];
         } else {
-            // circle layer: j == 0, k == 0, cnt == 8; T_1 entries hb/2 .. hb/2+3 = (x0, y0, x1, y1)
-            uint4 a = __ldg(reinterpret_cast<const uint4 *>(p.tw2 + (p.tree_len - (1u << (p.n - 1))) + (hb >> 1)));
+            // circle layer (j == 0, k == 0): T_1 entries (x0, y0, x1, y1) of this thread's 16 rows -> [y,-y,-x,x]
+            uint4 a = *reinterpret_cast<const uint4 *>(tws + (1 << (W - 2)) + (rbase >> 2));
             const uint32_t P2 = 0xfffffffeu;
             t[0] = a.y; t[1] = P2 - a.y; t[2] = P2 - a.x; t[3] = a.x;
             t[4] = a.w; t[5] = P2 - a.w; t[6] = P2 - a.z; t[7] = a.z;
@@ -92,15 +106,15 @@ template <int MAP> __device__ __forceinline__ int map_row(int rbase, int d)
 {
     return MAP == MAP_A ? rbase + d * 128 : MAP == MAP_B ? rbase + d * 8 : rbase + d;
 }
-// shared-memory unit (16 B) of (row r, half): half + 2r + 2(r>>4); conflict-free for all three maps
-template <int MAP> __device__ __forceinline__ int map_unit0(int rg, int half)
+// shared-memory unit (16 B) of row r inside a half tile: r + (r>>4); conflict-free for all three maps
+template <int MAP> __device__ __forceinline__ int map_unit0(int rg)
 {
     const int r = map_rbase<MAP>(rg);
-    return half + 2 * r + 2 * (r >> 4);
+    return r + (r >> 4);
 }
 template <int MAP> __device__ __forceinline__ constexpr int map_unit_off(int d)
 {
-    return MAP == MAP_A ? d * 272 : MAP == MAP_B ? 16 * d + 2 * (d >> 1) : 2 * d;
+    return MAP == MAP_A ? d * 136 : MAP == MAP_B ? 8 * d + (d >> 1) : d;
 }
 template <int MAP> __device__ __forceinline__ void smem_store(uint4 *sm, int u0, const uint32_t (&v)[16][4])
 {
@@ -115,6 +129,11 @@ template <int MAP> __device__ __forceinline__ void smem_load(const uint4 *sm, in
         v[d][0] = a.x; v[d][1] = a.y; v[d][2] = a.z; v[d][3] = a.w;
     }
 }
+__device__ __forceinline__ void half_barrier(int half)
+{
+    if (half) asm volatile("bar.sync 2, 128;" ::: "memory");
+    else asm volatile("bar.sync 1, 128;" ::: "memory");
+}
 
 // global I/O.  STRIDED: lanes = index bits [0,3) of one column (blockIdx.y); CONTIG: lanes = 8 columns.
 template <int MAP, bool STRIDED>
@@ -127,7 +146,7 @@ __device__ __forceinline__ void gmem_load(const PassParams &p, uint32_t tile_hi,
 #pragma unroll
         for (int d = 0; d < 16; d++) {
             uint32_t idx = (fixed | ((uint32_t)map_row<MAP>(rbase, d) << p.lo)) & p.src_mask;
-            uint4 a = __ldcg(reinterpret_cast<const uint4 *>(col + idx));
+            uint4 a = __ldg(reinterpret_cast<const uint4 *>(col + p.src.off(idx)));
             v[d][0] = a.x; v[d][1] = a.y; v[d][2] = a.z; v[d][3] = a.w;
         }
     } else {
@@ -137,7 +156,7 @@ __device__ __forceinline__ void gmem_load(const PassParams &p, uint32_t tile_hi,
             if (c0 + q < p.n_cols) {
                 const uint32_t *col = p.src.col(c0 + q);
                 if (MAP == MAP_C) {
-                    const uint32_t idx = ((tile_hi << W) | (uint32_t)rbase) & p.src_mask;
+                    const uint64_t idx = p.src.off(((tile_hi << W) | (uint32_t)rbase) & p.src_mask);
 #pragma unroll
                     for (int dd = 0; dd < 4; dd++) {
                         uint4 a = __ldg(reinterpret_cast<const uint4 *>(col + idx + 4 * dd));
@@ -146,7 +165,7 @@ __device__ __forceinline__ void gmem_load(const PassParams &p, uint32_t tile_hi,
                 } else {
 #pragma unroll
                     for (int d = 0; d < 16; d++)
-                        v[d][q] = __ldcg(col + (((tile_hi << W) | (uint32_t)map_row<MAP>(rbase, d)) & p.src_mask));
+                        v[d][q] = __ldcg(col + p.src.off(((tile_hi << W) | (uint32_t)map_row<MAP>(rbase, d)) & p.src_mask));
                 }
             } else {
 #pragma unroll
@@ -165,7 +184,7 @@ __device__ __forceinline__ void gmem_store(const PassParams &p, uint32_t tile_hi
 #pragma unroll
         for (int d = 0; d < 16; d++) {
             uint32_t idx = fixed | ((uint32_t)map_row<MAP>(rbase, d) << p.lo);
-            __stcg(reinterpret_cast<uint4 *>(col + idx), make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]));
+            __stcg(reinterpret_cast<uint4 *>(col + p.dst.off(idx)), make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]));
         }
     } else {
         const int c0 = blockIdx.y * 8 + half * 4;
@@ -174,25 +193,29 @@ __device__ __forceinline__ void gmem_store(const PassParams &p, uint32_t tile_hi
             if (c0 + q < p.n_cols) {
                 uint32_t *col = p.dst.col(c0 + q);
                 if (MAP == MAP_C) {
-                    const uint32_t idx = (tile_hi << W) | (uint32_t)rbase;
+                    const uint64_t idx = p.dst.off((tile_hi << W) | (uint32_t)rbase);
 #pragma unroll
                     for (int dd = 0; dd < 4; dd++)
                         __stcg(reinterpret_cast<uint4 *>(col + idx + 4 * dd),
                                make_uint4(v[4 * dd][q], v[4 * dd + 1][q], v[4 * dd + 2][q], v[4 * dd + 3][q]));
                 } else {
 #pragma unroll
-                    for (int d = 0; d < 16; d++) __stcg(col + ((tile_hi << W) | (uint32_t)map_row<MAP>(rbase, d)), v[d][q]);
+                    for (int d = 0; d < 16; d++) __stcg(col + p.dst.off((tile_hi << W) | (uint32_t)map_row<MAP>(rbase, d)), v[d][q]);
                 }
             }
         }
     }
 }
 
+// 256 threads = two independent half tiles (warps 0-3 / 4-7, 4 lanes each) that share the tile's twiddles and
+// synchronise separately (named barriers), so one half's exchange overlaps the other half's butterflies.
 template <bool INV, bool STRIDED>
 __global__ void __launch_bounds__(PASS_THREADS, 2) fft_pass_kernel(const PassParams p)
 {
-    extern __shared__ uint4 sm[];
-    const int tid = threadIdx.x, half = tid & 1, rg = tid >> 1;
+    extern __shared__ uint4 sm_all[];
+    const int tid = threadIdx.x, half = tid >> 7, rg = tid & 127;
+    uint4 *sm = sm_all + half * HALF_UNITS;
+    uint32_t *tws = reinterpret_cast<uint32_t *>(sm_all + 2 * HALF_UNITS);
     uint32_t tile_hi, mid;
     if (STRIDED) {
         tile_hi = blockIdx.x >> (p.lo - 3);
@@ -201,32 +224,37 @@ __global__ void __launch_bounds__(PASS_THREADS, 2) fft_pass_kernel(const PassPar
         tile_hi = blockIdx.x;
         mid = 0;
     }
+    tile_twiddles_async(tws, p, tile_hi, tid);
     uint32_t v[16][4];
     const int rA = map_rbase<MAP_A>(rg), rB = map_rbase<MAP_B>(rg), rC = map_rbase<MAP_C>(rg);
-    const int uA = map_unit0<MAP_A>(rg, half), uB = map_unit0<MAP_B>(rg, half), uC = map_unit0<MAP_C>(rg, half);
+    const int uA = map_unit0<MAP_A>(rg), uB = map_unit0<MAP_B>(rg), uC = map_unit0<MAP_C>(rg);
     if (!INV) {
         gmem_load<MAP_A, STRIDED>(p, tile_hi, mid, rA, half, v);
-        stage<7, 4, false>(v, p, tile_hi, rA);
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncthreads();
+        stage<7, 4, false>(v, p, tws, rA);
         smem_store<MAP_A>(sm, uA, v);
-        __syncthreads();
+        half_barrier(half);
         smem_load<MAP_B>(sm, uB, v);
-        stage<3, 4, false>(v, p, tile_hi, rB);
+        stage<3, 4, false>(v, p, tws, rB);
         smem_store<MAP_B>(sm, uB, v);
-        __syncthreads();
+        half_barrier(half);
         smem_load<MAP_C>(sm, uC, v);
-        stage<0, 3, false>(v, p, tile_hi, rC);
+        stage<0, 3, false>(v, p, tws, rC);
         gmem_store<MAP_C, STRIDED>(p, tile_hi, mid, rC, half, v);
     } else {
         gmem_load<MAP_C, STRIDED>(p, tile_hi, mid, rC, half, v);
-        stage<0, 3, true>(v, p, tile_hi, rC);
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncthreads();
+        stage<0, 3, true>(v, p, tws, rC);
         smem_store<MAP_C>(sm, uC, v);
-        __syncthreads();
+        half_barrier(half);
         smem_load<MAP_B>(sm, uB, v);
-        stage<3, 4, true>(v, p, tile_hi, rB);
+        stage<3, 4, true>(v, p, tws, rB);
         smem_store<MAP_B>(sm, uB, v);
-        __syncthreads();
+        half_barrier(half);
         smem_load<MAP_A>(sm, uA, v);
-        stage<7, 4, true>(v, p, tile_hi, rA);
+        stage<7, 4, true>(v, p, tws, rA);
         if (p.scale2) {
 #pragma unroll
             for (int d = 0; d < 16; d++)
@@ -405,6 +433,7 @@ int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n,
         }
         return 0;
     }
+    if (dst.shard_log != 31) return fail(TSTWO_ERR_BAD_ARG, "row-sharded output needs poly_log >= %d", FAST_MIN_LOG);
     dim3 egrid((unsigned)((N + 255) / 256), (unsigned)n_cols);
     const bool in_place = (src.base == dst.base && src.table == dst.table && src.stride == dst.stride);
     if (!(in_place && L == n)) TS_LAUNCH(extend_kernel, egrid, 256, 0, src, dst, L, n);

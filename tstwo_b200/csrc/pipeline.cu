@@ -10,17 +10,34 @@
 using namespace tstwo;
 
 namespace {
+// scratch for coefficients the caller does not want to keep (they may not alias the evals they are extended into:
+// the coset passes of different CTAs read the same coefficients)
+uint32_t *g_coeff_scratch = nullptr;
+size_t g_coeff_scratch_words = 0;
+int coeff_scratch(size_t words, uint32_t **out)
+{
+    if (words > g_coeff_scratch_words) {
+        if (g_coeff_scratch) { TS_CUDA(cudaStreamSynchronize(ctx().stream)); TS_CUDA(cudaFree(g_coeff_scratch)); g_coeff_scratch = nullptr; g_coeff_scratch_words = 0; }
+        cudaError_t e = cudaMalloc(&g_coeff_scratch, words * 4);
+        if (e == cudaErrorMemoryAllocation) { cudaGetLastError(); return fail(TSTWO_ERR_OOM, "coefficient scratch out of memory"); }
+        TS_CUDA(e);
+        g_coeff_scratch_words = words;
+    }
+    *out = g_coeff_scratch;
+    return 0;
+}
+
 int lde_commit_device(const uint32_t *trace, int n_cols, int log_size, int log_blowup, TwiddleTree *t, uint32_t *coeffs,
                       uint32_t *evals, uint8_t *layers, uint8_t *root, uint32_t flags, bool sync_root)
 {
     const int ext = log_size + log_blowup;
     const uint64_t n = 1ull << log_size, ne = 1ull << ext;
-    // coefficients either kept (coeffs) or staged in the low half of each evals column (needs blowup >= 1)
+    int rc;
+    if (!coeffs && log_blowup > 0 && (rc = coeff_scratch((size_t)n_cols * n, &coeffs))) return rc;
     ColSet src = { trace, n, nullptr };
-    ColSet cf = coeffs ? ColSet{ coeffs, n, nullptr } : ColSet{ evals + (ne - n), ne, nullptr };
-    if (!coeffs && log_blowup == 0) cf = ColSet{ evals, ne, nullptr };
+    ColSet cf = coeffs ? ColSet{ coeffs, n, nullptr } : ColSet{ evals, ne, nullptr };   // blowup 0: in place in evals
     ColSet ev = { evals, ne, nullptr };
-    int rc = fft_interpolate(src, cf, n_cols, log_size, t, flags);
+    rc = fft_interpolate(src, cf, n_cols, log_size, t, flags);
     if (rc) return rc;
     rc = fft_evaluate(cf, log_size, ev, n_cols, ext, t, flags);
     if (rc) return rc;
@@ -66,10 +83,36 @@ int tstwo_lde_commit(tstwo_dptr trace, int n_cols, int log_size, int log_blowup,
     int rc = check_args(n_cols, log_size, log_blowup, tw, &t);
     if (rc) return rc;
     if (!trace || !evals) return fail(TSTWO_ERR_BAD_ARG, "null trace/evals");
-    if (!coeffs && log_blowup == 0 && trace != evals)
-        ;   // coefficients are produced directly in evals, then evaluated in place
     return lde_commit_device((const uint32_t *)trace, n_cols, log_size, log_blowup, t, (uint32_t *)coeffs, (uint32_t *)evals,
                              (uint8_t *)layers, root, flags, true);
+}
+
+// Column-sharded LDE for the multi-GPU path: this rank's n_cols columns are interpolated and extended, and the
+// evaluations are written grouped by destination rank, [n_shards][n_cols][2^(log_size+log_blowup)/n_shards], so that
+// one all-to-all (NCCL or peer stores) hands every rank all columns of its contiguous row range -- exactly the
+// column-major block the leaf-hash kernel reads.
+int tstwo_lde_columns_sharded(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, tstwo_dptr coeffs,
+                              tstwo_dptr evals, int n_shards, uint32_t flags)
+{
+    TS_REQUIRE_INIT();
+    TwiddleTree *t;
+    int rc = check_args(n_cols, log_size, log_blowup, tw, &t);
+    if (rc) return rc;
+    const int ext = log_size + log_blowup;
+    int sl = 0;
+    while ((1 << sl) < n_shards) sl++;
+    if (n_shards < 1 || (1 << sl) != n_shards || ext - sl < 11) return fail(TSTWO_ERR_BAD_ARG, "bad shard count %d", n_shards);
+    if (!trace || !evals) return fail(TSTWO_ERR_BAD_ARG, "null trace/evals");
+    const uint64_t n = 1ull << log_size, rows = 1ull << (ext - sl);
+    uint32_t *cf = (uint32_t *)coeffs;
+    if (!cf && (rc = coeff_scratch((size_t)n_cols * n, &cf))) return rc;
+    ColSet src = { (const uint32_t *)trace, n, nullptr };
+    ColSet cfs = { cf, n, nullptr };
+    ColSet ev = { (const uint32_t *)evals, rows, nullptr };
+    ev.shard_log = ext - sl;
+    ev.shard_adj = (uint64_t)n_cols * rows - rows;
+    if ((rc = fft_interpolate(src, cfs, n_cols, log_size, t, flags))) return rc;
+    return fft_evaluate(cfs, log_size, ev, n_cols, ext, t, flags);
 }
 
 // Host-resident trace: the columns are copied in chunks on a copy stream while the previous chunk's interpolate /
