@@ -216,12 +216,14 @@ def run_cuda(args):
         torch.cuda.synchronize()
 
     # ---- device-resident timing
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()          # nvidia-smi needs ~100s of ms to start; idle/ramp samples are filtered in stop()
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
-    sampler = ClockSampler(local)
     if rank == 0:
-        sampler.start()
+        sampler.rows.clear()     # keep only samples taken during the timed region
     l0 = L.tstwo_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()

@@ -11,7 +11,7 @@ def madd(a, b): return ((a.astype(np.uint64) + b) % P).astype(np.uint32)
 def msub(a, b): return ((a.astype(np.uint64) + P - b) % P).astype(np.uint32)
 def mmul(a, b): return ((a.astype(np.uint64) * b.astype(np.uint64)) % P).astype(np.uint32)
 
-W = 11  # window bits
+W0, W1 = 12, 10  # window bits: contiguous pass, strided passes
 
 def layer_table_offset(tree_log, n, i):
     """FFT layer i>=1 of a domain of log n: T_i has 2^(n-1-i) entries at offset 2^tree_log - 2^(n-i)."""
@@ -25,7 +25,7 @@ def twiddle(tree, tree_log, n, i, h):
     sign = ((h ^ (h >> 1)) & 1).astype(bool)
     return np.where(sign, (P - t1.astype(np.uint64)) % P, t1).astype(np.uint32)
 
-def run_pass(src, dst, n, src_mask, lo, j_min, j_max, tree, tree_log, inverse):
+def run_pass(src, dst, n, src_mask, lo, j_min, j_max, tree, tree_log, inverse, W):
     """One pass over the window of row bits [lo, lo+W).  src index = idx & src_mask (coset/zero-extension trick).
     Processes layers lo+j for j in [j_min, j_max)."""
     N = 1 << n
@@ -51,16 +51,20 @@ def run_pass(src, dst, n, src_mask, lo, j_min, j_max, tree, tree_log, inverse):
     dst[:] = v
 
 def plan(L):
-    """passes as (lo, j_min, j_max) in ascending layer order"""
+    """passes as (lo, j_min, j_max, W) in ascending layer order"""
     if L < 14: return None
-    if L <= 22: return [(0, 0, 11), (L - 11, 22 - L, 11)]
-    return [(0, 0, 11), (11, 0, 11), (L - 11, 33 - L, 11)]
+    out = [(0, 0, W0, W0)]
+    done = W0
+    while L - done > W1:
+        out.append((done, 0, W1, W1)); done += W1
+    out.append((L - W1, done - (L - W1), W1, W1))
+    return out
 
 def interpolate(vals, n, tree_itw, tree_log):
     buf = vals.copy()
-    for (lo, a, b) in plan(n):
+    for (lo, a, b, W) in plan(n):
         out = np.empty_like(buf)
-        run_pass(buf, out, n, (1 << n) - 1, lo, a, b, tree_itw, tree_log, True)
+        run_pass(buf, out, n, (1 << n) - 1, lo, a, b, tree_itw, tree_log, True, W)
         buf = out
     inv_n = pow(1 << n, 2**31 - 3, 2**31 - 1)
     return mmul(buf, np.full(1, inv_n, dtype=np.uint32))
@@ -68,15 +72,15 @@ def interpolate(vals, n, tree_itw, tree_log):
 def evaluate(coeffs, L, n, tree_tw, tree_log):
     src = coeffs
     mask = (1 << L) - 1
-    for (lo, a, b) in reversed(plan(L)):
+    for (lo, a, b, W) in reversed(plan(L)):
         out = np.empty(1 << n, dtype=np.uint32)
-        run_pass(src, out, n, mask, lo, a, b, tree_tw, tree_log, False)
+        run_pass(src, out, n, mask, lo, a, b, tree_tw, tree_log, False, W)
         src, mask = out, (1 << n) - 1
     return src
 
 if __name__ == "__main__":
     rng = np.random.default_rng(0)
-    for (L, blow, extra) in [(14, 0, 0), (14, 1, 0), (15, 2, 1), (16, 1, 0), (18, 1, 2)]:
+    for (L, blow, extra) in [(14, 0, 0), (14, 1, 0), (15, 2, 1), (16, 1, 0), (18, 1, 2), (22, 0, 0), (23, 0, 0)]:
         n = L + blow
         tree_log = n - 1 + extra
         init = orc.half_odds_index(tree_log)

@@ -86,7 +86,7 @@ int launch_coset_points(uint32_t *out2, int which, uint32_t init, int step_log, 
 cudaError_t elementwise_init();   // per-TU constant tables of elementwise.cu
 int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int log_size, const TwiddleTree *t, uint32_t flags);
 int fft_evaluate(const ColSet &src, int poly_log, const ColSet &dst, int n_cols, int domain_log, const TwiddleTree *t,
-                 uint32_t flags);
+                 uint32_t flags, const ColSet *work = nullptr);
 int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, int n_cols, uint8_t *out);
 
 }  // namespace tstwo

@@ -15,47 +15,73 @@
 
 namespace tstwo {
 
-constexpr int W = 11;
-constexpr int TILE_ROWS = 1 << W;
 constexpr int PASS_THREADS = 256;
-constexpr int HALF_UNITS = TILE_ROWS + TILE_ROWS / 16;       // uint4 units per half tile (1 pad unit per 16 rows)
-constexpr int TW_WORDS = TILE_ROWS;                          // twiddle heap: layer j at [2^(10-j), 2^(11-j))
-constexpr int SMEM_BYTES = 2 * HALF_UNITS * 16 + TW_WORDS * 4;
+constexpr int TILE_UNITS = 4096 + 256;                      // uint4 units per tile incl. padding (both shapes)
 constexpr int FAST_MIN_LOG = 14;
+
+// Tile shapes.  Both hold 4096 uint4 units (16 elements x 4 lanes per thread, 256 threads):
+//   CONTIG : 4096 rows = index bits [0,12) of 4 different columns (the 4 lanes), 12 layers, stages at bits 8/4/0
+//   STRIDED: 1024 rows = index bits [lo,lo+10) x 16 consecutive indices (4 thread groups x 4 lanes) of one column,
+//            10 layers, stages at bits 6/2/0 (the last stage applies only bits 1,0)
+template <bool STRIDED> struct Shape {
+    static constexpr int RHO = STRIDED ? 10 : 12;            // row bits per tile
+    static constexpr int SA = STRIDED ? 6 : 8, SB = STRIDED ? 2 : 4, SC = 0;
+    static constexpr int NLC = STRIDED ? 2 : 4;              // active layers of stage C
+    static constexpr int G = STRIDED ? 4 : 1;                // thread groups side by side in a row
+    static constexpr int TW_WORDS = 1 << RHO;
+};
 
 struct PassParams {
     ColSet src, dst;
     int n_cols;
     int n;                 // log size of the index space of dst
     uint32_t src_mask;     // src index = idx & src_mask (coset replication of zero-extended coefficients)
-    int lo;                // window = index bits [lo, lo+W)
-    int j_min;             // relative layers j in [j_min, W) are applied
+    int lo;                // window = index bits [lo, lo+RHO)
+    int j_min;             // relative layers j in [j_min, RHO) are applied
     const uint32_t *tw2;   // pre-doubled twiddle (or inverse twiddle) tree
     uint32_t tree_len;     // 2^root_log
     uint32_t scale2;       // 2/2^n after the last inverse layer, or 0
+    uint32_t zero;         // run-time 0 (forces IADD3 for half of the adds, see m31::butterfly_z)
 };
 
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
+}
+
 // Stage all twiddles of the tile in shared memory as a heap: relative layer j (absolute i = lo + j) needs
-// T_i[(tile_hi << (10-j)) + r], r < 2^(10-j); it is stored at tws[2^(10-j) + r].  cp.async, 8 words per thread.
+// T_i[(tile_hi << (RHO-1-j)) + r], r < 2^(RHO-1-j); it is stored at tws[2^(RHO-1-j) + r].  Layers of >= 4 entries are
+// fetched with 16-byte cp.async (source ranges are aligned to their size), the three small ones word by word.
+template <bool STRIDED>
 __device__ __forceinline__ void tile_twiddles_async(uint32_t *tws, const PassParams &p, uint32_t tile_hi, int tid)
 {
+    constexpr int RHO = Shape<STRIDED>::RHO;
 #pragma unroll
-    for (int e = tid; e < TW_WORDS; e += PASS_THREADS) {
-        if (e == 0) continue;
-        const int lg = 31 - __clz(e);            // 10 - j
-        const int j = (W - 1) - lg;
-        const int i = p.lo + j;
-        if (j < p.j_min || i < 1) continue;      // the circle layer derives its twiddles from T_1
-        const uint32_t r = (uint32_t)e - (1u << lg);
-        const uint32_t *g = p.tw2 + (p.tree_len - (1u << (p.n - i))) + (tile_hi << lg) + r;
-        const uint32_t sa = (uint32_t)__cvta_generic_to_shared(tws + e);
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(g));
+    for (int e = 4 * tid; e < (1 << RHO); e += 4 * PASS_THREADS) {
+        if (e == 0) {
+            // heap[1] = top layer (1 entry), heap[2..3] = next layer (2 entries)
+            for (int ee = 1; ee < 4; ee++) {
+                const int lg = ee >> 1;               // 0 or 1
+                const int j = (RHO - 1) - lg, i = p.lo + j;
+                if (j < p.j_min || i < 1) continue;
+                cp_async4(tws + ee, p.tw2 + (p.tree_len - (1u << (p.n - i))) + (tile_hi << lg) + (ee - (1 << lg)));
+            }
+            continue;
+        }
+        const int lg = 31 - __clz(e);
+        const int j = (RHO - 1) - lg, i = p.lo + j;
+        if (j < p.j_min || i < 1) continue;           // the circle layer derives its twiddles from T_1
+        cp_async16(tws + e, p.tw2 + (p.tree_len - (1u << (p.n - i))) + (tile_hi << lg) + (e - (1 << lg)));
     }
     asm volatile("cp.async.commit_group;");
 }
 
 // One radix-16 stage on v[16][4]: digit bit k <-> row bit S+k, layers j = S+k for k in [0, NL).
-template <int S, int NL, bool INV>
+template <int RHO, int S, int NL, bool INV>
 __device__ __forceinline__ void stage(uint32_t (&v)[16][4], const PassParams &p, const uint32_t *tws, int rbase)
 {
 #pragma unroll
@@ -66,7 +92,7 @@ __device__ __forceinline__ void stage(uint32_t (&v)[16][4], const PassParams &p,
         const int cnt = 8 >> k;
         uint32_t t[8];
         if (p.lo + j >= 1) {
-            const uint32_t *q = tws + (1 << (W - 1 - j)) + (rbase >> (j + 1));
+            const uint32_t *q = tws + (1 << (RHO - 1 - j)) + (rbase >> (j + 1));
             if (cnt == 8) {
                 uint4 a = *reinterpret_cast<const uint4 *>(q), b = *reinterpret_cast<const uint4 *>(q + 4);
                 t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w;
@@ -79,7 +105,7 @@ __device__ __forceinline__ void stage(uint32_t (&v)[16][4], const PassParams &p,
             } else t[0] = q[0];
         } else {
             // circle layer (j == 0, k == 0): T_1 entries (x0, y0, x1, y1) of this thread's 16 rows -> [y,-y,-x,x]
-            uint4 a = *reinterpret_cast<const uint4 *>(tws + (1 << (W - 2)) + (rbase >> 2));
+            uint4 a = *reinterpret_cast<const uint4 *>(tws + (1 << (RHO - 2)) + (rbase >> 2));
             const uint32_t P2 = 0xfffffffeu;
             t[0] = a.y; t[1] = P2 - a.y; t[2] = P2 - a.x; t[3] = a.x;
             t[4] = a.w; t[5] = P2 - a.w; t[6] = P2 - a.z; t[7] = a.z;
@@ -97,75 +123,83 @@ __device__ __forceinline__ void stage(uint32_t (&v)[16][4], const PassParams &p,
     }
 }
 
+// Thread -> rows maps.  rg = row group of the thread; digit d = 0..15 selects one of its 16 rows.
+//   A: digit = row bits [SA, SA+4)   rows rg + d * 2^SA
+//   B: digit = row bits [SB, SB+4)   rows (rg >> SB) * 2^(SB+4) + (rg & (2^SB - 1)) + d * 2^SB
+//   C: digit = row bits [0, 4)       rows 16 rg + d
 enum { MAP_A = 0, MAP_B = 1, MAP_C = 2 };
-template <int MAP> __device__ __forceinline__ int map_rbase(int rg)
+template <bool STRIDED, int MAP> __device__ __forceinline__ int map_rbase(int rg)
 {
-    return MAP == MAP_A ? rg : MAP == MAP_B ? ((rg >> 3) * 128 + (rg & 7)) : rg * 16;
+    constexpr int SB = Shape<STRIDED>::SB;
+    return MAP == MAP_A ? rg : MAP == MAP_B ? ((rg >> SB) << (SB + 4)) + (rg & ((1 << SB) - 1)) : rg * 16;
 }
-template <int MAP> __device__ __forceinline__ int map_row(int rbase, int d)
+template <bool STRIDED, int MAP> __device__ __forceinline__ int map_row(int rbase, int d)
 {
-    return MAP == MAP_A ? rbase + d * 128 : MAP == MAP_B ? rbase + d * 8 : rbase + d;
+    return MAP == MAP_A ? rbase + (d << Shape<STRIDED>::SA) : MAP == MAP_B ? rbase + (d << Shape<STRIDED>::SB) : rbase + d;
 }
-// shared-memory unit (16 B) of row r inside a half tile: r + (r>>4); conflict-free for all three maps
-template <int MAP> __device__ __forceinline__ int map_unit0(int rg)
+// Shared-memory unit (16 B) of (row r, group g): G*r + g + G*(r>>4) -- one pad row per 16 rows.  Every quarter warp
+// (8 lanes) then touches 8 distinct 16-byte bank groups in all three maps of both shapes ("exchange").
+template <bool STRIDED, int MAP> __device__ __forceinline__ int map_unit0(int rg, int g)
 {
-    const int r = map_rbase<MAP>(rg);
-    return r + (r >> 4);
+    constexpr int G = Shape<STRIDED>::G;
+    const int r = map_rbase<STRIDED, MAP>(rg);
+    return G * r + g + G * (r >> 4);
 }
-template <int MAP> __device__ __forceinline__ constexpr int map_unit_off(int d)
+template <bool STRIDED, int MAP> __device__ __forceinline__ constexpr int map_unit_off(int d)
 {
-    return MAP == MAP_A ? d * 136 : MAP == MAP_B ? 8 * d + (d >> 1) : d;
+    // row offset o(d) of digit d, unit offset G * (o + (o >> 4)) (o never carries into the pad of rbase)
+    return Shape<STRIDED>::G * (MAP == MAP_A ? (d << Shape<STRIDED>::SA) + ((d << Shape<STRIDED>::SA) >> 4)
+                                : MAP == MAP_B ? (d << Shape<STRIDED>::SB) + ((d << Shape<STRIDED>::SB) >> 4)
+                                               : d);
 }
-template <int MAP> __device__ __forceinline__ void smem_store(uint4 *sm, int u0, const uint32_t (&v)[16][4])
+template <bool STRIDED, int MAP> __device__ __forceinline__ void smem_store(uint4 *sm, int u0, const uint32_t (&v)[16][4])
 {
 #pragma unroll
-    for (int d = 0; d < 16; d++) sm[u0 + map_unit_off<MAP>(d)] = make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]);
+    for (int d = 0; d < 16; d++) sm[u0 + map_unit_off<STRIDED, MAP>(d)] = make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]);
 }
-template <int MAP> __device__ __forceinline__ void smem_load(const uint4 *sm, int u0, uint32_t (&v)[16][4])
+template <bool STRIDED, int MAP> __device__ __forceinline__ void smem_load(const uint4 *sm, int u0, uint32_t (&v)[16][4])
 {
 #pragma unroll
     for (int d = 0; d < 16; d++) {
-        uint4 a = sm[u0 + map_unit_off<MAP>(d)];
+        uint4 a = sm[u0 + map_unit_off<STRIDED, MAP>(d)];
         v[d][0] = a.x; v[d][1] = a.y; v[d][2] = a.z; v[d][3] = a.w;
     }
 }
-__device__ __forceinline__ void half_barrier(int half)
-{
-    if (half) asm volatile("bar.sync 2, 128;" ::: "memory");
-    else asm volatile("bar.sync 1, 128;" ::: "memory");
-}
 
-// global I/O.  STRIDED: lanes = index bits [0,3) of one column (blockIdx.y); CONTIG: lanes = 8 columns.
+// global I/O.  STRIDED: the tile is rows x 16 consecutive indices of column blockIdx.y; CONTIG: the 4 lanes are
+// columns 4*blockIdx.y .. +3.  All 64-bit address arithmetic is done once per thread (tile base); the 16 digit
+// offsets are compile-time (CONTIG) or a single runtime stride (STRIDED).  Only the contiguous pass honours the
+// row-sharded layout of ColSet (a 4096-row tile never straddles a shard).
 template <int MAP, bool STRIDED>
-__device__ __forceinline__ void gmem_load(const PassParams &p, uint32_t tile_hi, uint32_t mid, int rbase, int half,
+__device__ __forceinline__ void gmem_load(const PassParams &p, uint32_t tile_hi, uint32_t mid, int rbase, int g,
                                           uint32_t (&v)[16][4])
 {
+    constexpr int RHO = Shape<STRIDED>::RHO;
     if (STRIDED) {
-        const uint32_t *col = p.src.col(blockIdx.y);
-        const uint32_t fixed = (tile_hi << (p.lo + W)) | (mid << 3) | (half << 2);
+        const uint32_t base = (((tile_hi << (p.lo + RHO)) | (mid << 4) | (g << 2)) & p.src_mask) | ((uint32_t)rbase << p.lo);
+        const uint4 *ptr = reinterpret_cast<const uint4 *>(p.src.col(blockIdx.y) + base);
+        const uint32_t st = 1u << (p.lo + (MAP == MAP_A ? Shape<STRIDED>::SA : MAP == MAP_B ? Shape<STRIDED>::SB : 0) - 2);  // uint4 units
 #pragma unroll
         for (int d = 0; d < 16; d++) {
-            uint32_t idx = (fixed | ((uint32_t)map_row<MAP>(rbase, d) << p.lo)) & p.src_mask;
-            uint4 a = __ldg(reinterpret_cast<const uint4 *>(col + p.src.off(idx)));
+            uint4 a = __ldcg(ptr + (size_t)d * st);
             v[d][0] = a.x; v[d][1] = a.y; v[d][2] = a.z; v[d][3] = a.w;
         }
     } else {
-        const int c0 = blockIdx.y * 8 + half * 4;
+        const int c0 = blockIdx.y * 4;
+        const uint64_t tile_off = p.src.off((tile_hi << RHO) & p.src_mask) + (uint32_t)rbase;
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             if (c0 + q < p.n_cols) {
-                const uint32_t *col = p.src.col(c0 + q);
+                const uint32_t *ptr = p.src.col(c0 + q) + tile_off;
                 if (MAP == MAP_C) {
-                    const uint64_t idx = p.src.off(((tile_hi << W) | (uint32_t)rbase) & p.src_mask);
 #pragma unroll
                     for (int dd = 0; dd < 4; dd++) {
-                        uint4 a = __ldg(reinterpret_cast<const uint4 *>(col + idx + 4 * dd));
+                        uint4 a = __ldg(reinterpret_cast<const uint4 *>(ptr) + dd);
                         v[4 * dd][q] = a.x; v[4 * dd + 1][q] = a.y; v[4 * dd + 2][q] = a.z; v[4 * dd + 3][q] = a.w;
                     }
                 } else {
 #pragma unroll
-                    for (int d = 0; d < 16; d++)
-                        v[d][q] = __ldcg(col + p.src.off(((tile_hi << W) | (uint32_t)map_row<MAP>(rbase, d)) & p.src_mask));
+                    for (int d = 0; d < 16; d++) v[d][q] = __ldcg(ptr + map_row<STRIDED, MAP>(0, d));
                 }
             } else {
 #pragma unroll
@@ -175,93 +209,92 @@ __device__ __forceinline__ void gmem_load(const PassParams &p, uint32_t tile_hi,
     }
 }
 template <int MAP, bool STRIDED>
-__device__ __forceinline__ void gmem_store(const PassParams &p, uint32_t tile_hi, uint32_t mid, int rbase, int half,
+__device__ __forceinline__ void gmem_store(const PassParams &p, uint32_t tile_hi, uint32_t mid, int rbase, int g,
                                            const uint32_t (&v)[16][4])
 {
+    constexpr int RHO = Shape<STRIDED>::RHO;
     if (STRIDED) {
-        uint32_t *col = p.dst.col(blockIdx.y);
-        const uint32_t fixed = (tile_hi << (p.lo + W)) | (mid << 3) | (half << 2);
+        const uint32_t base = (tile_hi << (p.lo + RHO)) | (mid << 4) | (g << 2) | ((uint32_t)rbase << p.lo);
+        uint4 *ptr = reinterpret_cast<uint4 *>(p.dst.col(blockIdx.y) + base);
+        const uint32_t st = 1u << (p.lo + (MAP == MAP_A ? Shape<STRIDED>::SA : MAP == MAP_B ? Shape<STRIDED>::SB : 0) - 2);
 #pragma unroll
-        for (int d = 0; d < 16; d++) {
-            uint32_t idx = fixed | ((uint32_t)map_row<MAP>(rbase, d) << p.lo);
-            __stcg(reinterpret_cast<uint4 *>(col + p.dst.off(idx)), make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]));
-        }
+        for (int d = 0; d < 16; d++) __stcg(ptr + (size_t)d * st, make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]));
     } else {
-        const int c0 = blockIdx.y * 8 + half * 4;
+        const int c0 = blockIdx.y * 4;
+        const uint64_t tile_off = p.dst.off(tile_hi << RHO) + (uint32_t)rbase;
 #pragma unroll
         for (int q = 0; q < 4; q++) {
             if (c0 + q < p.n_cols) {
-                uint32_t *col = p.dst.col(c0 + q);
+                uint32_t *ptr = p.dst.col(c0 + q) + tile_off;
                 if (MAP == MAP_C) {
-                    const uint64_t idx = p.dst.off((tile_hi << W) | (uint32_t)rbase);
 #pragma unroll
                     for (int dd = 0; dd < 4; dd++)
-                        __stcg(reinterpret_cast<uint4 *>(col + idx + 4 * dd),
+                        __stcg(reinterpret_cast<uint4 *>(ptr) + dd,
                                make_uint4(v[4 * dd][q], v[4 * dd + 1][q], v[4 * dd + 2][q], v[4 * dd + 3][q]));
                 } else {
 #pragma unroll
-                    for (int d = 0; d < 16; d++) __stcg(col + p.dst.off((tile_hi << W) | (uint32_t)map_row<MAP>(rbase, d)), v[d][q]);
+                    for (int d = 0; d < 16; d++) __stcg(ptr + map_row<STRIDED, MAP>(0, d), v[d][q]);
                 }
             }
         }
     }
 }
 
-// 256 threads = two independent half tiles (warps 0-3 / 4-7, 4 lanes each) that share the tile's twiddles and
-// synchronise separately (named barriers), so one half's exchange overlaps the other half's butterflies.
 template <bool INV, bool STRIDED>
 __global__ void __launch_bounds__(PASS_THREADS, 2) fft_pass_kernel(const PassParams p)
 {
-    extern __shared__ uint4 sm_all[];
-    const int tid = threadIdx.x, half = tid >> 7, rg = tid & 127;
-    uint4 *sm = sm_all + half * HALF_UNITS;
-    uint32_t *tws = reinterpret_cast<uint32_t *>(sm_all + 2 * HALF_UNITS);
+    using SH = Shape<STRIDED>;
+    constexpr int RHO = SH::RHO;
+    extern __shared__ uint4 sm[];
+    uint32_t *tws = reinterpret_cast<uint32_t *>(sm + TILE_UNITS);
+    const int tid = threadIdx.x;
+    const int g = STRIDED ? (tid & 3) : 0, rg = STRIDED ? (tid >> 2) : tid;
     uint32_t tile_hi, mid;
     if (STRIDED) {
-        tile_hi = blockIdx.x >> (p.lo - 3);
-        mid = blockIdx.x & ((1u << (p.lo - 3)) - 1);
+        tile_hi = blockIdx.x >> (p.lo - 4);
+        mid = blockIdx.x & ((1u << (p.lo - 4)) - 1);
     } else {
         tile_hi = blockIdx.x;
         mid = 0;
     }
-    tile_twiddles_async(tws, p, tile_hi, tid);
+    tile_twiddles_async<STRIDED>(tws, p, tile_hi, tid);
     uint32_t v[16][4];
-    const int rA = map_rbase<MAP_A>(rg), rB = map_rbase<MAP_B>(rg), rC = map_rbase<MAP_C>(rg);
-    const int uA = map_unit0<MAP_A>(rg), uB = map_unit0<MAP_B>(rg), uC = map_unit0<MAP_C>(rg);
+    const int rA = map_rbase<STRIDED, MAP_A>(rg), rB = map_rbase<STRIDED, MAP_B>(rg), rC = map_rbase<STRIDED, MAP_C>(rg);
+    const int uA = map_unit0<STRIDED, MAP_A>(rg, g), uB = map_unit0<STRIDED, MAP_B>(rg, g), uC = map_unit0<STRIDED, MAP_C>(rg, g);
     if (!INV) {
-        gmem_load<MAP_A, STRIDED>(p, tile_hi, mid, rA, half, v);
+        gmem_load<MAP_A, STRIDED>(p, tile_hi, mid, rA, g, v);
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();
-        stage<7, 4, false>(v, p, tws, rA);
-        smem_store<MAP_A>(sm, uA, v);
-        half_barrier(half);
-        smem_load<MAP_B>(sm, uB, v);
-        stage<3, 4, false>(v, p, tws, rB);
-        smem_store<MAP_B>(sm, uB, v);
-        half_barrier(half);
-        smem_load<MAP_C>(sm, uC, v);
-        stage<0, 3, false>(v, p, tws, rC);
-        gmem_store<MAP_C, STRIDED>(p, tile_hi, mid, rC, half, v);
+        stage<RHO, SH::SA, 4, false>(v, p, tws, rA);
+        smem_store<STRIDED, MAP_A>(sm, uA, v);
+        __syncthreads();
+        smem_load<STRIDED, MAP_B>(sm, uB, v);
+        stage<RHO, SH::SB, 4, false>(v, p, tws, rB);
+        smem_store<STRIDED, MAP_B>(sm, uB, v);
+        __syncthreads();
+        smem_load<STRIDED, MAP_C>(sm, uC, v);
+        stage<RHO, SH::SC, SH::NLC, false>(v, p, tws, rC);
+        gmem_store<MAP_C, STRIDED>(p, tile_hi, mid, rC, g, v);
     } else {
-        gmem_load<MAP_C, STRIDED>(p, tile_hi, mid, rC, half, v);
+        gmem_load<MAP_C, STRIDED>(p, tile_hi, mid, rC, g, v);
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();
-        stage<0, 3, true>(v, p, tws, rC);
-        smem_store<MAP_C>(sm, uC, v);
-        half_barrier(half);
-        smem_load<MAP_B>(sm, uB, v);
-        stage<3, 4, true>(v, p, tws, rB);
-        smem_store<MAP_B>(sm, uB, v);
-        half_barrier(half);
-        smem_load<MAP_A>(sm, uA, v);
-        stage<7, 4, true>(v, p, tws, rA);
+        stage<RHO, SH::SC, SH::NLC, true>(v, p, tws, rC);
+        smem_store<STRIDED, MAP_C>(sm, uC, v);
+        __syncthreads();
+        smem_load<STRIDED, MAP_B>(sm, uB, v);
+        stage<RHO, SH::SB, 4, true>(v, p, tws, rB);
+        smem_store<STRIDED, MAP_B>(sm, uB, v);
+        __syncthreads();
+        smem_load<STRIDED, MAP_A>(sm, uA, v);
+        stage<RHO, SH::SA, 4, true>(v, p, tws, rA);
         if (p.scale2) {
 #pragma unroll
             for (int d = 0; d < 16; d++)
 #pragma unroll
                 for (int q = 0; q < 4; q++) v[d][q] = m31::mul2(v[d][q], p.scale2);
         }
-        gmem_store<MAP_A, STRIDED>(p, tile_hi, mid, rA, half, v);
+        gmem_store<MAP_A, STRIDED>(p, tile_hi, mid, rA, g, v);
     }
 }
 
@@ -337,36 +370,43 @@ __global__ void small_interp_kernel(ColSet cols, int n, uint32_t xi2, uint32_t y
 static bool g_force_naive = false;
 static bool g_smem_attr_set = false;
 
+static int smem_bytes(bool strided) { return TILE_UNITS * 16 + (strided ? Shape<true>::TW_WORDS : Shape<false>::TW_WORDS) * 4; }
+
 static int ensure_smem_attr()
 {
     if (g_smem_attr_set) return 0;
-    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(false)));
+    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(true)));
+    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(false)));
+    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(true)));
     g_smem_attr_set = true;
     return 0;
 }
 
 struct Pass { int lo, j_min; };
-// passes in ascending layer order for L real layers (see scripts/proto_fft.py)
-static int plan_passes(int L, Pass out[3])
+// passes in ascending layer order for L real layers (scripts/proto_fft.py): one contiguous 12-layer pass, then
+// strided 10-layer windows; the top window is aligned to L and skips the layers already done.
+constexpr int W0 = Shape<false>::RHO, W1 = Shape<true>::RHO;
+static int plan_passes(int L, Pass out[4])
 {
-    if (L <= 22) { out[0] = { 0, 0 }; out[1] = { L - W, 2 * W - L }; return 2; }
-    out[0] = { 0, 0 }; out[1] = { W, 0 }; out[2] = { L - W, 3 * W - L };
-    return 3;
+    int np = 0, done = W0;
+    out[np++] = { 0, 0 };
+    while (L - done > W1) { out[np++] = { done, 0 }; done += W1; }
+    out[np++] = { L - W1, done - (L - W1) };
+    return np;
 }
 
 static int launch_pass(bool inverse, const PassParams &p)
 {
     if (p.lo == 0) {
-        dim3 grid(1u << (p.n - W), (unsigned)((p.n_cols + 7) / 8));
-        if (inverse) TS_LAUNCH((fft_pass_kernel<true, false>), grid, PASS_THREADS, SMEM_BYTES, p);
-        else TS_LAUNCH((fft_pass_kernel<false, false>), grid, PASS_THREADS, SMEM_BYTES, p);
+        dim3 grid(1u << (p.n - W0), (unsigned)((p.n_cols + 3) / 4));
+        if (inverse) TS_LAUNCH((fft_pass_kernel<true, false>), grid, PASS_THREADS, smem_bytes(false), p);
+        else TS_LAUNCH((fft_pass_kernel<false, false>), grid, PASS_THREADS, smem_bytes(false), p);
     } else {
-        dim3 grid(1u << (p.n - W - 3), (unsigned)p.n_cols);
-        if (inverse) TS_LAUNCH((fft_pass_kernel<true, true>), grid, PASS_THREADS, SMEM_BYTES, p);
-        else TS_LAUNCH((fft_pass_kernel<false, true>), grid, PASS_THREADS, SMEM_BYTES, p);
+        if (p.src.shard_log != 31 || p.dst.shard_log != 31) return fail(TSTWO_ERR_BAD_ARG, "strided FFT pass on a row-sharded column set");
+        dim3 grid(1u << (p.n - W1 - 4), (unsigned)p.n_cols);
+        if (inverse) TS_LAUNCH((fft_pass_kernel<true, true>), grid, PASS_THREADS, smem_bytes(true), p);
+        else TS_LAUNCH((fft_pass_kernel<false, true>), grid, PASS_THREADS, smem_bytes(true), p);
     }
     return 0;
 }
@@ -383,13 +423,13 @@ int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int n, con
     if (n >= FAST_MIN_LOG && !g_force_naive) {
         int rc = ensure_smem_attr();
         if (rc) return rc;
-        Pass ps[3];
+        Pass ps[4];
         int np = plan_passes(n, ps);
         for (int k = 0; k < np; k++) {
             PassParams p;
             p.src = (k == 0) ? src : dst; p.dst = dst; p.n_cols = n_cols; p.n = n; p.src_mask = (uint32_t)(N - 1);
             p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.tw2 = t->itw2; p.tree_len = tree_len;
-            p.scale2 = (k == np - 1) ? inv_n2 : 0;
+            p.scale2 = (k == np - 1) ? inv_n2 : 0; p.zero = 0;
             rc = launch_pass(true, p);
             if (rc) return rc;
         }
@@ -412,22 +452,26 @@ int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int n, con
     return 0;
 }
 
-int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n, const TwiddleTree *t, uint32_t flags)
+// `work`: plain (non-sharded) column set the strided passes run in; equals dst unless dst is row-sharded, in which
+// case only the last (contiguous) pass writes dst.
+int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n, const TwiddleTree *t, uint32_t flags,
+                 const ColSet *work_in)
 {
     if (n_cols <= 0) return 0;
+    const ColSet &work = work_in ? *work_in : dst;
     const uint32_t tree_len = 1u << t->root_log;
     const uint64_t N = 1ull << n;
     if (L >= FAST_MIN_LOG && !g_force_naive) {
         int rc = ensure_smem_attr();
         if (rc) return rc;
-        Pass ps[3];
+        Pass ps[4];
         int np = plan_passes(L, ps);
         for (int k = np - 1; k >= 0; k--) {
             PassParams p;
             const bool first = (k == np - 1);
-            p.src = first ? src : dst; p.dst = dst; p.n_cols = n_cols; p.n = n;
+            p.src = first ? src : work; p.dst = (k == 0) ? dst : work; p.n_cols = n_cols; p.n = n;
             p.src_mask = first ? (uint32_t)((1ull << L) - 1) : (uint32_t)(N - 1);
-            p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.tw2 = t->tw2; p.tree_len = tree_len; p.scale2 = 0;
+            p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.tw2 = t->tw2; p.tree_len = tree_len; p.scale2 = 0; p.zero = 0;
             rc = launch_pass(false, p);
             if (rc) return rc;
         }

@@ -63,6 +63,22 @@ __device__ __forceinline__ void ibutterfly(uint32_t &v0, uint32_t &v1, uint32_t 
     v1 = mul2(sub(a, b), it2);
 }
 
+// Pipe-balanced butterflies for the FFT passes.  On sm_100 ptxas turns every two-input add into IMAD.IADD (FMA pipe),
+// which is also where IMAD.WIDE (~6 issue cycles) lives; the ALU pipe (LEA.HI, VIADDMNMX) is then under-used
+// (profiles/r01).  `z` is a run-time zero (kernel argument): a + b + z can only be an IADD3, i.e. an ALU-pipe add.
+__device__ __forceinline__ void butterfly_z(uint32_t &v0, uint32_t &v1, uint32_t t2, uint32_t z)
+{
+    uint32_t m = mul2(v1, t2), a = v0;
+    v0 = csub(a + m + z);
+    v1 = sub(a, m);
+}
+__device__ __forceinline__ void ibutterfly_z(uint32_t &v0, uint32_t &v1, uint32_t it2, uint32_t z)
+{
+    uint32_t a = v0, b = v1;
+    v0 = csub(a + b + z);
+    v1 = mul2(sub(a, b), it2);
+}
+
 // ---- CM31 = M31[i]/(i^2+1)  (fields/cm31.ts) ----
 struct CM { uint32_t re, im; };
 __device__ __forceinline__ CM cadd(CM a, CM b) { return { add(a.re, b.re), add(a.im, b.im) }; }

@@ -101,18 +101,22 @@ int tstwo_lde_columns_sharded(tstwo_dptr trace, int n_cols, int log_size, int lo
     const int ext = log_size + log_blowup;
     int sl = 0;
     while ((1 << sl) < n_shards) sl++;
-    if (n_shards < 1 || (1 << sl) != n_shards || ext - sl < 11) return fail(TSTWO_ERR_BAD_ARG, "bad shard count %d", n_shards);
+    if (n_shards < 1 || (1 << sl) != n_shards || ext - sl < 12) return fail(TSTWO_ERR_BAD_ARG, "bad shard count %d", n_shards);
     if (!trace || !evals) return fail(TSTWO_ERR_BAD_ARG, "null trace/evals");
     const uint64_t n = 1ull << log_size, rows = 1ull << (ext - sl);
-    uint32_t *cf = (uint32_t *)coeffs;
-    if (!cf && (rc = coeff_scratch((size_t)n_cols * n, &cf))) return rc;
+    // scratch: [coefficients (unless kept by the caller)] [plain evaluations the strided passes work in]
+    const uint64_t ne = 1ull << ext;
+    uint32_t *scr;
+    if ((rc = coeff_scratch((size_t)n_cols * (n + ne), &scr))) return rc;
+    uint32_t *cf = coeffs ? (uint32_t *)coeffs : scr;
+    ColSet work = { scr + (size_t)n_cols * n, ne, nullptr };
     ColSet src = { (const uint32_t *)trace, n, nullptr };
     ColSet cfs = { cf, n, nullptr };
     ColSet ev = { (const uint32_t *)evals, rows, nullptr };
     ev.shard_log = ext - sl;
     ev.shard_adj = (uint64_t)n_cols * rows - rows;
     if ((rc = fft_interpolate(src, cfs, n_cols, log_size, t, flags))) return rc;
-    return fft_evaluate(cfs, log_size, ev, n_cols, ext, t, flags);
+    return fft_evaluate(cfs, log_size, ev, n_cols, ext, t, flags, &work);
 }
 
 // Host-resident trace: the columns are copied in chunks on a copy stream while the previous chunk's interpolate /
