@@ -170,11 +170,18 @@ def run_cuda(args):
     chk(L.tstwo_twiddles_precompute(1 << (31 - (ext - 1) - 2), ext - 1, C.byref(tw)))
 
     # synthetic trace: uniform random canonical M31, column c of the job uses stream c
-    g = torch.Generator(device=dev); g.manual_seed(0x5EED0003 + rank)
-    trace = torch.randint(0, P, (lc, n), dtype=torch.int32, device=dev, generator=g)
-    coeffs = torch.empty((lc, n), dtype=torch.int32, device=dev)
-    evals = torch.empty((lc, ne), dtype=torch.int32, device=dev)
+    # generated in 8 column blocks with fixed seeds so that every world size <= 8 sees the same job (same root)
+    nblk = 8 if n_cols % 8 == 0 else 1
+    bs = n_cols // nblk
+    assert lc % bs == 0
+    trace = torch.empty((lc, n), dtype=torch.int32, device=dev)
+    for k in range(lc // bs):
+        g = torch.Generator(device=dev); g.manual_seed(0x5EED0003 + rank * (lc // bs) + k)
+        trace[k * bs:(k + 1) * bs] = torch.randint(0, P, (bs, n), dtype=torch.int32, device=dev, generator=g)
     root = (C.c_uint8 * 32)()
+    if world == 1:
+        coeffs = torch.empty((lc, n), dtype=torch.int32, device=dev)
+        evals = torch.empty((lc, ne), dtype=torch.int32, device=dev)
 
     if world == 1:
         layers = torch.empty(((2 << ext) - 1) * 8, dtype=torch.int32, device=dev)
@@ -184,29 +191,15 @@ def run_cuda(args):
                                    layers.data_ptr(), root, 0))
         launches_per_step = None
     else:
-        sub = ext - (world.bit_length() - 1)      # log rows per rank
-        rows = 1 << sub
-        recv = torch.empty((n_cols, rows), dtype=torch.int32, device=dev)
-        layers = torch.empty(((2 << sub) - 1) * 8, dtype=torch.int32, device=dev)
-        roots = torch.empty((world, 8), dtype=torch.int32, device=dev)
-        top = torch.empty(((2 * world) - 1) * 8, dtype=torch.int32, device=dev)
-        col_ptrs = _lib.dptr_array([recv.data_ptr() + 4 * rows * c for c in range(n_cols)])
-        col_logs = (C.c_int * n_cols)(*([sub] * n_cols))
+        from tstwo_b200.distributed import CudaShardOps, ShardedCommit
+        sc = ShardedCommit(CudaShardOps(local, stream), n_cols, log, blow)
+        trace_flat = trace.view(-1)
+        holder = {}
 
         def step():
-            # column-sharded LDE; evals come out grouped by destination rank: [dest][local col][rows]
-            chk(L.tstwo_lde_columns_sharded(trace.data_ptr(), lc, log, blow, tw.value, coeffs.data_ptr(), evals.data_ptr(),
-                                            world, 0))
-            dist.all_to_all_single(recv.view(-1), evals.view(-1))          # NVLink all-to-all: recv = [src][local col][rows]
-            chk(L.tstwo_merkle_commit(col_ptrs, col_logs, n_cols, layers.data_ptr(), None))
-            dist.all_gather_into_tensor(roots.view(-1), layers[:8])
-            if rank == 0:
-                prev = roots.data_ptr()
-                for k in range(world.bit_length() - 2, -1, -1):
-                    dst = top.data_ptr() + 32 * ((1 << k) - 1)
-                    chk(L.tstwo_merkle_commit_layer(k, prev, None, 0, dst))
-                    prev = dst
-                chk(L.tstwo_download(root, top.data_ptr(), 32))
+            r = sc.step(trace_flat)
+            if r is not None:
+                holder["root"] = r
             else:
                 chk(L.tstwo_sync())
 
@@ -240,7 +233,7 @@ def run_cuda(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     value = n_cols * n / (ms * 1e-3)
-    root_hex = bytes(root).hex()
+    root_hex = bytes(root).hex() if world == 1 else (holder.get("root", b"").hex() if rank == 0 else "")
 
     # ---- per-kernel timing (1 GPU): the roofline of the dominant kernel, measured live with CUDA events
     roof, kernels = None, None

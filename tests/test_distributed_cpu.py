@@ -1,0 +1,92 @@
+"""Host protocol of the multi-GPU path (tstwo_b200/distributed.py) on CPU: world_size 2 and 4 over gloo, with the
+oracle standing in for the device work.  Checks the shard layout, the all-to-all re-sharding and the top-of-tree
+combine against the single-process oracle root."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+P = 2147483647
+LOG, BLOW, N_COLS = 13, 1, 8
+
+
+class OracleShardOps:
+    """CPU provider with the interface of CudaShardOps (test infrastructure only)."""
+
+    def __init__(self):
+        import oracle
+        self.orc = oracle
+
+    def empty(self, n_words):
+        return torch.zeros(n_words, dtype=torch.int32)
+
+    def twiddles(self, ext):
+        init, log = self.orc.canonic_half_coset(ext)
+        return self.orc.precompute_twiddles(init, log)
+
+    def lde_sharded(self, trace, n_cols, log_size, log_blowup, tw, coeffs, evals, n_shards):
+        t = trace.numpy().view(np.uint32).reshape(n_cols, 1 << log_size)
+        cf, ev, _ = self.orc.lde_commit(t, log_blowup, tw[0], tw[1], want_coeffs=True, want_layers=False)
+        rows = ev.shape[1] // n_shards
+        out = np.stack([ev[:, s * rows:(s + 1) * rows] for s in range(n_shards)])       # [G][lc][rows]
+        evals.numpy().view(np.uint32)[:] = out.reshape(-1)
+        if coeffs is not None:
+            coeffs.numpy().view(np.uint32)[:] = cf.reshape(-1)
+
+    def merkle_commit(self, block, n_cols, log_rows, layers):
+        b = block.numpy().view(np.uint32).reshape(n_cols, 1 << log_rows)
+        lay = self.orc.merkle_commit(list(b))
+        layers.numpy().view(np.uint8)[:] = np.concatenate(lay).reshape(-1)
+
+    def commit_layer(self, log, prev, out):
+        h = self.orc.merkle_commit_layer(log, prev.numpy().view(np.uint8), [])
+        out.numpy().view(np.uint8)[:] = h.reshape(-1)
+
+    def to_host_bytes(self, t):
+        return t.numpy().tobytes()
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from tstwo_b200.distributed import ShardedCommit
+        rng = np.random.default_rng(1234)
+        full = rng.integers(0, P, (N_COLS, 1 << LOG), dtype=np.uint32)
+        lc = N_COLS // world
+        mine = torch.from_numpy(full[rank * lc:(rank + 1) * lc].copy().view(np.int32).reshape(-1))
+        sc = ShardedCommit(OracleShardOps(), N_COLS, LOG, BLOW)
+        root = sc.step(mine)
+        if rank == 0:
+            q.put(root)
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_commit_matches_single_process(orc, world):
+    rng = np.random.default_rng(1234)
+    full = rng.integers(0, P, (N_COLS, 1 << LOG), dtype=np.uint32)
+    init, log = orc.canonic_half_coset(LOG + BLOW)
+    tw, itw = orc.precompute_twiddles(init, log)
+    _, _, layers = orc.lde_commit(full, BLOW, tw, itw)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    root = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert root == layers[0][0].tobytes()

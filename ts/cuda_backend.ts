@@ -1,0 +1,115 @@
+// CudaBackend for TStwo over bun:ffi -- the reference-side binding of include/tstwo_cuda.h.
+// NOT executable in the build image (no bun); it documents exactly what a TStwo maintainer adds under
+// packages/core/src/backend/cuda/.  The Python mirror tstwo_b200/backend.py has the same classes and is what the
+// parity tests exercise.  Names follow packages/core/src/backend/cpu/{index,circle,blake2,fri}.ts.
+import { dlopen, FFIType, ptr, suffix } from "bun:ffi";
+import { CircleEvaluation, BitReversedOrder } from "../../poly/circle/evaluation";
+import { CirclePoly } from "../../poly/circle/poly";
+import type { CircleDomain } from "../../poly/circle/domain";
+import { CanonicCoset } from "../../poly/circle/canonic";
+import type { Coset } from "../../circle";
+
+const T = FFIType;
+const lib = dlopen(`libtstwo_cuda.${suffix}`, {
+  tstwo_init: { args: [T.i32], returns: T.i32 },
+  tstwo_last_error: { args: [], returns: T.cstring },
+  tstwo_malloc: { args: [T.u64, T.ptr], returns: T.i32 },
+  tstwo_free: { args: [T.u64], returns: T.i32 },
+  tstwo_upload: { args: [T.u64, T.ptr, T.u64], returns: T.i32 },
+  tstwo_download: { args: [T.ptr, T.u64, T.u64], returns: T.i32 },
+  tstwo_bit_reverse: { args: [T.u64, T.u64], returns: T.i32 },
+  tstwo_twiddles_precompute: { args: [T.u32, T.i32, T.ptr], returns: T.i32 },
+  tstwo_interpolate_columns: { args: [T.ptr, T.ptr, T.i32, T.i32, T.u32, T.u64, T.u32], returns: T.i32 },
+  tstwo_evaluate_columns: { args: [T.ptr, T.i32, T.ptr, T.i32, T.i32, T.u32, T.u64, T.u32], returns: T.i32 },
+  tstwo_merkle_commit_layer: { args: [T.i32, T.u64, T.ptr, T.i32, T.u64], returns: T.i32 },
+  tstwo_merkle_commit: { args: [T.ptr, T.ptr, T.i32, T.u64, T.ptr], returns: T.i32 },
+  tstwo_fold_line: { args: [T.ptr, T.i32, T.u32, T.ptr, T.ptr, T.u64], returns: T.i32 },
+  tstwo_fold_circle_into_line: { args: [T.ptr, T.ptr, T.i32, T.u32, T.ptr, T.u64], returns: T.i32 },
+  tstwo_lde_commit: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.u64, T.ptr, T.u32], returns: T.i32 },
+}).symbols;
+
+function check(rc: number): void {
+  if (rc !== 0) throw new Error(String(lib.tstwo_last_error()));   // same messages as the CpuBackend throws
+}
+check(lib.tstwo_init(Number(process.env.TSTWO_CUDA_DEVICE ?? 0)));
+const QUIRKS = process.env.TSTWO_QUIRKS === "0" ? 0 : 1;            // log-3 swap of backend/cpu/circle.ts:127-131
+
+/** Column<BaseField> resident on the device (backend/index.ts:53-74). */
+export class CudaColumn {
+  constructor(readonly dptr: bigint, readonly length: number) {}
+  static fromArray(values: Uint32Array): CudaColumn {
+    const out = new BigUint64Array(1);
+    check(lib.tstwo_malloc(BigInt(values.byteLength), ptr(out)));
+    check(lib.tstwo_upload(out[0], ptr(values), BigInt(values.byteLength)));
+    return new CudaColumn(out[0], values.length);
+  }
+  len(): number { return this.length; }
+  toCpu(): Uint32Array {
+    const host = new Uint32Array(this.length);
+    check(lib.tstwo_download(ptr(host), this.dptr, BigInt(host.byteLength)));
+    return host;
+  }
+  at(i: number): number {
+    const one = new Uint32Array(1);
+    check(lib.tstwo_download(ptr(one), this.dptr + BigInt(4 * i), 4n));
+    return one[0];
+  }
+}
+
+export class CudaTwiddleTree { constructor(readonly rootCoset: Coset, readonly handle: bigint) {} }
+
+function addrs(cols: CudaColumn[]): BigUint64Array { return BigUint64Array.from(cols.map((c) => c.dptr)); }
+
+/** Same statics as CpuCircleEvaluation (backend/cpu/circle.ts:17-37): duck-typed dispatch of evaluation.ts:138-166. */
+// @ts-expect-error -- as in the reference's CpuCircleEvaluation
+export class CudaCircleEvaluation extends CircleEvaluation<any, any, BitReversedOrder> {
+  static precomputeTwiddles(coset: Coset): CudaTwiddleTree {
+    const h = new BigUint64Array(1);
+    check(lib.tstwo_twiddles_precompute(coset.initial_index.value, coset.log_size, ptr(h)));
+    return new CudaTwiddleTree(coset, h[0]);
+  }
+  static bitReverseColumn(col: CudaColumn): void { check(lib.tstwo_bit_reverse(col.dptr, BigInt(col.length))); }
+  static to_cpu(values: CudaColumn): Uint32Array { return values.toCpu(); }
+  /** CpuCirclePoly.interpolate (backend/cpu/circle.ts:136-207), batched over columns of one domain. */
+  static interpolateColumns(evals: CudaCircleEvaluation[], tw: CudaTwiddleTree): CudaCirclePoly[] {
+    const d = evals[0].domain, n = d.size();
+    const out = evals.map(() => CudaColumn.fromArray(new Uint32Array(n)));
+    check(lib.tstwo_interpolate_columns(ptr(addrs(evals.map((e) => e.values as unknown as CudaColumn))), ptr(addrs(out)),
+      evals.length, d.log_size(), d.halfCoset.initial_index.value, tw.handle, QUIRKS));
+    return out.map((c) => new CudaCirclePoly(c as any));
+  }
+}
+
+export class CudaCirclePoly extends CirclePoly<any> {
+  static precomputeTwiddles = CudaCircleEvaluation.precomputeTwiddles;
+  /** CpuCirclePoly.evaluate with extend (backend/cpu/circle.ts:71-134). */
+  static evaluate(poly: CudaCirclePoly, domain: CircleDomain, tw: CudaTwiddleTree): CudaCircleEvaluation {
+    const src = poly.coeffs as unknown as CudaColumn;
+    const dst = CudaColumn.fromArray(new Uint32Array(domain.size()));
+    check(lib.tstwo_evaluate_columns(ptr(addrs([src])), Math.log2(src.length), ptr(addrs([dst])), 1, domain.log_size(),
+      domain.halfCoset.initial_index.value, tw.handle, QUIRKS));
+    return new CudaCircleEvaluation(domain, dst as any);
+  }
+}
+
+/** MerkleOps<Blake2sHash> (vcs/ops.ts:16-26): hashes stay on the device as a CudaColumn of 8 words per hash. */
+export class CudaMerkleOps {
+  commitOnLayer(logSize: number, prevLayer: CudaColumn | undefined, columns: CudaColumn[]): CudaColumn {
+    const out = CudaColumn.fromArray(new Uint32Array(8 << logSize));
+    check(lib.tstwo_merkle_commit_layer(logSize, prevLayer ? prevLayer.dptr : 0n, ptr(addrs(columns)), columns.length, out.dptr));
+    return out;
+  }
+}
+
+/** Stwo's CommitmentTreeProver::new (Rust text at pcs/prover.ts:215-235), fused on the device. */
+export function commitTrace(trace: CudaColumn, nCols: number, logSize: number, logBlowup: number, tw: CudaTwiddleTree) {
+  const n = 1 << logSize, ne = n << logBlowup, ext = logSize + logBlowup;
+  const coeffs = CudaColumn.fromArray(new Uint32Array(0)), root = new Uint8Array(32);
+  const evals = new BigUint64Array(1), layers = new BigUint64Array(1), cf = new BigUint64Array(1);
+  check(lib.tstwo_malloc(BigInt(4 * nCols * n), ptr(cf)));
+  check(lib.tstwo_malloc(BigInt(4 * nCols * ne), ptr(evals)));
+  check(lib.tstwo_malloc(BigInt(32 * ((2 << ext) - 1)), ptr(layers)));
+  check(lib.tstwo_lde_commit(trace.dptr, nCols, logSize, logBlowup, tw.handle, cf[0], evals[0], layers[0], ptr(root), QUIRKS));
+  void coeffs;
+  return { root, coeffs: cf[0], evals: evals[0], layers: layers[0], domain: CanonicCoset.new(ext).circleDomain() };
+}

@@ -1,0 +1,107 @@
+"""Multi-GPU LDE + Merkle commit: one process per GPU over torch.distributed (BASELINE config 3).
+
+Data flow for G ranks, n_cols columns of 2^log_size, blow-up 2^b (ext = log_size + b):
+  1. every rank interpolates + extends its n_cols/G columns (column-sharded LDE); the evaluations are written
+     grouped by destination rank, [G][n_cols/G][2^ext / G] (tstwo_lde_columns_sharded);
+  2. ONE all-to-all re-shards them by row range: rank d receives [G][n_cols/G][rows] = [n_cols][rows], i.e. all
+     columns of its contiguous row range -- a complete Merkle subtree of height ext - log2 G;
+  3. every rank hashes its leaves and builds its subtree (tstwo_merkle_commit);
+  4. the G subtree roots are all-gathered; rank 0 finishes the top log2 G layers (at most G-1 compressions).
+The root equals the single-GPU root bit for bit (tests/test_distributed_cpu.py, tests/test_gpu_pipeline.py).
+
+`ops` abstracts the device work so the host protocol can be exercised on CPU (gloo) with another provider; the
+product provider is CudaShardOps below (C ABI only, no fallback).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List
+
+import torch
+import torch.distributed as dist
+
+
+class CudaShardOps:
+    """Device work of the sharded commit through libtstwo_cuda.so on torch CUDA tensors."""
+
+    def __init__(self, device_index: int, stream=None):
+        from . import _lib
+        self._lib_mod = _lib
+        self.L = _lib.init(device_index)
+        self.dev = torch.device("cuda", device_index)
+        if stream is not None:
+            _lib.check(self.L.tstwo_set_stream(C.c_void_p(stream.cuda_stream)))
+
+    def empty(self, n_words: int) -> torch.Tensor:
+        return torch.empty(n_words, dtype=torch.int32, device=self.dev)
+
+    def twiddles(self, ext: int) -> int:
+        h = C.c_uint64()
+        self._lib_mod.check(self.L.tstwo_twiddles_precompute(1 << (31 - (ext - 1) - 2), ext - 1, C.byref(h)))
+        return h.value
+
+    def lde_sharded(self, trace: torch.Tensor, n_cols: int, log_size: int, log_blowup: int, tw: int, coeffs, evals: torch.Tensor,
+                    n_shards: int) -> None:
+        self._lib_mod.check(self.L.tstwo_lde_columns_sharded(trace.data_ptr(), n_cols, log_size, log_blowup, tw,
+                                                             coeffs.data_ptr() if coeffs is not None else 0, evals.data_ptr(),
+                                                             n_shards, 0))
+
+    def merkle_commit(self, block: torch.Tensor, n_cols: int, log_rows: int, layers: torch.Tensor) -> None:
+        rows = 1 << log_rows
+        ptrs = self._lib_mod.dptr_array([block.data_ptr() + 4 * rows * c for c in range(n_cols)])
+        logs = (C.c_int * n_cols)(*([log_rows] * n_cols))
+        self._lib_mod.check(self.L.tstwo_merkle_commit(ptrs, logs, n_cols, layers.data_ptr(), None))
+
+    def commit_layer(self, log: int, prev: torch.Tensor, out: torch.Tensor) -> None:
+        self._lib_mod.check(self.L.tstwo_merkle_commit_layer(log, prev.data_ptr(), None, 0, out.data_ptr()))
+
+    def to_host_bytes(self, t: torch.Tensor) -> bytes:
+        return t.cpu().numpy().tobytes()
+
+
+def top_layers(ops, roots: torch.Tensor, world: int) -> List[torch.Tensor]:
+    """Finish the tree above the subtree roots: roots = [world][8 words]; returns layers log2(world)-1 .. 0."""
+    out = []
+    prev = roots
+    for k in range(world.bit_length() - 2, -1, -1):
+        cur = ops.empty(8 << k)
+        ops.commit_layer(k, prev, cur)
+        out.append(cur)
+        prev = cur
+    return out
+
+
+class ShardedCommit:
+    """Buffers + one `step()` of the multi-rank pipeline.  trace: this rank's [n_cols/G][2^log_size] block."""
+
+    def __init__(self, ops, n_cols: int, log_size: int, log_blowup: int, keep_coeffs: bool = True):
+        self.ops = ops
+        self.world = dist.get_world_size()
+        self.rank = dist.get_rank()
+        G = self.world
+        if G & (G - 1) or n_cols % G:
+            raise ValueError("world size must be a power of two dividing n_cols")
+        self.n_cols, self.lc = n_cols, n_cols // G
+        self.log_size, self.blow, self.ext = log_size, log_blowup, log_size + log_blowup
+        self.sub = self.ext - (G.bit_length() - 1)               # log2 rows per rank
+        if self.sub < 12:
+            raise ValueError("row shards must hold at least 2^12 rows")
+        rows = 1 << self.sub
+        self.tw = ops.twiddles(self.ext)
+        self.coeffs = ops.empty(self.lc << log_size) if keep_coeffs else None
+        self.send = ops.empty(self.lc << self.ext)               # [G][lc][rows]
+        self.recv = ops.empty(n_cols * rows)                     # [G][lc][rows] == [n_cols][rows]
+        self.layers = ops.empty(8 * ((2 << self.sub) - 1))       # this rank's subtree, root first
+        self.roots = ops.empty(8 * G)
+        self.top: List[torch.Tensor] = []
+
+    def step(self, trace: torch.Tensor) -> bytes | None:
+        ops = self.ops
+        ops.lde_sharded(trace, self.lc, self.log_size, self.blow, self.tw, self.coeffs, self.send, self.world)
+        dist.all_to_all_single(self.recv, self.send)
+        ops.merkle_commit(self.recv, self.n_cols, self.sub, self.layers)
+        dist.all_gather_into_tensor(self.roots, self.layers[:8].contiguous())
+        if self.rank == 0:
+            self.top = top_layers(ops, self.roots, self.world)
+            return ops.to_host_bytes(self.top[-1] if self.top else self.roots)[:32]
+        return None
