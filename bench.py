@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample-cols", type=int, default=8)
+    ap.add_argument("--fft-radix", type=int, default=0, help="tuning: rows per thread of the FFT passes (8 or 16)")
     return ap.parse_args()
 
 
@@ -158,6 +159,8 @@ def run_cuda(args):
     stream = torch.cuda.Stream(device=local)
     torch.cuda.set_stream(stream)
     chk(L.tstwo_set_stream(C.c_void_p(stream.cuda_stream)))
+    if args.fft_radix:
+        L.tstwo_debug_set_fft_radix(args.fft_radix)
 
     log, blow, n_cols = args.log_size, LOG_BLOWUP, args.cols
     ext = log + blow

@@ -94,6 +94,56 @@ def test_blowup_contiguous_block(tb, orc, log, blow, extra, n_cols):
         assert (out[c].values.toCpu() == ee).all()
 
 
+@pytest.mark.parametrize("radix", [8, 16])
+@pytest.mark.parametrize("log,blow", [(14, 1), (15, 0), (17, 2), (21, 1)])
+def test_both_tile_radixes_vs_oracle(tb, orc, radix, log, blow):
+    """The tiled passes exist in two register blockings (8 / 16 rows per thread); both must match the oracle, including
+    sizes where the strided window is only partially active (log < 22) and a 3-pass size is covered on device below."""
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    L.tstwo_debug_set_fft_radix(radix)
+    try:
+        ext = log + blow
+        coset, tw, otw, oitw = _tree(tb, orc, ext - 1)
+        root = (coset.initial_index.value, coset.log_size)
+        rng = np.random.default_rng(radix * 100 + log)
+        n_cols = 5 if log < 20 else 2
+        vals = rng.integers(0, P, (n_cols, 1 << log), dtype=np.uint32)
+        dom = tb.CanonicCoset.new(log).circleDomain()
+        polys = tb.CudaBackend.interpolateColumns([tb.CudaCircleEvaluation.new(dom, v) for v in vals], tw)
+        out = tb.CudaBackend.evaluatePolynomials(polys, blow, tw)
+        big = tb.CanonicCoset.new(ext).circleDomain()
+        for c in (0, n_cols - 1):
+            ec = orc.interpolate(vals[c], dom.halfCoset.initial_index.value, root, oitw)
+            assert (polys[c].coeffs.toCpu() == ec).all()
+            assert (out[c].values.toCpu() == orc.evaluate(ec, ext, big.halfCoset.initial_index.value, root, otw)).all()
+    finally:
+        L.tstwo_debug_set_fft_radix(16)
+
+
+@pytest.mark.parametrize("radix", [8, 16])
+def test_three_pass_transform_on_device(tb, orc, radix):
+    """log 23 needs three passes (12 + 10 + partial window); cross-checked against the per-layer kernels."""
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    L.tstwo_debug_set_fft_radix(radix)
+    log = 23
+    tw = tb.CudaBackend.precomputeTwiddles(tb.Coset.half_odds(log - 1))
+    vals = np.random.default_rng(23).integers(0, P, 1 << log, dtype=np.uint32)
+    dom = tb.CanonicCoset.new(log).circleDomain()
+    res = []
+    try:
+        for naive in (0, 1):
+            L.tstwo_debug_force_naive_fft(naive)
+            poly = tb.CudaCircleEvaluation.new(dom, vals).interpolateWithTwiddles(tw)
+            back = poly.evaluateWithTwiddles(dom, tw)
+            res.append((poly.coeffs.toCpu(), back.values.toCpu()))
+    finally:
+        L.tstwo_debug_force_naive_fft(0)
+        L.tstwo_debug_set_fft_radix(16)
+    assert (res[0][0] == res[1][0]).all() and (res[0][1] == res[1][1]).all() and (res[0][1] == vals).all()
+
+
 @pytest.mark.parametrize("log", [14, 19, 20])
 def test_tiled_passes_match_layer_kernels_on_device(tb, orc, log):
     """At sizes where the oracle is slow the tiled radix-2^11 passes are cross-checked against the per-layer kernels."""

@@ -79,8 +79,9 @@ def load():
             fn = getattr(lib, name)   # AttributeError if the symbol is missing
             fn.restype = res
             fn.argtypes = args
-        lib.tstwo_debug_force_naive_fft.restype = C.c_int
-        lib.tstwo_debug_force_naive_fft.argtypes = [C.c_int]
+        for dbg in ("tstwo_debug_force_naive_fft", "tstwo_debug_set_fft_radix"):
+            getattr(lib, dbg).restype = C.c_int
+            getattr(lib, dbg).argtypes = [C.c_int]
         _lib = lib
     return _lib
 

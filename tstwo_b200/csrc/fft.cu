@@ -15,20 +15,25 @@
 
 namespace tstwo {
 
-constexpr int PASS_THREADS = 256;
-constexpr int TILE_UNITS = 4096 + 256;                      // uint4 units per tile incl. padding (both shapes)
 constexpr int FAST_MIN_LOG = 14;
 
-// Tile shapes.  Both hold 4096 uint4 units (16 elements x 4 lanes per thread, 256 threads):
-//   CONTIG : 4096 rows = index bits [0,12) of 4 different columns (the 4 lanes), 12 layers, stages at bits 8/4/0
-//   STRIDED: 1024 rows = index bits [lo,lo+10) x 16 consecutive indices (4 thread groups x 4 lanes) of one column,
-//            10 layers, stages at bits 6/2/0 (the last stage applies only bits 1,0)
-template <bool STRIDED> struct Shape {
+// Tile shapes.  A tile holds 4096 uint4 units; a thread owns 2^DIG rows x 4 lanes and applies up to DIG layers per
+// stage in registers, exchanging through shared memory between stages.
+//   CONTIG : 4096 rows = index bits [0,12) of 4 different columns (the 4 lanes)
+//   STRIDED: 1024 rows = index bits [lo,lo+10) x 16 consecutive indices (4 thread groups x 4 lanes) of one column
+//   DIG = 4: 256 threads, 16 rows per thread, 3 stages;  DIG = 3: 512 threads, 8 rows per thread, 4 stages
+template <bool STRIDED, int DIG> struct Shape {
     static constexpr int RHO = STRIDED ? 10 : 12;            // row bits per tile
-    static constexpr int SA = STRIDED ? 6 : 8, SB = STRIDED ? 2 : 4, SC = 0;
-    static constexpr int NLC = STRIDED ? 2 : 4;              // active layers of stage C
     static constexpr int G = STRIDED ? 4 : 1;                // thread groups side by side in a row
+    static constexpr int NE = 1 << DIG;
+    static constexpr int THREADS = 4096 / NE;
+    static constexpr int NST = DIG == 4 ? 3 : 4;             // stages, listed from the top row bits down
+    __host__ __device__ static constexpr int S(int k) { return DIG == 4 ? (STRIDED ? (k == 0 ? 6 : k == 1 ? 2 : 0) : (k == 0 ? 8 : k == 1 ? 4 : 0))
+                                                    : (STRIDED ? (k == 0 ? 7 : k == 1 ? 4 : k == 2 ? 2 : 0) : (k == 0 ? 9 : k == 1 ? 6 : k == 2 ? 3 : 0)); }
+    __host__ __device__ static constexpr int N(int k) { return DIG == 4 ? (STRIDED ? (k == 2 ? 2 : 4) : 4) : (STRIDED ? (k >= 2 ? 2 : 3) : 3); }
     static constexpr int TW_WORDS = 1 << RHO;
+    static constexpr int TILE_UNITS = ((1 << RHO) + ((1 << RHO) >> DIG)) * G;   // one pad row per 2^DIG rows
+    static constexpr int SMEM = TILE_UNITS * 16 + TW_WORDS * 4;
 };
 
 struct PassParams {
@@ -41,7 +46,7 @@ struct PassParams {
     const uint32_t *tw2;   // pre-doubled twiddle (or inverse twiddle) tree
     uint32_t tree_len;     // 2^root_log
     uint32_t scale2;       // 2/2^n after the last inverse layer, or 0
-    uint32_t zero;         // run-time 0 (forces IADD3 for half of the adds, see m31::butterfly_z)
+    uint32_t zero;         // run-time 0 (see m31::butterfly_z)
 };
 
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
@@ -56,16 +61,14 @@ __device__ __forceinline__ void cp_async4(void *smem, const void *gmem)
 // Stage all twiddles of the tile in shared memory as a heap: relative layer j (absolute i = lo + j) needs
 // T_i[(tile_hi << (RHO-1-j)) + r], r < 2^(RHO-1-j); it is stored at tws[2^(RHO-1-j) + r].  Layers of >= 4 entries are
 // fetched with 16-byte cp.async (source ranges are aligned to their size), the three small ones word by word.
-template <bool STRIDED>
+template <int RHO, int THREADS>
 __device__ __forceinline__ void tile_twiddles_async(uint32_t *tws, const PassParams &p, uint32_t tile_hi, int tid)
 {
-    constexpr int RHO = Shape<STRIDED>::RHO;
 #pragma unroll
-    for (int e = 4 * tid; e < (1 << RHO); e += 4 * PASS_THREADS) {
+    for (int e = 4 * tid; e < (1 << RHO); e += 4 * THREADS) {
         if (e == 0) {
-            // heap[1] = top layer (1 entry), heap[2..3] = next layer (2 entries)
-            for (int ee = 1; ee < 4; ee++) {
-                const int lg = ee >> 1;               // 0 or 1
+            for (int ee = 1; ee < 4; ee++) {          // heap[1] = top layer, heap[2..3] = the next one
+                const int lg = ee >> 1;
                 const int j = (RHO - 1) - lg, i = p.lo + j;
                 if (j < p.j_min || i < 1) continue;
                 cp_async4(tws + ee, p.tw2 + (p.tree_len - (1u << (p.n - i))) + (tile_hi << lg) + (ee - (1 << lg)));
@@ -80,38 +83,42 @@ __device__ __forceinline__ void tile_twiddles_async(uint32_t *tws, const PassPar
     asm volatile("cp.async.commit_group;");
 }
 
-// One radix-16 stage on v[16][4]: digit bit k <-> row bit S+k, layers j = S+k for k in [0, NL).
-template <int RHO, int S, int NL, bool INV>
-__device__ __forceinline__ void stage(uint32_t (&v)[16][4], const PassParams &p, const uint32_t *tws, int rbase)
+// One radix-2^DIG stage on v[NE][4]: digit bit k <-> row bit S+k, layers j = S+k for k in [0, NL).
+// FULL: every layer of the window is applied (no run-time j_min test, hence no control flow between layers);
+// CIRCLE: the window starts at index bit 0, so relative layer 0 is the circle layer.
+template <int NE, int RHO, int S, int NL, bool INV, bool FULL, bool CIRCLE>
+__device__ __forceinline__ void stage(uint32_t (&v)[NE][4], const PassParams &p, const uint32_t *tws, int rbase)
 {
 #pragma unroll
     for (int kk = 0; kk < NL; kk++) {
         const int k = INV ? kk : NL - 1 - kk;
         const int j = S + k;
-        if (j < p.j_min) continue;                     // uniform across the grid
-        const int cnt = 8 >> k;
-        uint32_t t[8];
-        if (p.lo + j >= 1) {
+        if (!FULL && j < p.j_min) continue;            // uniform across the grid
+        const int cnt = (NE / 2) >> k;
+        uint32_t t[NE / 2];
+        if (!(CIRCLE && j == 0)) {
             const uint32_t *q = tws + (1 << (RHO - 1 - j)) + (rbase >> (j + 1));
-            if (cnt == 8) {
-                uint4 a = *reinterpret_cast<const uint4 *>(q), b = *reinterpret_cast<const uint4 *>(q + 4);
-                t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w;
-            } else if (cnt == 4) {
-                uint4 a = *reinterpret_cast<const uint4 *>(q);
-                t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w;
+            if (cnt >= 4) {
+#pragma unroll
+                for (int c = 0; c < cnt / 4; c++) {
+                    uint4 a = *reinterpret_cast<const uint4 *>(q + 4 * c);
+                    t[4 * c] = a.x; t[4 * c + 1] = a.y; t[4 * c + 2] = a.z; t[4 * c + 3] = a.w;
+                }
             } else if (cnt == 2) {
                 uint2 a = *reinterpret_cast<const uint2 *>(q);
                 t[0] = a.x; t[1] = a.y;
             } else t[0] = q[0];
         } else {
-            // circle layer (j == 0, k == 0): T_1 entries (x0, y0, x1, y1) of this thread's 16 rows -> [y,-y,-x,x]
-            uint4 a = *reinterpret_cast<const uint4 *>(tws + (1 << (RHO - 2)) + (rbase >> 2));
+            // circle layer (j == 0, k == 0): T_1 entries (x, y) pairs of this thread's rows -> [y, -y, -x, x] each
             const uint32_t P2 = 0xfffffffeu;
-            t[0] = a.y; t[1] = P2 - a.y; t[2] = P2 - a.x; t[3] = a.x;
-            t[4] = a.w; t[5] = P2 - a.w; t[6] = P2 - a.z; t[7] = a.z;
+#pragma unroll
+            for (int c = 0; c < NE / 8; c++) {
+                uint2 a = *reinterpret_cast<const uint2 *>(tws + (1 << (RHO - 2)) + (rbase >> 2) + 2 * c);
+                t[4 * c] = a.y; t[4 * c + 1] = P2 - a.y; t[4 * c + 2] = P2 - a.x; t[4 * c + 3] = a.x;
+            }
         }
 #pragma unroll
-        for (int d = 0; d < 16; d++) {
+        for (int d = 0; d < NE; d++) {
             if (d & (1 << k)) continue;
             const uint32_t tw = t[d >> (k + 1)];
 #pragma unroll
@@ -123,64 +130,51 @@ __device__ __forceinline__ void stage(uint32_t (&v)[16][4], const PassParams &p,
     }
 }
 
-// Thread -> rows maps.  rg = row group of the thread; digit d = 0..15 selects one of its 16 rows.
-//   A: digit = row bits [SA, SA+4)   rows rg + d * 2^SA
-//   B: digit = row bits [SB, SB+4)   rows (rg >> SB) * 2^(SB+4) + (rg & (2^SB - 1)) + d * 2^SB
-//   C: digit = row bits [0, 4)       rows 16 rg + d
-enum { MAP_A = 0, MAP_B = 1, MAP_C = 2 };
-template <bool STRIDED, int MAP> __device__ __forceinline__ int map_rbase(int rg)
+// Thread -> rows map of the stage whose digit is row bits [S, S+DIG): rows rbase + (d << S), d = 0..2^DIG-1, with
+// rbase = ((rg >> S) << (S+DIG)) | (rg & (2^S - 1)).
+template <int DIG, int S> __device__ __forceinline__ int map_rbase(int rg) { return ((rg >> S) << (S + DIG)) | (rg & ((1 << S) - 1)); }
+// Shared-memory unit (16 B) of (row r, group g): G*(r + (r >> DIG)) + g -- one pad row per 2^DIG rows.  Every quarter
+// warp (8 lanes) then touches 8 distinct 16-byte bank groups in every map of both shapes (ncu: wavefronts == ideal).
+template <bool STRIDED, int DIG, int S> __device__ __forceinline__ int map_unit0(int rg, int g)
 {
-    constexpr int SB = Shape<STRIDED>::SB;
-    return MAP == MAP_A ? rg : MAP == MAP_B ? ((rg >> SB) << (SB + 4)) + (rg & ((1 << SB) - 1)) : rg * 16;
+    const int r = map_rbase<DIG, S>(rg);
+    return Shape<STRIDED, DIG>::G * (r + (r >> DIG)) + g;
 }
-template <bool STRIDED, int MAP> __device__ __forceinline__ int map_row(int rbase, int d)
+template <bool STRIDED, int DIG, int S> __device__ __forceinline__ constexpr int map_unit_off(int d)
 {
-    return MAP == MAP_A ? rbase + (d << Shape<STRIDED>::SA) : MAP == MAP_B ? rbase + (d << Shape<STRIDED>::SB) : rbase + d;
+    return Shape<STRIDED, DIG>::G * ((d << S) + ((d << S) >> DIG));
 }
-// Shared-memory unit (16 B) of (row r, group g): G*r + g + G*(r>>4) -- one pad row per 16 rows.  Every quarter warp
-// (8 lanes) then touches 8 distinct 16-byte bank groups in all three maps of both shapes ("exchange").
-template <bool STRIDED, int MAP> __device__ __forceinline__ int map_unit0(int rg, int g)
+template <bool STRIDED, int DIG, int S, int NE> __device__ __forceinline__ void smem_store(uint4 *sm, int rg, int g, const uint32_t (&v)[NE][4])
 {
-    constexpr int G = Shape<STRIDED>::G;
-    const int r = map_rbase<STRIDED, MAP>(rg);
-    return G * r + g + G * (r >> 4);
-}
-template <bool STRIDED, int MAP> __device__ __forceinline__ constexpr int map_unit_off(int d)
-{
-    // row offset o(d) of digit d, unit offset G * (o + (o >> 4)) (o never carries into the pad of rbase)
-    return Shape<STRIDED>::G * (MAP == MAP_A ? (d << Shape<STRIDED>::SA) + ((d << Shape<STRIDED>::SA) >> 4)
-                                : MAP == MAP_B ? (d << Shape<STRIDED>::SB) + ((d << Shape<STRIDED>::SB) >> 4)
-                                               : d);
-}
-template <bool STRIDED, int MAP> __device__ __forceinline__ void smem_store(uint4 *sm, int u0, const uint32_t (&v)[16][4])
-{
+    const int u0 = map_unit0<STRIDED, DIG, S>(rg, g);
 #pragma unroll
-    for (int d = 0; d < 16; d++) sm[u0 + map_unit_off<STRIDED, MAP>(d)] = make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]);
+    for (int d = 0; d < NE; d++) sm[u0 + map_unit_off<STRIDED, DIG, S>(d)] = make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]);
 }
-template <bool STRIDED, int MAP> __device__ __forceinline__ void smem_load(const uint4 *sm, int u0, uint32_t (&v)[16][4])
+template <bool STRIDED, int DIG, int S, int NE> __device__ __forceinline__ void smem_load(const uint4 *sm, int rg, int g, uint32_t (&v)[NE][4])
 {
+    const int u0 = map_unit0<STRIDED, DIG, S>(rg, g);
 #pragma unroll
-    for (int d = 0; d < 16; d++) {
-        uint4 a = sm[u0 + map_unit_off<STRIDED, MAP>(d)];
+    for (int d = 0; d < NE; d++) {
+        uint4 a = sm[u0 + map_unit_off<STRIDED, DIG, S>(d)];
         v[d][0] = a.x; v[d][1] = a.y; v[d][2] = a.z; v[d][3] = a.w;
     }
 }
 
 // global I/O.  STRIDED: the tile is rows x 16 consecutive indices of column blockIdx.y; CONTIG: the 4 lanes are
-// columns 4*blockIdx.y .. +3.  All 64-bit address arithmetic is done once per thread (tile base); the 16 digit
-// offsets are compile-time (CONTIG) or a single runtime stride (STRIDED).  Only the contiguous pass honours the
-// row-sharded layout of ColSet (a 4096-row tile never straddles a shard).
-template <int MAP, bool STRIDED>
-__device__ __forceinline__ void gmem_load(const PassParams &p, uint32_t tile_hi, uint32_t mid, int rbase, int g,
-                                          uint32_t (&v)[16][4])
+// columns 4*blockIdx.y .. +3.  All 64-bit address arithmetic is done once per thread (tile base); the digit offsets
+// are compile-time (CONTIG) or a single runtime stride (STRIDED).  Only the contiguous pass honours the row-sharded
+// layout of ColSet (a 4096-row tile never straddles a shard).
+template <int S, bool STRIDED, int DIG, int NE>
+__device__ __forceinline__ void gmem_load(const PassParams &p, uint32_t tile_hi, uint32_t mid, int rg, int g, uint32_t (&v)[NE][4])
 {
-    constexpr int RHO = Shape<STRIDED>::RHO;
+    constexpr int RHO = Shape<STRIDED, DIG>::RHO;
+    const int rbase = map_rbase<DIG, S>(rg);
     if (STRIDED) {
         const uint32_t base = (((tile_hi << (p.lo + RHO)) | (mid << 4) | (g << 2)) & p.src_mask) | ((uint32_t)rbase << p.lo);
         const uint4 *ptr = reinterpret_cast<const uint4 *>(p.src.col(blockIdx.y) + base);
-        const uint32_t st = 1u << (p.lo + (MAP == MAP_A ? Shape<STRIDED>::SA : MAP == MAP_B ? Shape<STRIDED>::SB : 0) - 2);  // uint4 units
+        const uint32_t st = 1u << (p.lo + S - 2);    // uint4 units between digits
 #pragma unroll
-        for (int d = 0; d < 16; d++) {
+        for (int d = 0; d < NE; d++) {
             uint4 a = __ldcg(ptr + (size_t)d * st);
             v[d][0] = a.x; v[d][1] = a.y; v[d][2] = a.z; v[d][3] = a.w;
         }
@@ -191,34 +185,34 @@ __device__ __forceinline__ void gmem_load(const PassParams &p, uint32_t tile_hi,
         for (int q = 0; q < 4; q++) {
             if (c0 + q < p.n_cols) {
                 const uint32_t *ptr = p.src.col(c0 + q) + tile_off;
-                if (MAP == MAP_C) {
+                if (S == 0) {
 #pragma unroll
-                    for (int dd = 0; dd < 4; dd++) {
+                    for (int dd = 0; dd < NE / 4; dd++) {
                         uint4 a = __ldg(reinterpret_cast<const uint4 *>(ptr) + dd);
                         v[4 * dd][q] = a.x; v[4 * dd + 1][q] = a.y; v[4 * dd + 2][q] = a.z; v[4 * dd + 3][q] = a.w;
                     }
                 } else {
 #pragma unroll
-                    for (int d = 0; d < 16; d++) v[d][q] = __ldcg(ptr + map_row<STRIDED, MAP>(0, d));
+                    for (int d = 0; d < NE; d++) v[d][q] = __ldcg(ptr + (d << S));
                 }
             } else {
 #pragma unroll
-                for (int d = 0; d < 16; d++) v[d][q] = 0;
+                for (int d = 0; d < NE; d++) v[d][q] = 0;
             }
         }
     }
 }
-template <int MAP, bool STRIDED>
-__device__ __forceinline__ void gmem_store(const PassParams &p, uint32_t tile_hi, uint32_t mid, int rbase, int g,
-                                           const uint32_t (&v)[16][4])
+template <int S, bool STRIDED, int DIG, int NE>
+__device__ __forceinline__ void gmem_store(const PassParams &p, uint32_t tile_hi, uint32_t mid, int rg, int g, const uint32_t (&v)[NE][4])
 {
-    constexpr int RHO = Shape<STRIDED>::RHO;
+    constexpr int RHO = Shape<STRIDED, DIG>::RHO;
+    const int rbase = map_rbase<DIG, S>(rg);
     if (STRIDED) {
         const uint32_t base = (tile_hi << (p.lo + RHO)) | (mid << 4) | (g << 2) | ((uint32_t)rbase << p.lo);
         uint4 *ptr = reinterpret_cast<uint4 *>(p.dst.col(blockIdx.y) + base);
-        const uint32_t st = 1u << (p.lo + (MAP == MAP_A ? Shape<STRIDED>::SA : MAP == MAP_B ? Shape<STRIDED>::SB : 0) - 2);
+        const uint32_t st = 1u << (p.lo + S - 2);
 #pragma unroll
-        for (int d = 0; d < 16; d++) __stcg(ptr + (size_t)d * st, make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]));
+        for (int d = 0; d < NE; d++) __stcg(ptr + (size_t)d * st, make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]));
     } else {
         const int c0 = blockIdx.y * 4;
         const uint64_t tile_off = p.dst.off(tile_hi << RHO) + (uint32_t)rbase;
@@ -226,27 +220,42 @@ __device__ __forceinline__ void gmem_store(const PassParams &p, uint32_t tile_hi
         for (int q = 0; q < 4; q++) {
             if (c0 + q < p.n_cols) {
                 uint32_t *ptr = p.dst.col(c0 + q) + tile_off;
-                if (MAP == MAP_C) {
+                if (S == 0) {
 #pragma unroll
-                    for (int dd = 0; dd < 4; dd++)
+                    for (int dd = 0; dd < NE / 4; dd++)
                         __stcg(reinterpret_cast<uint4 *>(ptr) + dd,
                                make_uint4(v[4 * dd][q], v[4 * dd + 1][q], v[4 * dd + 2][q], v[4 * dd + 3][q]));
                 } else {
 #pragma unroll
-                    for (int d = 0; d < 16; d++) __stcg(ptr + map_row<STRIDED, MAP>(0, d), v[d][q]);
+                    for (int d = 0; d < NE; d++) __stcg(ptr + (d << S), v[d][q]);
                 }
             }
         }
     }
 }
 
-template <bool INV, bool STRIDED>
-__global__ void __launch_bounds__(PASS_THREADS, 2) fft_pass_kernel(const PassParams p)
+// one stage k of the shape: [exchange in] -> butterflies -> [exchange out]
+template <bool INV, bool STRIDED, int DIG, bool FULL, int K>
+__device__ __forceinline__ void run_stage(uint32_t (&v)[1 << DIG][4], const PassParams &p, uint4 *sm, const uint32_t *tws, int rg, int g,
+                                          bool load_smem, bool store_smem)
 {
-    using SH = Shape<STRIDED>;
-    constexpr int RHO = SH::RHO;
+    using SH = Shape<STRIDED, DIG>;
+    constexpr int S = SH::S(K), N = SH::N(K);
+    if (load_smem) smem_load<STRIDED, DIG, S, SH::NE>(sm, rg, g, v);
+    stage<SH::NE, SH::RHO, S, N, INV, FULL, !STRIDED>(v, p, tws, map_rbase<DIG, S>(rg));
+    if (store_smem) {
+        smem_store<STRIDED, DIG, S, SH::NE>(sm, rg, g, v);
+        __syncthreads();
+    }
+}
+
+template <bool INV, bool STRIDED, int DIG, bool FULL>
+__global__ void __launch_bounds__(4096 >> DIG, 2) fft_pass_kernel(const PassParams p)
+{
+    using SH = Shape<STRIDED, DIG>;
+    constexpr int RHO = SH::RHO, NST = SH::NST, LAST = NST - 1;
     extern __shared__ uint4 sm[];
-    uint32_t *tws = reinterpret_cast<uint32_t *>(sm + TILE_UNITS);
+    uint32_t *tws = reinterpret_cast<uint32_t *>(sm + SH::TILE_UNITS);
     const int tid = threadIdx.x;
     const int g = STRIDED ? (tid & 3) : 0, rg = STRIDED ? (tid >> 2) : tid;
     uint32_t tile_hi, mid;
@@ -257,44 +266,32 @@ __global__ void __launch_bounds__(PASS_THREADS, 2) fft_pass_kernel(const PassPar
         tile_hi = blockIdx.x;
         mid = 0;
     }
-    tile_twiddles_async<STRIDED>(tws, p, tile_hi, tid);
-    uint32_t v[16][4];
-    const int rA = map_rbase<STRIDED, MAP_A>(rg), rB = map_rbase<STRIDED, MAP_B>(rg), rC = map_rbase<STRIDED, MAP_C>(rg);
-    const int uA = map_unit0<STRIDED, MAP_A>(rg, g), uB = map_unit0<STRIDED, MAP_B>(rg, g), uC = map_unit0<STRIDED, MAP_C>(rg, g);
+    tile_twiddles_async<RHO, SH::THREADS>(tws, p, tile_hi, tid);
+    uint32_t v[SH::NE][4];
     if (!INV) {
-        gmem_load<MAP_A, STRIDED>(p, tile_hi, mid, rA, g, v);
+        gmem_load<SH::S(0), STRIDED, DIG, SH::NE>(p, tile_hi, mid, rg, g, v);
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();
-        stage<RHO, SH::SA, 4, false>(v, p, tws, rA);
-        smem_store<STRIDED, MAP_A>(sm, uA, v);
-        __syncthreads();
-        smem_load<STRIDED, MAP_B>(sm, uB, v);
-        stage<RHO, SH::SB, 4, false>(v, p, tws, rB);
-        smem_store<STRIDED, MAP_B>(sm, uB, v);
-        __syncthreads();
-        smem_load<STRIDED, MAP_C>(sm, uC, v);
-        stage<RHO, SH::SC, SH::NLC, false>(v, p, tws, rC);
-        gmem_store<MAP_C, STRIDED>(p, tile_hi, mid, rC, g, v);
+        run_stage<INV, STRIDED, DIG, FULL, 0>(v, p, sm, tws, rg, g, false, true);
+        run_stage<INV, STRIDED, DIG, FULL, 1>(v, p, sm, tws, rg, g, true, true);
+        if (NST == 4) run_stage<INV, STRIDED, DIG, FULL, (NST == 4 ? 2 : 1)>(v, p, sm, tws, rg, g, true, true);
+        run_stage<INV, STRIDED, DIG, FULL, LAST>(v, p, sm, tws, rg, g, true, false);
+        gmem_store<SH::S(LAST), STRIDED, DIG, SH::NE>(p, tile_hi, mid, rg, g, v);
     } else {
-        gmem_load<MAP_C, STRIDED>(p, tile_hi, mid, rC, g, v);
+        gmem_load<SH::S(LAST), STRIDED, DIG, SH::NE>(p, tile_hi, mid, rg, g, v);
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();
-        stage<RHO, SH::SC, SH::NLC, true>(v, p, tws, rC);
-        smem_store<STRIDED, MAP_C>(sm, uC, v);
-        __syncthreads();
-        smem_load<STRIDED, MAP_B>(sm, uB, v);
-        stage<RHO, SH::SB, 4, true>(v, p, tws, rB);
-        smem_store<STRIDED, MAP_B>(sm, uB, v);
-        __syncthreads();
-        smem_load<STRIDED, MAP_A>(sm, uA, v);
-        stage<RHO, SH::SA, 4, true>(v, p, tws, rA);
+        run_stage<INV, STRIDED, DIG, FULL, LAST>(v, p, sm, tws, rg, g, false, true);
+        if (NST == 4) run_stage<INV, STRIDED, DIG, FULL, (NST == 4 ? 2 : 1)>(v, p, sm, tws, rg, g, true, true);
+        run_stage<INV, STRIDED, DIG, FULL, 1>(v, p, sm, tws, rg, g, true, true);
+        run_stage<INV, STRIDED, DIG, FULL, 0>(v, p, sm, tws, rg, g, true, false);
         if (p.scale2) {
 #pragma unroll
-            for (int d = 0; d < 16; d++)
+            for (int d = 0; d < SH::NE; d++)
 #pragma unroll
                 for (int q = 0; q < 4; q++) v[d][q] = m31::mul2(v[d][q], p.scale2);
         }
-        gmem_store<MAP_A, STRIDED>(p, tile_hi, mid, rA, g, v);
+        gmem_store<SH::S(0), STRIDED, DIG, SH::NE>(p, tile_hi, mid, rg, g, v);
     }
 }
 
@@ -370,15 +367,26 @@ __global__ void small_interp_kernel(ColSet cols, int n, uint32_t xi2, uint32_t y
 static bool g_force_naive = false;
 static bool g_smem_attr_set = false;
 
-static int smem_bytes(bool strided) { return TILE_UNITS * 16 + (strided ? Shape<true>::TW_WORDS : Shape<false>::TW_WORDS) * 4; }
+static int g_dig = 4;   // rows per thread = 2^g_dig (tstwo_debug_set_fft_radix): 4 -> 256 threads (default), 3 -> 512 threads
 
+template <bool INV, bool STRIDED, int DIG, bool FULL> static cudaError_t set_attr()
+{
+    return cudaFuncSetAttribute(fft_pass_kernel<INV, STRIDED, DIG, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                Shape<STRIDED, DIG>::SMEM);
+}
+template <int DIG> static int set_attrs()
+{
+    TS_CUDA((set_attr<false, false, DIG, true>())); TS_CUDA((set_attr<true, false, DIG, true>()));
+    TS_CUDA((set_attr<false, true, DIG, true>()));  TS_CUDA((set_attr<true, true, DIG, true>()));
+    TS_CUDA((set_attr<false, true, DIG, false>())); TS_CUDA((set_attr<true, true, DIG, false>()));
+    return 0;
+}
 static int ensure_smem_attr()
 {
     if (g_smem_attr_set) return 0;
-    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(false)));
-    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(true)));
-    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(false)));
-    TS_CUDA(cudaFuncSetAttribute(fft_pass_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(true)));
+    int rc = set_attrs<3>();
+    if (rc) return rc;
+    if ((rc = set_attrs<4>())) return rc;
     g_smem_attr_set = true;
     return 0;
 }
@@ -386,7 +394,7 @@ static int ensure_smem_attr()
 struct Pass { int lo, j_min; };
 // passes in ascending layer order for L real layers (scripts/proto_fft.py): one contiguous 12-layer pass, then
 // strided 10-layer windows; the top window is aligned to L and skips the layers already done.
-constexpr int W0 = Shape<false>::RHO, W1 = Shape<true>::RHO;
+constexpr int W0 = Shape<false, 3>::RHO, W1 = Shape<true, 3>::RHO;
 static int plan_passes(int L, Pass out[4])
 {
     int np = 0, done = W0;
@@ -396,20 +404,28 @@ static int plan_passes(int L, Pass out[4])
     return np;
 }
 
-static int launch_pass(bool inverse, const PassParams &p)
+template <int DIG> static int launch_pass_t(bool inverse, const PassParams &p)
 {
+    constexpr int T = 4096 >> DIG;
     if (p.lo == 0) {
         dim3 grid(1u << (p.n - W0), (unsigned)((p.n_cols + 3) / 4));
-        if (inverse) TS_LAUNCH((fft_pass_kernel<true, false>), grid, PASS_THREADS, smem_bytes(false), p);
-        else TS_LAUNCH((fft_pass_kernel<false, false>), grid, PASS_THREADS, smem_bytes(false), p);
+        if (inverse) TS_LAUNCH((fft_pass_kernel<true, false, DIG, true>), grid, T, (Shape<false, DIG>::SMEM), p);
+        else TS_LAUNCH((fft_pass_kernel<false, false, DIG, true>), grid, T, (Shape<false, DIG>::SMEM), p);
     } else {
         if (p.src.shard_log != 31 || p.dst.shard_log != 31) return fail(TSTWO_ERR_BAD_ARG, "strided FFT pass on a row-sharded column set");
         dim3 grid(1u << (p.n - W1 - 4), (unsigned)p.n_cols);
-        if (inverse) TS_LAUNCH((fft_pass_kernel<true, true>), grid, PASS_THREADS, smem_bytes(true), p);
-        else TS_LAUNCH((fft_pass_kernel<false, true>), grid, PASS_THREADS, smem_bytes(true), p);
+        const bool full = p.j_min == 0;
+        if (inverse) {
+            if (full) TS_LAUNCH((fft_pass_kernel<true, true, DIG, true>), grid, T, (Shape<true, DIG>::SMEM), p);
+            else TS_LAUNCH((fft_pass_kernel<true, true, DIG, false>), grid, T, (Shape<true, DIG>::SMEM), p);
+        } else {
+            if (full) TS_LAUNCH((fft_pass_kernel<false, true, DIG, true>), grid, T, (Shape<true, DIG>::SMEM), p);
+            else TS_LAUNCH((fft_pass_kernel<false, true, DIG, false>), grid, T, (Shape<true, DIG>::SMEM), p);
+        }
     }
     return 0;
 }
+static int launch_pass(bool inverse, const PassParams &p) { return g_dig == 4 ? launch_pass_t<4>(inverse, p) : launch_pass_t<3>(inverse, p); }
 
 static uint32_t dbl(uint32_t v) { return v + v; }
 
@@ -501,6 +517,8 @@ extern "C" {
 
 // test hook: force the per-layer kernels for every size (used by tests to cross-check the tiled passes on device)
 int tstwo_debug_force_naive_fft(int on) { g_force_naive = on != 0; return 0; }
+// tuning hook: rows per thread of the tiled passes (8 -> 512-thread CTAs, 16 -> 256-thread CTAs)
+int tstwo_debug_set_fft_radix(int rows_per_thread) { g_dig = rows_per_thread == 8 ? 3 : 4; return 0; }
 
 static int check_tree(tstwo_twiddles h, uint32_t half_init, int half_log, TwiddleTree **out)
 {
