@@ -79,7 +79,7 @@ def load():
             fn = getattr(lib, name)   # AttributeError if the symbol is missing
             fn.restype = res
             fn.argtypes = args
-        for dbg in ("tstwo_debug_force_naive_fft", "tstwo_debug_set_fft_radix"):
+        for dbg in ("tstwo_debug_force_naive_fft", "tstwo_debug_set_fft_radix", "tstwo_debug_set_fft_stream"):
             getattr(lib, dbg).restype = C.c_int
             getattr(lib, dbg).argtypes = [C.c_int]
         _lib = lib

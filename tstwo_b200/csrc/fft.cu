@@ -10,6 +10,7 @@
 // (contiguous pass, lo = 0) or the 8 lowest index bits of one column (strided pass, lo >= 3), so every twiddle a
 // thread loads is reused by 4 butterflies.  All twiddles are read pre-doubled (m31::mul2).
 #include "common.cuh"
+#include "fft_params.cuh"
 #include "host_m31.h"
 #include "m31.cuh"
 
@@ -36,18 +37,6 @@ template <bool STRIDED, int DIG> struct Shape {
     static constexpr int SMEM = TILE_UNITS * 16 + TW_WORDS * 4;
 };
 
-struct PassParams {
-    ColSet src, dst;
-    int n_cols;
-    int n;                 // log size of the index space of dst
-    uint32_t src_mask;     // src index = idx & src_mask (coset replication of zero-extended coefficients)
-    int lo;                // window = index bits [lo, lo+RHO)
-    int j_min;             // relative layers j in [j_min, RHO) are applied
-    const uint32_t *tw2;   // pre-doubled twiddle (or inverse twiddle) tree
-    uint32_t tree_len;     // 2^root_log
-    uint32_t scale2;       // 2/2^n after the last inverse layer, or 0
-    uint32_t zero;         // run-time 0 (see m31::butterfly_z)
-};
 
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
 {
@@ -425,7 +414,12 @@ template <int DIG> static int launch_pass_t(bool inverse, const PassParams &p)
     }
     return 0;
 }
-static int launch_pass(bool inverse, const PassParams &p) { return g_dig == 4 ? launch_pass_t<4>(inverse, p) : launch_pass_t<3>(inverse, p); }
+static int g_stream = 1;   // 1: persistent pipelined passes (fft_stream.cu, default); 0: one CTA per tile (this file)
+static int launch_pass(bool inverse, const PassParams &p)
+{
+    if (g_stream) return stream_pass(inverse, p);
+    return g_dig == 4 ? launch_pass_t<4>(inverse, p) : launch_pass_t<3>(inverse, p);
+}
 
 static uint32_t dbl(uint32_t v) { return v + v; }
 
@@ -519,6 +513,8 @@ extern "C" {
 int tstwo_debug_force_naive_fft(int on) { g_force_naive = on != 0; return 0; }
 // tuning hook: rows per thread of the tiled passes (8 -> 512-thread CTAs, 16 -> 256-thread CTAs)
 int tstwo_debug_set_fft_radix(int rows_per_thread) { g_dig = rows_per_thread == 8 ? 3 : 4; return 0; }
+// tuning / test hook: 1 = persistent pipelined passes (default), 0 = the one-CTA-per-tile passes of this file
+int tstwo_debug_set_fft_stream(int on) { g_stream = on != 0; return 0; }
 
 static int check_tree(tstwo_twiddles h, uint32_t half_init, int half_log, TwiddleTree **out)
 {
