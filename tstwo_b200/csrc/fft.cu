@@ -383,13 +383,16 @@ static int ensure_smem_attr()
 struct Pass { int lo, j_min; };
 // passes in ascending layer order for L real layers (scripts/proto_fft.py): one contiguous 12-layer pass, then
 // strided 10-layer windows; the top window is aligned to L and skips the layers already done.
+// The TMA passes (fft_tma.cu) use a 14-layer contiguous pass and 8-layer strided windows instead.
 constexpr int W0 = Shape<false, 3>::RHO, W1 = Shape<true, 3>::RHO;
-static int plan_passes(int L, Pass out[4])
+constexpr int MAX_PASSES = 4;
+static int plan_passes(int L, Pass out[MAX_PASSES], int w0, int w1)
 {
-    int np = 0, done = W0;
+    int np = 0, done = w0;
     out[np++] = { 0, 0 };
-    while (L - done > W1) { out[np++] = { done, 0 }; done += W1; }
-    out[np++] = { L - W1, done - (L - W1) };
+    if (L <= done) return np;
+    while (L - done > w1) { out[np++] = { done, 0 }; done += w1; }
+    out[np++] = { L - w1, done - (L - w1) };
     return np;
 }
 
@@ -414,11 +417,27 @@ template <int DIG> static int launch_pass_t(bool inverse, const PassParams &p)
     }
     return 0;
 }
-static int g_stream = 1;   // 1: persistent pipelined passes (fft_stream.cu, default); 0: one CTA per tile (this file)
-static int launch_pass(bool inverse, const PassParams &p)
+// 2: persistent passes fed by bulk copies (fft_tma.cu, default where the column sets allow it); 1: persistent passes
+// with per-thread cp.async (fft_stream.cu); 0: one CTA per tile (this file)
+static int g_stream = 2;
+static int launch_pass(int mode, bool inverse, const PassParams &p)
 {
-    if (g_stream) return stream_pass(inverse, p);
+    if (mode == 2) return tma_pass(inverse, p);
+    if (mode == 1) return stream_pass(inverse, p);
     return g_dig == 4 ? launch_pass_t<4>(inverse, p) : launch_pass_t<3>(inverse, p);
+}
+// the bulk-copy passes need uniformly spaced, 16-byte aligned columns and row shards of whole 2^14-index tiles
+static int pick_mode(const ColSet &a, const ColSet &b, const ColSet &c, int n_cols)
+{
+    if (g_stream != 2) return g_stream;
+    PassParams p;
+    p.n_cols = n_cols;
+    p.src = a; p.dst = b;
+    if (!tma_pass_supported(p)) return 1;
+    p.src = c;
+    if (!tma_pass_supported(p)) return 1;
+    if (a.shard_log < TMA_W0 || b.shard_log < TMA_W0 || c.shard_log < TMA_W0) return 1;
+    return 2;
 }
 
 static uint32_t dbl(uint32_t v) { return v + v; }
@@ -433,14 +452,15 @@ int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int n, con
     if (n >= FAST_MIN_LOG && !g_force_naive) {
         int rc = ensure_smem_attr();
         if (rc) return rc;
-        Pass ps[4];
-        int np = plan_passes(n, ps);
+        const int mode = pick_mode(src, dst, dst, n_cols);
+        Pass ps[MAX_PASSES];
+        int np = mode == 2 ? plan_passes(n, ps, TMA_W0, TMA_W1) : plan_passes(n, ps, W0, W1);
         for (int k = 0; k < np; k++) {
             PassParams p;
             p.src = (k == 0) ? src : dst; p.dst = dst; p.n_cols = n_cols; p.n = n; p.src_mask = (uint32_t)(N - 1);
             p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.tw2 = t->itw2; p.tree_len = tree_len;
             p.scale2 = (k == np - 1) ? inv_n2 : 0; p.zero = 0;
-            rc = launch_pass(true, p);
+            rc = launch_pass(mode, true, p);
             if (rc) return rc;
         }
         return 0;
@@ -474,15 +494,16 @@ int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n,
     if (L >= FAST_MIN_LOG && !g_force_naive) {
         int rc = ensure_smem_attr();
         if (rc) return rc;
-        Pass ps[4];
-        int np = plan_passes(L, ps);
+        const int mode = pick_mode(src, dst, work, n_cols);
+        Pass ps[MAX_PASSES];
+        int np = mode == 2 ? plan_passes(L, ps, TMA_W0, TMA_W1) : plan_passes(L, ps, W0, W1);
         for (int k = np - 1; k >= 0; k--) {
             PassParams p;
             const bool first = (k == np - 1);
             p.src = first ? src : work; p.dst = (k == 0) ? dst : work; p.n_cols = n_cols; p.n = n;
             p.src_mask = first ? (uint32_t)((1ull << L) - 1) : (uint32_t)(N - 1);
             p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.tw2 = t->tw2; p.tree_len = tree_len; p.scale2 = 0; p.zero = 0;
-            rc = launch_pass(false, p);
+            rc = launch_pass(mode, false, p);
             if (rc) return rc;
         }
         return 0;
@@ -513,8 +534,8 @@ extern "C" {
 int tstwo_debug_force_naive_fft(int on) { g_force_naive = on != 0; return 0; }
 // tuning hook: rows per thread of the tiled passes (8 -> 512-thread CTAs, 16 -> 256-thread CTAs)
 int tstwo_debug_set_fft_radix(int rows_per_thread) { g_dig = rows_per_thread == 8 ? 3 : 4; return 0; }
-// tuning / test hook: 1 = persistent pipelined passes (default), 0 = the one-CTA-per-tile passes of this file
-int tstwo_debug_set_fft_stream(int on) { g_stream = on != 0; return 0; }
+// tuning / test hook: 2 = bulk-copy persistent passes (default), 1 = cp.async persistent passes, 0 = one CTA per tile
+int tstwo_debug_set_fft_stream(int mode) { g_stream = mode < 0 ? 0 : mode > 2 ? 2 : mode; return 0; }
 
 static int check_tree(tstwo_twiddles h, uint32_t half_init, int half_log, TwiddleTree **out)
 {

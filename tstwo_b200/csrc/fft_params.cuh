@@ -22,4 +22,11 @@ struct PassParams {
 int stream_pass(bool inverse, const PassParams &p);
 int stream_pass_init();
 
+// fft_tma.cu: persistent CTAs fed by bulk asynchronous copies (TMA).  Window sizes differ from the kernels above:
+// the contiguous pass covers TMA_W0 = 14 layers (one column x 16384 indices per tile), strided passes TMA_W1 = 8.
+constexpr int TMA_W0 = 14, TMA_W1 = 8;
+int tma_pass(bool inverse, const PassParams &p);
+int tma_pass_init();
+bool tma_pass_supported(const PassParams &p);
+
 }  // namespace tstwo

@@ -1,0 +1,533 @@
+// Circle FFT / iFFT passes for sm_100a: persistent CTAs fed by the TMA engine (bulk asynchronous copies).
+//
+// Reference semantics: CpuCirclePoly.interpolate / evaluate (packages/core/src/backend/cpu/circle.ts:84-207) with the
+// butterflies of packages/core/src/fft.ts:12-30; same layer / twiddle indexing as fft.cu.
+//
+// Why this shape.  A 64 KiB tile costs ~650 SM clocks of integer-pipe time per layer (tools/microbench_bf.cu: 10.15 clk
+// per warp-butterfly per SM sub-partition, ALU-pipe bound) and ~6000 clocks of the SM's share of HBM bandwidth for
+// its read + write (22 B/clk/SM).  The two only overlap if no warp ever waits on a copy: per-thread copies (LDG/STG,
+// 16-byte cp.async) block the in-order warps in the load/store unit whenever DRAM is the momentary bottleneck
+// (scripts/fft_trace.py timelines, profiles/r01_g_*).  Here every byte moves by cp.async.bulk:
+//
+//   CONTIGUOUS pass  tile = 16384 consecutive indices of one column, layers 0..13 (the circle layer included):
+//                    16 bulk copies of 4 KiB each way, landing 4 KiB + 16 B apart (the pad rotates the banks);
+//   STRIDED pass     tile = 256 rows (index bits [lo, lo+8)) x 64 consecutive indices of one column, layers lo..lo+7:
+//                    ONE 3-D tensor-map copy (box 64 x 256 x 1) each way, dense in shared memory.
+//
+//   * 512 threads = two groups of 256; group g transforms tiles g, g+2, ... of the CTA's list, tile i in buffer i % 3;
+//   * a unit is 16 bytes (4 consecutive indices); a thread holds 16 units x 4 lanes and applies 4 unit-level layers
+//     per stage (+ the 2 lane layers in the lowest contiguous stage): 3 stages (6+4+4) / 2 stages (4+4) per tile,
+//     exchanging in place through the tile buffer under a per-group named barrier;
+//   * the last stage's results go back to the buffer and leave as bulk stores; the buffer is refilled (tile i+3, for
+//     the other group) at the owner group's next stage boundary, once cp.async.bulk.wait_group.read says the stores
+//     have been read out.  Arrival of a tile is an mbarrier transaction count.
+#include <cuda.h>
+
+#include <cstring>
+
+#include "fft_params.cuh"
+#include "m31.cuh"
+
+namespace tstwo {
+namespace {
+
+constexpr int THREADS = 512, NBUF = 3;
+constexpr int CHUNK_BYTES = 4096 + 16;                 // contiguous pass: 256 units + one pad unit
+constexpr int BUF_BYTES = 16 * CHUNK_BYTES;            // 65792 = 514 * 128 (keeps every buffer 128-byte aligned)
+// twiddles of a run of tiles (same high index bits): unit-level heap, level l (0 = lowest) at HEAP_BASE(l); levels
+// 0..5 and the T_1 slice carry 4 pad words per 256 units so that lanes 256 units apart hit distinct bank groups
+constexpr int HEAP_WORDS = 4096 + 6 * 64;
+constexpr int T1_WORDS = 4096 + 64;
+constexpr int SMEM_BYTES = NBUF * BUF_BYTES + (HEAP_WORDS + T1_WORDS) * 4 + 64;
+static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KiB of shared memory a CTA can opt into");
+
+struct alignas(64) TmaParams {
+    CUtensorMap src_map, dst_map;   // strided pass only
+    PassParams p;
+    uint32_t n_tiles;               // all tiles of the pass
+    uint32_t tiles_per_hi;          // consecutive tile ids sharing one twiddle heap
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void *src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t done, spins = 0;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (!done && ++spins > (1u << 22)) __trap();   // a lost tile is a bug: fail loudly instead of hanging the GPU
+    } while (!done);
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void *dst, uint32_t src, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tensor_g2s(uint32_t dst, const CUtensorMap *map, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tensor_s2g(const CUtensorMap *map, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t src)
+{
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3}], [%4];"
+                 ::"l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(src) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, 256;" ::"r"(g + 1) : "memory"); }
+
+#ifdef TSTWO_FFT_TRACE
+// debug timeline: per (CTA 0, group, tile, point) the SM clock; see scripts/fft_trace.py
+__device__ long long *g_trace = nullptr;
+__device__ int g_trace_cta = 0;
+#define TRACE(pt, dep) do { if (g_trace && blockIdx.x == g_trace_cta && tg == 0 && tr_n < 64) { long long c_; \
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c_) : "r"(dep) : "memory"); g_trace[(g * 64 + tr_n) * 16 + (pt)] = c_; } } while (0)
+// second region: start clock of every tile of CTA 0 (slot 2048 + 1024 g + n); third: per-CTA begin / end globaltimer
+#define TRACE_TILE() do { if (g_trace && blockIdx.x == g_trace_cta && tg == 0 && tr_all < 1024) { long long c_; \
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(c_) :: "memory"); g_trace[2048 + 1024 * g + tr_all] = c_; tr_all++; } } while (0)
+#define TRACE_CTA(which) do { if (g_trace && threadIdx.x == 0) { long long c_; \
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(c_) :: "memory"); g_trace[4096 + 2 * blockIdx.x + (which)] = c_; } } while (0)
+#else
+#define TRACE(pt, dep) do { } while (0)
+#define TRACE_TILE() do { } while (0)
+#define TRACE_CTA(which) do { } while (0)
+#endif
+
+// ---- stage geometry.  U = 12-bit unit index inside the tile: contiguous U = index >> 2; strided U = row << 4 |
+// (index >> 2 & 15).  A thread owns the 16 units U0 | d << SU.  In every map the lanes of a quarter warp differ in
+// bits that move the physical unit (U + PAD * (U >> 8)) across the 8 bank groups: U[0..2], or U[8..10] where the
+// thread owns U[0..3] itself (lowest contiguous stage; that is what the chunk pad is for).
+//   contiguous: ST0 = lanes + U[0..3] (layers 0..5), ST1 = U[4..7] (6..9), ST2 = U[8..11] (10..13)
+//   strided   : ST0 = U[4..7] (window layers 0..3), ST1 = U[8..11] (4..7)
+template <bool STRIDED, int ST> struct Stg {
+    static constexpr int SU = STRIDED ? 4 + 4 * ST : 4 * ST;
+    static constexpr int SL = STRIDED ? 4 * ST : 4 * ST;     // heap level of digit bit 0
+    static constexpr int PAD = STRIDED ? 0 : 1;
+    __device__ static __forceinline__ int u0(int tg)
+    {
+        if (SU == 0) return ((tg & 7) << 8) | (((tg >> 3) & 15) << 4) | ((tg >> 7) << 11);
+        if (SU == 4) return (tg & 15) | ((tg >> 4) << 8);
+        return tg;
+    }
+    __device__ static __forceinline__ constexpr int unit_off(int d) { return (d << SU) + PAD * ((d << SU) >> 8); }
+    __device__ static __forceinline__ int phys0(int tg) { const int U0 = u0(tg); return U0 + PAD * (U0 >> 8); }
+};
+
+template <bool STRIDED, int ST> __device__ __forceinline__ void tile_load(const uint4 *buf, int tg, uint32_t (&v)[16][4])
+{
+    using S = Stg<STRIDED, ST>;
+    const uint4 *b = buf + S::phys0(tg);
+#pragma unroll
+    for (int d = 0; d < 16; d++) {
+        const uint4 a = b[S::unit_off(d)];
+        v[d][0] = a.x; v[d][1] = a.y; v[d][2] = a.z; v[d][3] = a.w;
+    }
+}
+template <bool STRIDED, int ST> __device__ __forceinline__ void tile_store(uint4 *buf, int tg, const uint32_t (&v)[16][4])
+{
+    using S = Stg<STRIDED, ST>;
+    uint4 *b = buf + S::phys0(tg);
+#pragma unroll
+    for (int d = 0; d < 16; d++) b[S::unit_off(d)] = make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]);
+}
+
+// Heap position of entry q of level l.  NLEV levels (12 contiguous / 8 strided): level l holds 2^(NLEV-1-l) entries at
+// 2^(NLEV-1-l) + q; in the contiguous pass levels 0..5 are followed by 64 pad words each and entry q of such a level
+// moves up by 4 words per 256 units it lies into the tile (q >> (7 - l) == unit >> 8).
+template <bool STRIDED> __device__ __forceinline__ constexpr int heap_base(int l)
+{
+    return STRIDED ? (1 << (7 - l)) : (1 << (11 - l)) + (l <= 5 ? 64 * (5 - l) : 0);
+}
+
+// unit-level layers of one stage: digit bit k <-> heap level l = SL + k; the butterfly (d, d | 1 << k) uses entry
+// q = unit >> (l + 1); a thread needs 8 >> k consecutive entries per level.
+template <bool STRIDED, int ST, bool INV, bool FULL>
+__device__ __forceinline__ void unit_layers(uint32_t (&v)[16][4], const uint32_t *heap, int tg, int j_min)
+{
+    using S = Stg<STRIDED, ST>;
+    const int U0 = S::u0(tg);
+    const int ub = STRIDED ? (U0 >> 4) : U0;           // unit-level coordinate the heap is indexed by (row / unit)
+    const int padw = 4 * (U0 >> 8);
+#pragma unroll
+    for (int kk = 0; kk < 4; kk++) {
+        const int k = INV ? kk : 3 - kk;
+        const int l = S::SL + k;
+        if (!FULL && l < j_min) continue;              // uniform across the grid
+        const int cnt = 8 >> k;
+        const uint32_t *q = heap + heap_base<STRIDED>(l) + (ub >> (l + 1)) + ((!STRIDED && l <= 5) ? padw : 0);
+        uint32_t t[8];
+        if (cnt == 8) {
+            const uint4 a = *reinterpret_cast<const uint4 *>(q), b = *reinterpret_cast<const uint4 *>(q + 4);
+            t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w;
+        } else if (cnt == 4) {
+            const uint4 a = *reinterpret_cast<const uint4 *>(q);
+            t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w;
+        } else if (cnt == 2) {
+            const uint2 a = *reinterpret_cast<const uint2 *>(q);
+            t[0] = a.x; t[1] = a.y;
+        } else t[0] = q[0];
+#pragma unroll
+        for (int d = 0; d < 16; d++) {
+            if (d & (1 << k)) continue;
+            const uint32_t tw = t[d >> (k + 1)];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                if (INV) m31::ibutterfly(v[d][e], v[d | (1 << k)][e], tw);
+                else m31::butterfly(v[d][e], v[d | (1 << k)][e], tw);
+            }
+        }
+    }
+}
+
+// layers 1 and 0 of the contiguous pass act inside a unit (lanes = index bits 0..1); both read the T_1 slice:
+// layer 1: (lane 0, lane 2), (lane 1, lane 3) with T_1[unit]; circle layer 0: (0,1), (2,3) with, per unit pair
+// (x, y) = T_1[2e], T_1[2e+1]:  unit 2e -> [y, -y], unit 2e+1 -> [-x, x]   (circle.ts:270-278)
+template <bool INV> __device__ __forceinline__ void lane_layers(uint32_t (&v)[16][4], const uint32_t *tw1, int tg)
+{
+    const uint32_t P2 = 0xfffffffeu;
+    const int U0 = Stg<false, 0>::u0(tg);
+    const uint32_t *q = tw1 + U0 + 4 * (U0 >> 8);
+#pragma unroll
+    for (int h = 0; h < 4; h++) {                      // 4 units at a time keeps the twiddle registers short-lived
+        const uint4 a = *reinterpret_cast<const uint4 *>(q + 4 * h);
+        const uint32_t t[4] = { a.x, a.y, a.z, a.w };
+#pragma unroll
+        for (int pass = 0; pass < 2; pass++) {
+            const bool circle = INV ? pass == 0 : pass == 1;
+            if (circle) {
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+                    const uint32_t x = t[2 * e], y = t[2 * e + 1];
+                    uint32_t(&a0)[4] = v[4 * h + 2 * e], (&a1)[4] = v[4 * h + 2 * e + 1];
+                    if (INV) {
+                        m31::ibutterfly(a0[0], a0[1], y); m31::ibutterfly(a0[2], a0[3], P2 - y);
+                        m31::ibutterfly(a1[0], a1[1], P2 - x); m31::ibutterfly(a1[2], a1[3], x);
+                    } else {
+                        m31::butterfly(a0[0], a0[1], y); m31::butterfly(a0[2], a0[3], P2 - y);
+                        m31::butterfly(a1[0], a1[1], P2 - x); m31::butterfly(a1[2], a1[3], x);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    uint32_t(&a)[4] = v[4 * h + e];
+                    if (INV) { m31::ibutterfly(a[0], a[2], t[e]); m31::ibutterfly(a[1], a[3], t[e]); }
+                    else { m31::butterfly(a[0], a[2], t[e]); m31::butterfly(a[1], a[3], t[e]); }
+                }
+            }
+        }
+    }
+}
+
+template <bool STRIDED, int ST, bool INV, bool FULL>
+__device__ __forceinline__ void stage_math(uint32_t (&v)[16][4], const uint32_t *heap, int tg, int j_min)
+{
+    if (!STRIDED && ST == 0 && INV) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
+    unit_layers<STRIDED, ST, INV, FULL>(v, heap, tg, j_min);
+    if (!STRIDED && ST == 0 && !INV) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
+}
+
+// ---- tile coordinates
+struct Tile { uint32_t hi, col, mid; };
+template <bool STRIDED> __device__ __forceinline__ Tile decode(const TmaParams &sp, uint32_t t, uint32_t hi)
+{
+    const uint32_t rem = t - hi * sp.tiles_per_hi;
+    if (STRIDED) return { hi, rem >> (sp.p.lo - 6), rem & ((1u << (sp.p.lo - 6)) - 1) };
+    return { hi, rem, 0 };
+}
+
+// fetch tile `tl` into the buffer at shared address `buf`; its 64 KiB complete one phase of `bar`
+template <bool STRIDED>
+__device__ __forceinline__ void tile_fetch(const TmaParams &sp, const Tile tl, uint32_t buf, uint32_t bar, int tg)
+{
+    const PassParams &p = sp.p;
+    if (STRIDED) {
+        if (tg == 0) {
+            mbar_arrive_expect_tx(bar, 65536);
+            tensor_g2s(buf, &sp.src_map, tl.mid << 6, ((tl.hi << (p.lo + 8)) & p.src_mask) >> p.lo, tl.col, bar);
+        }
+    } else if (tg < 16) {
+        if (tg == 0) mbar_arrive_expect_tx(bar, 65536);
+        __syncwarp(0xffffu);
+        const uint32_t *src = p.src.col(tl.col) + p.src.off((tl.hi << 14) & p.src_mask) + 1024 * tg;
+        bulk_g2s(buf + tg * CHUNK_BYTES, src, 4096, bar);
+    }
+}
+// the transformed tile (complete in the buffer, made visible to the async proxy by the caller) leaves as bulk stores
+template <bool STRIDED>
+__device__ __forceinline__ void tile_drain(const TmaParams &sp, const Tile tl, uint32_t buf, int tg)
+{
+    const PassParams &p = sp.p;
+    if (STRIDED) {
+        if (tg == 0) { tensor_s2g(&sp.dst_map, tl.mid << 6, tl.hi << 8, tl.col, buf); bulk_commit(); }
+    } else if (tg < 16) {
+        uint32_t *dst = p.dst.col(tl.col) + p.dst.off(tl.hi << 14) + 1024 * tg;
+        bulk_s2g(dst, buf + tg * CHUNK_BYTES, 4096);
+        bulk_commit();
+    }
+}
+
+// twiddles of the run of tiles with high bits `hi` (all 512 threads; one cp.async group)
+template <bool STRIDED> __device__ __forceinline__ void stage_twiddles(uint32_t *heap, const PassParams &p, uint32_t hi, int tid)
+{
+    constexpr int NLEV = STRIDED ? 8 : 12;
+    const int base_layer = STRIDED ? p.lo : 2;         // tree layer of heap level 0
+    for (int e = 4 * tid; e < (1 << NLEV); e += 4 * THREADS) {
+        if (e == 0) {
+            for (int ee = 1; ee < 4; ee++) {           // the top level (1 entry) and the one below (2 entries)
+                const int lg = ee >> 1, l = NLEV - 1 - lg, i = base_layer + l;
+                if (STRIDED && l < p.j_min) continue;
+                cp_async4(smem_u32(heap + ee), p.tw2 + (p.tree_len - (1u << (p.n - i))) + (hi << lg) + (ee - (1 << lg)));
+            }
+            continue;
+        }
+        const int lg = 31 - __clz(e), l = NLEV - 1 - lg, i = base_layer + l, q = e - (1 << lg);
+        if (STRIDED && l < p.j_min) continue;
+        const int dst = STRIDED ? e : e + (l <= 5 ? 64 * (5 - l) + 4 * (q >> (7 - l)) : 0);
+        cp_async16(smem_u32(heap + dst), p.tw2 + (p.tree_len - (1u << (p.n - i))) + (hi << lg) + q);
+    }
+    if (!STRIDED)
+        for (int u = 4 * tid; u < 4096; u += 4 * THREADS)
+            cp_async16(smem_u32(heap + HEAP_WORDS + u + 4 * (u >> 8)), p.tw2 + (p.tree_len - (1u << (p.n - 1))) + (hi << 12) + u);
+    asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
+// one stage of a tile: load -> butterflies -> store back
+template <bool STRIDED, int ST, bool INV, bool FULL>
+__device__ __forceinline__ void run_stage(uint4 *buf, const uint32_t *heap, int tg, int j_min, uint32_t scale2)
+{
+    uint32_t v[16][4];
+    tile_load<STRIDED, ST>(buf, tg, v);
+    stage_math<STRIDED, ST, INV, FULL>(v, heap, tg, j_min);
+    if (scale2) {
+#pragma unroll
+        for (int d = 0; d < 16; d++)
+#pragma unroll
+            for (int e = 0; e < 4; e++) v[d][e] = m31::mul2(v[d][e], scale2);
+    }
+    tile_store<STRIDED, ST>(buf, tg, v);
+}
+
+template <bool INV, bool STRIDED, bool FULL>
+__global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_constant__ TmaParams sp)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint32_t *heap = reinterpret_cast<uint32_t *>(smem + NBUF * BUF_BYTES);
+    const uint32_t bar0 = smem_u32(heap + HEAP_WORDS + T1_WORDS);
+    const uint32_t buf0 = smem_u32(smem);
+    const PassParams &p = sp.p;
+    const int tid = threadIdx.x, g = tid >> 8, tg = tid & 255;
+
+    // this CTA's tile list: t(k) = start + k * step.  Strided passes interleave CTAs (neighbouring tiles, i.e.
+    // neighbouring 256-byte pieces of the same rows, are in flight together); the contiguous pass walks consecutive
+    // tiles of its own block.  Either way a twiddle heap serves a long run of tiles.
+    uint32_t start, step, count;
+    if (STRIDED) {
+        start = blockIdx.x; step = gridDim.x;
+        count = start < sp.n_tiles ? (sp.n_tiles - start + step - 1) / step : 0;
+    } else {
+        const uint32_t a = (uint32_t)((uint64_t)sp.n_tiles * blockIdx.x / gridDim.x);
+        const uint32_t b = (uint32_t)((uint64_t)sp.n_tiles * (blockIdx.x + 1) / gridDim.x);
+        start = a; step = 1; count = b - a;
+    }
+    if (tid == 0) {
+        for (int b = 0; b < NBUF; b++) mbar_init(bar0 + 8 * b, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    uint32_t fills0 = 0, fills1 = 0, fills2 = 0;       // completed phases of the three barriers
+#ifdef TSTWO_FFT_TRACE
+    int tr_n = 0, tr_all = 0;
+#endif
+    TRACE_CTA(0);
+
+    uint32_t k = 0;
+    while (k < count) {
+        const uint32_t t0 = start + k * step;
+        const uint32_t hi = t0 / sp.tiles_per_hi;
+        uint32_t len = ((hi + 1) * sp.tiles_per_hi - t0 + step - 1) / step;   // tiles of this run that are mine
+        if (len > count - k) len = count - k;
+        __syncthreads();                               // previous run drained: buffers and heap are free
+        stage_twiddles<STRIDED>(heap, p, hi, tid);
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < NBUF; i++)
+            if ((uint32_t)i < len && (i & 1) == g)
+                tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar0 + 8 * i, tg);
+        uint32_t refill = 0xffffffffu;                 // tile of mine whose buffer is refilled once its stores have drained
+
+        for (uint32_t i = g; i < len; i += 2) {
+            const uint32_t b = i % 3, round = i / 3;
+            const uint32_t fills = b == 0 ? fills0 : b == 1 ? fills1 : fills2;
+            uint4 *buf = reinterpret_cast<uint4 *>(smem + b * BUF_BYTES);
+            const Tile tl = decode<STRIDED>(sp, t0 + i * step, hi);
+            TRACE(0, i);
+            TRACE_TILE();
+            mbar_wait(bar0 + 8 * b, (fills + round) & 1);
+            TRACE(1, i);
+            constexpr int NST = STRIDED ? 2 : 3;
+            constexpr int FIRST = INV ? 0 : NST - 1, LAST = INV ? NST - 1 : 0;
+            run_stage<STRIDED, FIRST, INV, FULL>(buf, heap, tg, p.j_min, 0);
+            TRACE(2, i);
+            if (refill != 0xffffffffu && tg < 16) bulk_wait_read();   // my stores of tile `refill` have been read out
+            group_sync(g);
+            if (refill != 0xffffffffu) {               // ... and so have everybody else's: fetch tile refill + 3 there
+                const uint32_t rb = refill % 3;
+                tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (refill + 3) * step, hi), buf0 + rb * BUF_BYTES, bar0 + 8 * rb, tg);
+                refill = 0xffffffffu;
+            }
+            TRACE(3, i);
+            if (NST == 3) {
+                run_stage<STRIDED, 1, INV, FULL>(buf, heap, tg, p.j_min, 0);
+                TRACE(4, i);
+                group_sync(g);
+                TRACE(5, i);
+            }
+            run_stage<STRIDED, LAST, INV, FULL>(buf, heap, tg, p.j_min, INV ? p.scale2 : 0u);
+            TRACE(6, i);
+            fence_proxy_async();                       // generic-proxy stores above -> async-proxy reads below
+            group_sync(g);
+            tile_drain<STRIDED>(sp, tl, buf0 + b * BUF_BYTES, tg);
+            if (i + 3 < len) refill = i;
+            TRACE(7, i);
+#ifdef TSTWO_FFT_TRACE
+            tr_n++;
+#endif
+        }
+        if (tg < 16) bulk_wait_read();                 // the buffers are reused by the next run and must outlive the copies
+        fills0 += (len + 2) / 3; fills1 += (len + 1) / 3; fills2 += len / 3;
+        k += len;
+    }
+    TRACE_CTA(1);
+}
+
+template <bool INV, bool STRIDED, bool FULL> cudaError_t set_attr()
+{
+    return cudaFuncSetAttribute(fft_tma_kernel<INV, STRIDED, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+}
+bool g_ready = false;
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+
+// 3-D view of a column set for the strided pass: (index & (2^lo - 1), index >> lo, column), box 64 x 256 x 1
+int make_map(CUtensorMap *map, const ColSet &cs, int n_cols, int log_len, int lo)
+{
+    const cuuint64_t dims[3] = { 1ull << lo, 1ull << (log_len - lo), (cuuint64_t)n_cols };
+    const cuuint64_t strides[2] = { 4ull << lo, n_cols > 1 ? cs.stride * 4 : (4ull << log_len) };
+    const cuuint32_t box[3] = { 64, 256, 1 }, estr[3] = { 1, 1, 1 };
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<uint32_t *>(cs.base), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(TSTWO_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for lo=%d len=2^%d cols=%d", (int)r, lo, log_len, n_cols);
+    return 0;
+}
+
+}  // namespace
+
+#ifdef TSTWO_FFT_TRACE
+int tma_trace_set(long long *buf)
+{
+    TS_CUDA(cudaMemcpyToSymbol(g_trace, &buf, sizeof buf));
+    return 0;
+}
+int tma_trace_cta(int cta)
+{
+    TS_CUDA(cudaMemcpyToSymbol(g_trace_cta, &cta, sizeof cta));
+    return 0;
+}
+#endif
+
+int tma_pass_init()
+{
+    if (g_ready) return 0;
+    TS_CUDA((set_attr<false, false, true>())); TS_CUDA((set_attr<true, false, true>()));
+    TS_CUDA((set_attr<false, true, true>()));  TS_CUDA((set_attr<true, true, true>()));
+    TS_CUDA((set_attr<false, true, false>())); TS_CUDA((set_attr<true, true, false>()));
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    TS_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (!fn || qres != cudaDriverEntryPointSuccess) return fail(TSTWO_ERR_CUDA, "driver has no cuTensorMapEncodeTiled");
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    g_ready = true;
+    return 0;
+}
+
+// Column sets the bulk copies can address: uniformly spaced columns (one tensor map covers them).  Scattered column
+// tables fall back to the per-thread-copy kernels of fft_stream.cu / fft.cu.
+bool tma_pass_supported(const PassParams &p)
+{
+    if (p.src.table || p.dst.table) return false;
+    if ((reinterpret_cast<uintptr_t>(p.src.base) | reinterpret_cast<uintptr_t>(p.dst.base)) & 15) return false;
+    if (p.n_cols > 1 && ((p.src.stride | p.dst.stride) & 3)) return false;
+    return true;
+}
+
+int tma_pass(bool inverse, const PassParams &p)
+{
+    int rc = tma_pass_init();
+    if (rc) return rc;
+    TmaParams sp;
+    memset(&sp, 0, sizeof sp);
+    sp.p = p;
+    const bool strided = p.lo != 0;
+    uint64_t n_hi, per_hi;
+    if (strided) {
+        if (p.src.shard_log != 31 || p.dst.shard_log != 31) return fail(TSTWO_ERR_BAD_ARG, "strided FFT pass on a row-sharded column set");
+        if (p.lo < 6 || p.lo + TMA_W1 > p.n) return fail(TSTWO_ERR_BAD_ARG, "bad strided window lo=%d n=%d", p.lo, p.n);
+        int src_log = 0;
+        while ((1ull << src_log) <= p.src_mask) src_log++;          // src holds 2^src_log words per column
+        if ((rc = make_map(&sp.src_map, p.src, p.n_cols, src_log, p.lo))) return rc;
+        if ((rc = make_map(&sp.dst_map, p.dst, p.n_cols, p.n, p.lo))) return rc;
+        n_hi = 1ull << (p.n - p.lo - TMA_W1);
+        per_hi = ((uint64_t)p.n_cols) << (p.lo - 6);
+    } else {
+        n_hi = 1ull << (p.n - TMA_W0);
+        per_hi = (uint64_t)p.n_cols;
+    }
+    if (n_hi * per_hi >= (1ull << 31)) return fail(TSTWO_ERR_BAD_ARG, "FFT pass too large (%llu tiles)", (unsigned long long)(n_hi * per_hi));
+    sp.n_tiles = (uint32_t)(n_hi * per_hi);
+    sp.tiles_per_hi = (uint32_t)per_hi;
+    unsigned grid = (unsigned)ctx().sm_count;
+    if (grid > sp.n_tiles) grid = sp.n_tiles;
+    if (!strided) {
+        if (inverse) TS_LAUNCH((fft_tma_kernel<true, false, true>), grid, THREADS, SMEM_BYTES, sp);
+        else TS_LAUNCH((fft_tma_kernel<false, false, true>), grid, THREADS, SMEM_BYTES, sp);
+    } else if (p.j_min == 0) {
+        if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, true>), grid, THREADS, SMEM_BYTES, sp);
+        else TS_LAUNCH((fft_tma_kernel<false, true, true>), grid, THREADS, SMEM_BYTES, sp);
+    } else {
+        if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, false>), grid, THREADS, SMEM_BYTES, sp);
+        else TS_LAUNCH((fft_tma_kernel<false, true, false>), grid, THREADS, SMEM_BYTES, sp);
+    }
+    return 0;
+}
+
+}  // namespace tstwo
+
+#ifdef TSTWO_FFT_TRACE
+extern "C" int tstwo_debug_fft_trace(tstwo_dptr buf) { return tstwo::tma_trace_set((long long *)buf); }
+extern "C" int tstwo_debug_fft_trace_cta(int cta) { return tstwo::tma_trace_cta(cta); }
+#endif
