@@ -31,7 +31,7 @@ def run(n_cols, log):
     chk(L.tstwo_twiddles_precompute(C.c_uint32(1 << (31 - log - 2)), log, C.byref(tw)))
     TB = 4096 + 2 * 160
     tb = malloc(TB * 8)
-    names = ["wait", "got", "stageA", "sync+refill", "stageB", "sync", "stageC", "fence+sync+drain"]
+    names = ["wait", "got", "stages", "sync+drain+refill"]
     root = (C.c_uint8 * 32)()
     for which in range(4):
         # passes run in the order inv-contig, inv-strided, fwd-strided, fwd-contig: trace one at a time by arming the

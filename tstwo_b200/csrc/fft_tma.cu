@@ -46,6 +46,9 @@ struct alignas(64) TmaParams {
     PassParams p;
     uint32_t n_tiles;               // all tiles of the pass
     uint32_t tiles_per_hi;          // consecutive tile ids sharing one twiddle heap
+    uint32_t cosets_log;            // strided pass reading zero-extended coefficients (src_mask): the 2^cosets_log tiles that
+                                    // read the same source tile are neighbours in the list (the re-reads hit L2) and all
+                                    // their heaps are resident; the tile's coset is then its "hi"
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -161,22 +164,24 @@ template <bool STRIDED> __device__ __forceinline__ constexpr int heap_base(int l
     return STRIDED ? (1 << (7 - l)) : (1 << (11 - l)) + (l <= 5 ? 64 * (5 - l) : 0);
 }
 
-// unit-level layers of one stage: digit bit k <-> heap level l = SL + k; the butterfly (d, d | 1 << k) uses entry
-// q = unit >> (l + 1); a thread needs 8 >> k consecutive entries per level.
-template <bool STRIDED, int ST, bool INV, bool FULL>
-__device__ __forceinline__ void unit_layers(uint32_t (&v)[16][4], const uint32_t *heap, int tg, int j_min)
+// unit-level layers of one stage: digit bit k <-> heap level l = sl + k; the butterfly (d, d | 1 << k) uses entry
+// q = unit >> (l + 1); a thread needs 8 >> k consecutive entries per level.  The stage is a RUN-TIME parameter (U0 =
+// the thread's base unit, sl = heap level of digit bit 0): one copy of the butterfly code serves all stages, which
+// keeps a kernel's loop body within the instruction cache (fully unrolled per stage it is ~64 KiB and the two groups,
+// sitting in different stages, evict each other: ncu stall_no_instruction 2.9 per issue, profiles/r01_k_*).
+template <bool STRIDED, bool INV, bool FULL>
+__device__ __forceinline__ void unit_layers(uint32_t (&v)[16][4], const uint32_t *heap, int U0, int sl, int j_min)
 {
-    using S = Stg<STRIDED, ST>;
-    const int U0 = S::u0(tg);
     const int ub = STRIDED ? (U0 >> 4) : U0;           // unit-level coordinate the heap is indexed by (row / unit)
     const int padw = 4 * (U0 >> 8);
 #pragma unroll
     for (int kk = 0; kk < 4; kk++) {
         const int k = INV ? kk : 3 - kk;
-        const int l = S::SL + k;
+        const int l = sl + k;
         if (!FULL && l < j_min) continue;              // uniform across the grid
         const int cnt = 8 >> k;
-        const uint32_t *q = heap + heap_base<STRIDED>(l) + (ub >> (l + 1)) + ((!STRIDED && l <= 5) ? padw : 0);
+        const int base = STRIDED ? (1 << (7 - l)) : (1 << (11 - l)) + (l <= 5 ? 64 * (5 - l) + padw : 0);
+        const uint32_t *q = heap + base + (ub >> (l + 1));
         uint32_t t[8];
         if (cnt == 8) {
             const uint4 a = *reinterpret_cast<const uint4 *>(q), b = *reinterpret_cast<const uint4 *>(q + 4);
@@ -241,18 +246,14 @@ template <bool INV> __device__ __forceinline__ void lane_layers(uint32_t (&v)[16
     }
 }
 
-template <bool STRIDED, int ST, bool INV, bool FULL>
-__device__ __forceinline__ void stage_math(uint32_t (&v)[16][4], const uint32_t *heap, int tg, int j_min)
-{
-    if (!STRIDED && ST == 0 && INV) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
-    unit_layers<STRIDED, ST, INV, FULL>(v, heap, tg, j_min);
-    if (!STRIDED && ST == 0 && !INV) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
-}
-
 // ---- tile coordinates
 struct Tile { uint32_t hi, col, mid; };
 template <bool STRIDED> __device__ __forceinline__ Tile decode(const TmaParams &sp, uint32_t t, uint32_t hi)
 {
+    if (STRIDED && sp.cosets_log) {
+        const uint32_t r = t >> sp.cosets_log;
+        return { t & ((1u << sp.cosets_log) - 1), r >> (sp.p.lo - 6), r & ((1u << (sp.p.lo - 6)) - 1) };
+    }
     const uint32_t rem = t - hi * sp.tiles_per_hi;
     if (STRIDED) return { hi, rem >> (sp.p.lo - 6), rem & ((1u << (sp.p.lo - 6)) - 1) };
     return { hi, rem, 0 };
@@ -314,20 +315,35 @@ template <bool STRIDED> __device__ __forceinline__ void stage_twiddles(uint32_t 
     asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 }
 
-// one stage of a tile: load -> butterflies -> store back
-template <bool STRIDED, int ST, bool INV, bool FULL>
-__device__ __forceinline__ void run_stage(uint4 *buf, const uint32_t *heap, int tg, int j_min, uint32_t scale2)
+// all stages of a tile, in place in its buffer: load -> butterflies -> store back, group barrier between stages
+template <bool STRIDED, bool INV, bool FULL, typename AtFirstBoundary>
+__device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap, int tg, int g, int j_min, uint32_t scale2,
+                                               AtFirstBoundary at_first_boundary)
 {
-    uint32_t v[16][4];
-    tile_load<STRIDED, ST>(buf, tg, v);
-    stage_math<STRIDED, ST, INV, FULL>(v, heap, tg, j_min);
-    if (scale2) {
+    constexpr int NST = STRIDED ? 2 : 3, TOP = NST - 1;
+#pragma unroll 1
+    for (int s = 0; s < NST; s++) {
+        const int st = INV ? s : TOP - s;
+        uint32_t v[16][4];
+        int U0;
+        if (st == 0) { tile_load<STRIDED, 0>(buf, tg, v); U0 = Stg<STRIDED, 0>::u0(tg); }
+        else if (st == TOP) { tile_load<STRIDED, TOP>(buf, tg, v); U0 = Stg<STRIDED, TOP>::u0(tg); }
+        else { tile_load<STRIDED, 1>(buf, tg, v); U0 = Stg<STRIDED, 1>::u0(tg); }
+        if (!STRIDED && INV && st == 0) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
+        unit_layers<STRIDED, INV, FULL>(v, heap, U0, 4 * st, j_min);
+        if (!STRIDED && !INV && st == 0) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
+        if (INV && s == TOP && scale2) {
 #pragma unroll
-        for (int d = 0; d < 16; d++)
+            for (int d = 0; d < 16; d++)
 #pragma unroll
-            for (int e = 0; e < 4; e++) v[d][e] = m31::mul2(v[d][e], scale2);
+                for (int e = 0; e < 4; e++) v[d][e] = m31::mul2(v[d][e], scale2);
+        }
+        if (st == 0) tile_store<STRIDED, 0>(buf, tg, v);
+        else if (st == TOP) tile_store<STRIDED, TOP>(buf, tg, v);
+        else tile_store<STRIDED, 1>(buf, tg, v);
+        if (s == 0) at_first_boundary();
+        if (s < TOP) group_sync(g);
     }
-    tile_store<STRIDED, ST>(buf, tg, v);
 }
 
 template <bool INV, bool STRIDED, bool FULL>
@@ -369,13 +385,14 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
         uint32_t len = ((hi + 1) * sp.tiles_per_hi - t0 + step - 1) / step;   // tiles of this run that are mine
         if (len > count - k) len = count - k;
         __syncthreads();                               // previous run drained: buffers and heap are free
-        stage_twiddles<STRIDED>(heap, p, hi, tid);
+        if (STRIDED && sp.cosets_log) {
+            for (uint32_t c = 0; c < (1u << sp.cosets_log); c++) stage_twiddles<STRIDED>(heap + 256 * c, p, c, tid);
+        } else stage_twiddles<STRIDED>(heap, p, hi, tid);
         __syncthreads();
 #pragma unroll
         for (int i = 0; i < NBUF; i++)
             if ((uint32_t)i < len && (i & 1) == g)
-                tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar0 + 8 * i, tg);
-        uint32_t refill = 0xffffffffu;                 // tile of mine whose buffer is refilled once its stores have drained
+                tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar0 + 8 * i, tg);        uint32_t refill = 0xffffffffu;                 // DEFER: tile of mine whose buffer is still to be refilled
 
         for (uint32_t i = g; i < len; i += 2) {
             const uint32_t b = i % 3, round = i / 3;
@@ -386,31 +403,31 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
             TRACE_TILE();
             mbar_wait(bar0 + 8 * b, (fills + round) & 1);
             TRACE(1, i);
-            constexpr int NST = STRIDED ? 2 : 3;
-            constexpr int FIRST = INV ? 0 : NST - 1, LAST = INV ? NST - 1 : 0;
-            run_stage<STRIDED, FIRST, INV, FULL>(buf, heap, tg, p.j_min, 0);
+            // The lanes that issue the stores wait until those have been read out of shared memory and refill the buffer
+            // at once (the other seven warps are already on the next tile).  DEFER = refill at the first stage boundary
+            // of the group's next tile instead, so that nobody blocks on the read-out.
+            constexpr bool DEFER = false;   // measured: deferring costs the inverse contiguous pass 20 % (its first stage is the longest)
+            const uint32_t *tile_heap = (STRIDED && sp.cosets_log) ? heap + 256 * tl.hi : heap;
+            transform_tile<STRIDED, INV, FULL>(buf, tile_heap, tg, g, p.j_min, p.scale2, [&]() {
+                if (DEFER && refill != 0xffffffffu) {
+                    if (tg < 16) bulk_wait_read();
+                    const uint32_t rb = refill % 3;
+                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (refill + 3) * step, hi), buf0 + rb * BUF_BYTES, bar0 + 8 * rb, tg);
+                    refill = 0xffffffffu;
+                }
+            });
             TRACE(2, i);
-            if (refill != 0xffffffffu && tg < 16) bulk_wait_read();   // my stores of tile `refill` have been read out
-            group_sync(g);
-            if (refill != 0xffffffffu) {               // ... and so have everybody else's: fetch tile refill + 3 there
-                const uint32_t rb = refill % 3;
-                tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (refill + 3) * step, hi), buf0 + rb * BUF_BYTES, bar0 + 8 * rb, tg);
-                refill = 0xffffffffu;
-            }
-            TRACE(3, i);
-            if (NST == 3) {
-                run_stage<STRIDED, 1, INV, FULL>(buf, heap, tg, p.j_min, 0);
-                TRACE(4, i);
-                group_sync(g);
-                TRACE(5, i);
-            }
-            run_stage<STRIDED, LAST, INV, FULL>(buf, heap, tg, p.j_min, INV ? p.scale2 : 0u);
-            TRACE(6, i);
             fence_proxy_async();                       // generic-proxy stores above -> async-proxy reads below
             group_sync(g);
             tile_drain<STRIDED>(sp, tl, buf0 + b * BUF_BYTES, tg);
-            if (i + 3 < len) refill = i;
-            TRACE(7, i);
+            if (i + 3 < len) {
+                if (DEFER) refill = i;
+                else {
+                    if (tg < 16) bulk_wait_read();
+                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (i + 3) * step, hi), buf0 + b * BUF_BYTES, bar0 + 8 * b, tg);
+                }
+            }
+            TRACE(3, i);
 #ifdef TSTWO_FFT_TRACE
             tr_n++;
 #endif
@@ -503,6 +520,11 @@ int tma_pass(bool inverse, const PassParams &p)
         if ((rc = make_map(&sp.dst_map, p.dst, p.n_cols, p.n, p.lo))) return rc;
         n_hi = 1ull << (p.n - p.lo - TMA_W1);
         per_hi = ((uint64_t)p.n_cols) << (p.lo - 6);
+        if (src_log < p.n && p.lo + TMA_W1 == src_log && p.n - src_log <= 3) {   // top window of a blown-up evaluation
+            sp.cosets_log = (uint32_t)(p.n - src_log);
+            per_hi *= n_hi;                                                      // one run: every coset's heap is staged
+            n_hi = 1;
+        }
     } else {
         n_hi = 1ull << (p.n - TMA_W0);
         per_hi = (uint64_t)p.n_cols;
