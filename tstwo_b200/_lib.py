@@ -82,6 +82,8 @@ def load():
         for dbg in ("tstwo_debug_force_naive_fft", "tstwo_debug_set_fft_radix", "tstwo_debug_set_fft_stream"):
             getattr(lib, dbg).restype = C.c_int
             getattr(lib, dbg).argtypes = [C.c_int]
+        lib.tstwo_debug_last_fft_mode.restype = C.c_int
+        lib.tstwo_debug_last_fft_mode.argtypes = []
         _lib = lib
     return _lib
 

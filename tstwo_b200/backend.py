@@ -426,7 +426,8 @@ class CudaBackend:
         for i, ev in enumerate(columns):
             groups.setdefault(ev.domain, []).append(i)
         for dom, idxs in groups.items():
-            dst = [CudaColumn.uninitialized(dom.size()) for _ in idxs]
+            block = CudaColumn.uninitialized(dom.size() * len(idxs))   # one block: evenly spaced columns (bulk-copy passes)
+            dst = [block.slice(k * dom.size(), dom.size()) for k in range(len(idxs))]
             try:
                 check(_L().tstwo_interpolate_columns(dptr_array([columns[i].values.ptr for i in idxs]),
                                                      dptr_array([d.ptr for d in dst]), len(idxs), dom.logSize(),
@@ -446,7 +447,8 @@ class CudaBackend:
         for plog, idxs in groups.items():
             if plog > domain.logSize():
                 raise ValueError("log size too small")
-            dst = [CudaColumn.uninitialized(domain.size()) for _ in idxs]
+            block = CudaColumn.uninitialized(domain.size() * len(idxs))
+            dst = [block.slice(k * domain.size(), domain.size()) for k in range(len(idxs))]
             check(_L().tstwo_evaluate_columns(dptr_array([polys[i].coeffs.ptr for i in idxs]), plog,
                                               dptr_array([d.ptr for d in dst]), len(idxs), domain.logSize(),
                                               domain.halfCoset.initial_index.value, twiddles.handle, _flags()))

@@ -28,9 +28,10 @@ static const size_t PTR_SLOT_CAP = 4096;   // addresses per slot
 
 int make_colset(const tstwo_dptr *cols, int n_cols, int slot, ColSet *out)
 {
-    out->base = nullptr; out->stride = 0; out->table = nullptr;
+    out->base = nullptr; out->stride = 0; out->table = nullptr; out->aligned16 = true;
     if (n_cols <= 0) return 0;
     if (!cols) return fail(TSTWO_ERR_BAD_ARG, "null column list");
+    for (int c = 0; c < n_cols; c++) out->aligned16 = out->aligned16 && (cols[c] & 15) == 0;
     bool uniform = true;
     int64_t stride = n_cols > 1 ? (int64_t)(cols[1] - cols[0]) : 0;
     for (int c = 1; c < n_cols && uniform; c++) uniform = (int64_t)(cols[c] - cols[c - 1]) == stride;

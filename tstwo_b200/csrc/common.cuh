@@ -59,6 +59,7 @@ struct ColSet {
     // col(c) + idx + (idx >> shard_log) * shard_adj  (shard_log = 31 disables it: idx < 2^31).
     int shard_log = 31;
     uint64_t shard_adj = 0;
+    bool aligned16 = true;      // every column starts on a 16-byte boundary (what the bulk copies of fft_tma.cu need)
     __host__ __device__ __forceinline__ uint32_t *col(int c) const
     {
         return table ? reinterpret_cast<uint32_t *>(table[c]) : const_cast<uint32_t *>(base) + (uint64_t)c * stride;

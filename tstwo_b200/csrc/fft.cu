@@ -420,23 +420,26 @@ template <int DIG> static int launch_pass_t(bool inverse, const PassParams &p)
 // 2: persistent passes fed by bulk copies (fft_tma.cu, default where the column sets allow it); 1: persistent passes
 // with per-thread cp.async (fft_stream.cu); 0: one CTA per tile (this file)
 static int g_stream = 2;
+static int g_last_mode = -1;   // what the last tiled transform actually ran (tstwo_debug_last_fft_mode)
 static int launch_pass(int mode, bool inverse, const PassParams &p)
 {
     if (mode == 2) return tma_pass(inverse, p);
     if (mode == 1) return stream_pass(inverse, p);
     return g_dig == 4 ? launch_pass_t<4>(inverse, p) : launch_pass_t<3>(inverse, p);
 }
-// the bulk-copy passes need uniformly spaced, 16-byte aligned columns and row shards of whole 2^14-index tiles
-static int pick_mode(const ColSet &a, const ColSet &b, const ColSet &c, int n_cols)
+// the bulk-copy passes are used when every pass of the transform can address its column sets (fft_tma.cu)
+static int pick_mode(bool inverse, const ColSet &src, const ColSet &dst, const ColSet &work, int n_cols, int L)
 {
     if (g_stream != 2) return g_stream;
-    PassParams p;
-    p.n_cols = n_cols;
-    p.src = a; p.dst = b;
-    if (!tma_pass_supported(p)) return 1;
-    p.src = c;
-    if (!tma_pass_supported(p)) return 1;
-    if (a.shard_log < TMA_W0 || b.shard_log < TMA_W0 || c.shard_log < TMA_W0) return 1;
+    Pass ps[MAX_PASSES];
+    const int np = plan_passes(L, ps, TMA_W0, TMA_W1);
+    for (int k = 0; k < np; k++) {
+        PassParams p;
+        p.n_cols = n_cols; p.lo = ps[k].lo;
+        if (inverse) { p.src = (k == 0) ? src : dst; p.dst = dst; }
+        else { p.src = (k == np - 1) ? src : work; p.dst = (k == 0) ? dst : work; }
+        if (!tma_pass_supported(p)) return 1;
+    }
     return 2;
 }
 
@@ -452,7 +455,7 @@ int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int n, con
     if (n >= FAST_MIN_LOG && !g_force_naive) {
         int rc = ensure_smem_attr();
         if (rc) return rc;
-        const int mode = pick_mode(src, dst, dst, n_cols);
+        const int mode = g_last_mode = pick_mode(true, src, dst, dst, n_cols, n);
         Pass ps[MAX_PASSES];
         int np = mode == 2 ? plan_passes(n, ps, TMA_W0, TMA_W1) : plan_passes(n, ps, W0, W1);
         for (int k = 0; k < np; k++) {
@@ -494,7 +497,7 @@ int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n,
     if (L >= FAST_MIN_LOG && !g_force_naive) {
         int rc = ensure_smem_attr();
         if (rc) return rc;
-        const int mode = pick_mode(src, dst, work, n_cols);
+        const int mode = g_last_mode = pick_mode(false, src, dst, work, n_cols, L);
         Pass ps[MAX_PASSES];
         int np = mode == 2 ? plan_passes(L, ps, TMA_W0, TMA_W1) : plan_passes(L, ps, W0, W1);
         for (int k = np - 1; k >= 0; k--) {
@@ -535,6 +538,8 @@ int tstwo_debug_force_naive_fft(int on) { g_force_naive = on != 0; return 0; }
 // tuning hook: rows per thread of the tiled passes (8 -> 512-thread CTAs, 16 -> 256-thread CTAs)
 int tstwo_debug_set_fft_radix(int rows_per_thread) { g_dig = rows_per_thread == 8 ? 3 : 4; return 0; }
 // tuning / test hook: 2 = bulk-copy persistent passes (default), 1 = cp.async persistent passes, 0 = one CTA per tile
+// test hook: pass family used by the last tiled transform (2 bulk-copy, 1 cp.async persistent, 0 one CTA per tile)
+int tstwo_debug_last_fft_mode(void) { return g_last_mode; }
 int tstwo_debug_set_fft_stream(int mode) { g_stream = mode < 0 ? 0 : mode > 2 ? 2 : mode; return 0; }
 
 static int check_tree(tstwo_twiddles h, uint32_t half_init, int half_log, TwiddleTree **out)

@@ -31,15 +31,27 @@
 namespace tstwo {
 namespace {
 
-constexpr int THREADS = 512, NBUF = 3;
+constexpr int THREADS = 512;
 constexpr int CHUNK_BYTES = 4096 + 16;                 // contiguous pass: 256 units + one pad unit
-constexpr int BUF_BYTES = 16 * CHUNK_BYTES;            // 65792 = 514 * 128 (keeps every buffer 128-byte aligned)
+// Per pass type: groups per CTA, tile buffers, bytes per buffer.
+//   contiguous: 2 groups x 256 threads, 64 KiB tiles (padded chunks), 3 buffers -- integer-bound, the deep layer count wins
+//   strided   : 4 groups x 128 threads, 32 KiB tiles, 6 buffers -- the copies dominate: more, smaller tiles in flight and
+//               four independent instruction streams keep both the pipes and HBM busier
+template <bool STRIDED> struct Cfg {
+    static constexpr int G = STRIDED ? 4 : 2, GS = THREADS / G, NBUF = STRIDED ? 6 : 3;
+    static constexpr int TILE_BYTES = GS * 16 * 16;
+    static constexpr int BUF_BYTES = STRIDED ? TILE_BYTES : 16 * CHUNK_BYTES;   // 65792 = 514 * 128: buffers stay 128-byte aligned
+};
 // twiddles of a run of tiles (same high index bits): unit-level heap, level l (0 = lowest) at HEAP_BASE(l); levels
 // 0..5 and the T_1 slice carry 4 pad words per 256 units so that lanes 256 units apart hit distinct bank groups
 constexpr int HEAP_WORDS = 4096 + 6 * 64;
 constexpr int T1_WORDS = 4096 + 64;
-constexpr int SMEM_BYTES = NBUF * BUF_BYTES + (HEAP_WORDS + T1_WORDS) * 4 + 64;
-static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KiB of shared memory a CTA can opt into");
+constexpr int STRIDED_HEAP_WORDS = 8 * 256;            // up to 8 coset heaps of 255 words
+template <bool STRIDED> constexpr int smem_bytes()
+{
+    return Cfg<STRIDED>::NBUF * Cfg<STRIDED>::BUF_BYTES + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS) * 4 + 64;
+}
+static_assert(smem_bytes<false>() <= 232448 && smem_bytes<true>() <= 232448, "exceeds the 227 KiB of shared memory a CTA can opt into");
 
 struct alignas(64) TmaParams {
     CUtensorMap src_map, dst_map;   // strided pass only
@@ -99,7 +111,7 @@ __device__ __forceinline__ void tensor_s2g(const CUtensorMap *map, uint32_t c0, 
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, 256;" ::"r"(g + 1) : "memory"); }
+template <int GS> __device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "n"(GS) : "memory"); }
 
 #ifdef TSTWO_FFT_TRACE
 // debug timeline: per (CTA 0, group, tile, point) the SM clock; see scripts/fft_trace.py
@@ -118,18 +130,19 @@ __device__ int g_trace_cta = 0;
 #define TRACE_CTA(which) do { } while (0)
 #endif
 
-// ---- stage geometry.  U = 12-bit unit index inside the tile: contiguous U = index >> 2; strided U = row << 4 |
-// (index >> 2 & 15).  A thread owns the 16 units U0 | d << SU.  In every map the lanes of a quarter warp differ in
+// ---- stage geometry.  U = unit index inside the tile: contiguous (12 bits) U = index >> 2; strided (11 bits) U =
+// row << 3 | (index >> 2 & 7).  A thread owns the 16 units U0 | d << SU.  In every map the lanes of a quarter warp differ in
 // bits that move the physical unit (U + PAD * (U >> 8)) across the 8 bank groups: U[0..2], or U[8..10] where the
 // thread owns U[0..3] itself (lowest contiguous stage; that is what the chunk pad is for).
 //   contiguous: ST0 = lanes + U[0..3] (layers 0..5), ST1 = U[4..7] (6..9), ST2 = U[8..11] (10..13)
-//   strided   : ST0 = U[4..7] (window layers 0..3), ST1 = U[8..11] (4..7)
+//   strided   : ST0 = U[3..6] (window layers 0..3), ST1 = U[7..10] (4..7)
 template <bool STRIDED, int ST> struct Stg {
-    static constexpr int SU = STRIDED ? 4 + 4 * ST : 4 * ST;
+    static constexpr int SU = STRIDED ? 3 + 4 * ST : 4 * ST;
     static constexpr int SL = STRIDED ? 4 * ST : 4 * ST;     // heap level of digit bit 0
     static constexpr int PAD = STRIDED ? 0 : 1;
     __device__ static __forceinline__ int u0(int tg)
     {
+        if (STRIDED) return SU == 3 ? ((tg & 7) | ((tg >> 3) << 7)) : tg;
         if (SU == 0) return ((tg & 7) << 8) | (((tg >> 3) & 15) << 4) | ((tg >> 7) << 11);
         if (SU == 4) return (tg & 15) | ((tg >> 4) << 8);
         return tg;
@@ -172,7 +185,7 @@ template <bool STRIDED> __device__ __forceinline__ constexpr int heap_base(int l
 template <bool STRIDED, bool INV, bool FULL>
 __device__ __forceinline__ void unit_layers(uint32_t (&v)[16][4], const uint32_t *heap, int U0, int sl, int j_min)
 {
-    const int ub = STRIDED ? (U0 >> 4) : U0;           // unit-level coordinate the heap is indexed by (row / unit)
+    const int ub = STRIDED ? (U0 >> 3) : U0;           // unit-level coordinate the heap is indexed by (row / unit)
     const int padw = 4 * (U0 >> 8);
 #pragma unroll
     for (int kk = 0; kk < 4; kk++) {
@@ -252,10 +265,10 @@ template <bool STRIDED> __device__ __forceinline__ Tile decode(const TmaParams &
 {
     if (STRIDED && sp.cosets_log) {
         const uint32_t r = t >> sp.cosets_log;
-        return { t & ((1u << sp.cosets_log) - 1), r >> (sp.p.lo - 6), r & ((1u << (sp.p.lo - 6)) - 1) };
+        return { t & ((1u << sp.cosets_log) - 1), r >> (sp.p.lo - 5), r & ((1u << (sp.p.lo - 5)) - 1) };
     }
     const uint32_t rem = t - hi * sp.tiles_per_hi;
-    if (STRIDED) return { hi, rem >> (sp.p.lo - 6), rem & ((1u << (sp.p.lo - 6)) - 1) };
+    if (STRIDED) return { hi, rem >> (sp.p.lo - 5), rem & ((1u << (sp.p.lo - 5)) - 1) };
     return { hi, rem, 0 };
 }
 
@@ -266,8 +279,8 @@ __device__ __forceinline__ void tile_fetch(const TmaParams &sp, const Tile tl, u
     const PassParams &p = sp.p;
     if (STRIDED) {
         if (tg == 0) {
-            mbar_arrive_expect_tx(bar, 65536);
-            tensor_g2s(buf, &sp.src_map, tl.mid << 6, ((tl.hi << (p.lo + 8)) & p.src_mask) >> p.lo, tl.col, bar);
+            mbar_arrive_expect_tx(bar, Cfg<true>::TILE_BYTES);
+            tensor_g2s(buf, &sp.src_map, tl.mid << 5, ((tl.hi << (p.lo + 8)) & p.src_mask) >> p.lo, tl.col, bar);
         }
     } else if (tg < 16) {
         if (tg == 0) mbar_arrive_expect_tx(bar, 65536);
@@ -282,7 +295,7 @@ __device__ __forceinline__ void tile_drain(const TmaParams &sp, const Tile tl, u
 {
     const PassParams &p = sp.p;
     if (STRIDED) {
-        if (tg == 0) { tensor_s2g(&sp.dst_map, tl.mid << 6, tl.hi << 8, tl.col, buf); bulk_commit(); }
+        if (tg == 0) { tensor_s2g(&sp.dst_map, tl.mid << 5, tl.hi << 8, tl.col, buf); bulk_commit(); }
     } else if (tg < 16) {
         uint32_t *dst = p.dst.col(tl.col) + p.dst.off(tl.hi << 14) + 1024 * tg;
         bulk_s2g(dst, buf + tg * CHUNK_BYTES, 4096);
@@ -342,7 +355,7 @@ __device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap,
         else if (st == TOP) tile_store<STRIDED, TOP>(buf, tg, v);
         else tile_store<STRIDED, 1>(buf, tg, v);
         if (s == 0) at_first_boundary();
-        if (s < TOP) group_sync(g);
+        if (s < TOP) group_sync<Cfg<STRIDED>::GS>(g);
     }
 }
 
@@ -350,11 +363,13 @@ template <bool INV, bool STRIDED, bool FULL>
 __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_constant__ TmaParams sp)
 {
     extern __shared__ __align__(1024) uint8_t smem[];
+    using C = Cfg<STRIDED>;
+    constexpr int NBUF = C::NBUF, BUF_BYTES = C::BUF_BYTES, G = C::G;
     uint32_t *heap = reinterpret_cast<uint32_t *>(smem + NBUF * BUF_BYTES);
-    const uint32_t bar0 = smem_u32(heap + HEAP_WORDS + T1_WORDS);
+    const uint32_t bar0 = smem_u32(heap + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS));
     const uint32_t buf0 = smem_u32(smem);
     const PassParams &p = sp.p;
-    const int tid = threadIdx.x, g = tid >> 8, tg = tid & 255;
+    const int tid = threadIdx.x, g = tid / C::GS, tg = tid % C::GS;
 
     // this CTA's tile list: t(k) = start + k * step.  Strided passes interleave CTAs (neighbouring tiles, i.e.
     // neighbouring 256-byte pieces of the same rows, are in flight together); the contiguous pass walks consecutive
@@ -372,7 +387,7 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
         for (int b = 0; b < NBUF; b++) mbar_init(bar0 + 8 * b, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    uint32_t fills0 = 0, fills1 = 0, fills2 = 0;       // completed phases of the three barriers
+    uint32_t par = 0;                                  // bit b: parity of the completed phases of buffer b's barrier
 #ifdef TSTWO_FFT_TRACE
     int tr_n = 0, tr_all = 0;
 #endif
@@ -391,17 +406,16 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
         __syncthreads();
 #pragma unroll
         for (int i = 0; i < NBUF; i++)
-            if ((uint32_t)i < len && (i & 1) == g)
+            if ((uint32_t)i < len && (i % G) == g)
                 tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar0 + 8 * i, tg);        uint32_t refill = 0xffffffffu;                 // DEFER: tile of mine whose buffer is still to be refilled
 
-        for (uint32_t i = g; i < len; i += 2) {
-            const uint32_t b = i % 3, round = i / 3;
-            const uint32_t fills = b == 0 ? fills0 : b == 1 ? fills1 : fills2;
+        for (uint32_t i = g; i < len; i += G) {
+            const uint32_t b = i % NBUF, round = i / NBUF;
             uint4 *buf = reinterpret_cast<uint4 *>(smem + b * BUF_BYTES);
             const Tile tl = decode<STRIDED>(sp, t0 + i * step, hi);
             TRACE(0, i);
             TRACE_TILE();
-            mbar_wait(bar0 + 8 * b, (fills + round) & 1);
+            mbar_wait(bar0 + 8 * b, ((par >> b) ^ round) & 1);
             TRACE(1, i);
             // The lanes that issue the stores wait until those have been read out of shared memory and refill the buffer
             // at once (the other seven warps are already on the next tile).  DEFER = refill at the first stage boundary
@@ -411,20 +425,20 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
             transform_tile<STRIDED, INV, FULL>(buf, tile_heap, tg, g, p.j_min, p.scale2, [&]() {
                 if (DEFER && refill != 0xffffffffu) {
                     if (tg < 16) bulk_wait_read();
-                    const uint32_t rb = refill % 3;
-                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (refill + 3) * step, hi), buf0 + rb * BUF_BYTES, bar0 + 8 * rb, tg);
+                    const uint32_t rb = refill % NBUF;
+                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (refill + NBUF) * step, hi), buf0 + rb * BUF_BYTES, bar0 + 8 * rb, tg);
                     refill = 0xffffffffu;
                 }
             });
             TRACE(2, i);
             fence_proxy_async();                       // generic-proxy stores above -> async-proxy reads below
-            group_sync(g);
+            group_sync<C::GS>(g);
             tile_drain<STRIDED>(sp, tl, buf0 + b * BUF_BYTES, tg);
-            if (i + 3 < len) {
+            if (i + NBUF < len) {
                 if (DEFER) refill = i;
                 else {
                     if (tg < 16) bulk_wait_read();
-                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (i + 3) * step, hi), buf0 + b * BUF_BYTES, bar0 + 8 * b, tg);
+                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (i + NBUF) * step, hi), buf0 + b * BUF_BYTES, bar0 + 8 * b, tg);
                 }
             }
             TRACE(3, i);
@@ -433,7 +447,8 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
 #endif
         }
         if (tg < 16) bulk_wait_read();                 // the buffers are reused by the next run and must outlive the copies
-        fills0 += (len + 2) / 3; fills1 += (len + 1) / 3; fills2 += len / 3;
+#pragma unroll
+        for (int b = 0; b < NBUF; b++) par ^= (((len + NBUF - 1 - b) / NBUF) & 1) << b;
         k += len;
     }
     TRACE_CTA(1);
@@ -441,7 +456,7 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
 
 template <bool INV, bool STRIDED, bool FULL> cudaError_t set_attr()
 {
-    return cudaFuncSetAttribute(fft_tma_kernel<INV, STRIDED, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    return cudaFuncSetAttribute(fft_tma_kernel<INV, STRIDED, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<STRIDED>());
 }
 bool g_ready = false;
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
@@ -449,12 +464,12 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
 
-// 3-D view of a column set for the strided pass: (index & (2^lo - 1), index >> lo, column), box 64 x 256 x 1
+// 3-D view of a column set for the strided pass: (index & (2^lo - 1), index >> lo, column), box 32 x 256 x 1
 int make_map(CUtensorMap *map, const ColSet &cs, int n_cols, int log_len, int lo)
 {
     const cuuint64_t dims[3] = { 1ull << lo, 1ull << (log_len - lo), (cuuint64_t)n_cols };
     const cuuint64_t strides[2] = { 4ull << lo, n_cols > 1 ? cs.stride * 4 : (4ull << log_len) };
-    const cuuint32_t box[3] = { 64, 256, 1 }, estr[3] = { 1, 1, 1 };
+    const cuuint32_t box[3] = { 32, 256, 1 }, estr[3] = { 1, 1, 1 };
     CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<uint32_t *>(cs.base), dims, strides, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -492,11 +507,13 @@ int tma_pass_init()
     return 0;
 }
 
-// Column sets the bulk copies can address: uniformly spaced columns (one tensor map covers them).  Scattered column
-// tables fall back to the per-thread-copy kernels of fft_stream.cu / fft.cu.
+// What a pass needs of its column sets: 16-byte aligned columns; the strided pass, whose tensor maps describe a whole
+// column set, also uniformly spaced columns (the contiguous pass copies column by column and takes any table).
 bool tma_pass_supported(const PassParams &p)
 {
-    if (p.src.table || p.dst.table) return false;
+    if (!p.src.aligned16 || !p.dst.aligned16) return false;
+    if (p.lo == 0) return p.src.shard_log >= TMA_W0 && p.dst.shard_log >= TMA_W0;
+    if (p.src.table || p.dst.table || p.src.shard_log != 31 || p.dst.shard_log != 31) return false;
     if ((reinterpret_cast<uintptr_t>(p.src.base) | reinterpret_cast<uintptr_t>(p.dst.base)) & 15) return false;
     if (p.n_cols > 1 && ((p.src.stride | p.dst.stride) & 3)) return false;
     return true;
@@ -513,13 +530,13 @@ int tma_pass(bool inverse, const PassParams &p)
     uint64_t n_hi, per_hi;
     if (strided) {
         if (p.src.shard_log != 31 || p.dst.shard_log != 31) return fail(TSTWO_ERR_BAD_ARG, "strided FFT pass on a row-sharded column set");
-        if (p.lo < 6 || p.lo + TMA_W1 > p.n) return fail(TSTWO_ERR_BAD_ARG, "bad strided window lo=%d n=%d", p.lo, p.n);
+        if (p.lo < 5 || p.lo + TMA_W1 > p.n) return fail(TSTWO_ERR_BAD_ARG, "bad strided window lo=%d n=%d", p.lo, p.n);
         int src_log = 0;
         while ((1ull << src_log) <= p.src_mask) src_log++;          // src holds 2^src_log words per column
         if ((rc = make_map(&sp.src_map, p.src, p.n_cols, src_log, p.lo))) return rc;
         if ((rc = make_map(&sp.dst_map, p.dst, p.n_cols, p.n, p.lo))) return rc;
         n_hi = 1ull << (p.n - p.lo - TMA_W1);
-        per_hi = ((uint64_t)p.n_cols) << (p.lo - 6);
+        per_hi = ((uint64_t)p.n_cols) << (p.lo - 5);
         if (src_log < p.n && p.lo + TMA_W1 == src_log && p.n - src_log <= 3) {   // top window of a blown-up evaluation
             sp.cosets_log = (uint32_t)(p.n - src_log);
             per_hi *= n_hi;                                                      // one run: every coset's heap is staged
@@ -535,14 +552,14 @@ int tma_pass(bool inverse, const PassParams &p)
     unsigned grid = (unsigned)ctx().sm_count;
     if (grid > sp.n_tiles) grid = sp.n_tiles;
     if (!strided) {
-        if (inverse) TS_LAUNCH((fft_tma_kernel<true, false, true>), grid, THREADS, SMEM_BYTES, sp);
-        else TS_LAUNCH((fft_tma_kernel<false, false, true>), grid, THREADS, SMEM_BYTES, sp);
+        if (inverse) TS_LAUNCH((fft_tma_kernel<true, false, true>), grid, THREADS, smem_bytes<false>(), sp);
+        else TS_LAUNCH((fft_tma_kernel<false, false, true>), grid, THREADS, smem_bytes<false>(), sp);
     } else if (p.j_min == 0) {
-        if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, true>), grid, THREADS, SMEM_BYTES, sp);
-        else TS_LAUNCH((fft_tma_kernel<false, true, true>), grid, THREADS, SMEM_BYTES, sp);
+        if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, true>), grid, THREADS, smem_bytes<true>(), sp);
+        else TS_LAUNCH((fft_tma_kernel<false, true, true>), grid, THREADS, smem_bytes<true>(), sp);
     } else {
-        if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, false>), grid, THREADS, SMEM_BYTES, sp);
-        else TS_LAUNCH((fft_tma_kernel<false, true, false>), grid, THREADS, SMEM_BYTES, sp);
+        if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, false>), grid, THREADS, smem_bytes<true>(), sp);
+        else TS_LAUNCH((fft_tma_kernel<false, true, false>), grid, THREADS, smem_bytes<true>(), sp);
     }
     return 0;
 }
