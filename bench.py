@@ -24,6 +24,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_COLS, LOG_SIZE, LOG_BLOWUP = 256, 22, 1
+# DRAM bytes (read + written) per launch of the kernels below at the headline size, from ncu (profiles/r01_launches_tma.txt)
+NCU_TRAFFIC = {"merkle_leaf_layer": 8.59e9 + 0.21e9, "evaluate (2 fft launches)": (4.51e9 + 8.53e9 + 8.61e9 + 8.53e9) / 2,
+               "interpolate (2 fft launches)": (4.31e9 + 4.25e9 + 4.31e9 + 4.23e9) / 2}
 METRIC = "lde_blake2s_commit_throughput"
 UNIT = "M31 trace elements/s"
 P = 2147483647
@@ -239,7 +242,7 @@ def run_cuda(args):
     root_hex = bytes(root).hex() if world == 1 else (holder.get("root", b"").hex() if rank == 0 else "")
 
     # ---- per-kernel timing (1 GPU): the roofline of the dominant kernel, measured live with CUDA events
-    roof, kernels = None, None
+    roof, kernels, int_roof = None, None, None
     if world == 1:
         kernels = kernel_breakdown(L, chk, torch, stream, trace, coeffs, evals, layers, tw, n_cols, log, blow)
         peaks = {}
@@ -248,11 +251,27 @@ def run_cuda(args):
         except Exception:
             pass
         peak, which = (peaks.get("hbm_gbs"), "measured (MEASURED_PEAKS.json hbm_gbs)") if peaks.get("hbm_gbs") else (6650.0, "fallback")
-        top_k = max(kernels, key=lambda k: kernels[k]["ms"])
+        # dominant kernel = the longest single launch (a transform is 2 launches, the leaf layer is 1)
+        top_k = max(kernels, key=lambda k: kernels[k]["ms"] / kernels[k]["launches"])
         kk = kernels[top_k]
-        roof = {"bound": "hbm", "kernel": top_k, "achieved": kk["gbs"], "peak": peak, "unit": "GB/s", "frac": kk["gbs"] / peak,
-                "traffic": None, "peak_source": which, "algorithmic_bytes_per_launch": kk["bytes"], "ms_per_launch": kk["ms"],
-                "note": "integer-issue bound, not HBM bound: see int_roofline and DESIGN.md"}
+        ms_launch, by_launch = kk["ms"] / kk["launches"], kk["bytes"] / kk["launches"]
+        roof = {"bound": "hbm", "kernel": top_k, "achieved": by_launch / ms_launch / 1e6, "peak": peak, "unit": "GB/s",
+                "frac": by_launch / ms_launch / 1e6 / peak, "traffic": NCU_TRAFFIC.get(top_k) if (n_cols, log, blow) == (N_COLS, LOG_SIZE, LOG_BLOWUP) else None, "peak_source": which,
+                "algorithmic_bytes_per_launch": by_launch, "ms_per_launch": ms_launch,
+                "note": "this kernel is integer-pipe bound, not HBM bound (see int_roofline); traffic = dram bytes read+written "
+                        "per launch from profiles/r01_launches_tma.txt"}
+        # integer-pipe rooflines measured on this pool with tools/microbench*.cu (profiles/r01_microbench_*.txt):
+        # 3.667e12 M31 butterflies/s (ALU-pipe bound, 10.15 clk per warp-butterfly per SM sub-partition) and
+        # 23.9e9 Blake2s compressions/s (1555 clk per warp-compression per sub-partition) at 1965 MHz
+        n_bf = n_cols * (log * (n // 2) + log * (ne // 2))          # the top log_blowup layers of evaluate are copies
+        n_cmp = ne * ((4 * n_cols + 63) // 64) + ne - 1
+        t_fft = kernels["interpolate (2 fft launches)"]["ms"] + kernels["evaluate (2 fft launches)"]["ms"]
+        t_mk = kernels["merkle_leaf_layer"]["ms"] + 2 * kernels["merkle_node_layer_top"]["ms"]   # node layers halve: sum ~ 2x the top one
+        int_roof = {"fft": {"butterflies": n_bf, "ms": t_fft, "achieved": n_bf / t_fft / 1e6, "peak": 3667.0, "unit": "G butterflies/s",
+                            "frac": n_bf / t_fft / 1e6 / 3667.0},
+                    "blake2s": {"compressions": n_cmp, "ms": t_mk, "achieved": n_cmp / t_mk / 1e6, "peak": 23.9, "unit": "G compressions/s",
+                                "frac": n_cmp / t_mk / 1e6 / 23.9},
+                    "peak_source": "tools/microbench.cu, tools/microbench_bf.cu on B200 (profiles/r01_microbench_int_pipes.txt, r01_microbench_stage.txt)"}
 
     # ---- end to end through the C ABI with HOST buffers (1 GPU)
     e2e = None
@@ -290,6 +309,7 @@ def run_cuda(args):
             "gpu_launches": launches, "clocks": clocks, "root": root_hex,
         }
         if roof: out["roofline"] = roof
+        if int_roof: out["int_roofline"] = int_roof
         if kernels: out["kernels"] = kernels
         if e2e: out["e2e"] = e2e
         if cpu: out["cpu_baseline"] = cpu
@@ -326,7 +346,7 @@ def kernel_breakdown(L, chk, torch, stream, trace, coeffs, evals, layers, tw, n_
     b_int, b_ev = 8 * n_cols * n, (4 + 4 * (1 << blow)) * n_cols * n
     b_leaf, b_node = (4 * n_cols + 32) * ne, 96 * (ne // 2)
     mk = lambda ms, by, launches: {"ms": ms, "bytes": by, "gbs": by / ms / 1e6, "launches": launches}
-    return {"interpolate (2 fft_pass launches)": mk(t_int, b_int, 2), "evaluate (2 fft_pass launches)": mk(t_ev, b_ev, 2),
+    return {"interpolate (2 fft launches)": mk(t_int, b_int, 2), "evaluate (2 fft launches)": mk(t_ev, b_ev, 2),
             "merkle_leaf_layer": mk(t_leaf, b_leaf, 1), "merkle_node_layer_top": mk(t_node, b_node, 1)}
 
 

@@ -36,10 +36,13 @@ def test_lde_commit_vs_oracle(tb, orc, log, blow, n_cols, keep):
         assert (tree.commitment.layer_bytes(k) == layers[k]).all()
 
 
-def test_lde_commit_host_matches_device(tb, orc):
+@pytest.mark.parametrize("n_cols", [40, 16, 7, 33, 64])
+def test_lde_commit_host_matches_device(tb, orc, n_cols):
+    """Host-fed pipeline: the leaf hashes absorb 16 columns per PCIe chunk (ragged last chunk, fewer than one chunk,
+    whole chunks) and must give the root of the device-resident path."""
     from tstwo_b200 import _lib
     L = _lib.init(0)
-    log, blow, n_cols = 14, 1, 40
+    log, blow = 14, 1
     rng = np.random.default_rng(5)
     trace = rng.integers(0, P, (n_cols, 1 << log), dtype=np.uint32)
     tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(log + blow).half_coset())

@@ -104,6 +104,39 @@ __global__ void __launch_bounds__(256) merkle_layer_kernel(const uint4 *__restri
     out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
 }
 
+// Leaf layer in column chunks (host-fed pipeline: columns arrive over PCIe 16 at a time).  The BLAKE2s chaining value of
+// every row lives in the leaf layer itself; a launch absorbs columns [c0, c0 + nc) of a leaf of `total_cols` words
+// (c0 a multiple of 16; nc a multiple of 16 unless the chunk is the last) and the chunk holding the last word finalises.
+// Same digests as merkle_layer_kernel<false>: the block boundaries and counters are those of the one-shot hash.
+__global__ void __launch_bounds__(256) merkle_leaf_absorb_kernel(ColSet cols, int c0, int nc, int total_cols, uint64_t n_rows,
+                                                                 uint4 *__restrict__ state, uint32_t one)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rows) return;
+    uint32_t h[8], m[16];
+    if (c0 == 0) b2s_init(h);
+    else {
+        const uint4 a = state[2 * i], b = state[2 * i + 1];
+        h[0] = a.x; h[1] = a.y; h[2] = a.z; h[3] = a.w; h[4] = b.x; h[5] = b.y; h[6] = b.z; h[7] = b.w;
+    }
+    for (int b0 = 0; b0 < nc; b0 += 16) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) m[k] = (b0 + k < nc) ? __ldcs(cols.col(b0 + k) + i) : 0u;
+        const bool last = c0 + b0 + 16 >= total_cols;
+        b2s_compress(h, m, last ? (uint32_t)total_cols * 4u : (uint32_t)(c0 + b0 + 16) * 4u, last, one);
+    }
+    state[2 * i] = make_uint4(h[0], h[1], h[2], h[3]);
+    state[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
+}
+
+int merkle_leaf_absorb(int log_size, const ColSet &cols, int c0, int nc, int total_cols, uint8_t *leaf_layer)
+{
+    const uint64_t n = 1ull << log_size;
+    if (c0 % 16 || nc <= 0 || (nc % 16 && c0 + nc != total_cols)) return fail(TSTWO_ERR_BAD_ARG, "leaf chunk [%d, %d) of %d is not block aligned", c0, c0 + nc, total_cols);
+    TS_LAUNCH(merkle_leaf_absorb_kernel, (unsigned)((n + 255) / 256), 256, 0, cols, c0, nc, total_cols, n, (uint4 *)leaf_layer, 1u);
+    return 0;
+}
+
 int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, int n_cols, uint8_t *out)
 {
     const uint64_t n = 1ull << log_size;

@@ -133,7 +133,7 @@ int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, 
     Context &c = ctx();
     const int ext = log_size + log_blowup;
     const uint64_t n = 1ull << log_size, ne = 1ull << ext;
-    const int chunk = 16;   // columns per H2D chunk (multiple of the 8-column FFT tile)
+    const int chunk = 16;   // columns per H2D chunk = one 64-byte BLAKE2s block of every leaf
     const int n_chunks = (n_cols + chunk - 1) / chunk;
     std::vector<cudaEvent_t> ev((size_t)n_chunks);
     uint32_t *stage = (uint32_t *)trace_staging;
@@ -151,13 +151,20 @@ int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, 
         rc = lde_commit_device(stage + (uint64_t)c0 * n, nc, log_size, log_blowup, t, cf, (uint32_t *)evals + (uint64_t)c0 * ne,
                                nullptr, nullptr, flags, false);
         if (rc) return rc;
+        if (layers) {
+            // the leaf hashes absorb this chunk's 16 columns now (one BLAKE2s block per row), so that only the last
+            // chunk's block and the node layers are left once the last column has crossed PCIe
+            ColSet evs = { (const uint32_t *)evals + (uint64_t)c0 * ne, ne, nullptr };
+            rc = merkle_leaf_absorb(ext, evs, c0, nc, n_cols, (uint8_t *)layers + 32ull * ((1ull << ext) - 1));
+            if (rc) return rc;
+        }
     }
     if (layers) {
-        const uint8_t *prev = nullptr;
-        ColSet evs = { (const uint32_t *)evals, ne, nullptr }, none = { nullptr, 0, nullptr };
-        for (int log = ext; log >= 0; log--) {
+        const uint8_t *prev = (const uint8_t *)layers + 32ull * ((1ull << ext) - 1);
+        ColSet none = { nullptr, 0, nullptr };
+        for (int log = ext - 1; log >= 0; log--) {
             uint8_t *dst = (uint8_t *)layers + 32ull * ((1ull << log) - 1);
-            rc = merkle_commit_layer(log, prev, log == ext ? evs : none, log == ext ? n_cols : 0, dst);
+            rc = merkle_commit_layer(log, prev, none, 0, dst);
             if (rc) return rc;
             prev = dst;
         }
