@@ -41,6 +41,8 @@ def parse():
     ap.add_argument("--log-size", type=int, default=LOG_SIZE)
     ap.add_argument("--cols", type=int, default=N_COLS)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: 'peer' = last FFT pass stores into the peers' leaf buffers over NVLink; 'nccl' = all-to-all")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample-cols", type=int, default=8)
     ap.add_argument("--fft-radix", type=int, default=0, help="tuning: rows per thread of the FFT passes (8 or 16)")
@@ -142,6 +144,9 @@ def cpu_baseline(args):
 
 
 def run_cuda(args):
+    # NCCL prints its version banner on stdout when NCCL_DEBUG=VERSION: the driver wants exactly one JSON line there
+    # (NCCL_DEBUG >= VERSION, which this image sets); keep the level, send NCCL's log to stderr instead
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -197,8 +202,11 @@ def run_cuda(args):
                                    layers.data_ptr(), root, 0))
         launches_per_step = None
     else:
-        from tstwo_b200.distributed import CudaShardOps, ShardedCommit
-        sc = ShardedCommit(CudaShardOps(local, stream), n_cols, log, blow)
+        from tstwo_b200.distributed import CudaShardOps, PeerShardedCommit, ShardedCommit
+        if args.exchange == "peer":
+            sc = PeerShardedCommit(local, stream, n_cols, log, blow)
+        else:
+            sc = ShardedCommit(CudaShardOps(local, stream), n_cols, log, blow)
         trace_flat = trace.view(-1)
         holder = {}
 
@@ -305,7 +313,8 @@ def run_cuda(args):
             "config": {"workload": f"{n_cols} cols x 2^{log} M31, blowup 2 (2^{ext} rows), Blake2s Merkle commit",
                        "n_cols": n_cols, "log_size": log, "log_blowup": blow,
                        "l2": "inputs (%.1f GiB) and outputs exceed the 126 MB L2; no flush needed" % (n_cols * n * 4 / 2**30),
-                       "parallelism": "1 GPU" if world == 1 else f"column-sharded LDE -> NCCL all-to-all -> row-sharded Merkle x{world}"},
+                       "parallelism": "1 GPU" if world == 1 else (f"column-sharded LDE, last FFT pass stores rows to their owner over NVLink peer memory -> row-sharded Merkle x{world}"
+                                                                       if args.exchange == "peer" else f"column-sharded LDE -> NCCL all-to-all -> row-sharded Merkle x{world}")},
             "gpu_launches": launches, "clocks": clocks, "root": root_hex,
         }
         if roof: out["roofline"] = roof
@@ -315,6 +324,8 @@ def run_cuda(args):
         if cpu: out["cpu_baseline"] = cpu
         print(json.dumps(out))
     if world > 1:
+        if hasattr(sc, "close"):
+            sc.close()
         dist.destroy_process_group()
 
 

@@ -119,6 +119,17 @@ int tstwo_lde_commit(tstwo_dptr trace, int n_cols, int log_size, int log_blowup,
  * for one all-to-all.  The receiver then calls tstwo_merkle_commit on its [all columns][rows] block. */
 int tstwo_lde_columns_sharded(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
                               tstwo_dptr coeffs, tstwo_dptr evals, int n_shards, uint32_t flags);
+/* Multi-GPU, exchange fused into the last FFT pass: the rows of shard d are stored straight into shard_bases[d], the
+ * [total columns][2^(log_size+log_blowup)/n_shards] leaf buffer of rank d (its own, or a peer's mapped with
+ * tstwo_ipc_import), at column col_offset + c.  work: n_cols * 2^(log_size+log_blowup) words of local scratch.
+ * Replaces tstwo_lde_columns_sharded + all-to-all; the caller synchronises the ranks before the receivers hash. */
+int tstwo_lde_columns_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
+                               tstwo_dptr coeffs, tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards,
+                               int col_offset, uint32_t flags);
+/* CUDA IPC for the above (one process per GPU): 64-byte handle of a tstwo_malloc'ed buffer / mapping of a peer's. */
+int tstwo_ipc_export(tstwo_dptr ptr, uint8_t handle[64]);
+int tstwo_ipc_import(const uint8_t handle[64], tstwo_dptr *out);
+int tstwo_ipc_close(tstwo_dptr ptr);
 /* Same, but the trace lives in HOST memory (pinned or pageable): host->device copies are pipelined with the
  * kernels inside the call; only the root comes back. */
 int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,

@@ -124,3 +124,31 @@ def test_lde_columns_sharded_layout(tb, orc, n_shards):
     mp = tb.MerkleProver.commit(tb.CudaBackend.merkleOps, [shard.slice(c * rows, rows) for c in range(n_cols)])
     k = n_shards.bit_length() - 1
     assert mp.root() == ref.commitment.layer_bytes(k)[1].tobytes()
+
+
+@pytest.mark.parametrize("n_shards,col_offset,total", [(2, 0, 3), (4, 2, 6), (1, 1, 4)])
+def test_lde_columns_to_peers_local_bases(tb, orc, n_shards, col_offset, total):
+    """tstwo_lde_columns_to_peers with every shard base pointing at a LOCAL buffer (the multi-GPU run maps peers' buffers
+    there): shard d must receive rows [d * rows, (d+1) * rows) of every evaluation at column col_offset + c, and nothing
+    else may be touched."""
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    log, blow, n_cols = 16, 1, 3
+    ext = log + blow
+    rows = (1 << ext) // n_shards
+    rng = np.random.default_rng(11 * n_shards + col_offset)
+    trace = rng.integers(0, P, (n_cols, 1 << log), dtype=np.uint32)
+    tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(ext).half_coset())
+    ref = tb.CommitmentTreeProver.from_trace(tb.CudaColumn.from_cpu(trace.reshape(-1)), n_cols, log, blow, tw)
+    shards = [tb.CudaColumn.from_cpu(np.full(total * rows, 7, dtype=np.uint32)) for _ in range(n_shards)]
+    work = tb.CudaColumn.uninitialized(n_cols << ext)
+    _lib.check(L.tstwo_lde_columns_to_peers(tb.CudaColumn.from_cpu(trace.reshape(-1)).ptr, n_cols, log, blow, tw.handle, 0, work.ptr,
+                                            _lib.dptr_array([s.ptr for s in shards]), n_shards, col_offset, 0))
+    for d in range(n_shards):
+        got = shards[d].toCpu().reshape(total, rows)
+        for c in range(total):
+            if col_offset <= c < col_offset + n_cols:
+                want = ref.evaluations[c - col_offset].values.toCpu()[d * rows:(d + 1) * rows]
+                assert (got[c] == want).all(), f"shard {d} column {c}"
+            else:
+                assert (got[c] == 7).all(), f"shard {d} column {c} must be untouched"

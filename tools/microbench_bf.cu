@@ -10,8 +10,22 @@
 
 // V: 0 plain (compiler picks IMAD.IADD for both adds), 1 sum as IADD3 (a+m+z), 2 alternate 0/1 by unit parity,
 //    3 both adds IADD3, 4 alternate 0/1 by lane parity, 5: 3 of 4 plain, 1 of 4 z
+// fold of the 62-bit product on the FMA pipe: hi + (lo >> 1) = mad.hi(lo, 2^31, hi)
+__device__ __forceinline__ uint32_t mul2_madhi(uint32_t a, uint32_t t2, uint32_t half)   // half = 2^31, run-time so that ptxas keeps the IMAD.HI
+{
+    uint64_t p = (uint64_t)a * t2;
+    uint32_t lo = (uint32_t)p, hi = (uint32_t)(p >> 32), s;
+    asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(s) : "r"(lo), "r"(half), "r"(hi));
+    return m31::csub(s);
+}
 template <int V> __device__ __forceinline__ void bf(uint32_t &a, uint32_t &b, uint32_t t, uint32_t z, int d, int e)
 {
+    if (V >= 6 && V <= 8) {       // 6: every butterfly folds with mad.hi; 7: lanes 1 of 4; 8: lanes 2 of 4
+        const bool hi = V == 6 || (V == 7 && e == 3) || (V == 8 && (e & 1));
+        uint32_t m = hi ? mul2_madhi(b, t, z) : m31::mul2(b, t), x = a;
+        a = m31::add(x, m); b = m31::sub(x, m);
+        return;
+    }
     bool usez = V == 1 || (V == 2 && (d & 1)) || (V == 4 && (e & 1)) || (V == 5 && (e == 3));
     if (V == 3) {
         uint32_t m = m31::mul2(b, t), x = a;
@@ -54,8 +68,9 @@ template <int V, int THREADS> int run(const char *name, int sms, int bps, uint32
 {
     int iters = 2048, grid = sms * bps;
     cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-    k_stage<V, THREADS><<<grid, THREADS>>>(out, tw, 16, 0); CK(cudaDeviceSynchronize());
-    CK(cudaEventRecord(e0)); k_stage<V, THREADS><<<grid, THREADS>>>(out, tw, iters, 0); CK(cudaEventRecord(e1)); CK(cudaDeviceSynchronize());
+    const uint32_t z = (V >= 6 && V <= 8) ? 0x80000000u : 0u;
+    k_stage<V, THREADS><<<grid, THREADS>>>(out, tw, 16, z); CK(cudaDeviceSynchronize());
+    CK(cudaEventRecord(e0)); k_stage<V, THREADS><<<grid, THREADS>>>(out, tw, iters, z); CK(cudaEventRecord(e1)); CK(cudaDeviceSynchronize());
     float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
     double bfs = (double)grid * THREADS * 128.0 * iters;       // butterflies
     double per_smsp_clk = bfs / 32 / (sms * 4) / (ms * 1e-3 * 1.965e9);
@@ -77,6 +92,9 @@ int main()
     run<4, 256>("alternate by lane", sms, 2, out, tw);
     run<5, 256>("1 of 4 lanes IADD3", sms, 2, out, tw);
     run<3, 256>("both IADD3", sms, 2, out, tw);
+    run<6, 256>("fold by mad.hi (all)", sms, 2, out, tw);
+    run<7, 256>("fold by mad.hi (1 of 4 lanes)", sms, 2, out, tw);
+    run<8, 256>("fold by mad.hi (2 of 4 lanes)", sms, 2, out, tw);
     run<2, 256>("alternate by unit, 2 warps/SMSP", sms, 1, out, tw);
     run<4, 256>("alternate by lane, 2 warps/SMSP", sms, 1, out, tw);
     return 0;

@@ -60,6 +60,10 @@ SIGNATURES = {
     "tstwo_accumulate_quotients": (C.c_int, [C.c_int, C.c_uint32, dptrp, C.c_int, u32p, C.c_int, u32p, intp, intp, u32p, dptrp]),
     "tstwo_lde_commit": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptr, C.POINTER(C.c_uint8), C.c_uint32]),
     "tstwo_lde_columns_sharded": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, C.c_int, C.c_uint32]),
+    "tstwo_lde_columns_to_peers": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptrp, C.c_int, C.c_int, C.c_uint32]),
+    "tstwo_ipc_export": (C.c_int, [dptr, C.POINTER(C.c_uint8)]),
+    "tstwo_ipc_import": (C.c_int, [C.POINTER(C.c_uint8), C.POINTER(C.c_uint64)]),
+    "tstwo_ipc_close": (C.c_int, [dptr]),
     "tstwo_lde_commit_host": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptr, dptr,
                                         C.POINTER(C.c_uint8), C.c_uint32]),
 }

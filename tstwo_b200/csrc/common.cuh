@@ -60,6 +60,17 @@ struct ColSet {
     int shard_log = 31;
     uint64_t shard_adj = 0;
     bool aligned16 = true;      // every column starts on a 16-byte boundary (what the bulk copies of fft_tma.cu need)
+    // Optional per-shard base addresses (device array of 2^k pointers): shard s = idx >> shard_log of column c starts at
+    // shard_bases[s] + c * stride words.  The bases may be PEER memory (another GPU's buffer mapped over NVLink): this
+    // is how the last FFT pass of the multi-GPU path stores every row range straight into its owner's leaf buffer.
+    const uint64_t *shard_bases = nullptr;
+    // address of element idx of column c; runs of a tile (<= 2^shard_log aligned indices) are contiguous from it
+    __device__ __forceinline__ uint32_t *ptr(int c, uint32_t idx) const
+    {
+        if (shard_bases)
+            return reinterpret_cast<uint32_t *>(shard_bases[idx >> shard_log]) + (uint64_t)c * stride + (idx & ((1u << shard_log) - 1));
+        return col(c) + off(idx);
+    }
     __host__ __device__ __forceinline__ uint32_t *col(int c) const
     {
         return table ? reinterpret_cast<uint32_t *>(table[c]) : const_cast<uint32_t *>(base) + (uint64_t)c * stride;

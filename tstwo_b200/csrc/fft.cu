@@ -498,6 +498,7 @@ int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n,
         int rc = ensure_smem_attr();
         if (rc) return rc;
         const int mode = g_last_mode = pick_mode(false, src, dst, work, n_cols, L);
+        if (dst.shard_bases && mode != 2) return fail(TSTWO_ERR_BAD_ARG, "per-shard output bases need the bulk-copy FFT passes");
         Pass ps[MAX_PASSES];
         int np = mode == 2 ? plan_passes(L, ps, TMA_W0, TMA_W1) : plan_passes(L, ps, W0, W1);
         for (int k = np - 1; k >= 0; k--) {
@@ -511,7 +512,7 @@ int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n,
         }
         return 0;
     }
-    if (dst.shard_log != 31) return fail(TSTWO_ERR_BAD_ARG, "row-sharded output needs poly_log >= %d", FAST_MIN_LOG);
+    if (dst.shard_log != 31 || dst.shard_bases) return fail(TSTWO_ERR_BAD_ARG, "row-sharded output needs poly_log >= %d", FAST_MIN_LOG);
     dim3 egrid((unsigned)((N + 255) / 256), (unsigned)n_cols);
     const bool in_place = (src.base == dst.base && src.table == dst.table && src.stride == dst.stride);
     if (!(in_place && L == n)) TS_LAUNCH(extend_kernel, egrid, 256, 0, src, dst, L, n);

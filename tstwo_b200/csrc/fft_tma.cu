@@ -297,7 +297,7 @@ __device__ __forceinline__ void tile_drain(const TmaParams &sp, const Tile tl, u
     if (STRIDED) {
         if (tg == 0) { tensor_s2g(&sp.dst_map, tl.mid << 5, tl.hi << 8, tl.col, buf); bulk_commit(); }
     } else if (tg < 16) {
-        uint32_t *dst = p.dst.col(tl.col) + p.dst.off(tl.hi << 14) + 1024 * tg;
+        uint32_t *dst = p.dst.ptr(tl.col, tl.hi << 14) + 1024 * tg;
         bulk_s2g(dst, buf + tg * CHUNK_BYTES, 4096);
         bulk_commit();
     }
@@ -511,7 +511,8 @@ int tma_pass_init()
 // column set, also uniformly spaced columns (the contiguous pass copies column by column and takes any table).
 bool tma_pass_supported(const PassParams &p)
 {
-    if (!p.src.aligned16 || !p.dst.aligned16) return false;
+    if (!p.src.aligned16 || !p.dst.aligned16 || p.src.shard_bases) return false;
+    if (p.dst.shard_bases && p.lo != 0) return false;
     if (p.lo == 0) return p.src.shard_log >= TMA_W0 && p.dst.shard_log >= TMA_W0;
     if (p.src.table || p.dst.table || p.src.shard_log != 31 || p.dst.shard_log != 31) return false;
     if ((reinterpret_cast<uintptr_t>(p.src.base) | reinterpret_cast<uintptr_t>(p.dst.base)) & 15) return false;

@@ -2,6 +2,7 @@
 // packages/core/src/pcs/prover.ts:215-235 (interpolate -> evaluate on the blown-up canonic domain -> Merkle commit),
 // i.e. PolyOps.interpolateColumns + evaluatePolynomials (poly/circle/ops.ts:73-101) + MerkleProver.commit
 // (vcs/prover.ts:13-30) on device-resident columns.
+#include <cstring>
 #include <vector>
 
 #include "common.cuh"
@@ -117,6 +118,72 @@ int tstwo_lde_columns_sharded(tstwo_dptr trace, int n_cols, int log_size, int lo
     ev.shard_adj = (uint64_t)n_cols * rows - rows;
     if ((rc = fft_interpolate(src, cfs, n_cols, log_size, t, flags))) return rc;
     return fft_evaluate(cfs, log_size, ev, n_cols, ext, t, flags, &work);
+}
+
+// Multi-GPU, fused exchange: like tstwo_lde_columns_sharded, but the last FFT pass stores the rows of shard d straight
+// into shard_bases[d] -- the leaf buffer [total columns][rows] of rank d, mapped into this process with
+// tstwo_ipc_import -- at column col_offset + c.  No send buffer, no all-to-all: the stores travel over NVLink while the
+// butterflies of the next tiles run.  The caller orders the step with one (tiny) collective before the receivers hash.
+int tstwo_lde_columns_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, tstwo_dptr coeffs,
+                               tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards, int col_offset, uint32_t flags)
+{
+    TS_REQUIRE_INIT();
+    TwiddleTree *t;
+    int rc = check_args(n_cols, log_size, log_blowup, tw, &t);
+    if (rc) return rc;
+    const int ext = log_size + log_blowup;
+    int sl = 0;
+    while ((1 << sl) < n_shards) sl++;
+    if (n_shards < 1 || n_shards > 64 || (1 << sl) != n_shards || ext - sl < 14) return fail(TSTWO_ERR_BAD_ARG, "bad shard count %d", n_shards);
+    if (!trace || !work || !shard_bases || col_offset < 0) return fail(TSTWO_ERR_BAD_ARG, "null trace/work/shard bases");
+    const uint64_t n = 1ull << log_size, ne = 1ull << ext, rows = 1ull << (ext - sl);
+    uint32_t *scr = nullptr;
+    if (!coeffs && (rc = coeff_scratch((size_t)n_cols * n, &scr))) return rc;
+    uint32_t *cf = coeffs ? (uint32_t *)coeffs : scr;
+    // per-shard bases, already advanced to this rank's first column, in the library's device pointer table (slot 2)
+    Context &c = ctx();
+    uint64_t host_bases[64];
+    for (int d = 0; d < n_shards; d++) {
+        if (!shard_bases[d] || (shard_bases[d] & 15)) return fail(TSTWO_ERR_BAD_ARG, "shard base %d null or not 16-byte aligned", d);
+        host_bases[d] = shard_bases[d] + (uint64_t)col_offset * rows * 4;
+    }
+    uint64_t *dev_bases = c.d_ptr_table + 2 * 4096;
+    TS_CUDA(cudaMemcpyAsync(dev_bases, host_bases, sizeof(uint64_t) * (size_t)n_shards, cudaMemcpyHostToDevice, c.stream));
+    ColSet src = { (const uint32_t *)trace, n, nullptr };
+    ColSet cfs = { cf, n, nullptr };
+    ColSet wk = { (const uint32_t *)work, ne, nullptr };
+    ColSet ev = { nullptr, rows, nullptr };
+    ev.shard_log = ext - sl;
+    ev.shard_bases = dev_bases;
+    if ((rc = fft_interpolate(src, cfs, n_cols, log_size, t, flags))) return rc;
+    return fft_evaluate(cfs, log_size, ev, n_cols, ext, t, flags, &wk);
+}
+
+// CUDA IPC plumbing for the above (one process per GPU): export a tstwo_malloc'ed buffer, import a peer's.
+int tstwo_ipc_export(tstwo_dptr ptr, uint8_t handle[64])
+{
+    TS_REQUIRE_INIT();
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    cudaIpcMemHandle_t h;
+    TS_CUDA(cudaIpcGetMemHandle(&h, (void *)ptr));
+    memcpy(handle, &h, 64);
+    return 0;
+}
+int tstwo_ipc_import(const uint8_t handle[64], tstwo_dptr *out)
+{
+    TS_REQUIRE_INIT();
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    void *p = nullptr;
+    TS_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *out = (tstwo_dptr)p;
+    return 0;
+}
+int tstwo_ipc_close(tstwo_dptr ptr)
+{
+    TS_REQUIRE_INIT();
+    TS_CUDA(cudaIpcCloseMemHandle((void *)ptr));
+    return 0;
 }
 
 // Host-resident trace: the columns are copied in chunks on a copy stream while the previous chunk's interpolate /

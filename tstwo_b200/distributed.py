@@ -105,3 +105,90 @@ class ShardedCommit:
             self.top = top_layers(ops, self.roots, self.world)
             return ops.to_host_bytes(self.top[-1] if self.top else self.roots)[:32]
         return None
+
+
+class PeerShardedCommit:
+    """The same pipeline with the exchange FUSED into the last FFT pass (no send buffer, no all-to-all): every rank maps
+    the leaf buffers of all ranks (CUDA IPC over NVLink) and its last evaluate pass stores each row range straight into
+    the owner's [n_cols][rows] buffer (tstwo_lde_columns_to_peers) while the butterflies of the next tiles run.
+      1. LDE of the n_cols/G local columns, evaluations stored into the G leaf buffers at column rank * n_cols/G + c;
+      2. one 4-byte all-reduce orders the step: when it completes on a rank, every rank's stores have been issued and
+         completed (stream order + kernel completion), so the rank may hash its leaves;
+      3. subtree per rank, all-gather of the G roots (which also keeps a fast rank from overwriting a leaf buffer that
+         is still being hashed in the next step), top log2 G layers on rank 0.
+    CUDA-only (needs peer access); the protocol above the device work is the one tests/test_distributed_cpu.py covers."""
+
+    def __init__(self, device_index: int, stream, n_cols: int, log_size: int, log_blowup: int, keep_coeffs: bool = False):
+        from . import _lib
+        self._lib_mod = _lib
+        self.L = _lib.init(device_index)
+        chk = _lib.check
+        self.dev = torch.device("cuda", device_index)
+        if stream is not None:
+            chk(self.L.tstwo_set_stream(C.c_void_p(stream.cuda_stream)))
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        G = self.world
+        if G & (G - 1) or n_cols % G:
+            raise ValueError("world size must be a power of two dividing n_cols")
+        self.n_cols, self.lc = n_cols, n_cols // G
+        self.log_size, self.blow, self.ext = log_size, log_blowup, log_size + log_blowup
+        self.sub = self.ext - (G.bit_length() - 1)
+        if self.sub < 14:
+            raise ValueError("row shards must hold at least 2^14 rows")
+        rows = 1 << self.sub
+        self.ops = CudaShardOps(device_index)      # merkle / top layers
+        self.tw = self.ops.twiddles(self.ext)
+        self.coeffs = self.ops.empty(self.lc << log_size) if keep_coeffs else None
+        self.work = self.ops.empty(self.lc << self.ext)
+        self.layers = self.ops.empty(8 * ((2 << self.sub) - 1))
+        self.roots = self.ops.empty(8 * G)
+        self.flag = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        self.top: List[torch.Tensor] = []
+        # leaf buffer of this rank: its own cudaMalloc (IPC exports whole allocations), exported to every peer
+        p = C.c_uint64()
+        chk(self.L.tstwo_malloc(4 * n_cols * rows, C.byref(p)))
+        self.recv_ptr = p.value
+        handle = (C.c_uint8 * 64)()
+        chk(self.L.tstwo_ipc_export(self.recv_ptr, handle))
+        mine = torch.tensor(list(bytes(handle)), dtype=torch.uint8, device=self.dev)
+        allh = torch.empty(64 * G, dtype=torch.uint8, device=self.dev)
+        dist.all_gather_into_tensor(allh, mine)
+        allh = allh.cpu().numpy()
+        self.bases, self._imported = [], []
+        for r in range(G):
+            if r == self.rank:
+                self.bases.append(self.recv_ptr)
+                continue
+            q = C.c_uint64()
+            h = (C.c_uint8 * 64)(*allh[64 * r:64 * (r + 1)].tolist())
+            chk(self.L.tstwo_ipc_import(h, C.byref(q)))
+            self.bases.append(q.value)
+            self._imported.append(q.value)
+        self._bases_arr = _lib.dptr_array(self.bases)
+        dist.barrier()
+
+    def step(self, trace: torch.Tensor):
+        chk = self._lib_mod.check
+        chk(self.L.tstwo_lde_columns_to_peers(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw,
+                                              self.coeffs.data_ptr() if self.coeffs is not None else 0, self.work.data_ptr(),
+                                              self._bases_arr, self.world, self.rank * self.lc, 0))
+        dist.all_reduce(self.flag)                 # every rank's stores into my leaf buffer are complete after this
+        rows = 1 << self.sub
+        ptrs = self._lib_mod.dptr_array([self.recv_ptr + 4 * rows * c for c in range(self.n_cols)])
+        logs = (C.c_int * self.n_cols)(*([self.sub] * self.n_cols))
+        chk(self.L.tstwo_merkle_commit(ptrs, logs, self.n_cols, self.layers.data_ptr(), None))
+        dist.all_gather_into_tensor(self.roots, self.layers[:8].contiguous())
+        if self.rank == 0:
+            self.top = top_layers(self.ops, self.roots, self.world)
+            return self.ops.to_host_bytes(self.top[-1] if self.top else self.roots)[:32]
+        return None
+
+    def close(self):
+        torch.cuda.synchronize()
+        dist.barrier()
+        for q in self._imported:
+            self.L.tstwo_ipc_close(q)
+        self._imported = []
+        if self.recv_ptr:
+            self.L.tstwo_free(self.recv_ptr)
+            self.recv_ptr = 0
