@@ -23,6 +23,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+_REAL_STDOUT = sys.stdout
 N_COLS, LOG_SIZE, LOG_BLOWUP = 256, 22, 1
 # DRAM bytes (read + written) per launch of the kernels below at the headline size, from ncu (profiles/r01_launches_tma.txt)
 NCU_TRAFFIC = {"merkle_leaf_layer": 8.59e9 + 0.21e9, "evaluate (2 fft launches)": (4.51e9 + 8.53e9 + 8.61e9 + 8.53e9) / 2,
@@ -44,7 +45,7 @@ def parse():
     ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
                     help="N > 1: 'peer' = last FFT pass stores into the peers' leaf buffers over NVLink; 'nccl' = all-to-all")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--cpu-sample-cols", type=int, default=8)
+    ap.add_argument("--cpu-sample-cols", type=int, default=64)
     ap.add_argument("--fft-radix", type=int, default=0, help="tuning: rows per thread of the FFT passes (8 or 16)")
     return ap.parse_args()
 
@@ -145,8 +146,12 @@ def cpu_baseline(args):
 
 def run_cuda(args):
     # NCCL prints its version banner on stdout when NCCL_DEBUG=VERSION: the driver wants exactly one JSON line there
-    # (NCCL_DEBUG >= VERSION, which this image sets); keep the level, send NCCL's log to stderr instead
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # ("NCCL version ..." appears there on this image): everything written to fd 1 from here on goes to stderr, and
+    # rank 0 prints the JSON line on the saved original stdout
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -322,7 +327,7 @@ def run_cuda(args):
         if kernels: out["kernels"] = kernels
         if e2e: out["e2e"] = e2e
         if cpu: out["cpu_baseline"] = cpu
-        print(json.dumps(out))
+        print(json.dumps(out), file=_REAL_STDOUT, flush=True)
     if world > 1:
         if hasattr(sc, "close"):
             sc.close()
