@@ -110,6 +110,40 @@ __global__ void __launch_bounds__(256) k_blake_v(uint32_t *out, int iters, uint3
     for (int i = 0; i < 8; i++) s ^= h[i];
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
+// ---- what separates the leaf kernel from the pure compress loop: launch shape and message loads
+// LOADS: 0 = message stays in registers, 1 = 16 column-major loads per compression (row i of column c at in[c * n_rows + i]),
+// each CTA handles row tiles of 256 rows: tile = blockIdx.x, blockIdx.x + gridDim.x, ... ; `blocks` compressions per row.
+template <int LOADS>
+__global__ void __launch_bounds__(256) k_blake_shape(uint32_t *out, const uint32_t *__restrict__ in, unsigned long long n_rows, int blocks, uint32_t one)
+{
+    for (unsigned long long row0 = (unsigned long long)blockIdx.x * 256; row0 < n_rows; row0 += (unsigned long long)gridDim.x * 256) {
+        uint32_t h[8], m[16];
+        const unsigned long long i = row0 + threadIdx.x;
+        for (int k = 0; k < 8; k++) h[k] = threadIdx.x * 31 + k;
+        for (int k = 0; k < 16; k++) m[k] = threadIdx.x * 17 + k * 3 + blockIdx.x;
+        for (int b = 0; b < blocks; b++) {
+            if (LOADS) {
+#pragma unroll
+                for (int k = 0; k < 16; k++) m[k] = __ldcs(in + (unsigned long long)(16 * b + k) * n_rows + i);
+            }
+            compress_v<1>(h, m, b, one);
+        }
+        uint32_t s = 0;
+        for (int k = 0; k < 8; k++) s ^= h[k];
+        out[i] = s;
+    }
+}
+template <int LOADS> int run_shape(const char *name, int grid, uint32_t *out, const uint32_t *in, unsigned long long n_rows, int blocks, int sms)
+{
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    k_blake_shape<LOADS><<<grid, 256>>>(out, in, n_rows, blocks, 1u); CK(cudaDeviceSynchronize());
+    CK(cudaEventRecord(e0)); k_blake_shape<LOADS><<<grid, 256>>>(out, in, n_rows, blocks, 1u); CK(cudaEventRecord(e1)); CK(cudaDeviceSynchronize());
+    float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+    double comp = (double)n_rows * blocks;
+    printf("blake2s shape %-44s grid=%6d  chip %7.2f Gcompress/s  => %.0f clk per warp-compress per SMSP @1965MHz (%.3f ms)\n",
+           name, grid, comp / ms / 1e6, 1.965e9 / (comp / (ms * 1e-3) / 32 / (sms * 4)), ms);
+    return 0;
+}
 template <int VAR> int run_blake(const char *name, int sms, uint32_t *out)
 {
     for (int bps : {2, 4, 6}) {
@@ -194,6 +228,17 @@ int main()
     run_blake<0>("iadd3 adds (as compiled)", sms, out);
     run_blake<1>("all adds IMAD*one", sms, out);
     run_blake<2>("2-input adds IMAD*one", sms, out);
+    {
+        const unsigned long long n_rows = 1ull << 23;
+        const int cols = 256;
+        uint32_t *in, *o2; CK(cudaMalloc(&in, n_rows * cols * 4)); CK(cudaMalloc(&o2, n_rows * 4)); CK(cudaMemset(in, 5, n_rows * cols * 4));
+        run_shape<0>("registers, one CTA per row tile", (int)(n_rows / 256), o2, in, n_rows, cols / 16, sms);
+        run_shape<0>("registers, persistent (4 CTAs/SM)", sms * 4, o2, in, n_rows, cols / 16, sms);
+        run_shape<1>("column loads, one CTA per row tile", (int)(n_rows / 256), o2, in, n_rows, cols / 16, sms);
+        run_shape<1>("column loads, persistent (4 CTAs/SM)", sms * 4, o2, in, n_rows, cols / 16, sms);
+        run_shape<1>("column loads, persistent (3 CTAs/SM)", sms * 3, o2, in, n_rows, cols / 16, sms);
+        CK(cudaFree(in)); CK(cudaFree(o2));
+    }
     for (int bps : {8}) {
         int iters = 2048, grid = sms * bps;
         cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));

@@ -6,9 +6,12 @@
 // One thread per node.  The message words of a node come straight from column-major loads: for a fixed column
 // the 32 lanes of a warp read 32 consecutive rows (128 B, fully coalesced).  Rotations by 16/8 are PRMT, by
 // 12/7 funnel shifts; the ten rounds are fully unrolled with compile-time message schedules.
+#include <cuda.h>
+
 #include <vector>
 
 #include "common.cuh"
+#include "fft_params.cuh"
 
 namespace tstwo {
 
@@ -104,6 +107,125 @@ __global__ void __launch_bounds__(256) merkle_layer_kernel(const uint4 *__restri
     out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
 }
 
+// ---- leaf layer fed by bulk tensor copies -----------------------------------------------------------------------
+// The leaf hash of row i absorbs column words c = 0, 1, ... of that row, 16 per compression.  With uniformly spaced
+// columns the message blocks of 256 consecutive rows are boxes [16 columns x 256 rows] (16 KiB, sixteen 1 KiB runs) of
+// one 2-D tensor (rows fastest).  A CTA keeps two boxes in shared memory: while it compresses block b the copy engine
+// fetches block b + 1; the warp that is LAST to pull its message words out of a box (a shared-memory counter tells it)
+// immediately asks for the box two blocks ahead, so no warp ever waits for a designated producer.  A thread's 16 message
+// words are 16 conflict-free shared-memory loads with immediate offsets: no per-column address arithmetic (~10 % of
+// the ALU slots of merkle_layer_kernel) and no register double buffer, which is what lets 5 CTAs (40 warps) fit an SM.
+// Columns past n_cols are out of bounds of the tensor and arrive as zeros: exactly BLAKE2s's padding of the last block.
+// (Per-warp boxes of [16 x 32] rows were tried: sixteen 128-byte runs per 2 KiB make the copy engine the bottleneck.)
+constexpr int LEAF_ROWS = 256, LEAF_STAGES = 2, LEAF_STAGE_BYTES = 16 * LEAF_ROWS * 4;
+constexpr int LEAF_SMEM = LEAF_STAGES * LEAF_STAGE_BYTES + 64;   // stages, then LEAF_STAGES barriers and LEAF_STAGES counters
+
+__device__ __forceinline__ uint32_t leaf_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+// The wait is one asm block (try_wait, branch back) rather than a C++ loop on purpose: with a C++ loop AND the lane-0 branch
+// below in the hash loop, ptxas keeps `one` (B2S_ADD) in a vector register and allocates registers for three-operand IMADs,
+// which leaves ~350 same-bank operand pairs per compression; with this form it uses IMAD R, R, UR, R and the pairs drop
+// below 30 (cuobjdump -sass; dispatch stalls 0.9 -> 0.4 per issue).  A lost box traps after 2^22 polls instead of hanging.
+__device__ __forceinline__ void leaf_mbar_wait(uint32_t bar, uint32_t parity)
+{
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .u32 n;\n\tmov.u32 n, 0;\n"
+                 "LEAF_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra LEAF_DONE;\n\t"
+                 "add.u32 n, n, 1;\n\tsetp.lt.u32 p, n, 0x400000;\n\t@p bra LEAF_WAIT;\n\ttrap;\n"
+                 "LEAF_DONE:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void leaf_fetch(uint32_t dst, const CUtensorMap *map, uint32_t row0, uint32_t col0, uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(LEAF_STAGE_BYTES) : "memory");
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(row0), "r"(col0), "r"(bar) : "memory");
+}
+__device__ __forceinline__ uint32_t leaf_lds(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(LEAF_ROWS, 5) merkle_leaf_tma_kernel(const __grid_constant__ CUtensorMap map, int n_cols,
+                                                                       uint4 *__restrict__ out, uint32_t one)
+{
+    extern __shared__ __align__(128) uint8_t leaf_smem[];
+    const uint32_t base = leaf_smem_u32(leaf_smem);                 // stage s at base + s * LEAF_STAGE_BYTES
+    const uint32_t ctl = base + LEAF_STAGES * LEAF_STAGE_BYTES;     // barrier s at ctl + 8 s, reader counter s at ctl + 32 + 4 s
+    const uint32_t n_blocks = ((uint32_t)n_cols + 15u) / 16u;
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < LEAF_STAGES; s++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(ctl + 8 * s), "r"(1) : "memory");
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(ctl + 32 + 4 * s), "r"(0) : "memory");
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#pragma unroll
+        for (uint32_t s = 0; s < LEAF_STAGES; s++)
+            if (s < n_blocks) leaf_fetch(base + s * LEAF_STAGE_BYTES, &map, blockIdx.x * LEAF_ROWS, 16 * s, ctl + 8 * s);
+    }
+    __syncthreads();
+    uint32_t h[8], m[16];
+    b2s_init(h);
+    uint32_t s = 0, ph = 0;          // stage and phase of block b
+#pragma unroll 1
+    for (uint32_t b = 0; b < n_blocks; b++) {
+        leaf_mbar_wait(ctl + 8 * s, ph);
+#pragma unroll
+        for (int k = 0; k < 16; k++) m[k] = leaf_lds(base + s * LEAF_STAGE_BYTES + 4 * threadIdx.x + 4 * LEAF_ROWS * k);
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) {
+            // shared-memory operations of a warp are performed in order: the loads above precede this counter update,
+            // and the refill it may trigger is ordered after the update of every warp
+            uint32_t old;
+            asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(ctl + 32 + 4 * s) : "memory");
+            if ((old & (LEAF_ROWS / 32 - 1)) == LEAF_ROWS / 32 - 1 && b + LEAF_STAGES < n_blocks)
+                leaf_fetch(base + s * LEAF_STAGE_BYTES, &map, blockIdx.x * LEAF_ROWS, 16 * (b + LEAF_STAGES), ctl + 8 * s);
+        }
+        const bool last = b + 1 == n_blocks;
+        b2s_compress(h, m, last ? (uint32_t)n_cols * 4u : (b + 1) * 64u, last, one);
+        if (++s == LEAF_STAGES) { s = 0; ph ^= 1; }
+    }
+    const uint64_t i = (uint64_t)blockIdx.x * LEAF_ROWS + threadIdx.x;
+    out[2 * i] = make_uint4(h[0], h[1], h[2], h[3]);
+    out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
+}
+
+static int g_leaf_mode = 1;    // 1: bulk-copy-fed leaf kernel where it applies; 0: merkle_layer_kernel always (tstwo_debug_set_leaf_mode)
+static int g_last_leaf = -1;
+
+typedef CUresult (*LeafEncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static bool leaf_tma_applies(const ColSet &cs, int n_cols, uint64_t n)
+{
+    return g_leaf_mode != 0 && n_cols >= 1 && !cs.table && !cs.shard_bases && cs.shard_log == 31 && n >= LEAF_ROWS && n < (1ull << 32) &&
+           (reinterpret_cast<uintptr_t>(cs.base) & 15) == 0 && (n_cols == 1 || ((cs.stride * 4) % 16 == 0 && cs.stride >= n && cs.stride * 4 < (1ull << 40)));
+}
+
+static int merkle_leaf_tma(const ColSet &cs, int n_cols, uint64_t n, uint8_t *out)
+{
+    static bool attr_done = false;
+    LeafEncodeFn enc = reinterpret_cast<LeafEncodeFn>(tma_encode_tiled_fn());
+    if (!enc) return TSTWO_ERR_CUDA;
+    if (!attr_done) {
+        TS_CUDA(cudaFuncSetAttribute(merkle_leaf_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LEAF_SMEM));
+        TS_CUDA(cudaFuncSetAttribute(merkle_leaf_tma_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        attr_done = true;
+    }
+    CUtensorMap map;
+    const cuuint64_t dims[2] = { n, (cuuint64_t)n_cols };
+    const cuuint64_t strides[1] = { n_cols > 1 ? cs.stride * 4 : n * 4 };
+    const cuuint32_t box[2] = { LEAF_ROWS, 16 }, estr[2] = { 1, 1 };
+    CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<uint32_t *>(cs.base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(TSTWO_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for %d leaf columns of %llu rows", (int)r, n_cols, (unsigned long long)n);
+    TS_LAUNCH(merkle_leaf_tma_kernel, (unsigned)(n / LEAF_ROWS), LEAF_ROWS, LEAF_SMEM, map, n_cols, (uint4 *)out, 1u);
+    return 0;
+}
+
 // Leaf layer in column chunks (host-fed pipeline: columns arrive over PCIe 16 at a time).  The BLAKE2s chaining value of
 // every row lives in the leaf layer itself; a launch absorbs columns [c0, c0 + nc) of a leaf of `total_cols` words
 // (c0 a multiple of 16; nc a multiple of 16 unless the chunk is the last) and the chunk holding the last word finalises.
@@ -142,6 +264,11 @@ int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, i
     const uint64_t n = 1ull << log_size;
     const unsigned block = 256;
     const unsigned grid = (unsigned)((n + block - 1) / block);
+    g_last_leaf = 0;
+    if (!prev && leaf_tma_applies(cols, n_cols, n)) {
+        g_last_leaf = g_leaf_mode;
+        return merkle_leaf_tma(cols, n_cols, n, out);
+    }
     if (prev) TS_LAUNCH((merkle_layer_kernel<true>), grid, block, 0, (const uint4 *)prev, cols, n_cols, n, (uint4 *)out, 1u);
     else TS_LAUNCH((merkle_layer_kernel<false>), grid, block, 0, (const uint4 *)nullptr, cols, n_cols, n, (uint4 *)out, 1u);
     return 0;
@@ -152,6 +279,9 @@ int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, i
 using namespace tstwo;
 
 extern "C" {
+
+int tstwo_debug_set_leaf_mode(int mode) { g_leaf_mode = mode; return 0; }
+int tstwo_debug_last_leaf_mode(void) { return g_last_leaf; }
 
 int tstwo_merkle_commit_layer(int log_size, tstwo_dptr prev_layer, const tstwo_dptr *cols, int n_cols, tstwo_dptr out_layer)
 {

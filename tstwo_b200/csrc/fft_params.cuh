@@ -28,5 +28,7 @@ constexpr int TMA_W0 = 14, TMA_W1 = 8;
 int tma_pass(bool inverse, const PassParams &p);
 int tma_pass_init();
 bool tma_pass_supported(const PassParams &p);
+// cuTensorMapEncodeTiled of the loaded driver (resolved once by tma_pass_init), or nullptr; also used by blake2s.cu
+void *tma_encode_tiled_fn();
 
 }  // namespace tstwo

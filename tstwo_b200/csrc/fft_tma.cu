@@ -507,6 +507,8 @@ int tma_pass_init()
     return 0;
 }
 
+void *tma_encode_tiled_fn() { return tma_pass_init() ? nullptr : reinterpret_cast<void *>(g_encode); }
+
 // What a pass needs of its column sets: 16-byte aligned columns; the strided pass, whose tensor maps describe a whole
 // column set, also uniformly spaced columns (the contiguous pass copies column by column and takes any table).
 bool tma_pass_supported(const PassParams &p)
