@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 _REAL_STDOUT = sys.stdout
 N_COLS, LOG_SIZE, LOG_BLOWUP = 256, 22, 1
 # DRAM bytes (read + written) per launch of the kernels below at the headline size, from ncu (profiles/r01_launches_tma.txt)
-NCU_TRAFFIC = {"merkle_leaf_layer": 8.59e9 + 0.21e9, "evaluate (2 fft launches)": (4.51e9 + 8.53e9 + 8.61e9 + 8.53e9) / 2,
+NCU_TRAFFIC = {"merkle_leaf_layer": 8.59e9 + 0.27e9, "evaluate (2 fft launches)": (4.51e9 + 8.53e9 + 8.61e9 + 8.53e9) / 2,
                "interpolate (2 fft launches)": (4.31e9 + 4.25e9 + 4.31e9 + 4.23e9) / 2}
 METRIC = "lde_blake2s_commit_throughput"
 UNIT = "M31 trace elements/s"
@@ -272,19 +272,19 @@ def run_cuda(args):
                 "frac": by_launch / ms_launch / 1e6 / peak, "traffic": NCU_TRAFFIC.get(top_k) if (n_cols, log, blow) == (N_COLS, LOG_SIZE, LOG_BLOWUP) else None, "peak_source": which,
                 "algorithmic_bytes_per_launch": by_launch, "ms_per_launch": ms_launch,
                 "note": "this kernel is integer-pipe bound, not HBM bound (see int_roofline); traffic = dram bytes read+written "
-                        "per launch from profiles/r01_launches_tma.txt"}
+                        "per launch from profiles/r01_launches_v.txt"}
         # integer-pipe rooflines measured on this pool with tools/microbench*.cu (profiles/r01_microbench_*.txt):
         # 3.667e12 M31 butterflies/s (ALU-pipe bound, 10.15 clk per warp-butterfly per SM sub-partition) and
-        # 23.9e9 Blake2s compressions/s (1555 clk per warp-compression per sub-partition) at 1965 MHz
+        # 27.7e9 Blake2s compressions/s (1345 clk per warp-compression per sub-partition, message in registers) at 1965 MHz
         n_bf = n_cols * (log * (n // 2) + log * (ne // 2))          # the top log_blowup layers of evaluate are copies
         n_cmp = ne * ((4 * n_cols + 63) // 64) + ne - 1
         t_fft = kernels["interpolate (2 fft launches)"]["ms"] + kernels["evaluate (2 fft launches)"]["ms"]
         t_mk = kernels["merkle_leaf_layer"]["ms"] + 2 * kernels["merkle_node_layer_top"]["ms"]   # node layers halve: sum ~ 2x the top one
         int_roof = {"fft": {"butterflies": n_bf, "ms": t_fft, "achieved": n_bf / t_fft / 1e6, "peak": 3667.0, "unit": "G butterflies/s",
                             "frac": n_bf / t_fft / 1e6 / 3667.0},
-                    "blake2s": {"compressions": n_cmp, "ms": t_mk, "achieved": n_cmp / t_mk / 1e6, "peak": 23.9, "unit": "G compressions/s",
-                                "frac": n_cmp / t_mk / 1e6 / 23.9},
-                    "peak_source": "tools/microbench.cu, tools/microbench_bf.cu on B200 (profiles/r01_microbench_int_pipes.txt, r01_microbench_stage.txt)"}
+                    "blake2s": {"compressions": n_cmp, "ms": t_mk, "achieved": n_cmp / t_mk / 1e6, "peak": 27.7, "unit": "G compressions/s",
+                                "frac": n_cmp / t_mk / 1e6 / 27.7},
+                    "peak_source": "tools/microbench.cu, tools/microbench_bf.cu on B200 (profiles/r01_microbench_int_pipes.txt, r01_microbench_stage.txt, r01_microbench_blake2s_forms.txt)"}
 
     # ---- end to end through the C ABI with HOST buffers (1 GPU)
     e2e = None

@@ -100,3 +100,26 @@ def test_batch_ops_with_scattered_inputs_use_bulk_copies(tb, orc):
         ec = orc.interpolate(vals[c], dom.halfCoset.initial_index.value, root, oitw)
         assert (polys[c].coeffs.toCpu() == ec).all()
         assert (out[c].values.toCpu() == orc.evaluate(ec, ext, big.halfCoset.initial_index.value, root, otw)).all()
+
+
+def test_partial_top_pass_repeats_exactly(tb):
+    """Regression: the 2-layer partial pass of a 2^24 transform finishes a tile faster than a bulk copy lands, so a group
+    could reach its next wait on a buffer one phase early and fall through on the barrier's parity (stale tile -> every
+    output wrong, about one run in eight).  Buffers now alternate between two barriers; repeat the transform and demand
+    the identical, correct result every time in both persistent families."""
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    log = 24
+    tw = tb.CudaBackend.precomputeTwiddles(tb.Coset.half_odds(log - 1))
+    vals = np.random.default_rng(99).integers(0, P, 1 << log, dtype=np.uint32)
+    dom = tb.CanonicCoset.new(log).circleDomain()
+    try:
+        for mode in (2, 1):
+            L.tstwo_debug_set_fft_stream(mode)
+            poly = tb.CudaCircleEvaluation.new(dom, vals).interpolateWithTwiddles(tw)
+            for _ in range(12):
+                back = poly.evaluateWithTwiddles(dom, tw)
+                assert L.tstwo_debug_last_fft_mode() == mode
+                assert (back.values.toCpu() == vals).all()
+    finally:
+        L.tstwo_debug_set_fft_stream(2)

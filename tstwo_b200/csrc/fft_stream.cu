@@ -314,8 +314,12 @@ __global__ void __launch_bounds__(THREADS, 1) fft_stream_kernel(const StreamPara
         start = a; step = 1; count = b - a;
     }
     if (tid == 0)
-        for (int b = 0; b < NBUF; b++) mbar_init(bar0 + 8 * b, GROUP);
-    uint32_t fills0 = 0, fills1 = 0, fills2 = 0;       // completed phases of the three barriers
+        for (int b = 0; b < 2 * NBUF; b++) mbar_init(bar0 + 8 * b, GROUP);
+    // Two barriers per buffer, for its even and its odd rounds: consecutive tiles of a buffer belong to different groups,
+    // and a group that is quick (the partial pass) could otherwise wait for round r + 1 while round r is still in flight,
+    // which a parity wait cannot tell apart.  Tiles i and i + 6 always belong to the same group.
+    auto bar_of = [&](uint32_t i) { return bar0 + 8 * (i % 3 + 3 * ((i / 3) & 1)); };
+    uint32_t par = 0;                                  // bit b + 3 x: parity of the completed phases of barrier x of buffer b
 
     uint32_t k = 0;
     while (k < count) {
@@ -329,14 +333,13 @@ __global__ void __launch_bounds__(THREADS, 1) fft_stream_kernel(const StreamPara
 #pragma unroll
         for (int i = 0; i < NBUF; i++)
             if ((uint32_t)i < len && (i & 1) == g)
-                tile_fetch<STRIDED>(p, decode<STRIDED>(sp, t0 + i * step, hi), smem_u32(sm + i * BUF_UNITS), bar0 + 8 * i, tg);
+                tile_fetch<STRIDED>(p, decode<STRIDED>(sp, t0 + i * step, hi), smem_u32(sm + i * BUF_UNITS), bar_of(i), tg);
 
         for (uint32_t i = g; i < len; i += 2) {
             const uint32_t b = i % 3, round = i / 3;
-            const uint32_t fills = b == 0 ? fills0 : b == 1 ? fills1 : fills2;
             uint4 *buf = sm + b * BUF_UNITS;
             const Tile tl = decode<STRIDED>(sp, t0 + i * step, hi);
-            mbar_wait(bar0 + 8 * b, (fills + round) & 1);
+            mbar_wait(bar_of(i), ((par >> (b + 3 * (round & 1))) ^ (round >> 1)) & 1);
             uint32_t v[16][4];
             constexpr int FIRST = INV ? 0 : 2, LAST = INV ? 2 : 0;
             tile_load<STRIDED, FIRST>(buf, tg, v);
@@ -352,7 +355,7 @@ __global__ void __launch_bounds__(THREADS, 1) fft_stream_kernel(const StreamPara
             if (!LINEAR_OUT) {
                 group_sync(g);                         // the whole group has read: the buffer can be refilled
                 if (i + 3 < len)
-                    tile_fetch<STRIDED>(p, decode<STRIDED>(sp, t0 + (i + 3) * step, hi), smem_u32(buf), bar0 + 8 * b, tg);
+                    tile_fetch<STRIDED>(p, decode<STRIDED>(sp, t0 + (i + 3) * step, hi), smem_u32(buf), bar_of(i + 3), tg);
             }
             stage_math<STRIDED, LAST, INV, FULL>(v, tws, tg, p.j_min);
             if (INV && p.scale2) {
@@ -367,10 +370,14 @@ __global__ void __launch_bounds__(THREADS, 1) fft_stream_kernel(const StreamPara
                 tile_write_linear(p, tl, buf, tg);
                 group_sync(g);
                 if (i + 3 < len)
-                    tile_fetch<STRIDED>(p, decode<STRIDED>(sp, t0 + (i + 3) * step, hi), smem_u32(buf), bar0 + 8 * b, tg);
+                    tile_fetch<STRIDED>(p, decode<STRIDED>(sp, t0 + (i + 3) * step, hi), smem_u32(buf), bar_of(i + 3), tg);
             } else tile_write<STRIDED, LAST>(p, tl, tg, v);
         }
-        fills0 += (len + 2) / 3; fills1 += (len + 1) / 3; fills2 += len / 3;
+#pragma unroll
+        for (int b = 0; b < 3; b++) {
+            const uint32_t uses = (len + 2 - b) / 3;               // rounds 0 .. uses - 1 of buffer b in this run
+            par ^= ((((uses + 1) >> 1) & 1) << b) ^ (((uses >> 1) & 1) << (b + 3));
+        }
         k += len;
     }
 }

@@ -49,7 +49,7 @@ constexpr int T1_WORDS = 4096 + 64;
 constexpr int STRIDED_HEAP_WORDS = 8 * 256;            // up to 8 coset heaps of 255 words
 template <bool STRIDED> constexpr int smem_bytes()
 {
-    return Cfg<STRIDED>::NBUF * Cfg<STRIDED>::BUF_BYTES + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS) * 4 + 64;
+    return Cfg<STRIDED>::NBUF * Cfg<STRIDED>::BUF_BYTES + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS) * 4 + 128;
 }
 static_assert(smem_bytes<false>() <= 232448 && smem_bytes<true>() <= 232448, "exceeds the 227 KiB of shared memory a CTA can opt into");
 
@@ -384,10 +384,15 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
         start = a; step = 1; count = b - a;
     }
     if (tid == 0) {
-        for (int b = 0; b < NBUF; b++) mbar_init(bar0 + 8 * b, 1);
+        for (int b = 0; b < 2 * NBUF; b++) mbar_init(bar0 + 8 * b, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    uint32_t par = 0;                                  // bit b: parity of the completed phases of buffer b's barrier
+    // Buffer b has TWO barriers, used by its even and odd rounds.  Consecutive tiles of a buffer belong to different
+    // groups (NBUF is not a multiple of G), and a group that finishes its tiles quickly (the 2-layer partial pass) could
+    // otherwise wait for round r + 1 while round r is still in flight -- a parity wait cannot tell those apart and
+    // would fall through onto stale data.  Tiles i and i + 2 NBUF always belong to the same group, which takes them in order.
+    auto bar_of = [&](uint32_t i) { return bar0 + 8 * (i % NBUF + NBUF * ((i / NBUF) & 1)); };
+    uint32_t par = 0;                                  // bit b + NBUF x: parity of the completed phases of barrier x of buffer b
 #ifdef TSTWO_FFT_TRACE
     int tr_n = 0, tr_all = 0;
 #endif
@@ -407,7 +412,7 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
 #pragma unroll
         for (int i = 0; i < NBUF; i++)
             if ((uint32_t)i < len && (i % G) == g)
-                tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar0 + 8 * i, tg);        uint32_t refill = 0xffffffffu;                 // DEFER: tile of mine whose buffer is still to be refilled
+                tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar_of(i), tg);        uint32_t refill = 0xffffffffu;                 // DEFER: tile of mine whose buffer is still to be refilled
 
         for (uint32_t i = g; i < len; i += G) {
             const uint32_t b = i % NBUF, round = i / NBUF;
@@ -415,7 +420,7 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
             const Tile tl = decode<STRIDED>(sp, t0 + i * step, hi);
             TRACE(0, i);
             TRACE_TILE();
-            mbar_wait(bar0 + 8 * b, ((par >> b) ^ round) & 1);
+            mbar_wait(bar_of(i), ((par >> (b + NBUF * (round & 1))) ^ (round >> 1)) & 1);
             TRACE(1, i);
             // The lanes that issue the stores wait until those have been read out of shared memory and refill the buffer
             // at once (the other seven warps are already on the next tile).  DEFER = refill at the first stage boundary
@@ -426,7 +431,7 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
                 if (DEFER && refill != 0xffffffffu) {
                     if (tg < 16) bulk_wait_read();
                     const uint32_t rb = refill % NBUF;
-                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (refill + NBUF) * step, hi), buf0 + rb * BUF_BYTES, bar0 + 8 * rb, tg);
+                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (refill + NBUF) * step, hi), buf0 + rb * BUF_BYTES, bar_of(refill + NBUF), tg);
                     refill = 0xffffffffu;
                 }
             });
@@ -438,7 +443,7 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
                 if (DEFER) refill = i;
                 else {
                     if (tg < 16) bulk_wait_read();
-                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (i + NBUF) * step, hi), buf0 + b * BUF_BYTES, bar0 + 8 * b, tg);
+                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (i + NBUF) * step, hi), buf0 + b * BUF_BYTES, bar_of(i + NBUF), tg);
                 }
             }
             TRACE(3, i);
@@ -448,7 +453,10 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
         }
         if (tg < 16) bulk_wait_read();                 // the buffers are reused by the next run and must outlive the copies
 #pragma unroll
-        for (int b = 0; b < NBUF; b++) par ^= (((len + NBUF - 1 - b) / NBUF) & 1) << b;
+        for (int b = 0; b < NBUF; b++) {
+            const uint32_t uses = (len + NBUF - 1 - b) / NBUF;      // rounds 0 .. uses - 1 of buffer b in this run
+            par ^= ((((uses + 1) >> 1) & 1) << b) ^ (((uses >> 1) & 1) << (b + NBUF));
+        }
         k += len;
     }
     TRACE_CTA(1);
