@@ -102,6 +102,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    orc.use_all_cores()
     log, blow, cols = args.log_size, LOG_BLOWUP, args.cpu_sample_cols
     root_init, root_log = orc.canonic_half_coset(log + blow)
     tw, itw = orc.precompute_twiddles(root_init, root_log)
@@ -130,6 +131,7 @@ def run_reference(args):
 def cpu_baseline(args):
     import numpy as np
     import oracle as orc
+    orc.use_all_cores()
     log, blow, cols = args.log_size, LOG_BLOWUP, args.cpu_sample_cols
     root_init, root_log = orc.canonic_half_coset(log + blow)
     tw, itw = orc.precompute_twiddles(root_init, root_log)

@@ -662,6 +662,15 @@ EXPORT int orc_lde_commit(const uint32_t *cols_in, int n_cols, int log_size, int
     }
     return 0;
 }
+/* torchrun exports OMP_NUM_THREADS=1 to its workers; the timed CPU baseline asks for the cores it may use explicitly. */
+EXPORT void orc_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
 EXPORT int orc_num_threads(void)
 {
 #ifdef _OPENMP
