@@ -63,6 +63,10 @@ int tstwo_upload(tstwo_dptr dst, const void *host, uint64_t bytes);      /* crea
 int tstwo_download(void *host, tstwo_dptr src, uint64_t bytes);          /* Column.toCpu() / at(i) */
 int tstwo_copy(tstwo_dptr dst, tstwo_dptr src, uint64_t bytes);
 int tstwo_bit_reverse(tstwo_dptr col, uint64_t len);                     /* ColumnOps.bitReverseColumn; len = #u32 */
+/* MerkleProver.decommit (vcs/prover.ts:32-109) and FRI's witness evaluations (fri.ts:346-384) read hashes and
+ * column values one index at a time; here the caller lists the device addresses (layer + 32 j, column + 4 i) and one
+ * launch gathers words_each consecutive u32 from each into host_out[n * words_each]. */
+int tstwo_gather_words(const tstwo_dptr *addrs, int n, int words_each, uint32_t *host_out);
 
 /* ---- PolyOps  (poly/circle/ops.ts:20-66; impl backend/cpu/circle.ts:17-239) -------------------------------- */
 /* precomputeTwiddles(coset): backend/cpu/circle.ts:210-239.  The tree holds 2^log words of twiddles+itwiddles. */

@@ -278,3 +278,150 @@ def use_all_cores() -> int:
     n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     lib().orc_set_num_threads(int(n))
     return num_threads()
+
+
+# ------------------------------------------------------------------------------------------------ Fiat-Shamir channel
+class Channel:
+    """CPU restatement of Blake2sChannel (core/src/channel/blake2.ts:25-224) and Blake2sMerkleChannel.mix_root
+    (core/src/vcs/blake2_merkle.ts:28-31) over the oracle's own BLAKE2s (orc_blake2s).  Pinned by the two digests the
+    reference's tests took from Stwo (core/test/channel/channel_exact_rust_tests.test.ts:97-118).  Test infrastructure only.
+
+    State: 32-byte digest (zeros at creation, blake2_hash.ts), ChannelTime (n_challenges, n_sent; every digest update
+    increments n_challenges and resets n_sent, channel/index.ts:97-104) and the queue of base-field draws that draw_felt
+    keeps between calls (blake2.ts:172-181; draw_felts uses a fresh local queue, :183-205)."""
+
+    P = 2147483647
+
+    def __init__(self):
+        self.digest = bytes(32)
+        self.n_challenges = 0
+        self.n_sent = 0
+        self.base_queue = []
+
+    def _update(self, new_digest: bytes):          # blake2.ts:75-79
+        self.digest = new_digest
+        self.n_challenges += 1
+        self.n_sent = 0
+
+    def mix_root(self, root: bytes):               # blake2_merkle.ts:29-31: H(digest || root)
+        self._update(blake2s(self.digest + bytes(root)))
+
+    def mix_felts(self, felts):                    # blake2.ts:113-118: H(digest || LE32 of every coordinate)
+        words = [int(w) for f in felts for w in f]
+        self._update(blake2s(self.digest + b"".join(int(w).to_bytes(4, "little") for w in words)))
+
+    def mix_u32s(self, data):                      # blake2.ts:120-137
+        self._update(blake2s(self.digest + b"".join(int(w).to_bytes(4, "little") for w in data)))
+
+    def mix_u64(self, value: int):                 # blake2.ts:139-151: low word first
+        self.mix_u32s([value & 0xFFFFFFFF, (value >> 32) & 0xFFFFFFFF])
+
+    def draw_random_bytes(self) -> bytes:          # blake2.ts:207-221: H(digest || LE32(n_sent) || 28 zero bytes)
+        out = blake2s(self.digest + self.n_sent.to_bytes(4, "little") + bytes(28))
+        self.n_sent += 1
+        return out
+
+    def _draw_base_felts(self):                    # blake2.ts:157-170: 8 words, retry unless all < 2P, then reduce
+        while True:
+            b = self.draw_random_bytes()
+            u = [int.from_bytes(b[4 * i:4 * i + 4], "little") for i in range(8)]
+            if all(x < 2 * self.P for x in u):
+                return [x % self.P for x in u]
+
+    def draw_felt(self):                           # blake2.ts:172-181
+        while len(self.base_queue) < 4:
+            self.base_queue += self._draw_base_felts()
+        out, self.base_queue = self.base_queue[:4], self.base_queue[4:]
+        return out
+
+    def draw_felts(self, n: int):                  # blake2.ts:183-205
+        out, queue = [], []
+        for _ in range(n):
+            while len(queue) < 4:
+                queue += self._draw_base_felts()
+            out.append(queue[:4]); queue = queue[4:]
+        return out
+
+    def trailing_zeros(self) -> int:               # blake2.ts:94-111: of the low 128 bits, little endian
+        v = int.from_bytes(self.digest[:16], "little")
+        return 128 if v == 0 else (v & -v).bit_length() - 1
+
+
+# ------------------------------------------------------------------------------------------------ Merkle decommit / verify
+def _next_node(last, pi, direct, di):
+    """nextDecommitmentNode, core/src/vcs/utils.ts:40-57."""
+    cand = []
+    if pi < len(last): cand.append(last[pi] // 2)
+    if di < len(direct): cand.append(direct[di])
+    return min(cand) if cand else None
+
+
+def merkle_decommit(layers, queries, cols):
+    """MerkleProver.decommit, core/src/vcs/prover.ts:32-109.  layers[k]: (2^k, 32) uint8 as returned by merkle_commit;
+    queries: {log_size: sorted positions}; cols: the committed columns.  Returns (queried, hash_witness, column_witness)."""
+    order = sorted(range(len(cols)), key=lambda i: -len(cols[i]))
+    queried, hash_w, col_w = [], [], []
+    ci, last = 0, []
+    for log in range(len(layers) - 1, -1, -1):
+        layer_cols = []
+        while ci < len(order) and len(cols[order[ci]]) == 1 << log:
+            layer_cols.append(cols[order[ci]]); ci += 1
+        child = layers[log + 1] if log + 1 < len(layers) else None
+        direct = list(queries.get(log, []))
+        pi = di = 0
+        nxt = []
+        while (node := _next_node(last, pi, direct, di)) is not None:
+            if child is not None:
+                for ch in (2 * node, 2 * node + 1):
+                    if pi < len(last) and last[pi] == ch: pi += 1
+                    else: hash_w.append(bytes(child[ch]))
+            vals = [int(c[node]) for c in layer_cols]
+            if di < len(direct) and direct[di] == node:
+                di += 1; queried += vals
+            else:
+                col_w += vals
+            nxt.append(node)
+        last = nxt
+    return queried, hash_w, col_w
+
+
+def merkle_verify(root: bytes, column_log_sizes, queries, queried, hash_w, col_w):
+    """MerkleVerifier.verify, core/src/vcs/verifier.ts:28-150, with Blake2sMerkleHasher.hashNode
+    (vcs/blake2_merkle.ts:9-24).  Raises ValueError with the reference's error names."""
+    if not column_log_sizes:
+        return
+    n_cols = {}
+    for l in column_log_sizes: n_cols[l] = n_cols.get(l, 0) + 1
+    qi = hi = wi = 0
+    last = None
+    for log in range(max(column_log_sizes), -1, -1):
+        prev_q = [q for q, _ in last] if last else []
+        direct = list(queries.get(log, []))
+        pi = di = 0       # pi walks prev_q for node selection, hp walks (index, hash) pairs for child look-up
+        hp = 0
+        cur = []
+        while (node := _next_node(prev_q, pi, direct, di)) is not None:
+            while pi < len(prev_q) and prev_q[pi] // 2 == node: pi += 1
+            msg = b""
+            if last is not None:
+                for ch in (2 * node, 2 * node + 1):
+                    if hp < len(last) and last[hp][0] == ch:
+                        msg += last[hp][1]; hp += 1
+                    else:
+                        if hi >= len(hash_w): raise ValueError("WitnessTooShort")
+                        msg += hash_w[hi]; hi += 1
+            from_q = di < len(direct) and direct[di] == node
+            if from_q: di += 1
+            for _ in range(n_cols.get(log, 0)):
+                if from_q:
+                    if qi >= len(queried): raise ValueError("TooFewQueriedValues")
+                    msg += int(queried[qi]).to_bytes(4, "little"); qi += 1
+                else:
+                    if wi >= len(col_w): raise ValueError("WitnessTooShort")
+                    msg += int(col_w[wi]).to_bytes(4, "little"); wi += 1
+            cur.append((node, blake2s(msg)))
+        last = cur
+    if hi != len(hash_w): raise ValueError("WitnessTooLong")
+    if qi != len(queried): raise ValueError("TooManyQueriedValues")
+    if wi != len(col_w): raise ValueError("WitnessTooLong")
+    if last[0][1] != bytes(root): raise ValueError("RootMismatch")

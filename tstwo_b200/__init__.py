@@ -2,9 +2,11 @@
 
 Layout: csrc/ (CUDA kernels + C ABI -> libtstwo_cuda.so), _lib.py (ctypes binding of include/tstwo_cuda.h),
 circle.py (host index arithmetic), backend.py (mirror of the reference's backend interfaces)."""
-from .backend import (CommitmentTreeProver, CudaBackend, CudaCircleEvaluation, CudaCirclePoly, CudaColumn, CudaFriOps,
+from .backend import (CommitmentSchemeProver, CommitmentTreeProver, FriConfig, MerkleDecommitment, PcsConfig, TreeBuilder, TreeSubspan,
+                      CudaBackend, CudaCircleEvaluation, CudaCirclePoly, CudaColumn, CudaFriOps,
                       CudaMerkleOps, LineEvaluation, MerkleProver, SecureColumnByCoords, SecureEvaluation, TwiddleTree,
                       accumulate, accumulate_quotients, fold_circle_into_line, fold_line)
+from .channel import Blake2sChannel, Blake2sMerkleChannel, ChannelTime
 from .circle import CanonicCoset, CircleDomain, CirclePointIndex, Coset, LineDomain
 from ._lib import TstwoError, TwiddleMismatch
 

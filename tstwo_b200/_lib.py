@@ -43,6 +43,7 @@ SIGNATURES = {
     "tstwo_memset_zero": (C.c_int, [dptr, C.c_uint64]),
     "tstwo_upload": (C.c_int, [dptr, C.c_void_p, C.c_uint64]),
     "tstwo_download": (C.c_int, [C.c_void_p, dptr, C.c_uint64]),
+    "tstwo_gather_words": (C.c_int, [C.POINTER(dptr), C.c_int, C.c_int, C.POINTER(C.c_uint32)]),
     "tstwo_copy": (C.c_int, [dptr, dptr, C.c_uint64]),
     "tstwo_bit_reverse": (C.c_int, [dptr, C.c_uint64]),
     "tstwo_twiddles_precompute": (C.c_int, [C.c_uint32, C.c_int, dptrp]),

@@ -24,6 +24,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import FLAG_QUIRKS, TstwoError, TwiddleMismatch, check, dptr_array, u32_array
+from .channel import Blake2sChannel, Blake2sMerkleChannel
 from .circle import CanonicCoset, CircleDomain, CirclePointIndex, Coset, LineDomain
 
 P = 2147483647
@@ -292,6 +293,66 @@ class MerkleProver:
     def layer_bytes(self, k: int) -> np.ndarray:
         return self.layers[k].toCpu().view(np.uint8).reshape(-1, 32)
 
+    def decommit(self, queriesPerLogSize, columns: Sequence[CudaColumn]):
+        """vcs/prover.ts:32-109: (queried values, MerkleDecommitment) for sorted query positions per column log size.
+        Which hashes and values go into the witness depends on the queries only, so the tree walk runs on the host and
+        the witness itself is collected from device memory by two gather launches (tstwo_gather_words)."""
+        cols = sorted(columns, key=lambda c: -c.len())          # stable, as Array.prototype.sort in the reference
+        col_i = 0
+        hash_addrs: List[int] = []                              # device address of every witness hash, in order
+        value_addrs: List[int] = []                             # ... of every column value, in node order
+        value_is_query: List[bool] = []
+        last: List[int] = []
+        for log in range(len(self.layers) - 1, -1, -1):
+            layer_cols = []
+            while col_i < len(cols) and cols[col_i].len() == 1 << log:
+                layer_cols.append(cols[col_i]); col_i += 1
+            child = self.layers[log + 1] if log + 1 < len(self.layers) else None
+            direct = list(queriesPerLogSize.get(log, ()) or ())
+            pi = di = 0
+            nxt: List[int] = []
+            while pi < len(last) or di < len(direct):
+                cand = []                                        # nextDecommitmentNode, vcs/utils.ts:40-57
+                if pi < len(last): cand.append(last[pi] >> 1)
+                if di < len(direct): cand.append(direct[di])
+                node = min(cand)
+                if child is not None:
+                    for ch in (2 * node, 2 * node + 1):
+                        if pi < len(last) and last[pi] == ch:
+                            pi += 1                              # the verifier recomputes this child itself
+                        else:
+                            if ch >= child.len() // 8:
+                                raise IndexError(f"MerkleProver.decommit: child {ch} is outside layer {log + 1}")
+                            hash_addrs.append(child.ptr + 32 * ch)
+                queried = di < len(direct) and direct[di] == node
+                if queried:
+                    di += 1
+                if node >= 1 << log:
+                    raise IndexError(f"MerkleProver.decommit: query {node} is outside layer {log}")
+                for c in layer_cols:
+                    value_addrs.append(c.ptr + 4 * node)
+                    value_is_query.append(queried)
+                nxt.append(node)
+            last = nxt
+        hashes = np.zeros((len(hash_addrs), 8), dtype=np.uint32)
+        values = np.zeros(len(value_addrs), dtype=np.uint32)
+        if hash_addrs:
+            check(_L().tstwo_gather_words(dptr_array(hash_addrs), len(hash_addrs), 8, hashes.ctypes.data_as(C.POINTER(C.c_uint32))))
+        if value_addrs:
+            check(_L().tstwo_gather_words(dptr_array(value_addrs), len(value_addrs), 1, values.ctypes.data_as(C.POINTER(C.c_uint32))))
+        mask = np.array(value_is_query, dtype=bool)
+        return values[mask], MerkleDecommitment([h.tobytes() for h in hashes], values[~mask])
+
+
+class MerkleDecommitment:
+    """vcs/verifier.ts:5-8."""
+
+    def __init__(self, hashWitness: List[bytes], columnWitness):
+        self.hashWitness = hashWitness
+        self.columnWitness = columnWitness
+    hash_witness = property(lambda self: self.hashWitness)
+    column_witness = property(lambda self: self.columnWitness)
+
 
 class LineEvaluation:
     """poly/line.ts:241-329 over device SecureColumnByCoords."""
@@ -482,14 +543,21 @@ class CommitmentTreeProver:
         self.commitment = commitment
 
     @staticmethod
-    def new(polynomials: Sequence[CudaCirclePoly], log_blowup_factor: int, twiddles: TwiddleTree) -> "CommitmentTreeProver":
+    def new(polynomials: Sequence[CudaCirclePoly], log_blowup_factor: int, twiddles: TwiddleTree, channel=None) -> "CommitmentTreeProver":
+        """`channel` (a Blake2sChannel) receives the root as in the Rust text (`MC::mix_root(channel, tree.root())`)."""
         evals = CudaBackend.evaluatePolynomials(polynomials, log_blowup_factor, twiddles)
         commitment = MerkleProver.commit(CudaBackend.merkleOps, [e.values for e in evals])
+        if channel is not None:
+            Blake2sMerkleChannel.mix_root(channel, commitment.root())
         return CommitmentTreeProver(list(polynomials), evals, commitment)
+
+    def decommit(self, queries):
+        """pcs/prover.ts:237-251 (Rust text): queried values and decommitment of this tree for {log size: positions}."""
+        return self.commitment.decommit(queries, [e.values for e in self.evaluations])
 
     @staticmethod
     def from_trace(trace: CudaColumn, n_cols: int, log_size: int, log_blowup_factor: int, twiddles: TwiddleTree,
-                   keep_coeffs: bool = True) -> "CommitmentTreeProver":
+                   keep_coeffs: bool = True, channel=None) -> "CommitmentTreeProver":
         ext = log_size + log_blowup_factor
         n, ne = 1 << log_size, 1 << ext
         if trace.len() != n_cols * n:
@@ -504,6 +572,84 @@ class CommitmentTreeProver:
         polys = [CudaCirclePoly(coeffs.slice(c * n, n)) for c in range(n_cols)] if coeffs else []
         evs = [CudaCircleEvaluation(dom, evals.slice(c * ne, ne)) for c in range(n_cols)]
         mp = MerkleProver([layers.slice(8 * ((1 << k) - 1), 8 << k) for k in range(ext + 1)], bytes(root))
+        if channel is not None:
+            Blake2sMerkleChannel.mix_root(channel, mp.root())
         return CommitmentTreeProver(polys, evs, mp)
 
     def root(self) -> bytes: return self.commitment.root()
+
+
+class FriConfig:
+    """fri.ts:35-70 (log_last_layer_degree_bound, log_blowup_factor, n_queries) with the reference's range checks."""
+    LOG_MIN_LAST_LAYER_DEGREE_BOUND, LOG_MAX_LAST_LAYER_DEGREE_BOUND = 0, 10
+    LOG_MIN_BLOWUP_FACTOR, LOG_MAX_BLOWUP_FACTOR = 1, 16
+
+    def __init__(self, log_last_layer_degree_bound: int, log_blowup_factor: int, n_queries: int):
+        if not self.LOG_MIN_LAST_LAYER_DEGREE_BOUND <= log_last_layer_degree_bound <= self.LOG_MAX_LAST_LAYER_DEGREE_BOUND:
+            raise ValueError("invalid log_last_layer_degree_bound")
+        if not self.LOG_MIN_BLOWUP_FACTOR <= log_blowup_factor <= self.LOG_MAX_BLOWUP_FACTOR:
+            raise ValueError("invalid log_blowup_factor")
+        self.log_last_layer_degree_bound = log_last_layer_degree_bound
+        self.log_blowup_factor = log_blowup_factor
+        self.n_queries = n_queries
+
+    def last_layer_domain_size(self) -> int:
+        return 1 << (self.log_last_layer_degree_bound + self.log_blowup_factor)
+
+
+class PcsConfig:
+    """pcs/index.ts: pow_bits + FriConfig."""
+
+    def __init__(self, pow_bits: int = 5, fri_config: Optional[FriConfig] = None):
+        self.pow_bits = pow_bits
+        self.fri_config = fri_config or FriConfig(0, 1, 3)
+
+
+class TreeSubspan:
+    def __init__(self, tree_index: int, col_start: int, col_end: int):
+        self.tree_index, self.col_start, self.col_end = tree_index, col_start, col_end
+
+    def __eq__(self, o): return (self.tree_index, self.col_start, self.col_end) == (o.tree_index, o.col_start, o.col_end)
+    def __repr__(self): return f"TreeSubspan({self.tree_index}, {self.col_start}, {self.col_end})"
+
+
+class TreeBuilder:
+    """pcs/prover.ts:170-213 (Rust text): collects the polynomials of one commitment tree."""
+
+    def __init__(self, scheme: "CommitmentSchemeProver"):
+        self.tree_index = len(scheme.trees)
+        self.commitment_scheme = scheme
+        self.polys: List[CudaCirclePoly] = []
+
+    def extend_evals(self, columns: Sequence[CudaCircleEvaluation]) -> TreeSubspan:
+        return self.extend_polys(CudaBackend.interpolateColumns(list(columns), self.commitment_scheme.twiddles))
+
+    def extend_polys(self, columns: Sequence[CudaCirclePoly]) -> TreeSubspan:
+        start = len(self.polys)
+        self.polys.extend(columns)
+        return TreeSubspan(self.tree_index, start, len(self.polys))
+
+    def commit(self, channel) -> None:
+        self.commitment_scheme._commit(self.polys, channel)
+
+
+class CommitmentSchemeProver:
+    """pcs/prover.ts:28-84 (Rust text; never ported by the reference): the trees committed so far, one
+    CommitmentTreeProver each, all on the same twiddle tree; every commit mixes its root into the channel."""
+
+    def __init__(self, config: PcsConfig, twiddles: TwiddleTree):
+        self.trees: List[CommitmentTreeProver] = []
+        self.config = config
+        self.twiddles = twiddles
+
+    def _commit(self, polynomials: Sequence[CudaCirclePoly], channel) -> None:
+        self.trees.append(CommitmentTreeProver.new(polynomials, self.config.fri_config.log_blowup_factor, self.twiddles, channel))
+
+    def tree_builder(self) -> TreeBuilder: return TreeBuilder(self)
+    def roots(self) -> List[bytes]: return [t.commitment.root() for t in self.trees]
+    def polynomials(self): return [list(t.polynomials) for t in self.trees]
+    def evaluations(self): return [list(t.evaluations) for t in self.trees]
+
+    def decommit(self, queries):
+        """The Merkle part of prove_values (pcs/prover.ts:139-146): per tree (queried values, decommitment)."""
+        return [t.decommit(queries) for t in self.trees]

@@ -245,6 +245,35 @@ int tstwo_copy(tstwo_dptr dst, tstwo_dptr src, uint64_t bytes)
     TS_CUDA(cudaMemcpyAsync((void *)dst, (const void *)src, bytes, cudaMemcpyDeviceToDevice, ctx().stream));
     return 0;
 }
+// gather for decommitments (vcs/prover.ts:32-109 reads childLayerHashes[j] and column[nodeIndex] one by one): the host
+// walks the query tree (it depends on the queries only, not on data), then ONE launch collects every witness word.
+__global__ void gather_words_kernel(const uint64_t *__restrict__ addrs, uint64_t total, int words, uint32_t *__restrict__ out)
+{
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= total) return;
+    out[t] = reinterpret_cast<const uint32_t *>(addrs[t / words])[t % words];
+}
+int tstwo_gather_words(const tstwo_dptr *addrs, int n, int words_each, uint32_t *host_out)
+{
+    TS_REQUIRE_INIT();
+    if (n < 0 || words_each <= 0 || words_each > 64 || (n && (!addrs || !host_out))) return fail(TSTWO_ERR_BAD_ARG, "bad gather arguments");
+    if (n == 0) return 0;
+    for (int k = 0; k < n; k++)
+        if (!addrs[k] || (addrs[k] & 3)) return fail(TSTWO_ERR_BAD_ARG, "gather address %d is null or not word aligned", k);
+    Context &c = ctx();
+    const uint64_t total = (uint64_t)n * words_each;
+    uint64_t *d_addrs = nullptr;
+    uint32_t *d_out = nullptr;
+    TS_CUDA(cudaMallocAsync(&d_addrs, sizeof(uint64_t) * n, c.stream));
+    TS_CUDA(cudaMallocAsync(&d_out, 4 * total, c.stream));
+    TS_CUDA(cudaMemcpyAsync(d_addrs, addrs, sizeof(uint64_t) * n, cudaMemcpyHostToDevice, c.stream));
+    TS_LAUNCH(gather_words_kernel, (unsigned)((total + 255) / 256), 256, 0, d_addrs, total, words_each, d_out);
+    TS_CUDA(cudaMemcpyAsync(host_out, d_out, 4 * total, cudaMemcpyDeviceToHost, c.stream));
+    TS_CUDA(cudaFreeAsync(d_addrs, c.stream));
+    TS_CUDA(cudaFreeAsync(d_out, c.stream));
+    TS_CUDA(cudaStreamSynchronize(c.stream));
+    return 0;
+}
 int tstwo_bit_reverse(tstwo_dptr col, uint64_t len)
 {
     TS_REQUIRE_INIT();
