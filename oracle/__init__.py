@@ -425,3 +425,106 @@ def merkle_verify(root: bytes, column_log_sizes, queries, queried, hash_w, col_w
     if qi != len(queried): raise ValueError("TooManyQueriedValues")
     if wi != len(col_w): raise ValueError("WitnessTooLong")
     if last[0][1] != bytes(root): raise ValueError("RootMismatch")
+
+
+# ------------------------------------------------------------------------------------------------ FRI commit / decommit flow
+def _bitrev_list(items):
+    n = len(items); log = n.bit_length() - 1
+    return [items[int(format(i, f"0{log}b")[::-1], 2) if log else 0] for i in range(n)]
+
+
+def line_interpolate(coset_init: int, log_size: int, coords):
+    """LineEvaluation.interpolate, core/src/poly/line.ts:311-328 with lineIfft :354-390: bit-reverse the evaluations, butterfly
+    layers with 1/x of the (repeatedly doubled) line domain, scale by 1/n.  Returns bit-reversed-order coefficients (n x 4)."""
+    Pm = 2147483647
+    n = 1 << log_size
+    vals = [_bitrev_list([int(v) for v in c]) for c in coords]
+    init, step, size = coset_init, subgroup_gen(log_size), n
+    while size > 1:
+        half = size // 2
+        inv = [pow(index_to_point(init + i * step)[0], Pm - 2, Pm) for i in range(half)]
+        for v in vals:
+            for start in range(0, n, size):
+                for i in range(half):
+                    a, b = v[start + i], v[start + i + half]
+                    v[start + i], v[start + i + half] = (a + b) % Pm, (a - b) * inv[i] % Pm
+        init, step, size = (2 * init) & 0x7FFFFFFF, (2 * step) & 0x7FFFFFFF, half      # Coset.double, circle.ts:268-276
+    n_inv = pow(n, Pm - 2, Pm)
+    return [[vals[k][i] * n_inv % Pm for k in range(4)] for i in range(n)]
+
+
+def fri_decommitment_positions(query_positions, fold_step):
+    """computeDecommitmentPositionsAndWitnessEvals (core/src/fri.ts:346-384), positions only: (all positions, witness positions)."""
+    positions, witness = [], []
+    i = 0
+    while i < len(query_positions):
+        coset = query_positions[i] >> fold_step
+        here = set()
+        while i < len(query_positions) and query_positions[i] >> fold_step == coset:
+            here.add(query_positions[i]); i += 1
+        for pos in range(coset << fold_step, (coset + 1) << fold_step):
+            positions.append(pos)
+            if pos not in here: witness.append(pos)
+    return positions, witness
+
+
+def fri_commit(channel: "Channel", log_last_layer_degree_bound: int, log_blowup: int, columns):
+    """FriProver.commit (core/src/fri.ts:645-754) with the placeholders filled in as in Stwo: first-layer tree over all coordinate
+    columns, mix_root, alpha = draw_felt, fold_circle_into_line; per inner layer: commit, mix_root, draw alpha, fold_line, fold in
+    the circle column whose folded size matches; last layer interpolated and mixed as felts.
+    columns: [(log_size, [4 coordinate arrays])] on canonic domains, strictly decreasing.  Returns a dict of everything a test
+    wants to compare."""
+    coord_cols = [c for _, col in columns for c in col]
+    first_layers = merkle_commit(coord_cols)
+    channel.mix_root(first_layers[0][0].tobytes())
+    alphas = [channel.draw_felt()]
+    first_log = columns[0][0] - 1
+    line_init, line_log = half_odds_index(first_log), first_log
+    zero = [np.zeros(1 << first_log, dtype=np.uint32) for _ in range(4)]
+    layer_eval = fold_circle_into_line(zero, columns[0][1], canonic_half_coset(columns[0][0])[0], alphas[0])
+    pending = list(columns[1:])
+    inner = []
+    last_size = 1 << (log_last_layer_degree_bound + log_blowup)
+    while len(layer_eval[0]) > last_size:
+        trees = merkle_commit(layer_eval)
+        channel.mix_root(trees[0][0].tobytes())
+        alpha = channel.draw_felt(); alphas.append(alpha)
+        inner.append({"evaluation": layer_eval, "layers": trees, "log": line_log})
+        layer_eval = fold_line(layer_eval, line_init, alpha)
+        line_init, line_log = (2 * line_init) & 0x7FFFFFFF, line_log - 1
+        if pending and (1 << pending[0][0]) >> 1 == len(layer_eval[0]):
+            log, col = pending.pop(0)
+            layer_eval = fold_circle_into_line(layer_eval, col, canonic_half_coset(log)[0], alpha)
+    assert not pending
+    assert len(layer_eval[0]) == last_size, "last layer domain size mismatch"
+    coeffs_br = line_interpolate(line_init, line_log, layer_eval)
+    ordered = _bitrev_list(coeffs_br)
+    bound = 1 << log_last_layer_degree_bound
+    if any(any(c) for c in ordered[bound:]):
+        raise ValueError("invalid degree")
+    last_poly = _bitrev_list(ordered[:bound])
+    channel.mix_felts(last_poly)
+    return {"columns": columns, "first_layers": first_layers, "inner": inner, "alphas": alphas, "last_poly": last_poly,
+            "last_eval": layer_eval}
+
+
+def fri_decommit_on_queries(state, positions, log_domain_size):
+    """FriProver.decommitOnQueries (core/src/fri.ts:769-785) with the first/inner layer decommit of Stwo in place of the TS
+    placeholders (:509-541).  Returns [(fri_witness, (queried, hash_witness, column_witness), root)] first layer first."""
+    fold = lambda pos, k: sorted({p >> k for p in pos})
+    out = []
+    by_log, witness = {}, []
+    for log, col in state["columns"]:
+        col_q = fold(positions, log_domain_size - log)
+        pos, wit = fri_decommitment_positions(col_q, 1)
+        by_log[log] = pos
+        witness += [[int(c[p]) for c in col] for p in wit]
+    coord_cols = [c for _, col in state["columns"] for c in col]
+    out.append((witness, merkle_decommit(state["first_layers"], by_log, coord_cols), state["first_layers"][0][0].tobytes()))
+    q = fold(positions, 1)
+    for layer in state["inner"]:
+        pos, wit = fri_decommitment_positions(q, 1)
+        w = [[int(c[p]) for c in layer["evaluation"]] for p in wit]
+        out.append((w, merkle_decommit(layer["layers"], {layer["log"]: pos}, layer["evaluation"]), layer["layers"][0][0].tobytes()))
+        q = fold(q, 1)
+    return out

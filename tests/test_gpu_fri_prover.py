@@ -1,0 +1,90 @@
+"""FriProver.commit / decommit on the device (tstwo_b200/fri.py) against the oracle's restatement of the same flow:
+layer roots, folding alphas (through the shared transcript), last-layer polynomial, FRI witnesses and Merkle
+decommitments; every layer's decommitment is then checked with the oracle's MerkleVerifier.  The polynomial inputs are
+low degree so that the last-layer degree check (core/src/fri.ts:733-748) is exercised for real."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+P = 2147483647
+
+
+@pytest.fixture(scope="module")
+def tb():
+    import tstwo_b200
+    return tstwo_b200
+
+
+def secure_column_of_degree(tb, orc, log_degree, log_blowup, seed):
+    """4 coordinate polynomials with 2^log_degree coefficients, evaluated on CanonicCoset(log_degree + log_blowup)."""
+    rng = np.random.default_rng(seed)
+    log = log_degree + log_blowup
+    root_init, root_log = orc.canonic_half_coset(log)
+    tw, _ = orc.precompute_twiddles(root_init, root_log)
+    coords = []
+    for _ in range(4):
+        coeffs = rng.integers(0, P, 1 << log_degree, dtype=np.uint32)
+        coords.append(orc.evaluate(coeffs, log, root_init, (root_init, root_log), tw))
+    return log, coords
+
+
+@pytest.mark.parametrize("log_degrees,log_last,blow,n_queries", [((6,), 0, 1, 3), ((8, 6, 5), 2, 1, 5), ((7, 4), 0, 2, 4), ((10,), 3, 1, 8)])
+def test_fri_commit_and_decommit(tb, orc, log_degrees, log_last, blow, n_queries):
+    from tstwo_b200.channel import Blake2sChannel
+    from tstwo_b200.fri import FriProver, Queries
+    cols = [secure_column_of_degree(tb, orc, d, blow, 100 * d + blow) for d in log_degrees]
+    channel, ochannel = Blake2sChannel.create(), orc.Channel()
+    channel.mix_u64(42); ochannel.mix_u64(42)
+    dev_cols = [tb.SecureEvaluation(tb.CanonicCoset.new(log).circleDomain(), tb.SecureColumnByCoords.from_cpu(c)) for log, c in cols]
+    config = tb.FriConfig(log_last, blow, n_queries)
+    prover = FriProver.commit(channel, config, dev_cols)
+    state = orc.fri_commit(ochannel, log_last, blow, cols)
+    assert prover.first_layer.merkle_tree.root() == state["first_layers"][0][0].tobytes()
+    assert len(prover.inner_layers) == len(state["inner"]) == log_degrees[0] + blow - 1 - (log_last + blow)
+    for layer, ol in zip(prover.inner_layers, state["inner"]):
+        assert layer.merkle_tree.root() == ol["layers"][0][0].tobytes()
+        assert all((a == b).all() for a, b in zip(layer.evaluation.values.to_cpu(), ol["evaluation"]))
+    assert prover.last_layer_poly.coeffs == state["last_poly"] and len(prover.last_layer_poly) == 1 << log_last
+    assert channel.digest() == ochannel.digest
+
+    # decommit: queries from the transcript, proof layer by layer
+    proof, by_log = prover.decommit(channel)
+    max_log = cols[0][0]
+    oq = Queries.generate(ochannel, max_log, n_queries)
+    assert by_log == {log: oq.fold(max_log - log).positions for log, _ in cols}
+    exp = orc.fri_decommit_on_queries(state, oq.positions, max_log)
+    got = [proof.first_layer] + proof.inner_layers
+    assert len(got) == len(exp)
+    for g, (w, (queried, hw, cw), root) in zip(got, exp):
+        assert g.fri_witness == w and g.commitment == root
+        assert g.decommitment.hashWitness == hw and list(g.decommitment.columnWitness) == cw
+    # every layer's decommitment verifies against its root
+    pos_by_log = {}
+    for log, _ in cols:
+        pos_by_log[log] = orc.fri_decommitment_positions(oq.fold(max_log - log).positions, 1)[0]
+    first_logs = [log for log, _ in cols for _ in range(4)]
+    queried, hw, cw = exp[0][1]
+    orc.merkle_verify(exp[0][2], first_logs, pos_by_log, queried, hw, cw)
+    q = oq.fold(1).positions
+    for ol, (w, (queried, hw, cw), root) in zip(state["inner"], exp[1:]):
+        pos = orc.fri_decommitment_positions(q, 1)[0]
+        orc.merkle_verify(root, [ol["log"]] * 4, {ol["log"]: pos}, queried, hw, cw)
+        q = sorted({p >> 1 for p in q})
+
+
+def test_fri_rejects_high_degree_and_bad_inputs(tb, orc):
+    from tstwo_b200.channel import Blake2sChannel
+    from tstwo_b200.fri import FriProver
+    log, coords = secure_column_of_degree(tb, orc, 6, 1, 1)
+    col = tb.SecureEvaluation(tb.CanonicCoset.new(log).circleDomain(), tb.SecureColumnByCoords.from_cpu(coords))
+    with pytest.raises(ValueError, match="no columns"):
+        FriProver.commit(Blake2sChannel.create(), tb.FriConfig(0, 1, 3), [])
+    with pytest.raises(ValueError, match="column sizes not decreasing"):
+        FriProver.commit(Blake2sChannel.create(), tb.FriConfig(0, 1, 3), [col, col])
+    # a column of degree 2^6 committed as if it had degree 2^5 (blow-up 2 on a 2^7 domain): last layer must reject
+    with pytest.raises(ValueError, match="invalid degree"):
+        FriProver.commit(Blake2sChannel.create(), tb.FriConfig(0, 2, 3), [col])
+    rnd = np.random.default_rng(3).integers(0, P, (4, 1 << 7), dtype=np.uint32)
+    bad = tb.SecureEvaluation(tb.CanonicCoset.new(7).circleDomain(), tb.SecureColumnByCoords.from_cpu(list(rnd)))
+    with pytest.raises(ValueError, match="invalid degree"):
+        FriProver.commit(Blake2sChannel.create(), tb.FriConfig(0, 1, 3), [bad])
