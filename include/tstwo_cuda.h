@@ -94,6 +94,9 @@ int tstwo_merkle_commit_layer(int log_size, tstwo_dptr prev_layer, const tstwo_d
 /* MerkleProver.commit (vcs/prover.ts:13-30): all layers, root first: layer k (2^k hashes) at byte offset
  * 32*(2^k-1) of `layers` ((2^(max_log+1)-1)*32 bytes).  root[32] is copied to the host (synchronises). */
 int tstwo_merkle_commit(const tstwo_dptr *cols, const int *col_logs, int n_cols, tstwo_dptr layers, uint8_t root[32]);
+/* GrindOps.grind (backend/cpu/grind.ts:31-42; Backend.grind, backend/index.ts): smallest nonce such that the Blake2sChannel
+ * digest after mix_u64(nonce) has >= pow_bits trailing zero bits (channel/blake2.ts:94-111,139-151). */
+int tstwo_grind(const uint8_t digest[32], uint32_t pow_bits, uint64_t *nonce);
 
 /* ---- FriOps  (fri.ts:93-110, :120-192; impl backend/cpu/fri.ts:23-164) -------------------------------------- */
 /* tw may be 0: the twiddles are then derived from the coset on the fly. */
@@ -111,6 +114,13 @@ int tstwo_accumulate_quotients(int log_size, uint32_t half_coset_initial_index, 
                                const uint32_t random_coeff[4], int n_batches, const uint32_t *points,
                                const int *batch_offsets, const int *col_index, const uint32_t *values,
                                const tstwo_dptr out[4]);
+/* Same with flags: TSTWO_FLAG_QUIRKS = the denominators exactly as backend/cpu/quotients.ts:160-178 computes them (from the M31
+ * parts of the sample point only; what the function above does), 0 = Stwo's CM31 denominators (pcs/quotients.ts Rust text,
+ * `denominator_inverses`), the ones for which the quotients are low degree and FRI accepts them. */
+int tstwo_accumulate_quotients_ex(int log_size, uint32_t half_coset_initial_index, const tstwo_dptr *cols, int n_cols,
+                                  const uint32_t random_coeff[4], int n_batches, const uint32_t *points,
+                                  const int *batch_offsets, const int *col_index, const uint32_t *values,
+                                  const tstwo_dptr out[4], uint32_t flags);
 
 /* ---- the metric path in one call: Stwo's CommitmentTreeProver::new (quoted at pcs/prover.ts:215-235) -------- */
 /* interpolate n_cols trace columns on CanonicCoset(log_size), evaluate on CanonicCoset(log_size+log_blowup),

@@ -229,8 +229,9 @@ def generate_secure_powers(felt, n: int):
     return out[:4 * n].reshape(n, 4)
 
 
-def accumulate_quotients(log_size: int, half_init: int, cols, random_coeff, batches):
-    """batches: list of (point=(px[4], py[4]), [(col_index, value[4]), ...])."""
+def accumulate_quotients(log_size: int, half_init: int, cols, random_coeff, batches, ts_denominators: bool = True):
+    """batches: list of (point=(px[4], py[4]), [(col_index, value[4]), ...]).  ts_denominators=False: Stwo's CM31 denominators."""
+    lib().orc_set_quotient_ts_denominators(1 if ts_denominators else 0)
     cols = [_u32(c) for c in cols]
     arr = (u32p * len(cols))(*[_p(c) for c in cols])
     pts = _u32([list(b[0][0]) + list(b[0][1]) for b in batches]).reshape(-1)
@@ -528,3 +529,14 @@ def fri_decommit_on_queries(state, positions, log_domain_size):
         out.append((w, merkle_decommit(layer["layers"], {layer["log"]: pos}, layer["evaluation"]), layer["layers"][0][0].tobytes()))
         q = fold(q, 1)
     return out
+
+
+def grind(channel: "Channel", pow_bits: int) -> int:
+    """GrindOps.grind, core/src/backend/cpu/grind.ts:31-42: clone, mix_u64(nonce), trailing_zeros() >= powBits, else nonce += 1."""
+    nonce = 0
+    while True:
+        c = Channel(); c.digest = channel.digest
+        c.mix_u64(nonce)
+        if c.trailing_zeros() >= pow_bits:
+            return nonce
+        nonce += 1

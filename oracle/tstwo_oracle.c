@@ -578,6 +578,10 @@ EXPORT void orc_generate_secure_powers(const uint32_t *felt4, int n, uint32_t *o
  * Batches are flattened: batch b has point (px,py: 8 words at points[8b]) and entries
  * [batch_offsets[b], batch_offsets[b+1]) of (col_index[], values[4*]).  Follows the TS code, including its
  * divergence from Stwo: denominatorInverses uses only the M31 parts c0.real / c0.imag (quotients.ts:160-178). */
+static int g_quotient_ts_denominators = 1;
+/* 1 (default): denominators as the TS code computes them; 0: Stwo's CM31 denominators (Rust `denominator_inverses`:
+ * (Re(p.x) - d.x) * Im(p.y) - (Re(p.y) - d.y) * Im(p.x) over the CM31 halves of the sample point), for which quotients are low degree. */
+EXPORT void orc_set_quotient_ts_denominators(int on) { g_quotient_ts_denominators = on; }
 EXPORT int orc_accumulate_quotients(int log_size, uint32_t half_init, const uint32_t *const *cols, int n_cols,
                                     const uint32_t *random_coeff4, int n_batches, const uint32_t *points,
                                     const int *batch_offsets, const int *col_index, const uint32_t *values,
@@ -597,8 +601,12 @@ EXPORT int orc_accumulate_quotients(int log_size, uint32_t half_init, const uint
             alpha = qm_mul(alpha, rc);               /* quotients.ts:124-139 columnLineCoeffs */
             pw = qm_mul(pw, rc);
             qm31 v = qm_ld(values + 4 * j);
-            qm31 a = qm_sub(qm_conj(v), v);          /* constraints.ts:117-129 complexConjugateLineCoeffs */
-            qm31 c = qm_sub(qm_conj(py), py);
+            /* constraints.ts:117-129 complexConjugateLineCoeffs; the TS QM31.complexConjugate conjugates both CM31 halves
+             * (qm31.ts:433-435) where Stwo maps u -> -u, i.e. (c0, -c1) */
+            qm31 cv = g_quotient_ts_denominators ? qm_conj(v) : qm(v.c0.re, v.c0.im, m31_neg(v.c1.re), m31_neg(v.c1.im));
+            qm31 cpy = g_quotient_ts_denominators ? qm_conj(py) : qm(py.c0.re, py.c0.im, m31_neg(py.c1.re), m31_neg(py.c1.im));
+            qm31 a = qm_sub(cv, v);
+            qm31 c = qm_sub(cpy, py);
             qm31 bb = qm_sub(qm_mul(v, c), qm_mul(a, py));
             la[j] = qm_mul(alpha, a); lb[j] = qm_mul(alpha, bb); lc[j] = qm_mul(alpha, c);
         }
@@ -615,6 +623,10 @@ EXPORT int orc_accumulate_quotients(int log_size, uint32_t half_init, const uint
             m31 prx = pt[0], pix = pt[1], pry = pt[4], piy = pt[5];
             m31 den = m31_sub(m31_mul(m31_sub(prx, dp.x), piy), m31_mul(m31_sub(pry, dp.y), pix));
             cm31 den_inv = cm(m31_inv(den), 0);
+            if (!g_quotient_ts_denominators) {
+                cm31 rx = cm(m31_sub(pt[0], dp.x), pt[1]), ix = cm(pt[2], pt[3]), ry = cm(m31_sub(pt[4], dp.y), pt[5]), iy = cm(pt[6], pt[7]);
+                den_inv = cm_inv(cm_sub(cm_mul(rx, iy), cm_mul(ry, ix)));
+            }
             qm31 num = qm(0, 0, 0, 0);
             for (int j = batch_offsets[b]; j < batch_offsets[b + 1]; j++) {
                 qm31 value = qm_mul(qm_from_m31(cols[col_index[j]][row]), lc[j]);

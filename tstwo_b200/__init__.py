@@ -10,6 +10,7 @@ from .backend import (CommitmentSchemeProver, CommitmentTreeProver, FriConfig, M
 from .channel import Blake2sChannel, Blake2sMerkleChannel, ChannelTime
 from .circle import CanonicCoset, CircleDomain, CirclePointIndex, Coset, LineDomain
 from .fri import FriLayerProof, FriProof, FriProver, LinePoly, Queries
+from .pcs import ColumnSampleBatch, CommitmentSchemeProof, PointSample, compute_fri_quotients, grind
 from ._lib import TstwoError, TwiddleMismatch
 
 __all__ = [n for n in dir() if not n.startswith("_")]

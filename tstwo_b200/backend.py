@@ -433,8 +433,10 @@ def accumulate(column: SecureColumnByCoords, other: SecureColumnByCoords) -> Non
 
 
 def accumulate_quotients(domain: CircleDomain, columns: Sequence[CudaCircleEvaluation], random_coeff, sample_batches,
-                         log_blowup_factor: int = 1) -> SecureEvaluation:
-    """backend/cpu/quotients.ts:52-75.  sample_batches: [(point=(x[4], y[4]), [(column_index, value[4]), ...]), ...]"""
+                         log_blowup_factor: int = 1, ts_denominators: bool = True) -> SecureEvaluation:
+    """backend/cpu/quotients.ts:52-75.  sample_batches: [(point=(x[4], y[4]), [(column_index, value[4]), ...]), ...]
+    ts_denominators: True = bit-exact with the TS CpuBackend (denominators from the M31 parts of the point only, quotients.ts:
+    160-178); False = Stwo's CM31 denominators, the only ones for which the result is a low-degree quotient."""
     pts, offs, ci, vals = [], [0], [], []
     for point, entries in sample_batches:
         pts += list(point[0]) + list(point[1])
@@ -442,10 +444,11 @@ def accumulate_quotients(domain: CircleDomain, columns: Sequence[CudaCircleEvalu
             ci.append(int(col)); vals += list(v)
         offs.append(len(ci))
     out = SecureColumnByCoords.uninitialized(domain.size())
-    check(_L().tstwo_accumulate_quotients(domain.logSize(), domain.halfCoset.initial_index.value,
-                                          dptr_array([c.values.ptr for c in columns]), len(columns), u32_array(random_coeff),
-                                          len(sample_batches), u32_array(pts), (C.c_int * len(offs))(*offs),
-                                          (C.c_int * max(1, len(ci)))(*ci), u32_array(vals), out.ptrs()))
+    check(_L().tstwo_accumulate_quotients_ex(domain.logSize(), domain.halfCoset.initial_index.value,
+                                             dptr_array([c.values.ptr for c in columns]), len(columns), u32_array(random_coeff),
+                                             len(sample_batches), u32_array(pts), (C.c_int * len(offs))(*offs),
+                                             (C.c_int * max(1, len(ci)))(*ci), u32_array(vals), out.ptrs(),
+                                             FLAG_QUIRKS if ts_denominators else 0))
     return SecureEvaluation(domain, out)
 
 

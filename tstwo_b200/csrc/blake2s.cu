@@ -191,6 +191,30 @@ __global__ void __launch_bounds__(LEAF_ROWS, 5) merkle_leaf_tma_kernel(const __g
     out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
 }
 
+// ---- proof-of-work grind (backend/cpu/grind.ts:31-42): the smallest nonce for which the channel digest after
+// mix_u64(nonce) -- BLAKE2s(digest || LE32(lo) || LE32(hi)), one 40-byte block (channel/blake2.ts:120-151) -- has at least
+// pow_bits trailing zero bits in its low 128 bits (:94-111).  Every thread tries nonces base + k * stride; a batch covers a
+// contiguous range, so the minimum over the first batch with a hit is the nonce the sequential search returns.
+__global__ void __launch_bounds__(256) grind_kernel(const uint32_t *__restrict__ digest, uint32_t pow_bits, uint64_t base, int iters,
+                                                    unsigned long long *__restrict__ best, uint32_t one)
+{
+    uint32_t m[16];
+#pragma unroll
+    for (int k = 0; k < 8; k++) m[k] = digest[k];
+#pragma unroll
+    for (int k = 10; k < 16; k++) m[k] = 0;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    uint64_t nonce = base + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (int it = 0; it < iters; it++, nonce += stride) {
+        uint32_t h[8];
+        b2s_init(h);
+        m[8] = (uint32_t)nonce; m[9] = (uint32_t)(nonce >> 32);
+        b2s_compress(h, m, 40u, true, one);
+        const uint32_t tz = h[0] ? __ffs(h[0]) - 1 : h[1] ? 32 + __ffs(h[1]) - 1 : h[2] ? 64 + __ffs(h[2]) - 1 : h[3] ? 96 + __ffs(h[3]) - 1 : 128;
+        if (tz >= pow_bits) atomicMin(best, (unsigned long long)nonce);
+    }
+}
+
 static int g_leaf_mode = 1;    // 1: bulk-copy-fed leaf kernel where it applies; 0: merkle_layer_kernel always (tstwo_debug_set_leaf_mode)
 static int g_last_leaf = -1;
 
@@ -282,6 +306,36 @@ extern "C" {
 
 int tstwo_debug_set_leaf_mode(int mode) { g_leaf_mode = mode; return 0; }
 int tstwo_debug_last_leaf_mode(void) { return g_last_leaf; }
+
+int tstwo_grind(const uint8_t digest[32], uint32_t pow_bits, uint64_t *nonce)
+{
+    TS_REQUIRE_INIT();
+    if (!digest || !nonce || pow_bits > 64) return fail(TSTWO_ERR_BAD_ARG, "bad grind arguments (pow_bits <= 64)");
+    Context &c = ctx();
+    uint32_t *d_digest = nullptr;
+    unsigned long long *d_best = nullptr, best = ~0ull;
+    TS_CUDA(cudaMallocAsync(&d_digest, 32, c.stream));
+    TS_CUDA(cudaMallocAsync(&d_best, 8, c.stream));
+    TS_CUDA(cudaMemcpyAsync(d_digest, digest, 32, cudaMemcpyHostToDevice, c.stream));
+    TS_CUDA(cudaMemcpyAsync(d_best, &best, 8, cudaMemcpyHostToDevice, c.stream));
+    const unsigned grid = 148 * 8;
+    uint64_t base = 0;
+    // first batch small (most proofs use few bits), then 2^25 nonces per launch (~1.3 ms)
+    for (int iters = 1;; iters = 64) {
+        TS_LAUNCH(grind_kernel, grid, 256, 0, d_digest, pow_bits, base, iters, d_best, 1u);
+        TS_CUDA(cudaMemcpyAsync(&best, d_best, 8, cudaMemcpyDeviceToHost, c.stream));
+        TS_CUDA(cudaStreamSynchronize(c.stream));
+        if (best != ~0ull) break;
+        const uint64_t step = (uint64_t)grid * 256 * iters;
+        if (base + step < base) { best = ~0ull; break; }
+        base += step;
+    }
+    TS_CUDA(cudaFreeAsync(d_digest, c.stream));
+    TS_CUDA(cudaFreeAsync(d_best, c.stream));
+    if (best == ~0ull) return fail(TSTWO_ERR_BAD_ARG, "no nonce with %u trailing zero bits", pow_bits);
+    *nonce = best;
+    return 0;
+}
 
 int tstwo_merkle_commit_layer(int log_size, tstwo_dptr prev_layer, const tstwo_dptr *cols, int n_cols, tstwo_dptr out_layer)
 {

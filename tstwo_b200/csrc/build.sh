@@ -17,5 +17,5 @@ for p in "${pids[@]}"; do wait $p; done
 $NVCC -gencode arch=compute_100a,code=sm_100a -shared -ccbin /usr/bin/g++ -o $OUT _obj/*.o -lcudart
 # SASS peephole on the BLAKE2s kernels: IMAD Rd, Ra, R_one, Rc -> IMAD.IADD Rd, Ra, 0x1, Rc (same value since one == 1; two
 # register reads instead of three: 1560 -> 1345 clk per warp-compression, profiles/r01_microbench_blake2s_forms.txt)
-${PYTHON:-python3} ../../scripts/sass_imad_iadd.py $OUT merkle_layer_kernel merkle_leaf_tma_kernel merkle_leaf_absorb_kernel
+${PYTHON:-python3} ../../scripts/sass_imad_iadd.py $OUT grind_kernel merkle_layer_kernel merkle_leaf_tma_kernel merkle_leaf_absorb_kernel
 echo "built $OUT"

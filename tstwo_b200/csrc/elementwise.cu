@@ -108,8 +108,11 @@ __global__ void accumulate_kernel(Q4 dst, CQ4 src, uint64_t n)
 }
 
 // backend/cpu/quotients.ts:52-116.  consts: per entry j three QM31 (a, b, c) at consts[12j..], per batch b the
-// batch coefficient at bcoef[4b..] and the sample point's (prx, pix, pry, piy) = (x.c0.re, x.c0.im, y.c0.re, y.c0.im)
-// at pts[4b..] (the TS denominator uses only these M31 parts, quotients.ts:160-178).
+// batch coefficient at bcoef[4b..] and the sample point (x[4], y[4]) at pts[8b..].  TS_DENOM: the denominator as the TS code
+// computes it, from the M31 parts x.c0.re, x.c0.im, y.c0.re, y.c0.im only (quotients.ts:160-178) -- bit-exact with CpuBackend but
+// not a quotient by the line through the point and its conjugate; otherwise Stwo's CM31 denominator
+// (Re(p.x) - d.x) Im(p.y) - (Re(p.y) - d.y) Im(p.x) with Re/Im the CM31 halves, which is what makes the quotient low degree.
+template <bool TS_DENOM>
 __global__ void quotients_kernel(int log_size, uint32_t half_init, ColSet cols, int n_batches, const uint32_t *consts,
                                  const uint32_t *bcoef, const uint32_t *pts, const int *offsets, const int *col_index, Q4 out)
 {
@@ -118,9 +121,17 @@ __global__ void quotients_kernel(int log_size, uint32_t half_init, ColSet cols, 
     m31::Pt dp = index_to_point(domain_index_at(half_init, log_size - 1, m31::bitrev((uint32_t)row, log_size)));
     m31::QM acc = { 0, 0, 0, 0 };
     for (int b = 0; b < n_batches; b++) {
-        const uint32_t prx = pts[4 * b], pix = pts[4 * b + 1], pry = pts[4 * b + 2], piy = pts[4 * b + 3];
-        uint32_t den = m31::sub(m31::mul(m31::sub(prx, dp.x), piy), m31::mul(m31::sub(pry, dp.y), pix));
-        uint32_t den_inv = m31::inv(den);
+        const uint32_t *pt = pts + 8 * b;
+        m31::CM den_inv;
+        if (TS_DENOM) {
+            const uint32_t prx = pt[0], pix = pt[1], pry = pt[4], piy = pt[5];
+            den_inv = { m31::inv(m31::sub(m31::mul(m31::sub(prx, dp.x), piy), m31::mul(m31::sub(pry, dp.y), pix))), 0 };
+        } else {
+            const m31::CM prx = { m31::sub(pt[0], dp.x), pt[1] }, pix = { pt[2], pt[3] }, pry = { m31::sub(pt[4], dp.y), pt[5] }, piy = { pt[6], pt[7] };
+            const m31::CM den = m31::csub2(m31::cmul(prx, piy), m31::cmul(pry, pix));
+            const uint32_t norm_inv = m31::inv(m31::add(m31::mul(den.re, den.re), m31::mul(den.im, den.im)));
+            den_inv = { m31::mul(den.re, norm_inv), m31::mul(m31::sub(0, den.im), norm_inv) };
+        }
         m31::QM num = { 0, 0, 0, 0 };
         for (int j = offsets[b]; j < offsets[b + 1]; j++) {
             const uint32_t *k = consts + 12 * j;
@@ -131,7 +142,7 @@ __global__ void quotients_kernel(int log_size, uint32_t half_init, ColSet cols, 
             num = m31::qadd(num, m31::qsub(value, lin));
         }
         m31::QM bc = { bcoef[4 * b], bcoef[4 * b + 1], bcoef[4 * b + 2], bcoef[4 * b + 3] };
-        acc = m31::qadd(m31::qmul(acc, bc), m31::qmul_m(num, den_inv));
+        acc = m31::qadd(m31::qmul(acc, bc), m31::qmul_cm(num, den_inv));
     }
     out.c[0][row] = acc.a; out.c[1][row] = acc.b; out.c[2][row] = acc.c; out.c[3][row] = acc.d;
 }
@@ -303,13 +314,22 @@ int tstwo_accumulate_quotients(int log_size, uint32_t half_init, const tstwo_dpt
                                int n_batches, const uint32_t *points, const int *batch_offsets, const int *col_index,
                                const uint32_t *values, const tstwo_dptr out[4])
 {
+    return tstwo_accumulate_quotients_ex(log_size, half_init, cols, n_cols, rc4, n_batches, points, batch_offsets, col_index, values, out,
+                                         TSTWO_FLAG_QUIRKS);
+}
+
+int tstwo_accumulate_quotients_ex(int log_size, uint32_t half_init, const tstwo_dptr *cols, int n_cols, const uint32_t rc4[4],
+                                  int n_batches, const uint32_t *points, const int *batch_offsets, const int *col_index,
+                                  const uint32_t *values, const tstwo_dptr out[4], uint32_t flags)
+{
     TS_REQUIRE_INIT();
     if (log_size < 1 || log_size > 30 || n_batches < 0) return fail(TSTWO_ERR_BAD_ARG, "bad quotient arguments");
     const int total = n_batches ? batch_offsets[n_batches] : 0;
     for (int j = 0; j < total; j++)
         if (col_index[j] < 0 || col_index[j] >= n_cols) return fail(TSTWO_ERR_BAD_ARG, "column index %d out of range", col_index[j]);
     // quotientConstants (quotients.ts:124-152, constraints.ts:117-129) on the host
-    std::vector<uint32_t> consts((size_t)total * 12 + 4), bcoef((size_t)n_batches * 4 + 4), pts((size_t)n_batches * 4 + 4);
+    const bool ts_quirks = (flags & TSTWO_FLAG_QUIRKS) != 0;
+    std::vector<uint32_t> consts((size_t)total * 12 + 4), bcoef((size_t)n_batches * 4 + 4), pts((size_t)n_batches * 8 + 8);
     host::QM rc = host::qld(rc4);
     for (int b = 0; b < n_batches; b++) {
         host::QM px = host::qld(points + 8 * b), py = host::qld(points + 8 * b + 4);
@@ -317,15 +337,17 @@ int tstwo_accumulate_quotients(int log_size, uint32_t half_init, const tstwo_dpt
         for (int j = batch_offsets[b]; j < batch_offsets[b + 1]; j++) {
             alpha = host::qmul(alpha, rc);
             host::QM v = host::qld(values + 4 * j);
-            host::QM a = host::qsub(host::qconj(v), v);
-            host::QM c = host::qsub(host::qconj(py), py);
+            // TS: QM31.complexConjugate conjugates both CM31 halves (qm31.ts:433-435); Stwo: u -> -u, i.e. (c0, -c1)
+            auto conj = [&](host::QM q) { return ts_quirks ? host::qconj(q) : host::QM{ q.a, q.b, host::neg(q.c), host::neg(q.d) }; };
+            host::QM a = host::qsub(conj(v), v);
+            host::QM c = host::qsub(conj(py), py);
             host::QM bb = host::qsub(host::qmul(v, c), host::qmul(a, py));
             host::qst(&consts[12 * j], host::qmul(alpha, a));
             host::qst(&consts[12 * j + 4], host::qmul(alpha, bb));
             host::qst(&consts[12 * j + 8], host::qmul(alpha, c));
         }
         host::qst(&bcoef[4 * b], alpha);   // random_coeff ^ len
-        pts[4 * b] = px.a; pts[4 * b + 1] = px.b; pts[4 * b + 2] = py.a; pts[4 * b + 3] = py.b;
+        for (int k = 0; k < 8; k++) pts[8 * b + k] = points[8 * b + k];
     }
     size_t w_consts = consts.size(), w_bc = bcoef.size(), w_pts = pts.size(), w_off = (size_t)n_batches + 1, w_ci = (size_t)total + 1;
     uint32_t *tmp;
@@ -345,8 +367,12 @@ int tstwo_accumulate_quotients(int log_size, uint32_t half_init, const tstwo_dpt
     Q4 o;
     for (int k = 0; k < 4; k++) o.c[k] = (uint32_t *)out[k];
     const uint64_t n = 1ull << log_size;
-    TS_LAUNCH(quotients_kernel, (unsigned)((n + 127) / 128), 128, 0, log_size, half_init & 0x7fffffffu, cs, n_batches, d_consts,
-              d_bc, d_pts, d_off, d_ci, o);
+    if (flags & TSTWO_FLAG_QUIRKS)
+        TS_LAUNCH(quotients_kernel<true>, (unsigned)((n + 127) / 128), 128, 0, log_size, half_init & 0x7fffffffu, cs, n_batches, d_consts,
+                  d_bc, d_pts, d_off, d_ci, o);
+    else
+        TS_LAUNCH(quotients_kernel<false>, (unsigned)((n + 127) / 128), 128, 0, log_size, half_init & 0x7fffffffu, cs, n_batches, d_consts,
+                  d_bc, d_pts, d_off, d_ci, o);
     TS_CUDA(cudaStreamSynchronize(st));   // host vectors go out of scope
     return 0;
 }

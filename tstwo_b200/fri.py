@@ -15,7 +15,7 @@ import numpy as np
 
 from ._lib import check, dptr_array
 from . import _lib
-from .backend import (CudaBackend, FriConfig, LineEvaluation, MerkleDecommitment, MerkleProver, SecureColumnByCoords, SecureEvaluation,
+from .backend import (_L, CudaBackend, FriConfig, LineEvaluation, MerkleDecommitment, MerkleProver, SecureColumnByCoords, SecureEvaluation,
                       TwiddleTree, fold_circle_into_line, fold_line)
 from .channel import Blake2sMerkleChannel
 from .circle import Coset, LineDomain
@@ -113,7 +113,7 @@ def compute_decommitment_positions_and_witness_evals(column: SecureColumnByCoord
     evals = np.zeros((len(witness), 4), dtype=np.uint32)
     if witness:
         addrs = [c.ptr + 4 * p for p in witness for c in column.columns]
-        check(_lib.load().tstwo_gather_words(dptr_array(addrs), len(addrs), 1, evals.ctypes.data_as(_lib.C.POINTER(_lib.C.c_uint32))))
+        check(_L().tstwo_gather_words(dptr_array(addrs), len(addrs), 1, evals.ctypes.data_as(_lib.C.POINTER(_lib.C.c_uint32))))
     return positions, [[int(x) for x in e] for e in evals]
 
 
