@@ -32,6 +32,10 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   tstwo_ipc_export: { args: [T.u64, T.ptr], returns: T.i32 },
   tstwo_ipc_import: { args: [T.ptr, T.ptr], returns: T.i32 },
   tstwo_ipc_close: { args: [T.u64], returns: T.i32 },
+  // decommitment witnesses, proof of work, Stwo-correct DEEP quotients (callers: MerkleProver.decommit, FriProver.decommit, prove_values)
+  tstwo_gather_words: { args: [T.ptr, T.i32, T.i32, T.ptr], returns: T.i32 },
+  tstwo_grind: { args: [T.ptr, T.u32, T.ptr], returns: T.i32 },
+  tstwo_accumulate_quotients_ex: { args: [T.i32, T.u32, T.ptr, T.i32, T.ptr, T.i32, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr, T.u32], returns: T.i32 },
 }).symbols;
 
 function check(rc: number): void {
@@ -118,4 +122,19 @@ export function commitTrace(trace: CudaColumn, nCols: number, logSize: number, l
   check(lib.tstwo_lde_commit(trace.dptr, nCols, logSize, logBlowup, tw.handle, cf[0], evals[0], layers[0], ptr(root), QUIRKS));
   void coeffs;
   return { root, coeffs: cf[0], evals: evals[0], layers: layers[0], domain: CanonicCoset.new(ext).circleDomain() };
+}
+
+// GrindOps for the CUDA backend (backend/cpu/grind.ts:31-42): the nonce search runs on the device, the channel stays on the host.
+export function grind(channel: { digest(): { bytes: Uint8Array } }, powBits: number): bigint {
+  const nonce = new BigUint64Array(1);
+  check(lib.tstwo_grind(ptr(channel.digest().bytes), powBits, ptr(nonce)));
+  return nonce[0];
+}
+
+// The witness half of MerkleProver.decommit / computeDecommitmentPositionsAndWitnessEvals: the index walk stays in TS
+// (vcs/prover.ts:32-109 depends on the queries only), the words come from device memory in one launch.
+export function gatherWords(addresses: bigint[], wordsEach: number): Uint32Array {
+  const out = new Uint32Array(addresses.length * wordsEach);
+  if (addresses.length) check(lib.tstwo_gather_words(ptr(BigUint64Array.from(addresses)), addresses.length, wordsEach, ptr(out)));
+  return out;
 }
