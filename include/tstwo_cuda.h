@@ -57,7 +57,8 @@ uint64_t tstwo_launch_count(void);          /* number of kernels this library ha
 
 /* ---- Column<T> / ColumnOps  (backend/index.ts:53-74, :12-14; impl backend/cpu/index.ts:18-53,85-157) ------ */
 int tstwo_malloc(uint64_t bytes, tstwo_dptr *out);                       /* Column.zeros/uninitialized */
-int tstwo_free(tstwo_dptr p);
+int tstwo_free(tstwo_dptr p);                                            /* returns the block to the library's free lists */
+int tstwo_mem_trim(void);                                                /* gives cached free blocks back to the driver */
 int tstwo_memset_zero(tstwo_dptr p, uint64_t bytes);
 int tstwo_upload(tstwo_dptr dst, const void *host, uint64_t bytes);      /* createBaseFieldColumn(data) */
 int tstwo_download(void *host, tstwo_dptr src, uint64_t bytes);          /* Column.toCpu() / at(i) */

@@ -36,6 +36,7 @@ SIGNATURES = {
     "tstwo_last_error": (C.c_char_p, []),
     "tstwo_set_stream": (C.c_int, [C.c_void_p]),
     "tstwo_sync": (C.c_int, []),
+    "tstwo_mem_trim": (C.c_int, []),
     "tstwo_device_info": (C.c_int, [intp, intp, intp, C.POINTER(C.c_uint64)]),
     "tstwo_launch_count": (C.c_uint64, []),
     "tstwo_malloc": (C.c_int, [C.c_uint64, dptrp]),

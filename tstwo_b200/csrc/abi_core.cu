@@ -8,6 +8,8 @@
 #include "common.cuh"
 #include "circle_dev.cuh"
 
+namespace tstwo { namespace { void release_cached_blocks(); } }   // column allocator, below
+
 namespace tstwo {
 
 static thread_local char g_err[512] = "";
@@ -159,6 +161,7 @@ int tstwo_shutdown(void)
     Context &c = ctx();
     if (!c.ready) return 0;
     cudaDeviceSynchronize();
+    release_cached_blocks();
     {
         std::lock_guard<std::mutex> lk(g_tree_mu);
         for (auto &kv : g_trees) {
@@ -201,22 +204,75 @@ int tstwo_device_info(int *sm_count, int *cc_major, int *cc_minor, uint64_t *tot
 }
 uint64_t tstwo_launch_count(void) { return ctx().launches; }
 
+// Column allocator.  The reference creates a fresh array for every result (Column.zeros / uninitialized in every fold, commit
+// layer, interpolate ...): through cudaMalloc / cudaFree that costs a device synchronisation and ~0.1-1 ms per call, which at FRI's
+// layer sizes is 50x the kernels (scripts/fri_bench.py).  Freed blocks are therefore kept in exact-size free lists and handed out
+// again without touching the driver; a block is only ever reused by work enqueued later on the library stream, so no
+// synchronisation is needed.  Blocks stay plain cudaMalloc memory (CUDA IPC export keeps working).
+}  // extern "C"
+namespace tstwo {
+namespace {
+std::unordered_map<uint64_t, std::vector<void *>> g_free_blocks;   // rounded size -> free blocks
+std::unordered_map<void *, uint64_t> g_block_size;                 // every live or cached block -> rounded size
+uint64_t g_cached_bytes = 0;
+constexpr uint64_t CACHE_CAP_BYTES = 24ull << 30;
+
+void release_cached_blocks()
+{
+    cudaDeviceSynchronize();
+    for (auto &kv : g_free_blocks)
+        for (void *p : kv.second) { cudaFree(p); g_block_size.erase(p); }
+    g_free_blocks.clear();
+    g_cached_bytes = 0;
+}
+}  // namespace
+}  // namespace tstwo
+extern "C" {
+
 int tstwo_malloc(uint64_t bytes, tstwo_dptr *out)
 {
     TS_REQUIRE_INIT();
     if (!out) return fail(TSTWO_ERR_BAD_ARG, "null out");
+    const uint64_t size = ((bytes ? bytes : 4) + 255) & ~255ull;
+    auto it = g_free_blocks.find(size);
+    if (it != g_free_blocks.end() && !it->second.empty()) {
+        *out = (tstwo_dptr)it->second.back();
+        it->second.pop_back();
+        g_cached_bytes -= size;
+        return 0;
+    }
     void *p = nullptr;
-    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 4);
+    cudaError_t e = cudaMalloc(&p, size);
+    if (e == cudaErrorMemoryAllocation) {          // give the cache back to the driver and try once more
+        cudaGetLastError();
+        release_cached_blocks();
+        e = cudaMalloc(&p, size);
+    }
     if (e == cudaErrorMemoryAllocation) { cudaGetLastError(); return fail(TSTWO_ERR_OOM, "cudaMalloc(%llu) out of memory", (unsigned long long)bytes); }
     TS_CUDA(e);
+    g_block_size[p] = size;
     *out = (tstwo_dptr)p;
     return 0;
 }
 int tstwo_free(tstwo_dptr p)
 {
     TS_REQUIRE_INIT();
+    if (!p) return 0;
+    auto it = g_block_size.find((void *)p);
+    if (it != g_block_size.end() && g_cached_bytes + it->second <= CACHE_CAP_BYTES) {
+        g_free_blocks[it->second].push_back((void *)p);
+        g_cached_bytes += it->second;
+        return 0;
+    }
+    if (it != g_block_size.end()) g_block_size.erase(it);
     TS_CUDA(cudaStreamSynchronize(ctx().stream));
     TS_CUDA(cudaFree((void *)p));
+    return 0;
+}
+int tstwo_mem_trim(void)
+{
+    TS_REQUIRE_INIT();
+    release_cached_blocks();
     return 0;
 }
 int tstwo_memset_zero(tstwo_dptr p, uint64_t bytes)
