@@ -14,6 +14,16 @@ evs = [tb.CudaCircleEvaluation(qdom, tb.CudaColumn.view(block.data_ptr() + 4 * (
 pt = ((1, 0, 478637715, 513582971), (992285211, 649143431, 740191619, 1186584352))
 batches = [(pt, [(c, [int(x) for x in rng.integers(0, P, 4)]) for c in range(ncols)])]
 alpha = [1, 2, 3, 4]
-for _ in range(3):
+mode = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+L.tstwo_debug_set_quot_mode(mode)
+for _ in range(4):
     t0 = time.perf_counter(); tb.accumulate_quotients(qdom, evs, alpha, batches, 1, ts_denominators=False); L.tstwo_sync()
     print(f"{(time.perf_counter() - t0) * 1e3:.3f} ms (API level)")
+if mode == 0:   # the two kernel forms must agree bit for bit
+    outs = []
+    for m in (1, 2):
+        L.tstwo_debug_set_quot_mode(m)
+        o = tb.accumulate_quotients(qdom, evs, alpha, batches, 1, ts_denominators=False)
+        outs.append([c.copy() for c in o.values.to_cpu()])
+    L.tstwo_debug_set_quot_mode(0)
+    print("integer-pipe and tensor-core kernels agree:", all((a == b).all() for a, b in zip(*outs)))

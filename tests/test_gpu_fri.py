@@ -127,3 +127,51 @@ def test_accumulate_quotients(tb, orc, log):
     exp = orc.accumulate_quotients(log, dom.halfCoset.initial_index.value, cols, rc, batches)
     for a, b in zip(out.values.to_cpu(), exp):
         assert (a == b).all()
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("ts", [True, False])
+def test_accumulate_quotients_both_kernels(tb, orc, mode, ts):
+    """The integer-pipe kernel (mode 1) and the INT8 tensor-core kernel (mode 2) against the oracle: ragged batches (1, 7, 8, 9
+    columns), a batch longer than one shared-memory chunk (300) and repeated columns."""
+    from tstwo_b200 import _lib
+    L = _lib.load()
+    log = 10
+    rng = np.random.default_rng(50 + mode)
+    dom = tb.CanonicCoset.new(log).circleDomain()
+    cols = [rng.integers(0, P, 1 << log, dtype=np.uint32) for _ in range(12)]
+    cols[3][:] = P - 1          # extreme bytes: 0x7ffffffe in every row
+    cols[4][:] = 0
+    rc = rq(rng)
+    batches = [((rq(rng), rq(rng)), [(int(c), rq(rng)) for c in rng.integers(0, 12, k)]) for k in (1, 7, 8, 9, 300)]
+    batches[1][1][0] = (3, [P - 1, P - 1, P - 1, P - 1])
+    evs = [tb.CudaCircleEvaluation.new(dom, c) for c in cols]
+    L.tstwo_debug_set_quot_mode(mode)
+    try:
+        out = tb.accumulate_quotients(dom, evs, rc, batches, ts_denominators=ts)
+        assert L.tstwo_debug_last_quot_mode() == mode
+    finally:
+        L.tstwo_debug_set_quot_mode(0)
+    exp = orc.accumulate_quotients(log, dom.halfCoset.initial_index.value, cols, rc, batches, ts_denominators=ts)
+    for a, b in zip(out.values.to_cpu(), exp):
+        assert (a == b).all()
+
+
+def test_accumulate_quotients_tensor_core_flush(tb, orc):
+    """More columns in one batch than the s32 accumulators of the tensor-core kernel may hold (flush every 4096), all at the
+    largest byte values."""
+    from tstwo_b200 import _lib
+    L = _lib.load()
+    log = 9
+    rng = np.random.default_rng(77)
+    dom = tb.CanonicCoset.new(log).circleDomain()
+    cols = [np.full(1 << log, 0x7f7fffff, dtype=np.uint32), rng.integers(0, P, 1 << log, dtype=np.uint32)]
+    # c = alpha^k (conj(py) - py): not controllable per byte, so take many terms instead: 9000 > 2 * 4096
+    batches = [((rq(rng), rq(rng)), [(int(k % 2 == 0 and 0 or rng.integers(0, 2)), rq(rng)) for k in range(9000)])]
+    evs = [tb.CudaCircleEvaluation.new(dom, c) for c in cols]
+    rc = rq(rng)
+    out = tb.accumulate_quotients(dom, evs, rc, batches)
+    assert L.tstwo_debug_last_quot_mode() == 2
+    exp = orc.accumulate_quotients(log, dom.halfCoset.initial_index.value, cols, rc, batches)
+    for a, b in zip(out.values.to_cpu(), exp):
+        assert (a == b).all()

@@ -88,13 +88,15 @@ def load():
             fn.restype = res
             fn.argtypes = args
         for dbg in ("tstwo_debug_force_naive_fft", "tstwo_debug_set_fft_radix", "tstwo_debug_set_fft_stream",
-                    "tstwo_debug_set_leaf_mode"):
+                    "tstwo_debug_set_leaf_mode", "tstwo_debug_set_quot_mode"):
             getattr(lib, dbg).restype = C.c_int
             getattr(lib, dbg).argtypes = [C.c_int]
         lib.tstwo_debug_last_fft_mode.restype = C.c_int
         lib.tstwo_debug_last_fft_mode.argtypes = []
         lib.tstwo_debug_last_leaf_mode.restype = C.c_int
         lib.tstwo_debug_last_leaf_mode.argtypes = []
+        lib.tstwo_debug_last_quot_mode.restype = C.c_int
+        lib.tstwo_debug_last_quot_mode.argtypes = []
         _lib = lib
     return _lib
 

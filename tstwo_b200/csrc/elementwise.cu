@@ -117,6 +117,22 @@ __global__ void accumulate_kernel(Q4 dst, CQ4 src, uint64_t n)
 // computes it, from the M31 parts x.c0.re, x.c0.im, y.c0.re, y.c0.im only (quotients.ts:160-178) -- bit-exact with CpuBackend but
 // not a quotient by the line through the point and its conjugate; otherwise Stwo's CM31 denominator
 // (Re(p.x) - d.x) Im(p.y) - (Re(p.y) - d.y) Im(p.x) with Re/Im the CM31 halves, which is what makes the quotient low degree.
+// Domain point of bit-reversed position j of a circle domain with 2^half_log points per half (CircleDomain.at,
+// poly/circle/domain.ts:76-98) from host-built digit tables: T[0][v] = point(half_init + step v), T[d][v] = point(step v 256^d),
+// so that the point is at most 3 group additions away instead of a 31-step divergent ladder per row.
+constexpr int PT_DIGITS = 4, PT_WORDS = PT_DIGITS * 256 * 2;
+__device__ __forceinline__ m31::Pt table_point(const uint2 *__restrict__ T, int half_log, uint32_t j)
+{
+    const uint32_t jm = j & ((1u << half_log) - 1u);
+    uint2 t = __ldg(T + (jm & 255u));
+    m31::Pt r = { t.x, t.y };
+    for (int d = 1; 8 * d < half_log; d++) {
+        t = __ldg(T + 256 * d + ((jm >> (8 * d)) & 255u));
+        r = m31::padd(r, m31::Pt{ t.x, t.y });
+    }
+    if (j >> half_log) r.y = m31::sub(0, r.y);
+    return r;
+}
 __device__ __forceinline__ uint64_t fold62(uint64_t s) { return (s >> 31) + (s & m31::P); }
 __device__ __forceinline__ uint32_t reduce64(uint64_t s)
 {
@@ -130,14 +146,15 @@ template <bool TS_DENOM>
 __global__ void __launch_bounds__(QUOT_THREADS) quotients_kernel(int log_size, uint32_t half_init, ColSet cols, int n_batches,
                                                                const uint4 *__restrict__ cvals, const uint32_t *__restrict__ ab,
                                                                const uint32_t *__restrict__ bcoef, const uint32_t *__restrict__ pts,
-                                                               const int *__restrict__ offsets, const int *__restrict__ col_index, Q4 out)
+                                                               const int *__restrict__ offsets, const int *__restrict__ col_index,
+                                                               const uint2 *__restrict__ ptab, Q4 out)
 {
     __shared__ uint4 sc[QUOT_SMEM_ENTRIES];
     __shared__ const uint32_t *scol[QUOT_SMEM_ENTRIES];   // column base pointers of the staged entries
     const uint64_t row = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = !(row >> log_size);
     const uint64_t r = live ? row : 0;
-    m31::Pt dp = index_to_point(domain_index_at(half_init, log_size - 1, m31::bitrev((uint32_t)r, log_size)));
+    m31::Pt dp = table_point(ptab, log_size - 1, m31::bitrev((uint32_t)r, log_size));
     m31::QM acc = { 0, 0, 0, 0 };
     for (int b = 0; b < n_batches; b++) {
         const uint32_t *pt = pts + 8 * b;
@@ -186,6 +203,155 @@ __global__ void __launch_bounds__(QUOT_THREADS) quotients_kernel(int log_size, u
         acc = m31::qadd(m31::qmul(acc, bc), m31::qmul_cm(num, den_inv));
     }
     if (live) { out.c[0][row] = acc.a; out.c[1][row] = acc.b; out.c[2][row] = acc.c; out.c[3][row] = acc.d; }
+}
+
+// Tensor-core form of the same sum.  sum_j c_j f_j(row) over the columns of a batch is a (rows x columns) x (columns x 4)
+// matrix product over M31; it is made exact on the INT8 tensor cores by splitting both factors into bytes:
+//   f = sum_i 2^(8i) f_i,   (2^(8i) c mod P) = sum_j' 2^(8j') w_(i,j')     =>     c f = sum_j' 2^(8j') sum_i f_i w_(i,j')   (mod P)
+// A column value loaded from HBM is already the 4 consecutive K-elements (column, byte i) of an mma.m16n8k32.u8 operand, so the
+// data goes from the load straight into the B fragment: no unpacking, 2 LDG.128 + 1 LDS.128 + 4 IMMA per 32 rows x 8 columns
+// instead of ~20 integer instructions per value.  The A operand holds the 16 weight rows m = 4 j' + coordinate; the host lays
+// the table out as one uint4 (a0..a3) per lane per 8-column step.  Row r of the thread's 4 mma's: n = groupID <-> row
+// base + 4 groupID + m, so that each thread's loads are 16 contiguous bytes of a column.  Byte products are < 2^16 and the s32
+// accumulators are flushed (transposed through shared memory to one row per lane, recombined mod P) at least every
+// QM_FLUSH columns: 4 QM_FLUSH 255^2 < 2^31.
+constexpr int QM_WARPS = 8, QM_CHUNK = 256, QM_PAD = 17, QM_FLUSH = 4096, QM_R = 2, QM_D = 2;
+__device__ __forceinline__ void imma_u8(int (&c)[4], const uint4 &a, uint32_t b0, uint32_t b1)
+{
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint4 ldcs4(const uint32_t *p) { return p ? __ldcs(reinterpret_cast<const uint4 *>(p)) : make_uint4(0, 0, 0, 0); }
+template <bool TS_DENOM, int R, int D>
+__global__ void __launch_bounds__(QM_WARPS * 32, 3) quotients_mma_kernel(int log_size, uint32_t half_init, int n_batches,
+                                                                     const uint4 *__restrict__ wtab, const uint32_t *const *__restrict__ colptr,
+                                                                     const uint32_t *__restrict__ ab, const uint32_t *__restrict__ bcoef,
+                                                                     const uint32_t *__restrict__ pts, const int *__restrict__ offsets,
+                                                                     const uint2 *__restrict__ ptab, Q4 out)
+{
+    __shared__ uint4 sw[QM_CHUNK / 8 * 32];
+    __shared__ const uint32_t *sp[QM_CHUNK];
+    __shared__ uint32_t st[QM_WARPS][32 * QM_PAD];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tig = lane & 3;
+    const uint64_t row0 = ((uint64_t)blockIdx.x * QM_WARPS + warp) * (32 * R);   // grid covers the domain exactly (host checks)
+    m31::Pt dp[R];
+    m31::QM acc[R];
+#pragma unroll
+    for (int q = 0; q < R; q++) {
+        dp[q] = table_point(ptab, log_size - 1, m31::bitrev((uint32_t)(row0 + 32 * q + lane), log_size));
+        acc[q] = { 0, 0, 0, 0 };
+    }
+    uint32_t *tr = st[warp];
+    for (int b = 0; b < n_batches; b++) {
+        int c[R][4][4];
+        uint32_t num[R][4];
+#pragma unroll
+        for (int q = 0; q < R; q++)
+#pragma unroll
+            for (int m = 0; m < 4; m++) { num[q][m] = 0; c[q][m][0] = c[q][m][1] = c[q][m][2] = c[q][m][3] = 0; }
+        auto flush = [&]() {
+#pragma unroll
+            for (int q = 0; q < R; q++) {
+#pragma unroll
+                for (int m = 0; m < 4; m++) {
+                    tr[(8 * tig + m) * QM_PAD + g] = c[q][m][0];     tr[(8 * tig + 4 + m) * QM_PAD + g] = c[q][m][1];
+                    tr[(8 * tig + m) * QM_PAD + g + 8] = c[q][m][2]; tr[(8 * tig + 4 + m) * QM_PAD + g + 8] = c[q][m][3];
+                    c[q][m][0] = c[q][m][1] = c[q][m][2] = c[q][m][3] = 0;
+                }
+                __syncwarp();
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t *t = tr + lane * QM_PAD + k;
+                    const uint64_t v = (uint64_t)t[0] + ((uint64_t)t[4] << 8) + ((uint64_t)t[8] << 16) + ((uint64_t)t[12] << 24);
+                    num[q][k] = m31::add(num[q][k], reduce64(v));
+                }
+                __syncwarp();
+            }
+        };
+        int since = 0;
+        for (int j0 = offsets[b]; j0 < offsets[b + 1]; j0 += QM_CHUNK) {
+            const int cnt = min(QM_CHUNK, offsets[b + 1] - j0);     // a multiple of 8
+            __syncthreads();
+            for (int e = threadIdx.x; e < cnt * 4; e += QM_WARPS * 32) sw[e] = wtab[(size_t)j0 * 4 + e];
+            for (int e = threadIdx.x; e < cnt; e += QM_WARPS * 32) sp[e] = colptr[j0 + e];
+            __syncthreads();
+            if (since + cnt > QM_FLUSH) { flush(); since = 0; }
+            since += cnt;
+            // D steps of column loads in flight per warp ahead of the mma's that consume them
+            const int steps = cnt / 8;
+            uint4 x[D][R], y[D][R];
+            auto fetch = [&](int s, uint4 (&xs)[R], uint4 (&ys)[R]) {
+                const uint32_t *p0 = sp[8 * s + tig], *p1 = sp[8 * s + 4 + tig];
+#pragma unroll
+                for (int q = 0; q < R; q++) {
+                    xs[q] = ldcs4(p0 ? p0 + row0 + 32 * q + 4 * g : nullptr);
+                    ys[q] = ldcs4(p1 ? p1 + row0 + 32 * q + 4 * g : nullptr);
+                }
+            };
+#pragma unroll
+            for (int d = 0; d < D - 1; d++)
+                if (d < steps) fetch(d, x[d], y[d]);
+            for (int s0 = 0; s0 < steps; s0 += D) {
+#pragma unroll
+                for (int d = 0; d < D; d++) {
+                    const int s = s0 + d;
+                    if (s < steps) {
+                        if (s + D - 1 < steps) fetch(s + D - 1, x[(d + D - 1) % D], y[(d + D - 1) % D]);
+                        const uint4 w = sw[s * 32 + lane];
+#pragma unroll
+                        for (int q = 0; q < R; q++) {
+                            imma_u8(c[q][0], w, x[d][q].x, y[d][q].x); imma_u8(c[q][1], w, x[d][q].y, y[d][q].y);
+                            imma_u8(c[q][2], w, x[d][q].z, y[d][q].z); imma_u8(c[q][3], w, x[d][q].w, y[d][q].w);
+                        }
+                    }
+                }
+            }
+        }
+        flush();
+        const uint32_t *pt = pts + 8 * b, *k = ab + 8 * b;
+        const m31::QM A = { k[0], k[1], k[2], k[3] }, B = { k[4], k[5], k[6], k[7] };
+        const m31::QM bc = { bcoef[4 * b], bcoef[4 * b + 1], bcoef[4 * b + 2], bcoef[4 * b + 3] };
+        // the M31 value to invert per row (the denominator itself, or the norm of the CM31 denominator); the R rows of a thread
+        // share one inversion (Montgomery), with the reference's inv(0) = 0 kept by a rare second path
+        uint32_t dv[R], di[R];
+        m31::CM den[R];
+#pragma unroll
+        for (int q = 0; q < R; q++) {
+            if (TS_DENOM) {
+                dv[q] = m31::sub(m31::mul(m31::sub(pt[0], dp[q].x), pt[5]), m31::mul(m31::sub(pt[4], dp[q].y), pt[1]));
+            } else {
+                const m31::CM prx = { m31::sub(pt[0], dp[q].x), pt[1] }, pix = { pt[2], pt[3] }, pry = { m31::sub(pt[4], dp[q].y), pt[5] }, piy = { pt[6], pt[7] };
+                den[q] = m31::csub2(m31::cmul(prx, piy), m31::cmul(pry, pix));
+                dv[q] = m31::add(m31::mul(den[q].re, den[q].re), m31::mul(den[q].im, den[q].im));
+            }
+        }
+        if (R == 2) {
+            const uint32_t prod = m31::mul(dv[0], dv[R - 1]);
+            if (prod != 0) {
+                const uint32_t t = m31::inv(prod);
+                di[0] = m31::mul(t, dv[R - 1]); di[R - 1] = m31::mul(t, dv[0]);
+            } else {
+                di[0] = m31::inv(dv[0]); di[R - 1] = m31::inv(dv[R - 1]);
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < R; q++) di[q] = m31::inv(dv[q]);
+        }
+#pragma unroll
+        for (int q = 0; q < R; q++) {
+            m31::CM den_inv;
+            if (TS_DENOM) den_inv = { di[q], 0 };
+            else den_inv = { m31::mul(den[q].re, di[q]), m31::mul(m31::sub(0, den[q].im), di[q]) };
+            m31::QM nm = { num[q][0], num[q][1], num[q][2], num[q][3] };
+            nm = m31::qsub(nm, m31::qadd(m31::qmul_m(A, dp[q].y), B));
+            acc[q] = m31::qadd(m31::qmul(acc[q], bc), m31::qmul_cm(nm, den_inv));
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < R; q++) {
+        const uint64_t row = row0 + 32 * q + lane;
+        out.c[0][row] = acc[q].a; out.c[1][row] = acc[q].b; out.c[2][row] = acc[q].c; out.c[3][row] = acc[q].d;
+    }
 }
 
 // eval_at_point (backend/cpu/circle.ts:52-69, poly/utils.ts:36-59 fold): bottom-up pairwise folding, 4 levels
@@ -351,6 +517,10 @@ int tstwo_accumulate(const tstwo_dptr dst[4], const tstwo_dptr src[4], uint64_t 
     return 0;
 }
 
+static int g_quot_mode = 0, g_last_quot = 0;   // 0 auto, 1 integer-pipe kernel, 2 tensor-core kernel
+int tstwo_debug_set_quot_mode(int mode) { g_quot_mode = mode; return 0; }
+int tstwo_debug_last_quot_mode(void) { return g_last_quot; }
+
 int tstwo_accumulate_quotients(int log_size, uint32_t half_init, const tstwo_dptr *cols, int n_cols, const uint32_t rc4[4],
                                int n_batches, const uint32_t *points, const int *batch_offsets, const int *col_index,
                                const uint32_t *values, const tstwo_dptr out[4])
@@ -368,57 +538,113 @@ int tstwo_accumulate_quotients_ex(int log_size, uint32_t half_init, const tstwo_
     const int total = n_batches ? batch_offsets[n_batches] : 0;
     for (int j = 0; j < total; j++)
         if (col_index[j] < 0 || col_index[j] >= n_cols) return fail(TSTWO_ERR_BAD_ARG, "column index %d out of range", col_index[j]);
-    // quotientConstants (quotients.ts:124-152, constraints.ts:117-129) on the host
     const bool ts_quirks = (flags & TSTWO_FLAG_QUIRKS) != 0;
-    std::vector<uint32_t> consts((size_t)total * 4 + 4), ab((size_t)n_batches * 8 + 8), bcoef((size_t)n_batches * 4 + 4), pts((size_t)n_batches * 8 + 8);
+    const uint64_t n = 1ull << log_size;
+    // tensor-core form: whole CTAs of QM_WARPS x 32 QM_R rows, 16-byte aligned columns
+    bool mma = g_quot_mode != 1 && n >= (uint64_t)QM_WARPS * 32 * QM_R && total > 0;
+    for (int j = 0; j < total && mma; j++) mma = ((uintptr_t)cols[col_index[j]] & 15) == 0;
+    if (g_quot_mode == 2 && !mma) return fail(TSTWO_ERR_BAD_ARG, "tensor-core quotient kernel does not apply");
+    g_last_quot = mma ? 2 : 1;
+    // padded batch layout of the tensor-core form: every batch starts at a multiple of 8 entries
+    std::vector<int> poff(n_batches + 1, 0);
+    for (int b = 0; b < n_batches; b++) poff[b + 1] = poff[b] + (batch_offsets[b + 1] - batch_offsets[b] + 7) / 8 * 8;
+    const size_t ptotal = mma ? (size_t)poff[n_batches] : 0;
+
+    // one host image of everything the kernel reads, one copy.  Sections (32-bit words, each a multiple of 4 words):
+    auto round4 = [](size_t w) { return (w + 3) & ~(size_t)3; };
+    const size_t o_ptab = 0, o_wt = o_ptab + PT_WORDS, o_ptr = o_wt + ptotal * 16, o_consts = o_ptr + round4(ptotal * 2 + 2),
+                 o_ab = o_consts + (size_t)total * 4 + 4, o_bc = o_ab + (size_t)n_batches * 8 + 8, o_pts = o_bc + (size_t)n_batches * 4 + 4,
+                 o_off = o_pts + (size_t)n_batches * 8 + 8, o_ci = o_off + round4((size_t)n_batches + 1), o_end = o_ci + round4((size_t)total + 1);
+    std::vector<uint32_t> h(o_end, 0);
+    {   // digit tables of the domain points (table_point)
+        const int half_log = log_size - 1;
+        const uint32_t step = half_log == 0 ? 0u : 1u << (31 - half_log);
+        for (int d = 0; d < PT_DIGITS; d++) {
+            const host::Pt gd = host::index_to_point((uint32_t)(((uint64_t)step << (8 * d)) & 0x7fffffffu));
+            host::Pt cur = d ? host::Pt{ 1u, 0u } : host::index_to_point(half_init & 0x7fffffffu);
+            for (int v = 0; v < 256; v++) { h[o_ptab + (256 * d + v) * 2] = cur.x; h[o_ptab + (256 * d + v) * 2 + 1] = cur.y; cur = host::padd(cur, gd); }
+        }
+    }
+    // quotientConstants (quotients.ts:124-152, constraints.ts:117-129) on the host
+    uint32_t *consts = &h[o_consts];
     host::QM rc = host::qld(rc4);
     for (int b = 0; b < n_batches; b++) {
         host::QM py = host::qld(points + 8 * b + 4);
         host::QM alpha = { 1, 0, 0, 0 }, sum_a = { 0, 0, 0, 0 }, sum_b = { 0, 0, 0, 0 };
+        // TS: QM31.complexConjugate conjugates both CM31 halves (qm31.ts:433-435); Stwo: u -> -u, i.e. (c0, -c1)
+        auto conj = [&](host::QM q) { return ts_quirks ? host::qconj(q) : host::QM{ q.a, q.b, host::neg(q.c), host::neg(q.d) }; };
+        const host::QM c = host::qsub(conj(py), py);
         for (int j = batch_offsets[b]; j < batch_offsets[b + 1]; j++) {
             alpha = host::qmul(alpha, rc);
             host::QM v = host::qld(values + 4 * j);
-            // TS: QM31.complexConjugate conjugates both CM31 halves (qm31.ts:433-435); Stwo: u -> -u, i.e. (c0, -c1)
-            auto conj = [&](host::QM q) { return ts_quirks ? host::qconj(q) : host::QM{ q.a, q.b, host::neg(q.c), host::neg(q.d) }; };
             host::QM a = host::qsub(conj(v), v);
-            host::QM c = host::qsub(conj(py), py);
             host::QM bb = host::qsub(host::qmul(v, c), host::qmul(a, py));
             sum_a = host::qadd(sum_a, host::qmul(alpha, a));
             sum_b = host::qadd(sum_b, host::qmul(alpha, bb));
             host::qst(&consts[4 * j], host::qmul(alpha, c));
         }
-        host::qst(&ab[8 * b], sum_a);
-        host::qst(&ab[8 * b + 4], sum_b);
-        host::qst(&bcoef[4 * b], alpha);   // random_coeff ^ len
-        for (int k = 0; k < 8; k++) pts[8 * b + k] = points[8 * b + k];
+        host::qst(&h[o_ab + 8 * b], sum_a);
+        host::qst(&h[o_ab + 8 * b + 4], sum_b);
+        host::qst(&h[o_bc + 4 * b], alpha);   // random_coeff ^ len
+        for (int k = 0; k < 8; k++) h[o_pts + 8 * b + k] = points[8 * b + k];
     }
-    size_t w_consts = consts.size(), w_ab = ab.size(), w_bc = bcoef.size(), w_pts = pts.size(), w_off = (size_t)n_batches + 1, w_ci = (size_t)total + 1;
-    uint32_t *tmp;
-    int r = scratch((w_consts + w_ab + w_bc + w_pts + w_off + w_ci) * 4, &tmp);
+    if (mma) {
+        // weight rows m = 4 j' + coordinate of an entry: word = bytes j' of (2^(8i) c mod P), i = 0..3; lane (g, tig) of an
+        // 8-entry step holds a0 = W[tig][g], a1 = W[tig][g+8], a2 = W[4+tig][g], a3 = W[4+tig][g+8]
+        uint64_t *ptrs = reinterpret_cast<uint64_t *>(&h[o_ptr]);
+        for (int b = 0; b < n_batches; b++)
+            for (int j = batch_offsets[b]; j < batch_offsets[b + 1]; j++) {
+                const int e = poff[b] + (j - batch_offsets[b]), step = e >> 3, le = e & 7;
+                ptrs[e] = (uint64_t)cols[col_index[j]];
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t cv = consts[4 * (size_t)j + k];
+                    uint32_t rot[4];
+                    for (int i = 0; i < 4; i++) rot[i] = i ? ((cv << (8 * i)) | (cv >> (31 - 8 * i))) & 0x7fffffffu : cv;   // 2^(8i) c mod P
+                    for (int jb = 0; jb < 4; jb++) {
+                        const int m = 4 * jb + k;
+                        uint32_t word = 0;
+                        for (int i = 0; i < 4; i++) word |= ((rot[i] >> (8 * jb)) & 0xffu) << (8 * i);
+                        const int lane = (m & 7) * 4 + (le & 3), reg = (le >> 2) * 2 + (m >> 3);
+                        h[o_wt + ((size_t)step * 32 + lane) * 4 + reg] = word;
+                    }
+                }
+            }
+        for (int b = 0; b <= n_batches; b++) h[o_off + b] = (uint32_t)poff[b];
+    } else {
+        for (int b = 0; b <= n_batches; b++) h[o_off + b] = n_batches ? (uint32_t)batch_offsets[b] : 0u;
+        for (int j = 0; j < total; j++) h[o_ci + j] = (uint32_t)col_index[j];
+    }
+    uint32_t *d;
+    int r = scratch(o_end * 4, &d);
     if (r) return r;
-    uint32_t *d_consts = tmp, *d_ab = d_consts + w_consts, *d_bc = d_ab + w_ab, *d_pts = d_bc + w_bc;
-    int *d_off = (int *)(d_pts + w_pts), *d_ci = d_off + w_off;
     cudaStream_t st = ctx().stream;
-    TS_CUDA(cudaMemcpyAsync(d_consts, consts.data(), w_consts * 4, cudaMemcpyHostToDevice, st));
-    TS_CUDA(cudaMemcpyAsync(d_ab, ab.data(), w_ab * 4, cudaMemcpyHostToDevice, st));
-    TS_CUDA(cudaMemcpyAsync(d_bc, bcoef.data(), w_bc * 4, cudaMemcpyHostToDevice, st));
-    TS_CUDA(cudaMemcpyAsync(d_pts, pts.data(), w_pts * 4, cudaMemcpyHostToDevice, st));
-    std::vector<int> off0(1, 0);
-    TS_CUDA(cudaMemcpyAsync(d_off, n_batches ? batch_offsets : off0.data(), w_off * 4, cudaMemcpyHostToDevice, st));
-    if (total) TS_CUDA(cudaMemcpyAsync(d_ci, col_index, (size_t)total * 4, cudaMemcpyHostToDevice, st));
-    ColSet cs;
-    if ((r = make_colset(cols, n_cols, 0, &cs))) return r;
+    TS_CUDA(cudaMemcpyAsync(d, h.data(), o_end * 4, cudaMemcpyHostToDevice, st));
     Q4 o;
     for (int k = 0; k < 4; k++) o.c[k] = (uint32_t *)out[k];
-    const uint64_t n = 1ull << log_size;
-    const unsigned grid = (unsigned)((n + QUOT_THREADS - 1) / QUOT_THREADS);
-    if (flags & TSTWO_FLAG_QUIRKS)
-        TS_LAUNCH(quotients_kernel<true>, grid, QUOT_THREADS, 0, log_size, half_init & 0x7fffffffu, cs, n_batches, (const uint4 *)d_consts,
-                  d_ab, d_bc, d_pts, d_off, d_ci, o);
-    else
-        TS_LAUNCH(quotients_kernel<false>, grid, QUOT_THREADS, 0, log_size, half_init & 0x7fffffffu, cs, n_batches, (const uint4 *)d_consts,
-                  d_ab, d_bc, d_pts, d_off, d_ci, o);
-    TS_CUDA(cudaStreamSynchronize(st));   // host vectors go out of scope
+    const uint32_t hi = half_init & 0x7fffffffu;
+    const uint2 *d_ptab = (const uint2 *)(d + o_ptab);
+    if (mma) {
+        const unsigned grid = (unsigned)(n / (QM_WARPS * 32 * QM_R));
+        const uint4 *d_wt = (const uint4 *)(d + o_wt);
+        const uint32_t *const *d_ptr = (const uint32_t *const *)(d + o_ptr);
+        if (ts_quirks)
+            TS_LAUNCH((quotients_mma_kernel<true, QM_R, QM_D>), grid, QM_WARPS * 32, 0, log_size, hi, n_batches, d_wt, d_ptr, d + o_ab, d + o_bc,
+                      d + o_pts, (const int *)(d + o_off), d_ptab, o);
+        else
+            TS_LAUNCH((quotients_mma_kernel<false, QM_R, QM_D>), grid, QM_WARPS * 32, 0, log_size, hi, n_batches, d_wt, d_ptr, d + o_ab, d + o_bc,
+                      d + o_pts, (const int *)(d + o_off), d_ptab, o);
+    } else {
+        ColSet cs;
+        if ((r = make_colset(cols, n_cols, 0, &cs))) return r;
+        const unsigned grid = (unsigned)((n + QUOT_THREADS - 1) / QUOT_THREADS);
+        if (ts_quirks)
+            TS_LAUNCH(quotients_kernel<true>, grid, QUOT_THREADS, 0, log_size, hi, cs, n_batches, (const uint4 *)(d + o_consts), d + o_ab, d + o_bc,
+                      d + o_pts, (const int *)(d + o_off), (const int *)(d + o_ci), d_ptab, o);
+        else
+            TS_LAUNCH(quotients_kernel<false>, grid, QUOT_THREADS, 0, log_size, hi, cs, n_batches, (const uint4 *)(d + o_consts), d + o_ab, d + o_bc,
+                      d + o_pts, (const int *)(d + o_off), (const int *)(d + o_ci), d_ptab, o);
+    }
+    TS_CUDA(cudaStreamSynchronize(st));   // the host image goes out of scope
     return 0;
 }
 
