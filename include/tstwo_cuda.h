@@ -123,6 +123,16 @@ int tstwo_accumulate_quotients_ex(int log_size, uint32_t half_coset_initial_inde
                                   const int *batch_offsets, const int *col_index, const uint32_t *values,
                                   const tstwo_dptr out[4], uint32_t flags);
 
+/* Wide-Fibonacci constraint quotients over the evaluation domain (examples/fibonacci.ts:72-91: constraint i is
+ * c - (a^2 + b^2) on columns i, i+1, i+2; the domain loop is Stwo's FrameworkComponent::evaluate_constraint_quotients_on_domain,
+ * a placeholder at constraint_framework/index.ts:131-152).  cols: n_cols evaluations of the trace on
+ * CanonicCoset(eval_log_size).circleDomain(), bit-reversed.  coeffs: n_cols-2 QM31, the random-coefficient power that multiplies
+ * constraint i (ColumnAccumulator.randomCoeffPowers reversed, air/accumulator.ts:159-176).  denom_inv: 2^(eval_log_size -
+ * trace_log_size) M31, 1 / coset_vanishing(CanonicCoset(trace_log_size).coset, domain.at(i)) bit-reversed (constraints.ts:32-47).
+ * out[row] += denom_inv[row >> trace_log_size] * sum_i coeffs[i] * constraint_i(row).  Host arrays except cols / out. */
+int tstwo_widefib_constraints(int trace_log_size, int eval_log_size, const tstwo_dptr *cols, int n_cols, const uint32_t *coeffs,
+                              const uint32_t *denom_inv, const tstwo_dptr out[4]);
+
 /* ---- the metric path in one call: Stwo's CommitmentTreeProver::new (quoted at pcs/prover.ts:215-235) -------- */
 /* interpolate n_cols trace columns on CanonicCoset(log_size), evaluate on CanonicCoset(log_size+log_blowup),
  * Blake2s Merkle commit.  trace/coeffs/evals are contiguous column-major blocks (column c at base + c*len).

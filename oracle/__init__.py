@@ -250,6 +250,39 @@ def accumulate_quotients(log_size: int, half_init: int, cols, random_coeff, batc
     return out
 
 
+def coset_vanishing(coset_initial_index: int, coset_log_size: int, p):
+    """constraints.ts:32-47 for an M31 point p = (x, y): x-coordinate of (p - initial + half_step), doubled log_size - 1 times."""
+    P = 2147483647
+    ix, iy = index_to_point(coset_initial_index)
+    hx, hy = index_to_point(subgroup_gen(coset_log_size) >> 1)
+    sx, sy = (p[0] * ix + p[1] * iy) % P, (p[1] * ix - p[0] * iy) % P      # p - initial
+    x = (sx * hx - sy * hy) % P                                            # + half, x only
+    for _ in range(1, coset_log_size):
+        x = (2 * x * x - 1) % P
+    return x
+
+
+def widefib_denom_inv(trace_log: int, eval_log: int):
+    """Stwo FrameworkComponent::evaluate_constraint_quotients_on_domain: inverse of the vanishing polynomial of
+    CanonicCoset(trace_log).coset (Coset.odds: initial G_{2^(log+1)}, canonic.ts:24-40) at eval_domain.at(i), i < 2^(eval_log - trace_log),
+    then bit-reversed."""
+    P = 2147483647
+    hi, hl = canonic_half_coset(eval_log)
+    vals = [pow(coset_vanishing(subgroup_gen(trace_log + 1), trace_log, domain_point(hi, hl, i)), P - 2, P)
+            for i in range(1 << (eval_log - trace_log))]
+    return _bitrev_list(vals)
+
+
+def widefib_constraints(trace_log: int, eval_log: int, cols, coeffs, denom_inv, out4):
+    """out4 (4 uint32 arrays) += denom_inv[row >> trace_log] * sum_i coeffs[i] (c - a^2 - b^2)_i(row).  parity unpinned."""
+    cols = [_u32(c) for c in cols]
+    arr = (u32p * len(cols))(*[_p(c) for c in cols])
+    co = _u32([x for q in coeffs for x in q] or [0])
+    out = [_u32(o).copy() for o in out4]
+    lib().orc_widefib_constraints(trace_log, eval_log, arr, len(cols), _p(co), _p(_u32(denom_inv)), *[_p(o) for o in out])
+    return out
+
+
 # ---- the metric pipeline ----
 def lde_commit(cols_in: np.ndarray, log_blowup: int, tw, itw, want_coeffs=False, want_layers=True, quirks=True):
     """cols_in: (n_cols, 2^log) uint32.  Returns (coeffs|None, evals, layers|None)."""

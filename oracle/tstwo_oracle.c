@@ -574,6 +574,29 @@ EXPORT void orc_generate_secure_powers(const uint32_t *felt4, int n, uint32_t *o
     for (int i = 0; i < n; i++) { qm_st(out + 4 * i, acc); acc = qm_mul(acc, f); }
 }
 
+/* Wide-Fibonacci constraint quotients over the evaluation domain.  The constraint is examples/fibonacci.ts:72-91
+ * (c - (a^2 + b^2) on three consecutive columns); the loop over the domain is the one the TS code leaves as a placeholder
+ * (constraint_framework/index.ts:131-152) and Stwo's FrameworkComponent::evaluate_constraint_quotients_on_domain does:
+ * per row, row_res = sum_i coeffs[i] * constraint_i(row), then col[row] += row_res * denom_inv[row >> trace_log_size].
+ * parity unpinned: no reference golden exists for this function. */
+EXPORT void orc_widefib_constraints(int trace_log_size, int eval_log_size, const uint32_t *const *cols, int n_cols,
+                                    const uint32_t *coeffs, const uint32_t *denom_inv,
+                                    uint32_t *o0, uint32_t *o1, uint32_t *o2, uint32_t *o3)
+{
+    const uint64_t n = 1ull << eval_log_size;
+    for (uint64_t row = 0; row < n; row++) {
+        qm31 res = qm(0, 0, 0, 0);
+        for (int i = 0; i + 2 < n_cols; i++) {
+            uint32_t a = cols[i][row], b = cols[i + 1][row], c = cols[i + 2][row];
+            uint32_t con = m31_sub(c, m31_add(m31_mul(a, a), m31_mul(b, b)));
+            res = qm_add(res, qm_mul_m31(qm_ld(coeffs + 4 * i), con));
+        }
+        res = qm_mul_m31(res, denom_inv[row >> trace_log_size]);
+        o0[row] = m31_add(o0[row], res.c0.re); o1[row] = m31_add(o1[row], res.c0.im);
+        o2[row] = m31_add(o2[row], res.c1.re); o3[row] = m31_add(o3[row], res.c1.im);
+    }
+}
+
 /* backend/cpu/quotients.ts:52-178 accumulateQuotients.
  * Batches are flattened: batch b has point (px,py: 8 words at points[8b]) and entries
  * [batch_offsets[b], batch_offsets[b+1]) of (col_index[], values[4*]).  Follows the TS code, including its

@@ -1,12 +1,14 @@
 """tstwo_b200: B200-native (sm_100a) CudaBackend for TStwo's LDE + Blake2s-commit hot path.
 
 Layout: csrc/ (CUDA kernels + C ABI -> libtstwo_cuda.so), _lib.py (ctypes binding of include/tstwo_cuda.h),
-circle.py (host index arithmetic), backend.py (mirror of the reference's backend interfaces), channel.py (Fiat-Shamir
+circle.py (host index arithmetic), air.py (accumulators, wide-Fibonacci component), backend.py (mirror of the reference's backend interfaces), channel.py (Fiat-Shamir
 channel), fri.py (FRI commit / decommit over the device folds and Merkle trees)."""
 from .backend import (CommitmentSchemeProver, CommitmentTreeProver, FriConfig, MerkleDecommitment, PcsConfig, TreeBuilder, TreeSubspan,
                       CudaBackend, CudaCircleEvaluation, CudaCirclePoly, CudaColumn, CudaFriOps,
                       CudaMerkleOps, LineEvaluation, MerkleProver, SecureColumnByCoords, SecureEvaluation, TwiddleTree,
                       accumulate, accumulate_quotients, fold_circle_into_line, fold_line)
+from .air import (ColumnAccumulator, DomainEvaluationAccumulator, PointEvaluationAccumulator, SecureCirclePoly, WideFibonacciComponent,
+                  WideFibonacciEval, generate_secure_powers, generate_wide_fibonacci_trace, widefib_constraints)
 from .channel import Blake2sChannel, Blake2sMerkleChannel, ChannelTime
 from .circle import CanonicCoset, CircleDomain, CirclePointIndex, Coset, LineDomain
 from .fri import FriLayerProof, FriProof, FriProver, LinePoly, Queries

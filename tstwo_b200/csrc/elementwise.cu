@@ -354,6 +354,123 @@ __global__ void __launch_bounds__(QM_WARPS * 32, 3) quotients_mma_kernel(int log
     }
 }
 
+// Wide-Fibonacci constraint quotients on the evaluation domain (examples/fibonacci.ts:72-91 c - (a^2 + b^2); the domain
+// evaluation is Stwo's FrameworkComponent::evaluate_constraint_quotients_on_domain, a placeholder in
+// constraint_framework/index.ts:131-152):   out[row] += denom_inv[row >> trace_log] * sum_i coeff_i (f_{i+2} - f_{i+1}^2 - f_i^2)(row).
+// Reference form, one thread per row (small or unaligned inputs):
+__global__ void __launch_bounds__(256) widefib_kernel(uint64_t n, int trace_log, ColSet cols, int n_cols, const uint4 *__restrict__ coeffs,
+                                                      const uint32_t *__restrict__ denom_inv, Q4 out)
+{
+    const uint64_t row = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n) return;
+    uint32_t a = cols.col(0)[row], b = cols.col(1)[row];
+    uint32_t sa = m31::mul(a, a), sb = m31::mul(b, b);
+    m31::QM acc = { 0, 0, 0, 0 };
+    for (int k = 2; k < n_cols; k++) {
+        const uint32_t c = cols.col(k)[row];
+        const uint32_t g = m31::sub(c, m31::add(sa, sb));
+        const uint4 w = coeffs[k - 2];
+        acc = m31::qadd(acc, m31::qmul_m(m31::QM{ w.x, w.y, w.z, w.w }, g));
+        sa = sb; sb = m31::mul(c, c);
+    }
+    acc = m31::qmul_m(acc, denom_inv[row >> trace_log]);
+    out.c[0][row] = m31::add(out.c[0][row], acc.a); out.c[1][row] = m31::add(out.c[1][row], acc.b);
+    out.c[2][row] = m31::add(out.c[2][row], acc.c); out.c[3][row] = m31::add(out.c[3][row], acc.d);
+}
+// Tensor-core form.  The sum is linear in the column values and in their squares:
+//   sum_i coeff_i (f_{i+2} - f_{i+1}^2 - f_i^2) = sum_k U_k f_k + sum_k V_k f_k^2,   U_k = coeff_{k-2},  V_k = -(coeff_{k-1} + coeff_k)
+// so each thread squares the values it loaded (no neighbouring columns needed) and the two sums are the byte-split INT8 products
+// of quotients_mma_kernel with two weight tables.  8 mma's per 32 rows x 8 columns, flush every WF_FLUSH columns.
+constexpr int WF_CHUNK = 128, WF_FLUSH = 2048, WF_R = 2;
+template <int R>
+__global__ void __launch_bounds__(QM_WARPS * 32, 3) widefib_mma_kernel(int trace_log, int n_entries, const uint4 *__restrict__ wtab_f,
+                                                                      const uint4 *__restrict__ wtab_s, const uint32_t *const *__restrict__ colptr,
+                                                                      const uint32_t *__restrict__ denom_inv, Q4 out)
+{
+    __shared__ uint4 swf[WF_CHUNK / 8 * 32], sws[WF_CHUNK / 8 * 32];
+    __shared__ const uint32_t *sp[WF_CHUNK];
+    __shared__ uint32_t st[QM_WARPS][32 * QM_PAD];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tig = lane & 3;
+    const uint64_t row0 = ((uint64_t)blockIdx.x * QM_WARPS + warp) * (32 * R);
+    uint32_t *tr = st[warp];
+    int c[R][4][4];
+    uint32_t num[R][4];
+#pragma unroll
+    for (int q = 0; q < R; q++)
+#pragma unroll
+        for (int m = 0; m < 4; m++) { num[q][m] = 0; c[q][m][0] = c[q][m][1] = c[q][m][2] = c[q][m][3] = 0; }
+    auto flush = [&]() {
+#pragma unroll
+        for (int q = 0; q < R; q++) {
+#pragma unroll
+            for (int m = 0; m < 4; m++) {
+                tr[(8 * tig + m) * QM_PAD + g] = c[q][m][0];     tr[(8 * tig + 4 + m) * QM_PAD + g] = c[q][m][1];
+                tr[(8 * tig + m) * QM_PAD + g + 8] = c[q][m][2]; tr[(8 * tig + 4 + m) * QM_PAD + g + 8] = c[q][m][3];
+                c[q][m][0] = c[q][m][1] = c[q][m][2] = c[q][m][3] = 0;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint32_t *t = tr + lane * QM_PAD + k;
+                const uint64_t v = (uint64_t)t[0] + ((uint64_t)t[4] << 8) + ((uint64_t)t[8] << 16) + ((uint64_t)t[12] << 24);
+                num[q][k] = m31::add(num[q][k], reduce64(v));
+            }
+            __syncwarp();
+        }
+    };
+    // v^2 mod P up to one multiple of P: any 32-bit representative works as an operand of the integer byte products
+    auto sq = [](uint32_t v) { const uint64_t p = (uint64_t)v * v; return ((uint32_t)p & m31::P) + (uint32_t)(p >> 31); };
+    auto sq4 = [&](uint4 v) { return make_uint4(sq(v.x), sq(v.y), sq(v.z), sq(v.w)); };
+    int since = 0;
+    for (int j0 = 0; j0 < n_entries; j0 += WF_CHUNK) {
+        const int cnt = min(WF_CHUNK, n_entries - j0);     // a multiple of 8
+        __syncthreads();
+        for (int e = threadIdx.x; e < cnt * 4; e += QM_WARPS * 32) { swf[e] = wtab_f[(size_t)j0 * 4 + e]; sws[e] = wtab_s[(size_t)j0 * 4 + e]; }
+        for (int e = threadIdx.x; e < cnt; e += QM_WARPS * 32) sp[e] = colptr[j0 + e];
+        __syncthreads();
+        if (since + cnt > WF_FLUSH) { flush(); since = 0; }
+        since += cnt;
+        const int steps = cnt / 8;
+        constexpr int D = 2;      // load steps in flight ahead of the squares and mma's that consume them
+        uint4 x[D][R], y[D][R];
+        auto fetch = [&](int s, uint4 (&xs)[R], uint4 (&ys)[R]) {
+            const uint32_t *p0 = sp[8 * s + tig], *p1 = sp[8 * s + 4 + tig];
+#pragma unroll
+            for (int q = 0; q < R; q++) {
+                xs[q] = ldcs4(p0 ? p0 + row0 + 32 * q + 4 * g : nullptr);
+                ys[q] = ldcs4(p1 ? p1 + row0 + 32 * q + 4 * g : nullptr);
+            }
+        };
+        fetch(0, x[0], y[0]);
+        for (int s0 = 0; s0 < steps; s0 += D) {
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                const int s = s0 + d;
+                if (s < steps) {
+                    if (s + 1 < steps) fetch(s + 1, x[(d + 1) % D], y[(d + 1) % D]);
+                    const uint4 wf = swf[s * 32 + lane], ws = sws[s * 32 + lane];
+#pragma unroll
+                    for (int q = 0; q < R; q++) {
+                        imma_u8(c[q][0], wf, x[d][q].x, y[d][q].x); imma_u8(c[q][1], wf, x[d][q].y, y[d][q].y);
+                        imma_u8(c[q][2], wf, x[d][q].z, y[d][q].z); imma_u8(c[q][3], wf, x[d][q].w, y[d][q].w);
+                        const uint4 xs = sq4(x[d][q]), ys = sq4(y[d][q]);
+                        imma_u8(c[q][0], ws, xs.x, ys.x); imma_u8(c[q][1], ws, xs.y, ys.y);
+                        imma_u8(c[q][2], ws, xs.z, ys.z); imma_u8(c[q][3], ws, xs.w, ys.w);
+                    }
+                }
+            }
+        }
+    }
+    flush();
+#pragma unroll
+    for (int q = 0; q < R; q++) {
+        const uint64_t row = row0 + 32 * q + lane;
+        const uint32_t di = denom_inv[row >> trace_log];
+        out.c[0][row] = m31::add(out.c[0][row], m31::mul(num[q][0], di)); out.c[1][row] = m31::add(out.c[1][row], m31::mul(num[q][1], di));
+        out.c[2][row] = m31::add(out.c[2][row], m31::mul(num[q][2], di)); out.c[3][row] = m31::add(out.c[3][row], m31::mul(num[q][3], di));
+    }
+}
+
 // eval_at_point (backend/cpu/circle.ts:52-69, poly/utils.ts:36-59 fold): bottom-up pairwise folding, 4 levels
 // (16 values) per thread.  Level l combines (w[2k], w[2k+1]) -> w[2k] + f_l w[2k+1]; f_0 = y, f_1 = x, f_2 = pi(x)...
 struct FoldFactors { m31::QM f[32]; };
@@ -517,6 +634,25 @@ int tstwo_accumulate(const tstwo_dptr dst[4], const tstwo_dptr src[4], uint64_t 
     return 0;
 }
 
+// Weight words of entry e of an INT8 product table (quotients_mma_kernel, widefib_mma_kernel): rows m = 4 j' + coordinate,
+// word = bytes j' of (2^(8i) c mod P), i = 0..3; lane (g, tig) of an 8-entry step holds a0 = W[tig][g], a1 = W[tig][g+8],
+// a2 = W[4+tig][g], a3 = W[4+tig][g+8].
+static void put_mma_weights(uint32_t *wt, int e, const uint32_t c4[4])
+{
+    const int step = e >> 3, le = e & 7;
+    for (int k = 0; k < 4; k++) {
+        const uint32_t cv = c4[k];
+        uint32_t rot[4];
+        for (int i = 0; i < 4; i++) rot[i] = i ? ((cv << (8 * i)) | (cv >> (31 - 8 * i))) & 0x7fffffffu : cv;   // 2^(8i) c mod P
+        for (int jb = 0; jb < 4; jb++) {
+            const int m = 4 * jb + k;
+            uint32_t word = 0;
+            for (int i = 0; i < 4; i++) word |= ((rot[i] >> (8 * jb)) & 0xffu) << (8 * i);
+            const int lane = (m & 7) * 4 + (le & 3), reg = (le >> 2) * 2 + (m >> 3);
+            wt[((size_t)step * 32 + lane) * 4 + reg] = word;
+        }
+    }
+}
 static int g_quot_mode = 0, g_last_quot = 0;   // 0 auto, 1 integer-pipe kernel, 2 tensor-core kernel
 int tstwo_debug_set_quot_mode(int mode) { g_quot_mode = mode; return 0; }
 int tstwo_debug_last_quot_mode(void) { return g_last_quot; }
@@ -589,25 +725,12 @@ int tstwo_accumulate_quotients_ex(int log_size, uint32_t half_init, const tstwo_
         for (int k = 0; k < 8; k++) h[o_pts + 8 * b + k] = points[8 * b + k];
     }
     if (mma) {
-        // weight rows m = 4 j' + coordinate of an entry: word = bytes j' of (2^(8i) c mod P), i = 0..3; lane (g, tig) of an
-        // 8-entry step holds a0 = W[tig][g], a1 = W[tig][g+8], a2 = W[4+tig][g], a3 = W[4+tig][g+8]
         uint64_t *ptrs = reinterpret_cast<uint64_t *>(&h[o_ptr]);
         for (int b = 0; b < n_batches; b++)
             for (int j = batch_offsets[b]; j < batch_offsets[b + 1]; j++) {
-                const int e = poff[b] + (j - batch_offsets[b]), step = e >> 3, le = e & 7;
+                const int e = poff[b] + (j - batch_offsets[b]);
                 ptrs[e] = (uint64_t)cols[col_index[j]];
-                for (int k = 0; k < 4; k++) {
-                    const uint32_t cv = consts[4 * (size_t)j + k];
-                    uint32_t rot[4];
-                    for (int i = 0; i < 4; i++) rot[i] = i ? ((cv << (8 * i)) | (cv >> (31 - 8 * i))) & 0x7fffffffu : cv;   // 2^(8i) c mod P
-                    for (int jb = 0; jb < 4; jb++) {
-                        const int m = 4 * jb + k;
-                        uint32_t word = 0;
-                        for (int i = 0; i < 4; i++) word |= ((rot[i] >> (8 * jb)) & 0xffu) << (8 * i);
-                        const int lane = (m & 7) * 4 + (le & 3), reg = (le >> 2) * 2 + (m >> 3);
-                        h[o_wt + ((size_t)step * 32 + lane) * 4 + reg] = word;
-                    }
-                }
+                put_mma_weights(&h[o_wt], e, &consts[4 * (size_t)j]);
             }
         for (int b = 0; b <= n_batches; b++) h[o_off + b] = (uint32_t)poff[b];
     } else {
@@ -643,6 +766,59 @@ int tstwo_accumulate_quotients_ex(int log_size, uint32_t half_init, const tstwo_
         else
             TS_LAUNCH(quotients_kernel<false>, grid, QUOT_THREADS, 0, log_size, hi, cs, n_batches, (const uint4 *)(d + o_consts), d + o_ab, d + o_bc,
                       d + o_pts, (const int *)(d + o_off), (const int *)(d + o_ci), d_ptab, o);
+    }
+    TS_CUDA(cudaStreamSynchronize(st));   // the host image goes out of scope
+    return 0;
+}
+
+int tstwo_widefib_constraints(int trace_log_size, int eval_log_size, const tstwo_dptr *cols, int n_cols, const uint32_t *coeffs,
+                              const uint32_t *denom_inv, const tstwo_dptr out[4])
+{
+    TS_REQUIRE_INIT();
+    if (trace_log_size < 0 || eval_log_size < trace_log_size || eval_log_size > 30 || eval_log_size - trace_log_size > 16 || n_cols < 2)
+        return fail(TSTWO_ERR_BAD_ARG, "bad wide-Fibonacci arguments");
+    if (n_cols == 2) return 0;   // no constraints
+    const uint64_t n = 1ull << eval_log_size;
+    const int n_den = 1 << (eval_log_size - trace_log_size), n_con = n_cols - 2;
+    bool mma = g_quot_mode != 1 && n >= (uint64_t)QM_WARPS * 32 * WF_R;
+    for (int k = 0; k < n_cols && mma; k++) mma = ((uintptr_t)cols[k] & 15) == 0;
+    if (g_quot_mode == 2 && !mma) return fail(TSTWO_ERR_BAD_ARG, "tensor-core wide-Fibonacci kernel does not apply");
+    g_last_quot = mma ? 2 : 1;
+    const size_t pcols = ((size_t)n_cols + 7) / 8 * 8;
+    auto round4 = [](size_t w) { return (w + 3) & ~(size_t)3; };
+    const size_t o_wf = 0, o_ws = o_wf + (mma ? pcols * 16 : 0), o_ptr = o_ws + (mma ? pcols * 16 : 0), o_co = o_ptr + (mma ? pcols * 2 : 0),
+                 o_den = o_co + (size_t)n_con * 4, o_end = o_den + round4(n_den);
+    std::vector<uint32_t> h(o_end, 0);
+    memcpy(&h[o_co], coeffs, (size_t)n_con * 16);
+    memcpy(&h[o_den], denom_inv, (size_t)n_den * 4);
+    for (size_t i = 0; i < (size_t)n_con * 4 + n_den; i++)
+        if (h[o_co + i] >= host::P) return fail(TSTWO_ERR_BAD_ARG, "field element out of range");
+    if (mma) {
+        uint64_t *ptrs = reinterpret_cast<uint64_t *>(&h[o_ptr]);
+        auto coeff = [&](int i) { return i >= 0 && i < n_con ? host::qld(coeffs + 4 * i) : host::QM{ 0, 0, 0, 0 }; };
+        for (int k = 0; k < n_cols; k++) {
+            ptrs[k] = (uint64_t)cols[k];
+            uint32_t u[4], v[4];
+            host::qst(u, coeff(k - 2));
+            host::qst(v, host::qsub(host::QM{ 0, 0, 0, 0 }, host::qadd(coeff(k - 1), coeff(k))));
+            put_mma_weights(&h[o_wf], k, u);
+            put_mma_weights(&h[o_ws], k, v);
+        }
+    }
+    uint32_t *d;
+    int r = scratch(o_end * 4, &d);
+    if (r) return r;
+    cudaStream_t st = ctx().stream;
+    TS_CUDA(cudaMemcpyAsync(d, h.data(), o_end * 4, cudaMemcpyHostToDevice, st));
+    Q4 o;
+    for (int k = 0; k < 4; k++) o.c[k] = (uint32_t *)out[k];
+    if (mma) {
+        TS_LAUNCH((widefib_mma_kernel<WF_R>), (unsigned)(n / (QM_WARPS * 32 * WF_R)), QM_WARPS * 32, 0, trace_log_size, (int)pcols,
+                  (const uint4 *)(d + o_wf), (const uint4 *)(d + o_ws), (const uint32_t *const *)(d + o_ptr), d + o_den, o);
+    } else {
+        ColSet cs;
+        if ((r = make_colset(cols, n_cols, 0, &cs))) return r;
+        TS_LAUNCH(widefib_kernel, (unsigned)((n + 255) / 256), 256, 0, n, trace_log_size, cs, n_cols, (const uint4 *)(d + o_co), d + o_den, o);
     }
     TS_CUDA(cudaStreamSynchronize(st));   // the host image goes out of scope
     return 0;
