@@ -36,6 +36,9 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   tstwo_gather_words: { args: [T.ptr, T.i32, T.i32, T.ptr], returns: T.i32 },
   tstwo_grind: { args: [T.ptr, T.u32, T.ptr], returns: T.i32 },
   tstwo_accumulate_quotients_ex: { args: [T.i32, T.u32, T.ptr, T.i32, T.ptr, T.i32, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr, T.u32], returns: T.i32 },
+  // wide-Fibonacci constraint quotients over the evaluation domain (ComponentProver.evaluateConstraintQuotientsOnDomain); allocator trim
+  tstwo_widefib_constraints: { args: [T.i32, T.i32, T.ptr, T.i32, T.ptr, T.ptr, T.ptr], returns: T.i32 },
+  tstwo_mem_trim: { args: [], returns: T.i32 },
 }).symbols;
 
 function check(rc: number): void {
@@ -137,4 +140,16 @@ export function gatherWords(addresses: bigint[], wordsEach: number): Uint32Array
   const out = new Uint32Array(addresses.length * wordsEach);
   if (addresses.length) check(lib.tstwo_gather_words(ptr(BigUint64Array.from(addresses)), addresses.length, wordsEach, ptr(out)));
   return out;
+}
+
+// ComponentProver.evaluateConstraintQuotientsOnDomain for the wide-Fibonacci component (the loop that
+// constraint_framework/index.ts:131-152 leaves as a placeholder): `evals` are the trace columns on
+// CanonicCoset(logSize + 1).circleDomain(); `coeffs` = accum.randomCoeffPowers reversed (constraint i gets alpha^(N-1-i),
+// air/accumulator.ts:159-176); `denomInv[i]` = 1 / cosetVanishing(CanonicCoset(logSize).coset, evalDomain.at(i)), bit-reversed.
+// Adds denomInv[row >> logSize] * sum_i coeffs[i] * (c - a^2 - b^2)_i(row) into the accumulator's 4 coordinate columns.
+export function wideFibonacciConstraintQuotients(logSize: number, evals: CudaColumn[], coeffs: Uint32Array, denomInv: Uint32Array,
+                                                 accCoords: [CudaColumn, CudaColumn, CudaColumn, CudaColumn]): void {
+  const cols = BigUint64Array.from(evals.map((c) => c.dptr));
+  const out = BigUint64Array.from(accCoords.map((c) => c.dptr));
+  check(lib.tstwo_widefib_constraints(logSize, logSize + 1, ptr(cols), evals.length, ptr(coeffs), ptr(denomInv), ptr(out)));
 }
