@@ -34,6 +34,36 @@ def qm31_mul(x, y):
     return [(ac[0] + rbd[0]) % P, (ac[1] + rbd[1]) % P, (ad[0] + bc[0]) % P, (ad[1] + bc[1]) % P]
 
 
+def qm31_sub(x, y): return [(a - b) % P for a, b in zip(x, y)]
+
+
+def qm31_scale(x, k: int): return [a * k % P for a in x]
+
+
+def qm31_inv(x):
+    """qm31.ts:282-305: (a + bu)^-1 = (a - bu) / (a^2 - (2 + i) b^2), the denominator a CM31 (cm31.ts inverse)."""
+    a, b = (x[0], x[1]), (x[2], x[3])
+    b2 = _cm_mul(b, b)
+    rb2 = _cm_mul((2, 1), b2)
+    a2 = _cm_mul(a, a)
+    den = ((a2[0] - rb2[0]) % P, (a2[1] - rb2[1]) % P)
+    norm = (den[0] * den[0] + den[1] * den[1]) % P
+    if norm == 0:
+        raise ZeroDivisionError("0 has no inverse")
+    ninv = pow(norm, P - 2, P)
+    dinv = (den[0] * ninv % P, (-den[1]) * ninv % P)
+    ra, rb = _cm_mul(a, dinv), _cm_mul(((-b[0]) % P, (-b[1]) % P), dinv)
+    return [ra[0], ra[1], rb[0], rb[1]]
+
+
+def from_partial_evals(evals: Sequence[Sequence[int]]) -> List[int]:
+    """qm31.ts:411-428: e0 + e1 i + e2 u + e3 iu."""
+    res = list(evals[0])
+    for k, unit in ((1, [0, 1, 0, 0]), (2, [0, 0, 1, 0]), (3, [0, 0, 0, 1])):
+        res = qm31_add(res, qm31_mul(list(evals[k]), unit))
+    return res
+
+
 def generate_secure_powers(felt: Sequence[int], n_powers: int) -> List[List[int]]:
     """backend/cpu/accumulation.ts:52-63 / DomainEvaluationAccumulator.generateSecurePowers (accumulator.ts:247-257)."""
     out, cur = [], [1, 0, 0, 0]
@@ -78,11 +108,7 @@ class SecureCirclePoly:
 
     def eval_at_point(self, point) -> List[int]:
         """from_partial_evals (qm31.ts:411-428): e0 + e1 i + e2 u + e3 iu."""
-        e = self.eval_columns_at_point(point)
-        res = e[0]
-        for k, unit in ((1, [0, 1, 0, 0]), (2, [0, 0, 1, 0]), (3, [0, 0, 0, 1])):
-            res = qm31_add(res, qm31_mul(e[k], unit))
-        return res
+        return from_partial_evals(self.eval_columns_at_point(point))
 
     def evaluateWithTwiddles(self, domain, twiddles) -> "_b.SecureEvaluation":
         evs = _b.CudaBackend.evaluatePolynomialsOnDomain(self.polys, domain, twiddles)
@@ -175,6 +201,27 @@ def coset_vanishing(coset: Coset, p: Tuple[int, int]) -> int:
     return x
 
 
+def coset_vanishing_secure(coset: Coset, p) -> List[int]:
+    """constraints.ts:32-47 at a CirclePoint<SecureField> p = (x[4], y[4])."""
+    hx, hy = coset.step_size.half().to_point()
+    ix, iy = coset.initial_index.to_point()
+    px, py = list(p[0]), list(p[1])
+    sx = qm31_add(qm31_scale(px, ix), qm31_scale(py, iy))            # p - initial
+    sy = qm31_sub(qm31_scale(py, ix), qm31_scale(px, iy))
+    x = qm31_sub(qm31_scale(sx, hx), qm31_scale(sy, hy))             # + half, x only
+    for _ in range(1, coset.log_size):
+        x = qm31_sub(qm31_scale(qm31_mul(x, x), 2), [1, 0, 0, 0])
+    return x
+
+
+def get_random_point(channel):
+    """CirclePoint.get_random_point (circle.ts:126-133): t = draw_felt(); ((1 - t^2) / (1 + t^2), 2t / (1 + t^2))."""
+    t = channel.draw_felt()
+    t2 = qm31_mul(t, t)
+    inv = qm31_inv(qm31_add(t2, [1, 0, 0, 0]))
+    return (tuple(qm31_mul(qm31_sub([1, 0, 0, 0], t2), inv)), tuple(qm31_mul(qm31_scale(t, 2), inv)))
+
+
 def bit_reverse_list(items):
     n = len(items)
     bits = n.bit_length() - 1
@@ -222,12 +269,33 @@ class WideFibonacciEval:
 class WideFibonacciComponent:
     """FrameworkComponent<WideFibonacciEval> (constraint_framework/index.ts:38-170) for the prover side."""
 
-    def __init__(self, evaluator: WideFibonacciEval):
-        self.evaluator = evaluator
+    def __init__(self, evaluator: WideFibonacciEval, trace_tree: int = 1, col_offset: int = 0):
+        self.evaluator, self.trace_tree, self.col_offset = evaluator, trace_tree, col_offset
 
     def nConstraints(self) -> int: return self.evaluator.nConstraints()
     def maxConstraintLogDegreeBound(self) -> int: return self.evaluator.maxConstraintLogDegreeBound()
     def getEvaluator(self): return self.evaluator
+
+    def traceLogDegreeBounds(self):
+        """TreeVec [preprocessed, main trace] of column log degree bounds (constraint_framework/index.ts:97-106)."""
+        return [[], [self.evaluator.logSize()] * self.evaluator.sequenceLength]
+
+    def maskPoints(self, point):
+        """Every column is read at offset 0 only (constraint_framework/index.ts:108-114)."""
+        return [[], [[point] for _ in range(self.evaluator.sequenceLength)]]
+
+    def evaluateConstraintQuotientsAtPoint(self, point, mask, accumulator: PointEvaluationAccumulator) -> None:
+        """constraint_framework/index.ts:120-129 with Stwo's PointEvaluator: accumulate(denom_inverse * constraint) per constraint,
+        denom = coset_vanishing(CanonicCoset(log).coset, point).  mask[tree][column] = sampled values of that column."""
+        ev = self.evaluator
+        cols = mask[self.trace_tree][self.col_offset:self.col_offset + ev.sequenceLength]
+        denom_inv = qm31_inv(coset_vanishing_secure(CanonicCoset.new(ev.logSize()).coset, point))
+        a, b = list(cols[0][0]), list(cols[1][0])
+        for k in range(2, ev.sequenceLength):
+            c = list(cols[k][0])
+            constraint = qm31_sub(c, qm31_add(qm31_mul(a, a), qm31_mul(b, b)))
+            accumulator.accumulate(qm31_mul(denom_inv, constraint))
+            a, b = b, c
 
     def denominator_inverses(self) -> List[int]:
         """1 / coset_vanishing(trace coset, eval_domain.at(i)), i < 2^log_expand, bit-reversed (Stwo component.rs)."""
@@ -237,14 +305,23 @@ class WideFibonacciComponent:
         n = 1 << (ev.maxConstraintLogDegreeBound() - ev.logSize())
         return bit_reverse_list([pow(coset_vanishing(trace_coset, eval_domain.at(i)), P - 2, P) for i in range(n)])
 
-    def evaluateConstraintQuotientsOnDomain(self, trace_polys: Sequence[_b.CudaCirclePoly], accumulator: DomainEvaluationAccumulator,
-                                            twiddles=None) -> None:
-        """trace_polys: the interpolated trace columns.  Evaluates them on CanonicCoset(log + 1), then one kernel adds
-        denom_inv * sum_i alpha^(N-1-i) constraint_i into the accumulator's column of that size."""
+    def evaluateConstraintQuotientsOnDomain(self, trace, accumulator: DomainEvaluationAccumulator, twiddles=None) -> None:
+        """trace: the interpolated trace columns, or a Trace (polys / evals per tree, prover.py) of which this component reads
+        its span of the main-trace tree.  Committed evaluations on CanonicCoset(log + 1) are used as they are (blow-up 2);
+        otherwise the polynomials are evaluated there.  One kernel then adds denom_inv * sum_i alpha^(N-1-i) constraint_i into
+        the accumulator's column of that size."""
         ev = self.evaluator
+        eval_log = ev.maxConstraintLogDegreeBound()
+        span = slice(self.col_offset, self.col_offset + ev.sequenceLength)
+        if hasattr(trace, "polys"):
+            evals = trace.evals[self.trace_tree][span]
+            if len(evals) == ev.sequenceLength and all(e.values.len() == 1 << eval_log for e in evals):
+                return self.evaluate_on_evals(evals, accumulator)
+            trace_polys = trace.polys[self.trace_tree][span]
+        else:
+            trace_polys = list(trace)
         if len(trace_polys) != ev.sequenceLength:
             raise ValueError("trace width does not match the sequence length")
-        eval_log = ev.maxConstraintLogDegreeBound()
         domain = CanonicCoset.new(eval_log).circle_domain()
         tw = twiddles or _b.CudaBackend.precomputeTwiddles(domain.halfCoset)
         evals = _b.CudaBackend.evaluatePolynomialsOnDomain(list(trace_polys), domain, tw)
