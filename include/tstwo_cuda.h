@@ -68,6 +68,15 @@ int tstwo_bit_reverse(tstwo_dptr col, uint64_t len);                     /* Colu
  * column values one index at a time; here the caller lists the device addresses (layer + 32 j, column + 4 i) and one
  * launch gathers words_each consecutive u32 from each into host_out[n * words_each]. */
 int tstwo_gather_words(const tstwo_dptr *addrs, int n, int words_each, uint32_t *host_out);
+/* MerkleProver.decommit (vcs/prover.ts:32-109) on a tree written by tstwo_merkle_commit (root first: layer k at byte
+ * 32 (2^k - 1) of `tree`, max_log = its deepest layer).  cols / col_logs: the committed columns in the caller's order (taken
+ * largest first, stable, as the reference sorts them).  Queries: sorted positions of the columns of log size l at
+ * query_positions[query_offsets[l] .. query_offsets[l+1]), l = 0..max_log (max_log + 2 offsets).  counts = {queried values,
+ * witness hashes, witness column values}.  Called with the three output pointers NULL it only sizes; otherwise the outputs
+ * (host) must hold counts[0] words, 32 counts[1] bytes and counts[2] words. */
+int tstwo_merkle_decommit(tstwo_dptr tree, int max_log, const tstwo_dptr *cols, const int *col_logs, int n_cols,
+                          const int *query_offsets, const uint32_t *query_positions, uint32_t *queried_values,
+                          uint8_t *hash_witness, uint32_t *column_witness, uint64_t counts[3]);
 
 /* ---- PolyOps  (poly/circle/ops.ts:20-66; impl backend/cpu/circle.ts:17-239) -------------------------------- */
 /* precomputeTwiddles(coset): backend/cpu/circle.ts:210-239.  The tree holds 2^log words of twiddles+itwiddles. */

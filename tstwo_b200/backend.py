@@ -104,7 +104,7 @@ class CudaColumn:
         return CudaColumn(self.ptr + 4 * off, length, owner=self)
 
     def __del__(self):
-        if getattr(self, "_owns", False) and self.ptr and _lib._lib is not None:
+        if getattr(self, "_owns", False) and self.ptr and _lib is not None and _lib._lib is not None:   # module globals go first at exit
             try:
                 _lib._lib.tstwo_free(self.ptr)
             except Exception:
@@ -158,7 +158,7 @@ class TwiddleTree:
         return CudaColumn.view(self._info()[1], self.rootCoset.size(), self)
 
     def __del__(self):
-        if self.handle and _lib._lib is not None:
+        if self.handle and _lib is not None and _lib._lib is not None:
             try:
                 _lib._lib.tstwo_twiddles_free(self.handle)
             except Exception:
@@ -297,6 +297,10 @@ class MerkleProver:
         """vcs/prover.ts:32-109: (queried values, MerkleDecommitment) for sorted query positions per column log size.
         Which hashes and values go into the witness depends on the queries only, so the tree walk runs on the host and
         the witness itself is collected from device memory by two gather launches (tstwo_gather_words)."""
+        max_log = len(self.layers) - 1
+        base = self.layers[0].ptr
+        if all(self.layers[k].ptr == base + 32 * ((1 << k) - 1) for k in range(max_log + 1)):
+            return self._decommit_native(queriesPerLogSize, list(columns), base, max_log)
         cols = sorted(columns, key=lambda c: -c.len())          # stable, as Array.prototype.sort in the reference
         col_i = 0
         hash_addrs: List[int] = []                              # device address of every witness hash, in order
@@ -342,6 +346,33 @@ class MerkleProver:
             check(_L().tstwo_gather_words(dptr_array(value_addrs), len(value_addrs), 1, values.ctypes.data_as(C.POINTER(C.c_uint32))))
         mask = np.array(value_is_query, dtype=bool)
         return values[mask], MerkleDecommitment([h.tobytes() for h in hashes], values[~mask])
+
+
+    def _decommit_native(self, queriesPerLogSize, columns, base: int, max_log: int):
+        """The same walk inside the library (tstwo_merkle_decommit): one call, two gather launches, one synchronisation."""
+        offsets, flat = [0], []
+        for log in range(max_log + 1):
+            direct = list(queriesPerLogSize.get(log, ()) or ())
+            if direct and max(direct) >> log:
+                raise IndexError(f"MerkleProver.decommit: query {max(direct)} is outside layer {log}")
+            flat.extend(direct); offsets.append(len(flat))
+        logs = []
+        for c in columns:
+            n = c.len()
+            if n == 0 or n & (n - 1) or n.bit_length() - 1 > max_log:
+                raise ValueError("column does not fit the tree")
+            logs.append(n.bit_length() - 1)
+        L = _L()
+        args = (base, max_log, dptr_array([c.ptr for c in columns]), (C.c_int * max(1, len(logs)))(*logs), len(columns),
+                (C.c_int * len(offsets))(*offsets), u32_array(flat if flat else [0]))
+        counts = (C.c_uint64 * 3)()
+        check(L.tstwo_merkle_decommit(*args, None, None, None, counts))
+        queried = np.zeros(max(1, counts[0]), dtype=np.uint32)
+        hashes = np.zeros((max(1, counts[1]), 32), dtype=np.uint8)
+        witness = np.zeros(max(1, counts[2]), dtype=np.uint32)
+        check(L.tstwo_merkle_decommit(*args, queried.ctypes.data_as(C.POINTER(C.c_uint32)), hashes.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                      witness.ctypes.data_as(C.POINTER(C.c_uint32)), counts))
+        return queried[:counts[0]], MerkleDecommitment([h.tobytes() for h in hashes[:counts[1]]], witness[:counts[2]])
 
 
 class MerkleDecommitment:

@@ -149,6 +149,13 @@ int tstwo_init(int device)
     TS_CUDA(cudaStreamCreateWithFlags(&c.copy_stream, cudaStreamNonBlocking));
     c.stream = c.own_stream;
     TS_CUDA(cudaMalloc(&c.d_ptr_table, sizeof(uint64_t) * PTR_SLOTS * PTR_SLOT_CAP));
+    {   // temporaries of the gather / decommit calls come from the stream-ordered pool: keep what it holds across synchronisations
+        // (the default threshold 0 hands the memory back at every sync, ~0.3 ms per call afterwards)
+        cudaMemPool_t pool;
+        uint64_t keep = 256ull << 20;
+        TS_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+        TS_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     TS_CUDA(upload_gen_table());
     TS_CUDA(elementwise_init());
     c.launches = 0;
@@ -328,6 +335,77 @@ int tstwo_gather_words(const tstwo_dptr *addrs, int n, int words_each, uint32_t 
     TS_CUDA(cudaFreeAsync(d_addrs, c.stream));
     TS_CUDA(cudaFreeAsync(d_out, c.stream));
     TS_CUDA(cudaStreamSynchronize(c.stream));
+    return 0;
+}
+// MerkleProver.decommit (vcs/prover.ts:32-109) in one call: the walk over the query tree on the host (nextDecommitmentNode,
+// vcs/utils.ts:40-57), then one gather launch for the witness hashes and one for the column values, one synchronisation.
+int tstwo_merkle_decommit(tstwo_dptr tree, int max_log, const tstwo_dptr *cols, const int *col_logs, int n_cols, const int *query_offsets,
+                          const uint32_t *query_positions, uint32_t *queried_values, uint8_t *hash_witness, uint32_t *column_witness,
+                          uint64_t counts[3])
+{
+    TS_REQUIRE_INIT();
+    if (!tree || max_log < 0 || max_log > 30 || n_cols < 0 || !query_offsets || !counts) return fail(TSTWO_ERR_BAD_ARG, "bad decommit arguments");
+    for (int k = 0; k < n_cols; k++)
+        if (col_logs[k] < 0 || col_logs[k] > max_log || !cols[k]) return fail(TSTWO_ERR_BAD_ARG, "column %d does not fit the tree", k);
+    // columns by size, largest first, stable (Array.prototype.sort in the reference)
+    std::vector<std::vector<int>> by_log(max_log + 1);
+    for (int k = 0; k < n_cols; k++) by_log[col_logs[k]].push_back(k);
+    std::vector<uint64_t> hash_addrs, value_addrs;
+    std::vector<uint8_t> value_is_query;
+    std::vector<uint32_t> last, nxt;
+    for (int log = max_log; log >= 0; log--) {
+        const uint32_t *direct = query_positions + query_offsets[log];
+        const size_t n_direct = (size_t)(query_offsets[log + 1] - query_offsets[log]);
+        const bool has_child = log < max_log;
+        const uint64_t child_base = tree + 32ull * ((2ull << log) - 1);   // layer log + 1
+        size_t pi = 0, di = 0;
+        nxt.clear();
+        while (pi < last.size() || di < n_direct) {
+            uint32_t node = 0xffffffffu;
+            if (pi < last.size()) node = last[pi] >> 1;
+            if (di < n_direct && direct[di] < node) node = direct[di];
+            if (has_child)
+                for (uint32_t ch = 2 * node; ch <= 2 * node + 1; ch++) {
+                    if (pi < last.size() && last[pi] == ch) pi++;       // the verifier recomputes this child itself
+                    else hash_addrs.push_back(child_base + 32ull * ch);
+                }
+            const bool queried = di < n_direct && direct[di] == node;
+            if (queried) di++;
+            if (node >> log) return fail(TSTWO_ERR_BAD_ARG, "MerkleProver.decommit: query %u is outside layer %d", node, log);
+            for (int k : by_log[log]) { value_addrs.push_back(cols[k] + 4ull * node); value_is_query.push_back(queried); }
+            nxt.push_back(node);
+        }
+        last.swap(nxt);
+    }
+    uint64_t n_q = 0;
+    for (uint8_t q : value_is_query) n_q += q;
+    counts[0] = n_q; counts[1] = hash_addrs.size(); counts[2] = value_addrs.size() - n_q;
+    if (!queried_values && !hash_witness && !column_witness) return 0;      // sizing call
+    if ((n_q && !queried_values) || (counts[1] && !hash_witness) || (counts[2] && !column_witness))
+        return fail(TSTWO_ERR_BAD_ARG, "decommit output buffer missing");
+    const size_t nh = hash_addrs.size(), nv = value_addrs.size();
+    if (nh + nv == 0) return 0;
+    Context &c = ctx();
+    uint64_t *d_addrs = nullptr;
+    uint32_t *d_out = nullptr;
+    std::vector<uint64_t> addrs(hash_addrs);
+    addrs.insert(addrs.end(), value_addrs.begin(), value_addrs.end());
+    std::vector<uint32_t> words(8 * nh + nv);
+    TS_CUDA(cudaMallocAsync(&d_addrs, sizeof(uint64_t) * addrs.size(), c.stream));
+    TS_CUDA(cudaMallocAsync(&d_out, 4 * words.size(), c.stream));
+    TS_CUDA(cudaMemcpyAsync(d_addrs, addrs.data(), sizeof(uint64_t) * addrs.size(), cudaMemcpyHostToDevice, c.stream));
+    if (nh) TS_LAUNCH(gather_words_kernel, (unsigned)((8 * nh + 255) / 256), 256, 0, d_addrs, (uint64_t)8 * nh, 8, d_out);
+    if (nv) TS_LAUNCH(gather_words_kernel, (unsigned)((nv + 255) / 256), 256, 0, d_addrs + nh, (uint64_t)nv, 1, d_out + 8 * nh);
+    TS_CUDA(cudaMemcpyAsync(words.data(), d_out, 4 * words.size(), cudaMemcpyDeviceToHost, c.stream));
+    TS_CUDA(cudaFreeAsync(d_addrs, c.stream));
+    TS_CUDA(cudaFreeAsync(d_out, c.stream));
+    TS_CUDA(cudaStreamSynchronize(c.stream));
+    if (nh) memcpy(hash_witness, words.data(), 32 * nh);
+    size_t qi = 0, wi = 0;
+    for (size_t k = 0; k < nv; k++) {
+        if (value_is_query[k]) queried_values[qi++] = words[8 * nh + k];
+        else column_witness[wi++] = words[8 * nh + k];
+    }
     return 0;
 }
 int tstwo_bit_reverse(tstwo_dptr col, uint64_t len)
