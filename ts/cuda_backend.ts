@@ -35,6 +35,7 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   // decommitment witnesses, proof of work, Stwo-correct DEEP quotients (callers: MerkleProver.decommit, FriProver.decommit, prove_values)
   tstwo_gather_words: { args: [T.ptr, T.i32, T.i32, T.ptr], returns: T.i32 },
   tstwo_grind: { args: [T.ptr, T.u32, T.ptr], returns: T.i32 },
+  tstwo_merkle_decommit: { args: [T.u64, T.i32, T.ptr, T.ptr, T.i32, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr], returns: T.i32 },
   tstwo_accumulate_quotients_ex: { args: [T.i32, T.u32, T.ptr, T.i32, T.ptr, T.i32, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr, T.u32], returns: T.i32 },
   // wide-Fibonacci constraint quotients over the evaluation domain (ComponentProver.evaluateConstraintQuotientsOnDomain); allocator trim
   tstwo_widefib_constraints: { args: [T.i32, T.i32, T.ptr, T.i32, T.ptr, T.ptr, T.ptr], returns: T.i32 },
@@ -152,4 +153,22 @@ export function wideFibonacciConstraintQuotients(logSize: number, evals: CudaCol
   const cols = BigUint64Array.from(evals.map((c) => c.dptr));
   const out = BigUint64Array.from(accCoords.map((c) => c.dptr));
   check(lib.tstwo_widefib_constraints(logSize, logSize + 1, ptr(cols), evals.length, ptr(coeffs), ptr(denomInv), ptr(out)));
+}
+
+// MerkleProver.decommit (vcs/prover.ts:32-109) for a tree written by tstwo_merkle_commit: queriesPerLogSize as in the reference.
+export function merkleDecommit(tree: bigint, maxLog: number, columns: CudaColumn[], queriesPerLogSize: Map<number, number[]>):
+    { queried: Uint32Array; hashWitness: Uint8Array[]; columnWitness: Uint32Array } {
+  const offsets = new Int32Array(maxLog + 2), flat: number[] = [];
+  for (let log = 0; log <= maxLog; log++) { flat.push(...(queriesPerLogSize.get(log) ?? [])); offsets[log + 1] = flat.length; }
+  const cols = BigUint64Array.from(columns.map((c) => c.dptr)), logs = Int32Array.from(columns.map((c) => Math.log2(c.length)));
+  const positions = Uint32Array.from(flat.length ? flat : [0]), counts = new BigUint64Array(3);
+  const call = (q: Uint32Array | null, h: Uint8Array | null, w: Uint32Array | null) =>
+    check(lib.tstwo_merkle_decommit(tree, maxLog, ptr(cols), ptr(logs), columns.length, ptr(offsets), ptr(positions),
+                                    q ? ptr(q) : null, h ? ptr(h) : null, w ? ptr(w) : null, ptr(counts)));
+  call(null, null, null);                                          // sizing pass
+  const queried = new Uint32Array(Math.max(1, Number(counts[0]))), hashes = new Uint8Array(Math.max(1, 32 * Number(counts[1])));
+  const witness = new Uint32Array(Math.max(1, Number(counts[2])));
+  call(queried, hashes, witness);
+  const hashWitness = Array.from({ length: Number(counts[1]) }, (_, i) => hashes.slice(32 * i, 32 * i + 32));
+  return { queried: queried.subarray(0, Number(counts[0])), hashWitness, columnWitness: witness.subarray(0, Number(counts[2])) };
 }
