@@ -311,6 +311,37 @@ def run_cuda(args):
         e2e = {"value": n_cols * n / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "h2d_bytes_per_step": n_cols * n * 4,
                "d2h_bytes_per_step": 32, "api": "tstwo_lde_commit_host (C ABI, pinned host trace -> root)"}
 
+    # ---- end to end at N > 1: every rank's column shard starts in pinned HOST memory and crosses its own PCIe link inside the
+    # timed region (in column groups, overlapped with the transforms and the NVLink exchange); rank 0 reads the root back
+    if world > 1 and not args.no_e2e and args.exchange == "peer":
+        host = torch.empty((lc, n), dtype=torch.int32, pin_memory=True)
+        host.copy_(trace.cpu())
+        stage = torch.empty((lc, n), dtype=torch.int32, device=dev)
+        got = {}
+
+        def e2e_step():
+            r = sc.step_from_host(host, stage)
+            if r is not None:
+                got["root"] = r
+            else:
+                chk(L.tstwo_sync())
+        for _ in range(3):
+            e2e_step()
+        k = max(3, min(args.steps, 5))
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(k):
+            e2e_step()
+        barrier()
+        dt = torch.tensor([(time.perf_counter() - t0) / k], device=dev, dtype=torch.float64)
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        dt = float(dt.item())
+        if rank == 0:
+            assert got["root"].hex() == root_hex, "e2e root differs from device-resident root"
+        e2e = {"value": n_cols * n / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "h2d_bytes_per_step": n_cols * n * 4,
+               "d2h_bytes_per_step": 32,
+               "api": f"PeerShardedCommit.step_from_host (pinned host shard per rank -> root on rank 0), {world} PCIe links"}
+
     if rank == 0:
         cpu = None if args.no_cpu or world > 1 else cpu_baseline(args)
         out = {

@@ -124,6 +124,7 @@ class PeerShardedCommit:
         self.L = _lib.init(device_index)
         chk = _lib.check
         self.dev = torch.device("cuda", device_index)
+        self._stream = stream
         if stream is not None:
             chk(self.L.tstwo_set_stream(C.c_void_p(stream.cuda_stream)))
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
@@ -172,6 +173,10 @@ class PeerShardedCommit:
         chk(self.L.tstwo_lde_columns_to_peers(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw,
                                               self.coeffs.data_ptr() if self.coeffs is not None else 0, self.work.data_ptr(),
                                               self._bases_arr, self.world, self.rank * self.lc, 0))
+        return self._finish()
+
+    def _finish(self):
+        chk = self._lib_mod.check
         dist.all_reduce(self.flag)                 # every rank's stores into my leaf buffer are complete after this
         rows = 1 << self.sub
         ptrs = self._lib_mod.dptr_array([self.recv_ptr + 4 * rows * c for c in range(self.n_cols)])
@@ -182,6 +187,32 @@ class PeerShardedCommit:
             self.top = top_layers(self.ops, self.roots, self.world)
             return self.ops.to_host_bytes(self.top[-1] if self.top else self.roots)[:32]
         return None
+
+    def step_from_host(self, host: torch.Tensor, staging: torch.Tensor, chunks: int = 4):
+        """The same step with this rank's columns in pinned HOST memory (`host`, (n_cols/G, 2^log) int32): the columns cross PCIe
+        in `chunks` groups on a copy stream and each group's LDE + peer stores start as soon as it has landed, so the transfer
+        of the later groups overlaps the transforms and the NVLink exchange of the earlier ones."""
+        chk = self._lib_mod.check
+        main = self._stream if self._stream is not None else torch.cuda.current_stream()
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream(device=self.dev)
+        cs = self._copy_stream
+        chunks = max(1, min(chunks, self.lc))
+        while self.lc % chunks:
+            chunks -= 1
+        per, n = self.lc // chunks, 1 << self.log_size
+        cs.wait_stream(main)                       # the staging buffer is free once the previous step's transforms are done
+        for k in range(chunks):
+            with torch.cuda.stream(cs):
+                staging[k * per:(k + 1) * per].copy_(host[k * per:(k + 1) * per], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+            main.wait_event(ev)
+            chk(self.L.tstwo_lde_columns_to_peers(staging.data_ptr() + 4 * n * k * per, per, self.log_size, self.blow, self.tw,
+                                                  self.coeffs.data_ptr() + 4 * n * k * per if self.coeffs is not None else 0,
+                                                  self.work.data_ptr() + 4 * ((k * per) << self.ext),
+                                                  self._bases_arr, self.world, self.rank * self.lc + k * per, 0))
+        return self._finish()
 
     def close(self):
         torch.cuda.synchronize()
