@@ -95,6 +95,10 @@ int tstwo_evaluate_columns(const tstwo_dptr *coeffs, int poly_log, const tstwo_d
                            int domain_log, uint32_t half_coset_initial_index, tstwo_twiddles tw, uint32_t flags);
 /* CpuCirclePoly.eval_at_point (circle.ts:52-69): point = CirclePoint<SecureField>. */
 int tstwo_eval_at_point(tstwo_dptr coeffs, int log_size, const uint32_t px[4], const uint32_t py[4], uint32_t out[4]);
+/* The same for n_polys polynomials of one size at one point (the sampled values of a commitment tree): one batch of launches,
+ * out = n_polys x 4 words. */
+int tstwo_eval_at_point_many(const tstwo_dptr *coeffs, int n_polys, int log_size, const uint32_t px[4], const uint32_t py[4],
+                             uint32_t *out);
 
 /* ---- MerkleOps<Blake2sHash>  (vcs/ops.ts:16-26; vcs/blake2_merkle.ts:9-24; backend/cpu/blake2.ts:98-127) --- */
 /* commitOnLayer(logSize, prevLayer, columns): out_layer = 2^log_size hashes (32 B each); prev_layer = 0 or the

@@ -36,11 +36,13 @@ def test_twiddles_non_canonic(tb, orc):
 
 def test_bit_reverse(tb, orc):
     rng = np.random.default_rng(0)
-    for log in [0, 1, 5, 13]:
+    for log in [0, 1, 5, 11, 12, 13, 14, 17, 20]:      # 12 and up: the tiled kernel (odd and even numbers of middle bits, palindromic tiles)
         a = rng.integers(0, P, 1 << log, dtype=np.uint32)
         col = tb.CudaColumn.from_cpu(a)
         tb.CudaBackend.bitReverseColumn(col)
         assert (col.toCpu() == orc.bit_reverse(a)).all()
+        tb.CudaBackend.bitReverseColumn(col)                 # an involution
+        assert (col.toCpu() == a).all()
     with pytest.raises(ValueError):
         tb.CudaBackend.bitReverseColumn(tb.CudaColumn.from_cpu(np.zeros(6, dtype=np.uint32)))
 
@@ -193,6 +195,21 @@ def test_eval_at_point(tb, orc, log):
     px = [int(v) for v in rng.integers(0, P, 4)]; py = [int(v) for v in rng.integers(0, P, 4)]
     got = tb.CudaCirclePoly.eval_at_point(tb.CudaCirclePoly.new(coeffs), (px, py))
     assert got == orc.eval_at_point(coeffs, px, py)
+
+
+def test_eval_many_at_point(tb, orc):
+    """Batched form: mixed sizes (grouped per size), more polynomials than one pass holds at the largest size."""
+    rng = np.random.default_rng(77)
+    logs = [0, 3, 3, 7, 12, 12, 12, 5, 16, 16, 1]
+    coeffs = [rng.integers(0, P, 1 << l, dtype=np.uint32) for l in logs]
+    px = [int(v) for v in rng.integers(0, P, 4)]; py = [int(v) for v in rng.integers(0, P, 4)]
+    got = tb.CudaCirclePoly.eval_many_at_point([tb.CudaCirclePoly.new(c) for c in coeffs], (px, py))
+    assert got == [orc.eval_at_point(c, px, py) for c in coeffs]
+    assert tb.CudaCirclePoly.eval_many_at_point([], (px, py)) == []
+    big = [tb.CudaCirclePoly.new(rng.integers(0, P, 1 << 22, dtype=np.uint32)) for _ in range(50)]     # 6 MiB of scratch each, 256 MiB per pass: 2 passes
+    got = tb.CudaCirclePoly.eval_many_at_point(big, (px, py))
+    assert got == [tb.CudaCirclePoly.eval_at_point(p, (px, py)) for p in big]
+    assert got[7] == orc.eval_at_point(big[7].coeffs.toCpu(), px, py)
 
 
 def test_column_interface(tb):

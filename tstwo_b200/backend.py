@@ -198,6 +198,21 @@ class CudaCirclePoly:
         return list(out)
 
     @staticmethod
+    def eval_many_at_point(polys: Sequence["CudaCirclePoly"], point) -> List[List[int]]:
+        """eval_at_point of several polynomials at one point: one batch of launches per polynomial size (tstwo_eval_at_point_many)."""
+        out: List[Optional[List[int]]] = [None] * len(polys)
+        by_log = {}
+        for i, p in enumerate(polys):
+            by_log.setdefault(p.logSize(), []).append(i)
+        for log, idxs in by_log.items():
+            res = (C.c_uint32 * (4 * len(idxs)))()
+            check(_L().tstwo_eval_at_point_many(dptr_array([polys[i].coeffs.ptr for i in idxs]), len(idxs), log, u32_array(point[0]),
+                                                u32_array(point[1]), res))
+            for k, i in enumerate(idxs):
+                out[i] = list(res[4 * k:4 * k + 4])
+        return out
+
+    @staticmethod
     def extend(poly: "CudaCirclePoly", log_size: int) -> "CudaCirclePoly":
         if log_size < poly.logSize():
             raise ValueError("log size too small")

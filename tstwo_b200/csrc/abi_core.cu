@@ -59,6 +59,36 @@ __global__ void bit_reverse_kernel(uint32_t *a, int log_n)
     if (j > i) { uint32_t t = a[i]; a[i] = a[j]; a[j] = t; }
 }
 
+// Tiled form for 2^k >= 2^12 elements.  Index = (a : 6 high bits | m : k - 12 middle bits | b : 6 low bits); its bit reversal is
+// (rev b | rev m | rev a), so the 64 x 64 tile of all (a, b) with middle bits m goes, transposed and with a and b reversed, into the
+// tile with middle bits rev(m).  One CTA swaps the pair of tiles (m, rev m) through shared memory: every global access is a run
+// of 64 consecutive words (256 B) instead of one scattered word per thread.
+constexpr int BR_T = 6, BR_DIM = 1 << BR_T, BR_PAD = BR_DIM + 1;
+__global__ void __launch_bounds__(256) bit_reverse_tiled_kernel(uint32_t *__restrict__ a, int log_n)
+{
+    __shared__ uint32_t sa[BR_DIM * BR_PAD], sb[BR_DIM * BR_PAD];
+    const int mid_bits = log_n - 2 * BR_T;
+    const uint32_t m = blockIdx.x, mr = mid_bits ? m31::bitrev(m, mid_bits) : 0u;
+    if (m > mr) return;
+    const int col = threadIdx.x & (BR_DIM - 1), row0 = threadIdx.x >> BR_T;      // 4 rows per sweep of 256 threads
+    uint32_t *ta = a + ((uint64_t)m << BR_T), *tb = a + ((uint64_t)mr << BR_T);
+    const uint64_t row_stride = 1ull << (log_n - BR_T);
+#pragma unroll 4
+    for (int r = row0; r < BR_DIM; r += 4) {
+        sa[r * BR_PAD + col] = ta[r * row_stride + col];
+        if (m != mr) sb[r * BR_PAD + col] = tb[r * row_stride + col];
+    }
+    __syncthreads();
+    const int cr = (int)(__brev((unsigned)col) >> (32 - BR_T));
+#pragma unroll 4
+    for (int r = row0; r < BR_DIM; r += 4) {
+        const int rr = (int)(__brev((unsigned)r) >> (32 - BR_T));
+        // output (row r, column col) of tile rev(m) <- input (row rev(col), column rev(r)) of tile m
+        tb[r * row_stride + col] = sa[cr * BR_PAD + rr];
+        if (m != mr) ta[r * row_stride + col] = sb[cr * BR_PAD + rr];
+    }
+}
+
 // ---------------------------------------------------------------- twiddles (backend/cpu/circle.ts:210-239)
 
 // One thread per entry e of the 2^log tree buffer.  Layer i holds bitrev(x of first half of the i-times doubled
@@ -415,7 +445,10 @@ int tstwo_bit_reverse(tstwo_dptr col, uint64_t len)
     int log_n = 0;
     while ((1ull << log_n) < len) log_n++;
     if (log_n > 31) return fail(TSTWO_ERR_BAD_ARG, "column too long");
-    TS_LAUNCH(bit_reverse_kernel, (unsigned)((len + 255) / 256), 256, 0, (uint32_t *)col, log_n);
+    if (log_n >= 2 * BR_T)
+        TS_LAUNCH(bit_reverse_tiled_kernel, 1u << (log_n - 2 * BR_T), 256, 0, (uint32_t *)col, log_n);
+    else
+        TS_LAUNCH(bit_reverse_kernel, (unsigned)((len + 255) / 256), 256, 0, (uint32_t *)col, log_n);
     return 0;
 }
 

@@ -84,6 +84,46 @@ __global__ void half_sums_kernel(CQ4 src, uint64_t n, unsigned long long *sums)
     __syncthreads();
     if (threadIdx.x < 8) atomicAdd(&sums[threadIdx.x], sh[threadIdx.x]);
 }
+// the same for n >= 8 with 16-byte loads (a uint4 never straddles the halves), 4 loads in flight per thread
+__global__ void __launch_bounds__(256) half_sums_vec_kernel(CQ4 src, uint64_t n4, unsigned long long *sums)
+{
+    __shared__ unsigned long long sh[8];
+    if (threadIdx.x < 8) sh[threadIdx.x] = 0;
+    __syncthreads();
+    unsigned long long acc[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+    const uint64_t half4 = n4 / 2;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (uint64_t)gridDim.x * blockDim.x) {
+        const int hi = i >= half4;
+        uint4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) v[k] = __ldcs(reinterpret_cast<const uint4 *>(src.c[k]) + i);
+#pragma unroll
+        for (int k = 0; k < 4; k++) acc[2 * k + hi] += (unsigned long long)v[k].x + v[k].y + v[k].z + v[k].w;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        unsigned long long v = acc[k];
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(&sh[k], v);
+    }
+    __syncthreads();
+    if (threadIdx.x < 8) atomicAdd(&sums[threadIdx.x], sh[threadIdx.x]);
+}
+__global__ void __launch_bounds__(256) decompose_apply_vec_kernel(CQ4 src, Q4 g, uint64_t n4, m31::QM lambda)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    const bool second = i >= n4 / 2;
+    const uint32_t lam[4] = { lambda.a, lambda.b, lambda.c, lambda.d };
+    uint4 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[k] = __ldcs(reinterpret_cast<const uint4 *>(src.c[k]) + i);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint32_t l = second ? lam[k] : m31::sub(0, lam[k]);     // f + lambda on the second half, f - lambda on the first
+        reinterpret_cast<uint4 *>(g.c[k])[i] = make_uint4(m31::add(v[k].x, l), m31::add(v[k].y, l), m31::add(v[k].z, l), m31::add(v[k].w, l));
+    }
+}
 // backend/cpu/fri.ts:133-164: g = f - lambda on the first half, f + lambda on the second
 __global__ void decompose_apply_kernel(CQ4 src, Q4 g, uint64_t n, m31::QM lambda)
 {
@@ -474,16 +514,28 @@ __global__ void __launch_bounds__(QM_WARPS * 32, 3) widefib_mma_kernel(int trace
 // eval_at_point (backend/cpu/circle.ts:52-69, poly/utils.ts:36-59 fold): bottom-up pairwise folding, 4 levels
 // (16 values) per thread.  Level l combines (w[2k], w[2k+1]) -> w[2k] + f_l w[2k+1]; f_0 = y, f_1 = x, f_2 = pi(x)...
 struct FoldFactors { m31::QM f[32]; };
-__global__ void fold_base_kernel(const uint32_t *coeffs, uint64_t n_out, int levels, FoldFactors ff, uint32_t *out)
+// blockIdx.y = polynomial of the batch; out / in of polynomial p at + p * stride words
+__global__ void fold_base_kernel(ColSet polys, uint64_t n_out, int levels, FoldFactors ff, uint32_t *out, uint64_t out_stride)
 {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_out) return;
     const int cnt = 1 << levels;   // <= 16
     m31::QM w[8];
-    const uint32_t *c = coeffs + t * cnt;
+    const uint32_t *c = polys.col(blockIdx.y) + t * cnt;
+    uint32_t v[16];
+    if (levels == 4) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint4 q = __ldcs(reinterpret_cast<const uint4 *>(c) + k);
+            v[4 * k] = q.x; v[4 * k + 1] = q.y; v[4 * k + 2] = q.z; v[4 * k + 3] = q.w;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; k++) v[k] = k < cnt ? c[k] : 0u;
+    }
 #pragma unroll
     for (int k = 0; k < 8; k++)
-        if (2 * k + 1 < cnt) w[k] = m31::qadd(m31::qfrom(c[2 * k]), m31::qmul_m(ff.f[0], c[2 * k + 1]));
+        if (2 * k + 1 < cnt) w[k] = m31::qadd(m31::qfrom(v[2 * k]), m31::qmul_m(ff.f[0], v[2 * k + 1]));
 #pragma unroll
     for (int l = 1; l < 4; l++)
         if (l < levels) {
@@ -491,15 +543,17 @@ __global__ void fold_base_kernel(const uint32_t *coeffs, uint64_t n_out, int lev
             for (int k = 0; k < (8 >> l); k++)
                 if (k < (cnt >> (l + 1))) w[k] = m31::qadd(w[2 * k], m31::qmul(ff.f[l], w[2 * k + 1]));
         }
-    out[4 * t] = w[0].a; out[4 * t + 1] = w[0].b; out[4 * t + 2] = w[0].c; out[4 * t + 3] = w[0].d;
+    out += blockIdx.y * out_stride;
+    reinterpret_cast<uint4 *>(out)[t] = make_uint4(w[0].a, w[0].b, w[0].c, w[0].d);
 }
-__global__ void fold_qm_kernel(const uint32_t *in, uint64_t n_out, int levels, int level0, FoldFactors ff, uint32_t *out)
+__global__ void fold_qm_kernel(const uint32_t *in, uint64_t in_stride, uint64_t n_out, int levels, int level0, FoldFactors ff, uint32_t *out,
+                               uint64_t out_stride)
 {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_out) return;
     const int cnt = 1 << levels;   // <= 16
     m31::QM w[16];
-    const uint4 *c = reinterpret_cast<const uint4 *>(in) + t * cnt;
+    const uint4 *c = reinterpret_cast<const uint4 *>(in + blockIdx.y * in_stride) + t * cnt;
 #pragma unroll
     for (int k = 0; k < 16; k++)
         if (k < cnt) { uint4 a = c[k]; w[k] = { a.x, a.y, a.z, a.w }; }
@@ -510,7 +564,8 @@ __global__ void fold_qm_kernel(const uint32_t *in, uint64_t n_out, int levels, i
             for (int k = 0; k < (8 >> l); k++)
                 if (k < (cnt >> (l + 1))) w[k] = m31::qadd(w[2 * k], m31::qmul(ff.f[level0 + l], w[2 * k + 1]));
         }
-    out[4 * t] = w[0].a; out[4 * t + 1] = w[0].b; out[4 * t + 2] = w[0].c; out[4 * t + 3] = w[0].d;
+    out += blockIdx.y * out_stride;
+    reinterpret_cast<uint4 *>(out)[t] = make_uint4(w[0].a, w[0].b, w[0].c, w[0].d);
 }
 
 static m31::QM to_dev(const uint32_t a[4]) { return { a[0], a[1], a[2], a[3] }; }
@@ -605,9 +660,12 @@ int tstwo_fri_decompose(const tstwo_dptr src[4], int log_size, const tstwo_dptr 
     if (rc) return rc;
     unsigned long long *sums = (unsigned long long *)tmp;
     TS_CUDA(cudaMemsetAsync(sums, 0, 64, ctx().stream));
-    unsigned grid = (unsigned)((n + 255) / 256);
+    bool vec = n >= 8;
+    for (int k = 0; k < 4; k++) vec = vec && !((src[k] | g[k]) & 15);
+    unsigned grid = (unsigned)(((vec ? n / 4 : n) + 255) / 256);
     if (grid > 148 * 8) grid = 148 * 8;
-    TS_LAUNCH(half_sums_kernel, grid, 256, 0, s, n, sums);
+    if (vec) TS_LAUNCH(half_sums_vec_kernel, grid, 256, 0, s, n / 4, sums);
+    else TS_LAUNCH(half_sums_kernel, grid, 256, 0, s, n, sums);
     unsigned long long h[8];
     TS_CUDA(cudaMemcpyAsync(h, sums, 64, cudaMemcpyDeviceToHost, ctx().stream));
     TS_CUDA(cudaStreamSynchronize(ctx().stream));
@@ -619,7 +677,8 @@ int tstwo_fri_decompose(const tstwo_dptr src[4], int log_size, const tstwo_dptr 
         if (n == 1) lam[k] = host::neg(b);
         else lam[k] = host::mul(host::sub(a, b), n_inv);
     }
-    TS_LAUNCH(decompose_apply_kernel, (unsigned)((n + 255) / 256), 256, 0, s, d, n, to_dev(lam));
+    if (vec) TS_LAUNCH(decompose_apply_vec_kernel, (unsigned)((n / 4 + 255) / 256), 256, 0, s, d, n / 4, to_dev(lam));
+    else TS_LAUNCH(decompose_apply_kernel, (unsigned)((n + 255) / 256), 256, 0, s, d, n, to_dev(lam));
     if (lambda) memcpy(lambda, lam, 16);
     return 0;
 }
@@ -826,13 +885,21 @@ int tstwo_widefib_constraints(int trace_log_size, int eval_log_size, const tstwo
 
 int tstwo_eval_at_point(tstwo_dptr coeffs, int log_size, const uint32_t px[4], const uint32_t py[4], uint32_t out[4])
 {
+    return tstwo_eval_at_point_many(&coeffs, 1, log_size, px, py, out);
+}
+
+int tstwo_eval_at_point_many(const tstwo_dptr *coeffs, int n_polys, int log_size, const uint32_t px[4], const uint32_t py[4], uint32_t *out)
+{
     TS_REQUIRE_INIT();
-    if (log_size < 0 || log_size > 30 || !out) return fail(TSTWO_ERR_BAD_ARG, "bad eval_at_point arguments");
+    if (log_size < 0 || log_size > 30 || n_polys < 0 || (n_polys && (!out || !coeffs))) return fail(TSTWO_ERR_BAD_ARG, "bad eval_at_point arguments");
+    if (n_polys == 0) return 0;
     if (log_size == 0) {
-        uint32_t c0;
-        int rc = tstwo_download(&c0, coeffs, 4);
-        if (rc) return rc;
-        out[0] = c0; out[1] = out[2] = out[3] = 0;
+        for (int p = 0; p < n_polys; p++) {
+            uint32_t c0;
+            int rc = tstwo_download(&c0, coeffs[p], 4);
+            if (rc) return rc;
+            out[4 * p] = c0; out[4 * p + 1] = out[4 * p + 2] = out[4 * p + 3] = 0;
+        }
         return 0;
     }
     FoldFactors ff;
@@ -843,24 +910,37 @@ int tstwo_eval_at_point(tstwo_dptr coeffs, int log_size, const uint32_t px[4], c
         host::QM sx = host::qmul(x, x);
         x = host::qsub(host::qadd(sx, sx), one);     // circle.ts:37-40 double_x
     }
-    uint32_t *buf;
     const uint64_t n = 1ull << log_size;
-    int lv = log_size < 4 ? log_size : 4;
-    uint64_t cnt = n >> lv;
-    int rc = scratch((cnt + (cnt >> 1) + 64) * 16, &buf);
+    const int lv = log_size < 4 ? log_size : 4;
+    const uint64_t cnt0 = n >> lv, per_poly = 4 * (cnt0 + (cnt0 >> 1) + 64);      // words of scratch per polynomial (two ping-pong buffers)
+    // polynomials per pass: at most 256 MiB of scratch, at most 65535 (gridDim.y), at most the pointer-table slot
+    uint64_t fit = (256ull << 20) / (per_poly * 4);
+    if (fit < 1) fit = 1;
+    if (fit > 4096) fit = 4096;
+    const int batch = (int)(fit < (uint64_t)n_polys ? fit : (uint64_t)n_polys);
+    uint32_t *buf;
+    int rc = scratch((uint64_t)batch * per_poly * 4, &buf);
     if (rc) return rc;
-    uint32_t *cur = buf, *nxt = buf + 4 * cnt;
-    TS_LAUNCH(fold_base_kernel, (unsigned)((cnt + 127) / 128), 128, 0, (const uint32_t *)coeffs, cnt, lv, ff, cur);
-    int level = lv;
-    while (cnt > 1) {
-        int rem = log_size - level;
-        int l = rem < 4 ? rem : 4;
-        uint64_t ncnt = cnt >> l;
-        TS_LAUNCH(fold_qm_kernel, (unsigned)((ncnt + 127) / 128), 128, 0, cur, ncnt, l, level, ff, nxt);
-        uint32_t *t = cur; cur = nxt; nxt = t;
-        cnt = ncnt; level += l;
+    for (int p0 = 0; p0 < n_polys; p0 += batch) {
+        const int nb = batch < n_polys - p0 ? batch : n_polys - p0;
+        ColSet cs;
+        if ((rc = make_colset(coeffs + p0, nb, 0, &cs))) return rc;
+        uint64_t cnt = cnt0;
+        uint32_t *cur = buf, *nxt = buf + 4 * cnt0;
+        TS_LAUNCH(fold_base_kernel, dim3((unsigned)((cnt + 127) / 128), nb), 128, 0, cs, cnt, lv, ff, cur, per_poly);
+        int level = lv;
+        while (cnt > 1) {
+            const int rem = log_size - level, l = rem < 4 ? rem : 4;
+            const uint64_t ncnt = cnt >> l;
+            TS_LAUNCH(fold_qm_kernel, dim3((unsigned)((ncnt + 127) / 128), nb), 128, 0, cur, per_poly, ncnt, l, level, ff, nxt, per_poly);
+            uint32_t *t = cur; cur = nxt; nxt = t;
+            cnt = ncnt; level += l;
+        }
+        // the results sit at cur + p * per_poly: one strided copy
+        TS_CUDA(cudaMemcpy2DAsync(out + 4 * (size_t)p0, 16, cur, per_poly * 4, 16, nb, cudaMemcpyDeviceToHost, ctx().stream));
+        TS_CUDA(cudaStreamSynchronize(ctx().stream));
     }
-    return tstwo_download(out, (tstwo_dptr)cur, 16);
+    return 0;
 }
 
 }  // extern "C"

@@ -89,8 +89,22 @@ class CommitmentSchemeProof:
 
 def prove_values(self: CommitmentSchemeProver, sampled_points, channel) -> CommitmentSchemeProof:
     """pcs/prover.ts:85-156 (Rust text).  sampled_points[tree][column] = list of points (x[4], y[4])."""
-    samples = [[[PointSample(pt, CudaCirclePoly.eval_at_point(poly, pt)) for pt in pts] for poly, pts in zip(tree.polynomials, tree_pts)]
-               for tree, tree_pts in zip(self.trees, sampled_points)]
+    # every (polynomial, point) pair, evaluated point by point in batches (tstwo_eval_at_point_many)
+    by_point: Dict[Point, List[Tuple[int, int, int]]] = {}
+    for ti, (tree, tree_pts) in enumerate(zip(self.trees, sampled_points)):
+        if len(tree_pts) != len(tree.polynomials):
+            raise ValueError("one list of sample points per column")
+        for ci, pts in enumerate(tree_pts):
+            for k, pt in enumerate(pts):
+                key = (tuple(int(w) for w in pt[0]), tuple(int(w) for w in pt[1]))
+                by_point.setdefault(key, []).append((ti, ci, k))
+    values = {}
+    for pt, where in by_point.items():
+        res = CudaCirclePoly.eval_many_at_point([self.trees[ti].polynomials[ci] for ti, ci, _ in where], pt)
+        for w, v in zip(where, res):
+            values[w] = v
+    samples = [[[PointSample(pt, values[(ti, ci, k)]) for k, pt in enumerate(pts)] for ci, pts in enumerate(tree_pts)]
+               for ti, tree_pts in enumerate(sampled_points)]
     sampled_values = [[[s.value for s in col] for col in tree] for tree in samples]
     channel.mix_felts([v for tree in sampled_values for col in tree for v in col])
     columns = [e for tree in self.trees for e in tree.evaluations]
