@@ -42,7 +42,8 @@ def parse():
     ap.add_argument("--log-size", type=int, default=LOG_SIZE)
     ap.add_argument("--cols", type=int, default=N_COLS)
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+    ap.add_argument("--chunks", type=int, default=4, help="column groups per rank of --exchange ce")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "ce", "nccl"],
                     help="N > 1: 'peer' = last FFT pass stores into the peers' leaf buffers over NVLink; 'nccl' = all-to-all")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample-cols", type=int, default=64)
@@ -210,7 +211,7 @@ def run_cuda(args):
         launches_per_step = None
     else:
         from tstwo_b200.distributed import CudaShardOps, PeerShardedCommit, ShardedCommit
-        if args.exchange == "peer":
+        if args.exchange in ("peer", "ce"):
             sc = PeerShardedCommit(local, stream, n_cols, log, blow)
         else:
             sc = ShardedCommit(CudaShardOps(local, stream), n_cols, log, blow)
@@ -218,7 +219,7 @@ def run_cuda(args):
         holder = {}
 
         def step():
-            r = sc.step(trace_flat)
+            r = sc.step_pipelined(trace_flat, args.chunks) if args.exchange == "ce" else sc.step(trace_flat)
             if r is not None:
                 holder["root"] = r
             else:

@@ -164,6 +164,13 @@ int tstwo_lde_columns_sharded(tstwo_dptr trace, int n_cols, int log_size, int lo
 int tstwo_lde_columns_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
                                tstwo_dptr coeffs, tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards,
                                int col_offset, uint32_t flags);
+/* Multi-GPU, exchange on the copy engines: shard d of a tstwo_lde_columns_sharded block ([n_shards][n_cols][rows_per_shard]) is
+ * copied into shard_bases[d] at column col_offset (destination layout as above) on side streams, after the work the library's
+ * stream holds now and concurrently with what it is given next (the next column group's LDE).  tstwo_scatter_join makes the
+ * library's stream wait for all copies issued so far. */
+int tstwo_scatter_shards(tstwo_dptr evals_sharded, int n_cols, uint64_t rows_per_shard, const tstwo_dptr *shard_bases,
+                         int n_shards, int col_offset);
+int tstwo_scatter_join(void);
 /* CUDA IPC for the above (one process per GPU): 64-byte handle of a tstwo_malloc'ed buffer / mapping of a peer's. */
 int tstwo_ipc_export(tstwo_dptr ptr, uint8_t handle[64]);
 int tstwo_ipc_import(const uint8_t handle[64], tstwo_dptr *out);

@@ -338,6 +338,49 @@ int tstwo_copy(tstwo_dptr dst, tstwo_dptr src, uint64_t bytes)
     TS_CUDA(cudaMemcpyAsync((void *)dst, (const void *)src, bytes, cudaMemcpyDeviceToDevice, ctx().stream));
     return 0;
 }
+// Multi-GPU exchange on the copy engines: the shards of a [n_shards][n_cols][rows] block (tstwo_lde_columns_sharded) go to their
+// owners' leaf buffers by device-to-device copies on side streams, ordered after what the main stream holds now and running
+// concurrently with what it gets next (the next column group's transforms) -- the SMs never wait on NVLink.
+static cudaStream_t g_scatter_streams[4] = { nullptr, nullptr, nullptr, nullptr };
+static cudaEvent_t g_scatter_fork = nullptr, g_scatter_done[4] = { nullptr, nullptr, nullptr, nullptr };
+static bool g_scatter_pending = false;
+int tstwo_scatter_shards(tstwo_dptr evals_sharded, int n_cols, uint64_t rows_per_shard, const tstwo_dptr *shard_bases, int n_shards,
+                         int col_offset)
+{
+    TS_REQUIRE_INIT();
+    if (!evals_sharded || n_cols <= 0 || !rows_per_shard || !shard_bases || n_shards <= 0 || col_offset < 0)
+        return fail(TSTWO_ERR_BAD_ARG, "bad scatter arguments");
+    Context &c = ctx();
+    if (!g_scatter_fork) {
+        TS_CUDA(cudaEventCreateWithFlags(&g_scatter_fork, cudaEventDisableTiming));
+        for (int k = 0; k < 4; k++) {
+            TS_CUDA(cudaStreamCreateWithFlags(&g_scatter_streams[k], cudaStreamNonBlocking));
+            TS_CUDA(cudaEventCreateWithFlags(&g_scatter_done[k], cudaEventDisableTiming));
+        }
+    }
+    TS_CUDA(cudaEventRecord(g_scatter_fork, c.stream));
+    for (int k = 0; k < 4; k++) TS_CUDA(cudaStreamWaitEvent(g_scatter_streams[k], g_scatter_fork, 0));
+    const uint64_t bytes = 4ull * n_cols * rows_per_shard;
+    for (int d = 0; d < n_shards; d++) {
+        if (!shard_bases[d]) return fail(TSTWO_ERR_BAD_ARG, "shard base %d is null", d);
+        TS_CUDA(cudaMemcpyAsync((void *)(shard_bases[d] + 4ull * rows_per_shard * col_offset), (const void *)(evals_sharded + bytes * d), bytes,
+                                cudaMemcpyDeviceToDevice, g_scatter_streams[d & 3]));
+    }
+    g_scatter_pending = true;
+    return 0;
+}
+// the library's stream waits for every scatter copy issued so far
+int tstwo_scatter_join(void)
+{
+    TS_REQUIRE_INIT();
+    if (!g_scatter_pending) return 0;
+    for (int k = 0; k < 4; k++) {
+        TS_CUDA(cudaEventRecord(g_scatter_done[k], g_scatter_streams[k]));
+        TS_CUDA(cudaStreamWaitEvent(ctx().stream, g_scatter_done[k], 0));
+    }
+    g_scatter_pending = false;
+    return 0;
+}
 // gather for decommitments (vcs/prover.ts:32-109 reads childLayerHashes[j] and column[nodeIndex] one by one): the host
 // walks the query tree (it depends on the queries only, not on data), then ONE launch collects every witness word.
 __global__ void gather_words_kernel(const uint64_t *__restrict__ addrs, uint64_t total, int words, uint32_t *__restrict__ out)

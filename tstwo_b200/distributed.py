@@ -188,6 +188,25 @@ class PeerShardedCommit:
             return self.ops.to_host_bytes(self.top[-1] if self.top else self.roots)[:32]
         return None
 
+    def step_pipelined(self, trace: torch.Tensor, chunks: int = 4):
+        """The exchange on the copy engines instead of inside the last FFT pass: the local columns are transformed in `chunks`
+        groups, each written grouped by destination rank (tstwo_lde_columns_sharded) and pushed to the owners' leaf buffers by
+        device-to-device copies on side streams (tstwo_scatter_shards) while the SMs transform the next group.  Only the last
+        group's copies are exposed; the SMs never wait on NVLink."""
+        chk = self._lib_mod.check
+        chunks = max(1, min(chunks, self.lc))
+        while self.lc % chunks:
+            chunks -= 1
+        per, n, rows = self.lc // chunks, 1 << self.log_size, 1 << self.sub
+        for k in range(chunks):
+            work = self.work.data_ptr() + 4 * ((k * per) << self.ext)
+            chk(self.L.tstwo_lde_columns_sharded(trace.data_ptr() + 4 * n * k * per, per, self.log_size, self.blow, self.tw,
+                                                 self.coeffs.data_ptr() + 4 * n * k * per if self.coeffs is not None else 0,
+                                                 work, self.world, 0))
+            chk(self.L.tstwo_scatter_shards(work, per, rows, self._bases_arr, self.world, self.rank * self.lc + k * per))
+        chk(self.L.tstwo_scatter_join())
+        return self._finish()
+
     def step_from_host(self, host: torch.Tensor, staging: torch.Tensor, chunks: int = 4):
         """The same step with this rank's columns in pinned HOST memory (`host`, (n_cols/G, 2^log) int32): the columns cross PCIe
         in `chunks` groups on a copy stream and each group's LDE + peer stores start as soon as it has landed, so the transfer
