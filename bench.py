@@ -28,6 +28,8 @@ N_COLS, LOG_SIZE, LOG_BLOWUP = 256, 22, 1
 # DRAM bytes (read + written) per launch of the kernels below at the headline size, from ncu (profiles/r01_launches_tma.txt)
 NCU_TRAFFIC = {"merkle_leaf_layer": 8.59e9 + 0.27e9, "evaluate (2 fft launches)": (4.51e9 + 8.53e9 + 8.61e9 + 8.53e9) / 2,
                "interpolate (2 fft launches)": (4.31e9 + 4.25e9 + 4.31e9 + 4.23e9) / 2}
+# (column groups, SMs of the NVLink-bound pass) per world size for --overlap auto, from the sweeps in profiles/r01_overlap.txt
+OVERLAP_AUTO = {}
 METRIC = "lde_blake2s_commit_throughput"
 UNIT = "M31 trace elements/s"
 P = 2147483647
@@ -45,6 +47,8 @@ def parse():
     ap.add_argument("--chunks", type=int, default=4, help="column groups per rank of --exchange ce")
     ap.add_argument("--exchange", default="peer", choices=["peer", "ce", "nccl"],
                     help="N > 1: 'peer' = last FFT pass stores into the peers' leaf buffers over NVLink; 'nccl' = all-to-all")
+    ap.add_argument("--overlap", default="auto", help="N > 1, --exchange peer: 'groups,peer_sms' = column groups and SMs given to the "
+                    "NVLink-bound pass running beside the next group's transforms; 'off' = one group; 'auto' = per world size")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample-cols", type=int, default=64)
     ap.add_argument("--fft-radix", type=int, default=0, help="tuning: rows per thread of the FFT passes (8 or 16)")
@@ -212,7 +216,10 @@ def run_cuda(args):
     else:
         from tstwo_b200.distributed import CudaShardOps, PeerShardedCommit, ShardedCommit
         if args.exchange in ("peer", "ce"):
-            sc = PeerShardedCommit(local, stream, n_cols, log, blow)
+            ov = OVERLAP_AUTO.get(world) if args.overlap == "auto" else None if args.overlap == "off" else tuple(int(x) for x in args.overlap.split(","))
+            if args.exchange == "ce":
+                ov = None
+            sc = PeerShardedCommit(local, stream, n_cols, log, blow, overlap=ov)
         else:
             sc = ShardedCommit(CudaShardOps(local, stream), n_cols, log, blow)
         trace_flat = trace.view(-1)

@@ -164,6 +164,13 @@ int tstwo_lde_columns_sharded(tstwo_dptr trace, int n_cols, int log_size, int lo
 int tstwo_lde_columns_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
                                tstwo_dptr coeffs, tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards,
                                int col_offset, uint32_t flags);
+/* The same call with the exchange overlapped with ALL of the LDE's arithmetic: the columns are transformed in col_groups
+ * groups; the last pass of group k (the one whose stores cross NVLink) runs on a side stream on at most peer_sms SMs while the
+ * other SMs interpolate and extend group k + 1.  Identical results for every (col_groups, peer_sms); col_groups = 1 or
+ * peer_sms = 0 is tstwo_lde_columns_to_peers.  On return the library's stream is ordered after both streams' work. */
+int tstwo_lde_columns_to_peers_overlapped(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
+                                          tstwo_dptr coeffs, tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards,
+                                          int col_offset, uint32_t flags, int col_groups, int peer_sms);
 /* Multi-GPU, exchange on the copy engines: shard d of a tstwo_lde_columns_sharded block ([n_shards][n_cols][rows_per_shard]) is
  * copied into shard_bases[d] at column col_offset (destination layout as above) on side streams, after the work the library's
  * stream holds now and concurrently with what it is given next (the next column group's LDE).  tstwo_scatter_join makes the

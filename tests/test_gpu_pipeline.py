@@ -152,3 +152,44 @@ def test_lde_columns_to_peers_local_bases(tb, orc, n_shards, col_offset, total):
                 assert (got[c] == want).all(), f"shard {d} column {c}"
             else:
                 assert (got[c] == 7).all(), f"shard {d} column {c} must be untouched"
+
+
+@pytest.mark.parametrize("groups,peer_sms,n_cols", [(2, 48, 5), (4, 60, 9), (3, 100, 3), (8, 16, 4)])
+def test_lde_columns_to_peers_overlapped_matches(tb, orc, groups, peer_sms, n_cols):
+    """tstwo_lde_columns_to_peers_overlapped (last pass of each column group on a side stream with an SM budget) writes exactly
+    what the one-group call writes, for uneven groups too; checked against the oracle's evaluations on local shard buffers."""
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    log, blow, n_shards, col_offset = 15, 1, 4, 1
+    ext = log + blow
+    rows = (1 << ext) // n_shards
+    total = n_cols + 2
+    rng = np.random.default_rng(100 * groups + n_cols)
+    trace = rng.integers(0, P, (n_cols, 1 << log), dtype=np.uint32)
+    tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(ext).half_coset())
+    root_coset = tb.CanonicCoset.new(ext).half_coset()
+    otw, oitw = orc.precompute_twiddles(root_coset.initial_index.value, root_coset.log_size)
+    _, evals, _ = orc.lde_commit(trace, blow, otw, oitw, want_coeffs=True)
+    dtrace = tb.CudaColumn.from_cpu(trace.reshape(-1))
+    for rep in range(3):                      # repeated calls reuse the side stream and its events
+        shards = [tb.CudaColumn.from_cpu(np.full(total * rows, 7, dtype=np.uint32)) for _ in range(n_shards)]
+        work = tb.CudaColumn.uninitialized(n_cols << ext)
+        _lib.check(L.tstwo_lde_columns_to_peers_overlapped(dtrace.ptr, n_cols, log, blow, tw.handle, 0, work.ptr,
+                                                           _lib.dptr_array([s.ptr for s in shards]), n_shards, col_offset, 0,
+                                                           groups, peer_sms))
+        for d in range(n_shards):
+            got = shards[d].toCpu().reshape(total, rows)
+            for c in range(total):
+                if col_offset <= c < col_offset + n_cols:
+                    assert (got[c] == evals[c - col_offset][d * rows:(d + 1) * rows]).all(), f"rep {rep} shard {d} column {c}"
+                else:
+                    assert (got[c] == 7).all(), f"shard {d} column {c} must be untouched"
+
+
+def test_lde_columns_to_peers_overlapped_rejects_bad_budget(tb):
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(16).half_coset())
+    buf = tb.CudaColumn.uninitialized(1 << 17)
+    rc = L.tstwo_lde_columns_to_peers_overlapped(buf.ptr, 1, 15, 1, tw.handle, 0, buf.ptr, _lib.dptr_array([buf.ptr]), 1, 0, 0, 2, 100000)
+    assert rc != 0 and b"overlap" in L.tstwo_last_error()

@@ -29,6 +29,7 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   tstwo_lde_commit_host: { args: [T.ptr, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.u64, T.u64, T.ptr, T.u32], returns: T.i32 },
   // multi-GPU (one Bun worker per GPU): last FFT pass stores into the peers' leaf buffers, mapped through CUDA IPC
   tstwo_lde_columns_to_peers: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.ptr, T.i32, T.i32, T.u32], returns: T.i32 },
+  tstwo_lde_columns_to_peers_overlapped: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.ptr, T.i32, T.i32, T.u32, T.i32, T.i32], returns: T.i32 },
   tstwo_ipc_export: { args: [T.u64, T.ptr], returns: T.i32 },
   tstwo_ipc_import: { args: [T.ptr, T.ptr], returns: T.i32 },
   tstwo_ipc_close: { args: [T.u64], returns: T.i32 },

@@ -70,6 +70,8 @@ SIGNATURES = {
     "tstwo_lde_commit": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptr, C.POINTER(C.c_uint8), C.c_uint32]),
     "tstwo_lde_columns_sharded": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, C.c_int, C.c_uint32]),
     "tstwo_lde_columns_to_peers": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptrp, C.c_int, C.c_int, C.c_uint32]),
+    "tstwo_lde_columns_to_peers_overlapped": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptrp, C.c_int, C.c_int,
+                                                         C.c_uint32, C.c_int, C.c_int]),
     "tstwo_ipc_export": (C.c_int, [dptr, C.POINTER(C.c_uint8)]),
     "tstwo_ipc_import": (C.c_int, [C.POINTER(C.c_uint8), C.POINTER(C.c_uint64)]),
     "tstwo_ipc_close": (C.c_int, [dptr]),

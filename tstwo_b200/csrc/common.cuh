@@ -18,6 +18,8 @@ struct Context {
     cudaStream_t stream = nullptr;       // stream in use (own_stream or caller's)
     cudaStream_t copy_stream = nullptr;  // H2D pipeline for tstwo_lde_commit_host
     uint64_t launches = 0;
+    int grid_limit = 0;                  // > 0: persistent FFT passes launch at most this many CTAs (SM partitioning between
+                                         // two streams, tstwo_lde_columns_to_peers_overlapped); 0 = one CTA per SM
     // small device scratch for pointer tables / parameters
     uint64_t *d_ptr_table = nullptr;
     size_t ptr_table_cap = 0;
@@ -98,7 +100,7 @@ int launch_coset_points(uint32_t *out2, int which, uint32_t init, int step_log, 
 cudaError_t elementwise_init();   // per-TU constant tables of elementwise.cu
 int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int log_size, const TwiddleTree *t, uint32_t flags);
 int fft_evaluate(const ColSet &src, int poly_log, const ColSet &dst, int n_cols, int domain_log, const TwiddleTree *t,
-                 uint32_t flags, const ColSet *work = nullptr);
+                 uint32_t flags, const ColSet *work = nullptr, int pass_select = 0);
 int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, int n_cols, uint8_t *out);
 // leaf layer fed in column chunks: absorbs columns [c0, c0 + nc) (given as `cols`) of leaves of total_cols words
 int merkle_leaf_absorb(int log_size, const ColSet &cols, int c0, int nc, int total_cols, uint8_t *leaf_layer);

@@ -486,9 +486,11 @@ int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int n, con
 }
 
 // `work`: plain (non-sharded) column set the strided passes run in; equals dst unless dst is row-sharded, in which
-// case only the last (contiguous) pass writes dst.
+// case only the last (contiguous) pass writes dst.  pass_select (tiled sizes only): 0 = the whole transform, 1 = every
+// pass but the last, 2 = the last pass alone (the one that writes dst) -- the multi-GPU path runs the two parts on different
+// streams so that the pass whose stores cross NVLink overlaps the next column group's transforms.
 int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n, const TwiddleTree *t, uint32_t flags,
-                 const ColSet *work_in)
+                 const ColSet *work_in, int pass_select)
 {
     if (n_cols <= 0) return 0;
     const ColSet &work = work_in ? *work_in : dst;
@@ -501,7 +503,9 @@ int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n,
         if (dst.shard_bases && mode != 2) return fail(TSTWO_ERR_BAD_ARG, "per-shard output bases need the bulk-copy FFT passes");
         Pass ps[MAX_PASSES];
         int np = mode == 2 ? plan_passes(L, ps, TMA_W0, TMA_W1) : plan_passes(L, ps, W0, W1);
+        if (pass_select && np < 2) return fail(TSTWO_ERR_BAD_ARG, "split evaluation needs at least two passes");
         for (int k = np - 1; k >= 0; k--) {
+            if ((pass_select == 1 && k == 0) || (pass_select == 2 && k != 0)) continue;
             PassParams p;
             const bool first = (k == np - 1);
             p.src = first ? src : work; p.dst = (k == 0) ? dst : work; p.n_cols = n_cols; p.n = n;
@@ -512,7 +516,7 @@ int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n,
         }
         return 0;
     }
-    if (dst.shard_log != 31 || dst.shard_bases) return fail(TSTWO_ERR_BAD_ARG, "row-sharded output needs poly_log >= %d", FAST_MIN_LOG);
+    if (dst.shard_log != 31 || dst.shard_bases || pass_select) return fail(TSTWO_ERR_BAD_ARG, "row-sharded output needs poly_log >= %d", FAST_MIN_LOG);
     dim3 egrid((unsigned)((N + 255) / 256), (unsigned)n_cols);
     const bool in_place = (src.base == dst.base && src.table == dst.table && src.stride == dst.stride);
     if (!(in_place && L == n)) TS_LAUNCH(extend_kernel, egrid, 256, 0, src, dst, L, n);

@@ -561,6 +561,7 @@ int tma_pass(bool inverse, const PassParams &p)
     sp.n_tiles = (uint32_t)(n_hi * per_hi);
     sp.tiles_per_hi = (uint32_t)per_hi;
     unsigned grid = (unsigned)ctx().sm_count;
+    if (ctx().grid_limit > 0 && grid > (unsigned)ctx().grid_limit) grid = (unsigned)ctx().grid_limit;
     if (grid > sp.n_tiles) grid = sp.n_tiles;
     if (!strided) {
         if (inverse) TS_LAUNCH((fft_tma_kernel<true, false, true>), grid, THREADS, smem_bytes<false>(), sp);

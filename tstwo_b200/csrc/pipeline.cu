@@ -120,14 +120,25 @@ int tstwo_lde_columns_sharded(tstwo_dptr trace, int n_cols, int log_size, int lo
     return fft_evaluate(cfs, log_size, ev, n_cols, ext, t, flags, &work);
 }
 
+}  // extern "C" (reopened below)
+
 // Multi-GPU, fused exchange: like tstwo_lde_columns_sharded, but the last FFT pass stores the rows of shard d straight
 // into shard_bases[d] -- the leaf buffer [total columns][rows] of rank d, mapped into this process with
 // tstwo_ipc_import -- at column col_offset + c.  No send buffer, no all-to-all: the stores travel over NVLink while the
 // butterflies of the next tiles run.  The caller orders the step with one (tiny) collective before the receivers hash.
-int tstwo_lde_columns_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, tstwo_dptr coeffs,
-                               tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards, int col_offset, uint32_t flags)
+//
+// col_groups > 1 (tstwo_lde_columns_to_peers_overlapped): the NVLink-bound pass of column group k runs on a side stream
+// with at most peer_sms CTAs while the other SMs interpolate and extend group k + 1 on the library's stream -- the
+// exchange (7/8 of the evaluations at 8 GPUs, >= 1 ms at 900 GB/s) then overlaps ALL of the LDE's arithmetic, not just the
+// 14 layers of the pass that issues the stores.  Same bytes, same destinations: results are identical for any grouping.
+namespace {
+cudaStream_t g_peer_stream = nullptr;
+cudaEvent_t g_peer_ev[2] = { nullptr, nullptr };   // [0] group ready for its last pass (main -> side), [1] side drained
+
+int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, tstwo_dptr coeffs,
+                 tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards, int col_offset, uint32_t flags,
+                 int col_groups, int peer_sms)
 {
-    TS_REQUIRE_INIT();
     TwiddleTree *t;
     int rc = check_args(n_cols, log_size, log_blowup, tw, &t);
     if (rc) return rc;
@@ -136,29 +147,91 @@ int tstwo_lde_columns_to_peers(tstwo_dptr trace, int n_cols, int log_size, int l
     while ((1 << sl) < n_shards) sl++;
     if (n_shards < 1 || n_shards > 64 || (1 << sl) != n_shards || ext - sl < 14) return fail(TSTWO_ERR_BAD_ARG, "bad shard count %d", n_shards);
     if (!trace || !work || !shard_bases || col_offset < 0) return fail(TSTWO_ERR_BAD_ARG, "null trace/work/shard bases");
+    Context &c = ctx();
+    if (col_groups < 1 || peer_sms < 0 || peer_sms >= c.sm_count) return fail(TSTWO_ERR_BAD_ARG, "bad overlap parameters (%d groups, %d SMs)", col_groups, peer_sms);
+    if (log_size < 15 || peer_sms == 0) col_groups = 1;          // a one-pass evaluation has nothing to split off
+    if (col_groups > n_cols) col_groups = n_cols;
+    if (col_groups > 32) col_groups = 32;
     const uint64_t n = 1ull << log_size, ne = 1ull << ext, rows = 1ull << (ext - sl);
     uint32_t *scr = nullptr;
     if (!coeffs && (rc = coeff_scratch((size_t)n_cols * n, &scr))) return rc;
     uint32_t *cf = coeffs ? (uint32_t *)coeffs : scr;
-    // per-shard bases, already advanced to this rank's first column, in the library's device pointer table (slot 2)
-    Context &c = ctx();
-    uint64_t host_bases[64];
-    for (int d = 0; d < n_shards; d++) {
+    for (int d = 0; d < n_shards; d++)
         if (!shard_bases[d] || (shard_bases[d] & 15)) return fail(TSTWO_ERR_BAD_ARG, "shard base %d null or not 16-byte aligned", d);
-        host_bases[d] = shard_bases[d] + (uint64_t)col_offset * rows * 4;
+    if (col_groups > 1 && !g_peer_stream) {
+        int lo_pri = 0, hi_pri = 0;
+        TS_CUDA(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
+        TS_CUDA(cudaStreamCreateWithPriority(&g_peer_stream, cudaStreamNonBlocking, hi_pri));
+        for (auto &e : g_peer_ev) TS_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    cudaStream_t main_stream = c.stream;
+    // per-shard bases, advanced to each group's first column, in the library's device pointer table (slot 2, 64 per group)
+    uint64_t host_bases[32 * 64];
+    int c0 = 0;
+    for (int k = 0; k < col_groups; k++) {
+        const int nc = (n_cols - c0 + (col_groups - k) - 1) / (col_groups - k);   // remaining columns spread evenly
+        for (int d = 0; d < n_shards; d++) host_bases[64 * k + d] = shard_bases[d] + (uint64_t)(col_offset + c0) * rows * 4;
+        c0 += nc;
     }
     uint64_t *dev_bases = c.d_ptr_table + 2 * 4096;
-    TS_CUDA(cudaMemcpyAsync(dev_bases, host_bases, sizeof(uint64_t) * (size_t)n_shards, cudaMemcpyHostToDevice, c.stream));
-    ColSet src = { (const uint32_t *)trace, n, nullptr };
-    ColSet cfs = { cf, n, nullptr };
-    ColSet wk = { (const uint32_t *)work, ne, nullptr };
-    ColSet ev = { nullptr, rows, nullptr };
-    ev.shard_log = ext - sl;
-    ev.shard_bases = dev_bases;
-    if ((rc = fft_interpolate(src, cfs, n_cols, log_size, t, flags))) return rc;
-    return fft_evaluate(cfs, log_size, ev, n_cols, ext, t, flags, &wk);
+    TS_CUDA(cudaMemcpyAsync(dev_bases, host_bases, sizeof(uint64_t) * 64 * (size_t)col_groups, cudaMemcpyHostToDevice, main_stream));
+    c0 = 0;
+    for (int k = 0; k < col_groups && !rc; k++) {
+        const int nc = (n_cols - c0 + (col_groups - k) - 1) / (col_groups - k);
+        ColSet src = { (const uint32_t *)trace + (uint64_t)c0 * n, n, nullptr };
+        ColSet cfs = { cf + (uint64_t)c0 * n, n, nullptr };
+        ColSet wk = { (const uint32_t *)work + (uint64_t)c0 * ne, ne, nullptr };
+        ColSet ev = { nullptr, rows, nullptr };
+        ev.shard_log = ext - sl;
+        ev.shard_bases = dev_bases + 64 * k;
+        if (col_groups == 1) {
+            if ((rc = fft_interpolate(src, cfs, nc, log_size, t, flags))) break;
+            rc = fft_evaluate(cfs, log_size, ev, nc, ext, t, flags, &wk);
+            break;
+        }
+        // every pass but the last on the library's stream; while an earlier group's last pass may be running they leave it peer_sms SMs
+        c.grid_limit = k > 0 ? c.sm_count - peer_sms : 0;
+        if (!(rc = fft_interpolate(src, cfs, nc, log_size, t, flags))) rc = fft_evaluate(cfs, log_size, ev, nc, ext, t, flags, &wk, 1);
+        if (rc) break;
+        cudaError_t e = cudaEventRecord(g_peer_ev[0], main_stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(g_peer_stream, g_peer_ev[0], 0);
+        if (e != cudaSuccess) { rc = fail(TSTWO_ERR_CUDA, "event record/wait failed: %s", cudaGetErrorString(e)); break; }
+        // the pass whose stores cross NVLink, on the side stream; the last group's has the GPU to itself
+        c.stream = g_peer_stream;
+        c.grid_limit = k < col_groups - 1 ? peer_sms : 0;
+        rc = fft_evaluate(cfs, log_size, ev, nc, ext, t, flags, &wk, 2);
+        c.stream = main_stream;
+        c0 += nc;
+    }
+    c.stream = main_stream;
+    c.grid_limit = 0;
+    if (col_groups > 1) {                                         // join, also on the error path: the side stream may hold work
+        cudaError_t e = cudaEventRecord(g_peer_ev[1], g_peer_stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(main_stream, g_peer_ev[1], 0);
+        if (e != cudaSuccess && !rc) rc = fail(TSTWO_ERR_CUDA, "event record/wait failed: %s", cudaGetErrorString(e));
+    }
+    return rc;
+}
+}  // namespace
+
+extern "C" {
+int tstwo_lde_columns_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, tstwo_dptr coeffs,
+                               tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards, int col_offset, uint32_t flags)
+{
+    TS_REQUIRE_INIT();
+    return lde_to_peers(trace, n_cols, log_size, log_blowup, tw, coeffs, work, shard_bases, n_shards, col_offset, flags, 1, 0);
+}
+int tstwo_lde_columns_to_peers_overlapped(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
+                                          tstwo_dptr coeffs, tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards,
+                                          int col_offset, uint32_t flags, int col_groups, int peer_sms)
+{
+    TS_REQUIRE_INIT();
+    return lde_to_peers(trace, n_cols, log_size, log_blowup, tw, coeffs, work, shard_bases, n_shards, col_offset, flags,
+                        col_groups, peer_sms);
+}
 }
 
+extern "C" {
 // CUDA IPC plumbing for the above (one process per GPU): export a tstwo_malloc'ed buffer, import a peer's.
 int tstwo_ipc_export(tstwo_dptr ptr, uint8_t handle[64])
 {

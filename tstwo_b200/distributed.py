@@ -118,8 +118,12 @@ class PeerShardedCommit:
          is still being hashed in the next step), top log2 G layers on rank 0.
     CUDA-only (needs peer access); the protocol above the device work is the one tests/test_distributed_cpu.py covers."""
 
-    def __init__(self, device_index: int, stream, n_cols: int, log_size: int, log_blowup: int, keep_coeffs: bool = False):
+    def __init__(self, device_index: int, stream, n_cols: int, log_size: int, log_blowup: int, keep_coeffs: bool = False,
+                 overlap: tuple | None = None):
+        """overlap = (col_groups, peer_sms): run the NVLink-bound last pass of each column group on a side stream on peer_sms
+        SMs while the others transform the next group (tstwo_lde_columns_to_peers_overlapped); None = one group."""
         from . import _lib
+        self.overlap = overlap
         self._lib_mod = _lib
         self.L = _lib.init(device_index)
         chk = _lib.check
@@ -170,9 +174,11 @@ class PeerShardedCommit:
 
     def step(self, trace: torch.Tensor):
         chk = self._lib_mod.check
-        chk(self.L.tstwo_lde_columns_to_peers(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw,
-                                              self.coeffs.data_ptr() if self.coeffs is not None else 0, self.work.data_ptr(),
-                                              self._bases_arr, self.world, self.rank * self.lc, 0))
+        groups, peer_sms = self.overlap if self.overlap else (1, 0)
+        chk(self.L.tstwo_lde_columns_to_peers_overlapped(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw,
+                                                         self.coeffs.data_ptr() if self.coeffs is not None else 0,
+                                                         self.work.data_ptr(), self._bases_arr, self.world, self.rank * self.lc, 0,
+                                                         groups, peer_sms))
         return self._finish()
 
     def _finish(self):
