@@ -29,7 +29,7 @@ N_COLS, LOG_SIZE, LOG_BLOWUP = 256, 22, 1
 NCU_TRAFFIC = {"merkle_leaf_layer": 8.59e9 + 0.27e9, "evaluate (2 fft launches)": (4.51e9 + 8.53e9 + 8.61e9 + 8.53e9) / 2,
                "interpolate (2 fft launches)": (4.31e9 + 4.25e9 + 4.31e9 + 4.23e9) / 2}
 # (column groups, SMs of the NVLink-bound pass) per world size for --overlap auto, from the sweeps in profiles/r01_overlap.txt
-OVERLAP_AUTO = {}
+OVERLAP_AUTO = {2: (4, 62), 4: (4, 62), 8: (4, 62)}
 METRIC = "lde_blake2s_commit_throughput"
 UNIT = "M31 trace elements/s"
 P = 2147483647
@@ -295,6 +295,13 @@ def run_cuda(args):
                     "blake2s": {"compressions": n_cmp, "ms": t_mk, "achieved": n_cmp / t_mk / 1e6, "peak": 27.7, "unit": "G compressions/s",
                                 "frac": n_cmp / t_mk / 1e6 / 27.7},
                     "peak_source": "tools/microbench.cu, tools/microbench_bf.cu on B200 (profiles/r01_microbench_int_pipes.txt, r01_microbench_stage.txt, r01_microbench_blake2s_forms.txt)"}
+        # the dominant kernel's own integer-pipe roofline beside its HBM one (what actually bounds it)
+        if top_k == "merkle_leaf_layer":
+            n_leaf = ne * ((4 * n_cols + 63) // 64)
+            roof["int_pipe"] = {"achieved": n_leaf / ms_launch / 1e6, "peak": 27.7, "unit": "G compressions/s", "frac": n_leaf / ms_launch / 1e6 / 27.7}
+        else:
+            n_k = n_cols * log * ((ne if top_k.startswith("evaluate") else n) // 2) / kk["launches"]
+            roof["int_pipe"] = {"achieved": n_k / ms_launch / 1e6, "peak": 3667.0, "unit": "G butterflies/s", "frac": n_k / ms_launch / 1e6 / 3667.0}
 
     # ---- end to end through the C ABI with HOST buffers (1 GPU)
     e2e = None

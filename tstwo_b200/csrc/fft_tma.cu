@@ -405,14 +405,17 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
         uint32_t len = ((hi + 1) * sp.tiles_per_hi - t0 + step - 1) / step;   // tiles of this run that are mine
         if (len > count - k) len = count - k;
         __syncthreads();                               // previous run drained: buffers and heap are free
+        // the run's first tiles are requested BEFORE its twiddles are staged: both latencies overlap (a run is short when
+        // the column set is small -- the column groups of the multi-GPU path, the 16-column chunks of the host-fed path)
+#pragma unroll
+        for (int i = 0; i < NBUF; i++)
+            if ((uint32_t)i < len && (i % G) == g)
+                tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar_of(i), tg);
         if (STRIDED && sp.cosets_log) {
             for (uint32_t c = 0; c < (1u << sp.cosets_log); c++) stage_twiddles<STRIDED>(heap + 256 * c, p, c, tid);
         } else stage_twiddles<STRIDED>(heap, p, hi, tid);
         __syncthreads();
-#pragma unroll
-        for (int i = 0; i < NBUF; i++)
-            if ((uint32_t)i < len && (i % G) == g)
-                tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar_of(i), tg);        uint32_t refill = 0xffffffffu;                 // DEFER: tile of mine whose buffer is still to be refilled
+        uint32_t refill = 0xffffffffu;                 // DEFER: tile of mine whose buffer is still to be refilled
 
         for (uint32_t i = g; i < len; i += G) {
             const uint32_t b = i % NBUF, round = i / NBUF;
