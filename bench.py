@@ -57,15 +57,41 @@ def parse():
 
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """Samples SM clocks / throttle reasons during the timed region (B200_PROFILING.md recipe).  NVML is polled from a thread
+    every few ms (a multi-GPU timed region lasts tens of ms, shorter than one nvidia-smi -lms period); nvidia-smi is the
+    fallback when NVML cannot be loaded."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, index=0):
-        self.index, self.rows, self.proc = index, [], None
+    def __init__(self, index=0, uuid=None):
+        self.index, self.rows, self.proc, self.nv, self.h, self._stop, self.src = index, [], None, None, None, False, None
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = None
+            if uuid:
+                try:
+                    h = nv.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)) if not str(uuid).startswith("GPU-") else str(uuid))
+                except Exception:
+                    h = None
+            if h is None:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+                phys = int(vis.split(",")[index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else index
+                h = nv.nvmlDeviceGetHandleByIndex(phys)
+            nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+            self.nv, self.h = nv, h
+        except Exception:
+            self.nv = None
 
     def start(self):
+        if self.nv:
+            self.src = "nvml"
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
         try:
+            self.src = "nvidia-smi"
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
@@ -73,31 +99,57 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        nv, h = self.nv, self.h
+        masks = [nv.nvmlClocksEventReasonHwSlowdown, nv.nvmlClocksEventReasonHwThermalSlowdown,
+                 nv.nvmlClocksEventReasonSwThermalSlowdown, nv.nvmlClocksEventReasonSwPowerCap]
+        try:
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        except Exception:
+            mx = 0
+        while not self._stop:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                self.rows.append([str(sm), str(mx), "%.2f" % pw] + ["Active" if r & m else "Not Active" for m in masks])
+            except Exception:
+                pass
+            time.sleep(0.003)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
+    def mark(self):
+        """Start of the timed region: earlier samples (warm-up) are dropped."""
+        self.rows = []
+
     def stop(self):
-        if not self.proc:
+        if self.nv:
+            self._stop = True
+            self.t.join(timeout=1)
+        elif not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            pass
-        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        else:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                pass
+        rows = list(self.rows)
+        sm = sorted(int(r[0]) for r in rows if r and r[0].isdigit())
         reasons = set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            for k, nm in enumerate(names):
+        for r in rows:
+            for k, nm in enumerate(self.NAMES):
                 if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
                     reasons.add(nm)
-        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
-        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        mx = [int(r[1]) for r in rows if len(r) > 1 and r[1].isdigit()]
+        pw = [float(r[2]) for r in rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
         # "under load": drop samples below half of the largest seen (idle ramp)
         load = [s for s in sm if s >= 0.5 * sm[-1]] if sm else []
         return {"sm_mhz": load[len(load) // 2] if load else None, "sm_max_mhz": mx[0] if mx else None,
-                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons), "source": self.src}
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
@@ -238,14 +290,18 @@ def run_cuda(args):
         torch.cuda.synchronize()
 
     # ---- device-resident timing
-    sampler = ClockSampler(local)
+    try:
+        uuid = torch.cuda.get_device_properties(local).uuid
+    except Exception:
+        uuid = None
+    sampler = ClockSampler(local, uuid)
     if rank == 0:
         sampler.start()          # nvidia-smi needs ~100s of ms to start; idle/ramp samples are filtered in stop()
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
     if rank == 0:
-        sampler.rows.clear()     # keep only samples taken during the timed region
+        sampler.mark()           # keep only samples taken during the timed region
     l0 = L.tstwo_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
