@@ -18,13 +18,14 @@ lc = n_cols // world
 trace = torch.randint(0, P, (lc, 1 << log), dtype=torch.int32, device="cuda")
 sc = PeerShardedCommit(local, stream, n_cols, log, blow)
 ev = lambda: torch.cuda.Event(enable_timing=True)
+GROUPS, PEER_SMS = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (4, 62)
 
 def step(rec=None):
     chk = _lib.check
     e = [ev() for _ in range(5)]
     e[0].record(stream)
-    chk(sc.L.tstwo_lde_columns_to_peers(trace.data_ptr(), sc.lc, sc.log_size, sc.blow, sc.tw, 0, sc.work.data_ptr(), sc._bases_arr, sc.world,
-                                        sc.rank * sc.lc, 0))
+    chk(sc.L.tstwo_lde_columns_to_peers_overlapped(trace.data_ptr(), sc.lc, sc.log_size, sc.blow, sc.tw, 0, sc.work.data_ptr(), sc._bases_arr,
+                                                   sc.world, sc.rank * sc.lc, 0, GROUPS, PEER_SMS))
     e[1].record(stream)
     dist.all_reduce(sc.flag)
     e[2].record(stream)
@@ -55,6 +56,7 @@ t = torch.tensor(tot + [whole], device="cuda")
 mx = t.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
 mn = t.clone(); dist.all_reduce(mn, op=dist.ReduceOp.MIN)
 if rank == 0:
+    print(f"N={world} groups={GROUPS} peer_sms={PEER_SMS}")
     for i, nm in enumerate(names + ["whole step"]):
         print(f"{nm:32s} min over ranks {mn[i].item():7.3f} ms   max {mx[i].item():7.3f} ms")
 sc.close()
