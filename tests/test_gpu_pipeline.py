@@ -193,3 +193,64 @@ def test_lde_columns_to_peers_overlapped_rejects_bad_budget(tb):
     buf = tb.CudaColumn.uninitialized(1 << 17)
     rc = L.tstwo_lde_columns_to_peers_overlapped(buf.ptr, 1, 15, 1, tw.handle, 0, buf.ptr, _lib.dptr_array([buf.ptr]), 1, 0, 0, 2, 100000)
     assert rc != 0 and b"overlap" in L.tstwo_last_error()
+
+
+def test_config3_full_size_single_and_sharded(tb, orc):
+    """BASELINE config 3 at its FULL size on one GPU: 256 uniform-random columns of 2^22, blow-up 2.  (a) first / last
+    column against the oracle in full, (b) an authentication path re-hashed with hashlib, (c) round trip, and (d) the
+    multi-GPU data path emulated on one device: tstwo_lde_columns_to_peers_overlapped stores the rows of 8 shards into 8
+    LOCAL leaf buffers (the multi-GPU run maps the peers' buffers there), each shard's subtree is committed on its own and the
+    top log2(8) layers are finished as rank 0 does -- the root must equal the single-tree root."""
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    log, blow, n_cols, G = 22, 1, 256, 8
+    n, ext = 1 << log, log + blow
+    rng = np.random.default_rng(0x5EED0003)
+    cols = rng.integers(0, P, (n_cols, n), dtype=np.uint32)
+    root_coset = tb.CanonicCoset.new(ext).half_coset()
+    tw = tb.CudaBackend.precomputeTwiddles(root_coset)
+    dtrace = tb.CudaColumn.from_cpu(cols.reshape(-1))
+    tree = tb.CommitmentTreeProver.from_trace(dtrace, n_cols, log, blow, tw)
+    otw, oitw = orc.precompute_twiddles(root_coset.initial_index.value, root_coset.log_size)
+    for c in (0, n_cols - 1):
+        cf, ev, _ = orc.lde_commit(cols[c:c + 1], blow, otw, oitw, want_coeffs=True, want_layers=False)
+        assert (tree.polynomials[c].coeffs.toCpu() == cf[0]).all()
+        assert (tree.evaluations[c].values.toCpu() == ev[0]).all()
+    leaf = 0x6543210 % (1 << ext)
+    row = b"".join(struct.pack("<I", tree.evaluations[c].values.at(leaf)) for c in range(n_cols))
+    h = hashlib.blake2s(row).digest()
+    idx = leaf
+    for k in range(ext, 0, -1):
+        layer = tree.commitment.layers[k]
+        assert layer.slice(8 * idx, 8).toCpu().tobytes() == h
+        sib = layer.slice(8 * (idx ^ 1), 8).toCpu().tobytes()
+        h = hashlib.blake2s(h + sib if idx % 2 == 0 else sib + h).digest()
+        idx >>= 1
+    assert h == tree.root()
+    back = tb.CudaBackend.interpolateColumns([tree.evaluations[131]], tw)[0].coeffs.toCpu()
+    assert (back[:n] == tree.polynomials[131].coeffs.toCpu()).all() and not back[n:].any()
+    want_root = tree.root()
+    sub_layer = tree.commitment.layers[3].toCpu().tobytes()          # the 8 subtree roots of the single tree
+    del tree, back
+    # (d) sharded path, all "ranks" on this device: rank r transforms columns [32 r, 32 r + 32) and stores into all 8 buffers
+    rows, lc = (1 << ext) // G, n_cols // G
+    shards = [tb.CudaColumn.uninitialized(n_cols * rows) for _ in range(G)]
+    work = tb.CudaColumn.uninitialized(lc << ext)
+    bases = _lib.dptr_array([s.ptr for s in shards])
+    for r in range(G):
+        _lib.check(L.tstwo_lde_columns_to_peers_overlapped(dtrace.ptr + 4 * n * lc * r, lc, log, blow, tw.handle, 0, work.ptr, bases, G,
+                                                           r * lc, 0, 4 if r % 2 else 1, 62 if r % 2 else 0))
+    roots = tb.CudaColumn.uninitialized(8 * G)
+    sub = tb.CudaColumn.uninitialized(8 * ((2 * rows) - 1))
+    logs = (C.c_int * n_cols)(*([ext - 3] * n_cols))
+    for d in range(G):
+        ptrs = _lib.dptr_array([shards[d].ptr + 4 * rows * c for c in range(n_cols)])
+        _lib.check(L.tstwo_merkle_commit(ptrs, logs, n_cols, sub.ptr, None))
+        _lib.check(L.tstwo_copy(roots.ptr + 32 * d, sub.ptr, 32))
+    assert roots.toCpu().tobytes() == sub_layer, "subtree roots differ from layer 3 of the single tree"
+    prev = roots
+    for k in (2, 1, 0):
+        cur = tb.CudaColumn.uninitialized(8 << k)
+        _lib.check(L.tstwo_merkle_commit_layer(k, prev.ptr, None, 0, cur.ptr))
+        prev = cur
+    assert prev.toCpu().tobytes() == want_root
