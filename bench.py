@@ -295,6 +295,15 @@ def run_cuda(args):
     except Exception:
         uuid = None
     sampler = ClockSampler(local, uuid)
+    # one process per GPU: run on the CPUs of the GPU's own NUMA node, so that the pinned host shard of the end-to-end leg is
+    # allocated next to the PCIe root port it is read through (8 ranks pulling through one socket's memory halve the rate)
+    numa_bound = False
+    if world > 1 and sampler.nv is not None and not os.environ.get("TSTWO_NO_NUMA_BIND"):
+        try:
+            sampler.nv.nvmlDeviceSetCpuAffinity(sampler.h)
+            numa_bound = True
+        except Exception:
+            numa_bound = False
     if rank == 0:
         sampler.start()          # nvidia-smi needs ~100s of ms to start; idle/ramp samples are filtered in stop()
     for _ in range(max(args.warmup, 3)):
@@ -411,7 +420,8 @@ def run_cuda(args):
             assert got["root"].hex() == root_hex, "e2e root differs from device-resident root"
         e2e = {"value": n_cols * n / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "h2d_bytes_per_step": n_cols * n * 4,
                "d2h_bytes_per_step": 32,
-               "api": f"PeerShardedCommit.step_from_host (pinned host shard per rank -> root on rank 0), {world} PCIe links"}
+               "api": f"PeerShardedCommit.step_from_host (pinned host shard per rank -> root on rank 0), {world} PCIe links",
+               "cpu_affinity": "NUMA node of each rank's GPU (nvmlDeviceSetCpuAffinity)" if numa_bound else "unbound"}
 
     if rank == 0:
         cpu = None if args.no_cpu or world > 1 else cpu_baseline(args)

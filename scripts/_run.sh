@@ -1,3 +1,2 @@
-set -x
 mkdir -p gpurun_out
-(time timeout 600 python -m pytest tests/test_gpu_pipeline.py -x -q -k "config3 or overlapped" --durations=3) 2>&1 | tail -12
+timeout 300 python scripts/prove_profile.py 20 100 > gpurun_out/prove_profile.txt 2>&1; head -c 200 gpurun_out/prove_profile.txt
