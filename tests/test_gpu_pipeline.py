@@ -254,3 +254,48 @@ def test_config3_full_size_single_and_sharded(tb, orc):
         _lib.check(L.tstwo_merkle_commit_layer(k, prev.ptr, None, 0, cur.ptr))
         prev = cur
     assert prev.toCpu().tobytes() == want_root
+
+
+def test_shutdown_releases_side_streams_and_reinit_works():
+    """tstwo_shutdown frees what the pipeline keeps between calls (coefficient scratch, the side stream and events of the
+    overlapped exchange, the scatter streams); a second tstwo_init in the same process must give the same results.  Run in a
+    child process: shutting the library down under the other tests' columns would pull the memory from under them."""
+    import os, subprocess, sys, textwrap
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = textwrap.dedent("""
+        import ctypes as C, numpy as np, sys
+        sys.path.insert(0, %r)
+        from tstwo_b200 import _lib
+        P = 2147483647
+        log, blow, n_cols, G = 15, 1, 6, 2
+        ext, rows = log + blow, (1 << (log + blow)) // G
+        trace = np.random.default_rng(5).integers(0, P, n_cols << log, dtype=np.uint32)
+        outs = []
+        for rep in range(2):
+            L = _lib.init(0)
+            chk = _lib.check
+            def dmalloc(words):
+                p = C.c_uint64(); chk(L.tstwo_malloc(4 * words, C.byref(p))); return p.value
+            tw = C.c_uint64(); chk(L.tstwo_twiddles_precompute(1 << (31 - (ext - 1) - 2), ext - 1, C.byref(tw)))
+            d_trace, work = dmalloc(n_cols << log), dmalloc(n_cols << ext)
+            shards = [dmalloc(n_cols * rows) for _ in range(G)]
+            chk(L.tstwo_upload(d_trace, trace.ctypes.data, 4 * trace.size))
+            chk(L.tstwo_lde_columns_to_peers_overlapped(d_trace, n_cols, log, blow, tw.value, 0, work, _lib.dptr_array(shards), G, 0, 0, 3, 50))
+            sharded = dmalloc(n_cols << ext)
+            chk(L.tstwo_lde_columns_sharded(d_trace, n_cols, log, blow, tw.value, 0, sharded, G, 0))
+            copies = [dmalloc(n_cols * rows) for _ in range(G)]
+            chk(L.tstwo_scatter_shards(sharded, n_cols, rows, _lib.dptr_array(copies), G, 0)); chk(L.tstwo_scatter_join())
+            got = []
+            for a, b in zip(shards, copies):
+                x, y = np.empty(n_cols * rows, dtype=np.uint32), np.empty(n_cols * rows, dtype=np.uint32)
+                chk(L.tstwo_download(x.ctypes.data, a, 4 * x.size)); chk(L.tstwo_download(y.ctypes.data, b, 4 * y.size))
+                assert (x == y).all(), "peer stores and copy-engine scatter disagree"
+                got.append(x)
+            outs.append(np.concatenate(got))
+            assert L.tstwo_shutdown() == 0
+            _lib._inited = None
+        assert (outs[0] == outs[1]).all()
+        print("reinit ok")
+    """ % root)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "reinit ok" in r.stdout, r.stdout + r.stderr

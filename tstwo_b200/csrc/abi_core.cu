@@ -27,6 +27,7 @@ int fail(int code, const char *fmt, ...)
 
 static const int PTR_SLOTS = 4;
 static const size_t PTR_SLOT_CAP = 4096;   // addresses per slot
+void scatter_release();                     // side streams of tstwo_scatter_shards (defined with them)
 
 int make_colset(const tstwo_dptr *cols, int n_cols, int slot, ColSet *out)
 {
@@ -207,6 +208,8 @@ int tstwo_shutdown(void)
         }
         g_trees.clear();
     }
+    pipeline_release();
+    scatter_release();
     cudaFree(c.d_ptr_table);
     cudaStreamDestroy(c.own_stream);
     cudaStreamDestroy(c.copy_stream);
@@ -369,6 +372,18 @@ int tstwo_scatter_shards(tstwo_dptr evals_sharded, int n_cols, uint64_t rows_per
     g_scatter_pending = true;
     return 0;
 }
+}  // extern "C"
+void tstwo::scatter_release()
+{
+    for (int k = 0; k < 4; k++) {
+        if (g_scatter_streams[k]) cudaStreamDestroy(g_scatter_streams[k]);
+        if (g_scatter_done[k]) cudaEventDestroy(g_scatter_done[k]);
+        g_scatter_streams[k] = nullptr; g_scatter_done[k] = nullptr;
+    }
+    if (g_scatter_fork) cudaEventDestroy(g_scatter_fork);
+    g_scatter_fork = nullptr; g_scatter_pending = false;
+}
+extern "C" {
 // the library's stream waits for every scatter copy issued so far
 int tstwo_scatter_join(void)
 {

@@ -104,5 +104,7 @@ int fft_evaluate(const ColSet &src, int poly_log, const ColSet &dst, int n_cols,
 int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, int n_cols, uint8_t *out);
 // leaf layer fed in column chunks: absorbs columns [c0, c0 + nc) (given as `cols`) of leaves of total_cols words
 int merkle_leaf_absorb(int log_size, const ColSet &cols, int c0, int nc, int total_cols, uint8_t *leaf_layer);
+// tstwo_shutdown: frees the scratch and the side stream / events pipeline.cu keeps between calls
+void pipeline_release();
 
 }  // namespace tstwo

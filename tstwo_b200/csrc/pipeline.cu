@@ -214,6 +214,17 @@ int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tst
 }
 }  // namespace
 
+namespace tstwo {
+void pipeline_release()
+{
+    if (g_coeff_scratch) cudaFree(g_coeff_scratch);
+    g_coeff_scratch = nullptr; g_coeff_scratch_words = 0;
+    if (g_peer_stream) cudaStreamDestroy(g_peer_stream);
+    g_peer_stream = nullptr;
+    for (auto &e : g_peer_ev) { if (e) cudaEventDestroy(e); e = nullptr; }
+}
+}  // namespace tstwo
+
 extern "C" {
 int tstwo_lde_columns_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, tstwo_dptr coeffs,
                                tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards, int col_offset, uint32_t flags)
