@@ -185,6 +185,26 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------ cuda arm
+# Merkle root of the default job (256 x 2^22, blow-up 2, the trace of make_trace): equal at every world size, printed by
+# every round's driver run, and checked against the ORACLE's root of the same trace by
+# tests/test_gpu_config_sizes.py::test_config3_every_column_and_root_against_oracle
+BENCH_ROOT = "6625eaa9c95ec2ba1258dc34cd187601c8eae7333050c25a7a7cb66b3cd3a53d"
+
+
+def make_trace(torch, dev, rank, world, n_cols, n):
+    """This rank's column shard of the synthetic trace: uniform random canonical M31, generated on the device
+    in 8 column blocks with fixed seeds so that every world size <= 8 sees the same job (same root)."""
+    nblk = 8 if n_cols % 8 == 0 else 1
+    bs = n_cols // nblk
+    lc = n_cols // world
+    assert lc % bs == 0
+    trace = torch.empty((lc, n), dtype=torch.int32, device=dev)
+    for k in range(lc // bs):
+        g = torch.Generator(device=dev); g.manual_seed(0x5EED0003 + rank * (lc // bs) + k)
+        trace[k * bs:(k + 1) * bs] = torch.randint(0, P, (bs, n), dtype=torch.int32, device=dev, generator=g)
+    return trace
+
+
 def cpu_baseline(args):
     import numpy as np
     import oracle as orc
@@ -244,15 +264,7 @@ def run_cuda(args):
     tw = C.c_uint64()
     chk(L.tstwo_twiddles_precompute(1 << (31 - (ext - 1) - 2), ext - 1, C.byref(tw)))
 
-    # synthetic trace: uniform random canonical M31, column c of the job uses stream c
-    # generated in 8 column blocks with fixed seeds so that every world size <= 8 sees the same job (same root)
-    nblk = 8 if n_cols % 8 == 0 else 1
-    bs = n_cols // nblk
-    assert lc % bs == 0
-    trace = torch.empty((lc, n), dtype=torch.int32, device=dev)
-    for k in range(lc // bs):
-        g = torch.Generator(device=dev); g.manual_seed(0x5EED0003 + rank * (lc // bs) + k)
-        trace[k * bs:(k + 1) * bs] = torch.randint(0, P, (bs, n), dtype=torch.int32, device=dev, generator=g)
+    trace = make_trace(torch, dev, rank, world, n_cols, n)
     root = (C.c_uint8 * 32)()
     if world == 1:
         coeffs = torch.empty((lc, n), dtype=torch.int32, device=dev)

@@ -1,0 +1,44 @@
+/*
+ * tstwo_cuda_debug.h -- test / measurement hooks of libtstwo_cuda.so.  NOT part of the drop-in boundary
+ * (include/tstwo_cuda.h): nothing a TStwo host calls.  They exist so that tests/ can force every kernel family and
+ * replay the reference's golden field vectors on the device arithmetic, and so that bench.py can name what ran.
+ */
+#ifndef TSTWO_CUDA_DEBUG_H
+#define TSTWO_CUDA_DEBUG_H
+
+#include "tstwo_cuda.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* FFT pass family: 0 = bulk-copy (TMA) persistent passes where they apply (default), 1 = cp.async persistent passes
+ * (fft_stream.cu), 2 = one CTA per tile (fft.cu) */
+int tstwo_debug_set_fft_stream(int mode);
+/* per-layer kernels only (the on-device cross-check of the tiled passes) */
+int tstwo_debug_force_naive_fft(int on);
+/* rows per thread of the fft.cu family: 16 (default) or 8 */
+int tstwo_debug_set_fft_radix(int rows_per_thread);
+/* what the last transform ran: bit 0 tiled, bits 1.. family */
+int tstwo_debug_last_fft_mode(void);
+/* top stage of the bulk-copy passes: 1 = tensor cores (tcgen05 kind::i8, tc_stage.cuh; default), 0 = integer pipes */
+int tstwo_debug_set_fft_tc(int on);
+
+/* Merkle leaf layer: 1 = bulk-copy-fed kernel where it applies (default), 0 = merkle_layer_kernel always */
+int tstwo_debug_set_leaf_mode(int mode);
+int tstwo_debug_last_leaf_mode(void);
+
+/* DEEP quotients / wide-Fibonacci: 0 auto, 1 integer-pipe kernel, 2 INT8 tensor-core kernel */
+int tstwo_debug_set_quot_mode(int mode);
+int tstwo_debug_last_quot_mode(void);
+
+/* Device field arithmetic (csrc/m31.cuh), one operation per operand set.  a, b, out: HOST arrays of n x 4 words.
+ * field 0 = M31 (word 0), 1 = CM31 (words 0..1), 2 = QM31.  op: 0 add, 1 sub, 2 mul, 3 neg, 4 inverse,
+ * 5 QM31 x CM31 (fields/qm31.ts mul_cm31), 6 x M31 (b word 0), 7 M31 reduce of the u64 (a word 0 | word 1 << 32)
+ * (fields/m31.ts:60-101), 8 M31 partial_reduce (fields/m31.ts:39-44), 9 M31 square. */
+int tstwo_debug_field_op(int field, int op, const uint32_t *a, const uint32_t *b, uint32_t *out, int n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

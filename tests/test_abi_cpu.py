@@ -20,6 +20,19 @@ def test_library_exports_every_header_symbol():
     for n in names:
         assert hasattr(lib, n), n
         assert n in _lib.SIGNATURES, n
+    # the test / measurement hooks are declared too (include/tstwo_cuda_debug.h), and nothing named tstwo_* is exported
+    # without a declaration in one of the two headers
+    dbg = open(os.path.join(ROOT, "include", "tstwo_cuda_debug.h")).read()
+    dnames = set(re.findall(r"\b(tstwo_debug_[a-z0-9_]+)\s*\(", dbg))
+    assert dnames == set(_lib.DEBUG_SIGNATURES), dnames ^ set(_lib.DEBUG_SIGNATURES)
+    for n in dnames:
+        assert hasattr(lib, n), n
+    import subprocess
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.SO_PATH], capture_output=True, text=True).stdout
+    exported = set(re.findall(r" T (tstwo_[a-z0-9_]+)$", out, flags=re.M))
+    assert exported, "nm found no exports"
+    undeclared = exported - names - dnames
+    assert not undeclared, f"exported but declared in no header: {sorted(undeclared)}"
 
 
 def test_no_cpu_fallback():

@@ -1,0 +1,749 @@
+// Radix-16 M31 FFT stage on the 5th-generation tensor cores (tcgen05.mma kind::i8, accumulators in TMEM): exactness and
+// throughput probe for the circle-FFT passes of tstwo_b200/csrc/fft_tma.cu.
+//
+// A radix-16 stage applies one 16 x 16 matrix W over M31 (the product of four butterfly layers, fft.ts:12-30) to many
+// 16-element vectors.  Exact on INT8 tensor cores by byte splitting:  f = sum_i 2^(8i) f_i  and
+// (2^(8i) W[r][c]) mod P = sum_j 2^(8j) w[r][c][i][j]  give  out[r] = sum_j 2^(8j) sum_(c,i) f_(c,i) w[r][c][i][j]  (mod P):
+// a [vectors x 64] x [64 x 64] u8 product with s32 accumulators (each < 64 * 255^2 < 2^22), recombined mod P on the
+// integer pipes.  A u32 word of data IS four consecutive K-bytes of its vector, so with the A operand in TMEM (lane =
+// vector, column = element) the data need no byte transposition: LDS -> tcgen05.st -> tcgen05.mma -> tcgen05.ld.
+//
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o tools/tc_stage tools/tc_stage.cu
+// Run  : tools/tc_stage            (correctness of one MMA, layout probes on failure, then the throughput loop)
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../tstwo_b200/csrc/m31.cuh"
+#include "../tstwo_b200/csrc/tc_stage.cuh"
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at line %d\n", cudaGetErrorString(e_), __LINE__); exit(1); } } while (0)
+
+static constexpr uint32_t P = 0x7fffffffu;
+
+// ---------------------------------------------------------------- device helpers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t ncols)
+{
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t ncols)
+{
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st16(uint32_t addr, const uint32_t (&v)[16])
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+                 ::"r"(addr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+                 "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t addr, uint32_t *v)
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+                   "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t done, spins = 0;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (!done && ++spins > (1u << 20)) __trap();
+    } while (!done);
+}
+// D[tmem] (+)= A[tmem] * B[smem desc], M = 128, u8 x u8 -> s32
+__device__ __forceinline__ void mma_i8_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void mma_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// instruction descriptor (cute/arch/mma_sm100_desc.hpp InstrDescriptor): D = s32, A = B = u8, both K-major, M = 128, N
+__host__ __device__ constexpr uint32_t make_idesc(int n) { return (2u << 4) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24); }
+// shared-memory matrix descriptor, no swizzle (SmemDescriptor): start >> 4, LBO >> 4 at bit 16, SBO >> 4 at bit 32, version 1 at bit 46
+__device__ __forceinline__ uint64_t make_sdesc(uint32_t addr, uint32_t lbo, uint32_t sbo)
+{
+    return (uint64_t)((addr >> 4) & 0x3fff) | ((uint64_t)((lbo >> 4) & 0x3fff) << 16) | ((uint64_t)((sbo >> 4) & 0x3fff) << 32) | (1ull << 46);
+}
+
+// byte address of weight byte (n, k) inside a 64 x 64 K-major no-swizzle B tile: core matrix = 8 rows (n) x 16 bytes (k)
+__host__ __device__ constexpr int b_off(int n, int k) { return (k >> 4) * 1024 + (n >> 3) * 128 + (n & 7) * 16 + (k & 15); }
+constexpr uint32_t B_KCHUNK = 1024, B_NGROUP = 128, B_BYTES = 4096;
+
+// recombination of the four accumulators of one output: any u32 congruent to the value (feeds another tensor-core stage)
+__device__ __forceinline__ uint32_t recombine_lazy(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3)
+{
+    const uint32_t lo = a0 + (a1 << 8), hi = a2 + (a3 << 8);          // < 2^31 each
+    const uint64_t p = (uint64_t)hi * 0x20000u;                        // 2 * hi * 2^16
+    return lo + (uint32_t)(p >> 32) + ((uint32_t)p >> 1);              // < 2^32
+}
+__device__ __forceinline__ uint32_t canonical(uint32_t x) { return m31::csub((x & P) + (x >> 31)); }
+
+// ---------------------------------------------------------------- test 1: one MMA pair, raw accumulators out
+// variant bit 0: swap LBO / SBO in the B descriptor
+__global__ void __launch_bounds__(128, 1) k_one_mma(const uint32_t *data, const uint8_t *bmat, uint32_t *acc_out, int variant)
+{
+    __shared__ __align__(1024) uint8_t sB[B_BYTES];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < B_BYTES / 4; i += 128) reinterpret_cast<uint32_t *>(sB)[i] = reinterpret_cast<const uint32_t *>(bmat)[i];
+    if (tid == 0) { mbar_init(smem_u32(&bar), 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    if (warp == 0) tmem_alloc(smem_u32(&tmem_base_s), 128);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");        // generic-proxy writes of sB -> tensor-core (async proxy) reads
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tbase = tmem_base_s, lane_addr = tbase + ((uint32_t)(warp * 32) << 16);
+    uint32_t v[16];
+#pragma unroll
+    for (int c = 0; c < 16; c++) v[c] = data[tid * 16 + c];
+    tmem_st16(lane_addr + 0, v);
+    tc_wait_st();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+        tc_fence_after();
+        const uint32_t lbo = (variant & 1) ? B_NGROUP : B_KCHUNK, sbo = (variant & 1) ? B_KCHUNK : B_NGROUP;
+        const uint32_t idesc = make_idesc(64);
+        mma_i8_ts(tbase + 64, tbase + 0, make_sdesc(smem_u32(sB), lbo, sbo), idesc, 0);
+        mma_i8_ts(tbase + 64, tbase + 8, make_sdesc(smem_u32(sB) + 2 * B_KCHUNK, lbo, sbo), idesc, 1);
+        mma_commit(smem_u32(&bar));
+    }
+    mbar_wait(smem_u32(&bar), 0);
+    tc_fence_after();
+    uint32_t acc[64];
+#pragma unroll
+    for (int q = 0; q < 4; q++) tmem_ld16(lane_addr + 64 + 16 * q, acc + 16 * q);
+    tc_wait_ld();
+#pragma unroll
+    for (int n = 0; n < 64; n++) acc_out[tid * 64 + n] = acc[n];
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tbase, 128);
+}
+
+// ---------------------------------------------------------------- test 2: throughput of the whole stage on resident tiles
+// 512 threads = 4 groups of 128; each group owns a 32 KiB tile [256 rows][32 words] in shared memory (the strided-pass
+// tile of fft_tma.cu) and applies the stage over the upper row nibble: vector (rlow, w) = rows c * 16 + rlow, c = 0..15.
+// MODE 0: lazy recombination (next stage is another tensor-core stage); 1: canonical outputs; 2: no MMA / TMEM at all
+// (LDS + recombination of the loaded words + STS: the integer-side cost alone); 3: scalar butterflies (today's stage)
+__device__ long long g_tl[64];
+__device__ int g_stagger = 0;   // SM clocks of start delay per group index (desynchronises the four groups)
+__device__ __forceinline__ void stagger(int g) { const long long t0 = clock64(); while (clock64() - t0 < (long long)g * g_stagger) { } }
+#define TL(i) do { if (MODE == 0 && tid == 0 && blockIdx.x == 0 && it == 7 && b == 1) g_tl[i] = clock64(); } while (0)
+template <int MODE>
+__global__ void __launch_bounds__(512, 1) k_stage_loop(const uint8_t *bmat, const uint32_t *tw2, uint32_t *tiles_io, long long *clocks, int iters)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint32_t *tiles = reinterpret_cast<uint32_t *>(smem);                       // 4 x 8192 words
+    uint8_t *sB = smem + 4 * 32768;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sB + B_BYTES);
+    uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(bars + 4);
+    const int tid = threadIdx.x, g = tid >> 7, tg = tid & 127, q = tg >> 5, lane = tid & 31;
+    uint32_t *tile = tiles + g * 8192;
+    for (int i = tg; i < 8192; i += 128) tile[i] = tiles_io[((size_t)blockIdx.x * 4 + g) * 8192 + i];
+    for (int i = tid; i < B_BYTES / 4; i += 512) reinterpret_cast<uint32_t *>(sB)[i] = reinterpret_cast<const uint32_t *>(bmat)[i];
+    if (tid == 0) {
+        for (int i = 0; i < 4; i++) mbar_init(smem_u32(bars + i), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 32) tmem_alloc(smem_u32(tmem_base_s), 512);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tbase = *tmem_base_s + g * 128 + ((uint32_t)(q * 32) << 16);   // A at +0 (16 columns), D at +64 (64 columns)
+    const uint32_t idesc = make_idesc(64);
+    const uint64_t bd0 = make_sdesc(smem_u32(sB), B_KCHUNK, B_NGROUP), bd1 = make_sdesc(smem_u32(sB) + 2 * B_KCHUNK, B_KCHUNK, B_NGROUP);
+    const uint32_t bar = smem_u32(bars + g);
+    uint32_t parity = 0;
+    uint32_t t[15];
+    if (MODE == 3)
+#pragma unroll
+        for (int i = 0; i < 15; i++) t[i] = tw2[i];
+    const long long c0 = clock64();
+    if (MODE != 3) stagger(g);
+    for (int it = 0; it < iters; it++) {
+        if (MODE == 3) {
+            // today's mapping: a thread owns 16 units (rows c * 16 + r) x 4 lanes
+#pragma unroll 1
+            for (int half = 0; half < 1; half++) {
+                uint32_t v[16][4];
+                uint4 *b4 = reinterpret_cast<uint4 *>(tile) + tg;               // unit tg of row 0: row r = tg >> 3, 16-byte piece tg & 7
+#pragma unroll
+                for (int c = 0; c < 16; c++) { const uint4 a = b4[c * 128]; v[c][0] = a.x; v[c][1] = a.y; v[c][2] = a.z; v[c][3] = a.w; }
+#pragma unroll
+                for (int k = 3; k >= 0; k--)
+#pragma unroll
+                    for (int d = 0; d < 16; d++) {
+                        if (d & (1 << k)) continue;
+                        const uint32_t w = t[(8 >> k) - 1 + (d >> (k + 1))];
+#pragma unroll
+                        for (int e = 0; e < 4; e++) m31::butterfly(v[d][e], v[d | (1 << k)][e], w);
+                    }
+#pragma unroll
+                for (int c = 0; c < 16; c++) b4[c * 128] = make_uint4(v[c][0], v[c][1], v[c][2], v[c][3]);
+            }
+            asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
+            continue;
+        }
+#pragma unroll 1
+        for (int b = 0; b < 4; b++) {
+            uint32_t *col = tile + (4 * b + q) * 32 + lane;                     // element c of the vector at col[c * 512]
+            TL(0);
+            uint32_t v[16];
+#pragma unroll
+            for (int c = 0; c < 16; c++) v[c] = col[c * 512];
+            uint32_t o[16];
+            if (MODE == 2) {
+#pragma unroll
+                for (int r = 0; r < 16; r++) o[r] = recombine_lazy(v[r] & 0x3fffff, v[(r + 1) & 15] >> 10, v[(r + 2) & 15] & 0x3fffff, v[(r + 3) & 15] >> 10);
+            } else {
+                tmem_st16(tbase, v);
+                TL(1);
+                tc_wait_st();
+                TL(2);
+                tc_fence_before();
+                asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
+                TL(3);
+                if (tg == 0) {
+                    tc_fence_after();
+                    mma_i8_ts(tbase + 64, tbase, bd0, idesc, 0);
+                    mma_i8_ts(tbase + 64, tbase + 8, bd1, idesc, 1);
+                    mma_commit(bar);
+                }
+                TL(4);
+                mbar_wait(bar, parity);
+                TL(5);
+                parity ^= 1;
+                tc_fence_after();
+#pragma unroll
+                for (int h = 0; h < 4; h++) {
+                    uint32_t acc[16];
+                    tmem_ld16(tbase + 64 + 16 * h, acc);
+                    tc_wait_ld();
+#pragma unroll
+                    for (int r = 0; r < 4; r++) {
+                        const uint32_t x = recombine_lazy(acc[4 * r], acc[4 * r + 1], acc[4 * r + 2], acc[4 * r + 3]);
+                        o[4 * h + r] = MODE == 1 ? canonical(x) : x;
+                    }
+                }
+            }
+            TL(6);
+#pragma unroll
+            for (int c = 0; c < 16; c++) col[c * 512] = o[c];
+            TL(7);
+        }
+        asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
+    }
+    const long long c1 = clock64();
+    if (tid == 0) clocks[blockIdx.x] = c1 - c0;
+    for (int i = tg; i < 8192; i += 128) tiles_io[((size_t)blockIdx.x * 4 + g) * 8192 + i] = tile[i];
+    tc_fence_before();
+    __syncthreads();
+    if (tid < 32) tmem_dealloc(*tmem_base_s, 512);
+}
+
+
+// ---------------------------------------------------------------- test 2b: the stage as it would sit in fft_tma.cu
+// Same tile and groups; a thread owns 16 units x 4 lanes like the scalar stages (LDS.128 / STS.128), i.e. four vectors
+// (rlow = tg >> 3, w = 4 (tg & 7) + e).  All four go to TMEM at once (A_e = columns 16 e), then four MMA pairs run
+// through ONE accumulator block D; lanes signal "D read" with bar.arrive and only the issuing warp waits for it.
+// CANON: canonical outputs.
+template <bool CANON>
+__global__ void __launch_bounds__(512, 1) k_stage_loop4(const uint8_t *bmat, uint32_t *tiles_io, long long *clocks, int iters)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint32_t *tiles = reinterpret_cast<uint32_t *>(smem);
+    uint8_t *sB = smem + 4 * 32768;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sB + B_BYTES);
+    uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(bars + 4);
+    const int tid = threadIdx.x, g = tid >> 7, tg = tid & 127, q = tg >> 5;
+    uint32_t *tile = tiles + g * 8192;
+    for (int i = tg; i < 8192; i += 128) tile[i] = tiles_io[((size_t)blockIdx.x * 4 + g) * 8192 + i];
+    for (int i = tid; i < B_BYTES / 4; i += 512) reinterpret_cast<uint32_t *>(sB)[i] = reinterpret_cast<const uint32_t *>(bmat)[i];
+    if (tid == 0) {
+        for (int i = 0; i < 4; i++) mbar_init(smem_u32(bars + i), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 32) tmem_alloc(smem_u32(tmem_base_s), 512);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tcol = *tmem_base_s + g * 128;                                // A_e at +16 e, D at +64
+    const uint32_t tbase = tcol + ((uint32_t)(q * 32) << 16);
+    const uint32_t idesc = make_idesc(64);
+    const uint64_t bd0 = make_sdesc(smem_u32(sB), B_KCHUNK, B_NGROUP), bd1 = make_sdesc(smem_u32(sB) + 2 * B_KCHUNK, B_KCHUNK, B_NGROUP);
+    const uint32_t bar = smem_u32(bars + g);
+    uint32_t parity = 0;
+    uint4 *b4 = reinterpret_cast<uint4 *>(tile) + tg;
+    const long long c0 = clock64();
+    stagger(g);
+    for (int it = 0; it < iters; it++) {
+        uint32_t v[4][16];                                                       // v[e][c]
+#pragma unroll
+        for (int c = 0; c < 16; c++) { const uint4 a = b4[c * 128]; v[0][c] = a.x; v[1][c] = a.y; v[2][c] = a.z; v[3][c] = a.w; }
+#pragma unroll
+        for (int e = 0; e < 4; e++) tmem_st16(tbase + 16 * e, v[e]);
+        tc_wait_st();
+        tc_fence_before();
+        asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            if (tg == 0) {
+                tc_fence_after();
+                mma_i8_ts(tcol + 64, tcol + 16 * e, bd0, idesc, 0);
+                mma_i8_ts(tcol + 64, tcol + 16 * e + 8, bd1, idesc, 1);
+                mma_commit(bar);
+            }
+            mbar_wait(bar, parity);
+            parity ^= 1;
+            tc_fence_after();
+            uint32_t acc[2][16];
+            tmem_ld16(tbase + 64, acc[0]);
+#pragma unroll
+            for (int h = 0; h < 4; h++) {
+                tc_wait_ld();
+                if (h < 3) tmem_ld16(tbase + 64 + 16 * (h + 1), acc[(h + 1) & 1]);
+                else if (e < 3) {                                                // D has been read: the next MMA pair may overwrite it
+                    tc_fence_before();
+                    if (q == 0) asm volatile("bar.sync %0, 128;" ::"r"(g + 5) : "memory");
+                    else asm volatile("bar.arrive %0, 128;" ::"r"(g + 5) : "memory");
+                }
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    const uint32_t *a = acc[h & 1] + 4 * r;
+                    const uint32_t x = recombine_lazy(a[0], a[1], a[2], a[3]);
+                    v[e][4 * h + r] = CANON ? canonical(x) : x;
+                }
+                if (h == 3 && e < 3 && tg == 0) {
+                    // (the issue of the next pair sits at the top of the next e iteration)
+                }
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 16; c++) b4[c * 128] = make_uint4(v[0][c], v[1][c], v[2][c], v[3][c]);
+        asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
+    }
+    const long long c1 = clock64();
+    if (tid == 0) clocks[blockIdx.x] = c1 - c0;
+    for (int i = tg; i < 8192; i += 128) tiles_io[((size_t)blockIdx.x * 4 + g) * 8192 + i] = tile[i];
+    tc_fence_before();
+    __syncthreads();
+    if (tid < 32) tmem_dealloc(*tmem_base_s, 512);
+}
+
+// ---------------------------------------------------------------- test 2c: the shipped stage (tstwo_b200/csrc/tc_stage.cuh), weights built on the device
+__global__ void __launch_bounds__(512, 1) k_stage_loop6(const uint32_t *tw2, uint32_t *tiles_io, long long *clocks, int iters)
+{
+    namespace tc = tstwo::tc;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint32_t *tiles = reinterpret_cast<uint32_t *>(smem);
+    uint8_t *sB = smem + 4 * 32768;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sB + tc::B_BYTES);
+    uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(bars + 4);
+    uint32_t *heap = tmem_base_s + 4, *scratch = heap + 16;
+    const int tid = threadIdx.x, g = tid >> 7, tg = tid & 127, lane = tid & 31;
+    uint32_t *tile = tiles + g * 8192;
+    for (int i = tg; i < 8192; i += 128) tile[i] = tiles_io[((size_t)blockIdx.x * 4 + g) * 8192 + i];
+    // heap[(8 >> k) + j] = twiddle j of digit bit k  <-  the host's t[(8 >> k) - 1 + j]
+    if (tid < 15) heap[tid + 1] = tw2[tid];
+    if (tid == 0) {
+        for (int i = 0; i < 4; i++) mbar_init(smem_u32(bars + i), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 32) tc::tmem_alloc(smem_u32(tmem_base_s), 512);
+    tc::fence_before();
+    __syncthreads();
+    tc::fence_after();
+    tc::build_weights<false>(sB, scratch, heap, 0, tid, 512);
+    tc::Group gr;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    gr.tmem = __shfl_sync(0xffffffffu, *tmem_base_s, 0) + (uint32_t)(warp >> 2) * 128;
+    gr.tmem_lane = gr.tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    gr.bar = smem_u32(bars) + 8 * (warp >> 2);
+    gr.bar_a = 1 + (warp >> 2);
+    gr.bar_d = 5 + (warp >> 2);
+    gr.issuer_warp = (warp & 3) == 0;
+    const uint64_t bd0 = tc::make_sdesc(smem_u32(sB), tc::B_KCHUNK, tc::B_NGROUP), bd1 = tc::make_sdesc(smem_u32(sB) + 2 * tc::B_KCHUNK, tc::B_KCHUNK, tc::B_NGROUP);
+    uint4 *b4 = reinterpret_cast<uint4 *>(tile) + tg;
+    const long long c0 = clock64();
+    for (int it = 0; it < iters; it++) {
+        uint32_t v[16][4];
+#pragma unroll
+        for (int c = 0; c < 16; c++) { const uint4 a = b4[c * 128]; v[c][0] = a.x; v[c][1] = a.y; v[c][2] = a.z; v[c][3] = a.w; }
+        tc::stage16(v, gr, bd0, bd1, lane);
+#pragma unroll
+        for (int c = 0; c < 16; c++) b4[c * 128] = make_uint4(v[c][0], v[c][1], v[c][2], v[c][3]);
+        asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
+    }
+    const long long c1 = clock64();
+    if (tid == 0) clocks[blockIdx.x] = c1 - c0;
+    for (int i = tg; i < 8192; i += 128) tiles_io[((size_t)blockIdx.x * 4 + g) * 8192 + i] = tile[i];
+    tc::fence_before();
+    __syncthreads();
+    if (tid < 32) tc::tmem_dealloc(*tmem_base_s, 512);
+}
+
+// ---------------------------------------------------------------- test 3: TMEM read bandwidth (tcgen05.ld 32x32b.x16 / .x64), 16 warps per SM
+__device__ __forceinline__ void tmem_ld64(uint32_t addr, uint32_t *v)
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x64.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, "
+                 "%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, "
+                 "%48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [%64];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+                   "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]),
+                   "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]),
+                   "=r"(v[30]), "=r"(v[31]), "=r"(v[32]), "=r"(v[33]), "=r"(v[34]), "=r"(v[35]), "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]),
+                   "=r"(v[40]), "=r"(v[41]), "=r"(v[42]), "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]), "=r"(v[49]),
+                   "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]), "=r"(v[57]), "=r"(v[58]), "=r"(v[59]),
+                   "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63]) : "r"(addr) : "memory");
+}
+// WHAT 0: ld x16 (64 B per lane per instruction), 1: ld x64, 2: st x16.  WARPS warps per SM sub-partition.
+template <int WHAT>
+__global__ void __launch_bounds__(512, 1) k_tmem_bw(uint32_t *sink, long long *clocks, int iters)
+{
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x, g = tid >> 7, q = (tid >> 5) & 3;
+    if (tid < 32) tmem_alloc(smem_u32(&tmem_base_s), 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t base = tmem_base_s + g * 128 + ((uint32_t)(q * 32) << 16);
+    uint32_t acc = 0, v[64];
+#pragma unroll
+    for (int i = 0; i < 64; i++) v[i] = tid + i;
+    const long long c0 = clock64();
+    for (int it = 0; it < iters; it++) {
+        if (WHAT == 0) {
+#pragma unroll
+            for (int h = 0; h < 4; h++) tmem_ld16(base + 64 + 16 * h, v + 16 * h);
+            tc_wait_ld();
+        } else if (WHAT == 1) {
+            tmem_ld64(base + 64, v);
+            tc_wait_ld();
+        } else {
+#pragma unroll
+            for (int h = 0; h < 4; h++) tmem_st16(base + 64 + 16 * h, *reinterpret_cast<const uint32_t(*)[16]>(v + 16 * h));
+            tc_wait_st();
+        }
+        acc ^= v[0] ^ v[17] ^ v[42] ^ v[63];
+        if (WHAT == 2) v[5] += acc;
+    }
+    const long long c1 = clock64();
+    if (tid == 0) clocks[blockIdx.x] = c1 - c0;
+    sink[blockIdx.x * 512 + tid] = acc;
+    tc_fence_before();
+    __syncthreads();
+    if (tid < 32) tmem_dealloc(tmem_base_s, 512);
+}
+
+// ---------------------------------------------------------------- test 4: tensor-pipe rate of the MMA shapes in isolation
+// one thread issues `n` MMAs (independent accumulator blocks round-robin over NACC blocks, or all into one), then commits
+__device__ __forceinline__ void mma_i8_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// PATTERN: 0 = every MMA accumulates into one block; 1 = pairs (fresh, accumulate) alternating over 2 blocks (the stage's
+// pattern with double-buffered D); 2 = pairs into ONE block (single-buffered D); 3 = chains of 4 alternating over 2 blocks
+template <int N, int PATTERN, bool A_SMEM>
+__global__ void __launch_bounds__(128, 1) k_mma_rate(long long *clocks, int n8)
+{
+    extern __shared__ __align__(1024) uint8_t smem[];      // B: up to 256 x 32 bytes = 8 KiB; A (smem form): 128 x 32 = 4 KiB
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 16384 / 4; i += 128) reinterpret_cast<uint32_t *>(smem)[i] = 0x01010101u * (i & 3);
+    if (tid == 0) { mbar_init(smem_u32(&bar), 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    if (tid < 32) tmem_alloc(smem_u32(&tmem_base_s), 512);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tb = tmem_base_s;
+    if (tid == 0) {
+        const uint32_t idesc = make_idesc(N);
+        const uint64_t bd = make_sdesc(smem_u32(smem), (uint32_t)(N / 8) * 128, 128);
+        const uint64_t ad = make_sdesc(smem_u32(smem) + 8192, 16 * 128, 128);
+        const uint32_t d0 = tb + 64, d1 = tb + 64 + (N <= 128 ? N : 0);
+        const long long c0 = clock64();
+        for (int i = 0; i < n8; i++) {
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                uint32_t d = d0, accum = 1;
+                if (PATTERN == 1) { d = (u & 2) ? d1 : d0; accum = u & 1; }
+                if (PATTERN == 2) { accum = u & 1; }
+                if (PATTERN == 3) { d = (u & 4) ? d1 : d0; accum = (u & 3) != 0; }
+                if (A_SMEM) mma_i8_ss(d, ad, bd, idesc, accum);
+                else mma_i8_ts(d, tb, bd, idesc, accum);
+            }
+        }
+        mma_commit(smem_u32(&bar));
+        const long long c1 = clock64();
+        mbar_wait(smem_u32(&bar), 0);
+        const long long c2 = clock64();
+        clocks[0] = c1 - c0;
+        clocks[1] = c2 - c0;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (tid < 32) tmem_dealloc(tb, 512);
+}
+template <int N, int PATTERN, bool A_SMEM> void run_mma_rate(long long *dclk)
+{
+    const int n8 = 64;
+    CK(cudaFuncSetAttribute(k_mma_rate<N, PATTERN, A_SMEM>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    k_mma_rate<N, PATTERN, A_SMEM><<<1, 128, 16384>>>(dclk, n8);
+    CK(cudaDeviceSynchronize());
+    long long c[2];
+    CK(cudaMemcpy(c, dclk, 16, cudaMemcpyDeviceToHost));
+    const char *pat[] = { "one accumulate chain", "pairs, 2 D blocks", "pairs, 1 D block", "chains of 4, 2 D blocks" };
+    printf("MMA rate: kind::i8 M=128 N=%3d K=32, A from %s, %-24s: issue %.1f clk/MMA, complete %.1f clk/MMA (%.0f MACs/clk/SM)\n",
+           N, A_SMEM ? "smem" : "TMEM", pat[PATTERN], (double)c[0] / (8 * n8), (double)c[1] / (8 * n8), 128.0 * N * 32 * 8 * n8 / (double)c[1]);
+}
+
+// ---------------------------------------------------------------- host model
+static uint32_t h_add(uint32_t a, uint32_t b) { uint32_t s = a + b; return s >= P ? s - P : s; }
+static uint32_t h_sub(uint32_t a, uint32_t b) { return a >= b ? a - b : a + P - b; }
+static uint32_t h_mul(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a * b) % P); }
+// four forward butterfly layers (k = 3..0) on 16 elements; twiddle of pair (d, d | 1 << k) is t[(8 >> k) - 1 + (d >> (k + 1))]
+static void h_stage(uint32_t v[16], const uint32_t t[15])
+{
+    for (int k = 3; k >= 0; k--)
+        for (int d = 0; d < 16; d++) {
+            if (d & (1 << k)) continue;
+            const uint32_t w = t[(8 >> k) - 1 + (d >> (k + 1))];
+            const uint32_t m = h_mul(v[d | (1 << k)], w), a = v[d];
+            v[d] = h_add(a, m);
+            v[d | (1 << k)] = h_sub(a, m);
+        }
+}
+static uint64_t rng_state = 0x5eed0001;
+static uint32_t rnd() { rng_state = rng_state * 6364136223846793005ull + 1442695040888963407ull; return (uint32_t)(rng_state >> 33); }
+
+int main(int argc, char **argv)
+{
+    int iters = argc > 1 ? atoi(argv[1]) : 200;
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, 0));
+    printf("device %s, %d SMs, clock %d kHz\n", prop.name, prop.multiProcessorCount, prop.clockRate);
+
+    // stage matrix W from 15 random twiddles: column c of W = stage applied to the unit vector e_c
+    uint32_t t[15], W[16][16];
+    for (int i = 0; i < 15; i++) t[i] = rnd() % P;
+    for (int c = 0; c < 16; c++) {
+        uint32_t v[16] = { 0 };
+        v[c] = 1;
+        h_stage(v, t);
+        for (int r = 0; r < 16; r++) W[r][c] = v[r];
+    }
+    // byte weights: B[n = 4 r + j][k = 4 c + i] = byte j of (W[r][c] * 2^(8 i) mod P)
+    std::vector<uint8_t> hB(B_BYTES);
+    for (int r = 0; r < 16; r++)
+        for (int c = 0; c < 16; c++)
+            for (int i = 0; i < 4; i++) {
+                const uint32_t w = h_mul(W[r][c], 1u << (8 * i));
+                for (int j = 0; j < 4; j++) hB[b_off(4 * r + j, 4 * c + i)] = (uint8_t)(w >> (8 * j));
+            }
+    std::vector<uint32_t> hdata(128 * 16);
+    for (auto &x : hdata) x = rnd();                                            // arbitrary u32 (lazy representatives allowed)
+    hdata[0] = 0xffffffffu; hdata[1] = P; hdata[2] = 0;
+
+    uint8_t *dB; uint32_t *ddata, *dacc;
+    CK(cudaMalloc(&dB, B_BYTES)); CK(cudaMalloc(&ddata, hdata.size() * 4)); CK(cudaMalloc(&dacc, 128 * 64 * 4));
+    CK(cudaMemcpy(dB, hB.data(), B_BYTES, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ddata, hdata.data(), hdata.size() * 4, cudaMemcpyHostToDevice));
+
+    const int only_mode = argc > 2 ? atoi(argv[2]) : -1;   // profiling: run just this throughput mode
+    bool layout_ok = false;
+    int good_variant = -1;
+    std::vector<uint32_t> hacc(128 * 64);
+    for (int variant = 0; variant < 2 && !layout_ok; variant++) {
+        CK(cudaMemset(dacc, 0xff, 128 * 64 * 4));
+        k_one_mma<<<1, 128>>>(ddata, dB, dacc, variant);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("variant %d: kernel failed: %s\n", variant, cudaGetErrorString(e)); return 1; }
+        CK(cudaMemcpy(hacc.data(), dacc, hacc.size() * 4, cudaMemcpyDeviceToHost));
+        long bad = 0, bad_val = 0;
+        for (int m = 0; m < 128; m++) {
+            uint32_t vec[16];
+            for (int c = 0; c < 16; c++) vec[c] = hdata[m * 16 + c] % P;   // canonical value of the (lazy) input
+            h_stage(vec, t);
+            for (int n = 0; n < 64; n++) {
+                uint32_t want = 0;
+                const int r = n >> 2, j = n & 3;
+                for (int c = 0; c < 16; c++)
+                    for (int i = 0; i < 4; i++) {
+                        const uint32_t w = h_mul(W[r][c], 1u << (8 * i));
+                        want += ((hdata[m * 16 + c] >> (8 * i)) & 255) * ((w >> (8 * j)) & 255);
+                    }
+                if (hacc[m * 64 + n] != want) {
+                    if (bad < 6) printf("  variant %d: acc[m=%d][n=%d] = %u, want %u\n", variant, m, n, hacc[m * 64 + n], want);
+                    bad++;
+                }
+            }
+            for (int r = 0; r < 16; r++) {
+                uint64_t x = 0;
+                for (int j = 0; j < 4; j++) x += (uint64_t)hacc[m * 64 + 4 * r + j] << (8 * j);
+                if ((uint32_t)(x % P) != vec[r]) bad_val++;
+            }
+        }
+        printf("one MMA pair, variant %d (LBO/SBO %s): %ld of 8192 accumulators wrong, %ld of 2048 recombined values wrong\n",
+               variant, variant ? "swapped" : "as designed", bad, bad_val);
+        if (bad == 0 && bad_val == 0) { layout_ok = true; good_variant = variant; }
+    }
+    if (!layout_ok) {
+        // layout probes: A = one byte set (k0) in every lane, B[n][k] = 1 + (k * 7 + n * 3) % 200: acc[m][n] reveals which B entry met it
+        printf("layout probes (variant 0): data byte k0 set to 1 in every vector; acc[n] should be 1 + (k0 * 7 + n * 3) %% 200\n");
+        std::vector<uint8_t> pB(B_BYTES);
+        for (int n = 0; n < 64; n++) for (int k = 0; k < 64; k++) pB[b_off(n, k)] = (uint8_t)(1 + (k * 7 + n * 3) % 200);
+        CK(cudaMemcpy(dB, pB.data(), B_BYTES, cudaMemcpyHostToDevice));
+        const int k0s[] = { 0, 1, 3, 4, 15, 16, 17, 31, 32, 33, 48, 63 };
+        for (int k0 : k0s) {
+            std::vector<uint32_t> pd(128 * 16, 0);
+            for (int m = 0; m < 128; m++) pd[m * 16 + (k0 >> 2)] = 1u << (8 * (k0 & 3));
+            CK(cudaMemcpy(ddata, pd.data(), pd.size() * 4, cudaMemcpyHostToDevice));
+            k_one_mma<<<1, 128>>>(ddata, dB, dacc, 0);
+            CK(cudaDeviceSynchronize());
+            CK(cudaMemcpy(hacc.data(), dacc, hacc.size() * 4, cudaMemcpyDeviceToHost));
+            for (int m : { 0, 1, 33, 127 }) {
+                printf("  k0=%2d lane %3d:", k0, m);
+                for (int n : { 0, 1, 2, 7, 8, 9, 16, 63 }) printf(" n%d=%u(%d)", n, hacc[m * 64 + n], 1 + (k0 * 7 + n * 3) % 200);
+                printf("\n");
+            }
+        }
+        return 2;
+    }
+
+    // ---- throughput
+    const int nsm = prop.multiProcessorCount;
+    const size_t tile_words = (size_t)nsm * 4 * 8192;
+    std::vector<uint32_t> htiles(tile_words);
+    for (auto &x : htiles) x = rnd() % P;
+    uint32_t *dtiles, *dtw; long long *dclk;
+    CK(cudaMalloc(&dtiles, tile_words * 4)); CK(cudaMalloc(&dclk, nsm * 8)); CK(cudaMalloc(&dtw, 15 * 4));
+    uint32_t t2[15];
+    for (int i = 0; i < 15; i++) t2[i] = 2 * t[i];
+    CK(cudaMemcpy(dtw, t2, sizeof t2, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dB, hB.data(), B_BYTES, cudaMemcpyHostToDevice));
+    const int smem = 4 * 32768 + B_BYTES + 64;
+    CK(cudaFuncSetAttribute(k_stage_loop<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CK(cudaFuncSetAttribute(k_stage_loop<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CK(cudaFuncSetAttribute(k_stage_loop<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CK(cudaFuncSetAttribute(k_stage_loop<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    if (good_variant != 0) printf("NOTE: throughput kernels use the designed LBO/SBO; results below are timing only\n");
+
+    // exactness of the loop kernels against the host model: 3 iterations of the stage on tile (block 0, group 1)
+    CK(cudaFuncSetAttribute(k_stage_loop4<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CK(cudaFuncSetAttribute(k_stage_loop4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CK(cudaFuncSetAttribute(k_stage_loop6, cudaFuncAttributeMaxDynamicSharedMemorySize, smem + 2048));
+    for (int mode : { 0, 1, 3, 4, 5, 6 }) {
+        CK(cudaMemcpy(dtiles, htiles.data(), tile_words * 4, cudaMemcpyHostToDevice));
+        if (mode == 0) k_stage_loop<0><<<nsm, 512, smem>>>(dB, dtw, dtiles, dclk, 3);
+        if (mode == 1) k_stage_loop<1><<<nsm, 512, smem>>>(dB, dtw, dtiles, dclk, 3);
+        if (mode == 3) k_stage_loop<3><<<nsm, 512, smem>>>(dB, dtw, dtiles, dclk, 3);
+        if (mode == 4) k_stage_loop4<false><<<nsm, 512, smem>>>(dB, dtiles, dclk, 3);
+        if (mode == 5) k_stage_loop4<true><<<nsm, 512, smem>>>(dB, dtiles, dclk, 3);
+        if (mode == 6) k_stage_loop6<<<nsm, 512, smem + 2048>>>(dtw, dtiles, dclk, 3);
+        CK(cudaDeviceSynchronize());
+        std::vector<uint32_t> got(8192);
+        CK(cudaMemcpy(got.data(), dtiles + 8192, 8192 * 4, cudaMemcpyDeviceToHost));
+        long bad = 0, noncanon = 0;
+        for (int rlow = 0; rlow < 16; rlow++)
+            for (int w = 0; w < 32; w++) {
+                uint32_t vec[16];
+                for (int c = 0; c < 16; c++) vec[c] = htiles[8192 + (c * 16 + rlow) * 32 + w];
+                for (int it = 0; it < 3; it++) h_stage(vec, t);
+                for (int c = 0; c < 16; c++) {
+                    const uint32_t gv = got[(c * 16 + rlow) * 32 + w];
+                    if (gv % P != vec[c]) bad++;
+                    if (gv >= P) noncanon++;
+                }
+            }
+        printf("stage loop mode %d, 3 iterations vs host: %ld of 8192 wrong (mod P), %ld non-canonical words\n", mode, bad, noncanon);
+    }
+
+    for (int stg : { 0, 150, 330, 600 })
+    for (int mode = 0; mode < 7; mode++) {
+        if (stg && mode != 0 && mode != 4) continue;
+        if (only_mode >= 0 && (mode != only_mode || stg)) continue;
+        CK(cudaMemcpyToSymbol(g_stagger, &stg, sizeof stg));
+        CK(cudaMemcpy(dtiles, htiles.data(), tile_words * 4, cudaMemcpyHostToDevice));
+        cudaEvent_t e0, e1;
+        CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+        for (int rep = 0; rep < 2; rep++) {
+            CK(cudaEventRecord(e0));
+            if (mode == 0) k_stage_loop<0><<<nsm, 512, smem>>>(dB, dtw, dtiles, dclk, iters);
+            if (mode == 1) k_stage_loop<1><<<nsm, 512, smem>>>(dB, dtw, dtiles, dclk, iters);
+            if (mode == 2) k_stage_loop<2><<<nsm, 512, smem>>>(dB, dtw, dtiles, dclk, iters);
+            if (mode == 3) k_stage_loop<3><<<nsm, 512, smem>>>(dB, dtw, dtiles, dclk, iters);
+            if (mode == 4) k_stage_loop4<false><<<nsm, 512, smem>>>(dB, dtiles, dclk, iters);
+            if (mode == 5) k_stage_loop4<true><<<nsm, 512, smem>>>(dB, dtiles, dclk, iters);
+            if (mode == 6) k_stage_loop6<<<nsm, 512, smem + 2048>>>(dtw, dtiles, dclk, iters);
+            CK(cudaEventRecord(e1));
+            CK(cudaDeviceSynchronize());
+        }
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        std::vector<long long> clk(nsm);
+        CK(cudaMemcpy(clk.data(), dclk, nsm * 8, cudaMemcpyDeviceToHost));
+        double avg = 0;
+        for (auto c : clk) avg += (double)c;
+        avg /= nsm;
+        const double per_tile = avg / iters / 4.0;                              // SM clocks per 8192-element tile-stage (4 groups share the SM)
+        const char *names[] = { "tcgen05 i8, lazy recombination", "tcgen05 i8, canonical outputs", "integer side only (no MMA/TMEM)", "scalar butterflies (4 layers)", "tcgen05 i8, 4 vectors/thread, lazy", "tcgen05 i8, 4 vectors/thread, canon", "tc_stage.cuh stage16 (shipped form)" };
+        printf("stagger %3d mode %d %-34s: %8.1f clk per 8192-element tile-stage per SM  (%.2f elements/clk/SM, %.2f clk per warp-element per SMSP)  kernel %.3f ms\n",
+               stg, mode, names[mode], per_tile, 8192.0 / per_tile, per_tile * 4 * 32 / 8192.0, ms);
+    }
+    if (only_mode >= 0) return 0;
+    {
+        long long tl[64];
+        CK(cudaMemcpyFromSymbol(tl, g_tl, sizeof tl));
+        printf("timeline of one batch (mode 0, block 0, thread 0; SM clocks since batch start): lds_issued %lld st_issued %lld st_done %lld bar %lld mma_issued %lld mma_done %lld ld+recombine %lld sts %lld\n",
+               0ll, tl[1] - tl[0], tl[2] - tl[0], tl[3] - tl[0], tl[4] - tl[0], tl[5] - tl[0], tl[6] - tl[0], tl[7] - tl[0]);
+    }
+    run_mma_rate<64, 0, false>(dclk); run_mma_rate<64, 1, false>(dclk); run_mma_rate<64, 2, false>(dclk); run_mma_rate<64, 3, false>(dclk);
+    run_mma_rate<128, 0, false>(dclk); run_mma_rate<128, 1, false>(dclk); run_mma_rate<128, 3, false>(dclk);
+    run_mma_rate<256, 0, false>(dclk); run_mma_rate<256, 2, false>(dclk);
+    run_mma_rate<64, 0, true>(dclk); run_mma_rate<64, 1, true>(dclk); run_mma_rate<256, 0, true>(dclk);
+    for (int what = 0; what < 3; what++) {
+        uint32_t *dsink;
+        CK(cudaMalloc(&dsink, (size_t)nsm * 512 * 4));
+        const int n = 2000;
+        if (what == 0) k_tmem_bw<0><<<nsm, 512>>>(dsink, dclk, n);
+        if (what == 1) k_tmem_bw<1><<<nsm, 512>>>(dsink, dclk, n);
+        if (what == 2) k_tmem_bw<2><<<nsm, 512>>>(dsink, dclk, n);
+        CK(cudaDeviceSynchronize());
+        std::vector<long long> clk(nsm);
+        CK(cudaMemcpy(clk.data(), dclk, nsm * 8, cudaMemcpyDeviceToHost));
+        double avg = 0;
+        for (auto c : clk) avg += (double)c;
+        avg /= nsm;
+        const char *names[] = { "tcgen05.ld 32x32b.x16 x4", "tcgen05.ld 32x32b.x64", "tcgen05.st 32x32b.x16 x4" };
+        printf("TMEM %-26s: %.1f bytes/clk/SM (16 warps, 64 columns x 32 lanes x 4 B per warp per iteration, %.1f clk per iteration)\n",
+               names[what], 16.0 * 64 * 32 * 4 * n / avg, avg / n);
+        CK(cudaFree(dsink));
+    }
+    return 0;
+}

@@ -79,6 +79,20 @@ SIGNATURES = {
                                         C.POINTER(C.c_uint8), C.c_uint32]),
 }
 
+# include/tstwo_cuda_debug.h: test / measurement hooks, not part of the drop-in boundary
+DEBUG_SIGNATURES = {
+    "tstwo_debug_set_fft_stream": (C.c_int, [C.c_int]),
+    "tstwo_debug_force_naive_fft": (C.c_int, [C.c_int]),
+    "tstwo_debug_set_fft_radix": (C.c_int, [C.c_int]),
+    "tstwo_debug_last_fft_mode": (C.c_int, []),
+    "tstwo_debug_set_fft_tc": (C.c_int, [C.c_int]),
+    "tstwo_debug_set_leaf_mode": (C.c_int, [C.c_int]),
+    "tstwo_debug_last_leaf_mode": (C.c_int, []),
+    "tstwo_debug_set_quot_mode": (C.c_int, [C.c_int]),
+    "tstwo_debug_last_quot_mode": (C.c_int, []),
+    "tstwo_debug_field_op": (C.c_int, [C.c_int, C.c_int, u32p, u32p, u32p, C.c_int]),
+}
+
 _lib = None
 
 
@@ -94,16 +108,10 @@ def load():
             fn = getattr(lib, name)   # AttributeError if the symbol is missing
             fn.restype = res
             fn.argtypes = args
-        for dbg in ("tstwo_debug_force_naive_fft", "tstwo_debug_set_fft_radix", "tstwo_debug_set_fft_stream",
-                    "tstwo_debug_set_leaf_mode", "tstwo_debug_set_quot_mode"):
-            getattr(lib, dbg).restype = C.c_int
-            getattr(lib, dbg).argtypes = [C.c_int]
-        lib.tstwo_debug_last_fft_mode.restype = C.c_int
-        lib.tstwo_debug_last_fft_mode.argtypes = []
-        lib.tstwo_debug_last_leaf_mode.restype = C.c_int
-        lib.tstwo_debug_last_leaf_mode.argtypes = []
-        lib.tstwo_debug_last_quot_mode.restype = C.c_int
-        lib.tstwo_debug_last_quot_mode.argtypes = []
+        for name, (res, args) in DEBUG_SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
         _lib = lib
     return _lib
 

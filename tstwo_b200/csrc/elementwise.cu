@@ -586,11 +586,77 @@ static int scratch(size_t bytes, uint32_t **out)
     return 0;
 }
 
+// ---- tstwo_debug_field_op: the device field arithmetic of m31.cuh, one operation per thread, so that the reference's
+// golden vectors (test-vectors/*.json, replayed by test-equivalence/fields/*.test.ts) run on the DEVICE code one to one
+__global__ void field_op_kernel(int field, int op, const uint32_t *a, const uint32_t *b, uint32_t *out, int n)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t *x = a + 4 * i, *y = b + 4 * i;
+    uint32_t r[4] = { 0, 0, 0, 0 };
+    if (field == 0) {
+        switch (op) {
+        case 0: r[0] = m31::add(x[0], y[0]); break;
+        case 1: r[0] = m31::sub(x[0], y[0]); break;
+        case 2: r[0] = m31::mul(x[0], y[0]); break;
+        case 3: r[0] = m31::neg(x[0]); break;
+        case 4: r[0] = m31::inv(x[0]); break;
+        case 7: r[0] = m31::reduce((uint64_t)x[0] | ((uint64_t)x[1] << 32)); break;
+        case 8: r[0] = m31::partial_reduce(x[0]); break;
+        case 9: r[0] = m31::sqr(x[0]); break;
+        }
+    } else if (field == 1) {
+        const m31::CM u = { x[0], x[1] }, v = { y[0], y[1] };
+        m31::CM w = { 0, 0 };
+        switch (op) {
+        case 0: w = m31::cadd(u, v); break;
+        case 1: w = m31::csub2(u, v); break;
+        case 2: w = m31::cmul(u, v); break;
+        case 3: w = m31::cneg(u); break;
+        case 4: w = m31::cinv(u); break;
+        case 6: w = m31::cmul_m(u, y[0]); break;
+        }
+        r[0] = w.re; r[1] = w.im;
+    } else {
+        const m31::QM u = { x[0], x[1], x[2], x[3] }, v = { y[0], y[1], y[2], y[3] };
+        m31::QM w = { 0, 0, 0, 0 };
+        switch (op) {
+        case 0: w = m31::qadd(u, v); break;
+        case 1: w = m31::qsub(u, v); break;
+        case 2: w = m31::qmul(u, v); break;
+        case 3: w = m31::qneg(u); break;
+        case 4: w = m31::qinv(u); break;
+        case 5: w = m31::qmul_cm(u, { y[0], y[1] }); break;
+        case 6: w = m31::qmul_m(u, y[0]); break;
+        }
+        r[0] = w.a; r[1] = w.b; r[2] = w.c; r[3] = w.d;
+    }
+    for (int k = 0; k < 4; k++) out[4 * i + k] = r[k];
+}
+
 }  // namespace tstwo
 
 using namespace tstwo;
 
 extern "C" {
+
+int tstwo_debug_field_op(int field, int op, const uint32_t *a, const uint32_t *b, uint32_t *out, int n)
+{
+    TS_REQUIRE_INIT();
+    if (field < 0 || field > 2 || n < 0 || (n && (!a || !b || !out))) return fail(TSTWO_ERR_BAD_ARG, "bad field_op arguments");
+    if (n == 0) return 0;
+    uint32_t *d;
+    const size_t words = 4 * (size_t)n;
+    int rc = scratch(3 * words * 4, &d);
+    if (rc) return rc;
+    cudaStream_t st = ctx().stream;
+    TS_CUDA(cudaMemcpyAsync(d, a, words * 4, cudaMemcpyHostToDevice, st));
+    TS_CUDA(cudaMemcpyAsync(d + words, b, words * 4, cudaMemcpyHostToDevice, st));
+    TS_LAUNCH(field_op_kernel, (unsigned)((n + 127) / 128), 128, 0, field, op, d, d + words, d + 2 * words, n);
+    TS_CUDA(cudaMemcpyAsync(out, d + 2 * words, words * 4, cudaMemcpyDeviceToHost, st));
+    TS_CUDA(cudaStreamSynchronize(st));
+    return 0;
+}
 
 int tstwo_fold_line(const tstwo_dptr src[4], int log_size, uint32_t coset_init, const uint32_t alpha[4],
                     const tstwo_dptr dst[4], tstwo_twiddles tw)

@@ -21,12 +21,19 @@
 //   * the last stage's results go back to the buffer and leave as bulk stores; the buffer is refilled (tile i+3, for
 //     the other group) at the owner group's next stage boundary, once cp.async.bulk.wait_group.read says the stores
 //     have been read out.  Arrival of a tile is an mbarrier transaction count.
+//
+// TOP stage on the tensor cores (TC = true, strided full passes).  The twiddles of a pass's highest four layers depend
+// only on index bits above the tile, so that stage is ONE 16 x 16 matrix over M31 for every vector of a run of tiles:
+// tc_stage.cuh applies it exactly as a byte-split u8 GEMM (tcgen05.mma kind::i8, accumulators in TMEM); the 1 / 2^n of the
+// last inverse pass is folded into the weights.  The lower stage stays on the integer pipes (its matrix changes with the
+// upper row nibble: 32 vectors per matrix and tile, an MMA needs 128).
 #include <cuda.h>
 
 #include <cstring>
 
 #include "fft_params.cuh"
 #include "m31.cuh"
+#include "tc_stage.cuh"
 
 namespace tstwo {
 namespace {
@@ -47,11 +54,16 @@ template <bool STRIDED> struct Cfg {
 constexpr int HEAP_WORDS = 4096 + 6 * 64;
 constexpr int T1_WORDS = 4096 + 64;
 constexpr int STRIDED_HEAP_WORDS = 8 * 256;            // up to 8 coset heaps of 255 words
-template <bool STRIDED> constexpr int smem_bytes()
+// tensor-core stage (TC): after the tile barriers come [4 MMA mbarriers | TMEM base slot] (128 B), the weight-builder
+// scratch (1 KiB) and TC_MAX_W weight tiles of 4 KiB (one per coset heap of a zero-extended top pass)
+constexpr int TC_MAX_W = 4;
+constexpr int TC_EXTRA_BYTES = 128 + 1024 + TC_MAX_W * (int)tc::B_BYTES;
+template <bool STRIDED> constexpr int smem_bytes(bool tc_stage = false)
 {
-    return Cfg<STRIDED>::NBUF * Cfg<STRIDED>::BUF_BYTES + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS) * 4 + 128;
+    return Cfg<STRIDED>::NBUF * Cfg<STRIDED>::BUF_BYTES + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS) * 4 + 128 +
+           (tc_stage ? TC_EXTRA_BYTES : 0);
 }
-static_assert(smem_bytes<false>() <= 232448 && smem_bytes<true>() <= 232448, "exceeds the 227 KiB of shared memory a CTA can opt into");
+static_assert(smem_bytes<false>() <= 232448 && smem_bytes<true>(true) <= 232448, "exceeds the 227 KiB of shared memory a CTA can opt into");
 
 struct alignas(64) TmaParams {
     CUtensorMap src_map, dst_map;   // strided pass only
@@ -329,9 +341,10 @@ template <bool STRIDED> __device__ __forceinline__ void stage_twiddles(uint32_t 
 }
 
 // all stages of a tile, in place in its buffer: load -> butterflies -> store back, group barrier between stages
-template <bool STRIDED, bool INV, bool FULL, typename AtFirstBoundary>
+struct TcTile { tc::Group gr; uint64_t bd0, bd1; int lane; };   // what the tensor-core TOP stage of a tile needs
+template <bool STRIDED, bool INV, bool FULL, bool TC, typename AtFirstBoundary>
 __device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap, int tg, int g, int j_min, uint32_t scale2,
-                                               AtFirstBoundary at_first_boundary)
+                                               const TcTile &tct, AtFirstBoundary at_first_boundary)
 {
     constexpr int NST = STRIDED ? 2 : 3, TOP = NST - 1;
 #pragma unroll 1
@@ -343,9 +356,10 @@ __device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap,
         else if (st == TOP) { tile_load<STRIDED, TOP>(buf, tg, v); U0 = Stg<STRIDED, TOP>::u0(tg); }
         else { tile_load<STRIDED, 1>(buf, tg, v); U0 = Stg<STRIDED, 1>::u0(tg); }
         if (!STRIDED && INV && st == 0) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
-        unit_layers<STRIDED, INV, FULL>(v, heap, U0, 4 * st, j_min);
+        if (TC && st == TOP) tc::stage16(v, tct.gr, tct.bd0, tct.bd1, tct.lane);   // scale2 is folded into the weights
+        else unit_layers<STRIDED, INV, FULL>(v, heap, U0, 4 * st, j_min);
         if (!STRIDED && !INV && st == 0) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
-        if (INV && s == TOP && scale2) {
+        if (!TC && INV && s == TOP && scale2) {
 #pragma unroll
             for (int d = 0; d < 16; d++)
 #pragma unroll
@@ -359,9 +373,10 @@ __device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap,
     }
 }
 
-template <bool INV, bool STRIDED, bool FULL>
+template <bool INV, bool STRIDED, bool FULL, bool TC = false>
 __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_constant__ TmaParams sp)
 {
+    static_assert(!TC || (STRIDED && FULL), "the tensor-core TOP stage is wired for full strided passes");
     extern __shared__ __align__(1024) uint8_t smem[];
     using C = Cfg<STRIDED>;
     constexpr int NBUF = C::NBUF, BUF_BYTES = C::BUF_BYTES, G = C::G;
@@ -392,6 +407,30 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
     // otherwise wait for round r + 1 while round r is still in flight -- a parity wait cannot tell those apart and
     // would fall through onto stale data.  Tiles i and i + 2 NBUF always belong to the same group, which takes them in order.
     auto bar_of = [&](uint32_t i) { return bar0 + 8 * (i % NBUF + NBUF * ((i / NBUF) & 1)); };
+    // tensor-core stage: TMEM (all 512 columns: 128 per 128-thread MMA group), one mbarrier per group, weight tiles
+    uint8_t *tc_base = reinterpret_cast<uint8_t *>(heap + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS)) + 128;
+    uint32_t *tc_scratch = reinterpret_cast<uint32_t *>(tc_base + 128);
+    uint8_t *tc_weights = tc_base + 128 + 1024;
+    TcTile tct;
+    if (TC) {
+        if (tid == 0) {
+            for (int b = 0; b < 4; b++) mbar_init(smem_u32(tc_base) + 8 * b, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        if (tid < 32) tc::tmem_alloc(smem_u32(tc_base) + 32, 512);
+        tc::fence_before();
+        __syncthreads();
+        tc::fence_after();
+        const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0), mg = warp >> 2;
+        tct.gr.tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t *>(tc_base + 32), 0) + (uint32_t)mg * 128;
+        tct.gr.tmem_lane = tct.gr.tmem + ((uint32_t)((warp & 3) * 32) << 16);
+        tct.gr.bar = smem_u32(tc_base) + 8 * mg;
+        tct.gr.bar_a = 1 + mg;                         // the group's own barrier id (group_sync): same 128 threads, phases in order
+        tct.gr.bar_d = 5 + mg;
+        tct.gr.issuer_warp = (warp & 3) == 0;
+        tct.lane = tid & 31;
+        tct.bd0 = tct.bd1 = 0;
+    }
     uint32_t par = 0;                                  // bit b + NBUF x: parity of the completed phases of barrier x of buffer b
 #ifdef TSTWO_FFT_TRACE
     int tr_n = 0, tr_all = 0;
@@ -415,6 +454,11 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
             for (uint32_t c = 0; c < (1u << sp.cosets_log); c++) stage_twiddles<STRIDED>(heap + 256 * c, p, c, tid);
         } else stage_twiddles<STRIDED>(heap, p, hi, tid);
         __syncthreads();
+        if (TC) {                                      // the run's weight tiles, one per resident heap (ends with a __syncthreads)
+            const uint32_t nw = (STRIDED && sp.cosets_log) ? (1u << sp.cosets_log) : 1u;
+            for (uint32_t c = 0; c < nw; c++)
+                tc::build_weights<INV>(tc_weights + c * tc::B_BYTES, tc_scratch, heap + 256 * c, p.scale2, tid, THREADS);
+        }
         uint32_t refill = 0xffffffffu;                 // DEFER: tile of mine whose buffer is still to be refilled
 
         for (uint32_t i = g; i < len; i += G) {
@@ -430,7 +474,12 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
             // of the group's next tile instead, so that nobody blocks on the read-out.
             constexpr bool DEFER = false;   // measured: deferring costs the inverse contiguous pass 20 % (its first stage is the longest)
             const uint32_t *tile_heap = (STRIDED && sp.cosets_log) ? heap + 256 * tl.hi : heap;
-            transform_tile<STRIDED, INV, FULL>(buf, tile_heap, tg, g, p.j_min, p.scale2, [&]() {
+            if (TC) {
+                const uint32_t w = smem_u32(tc_weights) + ((STRIDED && sp.cosets_log) ? tl.hi * tc::B_BYTES : 0u);
+                tct.bd0 = tc::make_sdesc(w, tc::B_KCHUNK, tc::B_NGROUP);
+                tct.bd1 = tc::make_sdesc(w + 2 * tc::B_KCHUNK, tc::B_KCHUNK, tc::B_NGROUP);
+            }
+            transform_tile<STRIDED, INV, FULL, TC>(buf, tile_heap, tg, g, p.j_min, p.scale2, tct, [&]() {
                 if (DEFER && refill != 0xffffffffu) {
                     if (tg < 16) bulk_wait_read();
                     const uint32_t rb = refill % NBUF;
@@ -462,13 +511,19 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
         }
         k += len;
     }
+    if (TC) {
+        tc::fence_before();
+        __syncthreads();
+        if (tid < 32) tc::tmem_dealloc(*reinterpret_cast<volatile uint32_t *>(tc_base + 32), 512);
+    }
     TRACE_CTA(1);
 }
 
-template <bool INV, bool STRIDED, bool FULL> cudaError_t set_attr()
+template <bool INV, bool STRIDED, bool FULL, bool TC = false> cudaError_t set_attr()
 {
-    return cudaFuncSetAttribute(fft_tma_kernel<INV, STRIDED, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<STRIDED>());
+    return cudaFuncSetAttribute(fft_tma_kernel<INV, STRIDED, FULL, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<STRIDED>(TC));
 }
+bool g_use_tc = true;     // tstwo_debug_set_fft_tc
 bool g_ready = false;
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -509,6 +564,7 @@ int tma_pass_init()
     TS_CUDA((set_attr<false, false, true>())); TS_CUDA((set_attr<true, false, true>()));
     TS_CUDA((set_attr<false, true, true>()));  TS_CUDA((set_attr<true, true, true>()));
     TS_CUDA((set_attr<false, true, false>())); TS_CUDA((set_attr<true, true, false>()));
+    TS_CUDA((set_attr<false, true, true, true>())); TS_CUDA((set_attr<true, true, true, true>()));
     void *fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
     TS_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
@@ -569,6 +625,9 @@ int tma_pass(bool inverse, const PassParams &p)
     if (!strided) {
         if (inverse) TS_LAUNCH((fft_tma_kernel<true, false, true>), grid, THREADS, smem_bytes<false>(), sp);
         else TS_LAUNCH((fft_tma_kernel<false, false, true>), grid, THREADS, smem_bytes<false>(), sp);
+    } else if (p.j_min == 0 && g_use_tc && (1u << sp.cosets_log) <= (unsigned)TC_MAX_W) {
+        if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, true, true>), grid, THREADS, smem_bytes<true>(true), sp);
+        else TS_LAUNCH((fft_tma_kernel<false, true, true, true>), grid, THREADS, smem_bytes<true>(true), sp);
     } else if (p.j_min == 0) {
         if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, true>), grid, THREADS, smem_bytes<true>(), sp);
         else TS_LAUNCH((fft_tma_kernel<false, true, true>), grid, THREADS, smem_bytes<true>(), sp);
@@ -581,6 +640,7 @@ int tma_pass(bool inverse, const PassParams &p)
 
 }  // namespace tstwo
 
+extern "C" int tstwo_debug_set_fft_tc(int on) { tstwo::g_use_tc = on != 0; return 0; }
 #ifdef TSTWO_FFT_TRACE
 extern "C" int tstwo_debug_fft_trace(tstwo_dptr buf) { return tstwo::tma_trace_set((long long *)buf); }
 extern "C" int tstwo_debug_fft_trace_cta(int cta) { return tstwo::tma_trace_cta(cta); }

@@ -114,6 +114,28 @@ __device__ __forceinline__ QM qmul_cm(QM x, CM y)
     return { r0.re, r0.im, r1.re, r1.im };
 }
 __device__ __forceinline__ QM qfrom(uint32_t m) { return { m, 0, 0, 0 }; }
+__device__ __forceinline__ CM cneg(CM a) { return { neg(a.re), neg(a.im) }; }
+__device__ __forceinline__ QM qneg(QM x) { return { neg(x.a), neg(x.b), neg(x.c), neg(x.d) }; }
+// fields/cm31.ts:237-251: (a - bi) / (a^2 + b^2); inverse of 0 is left as 0 (the reference throws)
+__device__ __forceinline__ CM cinv(CM a) { return cmul_m({ a.re, neg(a.im) }, inv(add(sqr(a.re), sqr(a.im)))); }
+// fields/qm31.ts:411-428: with b2 = c1^2, denom = c0^2 - (2 b2 + i b2) = c0^2 - R b2; 1/(c0 + c1 u) = (c0 - c1 u) / denom
+__device__ __forceinline__ QM qinv(QM x)
+{
+    const CM c0 = { x.a, x.b }, c1 = { x.c, x.d };
+    const CM b2 = cmul(c1, c1);
+    const CM rb2 = { sub(add(b2.re, b2.re), b2.im), add(b2.re, add(b2.im, b2.im)) };
+    const CM di = cinv(csub2(cmul(c0, c0), rb2));
+    const CM r0 = cmul(c0, di), r1 = cneg(cmul(c1, di));
+    return { r0.re, r0.im, r1.re, r1.im };
+}
+// fields/m31.ts:39-44 partialReduce ([0, 2P) -> [0, P)) and :60-101 reduce (any u64): ((((v >> 31) + v + 1) >> 31) + v) & P
+__device__ __forceinline__ uint32_t partial_reduce(uint32_t v) { return v >= P ? v - P : v; }
+__device__ __forceinline__ uint32_t reduce(uint64_t v)
+{
+    // v < 2^64: fold 31 bits at a time (2^31 = 1 mod P), then the reference's closing step on a value < 2^33
+    uint64_t s = (v & P) + ((v >> 31) & P) + (v >> 62);
+    return (uint32_t)(((((s >> 31) + s + 1) >> 31) + s) & P);
+}
 
 // ---- circle group (circle.ts:102-106) ----
 struct Pt { uint32_t x, y; };
