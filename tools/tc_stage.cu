@@ -374,7 +374,7 @@ __global__ void __launch_bounds__(512, 1) k_stage_loop6(const uint32_t *tw2, uin
     tc::fence_before();
     __syncthreads();
     tc::fence_after();
-    tc::build_weights<false>(sB, scratch, heap, 0, tid, 512);
+    tc::build_weights<false>(sB, heap, 0, tid, 512);
     tc::Group gr;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     gr.tmem = __shfl_sync(0xffffffffu, *tmem_base_s, 0) + (uint32_t)(warp >> 2) * 128;
@@ -393,6 +393,52 @@ __global__ void __launch_bounds__(512, 1) k_stage_loop6(const uint32_t *tw2, uin
         tc::stage16(v, gr, bd0, bd1, lane);
 #pragma unroll
         for (int c = 0; c < 16; c++) b4[c * 128] = make_uint4(v[c][0], v[c][1], v[c][2], v[c][3]);
+        asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
+    }
+    const long long c1 = clock64();
+    if (tid == 0) clocks[blockIdx.x] = c1 - c0;
+    for (int i = tg; i < 8192; i += 128) tiles_io[((size_t)blockIdx.x * 4 + g) * 8192 + i] = tile[i];
+    tc::fence_before();
+    __syncthreads();
+    if (tid < 32) tc::tmem_dealloc(*tmem_base_s, 512);
+}
+
+// ---------------------------------------------------------------- test 2d: tc::stage16_smem (one vector per thread and batch, in place in shared memory)
+__global__ void __launch_bounds__(512, 1) k_stage_loop7(const uint32_t *tw2, uint32_t *tiles_io, long long *clocks, int iters)
+{
+    namespace tc = tstwo::tc;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint32_t *tiles = reinterpret_cast<uint32_t *>(smem);
+    uint8_t *sB = smem + 4 * 32768;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sB + tc::B_BYTES);
+    uint32_t *tmem_base_s = reinterpret_cast<uint32_t *>(bars + 4);
+    uint32_t *heap = tmem_base_s + 4, *scratch = heap + 16;
+    const int tid = threadIdx.x, g = tid >> 7, tg = tid & 127, lane = tid & 31;
+    uint32_t *tile = tiles + g * 8192;
+    for (int i = tg; i < 8192; i += 128) tile[i] = tiles_io[((size_t)blockIdx.x * 4 + g) * 8192 + i];
+    // heap[(8 >> k) + j] = twiddle j of digit bit k  <-  the host's t[(8 >> k) - 1 + j]
+    if (tid < 15) heap[tid + 1] = tw2[tid];
+    if (tid == 0) {
+        for (int i = 0; i < 4; i++) mbar_init(smem_u32(bars + i), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 32) tc::tmem_alloc(smem_u32(tmem_base_s), 512);
+    tc::fence_before();
+    __syncthreads();
+    tc::fence_after();
+    tc::build_weights<false>(sB, heap, 0, tid, 512);
+    tc::Group gr;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    gr.tmem = __shfl_sync(0xffffffffu, *tmem_base_s, 0) + (uint32_t)(warp >> 2) * 128;
+    gr.tmem_lane = gr.tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    gr.bar = smem_u32(bars) + 8 * (warp >> 2);
+    gr.bar_a = 1 + (warp >> 2);
+    gr.bar_d = 5 + (warp >> 2);
+    gr.issuer_warp = (warp & 3) == 0;
+    const uint64_t bd0 = tc::make_sdesc(smem_u32(sB), tc::B_KCHUNK, tc::B_NGROUP), bd1 = tc::make_sdesc(smem_u32(sB) + 2 * tc::B_KCHUNK, tc::B_KCHUNK, tc::B_NGROUP);
+    const long long c0 = clock64();
+    for (int it = 0; it < iters; it++) {
+        tc::stage16_smem<4>(tile + (tg >> 5) * 32 + lane, 512, 128, gr, bd0, bd1, lane);
         asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory");
     }
     const long long c1 = clock64();
@@ -658,7 +704,8 @@ int main(int argc, char **argv)
     CK(cudaFuncSetAttribute(k_stage_loop4<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     CK(cudaFuncSetAttribute(k_stage_loop4<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     CK(cudaFuncSetAttribute(k_stage_loop6, cudaFuncAttributeMaxDynamicSharedMemorySize, smem + 2048));
-    for (int mode : { 0, 1, 3, 4, 5, 6 }) {
+    CK(cudaFuncSetAttribute(k_stage_loop7, cudaFuncAttributeMaxDynamicSharedMemorySize, smem + 2048));
+    for (int mode : { 0, 1, 3, 4, 5, 6, 7 }) {
         CK(cudaMemcpy(dtiles, htiles.data(), tile_words * 4, cudaMemcpyHostToDevice));
         if (mode == 0) k_stage_loop<0><<<nsm, 512, smem>>>(dB, dtw, dtiles, dclk, 3);
         if (mode == 1) k_stage_loop<1><<<nsm, 512, smem>>>(dB, dtw, dtiles, dclk, 3);
@@ -666,6 +713,7 @@ int main(int argc, char **argv)
         if (mode == 4) k_stage_loop4<false><<<nsm, 512, smem>>>(dB, dtiles, dclk, 3);
         if (mode == 5) k_stage_loop4<true><<<nsm, 512, smem>>>(dB, dtiles, dclk, 3);
         if (mode == 6) k_stage_loop6<<<nsm, 512, smem + 2048>>>(dtw, dtiles, dclk, 3);
+        if (mode == 7) k_stage_loop7<<<nsm, 512, smem + 2048>>>(dtw, dtiles, dclk, 3);
         CK(cudaDeviceSynchronize());
         std::vector<uint32_t> got(8192);
         CK(cudaMemcpy(got.data(), dtiles + 8192, 8192 * 4, cudaMemcpyDeviceToHost));
@@ -685,7 +733,7 @@ int main(int argc, char **argv)
     }
 
     for (int stg : { 0, 150, 330, 600 })
-    for (int mode = 0; mode < 7; mode++) {
+    for (int mode = 0; mode < 8; mode++) {
         if (stg && mode != 0 && mode != 4) continue;
         if (only_mode >= 0 && (mode != only_mode || stg)) continue;
         CK(cudaMemcpyToSymbol(g_stagger, &stg, sizeof stg));
@@ -701,6 +749,7 @@ int main(int argc, char **argv)
             if (mode == 4) k_stage_loop4<false><<<nsm, 512, smem>>>(dB, dtiles, dclk, iters);
             if (mode == 5) k_stage_loop4<true><<<nsm, 512, smem>>>(dB, dtiles, dclk, iters);
             if (mode == 6) k_stage_loop6<<<nsm, 512, smem + 2048>>>(dtw, dtiles, dclk, iters);
+            if (mode == 7) k_stage_loop7<<<nsm, 512, smem + 2048>>>(dtw, dtiles, dclk, iters);
             CK(cudaEventRecord(e1));
             CK(cudaDeviceSynchronize());
         }
@@ -712,7 +761,7 @@ int main(int argc, char **argv)
         for (auto c : clk) avg += (double)c;
         avg /= nsm;
         const double per_tile = avg / iters / 4.0;                              // SM clocks per 8192-element tile-stage (4 groups share the SM)
-        const char *names[] = { "tcgen05 i8, lazy recombination", "tcgen05 i8, canonical outputs", "integer side only (no MMA/TMEM)", "scalar butterflies (4 layers)", "tcgen05 i8, 4 vectors/thread, lazy", "tcgen05 i8, 4 vectors/thread, canon", "tc_stage.cuh stage16 (shipped form)" };
+        const char *names[] = { "tcgen05 i8, lazy recombination", "tcgen05 i8, canonical outputs", "integer side only (no MMA/TMEM)", "scalar butterflies (4 layers)", "tcgen05 i8, 4 vectors/thread, lazy", "tcgen05 i8, 4 vectors/thread, canon", "tc_stage.cuh stage16 (registers)", "tc_stage.cuh stage16_smem (in place)" };
         printf("stagger %3d mode %d %-34s: %8.1f clk per 8192-element tile-stage per SM  (%.2f elements/clk/SM, %.2f clk per warp-element per SMSP)  kernel %.3f ms\n",
                stg, mode, names[mode], per_tile, 8192.0 / per_tile, per_tile * 4 * 32 / 8192.0, ms);
     }

@@ -54,14 +54,17 @@ template <bool STRIDED> struct Cfg {
 constexpr int HEAP_WORDS = 4096 + 6 * 64;
 constexpr int T1_WORDS = 4096 + 64;
 constexpr int STRIDED_HEAP_WORDS = 8 * 256;            // up to 8 coset heaps of 255 words
-// tensor-core stage (TC): after the tile barriers come [4 MMA mbarriers | TMEM base slot] (128 B), the weight-builder
-// scratch (1 KiB) and TC_MAX_W weight tiles of 4 KiB (one per coset heap of a zero-extended top pass)
+// tensor-core stage (TC).  Strided pass: after the tile barriers come [4 MMA mbarriers | TMEM base slot] (128 B) and
+// TC_MAX_W weight tiles of 4 KiB (one per coset heap of a zero-extended top pass).  Contiguous pass: its shared memory is
+// full (232064 of 232448 bytes), so heap level 1 (the 1024 twiddles of layer 3, 4352 bytes with its pads) is NOT staged --
+// every thread fetches its four entries per tile straight from the tree in L2 -- and the weight tile + barriers sit there.
 constexpr int TC_MAX_W = 4;
-constexpr int TC_EXTRA_BYTES = 128 + 1024 + TC_MAX_W * (int)tc::B_BYTES;
+constexpr int TC_EXTRA_BYTES = 128 + TC_MAX_W * (int)tc::B_BYTES;
+constexpr int HEAP_L1_WORD = 1024 + 64 * 4;            // first word of heap level 1 of the contiguous pass (1088 words)
 template <bool STRIDED> constexpr int smem_bytes(bool tc_stage = false)
 {
     return Cfg<STRIDED>::NBUF * Cfg<STRIDED>::BUF_BYTES + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS) * 4 + 128 +
-           (tc_stage ? TC_EXTRA_BYTES : 0);
+           (tc_stage && STRIDED ? TC_EXTRA_BYTES : 0);
 }
 static_assert(smem_bytes<false>() <= 232448 && smem_bytes<true>(true) <= 232448, "exceeds the 227 KiB of shared memory a CTA can opt into");
 
@@ -194,11 +197,17 @@ template <bool STRIDED> __device__ __forceinline__ constexpr int heap_base(int l
 // the thread's base unit, sl = heap level of digit bit 0): one copy of the butterfly code serves all stages, which
 // keeps a kernel's loop body within the instruction cache (fully unrolled per stage it is ~64 KiB and the two groups,
 // sitting in different stages, evict each other: ncu stall_no_instruction 2.9 per issue, profiles/r01_k_*).
+// l1_global != nullptr (contiguous pass with the tensor-core TOP stage): heap level 1 is not in shared memory; entry q of it is
+// l1_global[q] (the tree itself, L2-resident), fetched at the top of the stage that needs it so that the latency hides
+// behind the other layers' butterflies.
 template <bool STRIDED, bool INV, bool FULL>
-__device__ __forceinline__ void unit_layers(uint32_t (&v)[16][4], const uint32_t *heap, int U0, int sl, int j_min)
+__device__ __forceinline__ void unit_layers(uint32_t (&v)[16][4], const uint32_t *heap, int U0, int sl, int j_min,
+                                            const uint32_t *l1_global = nullptr)
 {
     const int ub = STRIDED ? (U0 >> 3) : U0;           // unit-level coordinate the heap is indexed by (row / unit)
     const int padw = 4 * (U0 >> 8);
+    uint4 l1 = make_uint4(0, 0, 0, 0);
+    if (!STRIDED && l1_global && sl == 0) l1 = __ldg(reinterpret_cast<const uint4 *>(l1_global + (ub >> 2)));
 #pragma unroll
     for (int kk = 0; kk < 4; kk++) {
         const int k = INV ? kk : 3 - kk;
@@ -212,7 +221,7 @@ __device__ __forceinline__ void unit_layers(uint32_t (&v)[16][4], const uint32_t
             const uint4 a = *reinterpret_cast<const uint4 *>(q), b = *reinterpret_cast<const uint4 *>(q + 4);
             t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w; t[4] = b.x; t[5] = b.y; t[6] = b.z; t[7] = b.w;
         } else if (cnt == 4) {
-            const uint4 a = *reinterpret_cast<const uint4 *>(q);
+            const uint4 a = (!STRIDED && l1_global && l == 1) ? l1 : *reinterpret_cast<const uint4 *>(q);
             t[0] = a.x; t[1] = a.y; t[2] = a.z; t[3] = a.w;
         } else if (cnt == 2) {
             const uint2 a = *reinterpret_cast<const uint2 *>(q);
@@ -316,7 +325,8 @@ __device__ __forceinline__ void tile_drain(const TmaParams &sp, const Tile tl, u
 }
 
 // twiddles of the run of tiles with high bits `hi` (all 512 threads; one cp.async group)
-template <bool STRIDED> __device__ __forceinline__ void stage_twiddles(uint32_t *heap, const PassParams &p, uint32_t hi, int tid)
+template <bool STRIDED, bool SKIP_L1 = false>
+__device__ __forceinline__ void stage_twiddles(uint32_t *heap, const PassParams &p, uint32_t hi, int tid)
 {
     constexpr int NLEV = STRIDED ? 8 : 12;
     const int base_layer = STRIDED ? p.lo : 2;         // tree layer of heap level 0
@@ -331,6 +341,7 @@ template <bool STRIDED> __device__ __forceinline__ void stage_twiddles(uint32_t 
         }
         const int lg = 31 - __clz(e), l = NLEV - 1 - lg, i = base_layer + l, q = e - (1 << lg);
         if (STRIDED && l < p.j_min) continue;
+        if (SKIP_L1 && l == 1) continue;
         const int dst = STRIDED ? e : e + (l <= 5 ? 64 * (5 - l) + 4 * (q >> (7 - l)) : 0);
         cp_async16(smem_u32(heap + dst), p.tw2 + (p.tree_len - (1u << (p.n - i))) + (hi << lg) + q);
     }
@@ -341,7 +352,7 @@ template <bool STRIDED> __device__ __forceinline__ void stage_twiddles(uint32_t 
 }
 
 // all stages of a tile, in place in its buffer: load -> butterflies -> store back, group barrier between stages
-struct TcTile { tc::Group gr; uint64_t bd0, bd1; int lane; };   // what the tensor-core TOP stage of a tile needs
+struct TcTile { tc::Group gr; uint64_t bd0, bd1; int lane; const uint32_t *l1_global; };   // what the tensor-core TOP stage of a tile needs
 template <bool STRIDED, bool INV, bool FULL, bool TC, typename AtFirstBoundary>
 __device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap, int tg, int g, int j_min, uint32_t scale2,
                                                const TcTile &tct, AtFirstBoundary at_first_boundary)
@@ -350,24 +361,32 @@ __device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap,
 #pragma unroll 1
     for (int s = 0; s < NST; s++) {
         const int st = INV ? s : TOP - s;
-        uint32_t v[16][4];
-        int U0;
-        if (st == 0) { tile_load<STRIDED, 0>(buf, tg, v); U0 = Stg<STRIDED, 0>::u0(tg); }
-        else if (st == TOP) { tile_load<STRIDED, TOP>(buf, tg, v); U0 = Stg<STRIDED, TOP>::u0(tg); }
-        else { tile_load<STRIDED, 1>(buf, tg, v); U0 = Stg<STRIDED, 1>::u0(tg); }
-        if (!STRIDED && INV && st == 0) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
-        if (TC && st == TOP) tc::stage16(v, tct.gr, tct.bd0, tct.bd1, tct.lane);   // scale2 is folded into the weights
-        else unit_layers<STRIDED, INV, FULL>(v, heap, U0, 4 * st, j_min);
-        if (!STRIDED && !INV && st == 0) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
-        if (!TC && INV && s == TOP && scale2) {
+        if (TC && st == TOP) {
+            // tensor-core stage, in place in the buffer: vector (rlow, w) = rows c * 16 + rlow (c = 0..15), word w; batch b of
+            // the group takes rows rlow = 4 b + warp, lanes = words.  scale2 is folded into the weights.
+            // Contiguous pass: vector w (word of a chunk, 0..1023) = words c * 1028 + w of the padded chunks; the group's two MMA
+            // groups take the batches w / 128 = 2 b + (tg >> 7).
+            if (STRIDED) tc::stage16_smem<4>(reinterpret_cast<uint32_t *>(buf) + (tg >> 5) * 32 + tct.lane, 512, 128, tct.gr, tct.bd0, tct.bd1, tct.lane);
+            else tc::stage16_smem<4>(reinterpret_cast<uint32_t *>(buf) + tg, CHUNK_BYTES / 4, 256, tct.gr, tct.bd0, tct.bd1, tct.lane);
+        } else {
+            uint32_t v[16][4];
+            int U0;
+            if (st == 0) { tile_load<STRIDED, 0>(buf, tg, v); U0 = Stg<STRIDED, 0>::u0(tg); }
+            else if (st == TOP) { tile_load<STRIDED, TOP>(buf, tg, v); U0 = Stg<STRIDED, TOP>::u0(tg); }
+            else { tile_load<STRIDED, 1>(buf, tg, v); U0 = Stg<STRIDED, 1>::u0(tg); }
+            if (!STRIDED && INV && st == 0) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
+            unit_layers<STRIDED, INV, FULL>(v, heap, U0, 4 * st, j_min, TC ? tct.l1_global : nullptr);
+            if (!STRIDED && !INV && st == 0) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
+            if (INV && s == TOP && scale2) {
 #pragma unroll
-            for (int d = 0; d < 16; d++)
+                for (int d = 0; d < 16; d++)
 #pragma unroll
-                for (int e = 0; e < 4; e++) v[d][e] = m31::mul2(v[d][e], scale2);
+                    for (int e = 0; e < 4; e++) v[d][e] = m31::mul2(v[d][e], scale2);
+            }
+            if (st == 0) tile_store<STRIDED, 0>(buf, tg, v);
+            else if (st == TOP) tile_store<STRIDED, TOP>(buf, tg, v);
+            else tile_store<STRIDED, 1>(buf, tg, v);
         }
-        if (st == 0) tile_store<STRIDED, 0>(buf, tg, v);
-        else if (st == TOP) tile_store<STRIDED, TOP>(buf, tg, v);
-        else tile_store<STRIDED, 1>(buf, tg, v);
         if (s == 0) at_first_boundary();
         if (s < TOP) group_sync<Cfg<STRIDED>::GS>(g);
     }
@@ -376,7 +395,7 @@ __device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap,
 template <bool INV, bool STRIDED, bool FULL, bool TC = false>
 __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_constant__ TmaParams sp)
 {
-    static_assert(!TC || (STRIDED && FULL), "the tensor-core TOP stage is wired for full strided passes");
+    static_assert(!TC || FULL, "the tensor-core TOP stage needs all layers of its window");
     extern __shared__ __align__(1024) uint8_t smem[];
     using C = Cfg<STRIDED>;
     constexpr int NBUF = C::NBUF, BUF_BYTES = C::BUF_BYTES, G = C::G;
@@ -408,10 +427,12 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
     // would fall through onto stale data.  Tiles i and i + 2 NBUF always belong to the same group, which takes them in order.
     auto bar_of = [&](uint32_t i) { return bar0 + 8 * (i % NBUF + NBUF * ((i / NBUF) & 1)); };
     // tensor-core stage: TMEM (all 512 columns: 128 per 128-thread MMA group), one mbarrier per group, weight tiles
-    uint8_t *tc_base = reinterpret_cast<uint8_t *>(heap + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS)) + 128;
-    uint32_t *tc_scratch = reinterpret_cast<uint32_t *>(tc_base + 128);
-    uint8_t *tc_weights = tc_base + 128 + 1024;
+    // strided: [barriers | slot] (128 B) then the weight tiles, behind the tile barriers; contiguous: weight tile then
+    // [barriers | slot] in the place of heap level 1
+    uint8_t *tc_weights = STRIDED ? reinterpret_cast<uint8_t *>(heap + STRIDED_HEAP_WORDS) + 128 + 128 : reinterpret_cast<uint8_t *>(heap + HEAP_L1_WORD);
+    uint8_t *tc_base = STRIDED ? reinterpret_cast<uint8_t *>(heap + STRIDED_HEAP_WORDS) + 128 : tc_weights + tc::B_BYTES;
     TcTile tct;
+    tct.l1_global = nullptr;
     if (TC) {
         if (tid == 0) {
             for (int b = 0; b < 4; b++) mbar_init(smem_u32(tc_base) + 8 * b, 1);
@@ -425,8 +446,8 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
         tct.gr.tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t *>(tc_base + 32), 0) + (uint32_t)mg * 128;
         tct.gr.tmem_lane = tct.gr.tmem + ((uint32_t)((warp & 3) * 32) << 16);
         tct.gr.bar = smem_u32(tc_base) + 8 * mg;
-        tct.gr.bar_a = 1 + mg;                         // the group's own barrier id (group_sync): same 128 threads, phases in order
-        tct.gr.bar_d = 5 + mg;
+        tct.gr.bar_a = 8 + mg;                         // named barriers 8..11: the 128 threads of an MMA group
+        tct.gr.bar_d = 12 + mg;
         tct.gr.issuer_warp = (warp & 3) == 0;
         tct.lane = tid & 31;
         tct.bd0 = tct.bd1 = 0;
@@ -452,12 +473,13 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
                 tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar_of(i), tg);
         if (STRIDED && sp.cosets_log) {
             for (uint32_t c = 0; c < (1u << sp.cosets_log); c++) stage_twiddles<STRIDED>(heap + 256 * c, p, c, tid);
-        } else stage_twiddles<STRIDED>(heap, p, hi, tid);
+        } else stage_twiddles<STRIDED, TC && !STRIDED>(heap, p, hi, tid);
         __syncthreads();
         if (TC) {                                      // the run's weight tiles, one per resident heap (ends with a __syncthreads)
             const uint32_t nw = (STRIDED && sp.cosets_log) ? (1u << sp.cosets_log) : 1u;
             for (uint32_t c = 0; c < nw; c++)
-                tc::build_weights<INV>(tc_weights + c * tc::B_BYTES, tc_scratch, heap + 256 * c, p.scale2, tid, THREADS);
+                tc::build_weights<INV>(tc_weights + c * tc::B_BYTES, heap + 256 * c, p.scale2, tid, THREADS);
+            if (!STRIDED) tct.l1_global = p.tw2 + (p.tree_len - (1u << (p.n - 3))) + (hi << 10);   // tree layer 3 = heap level 1
         }
         uint32_t refill = 0xffffffffu;                 // DEFER: tile of mine whose buffer is still to be refilled
 
@@ -565,6 +587,7 @@ int tma_pass_init()
     TS_CUDA((set_attr<false, true, true>()));  TS_CUDA((set_attr<true, true, true>()));
     TS_CUDA((set_attr<false, true, false>())); TS_CUDA((set_attr<true, true, false>()));
     TS_CUDA((set_attr<false, true, true, true>())); TS_CUDA((set_attr<true, true, true, true>()));
+    TS_CUDA((set_attr<false, false, true, true>())); TS_CUDA((set_attr<true, false, true, true>()));
     void *fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
     TS_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
@@ -622,7 +645,10 @@ int tma_pass(bool inverse, const PassParams &p)
     unsigned grid = (unsigned)ctx().sm_count;
     if (ctx().grid_limit > 0 && grid > (unsigned)ctx().grid_limit) grid = (unsigned)ctx().grid_limit;
     if (grid > sp.n_tiles) grid = sp.n_tiles;
-    if (!strided) {
+    if (!strided && g_use_tc) {
+        if (inverse) TS_LAUNCH((fft_tma_kernel<true, false, true, true>), grid, THREADS, smem_bytes<false>(true), sp);
+        else TS_LAUNCH((fft_tma_kernel<false, false, true, true>), grid, THREADS, smem_bytes<false>(true), sp);
+    } else if (!strided) {
         if (inverse) TS_LAUNCH((fft_tma_kernel<true, false, true>), grid, THREADS, smem_bytes<false>(), sp);
         else TS_LAUNCH((fft_tma_kernel<false, false, true>), grid, THREADS, smem_bytes<false>(), sp);
     } else if (p.j_min == 0 && g_use_tc && (1u << sp.cosets_log) <= (unsigned)TC_MAX_W) {

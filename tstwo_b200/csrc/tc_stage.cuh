@@ -6,7 +6,7 @@
 // vectors.  Exactly, by byte splitting: with f = sum_i 2^(8i) f_i and (2^(8i) W[r][c]) mod P = sum_j 2^(8j) w[r][c][i][j],
 //     out[r] = sum_j 2^(8j) * ( sum_(c,i) f_(c,i) * w[r][c][i][j] )      (mod P)
 // i.e. a [vectors x 64] x [64 x 64] u8 product; every accumulator is < 64 * 255^2 < 2^22 and the four of an output are
-// recombined mod P on the integer pipes (~6 instructions + 3 for the canonical form, against 14 for two butterflies).
+// recombined mod P on the integer pipes (6 instructions, canonical result, against 14 for two butterflies).
 // A u32 word of data IS four consecutive K-bytes (c, i = 0..3) of its vector, so with the A operand in TMEM (lane =
 // vector, column = element c) the data need no byte transposition: registers -> tcgen05.st -> tcgen05.mma -> tcgen05.ld.
 // Inputs may be ANY u32 representative of the residue (bytes are bytes); outputs are canonical.
@@ -49,6 +49,20 @@ __device__ __forceinline__ void ld16(uint32_t addr, uint32_t (&v)[16])
                  : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
                    "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]) : "r"(addr) : "memory");
 }
+__device__ __forceinline__ void ld64(uint32_t addr, uint32_t (&v)[64])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x64.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, "
+                 "%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, "
+                 "%48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [%64];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+                   "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]),
+                   "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]),
+                   "=r"(v[30]), "=r"(v[31]), "=r"(v[32]), "=r"(v[33]), "=r"(v[34]), "=r"(v[35]), "=r"(v[36]), "=r"(v[37]), "=r"(v[38]), "=r"(v[39]),
+                   "=r"(v[40]), "=r"(v[41]), "=r"(v[42]), "=r"(v[43]), "=r"(v[44]), "=r"(v[45]), "=r"(v[46]), "=r"(v[47]), "=r"(v[48]), "=r"(v[49]),
+                   "=r"(v[50]), "=r"(v[51]), "=r"(v[52]), "=r"(v[53]), "=r"(v[54]), "=r"(v[55]), "=r"(v[56]), "=r"(v[57]), "=r"(v[58]), "=r"(v[59]),
+                   "=r"(v[60]), "=r"(v[61]), "=r"(v[62]), "=r"(v[63]) : "r"(addr) : "memory");
+}
 // D[tmem] (+)= A[tmem] * B[smem descriptor]; M = 128, K = 32 bytes, u8 x u8 -> s32
 __device__ __forceinline__ void mma_i8_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
 {
@@ -82,51 +96,53 @@ __device__ __forceinline__ uint64_t make_sdesc(uint32_t addr, uint32_t lbo, uint
 constexpr uint32_t B_KCHUNK = 1024, B_NGROUP = 128, B_BYTES = 4096;
 __host__ __device__ constexpr int b_off(int n, int k) { return (k >> 4) * B_KCHUNK + (n >> 3) * B_NGROUP + (n & 7) * 16 + (k & 15); }
 
-// Builds the weight tile of one stage in shared memory, all `nthreads` threads of the caller cooperating (barrier id 0 =
-// __syncthreads, so the whole CTA must call it).  tw[(8 >> k) + j] = PRE-DOUBLED twiddle j of digit bit k (k = 0..3;
-// 8 >> k twiddles per level: the unit-level heap of fft_tma.cu, levels sl..sl+3).  INV = inverse butterflies in the order
-// k = 0..3, else forward butterflies k = 3..0.  scale2 != 0: every entry is multiplied by scale2 / 2 (the 1 / 2^n of the
-// last inverse pass).  `scratch` = 256 words of shared memory.
+// Builds the weight tile of one stage in shared memory, all `nthreads` (a multiple of 64) threads of the caller cooperating;
+// ends with a __syncthreads, so the whole CTA must call it.  tw[(8 >> k) + j] = PRE-DOUBLED twiddle j of digit bit k
+// (k = 0..3; 8 >> k twiddles per level: the unit-level heap of fft_tma.cu, levels sl..sl+3).  INV = inverse butterflies
+// in the order k = 0..3, else forward butterflies k = 3..0.  scale2 != 0: every entry is multiplied by scale2 / 2 (the
+// 1 / 2^n of the last inverse pass).  No scratch memory: thread t computes column c = t % 16 of W itself (32 butterflies
+// on the unit vector e_c) and expands the rows r = t / 64 + 8 m with the byte shift i = (t / 16) % 4.
 template <bool INV>
-__device__ __forceinline__ void build_weights(uint8_t *sB, uint32_t *scratch, const uint32_t *tw, uint32_t scale2, int tid, int nthreads)
+__device__ __forceinline__ void build_weights(uint8_t *sB, const uint32_t *tw, uint32_t scale2, int tid, int nthreads)
 {
-    if (tid < 16) {                                    // column c of W = the stage applied to the unit vector e_c
-        uint32_t v[16];
+    const int c = tid & 15, i = (tid >> 4) & 3;
+    uint32_t v[16];
 #pragma unroll
-        for (int d = 0; d < 16; d++) v[d] = d == tid ? 1u : 0u;
+    for (int d = 0; d < 16; d++) v[d] = d == c ? 1u : 0u;
 #pragma unroll
-        for (int kk = 0; kk < 4; kk++) {
-            const int k = INV ? kk : 3 - kk;
+    for (int kk = 0; kk < 4; kk++) {
+        const int k = INV ? kk : 3 - kk;
 #pragma unroll
-            for (int d = 0; d < 16; d++) {
-                if (d & (1 << k)) continue;
-                const uint32_t t = tw[(8 >> k) + (d >> (k + 1))];
-                if (INV) m31::ibutterfly(v[d], v[d | (1 << k)], t);
-                else m31::butterfly(v[d], v[d | (1 << k)], t);
-            }
+        for (int d = 0; d < 16; d++) {
+            if (d & (1 << k)) continue;
+            const uint32_t t = tw[(8 >> k) + (d >> (k + 1))];
+            if (INV) m31::ibutterfly(v[d], v[d | (1 << k)], t);
+            else m31::butterfly(v[d], v[d | (1 << k)], t);
         }
-#pragma unroll
-        for (int r = 0; r < 16; r++) scratch[r * 16 + tid] = scale2 ? m31::mul2(v[r], scale2) : v[r];
     }
-    __syncthreads();
-    for (int e = tid; e < 1024; e += nthreads) {       // e = (r, c, i): the four bytes j of W[r][c] * 2^(8 i) mod P
-        const int i = e & 3, c = (e >> 2) & 15, r = e >> 6;
-        const uint32_t w = m31::mul2(scratch[r * 16 + c], 2u << (8 * i));
+    for (int r0 = tid >> 6; r0 < 16; r0 += nthreads >> 6) {
+        uint32_t x = 0;
 #pragma unroll
-        for (int j = 0; j < 4; j++) sB[b_off(4 * r + j, 4 * c + i)] = (uint8_t)(w >> (8 * j));
+        for (int r = 0; r < 16; r++) x = r == r0 ? v[r] : x;
+        if (scale2) x = m31::mul2(x, scale2);
+        const uint32_t w = m31::mul2(x, 2u << (8 * i));   // W[r0][c] * 2^(8 i) mod P
+#pragma unroll
+        for (int j = 0; j < 4; j++) sB[b_off(4 * r0 + j, 4 * c + i)] = (uint8_t)(w >> (8 * j));
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> tensor-core (async-proxy) reads
     __syncthreads();
 }
 
-// any u32 congruent to a0 + 2^8 a1 + 2^16 a2 + 2^24 a3 (a_j < 2^22)
+// a0 + 2^8 a1 + 2^16 a2 + 2^24 a3 (mod P) in [0, 2P), for a_j <= 64 * 255^2 (< 2^22):
+//   lo = a0 + 2^8 a1 and hi = a2 + 2^8 a3 are <= 257 * 64 * 255^2 < 2^30;
+//   2^16 hi = 2^31 (hi >> 15) + 2^16 (hi & 0x7fff) = (hi >> 15) + ((hi << 17) mod 2^32 >> 1)   (mod P)
+//   sum < 2^30 + 2^15 + 2^31 < 2P, so ONE conditional subtraction makes it canonical.
+// 6 instructions: IMAD, IMAD, IMAD (FMA pipe); LEA.HI, LOP3, VIADDMNMX (ALU pipe) -- two butterflies are 14 (8 on the ALU pipe).
 __device__ __forceinline__ uint32_t recombine(uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3)
 {
-    const uint32_t lo = a0 + (a1 << 8), hi = a2 + (a3 << 8);          // < 2^31 each
-    const uint64_t p = (uint64_t)hi * 0x20000u;                        // 2 * (hi * 2^16): the fold of mul2()
-    return lo + (uint32_t)(p >> 32) + ((uint32_t)p >> 1);              // < 2^32
+    const uint32_t lo = a0 + (a1 << 8), hi = a2 + (a3 << 8);
+    return m31::csub((hi & 0x7fffu) * 65536u + (lo + (hi >> 15)));
 }
-__device__ __forceinline__ uint32_t canonical(uint32_t x) { return m31::csub((x & m31::P) + (x >> 31)); }
 
 // What a 128-thread MMA group (four consecutive warps: one per TMEM lane quarter) needs for its stages.  All fields are
 // warp-uniform; the TMEM addresses are passed through __shfl_sync by the caller so that ptxas keeps them in uniform
@@ -165,22 +181,73 @@ __device__ __forceinline__ void stage16(uint32_t (&v)[16][4], const Group &gr, u
         __syncwarp();
         mbar_wait(gr.bar, e & 1);
         fence_after();
-        uint32_t acc[2][16];
-        ld16(gr.tmem_lane + 64, acc[0]);
+        uint32_t acc[16];
 #pragma unroll
         for (int h = 0; h < 4; h++) {
+            ld16(gr.tmem_lane + 64 + 16 * h, acc);
             wait_ld();
-            if (h < 3) ld16(gr.tmem_lane + 64 + 16 * (h + 1), acc[(h + 1) & 1]);
-            else if (e < 3) {                          // D has been read: the next MMA pair may overwrite it
+            if (h == 3 && e < 3) {                     // D has been read: the next MMA pair may overwrite it
                 fence_before();
                 if (gr.issuer_warp) asm volatile("bar.sync %0, 128;" ::"r"(gr.bar_d) : "memory");
                 else asm volatile("bar.arrive %0, 128;" ::"r"(gr.bar_d) : "memory");
             }
 #pragma unroll
-            for (int r = 0; r < 4; r++) {
-                const uint32_t *a = acc[h & 1] + 4 * r;
-                v[4 * h + r][e] = canonical(recombine(a[0], a[1], a[2], a[3]));
+            for (int r = 0; r < 4; r++) v[4 * h + r][e] = recombine(acc[4 * r], acc[4 * r + 1], acc[4 * r + 2], acc[4 * r + 3]);
+        }
+    }
+}
+
+// The same stage applied IN PLACE to vectors that live in shared memory, one vector per thread and batch: element c of the
+// vector of (batch b, this thread) is the word base[b * stride_b + c * stride_c], where consecutive lanes of a warp own
+// consecutive words (LDS.32 / STS.32 without bank conflicts, no register transposition, ~50 registers).  Software
+// pipeline over the NB batches (NB even): A is double-buffered in TMEM (columns +0 / +16), so batch b + 1 is loaded and
+// stored to TMEM while the MMA pair of batch b runs; ONE 128-thread barrier per batch says "A(b+1) stored and D(b) read".
+// The caller orders the shared-memory accesses against the neighbouring stages (a group barrier before and after).
+template <int NB>
+__device__ __forceinline__ void stage16_smem(uint32_t *base, int stride_c, int stride_b, const Group &gr, uint64_t b_desc0, uint64_t b_desc1, int lane)
+{
+    static_assert(NB % 2 == 0, "the mbarrier phase must come back to 0");
+    constexpr uint32_t IDESC = make_idesc(64);
+    uint32_t v[16];
+#pragma unroll
+    for (int c = 0; c < 16; c++) v[c] = base[c * stride_c];
+    st16(gr.tmem_lane, v);
+    wait_st();
+    fence_before();
+    asm volatile("bar.sync %0, 128;" ::"r"(gr.bar_a) : "memory");
+    if (gr.issuer_warp && lane == 0) {
+        fence_after();
+        mma_i8_ts(gr.tmem + 64, gr.tmem, b_desc0, IDESC, 0);
+        mma_i8_ts(gr.tmem + 64, gr.tmem + 8, b_desc1, IDESC, 1);
+        mma_commit(gr.bar);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int b = 0; b < NB; b++) {
+        uint32_t *cur = base + b * stride_b;
+        if (b + 1 < NB) {
+#pragma unroll
+            for (int c = 0; c < 16; c++) v[c] = cur[stride_b + c * stride_c];
+            st16(gr.tmem_lane + 16 * ((b + 1) & 1), v);
+            wait_st();
+        }
+        mbar_wait(gr.bar, b & 1);
+        fence_after();
+        uint32_t acc[64];                              // all 64 accumulators of the vector in one TMEM round trip
+        ld64(gr.tmem_lane + 64, acc);
+        wait_ld();
+#pragma unroll
+        for (int r = 0; r < 16; r++) cur[r * stride_c] = recombine(acc[4 * r], acc[4 * r + 1], acc[4 * r + 2], acc[4 * r + 3]);
+        if (b + 1 < NB) {
+            fence_before();
+            asm volatile("bar.sync %0, 128;" ::"r"(gr.bar_a) : "memory");
+            if (gr.issuer_warp && lane == 0) {
+                fence_after();
+                mma_i8_ts(gr.tmem + 64, gr.tmem + 16 * ((b + 1) & 1), b_desc0, IDESC, 0);
+                mma_i8_ts(gr.tmem + 64, gr.tmem + 16 * ((b + 1) & 1) + 8, b_desc1, IDESC, 1);
+                mma_commit(gr.bar);
             }
+            __syncwarp();
         }
     }
 }
