@@ -25,9 +25,10 @@ sys.path.insert(0, ROOT)
 
 _REAL_STDOUT = sys.stdout
 N_COLS, LOG_SIZE, LOG_BLOWUP = 256, 22, 1
-# DRAM bytes (read + written) per launch of the kernels below at the headline size, from ncu (profiles/r01_launches_tma.txt)
-NCU_TRAFFIC = {"merkle_leaf_layer": 8.59e9 + 0.27e9, "evaluate (2 fft launches)": (4.51e9 + 8.53e9 + 8.61e9 + 8.53e9) / 2,
-               "interpolate (2 fft launches)": (4.31e9 + 4.25e9 + 4.31e9 + 4.23e9) / 2}
+# ncu evidence the roofline entries cite: per-kernel means of the launch list of THIS command at the headline size
+# (scripts/launch_list.py --json) and the --set full counters of the FFT passes (scripts/ncu_summary.py --json)
+NCU_LAUNCHES = "profiles/r02_launches.json"
+NCU_COUNTERS = "profiles/r02_fft_ncu.json"
 # (column groups, SMs of the NVLink-bound pass) per world size for --overlap auto, from the sweeps in profiles/r01_overlap.txt
 OVERLAP_AUTO = {2: (4, 62), 4: (4, 62), 8: (4, 62)}
 METRIC = "lde_blake2s_commit_throughput"
@@ -50,7 +51,9 @@ def parse():
     ap.add_argument("--overlap", default="auto", help="N > 1, --exchange peer: 'groups,peer_sms' = column groups and SMs given to the "
                     "NVLink-bound pass running beside the next group's transforms; 'off' = one group; 'auto' = per world size")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--cpu-sample-cols", type=int, default=64)
+    ap.add_argument("--cpu-sample-cols", type=int, default=0, help="columns of the CPU legs (0 = all of --cols: the whole config)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the config 4 (FRI) and config 5 (prove) timings")
+    ap.add_argument("--single-process", action="store_true", help="N GPUs driven by ONE process through tstwo_lde_commit_multi")
     ap.add_argument("--fft-radix", type=int, default=0, help="tuning: rows per thread of the FFT passes (8 or 16)")
     return ap.parse_args()
 
@@ -153,14 +156,23 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
+def _cpu_leg_setup(args):
+    """The CPU legs (reference arm, cpu_baseline): the oracle rebuilt -O3 -march=native ON THIS HOST, all its cores, the WHOLE
+    config (every column) unless --cpu-sample-cols asks for a sample."""
+    import oracle as orc
+    native = orc.use_native_build()
+    orc.use_all_cores()
+    cols = args.cpu_sample_cols if args.cpu_sample_cols > 0 else args.cols
+    return orc, min(cols, args.cols), native
+
+
 def run_reference(args):
     import numpy as np
-    import oracle as orc
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    orc.use_all_cores()
-    log, blow, cols = args.log_size, LOG_BLOWUP, args.cpu_sample_cols
+    orc, cols, native = _cpu_leg_setup(args)
+    log, blow = args.log_size, LOG_BLOWUP
     root_init, root_log = orc.canonic_half_coset(log + blow)
     tw, itw = orc.precompute_twiddles(root_init, root_log)
     rng = np.random.default_rng(0x5EED0003)
@@ -172,12 +184,15 @@ def run_reference(args):
         orc.lde_commit(trace, blow, tw, itw)
     dt = (time.perf_counter() - t0) / args.steps
     val = cols * (1 << log) / dt
-    sample = f"{cols} of {args.cols} columns at log_size {log}, blowup 2 (interpolate + evaluate + Merkle commit of those columns)"
+    whole = cols == args.cols
+    sample = (f"all {cols} columns" if whole else f"{cols} of {args.cols} columns") + \
+        f" at log_size {log}, blowup 2 (interpolate + evaluate + Merkle commit), oracle built {'-O3 -march=native on this host' if native else '-O3 -march=x86-64-v2'}"
     print(json.dumps({
         "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32 (M31)",
         "data": "synthetic", "impl": "reference",
-        "config": {"workload": f"{args.cols} cols x 2^{log}, blowup 2, Blake2s Merkle commit", "sample": sample},
+        "config": {"workload": f"{args.cols} cols x 2^{log} M31, blowup 2 (2^{log + blow} rows), Blake2s Merkle commit",
+                   "n_cols": args.cols, "log_size": log, "log_blowup": blow, "same_config": whole, "sample": sample},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": orc.num_threads(), "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference = C restatement of TStwo CpuBackend (oracle/); the TypeScript reference needs bun/node, absent here",
@@ -207,20 +222,21 @@ def make_trace(torch, dev, rank, world, n_cols, n):
 
 def cpu_baseline(args):
     import numpy as np
-    import oracle as orc
-    orc.use_all_cores()
-    log, blow, cols = args.log_size, LOG_BLOWUP, args.cpu_sample_cols
+    orc, cols, native = _cpu_leg_setup(args)
+    log, blow = args.log_size, LOG_BLOWUP
     root_init, root_log = orc.canonic_half_coset(log + blow)
     tw, itw = orc.precompute_twiddles(root_init, root_log)
     trace = np.random.default_rng(1).integers(0, P, (cols, 1 << log), dtype=np.uint32)
     t0 = time.perf_counter()
     reps = 0
-    while reps < 1 or (time.perf_counter() - t0 < 10 and reps < 4):
+    while reps < 1 or (time.perf_counter() - t0 < 10 and reps < 3):
         orc.lde_commit(trace, blow, tw, itw)
         reps += 1
     dt = (time.perf_counter() - t0) / reps
     return {"value": cols * (1 << log) / dt, "unit": UNIT, "cores": orc.num_threads(), "kind": "port",
-            "sample": f"{cols} of {args.cols} columns at log_size {log}, blowup 2, {reps} rep(s), {dt:.2f} s each"}
+            "sample": (f"all {cols} columns" if cols == args.cols else f"{cols} of {args.cols} columns") +
+                      f" at log_size {log}, blowup 2, {reps} rep(s), {dt:.2f} s each, oracle built "
+                      f"{'-O3 -march=native on this host' if native else '-O3 -march=x86-64-v2'}"}
 
 
 def run_cuda(args):
@@ -341,8 +357,34 @@ def run_cuda(args):
     value = n_cols * n / (ms * 1e-3)
     root_hex = bytes(root).hex() if world == 1 else (holder.get("root", b"").hex() if rank == 0 else "")
 
-    # ---- per-kernel timing (1 GPU): the roofline of the dominant kernel, measured live with CUDA events
-    roof, kernels, int_roof = None, None, None
+    # ---- per-rank phase breakdown (N > 1, fused peer stores): CUDA events at the phase boundaries, min / max over ranks, and
+    # the NVLink rate of the pass that stores the evaluations into the peers' leaf buffers
+    phases = None
+    if world > 1 and args.exchange == "peer":
+        recs = []
+        for _ in range(2):
+            sc.step_phases(trace_flat)
+        barrier()
+        for _ in range(6):
+            recs.append(sc.step_phases(trace_flat))
+        torch.cuda.synchronize()
+        names = ["lde_and_peer_stores", "fence_all_reduce", "leaf_layer_and_subtree", "root_gather_and_top_layers"]
+        tot = [sum(r[i].elapsed_time(r[i + 1]) for r in recs) / len(recs) for i in range(4)]
+        t = torch.tensor(tot, device=dev, dtype=torch.float64)
+        mx, mn = t.clone(), t.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX); dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+        sent = lc * ne * 4 * (world - 1) / world           # bytes this rank stores into peer memory per step
+        phases = {nm: {"ms_min_over_ranks": float(mn[i]), "ms_max_over_ranks": float(mx[i])} for i, nm in enumerate(names)}
+        phases["nvlink"] = {"bytes_stored_to_peers_per_rank": sent, "gbs_per_rank_over_the_lde_phase": sent / (float(mx[0]) * 1e-3) / 1e9,
+                            "reference": "770 GB/s per direction measured peer copy (B200_PROFILING.md), 900 nominal"}
+        phases["note"] = ("CUDA events on each rank's stream; a rank's fence / gather time includes waiting for the slowest peer. "
+                          "single-GPU pure LDE of the same shard = kernels.passes of the N=1 line / N")
+        barrier()
+
+    # ---- per-kernel timing (1 GPU), live CUDA events: `roofline` = the phase with the largest share of the step (the four
+    # circle-FFT passes), `rooflines` = every kernel of the step, each with its algorithmic bytes, its live
+    # duration, the fraction of the measured HBM peak and the DRAM traffic ncu saw for the same command (committed JSON)
+    roof, rooflines, kernels, int_roof = None, None, None, None
     if world == 1:
         kernels = kernel_breakdown(L, chk, torch, stream, trace, coeffs, evals, layers, tw, n_cols, log, blow)
         peaks = {}
@@ -350,35 +392,70 @@ def run_cuda(args):
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
-        peak, which = (peaks.get("hbm_gbs"), "measured (MEASURED_PEAKS.json hbm_gbs)") if peaks.get("hbm_gbs") else (6650.0, "fallback")
-        # dominant kernel = the longest single launch (a transform is 2 launches, the leaf layer is 1)
-        top_k = max(kernels, key=lambda k: kernels[k]["ms"] / kernels[k]["launches"])
-        kk = kernels[top_k]
-        ms_launch, by_launch = kk["ms"] / kk["launches"], kk["bytes"] / kk["launches"]
-        roof = {"bound": "hbm", "kernel": top_k, "achieved": by_launch / ms_launch / 1e6, "peak": peak, "unit": "GB/s",
-                "frac": by_launch / ms_launch / 1e6 / peak, "traffic": NCU_TRAFFIC.get(top_k) if (n_cols, log, blow) == (N_COLS, LOG_SIZE, LOG_BLOWUP) else None, "peak_source": which,
-                "algorithmic_bytes_per_launch": by_launch, "ms_per_launch": ms_launch,
-                "note": "this kernel is integer-pipe bound, not HBM bound (see int_roofline); traffic = dram bytes read+written "
-                        "per launch from profiles/r01_launches_v.txt"}
+        peak, which = (peaks.get("hbm_gbs"), "measured (MEASURED_PEAKS.json hbm_gbs)") if peaks.get("hbm_gbs") else (6650.0, "fallback (B200_PROFILING.md)")
+        headline = (n_cols, log, blow) == (N_COLS, LOG_SIZE, LOG_BLOWUP)
+        ncu_l, ncu_c = {}, {}
+        if headline:
+            try:
+                ncu_l = json.load(open(os.path.join(ROOT, NCU_LAUNCHES)))["kernels"]
+            except Exception:
+                ncu_l = {}
+            try:
+                ncu_c = json.load(open(os.path.join(ROOT, NCU_COUNTERS)))["kernels"]
+            except Exception:
+                ncu_c = {}
+
+        def entry(name, ncu_names, ms, by, launches, note=None):
+            tr = [ncu_l.get(k) for k in ncu_names]
+            traffic = sum(t["dram_read_bytes"] + t["dram_write_bytes"] for t in tr) if tr and all(tr) else None
+            e = {"kernel": name, "bound": "hbm", "launches_per_step": launches, "algorithmic_bytes": by, "ms": ms,
+                 "achieved": by / ms / 1e6, "peak": peak, "unit": "GB/s", "frac": by / ms / 1e6 / peak,
+                 "traffic": traffic, "traffic_source": NCU_LAUNCHES if traffic is not None else None, "share_of_step": ms / ms_step}
+            cs = [ncu_c.get(k) for k in ncu_names]
+            if cs and all(cs):
+                e["ncu"] = {"alu_pipe_active_pct": [c.get("alu_pipe_active_pct") for c in cs], "issue_active_pct": [c.get("issue_active_pct") for c in cs],
+                            "tensor_pipe_active_pct": [c.get("tensor_pipe_active_pct") for c in cs], "source": NCU_COUNTERS}
+            if note:
+                e["note"] = note
+            return e
+
+        ms_step = ms
+        el = n_cols * n
+        pk = kernels["passes"]
+        rooflines = []
+        pass_bytes = {"inverse contiguous": 8 * el, "inverse strided": 8 * el, "forward strided": (4 + 4 * (1 << blow)) * el,
+                      "forward contiguous": 8 * (1 << blow) * el}
+        for nm, v in pk.items():
+            rooflines.append(entry(f"fft pass: {nm} ({v['kernel']})", [v["kernel"]], v["ms"], pass_bytes.get(nm, 0), 1,
+                                   "bytes = this pass's own input read once + output written once"))
+        t_int, t_ev = kernels["interpolate (2 fft launches)"]["ms"], kernels["evaluate (2 fft launches)"]["ms"]
+        names_int = [v["kernel"] for nm, v in pk.items() if nm.startswith("inverse")]
+        names_ev = [v["kernel"] for nm, v in pk.items() if nm.startswith("forward")]
+        rooflines.append(entry("interpolate (2 fft passes)", names_int, t_int, 8 * el, 2, "SURVEY 8(d): 8 B per trace element"))
+        rooflines.append(entry("evaluate, blow-up 2 (2 fft passes)", names_ev, t_ev, (4 + 4 * (1 << blow)) * el, 2, "SURVEY 8(d): 12 B per trace element"))
+        t_leaf, t_nodes = kernels["merkle_leaf_layer"]["ms"], kernels["merkle_node_layers"]["ms"]
+        rooflines.append(entry("merkle leaf layer (merkle_leaf_tma_kernel)", ["merkle_leaf_tma_kernel"], t_leaf, (4 * n_cols + 32) * ne, 1,
+                               "integer-pipe bound (int_roofline.blake2s), not HBM bound"))
+        rooflines.append(entry(f"merkle node layers ({ext} launches of merkle_layer_kernel<1>)", [], t_nodes, 96 * (ne - 1), ext))
+        roof = entry("circle FFT: interpolate + evaluate (4 launches of fft_tma_kernel)", names_int + names_ev, t_int + t_ev,
+                     (8 + 4 + 4 * (1 << blow)) * el, 4,
+                     "largest share of the step; HBM is the bound SURVEY 8(d) assigns, the passes are integer-pipe / issue limited "
+                     "(ncu counters per pass in rooflines[].ncu; int_roofline.fft)")
         # integer-pipe rooflines measured on this pool with tools/microbench*.cu (profiles/r01_microbench_*.txt):
-        # 3.667e12 M31 butterflies/s (ALU-pipe bound, 10.15 clk per warp-butterfly per SM sub-partition) and
-        # 27.7e9 Blake2s compressions/s (1345 clk per warp-compression per sub-partition, message in registers) at 1965 MHz
+        # 3.667e12 M31 butterflies/s for the 7-instruction butterfly (10.15 clk per warp-butterfly per SM sub-partition), the
+        # hardware bound of its 4 ALU-pipe instructions is 8 clk -> 4.65e12/s; 27.7e9 Blake2s compressions/s (1345 clk per
+        # warp-compression per sub-partition, message in registers) at 1965 MHz
         n_bf = n_cols * (log * (n // 2) + log * (ne // 2))          # the top log_blowup layers of evaluate are copies
         n_cmp = ne * ((4 * n_cols + 63) // 64) + ne - 1
-        t_fft = kernels["interpolate (2 fft launches)"]["ms"] + kernels["evaluate (2 fft launches)"]["ms"]
-        t_mk = kernels["merkle_leaf_layer"]["ms"] + 2 * kernels["merkle_node_layer_top"]["ms"]   # node layers halve: sum ~ 2x the top one
+        t_fft, t_mk = t_int + t_ev, t_leaf + t_nodes
         int_roof = {"fft": {"butterflies": n_bf, "ms": t_fft, "achieved": n_bf / t_fft / 1e6, "peak": 3667.0, "unit": "G butterflies/s",
-                            "frac": n_bf / t_fft / 1e6 / 3667.0},
+                            "frac": n_bf / t_fft / 1e6 / 3667.0, "alu_pipe_bound": 4650.0, "frac_of_alu_pipe_bound": n_bf / t_fft / 1e6 / 4650.0,
+                            "note": "peak = this library's 7-instruction butterfly in a register-resident microbenchmark; alu_pipe_bound = "
+                                    "2 clk x 4 ALU-pipe instructions per warp-butterfly.  8 of the 44 layers run on the tensor cores "
+                                    "(tcgen05 kind::i8) and are counted as butterflies all the same."},
                     "blake2s": {"compressions": n_cmp, "ms": t_mk, "achieved": n_cmp / t_mk / 1e6, "peak": 27.7, "unit": "G compressions/s",
                                 "frac": n_cmp / t_mk / 1e6 / 27.7},
                     "peak_source": "tools/microbench.cu, tools/microbench_bf.cu on B200 (profiles/r01_microbench_int_pipes.txt, r01_microbench_stage.txt, r01_microbench_blake2s_forms.txt)"}
-        # the dominant kernel's own integer-pipe roofline beside its HBM one (what actually bounds it)
-        if top_k == "merkle_leaf_layer":
-            n_leaf = ne * ((4 * n_cols + 63) // 64)
-            roof["int_pipe"] = {"achieved": n_leaf / ms_launch / 1e6, "peak": 27.7, "unit": "G compressions/s", "frac": n_leaf / ms_launch / 1e6 / 27.7}
-        else:
-            n_k = n_cols * log * ((ne if top_k.startswith("evaluate") else n) // 2) / kk["launches"]
-            roof["int_pipe"] = {"achieved": n_k / ms_launch / 1e6, "peak": 3667.0, "unit": "G butterflies/s", "frac": n_k / ms_launch / 1e6 / 3667.0}
 
     # ---- end to end through the C ABI with HOST buffers (1 GPU)
     e2e = None
@@ -435,6 +512,22 @@ def run_cuda(args):
                "api": f"PeerShardedCommit.step_from_host (pinned host shard per rank -> root on rank 0), {world} PCIe links",
                "cpu_affinity": "NUMA node of each rank's GPU (nvmlDeviceSetCpuAffinity)" if numa_bound else "unbound"}
 
+    extras = None
+    if world == 1 and not args.no_extras:
+        del coeffs, evals, layers, trace
+        torch.cuda.empty_cache()
+        L.tstwo_mem_trim()
+        extras = {}
+        for key, fn in (("config4_fri", lambda: config4_fri(L, torch)), ("config5_prove", lambda: config5_prove(L, torch))):
+            try:
+                extras[key] = fn()
+            except Exception as e:   # an extra must never cost the headline line
+                extras[key] = {"error": f"{type(e).__name__}: {e}"[:300]}
+            L.tstwo_mem_trim()
+    try:
+        sass_patch = open(_lib.SO_PATH + ".sasspatch").read().strip()
+    except OSError:
+        sass_patch = "unknown"
     if rank == 0:
         cpu = None if args.no_cpu or world > 1 else cpu_baseline(args)
         out = {
@@ -446,9 +539,13 @@ def run_cuda(args):
                        "l2": "inputs (%.1f GiB) and outputs exceed the 126 MB L2; no flush needed" % (n_cols * n * 4 / 2**30),
                        "parallelism": "1 GPU" if world == 1 else (f"column-sharded LDE, last FFT pass stores rows to their owner over NVLink peer memory -> row-sharded Merkle x{world}"
                                                                        if args.exchange == "peer" else f"column-sharded LDE -> NCCL all-to-all -> row-sharded Merkle x{world}")},
-            "gpu_launches": launches, "clocks": clocks, "root": root_hex,
+            "gpu_launches": launches, "clocks": clocks, "root": root_hex, "root_matches_oracle_checked_root": root_hex == BENCH_ROOT if (n_cols, log, blow) == (N_COLS, LOG_SIZE, LOG_BLOWUP) else None,
+            "sass_patch": sass_patch,
         }
+        if extras: out["extras"] = extras
+        if phases: out["phases"] = phases
         if roof: out["roofline"] = roof
+        if rooflines: out["rooflines"] = rooflines
         if int_roof: out["int_roofline"] = int_roof
         if kernels: out["kernels"] = kernels
         if e2e: out["e2e"] = e2e
@@ -460,8 +557,87 @@ def run_cuda(args):
         dist.destroy_process_group()
 
 
+def config4_fri(L, torch):
+    """BASELINE config 4 as extra keys: the 23 folds of one QM31 column from 2^24 down to 2 elements (kernel time, CUDA events)
+    and FriProver.commit (folds + one Merkle tree per layer + transcript; wall clock with a device sync on both sides)."""
+    import numpy as np
+    import tstwo_b200 as tb
+    from tstwo_b200.channel import Blake2sChannel
+    from tstwo_b200.fri import FriProver
+    log = 24
+    rng = np.random.default_rng(0x5EED0004)
+    dom = tb.CanonicCoset.new(log).circleDomain()
+    tw = tb.CudaBackend.precomputeTwiddles(dom.halfCoset)
+    src = tb.SecureEvaluation(dom, tb.SecureColumnByCoords.from_cpu([rng.integers(0, P, 1 << log, dtype=np.uint32) for _ in range(4)]))
+    alpha = [int(x) for x in rng.integers(1, P, 4)]
+
+    def chain():
+        layer = tb.LineEvaluation.newZero(tb.LineDomain.new(dom.halfCoset))
+        tb.fold_circle_into_line(layer, src, alpha, tw)
+        while layer.len() > 2:
+            layer = tb.fold_line(layer, alpha, tw)
+    chain(); L.tstwo_sync()
+    best = 1e9
+    for _ in range(5):
+        L.tstwo_sync(); t0 = time.perf_counter(); chain(); L.tstwo_sync()
+        best = min(best, time.perf_counter() - t0)
+    n = 1 << log
+    by = 16 * n + 32 * (n // 2) + sum(16 * m + 16 * (m // 2) + 4 * (m // 2) for m in (1 << k for k in range(log - 1, 1, -1)))
+    coords = [tb.CudaCirclePoly.new(rng.integers(0, P, 1 << (log - 1), dtype=np.uint32)).evaluateWithTwiddles(dom, tw).values for _ in range(4)]
+    col = tb.SecureEvaluation(dom, tb.SecureColumnByCoords(coords))
+    cfg = tb.FriConfig(0, 1, 30)
+    FriProver.commit(Blake2sChannel.create(), cfg, [col], tw); L.tstwo_sync()
+    t0 = time.perf_counter(); pr = FriProver.commit(Blake2sChannel.create(), cfg, [col], tw); L.tstwo_sync()
+    t_commit = time.perf_counter() - t0
+    return {"workload": "one QM31 column on CanonicCoset(24): fold_circle_into_line + 22 fold_line (to 2 elements)",
+            "fold_chain_ms": best * 1e3, "fold_chain_algorithmic_bytes": by, "fold_chain_gbs": by / best / 1e9,
+            "qm31_elements_per_s": n / best, "fri_commit_ms": t_commit * 1e3, "fri_inner_layers": len(pr.inner_layers),
+            "timing": "wall clock, device sync on both sides (23 launches; includes launch latency)"}
+
+
+def config5_prove(L, torch):
+    """BASELINE config 5 as extra keys: wide-Fibonacci prove() at log_size 23 with 100 columns (Stwo's FIB_SEQUENCE_LENGTH),
+    blow-up 2, 70 queries, 10 proof-of-work bits; second pass (allocator warm).  The trace is built on the device."""
+    import tstwo_b200 as tb
+    from tstwo_b200 import air, prover
+    from tstwo_b200.channel import Blake2sChannel
+    log, n_cols, blow = 23, 100, 1
+    clock = lambda: (L.tstwo_sync(), time.perf_counter())[1]
+    # generateTestTrace (examples/fibonacci.ts:245-258) on the device: row r starts (1, r), then c = a^2 + b^2
+    n = 1 << log
+    trace = torch.empty((n_cols, n), dtype=torch.int32, device="cuda")
+    a = torch.ones(n, dtype=torch.int64, device="cuda")
+    b = torch.arange(n, dtype=torch.int64, device="cuda")
+    trace[0], trace[1] = a.to(torch.int32), b.to(torch.int32)
+    for k in range(2, n_cols):
+        a, b = b, (a * a % P + b * b % P) % P
+        trace[k] = b.to(torch.int32)
+    del a, b
+    torch.cuda.synchronize()
+    tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(log + 1 + blow).half_coset())
+    dom = tb.CanonicCoset.new(log).circleDomain()
+    cols = [tb.CudaCircleEvaluation(dom, tb.CudaColumn.view(trace.data_ptr() + 4 * (c << log), n, trace)) for c in range(n_cols)]
+    res = None
+    for rep in range(2):
+        channel = Blake2sChannel.create()
+        scheme = tb.CommitmentSchemeProver(tb.PcsConfig(10, tb.FriConfig(0, blow, 70)), tw)
+        t3 = clock()
+        b = scheme.tree_builder(); b.extend_evals([]); b.commit(channel)
+        b = scheme.tree_builder(); b.extend_evals(cols); b.commit(channel)
+        t4 = clock()
+        comp = air.WideFibonacciComponent(air.WideFibonacciEval.create(log, n_cols))
+        proof = prover.prove([comp], channel, scheme)
+        t5 = clock()
+        res = {"workload": f"wide-Fibonacci prove(), {n_cols} columns x 2^{log}, blow-up 2, 70 queries, 10 pow bits",
+               "trace_commit_ms": (t4 - t3) * 1e3, "prove_ms": (t5 - t4) * 1e3, "total_ms": (t5 - t3) * 1e3,
+               "trace_elements_per_s": n_cols * (1 << log) / (t5 - t3), "timing": "wall clock, device sync on both sides, second pass"}
+        del scheme, proof
+    return res
+
+
 def kernel_breakdown(L, chk, torch, stream, trace, coeffs, evals, layers, tw, n_cols, log, blow):
-    """Times the three phases of the step separately (CUDA events on the launching stream)."""
+    """Times the phases of the step separately (CUDA events on the launching stream) and every FFT pass launch on its own
+    (tstwo_debug_pass_timing: events recorded by the library around each launch)."""
     from tstwo_b200 import _lib
     ext = log + blow
     n, ne = 1 << log, 1 << ext
@@ -481,15 +657,38 @@ def kernel_breakdown(L, chk, torch, stream, trace, coeffs, evals, layers, tw, n_
     hi_small, hi_big = 1 << (31 - (log - 1) - 2), 1 << (31 - (ext - 1) - 2)
     t_int = timed(lambda: chk(L.tstwo_interpolate_columns(tp, cp, n_cols, log, hi_small, tw.value, 0)))
     t_ev = timed(lambda: chk(L.tstwo_evaluate_columns(cp, log, ep, n_cols, ext, hi_big, tw.value, 0)))
+    # every pass launch on its own
+    passes = {}
+    reps = 5
+    L.tstwo_debug_pass_timing(1)
+    for _ in range(reps):
+        chk(L.tstwo_interpolate_columns(tp, cp, n_cols, log, hi_small, tw.value, 0))
+        chk(L.tstwo_evaluate_columns(cp, log, ep, n_cols, ext, hi_big, tw.value, 0))
+    tags, mss = (C.c_int * 64)(), (C.c_float * 64)()
+    cnt = L.tstwo_debug_pass_times(64, tags, mss)
+    L.tstwo_debug_pass_timing(0)
+    acc = {}
+    for i in range(max(cnt, 0)):
+        acc.setdefault(tags[i], []).append(mss[i])
+    for tag, v in acc.items():
+        nm = ("inverse " if tag & 1 else "forward ") + ("strided" if tag & 2 else "contiguous")
+        passes[nm] = {"ms": sum(v) / len(v), "launches": len(v) // reps,
+                      "kernel": f"fft_tma_kernel<{tag & 1}, {(tag >> 1) & 1}, 1, {(tag >> 2) & 1}>", "tensor_core_top_stage": bool(tag & 4)}
     leaf = layers.data_ptr() + 32 * ((1 << ext) - 1)
     t_leaf = timed(lambda: chk(L.tstwo_merkle_commit_layer(ext, 0, ep, n_cols, leaf)))
-    node = layers.data_ptr() + 32 * ((1 << (ext - 1)) - 1)
-    t_node = timed(lambda: chk(L.tstwo_merkle_commit_layer(ext - 1, leaf, None, 0, node)))
+
+    def nodes():
+        prev = leaf
+        for k in range(ext - 1, -1, -1):
+            cur = layers.data_ptr() + 32 * ((1 << k) - 1)
+            chk(L.tstwo_merkle_commit_layer(k, prev, None, 0, cur))
+            prev = cur
+    t_nodes = timed(nodes)
     b_int, b_ev = 8 * n_cols * n, (4 + 4 * (1 << blow)) * n_cols * n
-    b_leaf, b_node = (4 * n_cols + 32) * ne, 96 * (ne // 2)
+    b_leaf, b_node = (4 * n_cols + 32) * ne, 96 * (ne - 1)
     mk = lambda ms, by, launches: {"ms": ms, "bytes": by, "gbs": by / ms / 1e6, "launches": launches}
     return {"interpolate (2 fft launches)": mk(t_int, b_int, 2), "evaluate (2 fft launches)": mk(t_ev, b_ev, 2),
-            "merkle_leaf_layer": mk(t_leaf, b_leaf, 1), "merkle_node_layer_top": mk(t_node, b_node, 1)}
+            "merkle_leaf_layer": mk(t_leaf, b_leaf, 1), "merkle_node_layers": mk(t_nodes, b_node, ext), "passes": passes}
 
 
 if __name__ == "__main__":

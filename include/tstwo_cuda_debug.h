@@ -21,8 +21,15 @@ int tstwo_debug_force_naive_fft(int on);
 int tstwo_debug_set_fft_radix(int rows_per_thread);
 /* what the last transform ran: bit 0 tiled, bits 1.. family */
 int tstwo_debug_last_fft_mode(void);
-/* top stage of the bulk-copy passes: 1 = tensor cores (tcgen05 kind::i8, tc_stage.cuh; default), 0 = integer pipes */
-int tstwo_debug_set_fft_tc(int on);
+/* top stage of the bulk-copy passes on the tensor cores (tcgen05 kind::i8, tc_stage.cuh): bit 0 = forward strided passes
+ * (default), bit 1 = contiguous passes, bit 2 = inverse strided passes; 0 = integer pipes everywhere */
+int tstwo_debug_set_fft_tc(int mask);
+
+/* CUDA events around every bulk-copy FFT pass launch from now on (on = 1; 0 stops and forgets).  tstwo_debug_pass_times
+ * waits for the recorded passes and returns how many there were (<= max): tags[i] bit 0 = inverse, bit 1 = strided pass,
+ * bit 2 = tensor-core top stage; ms[i] = duration of that launch on the library stream. */
+int tstwo_debug_pass_timing(int on);
+int tstwo_debug_pass_times(int max, int *tags, float *ms);
 
 /* Merkle leaf layer: 1 = bulk-copy-fed kernel where it applies (default), 0 = merkle_layer_kernel always */
 int tstwo_debug_set_leaf_mode(int mode);

@@ -26,6 +26,40 @@ def build(force: bool = False) -> str:
     return _SO
 
 
+def _cpu_stamp() -> str:
+    import hashlib
+    try:
+        txt = open("/proc/cpuinfo").read()
+        keep = [l for l in txt.splitlines() if l.startswith(("model name", "flags"))][:2]
+    except OSError:
+        keep = []
+    return hashlib.sha1("\n".join(keep).encode()).hexdigest()[:16]
+
+
+def use_native_build() -> bool:
+    """bench.py's CPU legs: rebuild the SAME source with -O3 -march=native for the host it runs on (the shipped .so is
+    -march=x86-64-v2 so that one build runs everywhere; a -march=native build made on another CPU may not).  Must be called
+    before the first lib() use.  Returns False (and keeps the portable build) if the compiler is missing or fails."""
+    global _SO, _lib
+    if _lib is not None:
+        return _SO.endswith("_native.so")
+    so = os.path.join(_DIR, "_build", "libtstwo_oracle_native.so")
+    stamp = so + ".cpu"
+    src = os.path.join(_DIR, "tstwo_oracle.c")
+    try:
+        fresh = (os.path.exists(so) and os.path.exists(stamp) and open(stamp).read() == _cpu_stamp()
+                 and os.path.getmtime(so) >= os.path.getmtime(src))
+        if not fresh:
+            os.makedirs(os.path.dirname(so), exist_ok=True)
+            subprocess.check_call(["/usr/bin/gcc", "-O3", "-march=native", "-fPIC", "-fvisibility=hidden", "-fopenmp", "-shared",
+                                   "-o", so, src], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            open(stamp, "w").write(_cpu_stamp())
+        _SO = so
+        return True
+    except Exception:
+        return False
+
+
 _lib = None
 
 

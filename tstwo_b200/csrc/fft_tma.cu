@@ -30,6 +30,7 @@
 #include <cuda.h>
 
 #include <cstring>
+#include <vector>
 
 #include "fft_params.cuh"
 #include "m31.cuh"
@@ -545,7 +546,15 @@ template <bool INV, bool STRIDED, bool FULL, bool TC = false> cudaError_t set_at
 {
     return cudaFuncSetAttribute(fft_tma_kernel<INV, STRIDED, FULL, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<STRIDED>(TC));
 }
-bool g_use_tc = true;     // tstwo_debug_set_fft_tc
+// tstwo_debug_set_fft_tc: bit 0 = forward strided passes, bit 1 = contiguous passes, bit 2 = inverse strided passes.
+// Default = forward strided only, the one pass where it wins (scripts/tc_ab.py, profiles/r02_tc_ab.txt: 2.98 -> 2.52 ms;
+// the inverse strided pass is already at 80 % of the HBM peak and loses 0.09 ms to the MMA round trips, the contiguous
+// passes with two 256-thread groups cannot hide them: +0.0 / +0.07 ms)
+int g_use_tc = 1;
+// tstwo_debug_pass_timing: CUDA events around every pass launch, so that bench.py reports each launch's duration live
+struct PassStamp { int tag; cudaEvent_t e0, e1; };
+bool g_timing = false;
+std::vector<PassStamp> g_stamps;
 bool g_ready = false;
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -645,13 +654,19 @@ int tma_pass(bool inverse, const PassParams &p)
     unsigned grid = (unsigned)ctx().sm_count;
     if (ctx().grid_limit > 0 && grid > (unsigned)ctx().grid_limit) grid = (unsigned)ctx().grid_limit;
     if (grid > sp.n_tiles) grid = sp.n_tiles;
-    if (!strided && g_use_tc) {
+    const bool use_tc = strided ? ((g_use_tc & (inverse ? 4 : 1)) && p.j_min == 0 && (1u << sp.cosets_log) <= (unsigned)TC_MAX_W) : (g_use_tc & 2) != 0;
+    PassStamp st{ (inverse ? 1 : 0) | (strided ? 2 : 0) | (use_tc ? 4 : 0), nullptr, nullptr };
+    if (g_timing) {
+        TS_CUDA(cudaEventCreate(&st.e0)); TS_CUDA(cudaEventCreate(&st.e1));
+        TS_CUDA(cudaEventRecord(st.e0, ctx().stream));
+    }
+    if (!strided && use_tc) {
         if (inverse) TS_LAUNCH((fft_tma_kernel<true, false, true, true>), grid, THREADS, smem_bytes<false>(true), sp);
         else TS_LAUNCH((fft_tma_kernel<false, false, true, true>), grid, THREADS, smem_bytes<false>(true), sp);
     } else if (!strided) {
         if (inverse) TS_LAUNCH((fft_tma_kernel<true, false, true>), grid, THREADS, smem_bytes<false>(), sp);
         else TS_LAUNCH((fft_tma_kernel<false, false, true>), grid, THREADS, smem_bytes<false>(), sp);
-    } else if (p.j_min == 0 && g_use_tc && (1u << sp.cosets_log) <= (unsigned)TC_MAX_W) {
+    } else if (use_tc) {
         if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, true, true>), grid, THREADS, smem_bytes<true>(true), sp);
         else TS_LAUNCH((fft_tma_kernel<false, true, true, true>), grid, THREADS, smem_bytes<true>(true), sp);
     } else if (p.j_min == 0) {
@@ -661,12 +676,34 @@ int tma_pass(bool inverse, const PassParams &p)
         if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, false>), grid, THREADS, smem_bytes<true>(), sp);
         else TS_LAUNCH((fft_tma_kernel<false, true, false>), grid, THREADS, smem_bytes<true>(), sp);
     }
+    if (g_timing) {
+        TS_CUDA(cudaEventRecord(st.e1, ctx().stream));
+        g_stamps.push_back(st);
+    }
     return 0;
 }
 
 }  // namespace tstwo
 
-extern "C" int tstwo_debug_set_fft_tc(int on) { tstwo::g_use_tc = on != 0; return 0; }
+extern "C" int tstwo_debug_set_fft_tc(int mask) { tstwo::g_use_tc = mask; return 0; }
+extern "C" int tstwo_debug_pass_timing(int on)
+{
+    for (auto &s : tstwo::g_stamps) { cudaEventDestroy(s.e0); cudaEventDestroy(s.e1); }
+    tstwo::g_stamps.clear();
+    tstwo::g_timing = on != 0;
+    return 0;
+}
+extern "C" int tstwo_debug_pass_times(int max, int *tags, float *ms)
+{
+    int n = 0;
+    for (auto &s : tstwo::g_stamps) {
+        if (n >= max) break;
+        if (cudaEventSynchronize(s.e1) != cudaSuccess || cudaEventElapsedTime(&ms[n], s.e0, s.e1) != cudaSuccess)
+            return tstwo::fail(TSTWO_ERR_CUDA, "pass timing events failed");
+        tags[n++] = s.tag;
+    }
+    return n;
+}
 #ifdef TSTWO_FFT_TRACE
 extern "C" int tstwo_debug_fft_trace(tstwo_dptr buf) { return tstwo::tma_trace_set((long long *)buf); }
 extern "C" int tstwo_debug_fft_trace_cta(int cta) { return tstwo::tma_trace_cta(cta); }

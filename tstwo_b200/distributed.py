@@ -29,8 +29,32 @@ class CudaShardOps:
         self._lib_mod = _lib
         self.L = _lib.init(device_index)
         self.dev = torch.device("cuda", device_index)
+        self._stream = stream
         if stream is not None:
             _lib.check(self.L.tstwo_set_stream(C.c_void_p(stream.cuda_stream)))
+
+    # torch.distributed collectives run on torch's CURRENT stream, the library's kernels on the library stream: the same
+    # stream only if the caller passed `stream` and made it current.  Otherwise order them explicitly, so that a collective
+    # neither overtakes the kernels before it nor is overtaken by the ones after it (with stream=None the library uses its own
+    # non-blocking stream, which torch cannot see: drain it).
+    def _same_stream(self) -> bool:
+        return self._stream is not None and torch.cuda.current_stream(self.dev).cuda_stream == self._stream.cuda_stream
+
+    def before_collective(self) -> None:
+        if self._same_stream():
+            return
+        if self._stream is not None:
+            torch.cuda.current_stream(self.dev).wait_stream(self._stream)
+        else:
+            self._lib_mod.check(self.L.tstwo_sync())
+
+    def after_collective(self) -> None:
+        if self._same_stream():
+            return
+        if self._stream is not None:
+            self._stream.wait_stream(torch.cuda.current_stream(self.dev))
+        else:
+            torch.cuda.current_stream(self.dev).synchronize()
 
     def empty(self, n_words: int) -> torch.Tensor:
         return torch.empty(n_words, dtype=torch.int32, device=self.dev)
@@ -97,10 +121,12 @@ class ShardedCommit:
 
     def step(self, trace: torch.Tensor) -> bytes | None:
         ops = self.ops
+        before = getattr(ops, "before_collective", lambda: None)
+        after = getattr(ops, "after_collective", lambda: None)
         ops.lde_sharded(trace, self.lc, self.log_size, self.blow, self.tw, self.coeffs, self.send, self.world)
-        dist.all_to_all_single(self.recv, self.send)
+        before(); dist.all_to_all_single(self.recv, self.send); after()
         ops.merkle_commit(self.recv, self.n_cols, self.sub, self.layers)
-        dist.all_gather_into_tensor(self.roots, self.layers[:8].contiguous())
+        before(); dist.all_gather_into_tensor(self.roots, self.layers[:8].contiguous()); after()
         if self.rank == 0:
             self.top = top_layers(ops, self.roots, self.world)
             return ops.to_host_bytes(self.top[-1] if self.top else self.roots)[:32]
@@ -181,18 +207,64 @@ class PeerShardedCommit:
                                                          groups, peer_sms))
         return self._finish()
 
-    def _finish(self):
+    def step_phases(self, trace: torch.Tensor):
+        """step() with a CUDA event at every phase boundary (for bench.py's per-rank breakdown): returns the 5 events around
+        [LDE + peer stores | fence (all-reduce) | leaves + subtree | root gather + top layers]."""
         chk = self._lib_mod.check
+        st = self._stream if self._stream is not None else torch.cuda.current_stream()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+        groups, peer_sms = self.overlap if self.overlap else (1, 0)
+        ev[0].record(st)
+        chk(self.L.tstwo_lde_columns_to_peers_overlapped(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw,
+                                                         self.coeffs.data_ptr() if self.coeffs is not None else 0,
+                                                         self.work.data_ptr(), self._bases_arr, self.world, self.rank * self.lc, 0,
+                                                         groups, peer_sms))
+        ev[1].record(st)
+        self._finish(ev, st)
+        return ev
+
+    def _finish(self, ev=None, st=None):
+        chk = self._lib_mod.check
+        self._order_before_collective()
         dist.all_reduce(self.flag)                 # every rank's stores into my leaf buffer are complete after this
+        self._order_after_collective()
+        if ev: ev[2].record(st)
         rows = 1 << self.sub
         ptrs = self._lib_mod.dptr_array([self.recv_ptr + 4 * rows * c for c in range(self.n_cols)])
         logs = (C.c_int * self.n_cols)(*([self.sub] * self.n_cols))
         chk(self.L.tstwo_merkle_commit(ptrs, logs, self.n_cols, self.layers.data_ptr(), None))
+        if ev: ev[3].record(st)
+        self._order_before_collective()
         dist.all_gather_into_tensor(self.roots, self.layers[:8].contiguous())
+        self._order_after_collective()
+        out = None
         if self.rank == 0:
             self.top = top_layers(self.ops, self.roots, self.world)
-            return self.ops.to_host_bytes(self.top[-1] if self.top else self.roots)[:32]
-        return None
+            out = self.ops.to_host_bytes(self.top[-1] if self.top else self.roots)[:32]
+        if ev: ev[4].record(st)
+        return out
+
+    # torch.distributed collectives run on torch's CURRENT stream, the library's kernels on the library stream.  They are the
+    # same stream only when the caller passed `stream` and made it current (bench.py does).  Otherwise the two are ordered
+    # here with events, so that a collective never overtakes the stores before it nor the hashing after it.
+    def _lib_stream_is_current(self) -> bool:
+        return self._stream is not None and torch.cuda.current_stream(self.dev).cuda_stream == self._stream.cuda_stream
+
+    def _order_before_collective(self):
+        if self._lib_stream_is_current():
+            return
+        if self._stream is not None:
+            torch.cuda.current_stream(self.dev).wait_stream(self._stream)
+        else:
+            self._lib_mod.check(self.L.tstwo_sync())       # library-owned stream: nothing to wait on from torch, drain it
+
+    def _order_after_collective(self):
+        if self._lib_stream_is_current():
+            return
+        if self._stream is not None:
+            self._stream.wait_stream(torch.cuda.current_stream(self.dev))
+        else:
+            torch.cuda.current_stream(self.dev).synchronize()
 
     def step_pipelined(self, trace: torch.Tensor, chunks: int = 4):
         """The exchange on the copy engines instead of inside the last FFT pass: the local columns are transformed in `chunks`
