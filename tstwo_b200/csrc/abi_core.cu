@@ -222,7 +222,13 @@ const char *tstwo_last_error(void) { return g_err; }
 int tstwo_set_stream(void *s)
 {
     TS_REQUIRE_INIT();
-    ctx().stream = s ? (cudaStream_t)s : ctx().own_stream;
+    cudaStream_t next = s ? (cudaStream_t)s : ctx().own_stream;
+    if (next != ctx().stream) {
+        // the column allocator hands freed blocks out again without events: that is only safe while everything runs on ONE
+        // stream, so work queued on the old stream (which may still touch cached blocks) is drained before the switch
+        TS_CUDA(cudaStreamSynchronize(ctx().stream));
+        ctx().stream = next;
+    }
     return 0;
 }
 int tstwo_sync(void)
@@ -252,12 +258,13 @@ uint64_t tstwo_launch_count(void) { return ctx().launches; }
 }  // extern "C"
 namespace tstwo {
 namespace {
+std::mutex g_alloc_mu;                                             // guards the three below
 std::unordered_map<uint64_t, std::vector<void *>> g_free_blocks;   // rounded size -> free blocks
 std::unordered_map<void *, uint64_t> g_block_size;                 // every live or cached block -> rounded size
 uint64_t g_cached_bytes = 0;
 constexpr uint64_t CACHE_CAP_BYTES = 24ull << 30;
 
-void release_cached_blocks()
+void release_cached_blocks()   // caller holds g_alloc_mu
 {
     cudaDeviceSynchronize();
     for (auto &kv : g_free_blocks)
@@ -274,6 +281,7 @@ int tstwo_malloc(uint64_t bytes, tstwo_dptr *out)
     TS_REQUIRE_INIT();
     if (!out) return fail(TSTWO_ERR_BAD_ARG, "null out");
     const uint64_t size = ((bytes ? bytes : 4) + 255) & ~255ull;
+    std::lock_guard<std::mutex> lock(g_alloc_mu);
     auto it = g_free_blocks.find(size);
     if (it != g_free_blocks.end() && !it->second.empty()) {
         *out = (tstwo_dptr)it->second.back();
@@ -298,6 +306,7 @@ int tstwo_free(tstwo_dptr p)
 {
     TS_REQUIRE_INIT();
     if (!p) return 0;
+    std::lock_guard<std::mutex> lock(g_alloc_mu);
     auto it = g_block_size.find((void *)p);
     if (it != g_block_size.end() && g_cached_bytes + it->second <= CACHE_CAP_BYTES) {
         g_free_blocks[it->second].push_back((void *)p);
@@ -312,6 +321,7 @@ int tstwo_free(tstwo_dptr p)
 int tstwo_mem_trim(void)
 {
     TS_REQUIRE_INIT();
+    std::lock_guard<std::mutex> lock(g_alloc_mu);
     release_cached_blocks();
     return 0;
 }

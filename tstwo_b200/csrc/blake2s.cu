@@ -315,23 +315,29 @@ int tstwo_grind(const uint8_t digest[32], uint32_t pow_bits, uint64_t *nonce)
     uint32_t *d_digest = nullptr;
     unsigned long long *d_best = nullptr, best = ~0ull;
     TS_CUDA(cudaMallocAsync(&d_digest, 32, c.stream));
-    TS_CUDA(cudaMallocAsync(&d_best, 8, c.stream));
-    TS_CUDA(cudaMemcpyAsync(d_digest, digest, 32, cudaMemcpyHostToDevice, c.stream));
-    TS_CUDA(cudaMemcpyAsync(d_best, &best, 8, cudaMemcpyHostToDevice, c.stream));
-    const unsigned grid = 148 * 8;
-    uint64_t base = 0;
-    // first batch small (most proofs use few bits), then 2^25 nonces per launch (~1.3 ms)
-    for (int iters = 1;; iters = 64) {
-        TS_LAUNCH(grind_kernel, grid, 256, 0, d_digest, pow_bits, base, iters, d_best, 1u);
-        TS_CUDA(cudaMemcpyAsync(&best, d_best, 8, cudaMemcpyDeviceToHost, c.stream));
-        TS_CUDA(cudaStreamSynchronize(c.stream));
-        if (best != ~0ull) break;
-        const uint64_t step = (uint64_t)grid * 256 * iters;
-        if (base + step < base) { best = ~0ull; break; }
-        base += step;
-    }
-    TS_CUDA(cudaFreeAsync(d_digest, c.stream));
-    TS_CUDA(cudaFreeAsync(d_best, c.stream));
+    if (cudaMallocAsync(&d_best, 8, c.stream) != cudaSuccess) { cudaFreeAsync(d_digest, c.stream); return fail(TSTWO_ERR_CUDA, "grind: cudaMallocAsync failed"); }
+    // every exit below releases the two buffers
+    auto search = [&]() -> int {
+        TS_CUDA(cudaMemcpyAsync(d_digest, digest, 32, cudaMemcpyHostToDevice, c.stream));
+        TS_CUDA(cudaMemcpyAsync(d_best, &best, 8, cudaMemcpyHostToDevice, c.stream));
+        const unsigned grid = (unsigned)(c.sm_count > 0 ? c.sm_count : 148) * 8;
+        uint64_t base = 0;
+        // first batch small (most proofs use few bits), then 2^25 nonces per launch (~1.3 ms)
+        for (int iters = 1;; iters = 64) {
+            TS_LAUNCH(grind_kernel, grid, 256, 0, d_digest, pow_bits, base, iters, d_best, 1u);
+            TS_CUDA(cudaMemcpyAsync(&best, d_best, 8, cudaMemcpyDeviceToHost, c.stream));
+            TS_CUDA(cudaStreamSynchronize(c.stream));
+            if (best != ~0ull) break;
+            const uint64_t step = (uint64_t)grid * 256 * iters;
+            if (base + step < base) { best = ~0ull; break; }
+            base += step;
+        }
+        return 0;
+    };
+    const int rc = search();
+    cudaFreeAsync(d_digest, c.stream);
+    cudaFreeAsync(d_best, c.stream);
+    if (rc) return rc;
     if (best == ~0ull) return fail(TSTWO_ERR_BAD_ARG, "no nonce with %u trailing zero bits", pow_bits);
     *nonce = best;
     return 0;

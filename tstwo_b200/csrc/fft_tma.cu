@@ -29,6 +29,7 @@
 // upper row nibble: 32 vectors per matrix and tile, an MMA needs 128).
 #include <cuda.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -602,6 +603,7 @@ int tma_pass_init()
     TS_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
     if (!fn || qres != cudaDriverEntryPointSuccess) return fail(TSTWO_ERR_CUDA, "driver has no cuTensorMapEncodeTiled");
     g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    if (const char *e = getenv("TSTWO_FFT_TC")) g_use_tc = atoi(e);   // A/B without a rebuild (see tstwo_debug_set_fft_tc)
     g_ready = true;
     return 0;
 }
