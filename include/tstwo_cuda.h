@@ -48,6 +48,14 @@ enum tstwo_status {
 
 /* ---- lifecycle ------------------------------------------------------------------------------------------- */
 int tstwo_init(int device);                 /* select device, create the library stream; idempotent */
+/* One process, several devices.  The reference host is ONE single-threaded process (MerkleProver.commit is called inline from
+ * prover/index.ts:582-662; no worker / IPC layer), so the multi-GPU fan-out lives inside the library: slot k drives CUDA device
+ * ids[k], all pairs get NVLink peer access, and ONE host thread issues everything (per-device streams, events as the
+ * cross-device fences).  Slot 0 is current afterwards; tstwo_set_device(slot) makes another slot the target of every
+ * following call of this thread (columns, twiddles, transforms ... are per device). */
+int tstwo_init_devices(int n_devices, const int *ids);
+int tstwo_device_count(void);               /* slots initialised (1 after tstwo_init) */
+int tstwo_set_device(int slot);
 int tstwo_shutdown(void);
 const char *tstwo_last_error(void);
 int tstwo_set_stream(void *cuda_stream);    /* run on a caller-owned cudaStream_t (NULL = library stream) */
@@ -187,6 +195,19 @@ int tstwo_ipc_close(tstwo_dptr ptr);
 int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
                           tstwo_dptr trace_staging, tstwo_dptr coeffs, tstwo_dptr evals, tstwo_dptr layers,
                           uint8_t root[32], uint32_t flags);
+
+/* The metric path on ALL devices of tstwo_init_devices in one call from one host thread (BASELINE config 3; CommitmentTreeProver
+ * ::new over the whole trace, pcs/prover.ts:215-235): columns are sharded by column for the LDE, the last FFT pass stores every
+ * row range into its owner's leaf buffer over NVLink peer memory, every device hashes its rows and builds its subtree, device 0
+ * finishes the top log2 G layers.  The root equals tstwo_lde_commit's on one device, bit for bit.  The library owns all device
+ * buffers (allocated at the first call for a shape).  G = tstwo_device_count() must be a power of two dividing n_cols, and every
+ * device needs >= 2^14 rows.
+ *   tstwo_lde_commit_multi      host_trace = [n_cols][2^log_size] words in HOST memory (pinned for full PCIe speed): every device
+ *                               pulls its shard over its own PCIe link, chunk by chunk, overlapped with the transforms;
+ *   tstwo_lde_commit_multi_dev  trace_shards[d] = device address ON slot d of columns [d n_cols/G, (d+1) n_cols/G). */
+int tstwo_lde_commit_multi(const uint32_t *host_trace, int n_cols, int log_size, int log_blowup, uint8_t root[32], uint32_t flags);
+int tstwo_lde_commit_multi_dev(const tstwo_dptr *trace_shards, int n_cols, int log_size, int log_blowup, uint8_t root[32],
+                               uint32_t flags);
 
 #ifdef __cplusplus
 }

@@ -32,6 +32,11 @@ class TwiddleMismatch(TstwoError):
 # name -> (restype, argtypes); mirrors include/tstwo_cuda.h one to one
 SIGNATURES = {
     "tstwo_init": (C.c_int, [C.c_int]),
+    "tstwo_init_devices": (C.c_int, [C.c_int, intp]),
+    "tstwo_device_count": (C.c_int, []),
+    "tstwo_set_device": (C.c_int, [C.c_int]),
+    "tstwo_lde_commit_multi": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint8), C.c_uint32]),
+    "tstwo_lde_commit_multi_dev": (C.c_int, [dptrp, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint8), C.c_uint32]),
     "tstwo_shutdown": (C.c_int, []),
     "tstwo_last_error": (C.c_char_p, []),
     "tstwo_set_stream": (C.c_int, [C.c_void_p]),

@@ -8,13 +8,26 @@
 #include "common.cuh"
 #include "circle_dev.cuh"
 
-namespace tstwo { namespace { void release_cached_blocks(); } }   // column allocator, below
+namespace tstwo { namespace { void release_cached_blocks(); std::mutex g_alloc_mu; } }   // column allocator, below (the mutex guards its maps)
 
 namespace tstwo {
 
 static thread_local char g_err[512] = "";
-static Context g_ctx;
-Context &ctx() { return g_ctx; }
+static Context g_ctxs[MAX_SLOTS];
+static thread_local int g_cur = 0;
+static int g_slots = 0;
+Context &ctx() { return g_ctxs[g_cur]; }
+Context &ctx_at(int slot) { return g_ctxs[slot]; }
+int ctx_slots() { return g_slots; }
+int ctx_select(int slot)
+{
+    const int prev = g_cur;
+    if (slot != prev || true) {
+        g_cur = slot;
+        if (g_ctxs[slot].ready) cudaSetDevice(g_ctxs[slot].device);
+    }
+    return prev;
+}
 
 int fail(int code, const char *fmt, ...)
 {
@@ -142,7 +155,8 @@ TwiddleTree *get_tree(tstwo_twiddles h)
 {
     std::lock_guard<std::mutex> lk(g_tree_mu);
     auto it = g_trees.find(h);
-    return it == g_trees.end() ? nullptr : it->second;
+    // a tree is device memory: only the slot it was built on may use it
+    return it == g_trees.end() || it->second->slot != ctx().slot ? nullptr : it->second;
 }
 bool is_doubling_of(uint32_t init, int log, const TwiddleTree *t)
 {
@@ -158,11 +172,13 @@ using namespace tstwo;
 
 extern "C" {
 
-int tstwo_init(int device)
+}  // extern "C"
+namespace tstwo {
+namespace {
+// brings up one slot on `device`: streams, pointer table, pool threshold, the per-device constant tables
+int init_slot(int slot, int device)
 {
-    Context &c = ctx();
-    if (c.ready && c.device == device) return 0;
-    if (c.ready) tstwo_shutdown();
+    Context &c = g_ctxs[slot];
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n == 0)
@@ -174,6 +190,8 @@ int tstwo_init(int device)
     TS_CUDA(cudaGetDeviceProperties(&prop, device));
     if (prop.major < 10)
         return fail(TSTWO_ERR_CUDA, "device is sm_%d%d; this library is built for sm_100a only", prop.major, prop.minor);
+    c = Context();
+    c.slot = slot;
     c.device = device;
     c.sm_count = prop.multiProcessorCount;
     TS_CUDA(cudaStreamCreateWithFlags(&c.own_stream, cudaStreamNonBlocking));
@@ -193,27 +211,97 @@ int tstwo_init(int device)
     c.ready = true;
     return 0;
 }
+void shutdown_slot(int slot)
+{
+    Context &c = g_ctxs[slot];
+    if (!c.ready) return;
+    const int prev = ctx_select(slot);
+    cudaDeviceSynchronize();
+    {
+        std::lock_guard<std::mutex> lock(g_alloc_mu);
+        release_cached_blocks();
+    }
+    pipeline_release();
+    if (c.ew_scratch) cudaFree(c.ew_scratch);
+    cudaFree(c.d_ptr_table);
+    cudaStreamDestroy(c.own_stream);
+    cudaStreamDestroy(c.copy_stream);
+    c = Context();
+    g_cur = prev;
+}
+}  // namespace
+void multi_release();   // multi.cu: per-device buffers of tstwo_lde_commit_multi
+}  // namespace tstwo
+extern "C" {
+
+int tstwo_init(int device)
+{
+    Context &c = g_ctxs[0];
+    if (c.ready && c.device == device && g_slots == 1) { ctx_select(0); return 0; }
+    if (g_slots) tstwo_shutdown();
+    g_cur = 0;
+    int rc = init_slot(0, device);
+    if (rc) return rc;
+    g_slots = 1;
+    return 0;
+}
+
+// One process, several devices (SURVEY 8b "Conventions": the reference host is ONE single-threaded process, so the multi-GPU
+// fan-out lives inside the library).  Slot k drives device ids[k]; every pair gets peer access (NVLink).  Slot 0 is current.
+int tstwo_init_devices(int n, const int *ids)
+{
+    if (n < 1 || n > MAX_SLOTS || !ids) return fail(TSTWO_ERR_BAD_ARG, "tstwo_init_devices: 1..%d devices", MAX_SLOTS);
+    for (int i = 0; i < n; i++)
+        for (int j = 0; j < i; j++)
+            if (ids[i] == ids[j]) return fail(TSTWO_ERR_BAD_ARG, "device %d listed twice", ids[i]);
+    if (g_slots) tstwo_shutdown();
+    for (int i = 0; i < n; i++) {
+        g_cur = i;
+        int rc = init_slot(i, ids[i]);
+        if (rc) { g_slots = i; tstwo_shutdown(); return rc; }
+    }
+    g_slots = n;
+    for (int i = 0; i < n; i++) {
+        TS_CUDA(cudaSetDevice(ids[i]));
+        for (int j = 0; j < n; j++) {
+            if (i == j) continue;
+            int can = 0;
+            TS_CUDA(cudaDeviceCanAccessPeer(&can, ids[i], ids[j]));
+            if (!can) { tstwo_shutdown(); return fail(TSTWO_ERR_CUDA, "device %d cannot access device %d as a peer", ids[i], ids[j]); }
+            cudaError_t e = cudaDeviceEnablePeerAccess(ids[j], 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else TS_CUDA(e);
+        }
+    }
+    ctx_select(0);
+    return 0;
+}
+int tstwo_device_count(void) { return g_slots; }
+// the slot (not the CUDA ordinal) every following call of this thread works on
+int tstwo_set_device(int slot)
+{
+    if (slot < 0 || slot >= g_slots || !g_ctxs[slot].ready) return fail(TSTWO_ERR_BAD_ARG, "device slot %d not initialised (%d slots)", slot, g_slots);
+    ctx_select(slot);
+    return 0;
+}
 
 int tstwo_shutdown(void)
 {
-    Context &c = ctx();
-    if (!c.ready) return 0;
-    cudaDeviceSynchronize();
-    release_cached_blocks();
+    if (!g_slots && !g_ctxs[0].ready) return 0;
+    multi_release();
     {
         std::lock_guard<std::mutex> lk(g_tree_mu);
         for (auto &kv : g_trees) {
+            if (g_ctxs[kv.second->slot].ready) cudaSetDevice(g_ctxs[kv.second->slot].device);
             cudaFree(kv.second->tw);
             delete kv.second;
         }
         g_trees.clear();
     }
-    pipeline_release();
     scatter_release();
-    cudaFree(c.d_ptr_table);
-    cudaStreamDestroy(c.own_stream);
-    cudaStreamDestroy(c.copy_stream);
-    c = Context();
+    for (int i = MAX_SLOTS - 1; i >= 0; i--) shutdown_slot(i);
+    g_slots = 0;
+    g_cur = 0;
     return 0;
 }
 
@@ -258,10 +346,15 @@ uint64_t tstwo_launch_count(void) { return ctx().launches; }
 }  // extern "C"
 namespace tstwo {
 namespace {
-std::mutex g_alloc_mu;                                             // guards the three below
-std::unordered_map<uint64_t, std::vector<void *>> g_free_blocks;   // rounded size -> free blocks
-std::unordered_map<void *, uint64_t> g_block_size;                 // every live or cached block -> rounded size
-uint64_t g_cached_bytes = 0;
+struct BlockCache {                                                // one per device slot
+    std::unordered_map<uint64_t, std::vector<void *>> free_blocks; // rounded size -> free blocks
+    std::unordered_map<void *, uint64_t> block_size;               // every live or cached block -> rounded size
+    uint64_t cached_bytes = 0;
+};
+BlockCache g_cache[MAX_SLOTS];
+#define g_free_blocks (g_cache[ctx().slot].free_blocks)
+#define g_block_size (g_cache[ctx().slot].block_size)
+#define g_cached_bytes (g_cache[ctx().slot].cached_bytes)
 constexpr uint64_t CACHE_CAP_BYTES = 24ull << 30;
 
 void release_cached_blocks()   // caller holds g_alloc_mu
@@ -529,7 +622,7 @@ int tstwo_twiddles_precompute(uint32_t init, int log, tstwo_twiddles *out)
     cudaError_t e = cudaMalloc(&buf, n * 4 * 4);
     if (e == cudaErrorMemoryAllocation) { cudaGetLastError(); return fail(TSTWO_ERR_OOM, "twiddle tree out of memory"); }
     TS_CUDA(e);
-    TwiddleTree *t = new TwiddleTree{ init & 0x7fffffffu, log, buf, buf + n, buf + 2 * n, buf + 3 * n };
+    TwiddleTree *t = new TwiddleTree{ ctx().slot, init & 0x7fffffffu, log, buf, buf + n, buf + 2 * n, buf + 3 * n };
     TS_LAUNCH(twiddle_tree_kernel, (unsigned)((n + 127) / 128), 128, 0, t->tw, t->itw, t->tw2, t->itw2, t->root_init, log);
     std::lock_guard<std::mutex> lk(g_tree_mu);
     uint64_t h = g_next_tree++;

@@ -230,13 +230,12 @@ static bool leaf_tma_applies(const ColSet &cs, int n_cols, uint64_t n)
 
 static int merkle_leaf_tma(const ColSet &cs, int n_cols, uint64_t n, uint8_t *out)
 {
-    static bool attr_done = false;
     LeafEncodeFn enc = reinterpret_cast<LeafEncodeFn>(tma_encode_tiled_fn());
     if (!enc) return TSTWO_ERR_CUDA;
-    if (!attr_done) {
+    if (!ctx().attr_leaf) {   // per device
         TS_CUDA(cudaFuncSetAttribute(merkle_leaf_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LEAF_SMEM));
         TS_CUDA(cudaFuncSetAttribute(merkle_leaf_tma_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
-        attr_done = true;
+        ctx().attr_leaf = true;
     }
     CUtensorMap map;
     const cuuint64_t dims[2] = { n, (cuuint64_t)n_cols };

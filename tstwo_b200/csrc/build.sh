@@ -7,7 +7,7 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -ccbin /usr/bin/g++"
 mkdir -p _obj
 pids=()
-for f in abi_core fft fft_stream fft_tma blake2s elementwise pipeline; do
+for f in abi_core fft fft_stream fft_tma blake2s elementwise pipeline multi; do
   if [ ! -f _obj/$f.o ] || [ $f.cu -nt _obj/$f.o ] || [ -n "$(find . -maxdepth 1 \( -name '*.cuh' -o -name '*.h' \) -newer _obj/$f.o 2>/dev/null)" ] || [ ../../include/tstwo_cuda.h -nt _obj/$f.o ]; then
     $NVCC $FLAGS -c $f.cu -o _obj/$f.o &
     pids+=($!)

@@ -10,8 +10,14 @@
 
 namespace tstwo {
 
+constexpr int MAX_SLOTS = 16;   // devices one process can drive (tstwo_init_devices)
+
+// Everything the library keeps per DEVICE.  One process may drive several devices from one host thread (the reference host
+// is a single process: SURVEY 8b "Conventions"): slot k holds device ids[k] of tstwo_init_devices, slot 0 is the device of
+// tstwo_init.  Entry points work on the CURRENT slot (tstwo_set_device; default 0).
 struct Context {
     bool ready = false;
+    int slot = 0;
     int device = -1;
     int sm_count = 0;
     cudaStream_t own_stream = nullptr;   // library stream
@@ -23,9 +29,28 @@ struct Context {
     // small device scratch for pointer tables / parameters
     uint64_t *d_ptr_table = nullptr;
     size_t ptr_table_cap = 0;
+    // per-device one-time kernel attributes (cudaFuncSetAttribute applies to the current device only)
+    bool attr_fft = false, attr_stream = false, attr_tma = false, attr_leaf = false;
+    // pipeline.cu: coefficient scratch, side stream + events of the overlapped peer-store path
+    uint32_t *coeff_scratch = nullptr;
+    size_t coeff_scratch_words = 0;
+    cudaStream_t peer_stream = nullptr;
+    cudaEvent_t peer_ev[2] = { nullptr, nullptr };
+    // elementwise.cu scratch
+    uint32_t *ew_scratch = nullptr;
+    size_t ew_scratch_bytes = 0;
 };
 
-Context &ctx();
+Context &ctx();                 // context of the calling thread's current slot
+Context &ctx_at(int slot);
+int ctx_slots();                // number of initialised slots
+// makes `slot` current for the calling thread (cudaSetDevice + ctx()); returns the previous slot
+int ctx_select(int slot);
+struct DeviceScope {            // RAII form
+    int prev;
+    explicit DeviceScope(int slot) : prev(ctx_select(slot)) {}
+    ~DeviceScope() { ctx_select(prev); }
+};
 int fail(int code, const char *fmt, ...);
 
 #define TS_CUDA(expr)                                                                              \
@@ -85,6 +110,7 @@ int make_colset(const tstwo_dptr *cols, int n_cols, int slot, ColSet *out);
 
 // ---- twiddle trees ----
 struct TwiddleTree {
+    int slot;                // device slot the tables live on
     uint32_t root_init;
     int root_log;
     uint32_t *tw, *itw;      // reference layout (backend/cpu/circle.ts:210-239), 2^root_log words each

@@ -571,8 +571,9 @@ __global__ void fold_qm_kernel(const uint32_t *in, uint64_t in_stride, uint64_t 
 static m31::QM to_dev(const uint32_t a[4]) { return { a[0], a[1], a[2], a[3] }; }
 
 // scratch buffer (grown on demand, freed at shutdown by process exit)
-static uint32_t *g_scratch = nullptr;
-static size_t g_scratch_bytes = 0;
+// per device (Context::ew_scratch)
+#define g_scratch (ctx().ew_scratch)
+#define g_scratch_bytes (ctx().ew_scratch_bytes)
 static int scratch(size_t bytes, uint32_t **out)
 {
     if (bytes > g_scratch_bytes) {

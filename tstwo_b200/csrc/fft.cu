@@ -354,7 +354,6 @@ __global__ void small_interp_kernel(ColSet cols, int n, uint32_t xi2, uint32_t y
 }
 
 static bool g_force_naive = false;
-static bool g_smem_attr_set = false;
 
 static int g_dig = 4;   // rows per thread = 2^g_dig (tstwo_debug_set_fft_radix): 4 -> 256 threads (default), 3 -> 512 threads
 
@@ -372,11 +371,11 @@ template <int DIG> static int set_attrs()
 }
 static int ensure_smem_attr()
 {
-    if (g_smem_attr_set) return 0;
+    if (ctx().attr_fft) return 0;   // per device: cudaFuncSetAttribute applies to the current device
     int rc = set_attrs<3>();
     if (rc) return rc;
     if ((rc = set_attrs<4>())) return rc;
-    g_smem_attr_set = true;
+    ctx().attr_fft = true;
     return 0;
 }
 

@@ -386,17 +386,16 @@ template <bool INV, bool STRIDED, bool FULL> cudaError_t set_attr()
 {
     return cudaFuncSetAttribute(fft_stream_kernel<INV, STRIDED, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
 }
-bool g_attr_set = false;
 
 }  // namespace
 
 int stream_pass_init()
 {
-    if (g_attr_set) return 0;
+    if (ctx().attr_stream) return 0;   // per device
     TS_CUDA((set_attr<false, false, true>())); TS_CUDA((set_attr<true, false, true>()));
     TS_CUDA((set_attr<false, true, true>()));  TS_CUDA((set_attr<true, true, true>()));
     TS_CUDA((set_attr<false, true, false>())); TS_CUDA((set_attr<true, true, false>()));
-    g_attr_set = true;
+    ctx().attr_stream = true;
     return 0;
 }
 

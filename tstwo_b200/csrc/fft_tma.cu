@@ -556,7 +556,6 @@ int g_use_tc = 1;
 struct PassStamp { int tag; cudaEvent_t e0, e1; };
 bool g_timing = false;
 std::vector<PassStamp> g_stamps;
-bool g_ready = false;
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -592,7 +591,7 @@ int tma_trace_cta(int cta)
 
 int tma_pass_init()
 {
-    if (g_ready) return 0;
+    if (ctx().attr_tma) return 0;      // per device: cudaFuncSetAttribute applies to the current device
     TS_CUDA((set_attr<false, false, true>())); TS_CUDA((set_attr<true, false, true>()));
     TS_CUDA((set_attr<false, true, true>()));  TS_CUDA((set_attr<true, true, true>()));
     TS_CUDA((set_attr<false, true, false>())); TS_CUDA((set_attr<true, true, false>()));
@@ -604,7 +603,7 @@ int tma_pass_init()
     if (!fn || qres != cudaDriverEntryPointSuccess) return fail(TSTWO_ERR_CUDA, "driver has no cuTensorMapEncodeTiled");
     g_encode = reinterpret_cast<EncodeTiledFn>(fn);
     if (const char *e = getenv("TSTWO_FFT_TC")) g_use_tc = atoi(e);   // A/B without a rebuild (see tstwo_debug_set_fft_tc)
-    g_ready = true;
+    ctx().attr_tma = true;
     return 0;
 }
 

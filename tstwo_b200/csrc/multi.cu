@@ -1,0 +1,229 @@
+// Multi-GPU LDE + Blake2s commit driven by ONE host thread of ONE process (SURVEY 8b "Conventions", 8e): the reference host is
+// a single-threaded Bun process that calls MerkleProver.commit inline (packages/core/src/vcs/prover.ts:13-30 from
+// prover/index.ts:582-662), so the fan-out over the devices of tstwo_init_devices lives inside the library:
+//
+//   device d  (its own stream)   LDE of columns [d * n_cols/G, (d+1) * n_cols/G); the last FFT pass stores every row range
+//                                straight into its owner's leaf buffer over NVLink peer memory (cudaDeviceEnablePeerAccess,
+//                                no CUDA IPC, no NCCL) -- the fused exchange of tstwo_lde_columns_to_peers_overlapped
+//   event fan-in                 device d waits for the "LDE done" events of ALL devices (cross-device cudaStreamWaitEvent),
+//   device d                     hashes its 2^ext/G leaves, builds its subtree, copies its root to device 0,
+//   device 0                     waits for the G roots, finishes the top log2 G layers, root to the host.
+//
+// Every call is enqueued asynchronously device by device; the only host wait is the final one for the root.
+#include <cstring>
+#include <vector>
+
+#include "common.cuh"
+#include "host_m31.h"
+
+using namespace tstwo;
+
+namespace {
+
+struct Dev {
+    tstwo_twiddles tw = 0;
+    uint32_t *stage = nullptr, *work = nullptr, *leaf = nullptr;   // host-fed staging [lc][n], evaluations scratch [lc][ne], leaf buffer [n_cols][rows]
+    uint8_t *layers = nullptr;                                     // this device's subtree, root first
+    cudaEvent_t lde_done = nullptr, sub_done = nullptr, stage_free = nullptr;
+    std::vector<cudaEvent_t> chunk_ev;
+};
+struct Multi {
+    int n_dev = 0, n_cols = 0, log_size = 0, log_blowup = 0;
+    bool has_stage = false, ran = false;
+    Dev d[MAX_SLOTS];
+    uint8_t *roots = nullptr, *top = nullptr;    // device 0: [G][32] subtree roots, top layers (G - 1 hashes, root first)
+    uint8_t *host_root = nullptr;                // pinned
+} g_m;
+
+void release_all()
+{
+    for (int i = 0; i < g_m.n_dev; i++) {
+        if (!ctx_at(i).ready) continue;
+        DeviceScope sc(i);
+        Dev &v = g_m.d[i];
+        cudaDeviceSynchronize();
+        if (v.tw) tstwo_twiddles_free(v.tw);
+        cudaFree(v.stage); cudaFree(v.work); cudaFree(v.leaf); cudaFree(v.layers);
+        for (cudaEvent_t e : { v.lde_done, v.sub_done, v.stage_free }) if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : v.chunk_ev) cudaEventDestroy(e);
+        if (i == 0) { cudaFree(g_m.roots); cudaFree(g_m.top); }
+        v = Dev();
+    }
+    if (g_m.host_root) cudaFreeHost(g_m.host_root);
+    g_m = Multi();
+}
+
+int dev_alloc(void **p, size_t bytes, const char *what)
+{
+    cudaError_t e = cudaMalloc(p, bytes);
+    if (e == cudaErrorMemoryAllocation) { cudaGetLastError(); return fail(TSTWO_ERR_OOM, "tstwo_lde_commit_multi: %s (%zu bytes) out of memory", what, bytes); }
+    TS_CUDA(e);
+    return 0;
+}
+
+int ensure(int n_cols, int log_size, int log_blowup, bool need_stage)
+{
+    const int G = ctx_slots();
+    if (g_m.n_dev == G && g_m.n_cols == n_cols && g_m.log_size == log_size && g_m.log_blowup == log_blowup && (g_m.has_stage || !need_stage))
+        return 0;
+    release_all();
+    const int ext = log_size + log_blowup;
+    int sl = 0;
+    while ((1 << sl) < G) sl++;
+    const uint64_t n = 1ull << log_size, ne = 1ull << ext, rows = ne >> sl;
+    const int lc = n_cols / G;
+    g_m.n_dev = G; g_m.n_cols = n_cols; g_m.log_size = log_size; g_m.log_blowup = log_blowup; g_m.has_stage = need_stage;
+    for (int i = 0; i < G; i++) {
+        DeviceScope sc(i);
+        Dev &v = g_m.d[i];
+        int rc = tstwo_twiddles_precompute(host::subgroup_gen(ext - 1 + 2), ext - 1, &v.tw);
+        if (rc) return rc;
+        if ((rc = dev_alloc((void **)&v.work, (size_t)lc * ne * 4, "evaluation scratch"))) return rc;
+        if ((rc = dev_alloc((void **)&v.leaf, (size_t)n_cols * rows * 4, "leaf buffer"))) return rc;
+        if ((rc = dev_alloc((void **)&v.layers, 32ull * (2 * rows - 1), "subtree"))) return rc;
+        if (need_stage && (rc = dev_alloc((void **)&v.stage, (size_t)lc * n * 4, "trace staging"))) return rc;
+        for (cudaEvent_t *e : { &v.lde_done, &v.sub_done, &v.stage_free }) TS_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+        if (i == 0) {
+            if ((rc = dev_alloc((void **)&g_m.roots, 32ull * G, "subtree roots"))) return rc;
+            if ((rc = dev_alloc((void **)&g_m.top, 32ull * (G > 1 ? G : 2), "top layers"))) return rc;
+        }
+    }
+    TS_CUDA(cudaMallocHost((void **)&g_m.host_root, 32));
+    return 0;
+}
+
+// column groups / SMs of the NVLink-bound pass for the overlapped exchange (profiles/r01_overlap.txt)
+void overlap_params(int G, int *groups, int *peer_sms) { *groups = G > 1 ? 4 : 1; *peer_sms = G > 1 ? 62 : 0; }
+
+int check(int n_cols, int log_size, int log_blowup)
+{
+    const int G = ctx_slots();
+    if (G < 1) return fail(TSTWO_ERR_NOT_INIT, "tstwo_init_devices() has not been called");
+    if (G & (G - 1)) return fail(TSTWO_ERR_BAD_ARG, "the number of devices (%d) must be a power of two", G);
+    if (n_cols < G || n_cols % G) return fail(TSTWO_ERR_BAD_ARG, "n_cols (%d) must be a multiple of the number of devices (%d)", n_cols, G);
+    int sl = 0;
+    while ((1 << sl) < G) sl++;
+    if (log_size < 1 || log_blowup < 0 || log_size + log_blowup > 30 || log_size + log_blowup - sl < 14)
+        return fail(TSTWO_ERR_BAD_ARG, "bad sizes: every device needs at least 2^14 rows of the evaluation domain");
+    return 0;
+}
+
+// steps 2..4 of the header comment, after every device's LDE has been enqueued and lde_done recorded
+int subtrees_and_top(uint8_t root[32])
+{
+    const int G = g_m.n_dev, n_cols = g_m.n_cols, ext = g_m.log_size + g_m.log_blowup;
+    int sl = 0;
+    while ((1 << sl) < G) sl++;
+    const uint64_t rows = (1ull << ext) >> sl;
+    std::vector<tstwo_dptr> ptrs((size_t)n_cols);
+    std::vector<int> logs((size_t)n_cols, ext - sl);
+    for (int i = 0; i < G; i++) {
+        DeviceScope sc(i);
+        Context &c = ctx();
+        Dev &v = g_m.d[i];
+        for (int e = 0; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].lde_done, 0));
+        for (int k = 0; k < n_cols; k++) ptrs[k] = (tstwo_dptr)(v.leaf + (uint64_t)k * rows);
+        int rc = tstwo_merkle_commit(ptrs.data(), logs.data(), n_cols, (tstwo_dptr)v.layers, nullptr);
+        if (rc) return rc;
+        TS_CUDA(cudaMemcpyPeerAsync(g_m.roots + 32 * i, ctx_at(0).device, v.layers, c.device, 32, c.stream));
+        TS_CUDA(cudaEventRecord(v.sub_done, c.stream));
+    }
+    DeviceScope sc(0);
+    Context &c = ctx();
+    for (int e = 1; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].sub_done, 0));
+    const uint8_t *prev = g_m.roots;
+    for (int k = sl - 1; k >= 0; k--) {                        // layer k has 2^k hashes, at byte 32 (2^k - 1) of `top`
+        uint8_t *dst = g_m.top + 32ull * ((1ull << k) - 1);
+        int rc = tstwo_merkle_commit_layer(k, (tstwo_dptr)prev, nullptr, 0, (tstwo_dptr)dst);
+        if (rc) return rc;
+        prev = dst;
+    }
+    TS_CUDA(cudaMemcpyAsync(g_m.host_root, prev, 32, cudaMemcpyDeviceToHost, c.stream));
+    TS_CUDA(cudaStreamSynchronize(c.stream));
+    if (root) memcpy(root, g_m.host_root, 32);
+    g_m.ran = true;
+    return 0;
+}
+
+}  // namespace
+
+namespace tstwo {
+void multi_release() { release_all(); }
+}
+
+extern "C" {
+
+// Device-resident shards: trace_shards[d] = columns [d * n_cols/G, (d+1) * n_cols/G) as [n_cols/G][2^log_size] words ON device
+// slot d.  The library owns every other buffer (allocated at the first call for a shape, kept until the shape changes).
+int tstwo_lde_commit_multi_dev(const tstwo_dptr *trace_shards, int n_cols, int log_size, int log_blowup, uint8_t root[32], uint32_t flags)
+{
+    int rc = check(n_cols, log_size, log_blowup);
+    if (rc) return rc;
+    if (!trace_shards) return fail(TSTWO_ERR_BAD_ARG, "null trace shards");
+    if ((rc = ensure(n_cols, log_size, log_blowup, false))) return rc;
+    const int G = g_m.n_dev, lc = n_cols / G;
+    int groups, peer_sms;
+    overlap_params(G, &groups, &peer_sms);
+    tstwo_dptr bases[MAX_SLOTS];
+    for (int i = 0; i < G; i++) bases[i] = (tstwo_dptr)g_m.d[i].leaf;
+    for (int i = 0; i < G; i++) {
+        if (!trace_shards[i]) return fail(TSTWO_ERR_BAD_ARG, "trace shard %d is null", i);
+        DeviceScope sc(i);
+        Context &c = ctx();
+        // my stores go into every device's leaf buffer: the previous step's hashing of those must be over
+        if (g_m.ran) for (int e = 0; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].sub_done, 0));
+        rc = tstwo_lde_columns_to_peers_overlapped(trace_shards[i], lc, log_size, log_blowup, g_m.d[i].tw, 0, (tstwo_dptr)g_m.d[i].work,
+                                                   bases, G, i * lc, flags, groups, peer_sms);
+        if (rc) return rc;
+        TS_CUDA(cudaEventRecord(g_m.d[i].lde_done, c.stream));
+    }
+    return subtrees_and_top(root);
+}
+
+// The host's call: host_trace = [n_cols][2^log_size] words in HOST memory (pinned for full PCIe speed; pageable works).  Every
+// device pulls its column shard over its own PCIe link in column chunks on its copy stream, and each chunk's LDE + peer stores
+// start as soon as it has landed.
+int tstwo_lde_commit_multi(const uint32_t *host_trace, int n_cols, int log_size, int log_blowup, uint8_t root[32], uint32_t flags)
+{
+    int rc = check(n_cols, log_size, log_blowup);
+    if (rc) return rc;
+    if (!host_trace) return fail(TSTWO_ERR_BAD_ARG, "null host trace");
+    if ((rc = ensure(n_cols, log_size, log_blowup, true))) return rc;
+    const int G = g_m.n_dev, lc = n_cols / G;
+    const uint64_t n = 1ull << log_size, ne = 1ull << (log_size + log_blowup);
+    int chunks = lc < 4 ? lc : 4;
+    while (lc % chunks) chunks--;
+    const int per = lc / chunks;
+    tstwo_dptr bases[MAX_SLOTS];
+    for (int i = 0; i < G; i++) bases[i] = (tstwo_dptr)g_m.d[i].leaf;
+    // all copies first, so that every PCIe link starts at once
+    for (int i = 0; i < G; i++) {
+        DeviceScope sc(i);
+        Context &c = ctx();
+        Dev &v = g_m.d[i];
+        while ((int)v.chunk_ev.size() < chunks) { cudaEvent_t e; TS_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); v.chunk_ev.push_back(e); }
+        if (g_m.ran) TS_CUDA(cudaStreamWaitEvent(c.copy_stream, v.stage_free, 0));   // the previous step's transforms have read the staging buffer
+        for (int k = 0; k < chunks; k++) {
+            TS_CUDA(cudaMemcpyAsync(v.stage + (uint64_t)k * per * n, host_trace + ((uint64_t)i * lc + (uint64_t)k * per) * n, (uint64_t)per * n * 4,
+                                    cudaMemcpyHostToDevice, c.copy_stream));
+            TS_CUDA(cudaEventRecord(v.chunk_ev[k], c.copy_stream));
+        }
+    }
+    for (int i = 0; i < G; i++) {
+        DeviceScope sc(i);
+        Context &c = ctx();
+        Dev &v = g_m.d[i];
+        if (g_m.ran) for (int e = 0; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].sub_done, 0));
+        for (int k = 0; k < chunks; k++) {
+            TS_CUDA(cudaStreamWaitEvent(c.stream, v.chunk_ev[k], 0));
+            rc = tstwo_lde_columns_to_peers((tstwo_dptr)(v.stage + (uint64_t)k * per * n), per, log_size, log_blowup, v.tw, 0,
+                                            (tstwo_dptr)(v.work + (uint64_t)k * per * ne), bases, G, i * lc + k * per, flags);
+            if (rc) return rc;
+        }
+        TS_CUDA(cudaEventRecord(v.stage_free, c.stream));
+        TS_CUDA(cudaEventRecord(v.lde_done, c.stream));
+    }
+    return subtrees_and_top(root);
+}
+
+}  // extern "C"

@@ -13,8 +13,9 @@ using namespace tstwo;
 namespace {
 // scratch for coefficients the caller does not want to keep (they may not alias the evals they are extended into:
 // the coset passes of different CTAs read the same coefficients)
-uint32_t *g_coeff_scratch = nullptr;
-size_t g_coeff_scratch_words = 0;
+// (per device: Context::coeff_scratch)
+#define g_coeff_scratch (ctx().coeff_scratch)
+#define g_coeff_scratch_words (ctx().coeff_scratch_words)
 int coeff_scratch(size_t words, uint32_t **out)
 {
     if (words > g_coeff_scratch_words) {
@@ -132,8 +133,9 @@ int tstwo_lde_columns_sharded(tstwo_dptr trace, int n_cols, int log_size, int lo
 // exchange (7/8 of the evaluations at 8 GPUs, >= 1 ms at 900 GB/s) then overlaps ALL of the LDE's arithmetic, not just the
 // 14 layers of the pass that issues the stores.  Same bytes, same destinations: results are identical for any grouping.
 namespace {
-cudaStream_t g_peer_stream = nullptr;
-cudaEvent_t g_peer_ev[2] = { nullptr, nullptr };   // [0] group ready for its last pass (main -> side), [1] side drained
+// per device (Context): peer_stream; peer_ev[0] group ready for its last pass (main -> side), [1] side drained
+#define g_peer_stream (ctx().peer_stream)
+#define g_peer_ev (ctx().peer_ev)
 
 int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, tstwo_dptr coeffs,
                  tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards, int col_offset, uint32_t flags,
