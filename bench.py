@@ -239,6 +239,77 @@ def cpu_baseline(args):
                       f"{'-O3 -march=native on this host' if native else '-O3 -march=x86-64-v2'}"}
 
 
+def run_single_process(args):
+    """N GPUs driven by ONE process / one host thread through tstwo_init_devices + tstwo_lde_commit_multi[_dev] (the form a
+    TStwo host can call: SURVEY 8b).  Same job, same trace, same JSON keys as the torchrun arm."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    import torch
+    from tstwo_b200 import _lib
+    G = args.gpus
+    L = _lib.load(); chk = _lib.check
+    chk(L.tstwo_init_devices(G, (C.c_int * G)(*range(G))))
+    log, blow, n_cols = args.log_size, LOG_BLOWUP, args.cols
+    n = 1 << log
+    lc = n_cols // G
+    shards = [make_trace(torch, torch.device("cuda", d), d, G, n_cols, n) for d in range(G)]
+    for d in range(G):
+        torch.cuda.synchronize(d)
+    ptrs = (C.c_uint64 * G)(*[s.data_ptr() for s in shards])
+    root = (C.c_uint8 * 32)()
+    step = lambda: chk(L.tstwo_lde_commit_multi_dev(ptrs, n_cols, log, blow, root, 0))
+    sampler = ClockSampler(0, None)
+    sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sampler.mark()
+    chk(L.tstwo_set_device(0))
+    l0 = L.tstwo_launch_count()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()                       # returns with the root on the host: every device has finished
+    ms = (time.perf_counter() - t0) / args.steps * 1e3
+    launches = 0
+    for d in range(G):
+        chk(L.tstwo_set_device(d)); launches += int(L.tstwo_launch_count())
+    chk(L.tstwo_set_device(0))
+    clocks = sampler.stop()
+    root_hex = bytes(root).hex()
+    e2e = None
+    if not args.no_e2e:
+        host = torch.empty((n_cols, n), dtype=torch.int32, pin_memory=True)
+        for d in range(G):
+            host[d * lc:(d + 1) * lc].copy_(shards[d].cpu())
+        del shards
+        root2 = (C.c_uint8 * 32)()
+        hstep = lambda: chk(L.tstwo_lde_commit_multi(C.c_void_p(host.data_ptr()), n_cols, log, blow, root2, 0))
+        for _ in range(3):
+            hstep()
+        k = max(3, min(args.steps, 5))
+        t0 = time.perf_counter()
+        for _ in range(k):
+            hstep()
+        dt = (time.perf_counter() - t0) / k
+        assert bytes(root2).hex() == root_hex, "e2e root differs from device-resident root"
+        e2e = {"value": n_cols * n / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "h2d_bytes_per_step": n_cols * n * 4, "d2h_bytes_per_step": 32,
+               "api": f"tstwo_lde_commit_multi (C ABI, one host thread, pinned host trace -> root), {G} PCIe links"}
+    out = {"metric": METRIC, "value": n_cols * n / (ms * 1e-3), "unit": UNIT, "n_gpus": G, "steps": args.steps, "warmup": max(args.warmup, 3),
+           "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u32 (M31)", "data": "synthetic",
+           "config": {"workload": f"{n_cols} cols x 2^{log} M31, blowup 2 (2^{log + blow} rows), Blake2s Merkle commit", "n_cols": n_cols,
+                      "log_size": log, "log_blowup": blow,
+                      "parallelism": f"ONE process, one host thread, {G} devices: tstwo_init_devices + tstwo_lde_commit_multi_dev "
+                                     "(column-sharded LDE, last FFT pass stores rows to their owner over NVLink peer access, events as fences)",
+                      "timing": "host wall clock around calls that return with the root on the host (every device done); "
+                                "launches = sum over devices"},
+           "gpu_launches": launches - int(l0), "clocks": clocks, "root": root_hex,
+           "root_matches_oracle_checked_root": root_hex == BENCH_ROOT if (n_cols, log, blow) == (N_COLS, LOG_SIZE, LOG_BLOWUP) else None}
+    if e2e: out["e2e"] = e2e
+    print(json.dumps(out), file=_REAL_STDOUT, flush=True)
+    chk(L.tstwo_shutdown())
+
+
 def run_cuda(args):
     # NCCL prints its version banner on stdout when NCCL_DEBUG=VERSION: the driver wants exactly one JSON line there
     # ("NCCL version ..." appears there on this image): everything written to fd 1 from here on goes to stderr, and
@@ -697,5 +768,7 @@ if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference(a)
+    elif a.single_process:
+        run_single_process(a)
     else:
         run_cuda(a)

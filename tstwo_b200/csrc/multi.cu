@@ -10,7 +10,11 @@
 //   device 0                     waits for the G roots, finishes the top log2 G layers, root to the host.
 //
 // Every call is enqueued asynchronously device by device; the only host wait is the final one for the root.
+#include <condition_variable>
 #include <cstring>
+#include <functional>
+#include <mutex>
+#include <thread>
 #include <vector>
 
 #include "common.cuh"
@@ -19,6 +23,75 @@
 using namespace tstwo;
 
 namespace {
+
+// The CALLER is one host thread (the reference host is single-threaded), but enqueuing ~70 launches / event operations per
+// device costs ~0.35 ms of host time each: at 8 devices that alone is the whole 2.9 ms step.  The library therefore keeps one
+// helper thread per extra device; for_each_device(fn) runs fn(slot) for all slots concurrently (slot 0 on the caller's thread)
+// and returns when all are done.  Helpers only enqueue; they never outlive tstwo_shutdown.
+class Fanout {
+public:
+    int run(int n, const std::function<int(int)> &fn)
+    {
+        ensure(n);
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            fn_ = &fn; pending_ = n - 1; gen_++;
+            for (int i = 0; i < n; i++) rc_[i] = 0;
+        }
+        cv_.notify_all();
+        rc_[0] = fn(0);
+        std::unique_lock<std::mutex> lk(mu_);
+        done_.wait(lk, [&] { return pending_ == 0; });
+        for (int i = 0; i < n; i++)
+            if (rc_[i]) { if (i) fail(rc_[i], "%s", err_[i]); return rc_[i]; }
+        return 0;
+    }
+    void stop()
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            quit_ = true; gen_++;
+        }
+        cv_.notify_all();
+        for (auto &t : th_) t.join();
+        th_.clear(); quit_ = false; n_ = 1;
+    }
+private:
+    void ensure(int n)
+    {
+        if (n == n_) return;
+        stop();
+        n_ = n;
+        const uint64_t g0 = gen_;
+        for (int i = 1; i < n; i++) th_.emplace_back([this, i, g0] { worker(i, g0); });
+    }
+    void worker(int slot, uint64_t seen)
+    {
+        for (;;) {
+            const std::function<int(int)> *fn;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (quit_) return;
+                fn = fn_;
+            }
+            int rc = (*fn)(slot);
+            if (rc) { strncpy(err_[slot], tstwo_last_error(), sizeof err_[slot] - 1); err_[slot][sizeof err_[slot] - 1] = 0; }
+            std::lock_guard<std::mutex> lk(mu_);
+            rc_[slot] = rc;
+            if (--pending_ == 0) done_.notify_one();
+        }
+    }
+    std::mutex mu_;
+    std::condition_variable cv_, done_;
+    std::vector<std::thread> th_;
+    const std::function<int(int)> *fn_ = nullptr;
+    uint64_t gen_ = 0;
+    int n_ = 1, pending_ = 0, rc_[MAX_SLOTS] = { 0 };
+    char err_[MAX_SLOTS][256];
+    bool quit_ = false;
+} g_fan;
 
 struct Dev {
     tstwo_twiddles tw = 0;
@@ -115,26 +188,28 @@ int subtrees_and_top(uint8_t root[32])
     int sl = 0;
     while ((1 << sl) < G) sl++;
     const uint64_t rows = (1ull << ext) >> sl;
-    std::vector<tstwo_dptr> ptrs((size_t)n_cols);
-    std::vector<int> logs((size_t)n_cols, ext - sl);
-    for (int i = 0; i < G; i++) {
+    int rc = g_fan.run(G, [&](int i) -> int {
+        std::vector<tstwo_dptr> ptrs((size_t)n_cols);
+        std::vector<int> logs((size_t)n_cols, ext - sl);
         DeviceScope sc(i);
         Context &c = ctx();
         Dev &v = g_m.d[i];
         for (int e = 0; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].lde_done, 0));
         for (int k = 0; k < n_cols; k++) ptrs[k] = (tstwo_dptr)(v.leaf + (uint64_t)k * rows);
-        int rc = tstwo_merkle_commit(ptrs.data(), logs.data(), n_cols, (tstwo_dptr)v.layers, nullptr);
-        if (rc) return rc;
+        int r = tstwo_merkle_commit(ptrs.data(), logs.data(), n_cols, (tstwo_dptr)v.layers, nullptr);
+        if (r) return r;
         TS_CUDA(cudaMemcpyPeerAsync(g_m.roots + 32 * i, ctx_at(0).device, v.layers, c.device, 32, c.stream));
         TS_CUDA(cudaEventRecord(v.sub_done, c.stream));
-    }
+        return 0;
+    });
+    if (rc) return rc;
     DeviceScope sc(0);
     Context &c = ctx();
     for (int e = 1; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].sub_done, 0));
     const uint8_t *prev = g_m.roots;
     for (int k = sl - 1; k >= 0; k--) {                        // layer k has 2^k hashes, at byte 32 (2^k - 1) of `top`
         uint8_t *dst = g_m.top + 32ull * ((1ull << k) - 1);
-        int rc = tstwo_merkle_commit_layer(k, (tstwo_dptr)prev, nullptr, 0, (tstwo_dptr)dst);
+        rc = tstwo_merkle_commit_layer(k, (tstwo_dptr)prev, nullptr, 0, (tstwo_dptr)dst);
         if (rc) return rc;
         prev = dst;
     }
@@ -148,7 +223,7 @@ int subtrees_and_top(uint8_t root[32])
 }  // namespace
 
 namespace tstwo {
-void multi_release() { release_all(); }
+void multi_release() { release_all(); g_fan.stop(); }
 }
 
 extern "C" {
@@ -166,17 +241,20 @@ int tstwo_lde_commit_multi_dev(const tstwo_dptr *trace_shards, int n_cols, int l
     overlap_params(G, &groups, &peer_sms);
     tstwo_dptr bases[MAX_SLOTS];
     for (int i = 0; i < G; i++) bases[i] = (tstwo_dptr)g_m.d[i].leaf;
-    for (int i = 0; i < G; i++) {
+    for (int i = 0; i < G; i++)
         if (!trace_shards[i]) return fail(TSTWO_ERR_BAD_ARG, "trace shard %d is null", i);
+    rc = g_fan.run(G, [&](int i) -> int {
         DeviceScope sc(i);
         Context &c = ctx();
         // my stores go into every device's leaf buffer: the previous step's hashing of those must be over
         if (g_m.ran) for (int e = 0; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].sub_done, 0));
-        rc = tstwo_lde_columns_to_peers_overlapped(trace_shards[i], lc, log_size, log_blowup, g_m.d[i].tw, 0, (tstwo_dptr)g_m.d[i].work,
-                                                   bases, G, i * lc, flags, groups, peer_sms);
-        if (rc) return rc;
+        int r = tstwo_lde_columns_to_peers_overlapped(trace_shards[i], lc, log_size, log_blowup, g_m.d[i].tw, 0, (tstwo_dptr)g_m.d[i].work,
+                                                      bases, G, i * lc, flags, groups, peer_sms);
+        if (r) return r;
         TS_CUDA(cudaEventRecord(g_m.d[i].lde_done, c.stream));
-    }
+        return 0;
+    });
+    if (rc) return rc;
     return subtrees_and_top(root);
 }
 
@@ -209,20 +287,22 @@ int tstwo_lde_commit_multi(const uint32_t *host_trace, int n_cols, int log_size,
             TS_CUDA(cudaEventRecord(v.chunk_ev[k], c.copy_stream));
         }
     }
-    for (int i = 0; i < G; i++) {
+    rc = g_fan.run(G, [&](int i) -> int {
         DeviceScope sc(i);
         Context &c = ctx();
         Dev &v = g_m.d[i];
         if (g_m.ran) for (int e = 0; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].sub_done, 0));
         for (int k = 0; k < chunks; k++) {
             TS_CUDA(cudaStreamWaitEvent(c.stream, v.chunk_ev[k], 0));
-            rc = tstwo_lde_columns_to_peers((tstwo_dptr)(v.stage + (uint64_t)k * per * n), per, log_size, log_blowup, v.tw, 0,
-                                            (tstwo_dptr)(v.work + (uint64_t)k * per * ne), bases, G, i * lc + k * per, flags);
-            if (rc) return rc;
+            int r = tstwo_lde_columns_to_peers((tstwo_dptr)(v.stage + (uint64_t)k * per * n), per, log_size, log_blowup, v.tw, 0,
+                                               (tstwo_dptr)(v.work + (uint64_t)k * per * ne), bases, G, i * lc + k * per, flags);
+            if (r) return r;
         }
         TS_CUDA(cudaEventRecord(v.stage_free, c.stream));
         TS_CUDA(cudaEventRecord(v.lde_done, c.stream));
-    }
+        return 0;
+    });
+    if (rc) return rc;
     return subtrees_and_top(root);
 }
 
