@@ -35,6 +35,32 @@ def test_library_exports_every_header_symbol():
     assert not undeclared, f"exported but declared in no header: {sorted(undeclared)}"
 
 
+def _header_decls():
+    """{name: (number of parameters, FFI return type)} of every function include/tstwo_cuda.h declares."""
+    h = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "tstwo_cuda.h")).read(), flags=re.S)
+    out = {}
+    for ret, name, args in re.findall(r"\b(int|uint64_t|const char \*)\s*(tstwo_[a-z0-9_]+)\s*\(([^;]*?)\)\s*;", h, flags=re.S):
+        params = [a for a in (x.strip() for x in args.split(",")) if a and a != "void"]
+        out[name] = (len(params), {"int": "T.i32", "uint64_t": "T.u64", "const char *": "T.cstring"}[ret])
+    return out
+
+
+def test_ts_binding_matches_header():
+    """ts/cuda_backend.ts (the bun:ffi binding a TStwo maintainer adds; not executable here, no Bun) declares EVERY entry point
+    of the header with the right number of arguments and the right return type -- and nothing the header does not have."""
+    decls = _header_decls()
+    ts = open(os.path.join(ROOT, "ts", "cuda_backend.ts")).read()
+    bound = {m.group(1): (len([x for x in m.group(2).split(",") if x.strip()]), m.group(3))
+             for m in re.finditer(r"^\s*(tstwo_[a-z0-9_]+): \{ args: \[([^\]]*)\], returns: (T\.[a-z0-9]+) \}", ts, flags=re.M)}
+    assert set(bound) == set(decls), (sorted(set(decls) - set(bound)), sorted(set(bound) - set(decls)))
+    for name, (n, ret) in decls.items():
+        assert bound[name] == (n, ret), (name, bound[name], (n, ret))
+    # and the ctypes table has the same arities
+    from tstwo_b200 import _lib
+    for name, (n, _) in decls.items():
+        assert len(_lib.SIGNATURES[name][1]) == n, name
+
+
 def test_no_cpu_fallback():
     import torch
     if torch.cuda.is_available():

@@ -27,7 +27,8 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   tstwo_fold_circle_into_line: { args: [T.ptr, T.ptr, T.i32, T.u32, T.ptr, T.u64], returns: T.i32 },
   tstwo_lde_commit: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.u64, T.ptr, T.u32], returns: T.i32 },
   tstwo_lde_commit_host: { args: [T.ptr, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.u64, T.u64, T.ptr, T.u32], returns: T.i32 },
-  // multi-GPU (one Bun worker per GPU): last FFT pass stores into the peers' leaf buffers, mapped through CUDA IPC
+  // multi-GPU, one process per GPU (the torchrun path of bench.py): last FFT pass stores into the peers' leaf buffers, mapped
+  // through CUDA IPC.  A single Bun process uses tstwo_init_devices + tstwo_lde_commit_multi below instead.
   tstwo_lde_columns_to_peers: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.ptr, T.i32, T.i32, T.u32], returns: T.i32 },
   tstwo_lde_columns_to_peers_overlapped: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.ptr, T.i32, T.i32, T.u32, T.i32, T.i32], returns: T.i32 },
   tstwo_ipc_export: { args: [T.u64, T.ptr], returns: T.i32 },
@@ -41,6 +42,29 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   // wide-Fibonacci constraint quotients over the evaluation domain (ComponentProver.evaluateConstraintQuotientsOnDomain); allocator trim
   tstwo_widefib_constraints: { args: [T.i32, T.i32, T.ptr, T.i32, T.ptr, T.ptr, T.ptr], returns: T.i32 },
   tstwo_mem_trim: { args: [], returns: T.i32 },
+  // the rest of include/tstwo_cuda.h (tests/test_abi_cpu.py keeps this table and the header in step)
+  tstwo_init_devices: { args: [T.i32, T.ptr], returns: T.i32 },
+  tstwo_device_count: { args: [], returns: T.i32 },
+  tstwo_set_device: { args: [T.i32], returns: T.i32 },
+  tstwo_shutdown: { args: [], returns: T.i32 },
+  tstwo_set_stream: { args: [T.ptr], returns: T.i32 },
+  tstwo_sync: { args: [], returns: T.i32 },
+  tstwo_device_info: { args: [T.ptr, T.ptr, T.ptr, T.ptr], returns: T.i32 },
+  tstwo_launch_count: { args: [], returns: T.u64 },
+  tstwo_memset_zero: { args: [T.u64, T.u64], returns: T.i32 },
+  tstwo_copy: { args: [T.u64, T.u64, T.u64], returns: T.i32 },
+  tstwo_twiddles_free: { args: [T.u64], returns: T.i32 },
+  tstwo_twiddles_info: { args: [T.u64, T.ptr, T.ptr, T.ptr, T.ptr], returns: T.i32 },
+  tstwo_eval_at_point: { args: [T.u64, T.i32, T.ptr, T.ptr, T.ptr], returns: T.i32 },
+  tstwo_eval_at_point_many: { args: [T.ptr, T.i32, T.i32, T.ptr, T.ptr, T.ptr], returns: T.i32 },
+  tstwo_fri_decompose: { args: [T.ptr, T.i32, T.ptr, T.ptr], returns: T.i32 },
+  tstwo_accumulate: { args: [T.ptr, T.ptr, T.u64], returns: T.i32 },
+  tstwo_accumulate_quotients: { args: [T.i32, T.u32, T.ptr, T.i32, T.ptr, T.i32, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr], returns: T.i32 },
+  tstwo_lde_columns_sharded: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.i32, T.u32], returns: T.i32 },
+  tstwo_scatter_shards: { args: [T.u64, T.i32, T.u64, T.ptr, T.i32, T.i32], returns: T.i32 },
+  tstwo_scatter_join: { args: [], returns: T.i32 },
+  tstwo_lde_commit_multi: { args: [T.ptr, T.i32, T.i32, T.i32, T.ptr, T.u32], returns: T.i32 },
+  tstwo_lde_commit_multi_dev: { args: [T.ptr, T.i32, T.i32, T.i32, T.ptr, T.u32], returns: T.i32 },
 }).symbols;
 
 function check(rc: number): void {
@@ -127,6 +151,21 @@ export function commitTrace(trace: CudaColumn, nCols: number, logSize: number, l
   check(lib.tstwo_lde_commit(trace.dptr, nCols, logSize, logBlowup, tw.handle, cf[0], evals[0], layers[0], ptr(root), QUIRKS));
   void coeffs;
   return { root, coeffs: cf[0], evals: evals[0], layers: layers[0], domain: CanonicCoset.new(ext).circleDomain() };
+}
+
+/** The same commitment over ALL GPUs of the box from this one Bun thread (BASELINE config 3): `devices` = CUDA ordinals, a power
+ * of two dividing nCols.  The trace is a host Uint32Array [nCols][2^logSize]; the library shards it by column, pulls every shard
+ * over its own PCIe link, exchanges the evaluations over NVLink peer memory inside the last FFT pass, builds one Merkle subtree
+ * per device and finishes the top layers on device 0.  The root equals commitTrace()'s bit for bit. */
+let multiDevices = 0;
+export function commitTraceMulti(trace: Uint32Array, nCols: number, logSize: number, logBlowup: number, devices: number[]): Uint8Array {
+  if (multiDevices !== devices.length) {
+    check(lib.tstwo_init_devices(devices.length, ptr(Int32Array.from(devices))));   // slot 0 stays current: single-device calls keep working
+    multiDevices = devices.length;
+  }
+  const root = new Uint8Array(32);
+  check(lib.tstwo_lde_commit_multi(ptr(trace), nCols, logSize, logBlowup, ptr(root), QUIRKS));
+  return root;
 }
 
 // GrindOps for the CUDA backend (backend/cpu/grind.ts:31-42): the nonce search runs on the device, the channel stays on the host.
