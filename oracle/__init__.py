@@ -12,7 +12,7 @@ import subprocess
 import numpy as np
 
 _DIR = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_DIR, "_build", "libtstwo_oracle.so")
+_SO = os.environ.get("TSTWO_ORACLE_SO") or os.path.join(_DIR, "_build", "libtstwo_oracle.so")   # scripts/oracle_asan.sh overrides
 
 P = 2147483647
 u32p = C.POINTER(C.c_uint32)
@@ -21,6 +21,8 @@ u8p = C.POINTER(C.c_uint8)
 
 def build(force: bool = False) -> str:
     src = os.path.join(_DIR, "tstwo_oracle.c")
+    if os.environ.get("TSTWO_ORACLE_SO"):
+        return _SO
     if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
         subprocess.check_call(["make", "-C", _DIR, "-B" if force else "-s"], stdout=subprocess.DEVNULL)
     return _SO

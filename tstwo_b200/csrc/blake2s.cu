@@ -309,6 +309,7 @@ int tstwo_debug_last_leaf_mode(void) { return g_last_leaf; }
 int tstwo_grind(const uint8_t digest[32], uint32_t pow_bits, uint64_t *nonce)
 {
     TS_REQUIRE_INIT();
+    Span span("Grind");
     if (!digest || !nonce || pow_bits > 64) return fail(TSTWO_ERR_BAD_ARG, "bad grind arguments (pow_bits <= 64)");
     Context &c = ctx();
     uint32_t *d_digest = nullptr;
@@ -355,6 +356,7 @@ int tstwo_merkle_commit_layer(int log_size, tstwo_dptr prev_layer, const tstwo_d
 int tstwo_merkle_commit(const tstwo_dptr *cols, const int *col_logs, int n_cols, tstwo_dptr layers, uint8_t root[32])
 {
     TS_REQUIRE_INIT();
+    Span span("Merkle");
     if (n_cols < 0 || !layers) return fail(TSTWO_ERR_BAD_ARG, "bad merkle_commit arguments");
     uint8_t *base = (uint8_t *)layers;
     if (n_cols == 0) {

@@ -1,6 +1,7 @@
 // Shared host-side plumbing for libtstwo_cuda.so: context, error slot, launch accounting.
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>   // header-only NVTX 3: ranges cost nothing unless a profiler is attached
 
 #include <cstdint>
 #include <cstdio>
@@ -52,6 +53,14 @@ struct DeviceScope {            // RAII form
     ~DeviceScope() { ctx_select(prev); }
 };
 int fail(int code, const char *fmt, ...);
+
+// NVTX range for the lifetime of the object; the names are Stwo's tracing spans (Rust text quoted in the reference at
+// packages/core/src/pcs/prover.ts:44,92-97,180,222-226): "Commitment", "Interpolation for commitment", "Extension", "Merkle",
+// "Evaluate columns out of domain", "Grind" -- so that an Nsight timeline of a TStwo host reads like Stwo's own trace
+struct Span {
+    explicit Span(const char *name) { nvtxRangePushA(name); }
+    ~Span() { nvtxRangePop(); }
+};
 
 #define TS_CUDA(expr)                                                                              \
     do {                                                                                           \

@@ -958,6 +958,7 @@ int tstwo_eval_at_point(tstwo_dptr coeffs, int log_size, const uint32_t px[4], c
 int tstwo_eval_at_point_many(const tstwo_dptr *coeffs, int n_polys, int log_size, const uint32_t px[4], const uint32_t py[4], uint32_t *out)
 {
     TS_REQUIRE_INIT();
+    Span span("Evaluate columns out of domain");
     if (log_size < 0 || log_size > 30 || n_polys < 0 || (n_polys && (!out || !coeffs))) return fail(TSTWO_ERR_BAD_ARG, "bad eval_at_point arguments");
     if (n_polys == 0) return 0;
     if (log_size == 0) {

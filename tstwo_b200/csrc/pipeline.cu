@@ -39,11 +39,19 @@ int lde_commit_device(const uint32_t *trace, int n_cols, int log_size, int log_b
     ColSet src = { trace, n, nullptr };
     ColSet cf = coeffs ? ColSet{ coeffs, n, nullptr } : ColSet{ evals, ne, nullptr };   // blowup 0: in place in evals
     ColSet ev = { evals, ne, nullptr };
-    rc = fft_interpolate(src, cf, n_cols, log_size, t, flags);
+    Span commitment("Commitment");
+    {
+        Span s("Interpolation for commitment");
+        rc = fft_interpolate(src, cf, n_cols, log_size, t, flags);
+    }
     if (rc) return rc;
-    rc = fft_evaluate(cf, log_size, ev, n_cols, ext, t, flags);
+    {
+        Span s("Extension");
+        rc = fft_evaluate(cf, log_size, ev, n_cols, ext, t, flags);
+    }
     if (rc) return rc;
     if (layers) {
+        Span s("Merkle");
         const uint8_t *prev = nullptr;
         ColSet none = { nullptr, 0, nullptr };
         for (int log = ext; log >= 0; log--) {
@@ -187,7 +195,9 @@ int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tst
         ev.shard_log = ext - sl;
         ev.shard_bases = dev_bases + 64 * k;
         if (col_groups == 1) {
-            if ((rc = fft_interpolate(src, cfs, nc, log_size, t, flags))) break;
+            { Span s("Interpolation for commitment"); rc = fft_interpolate(src, cfs, nc, log_size, t, flags); }
+            if (rc) break;
+            Span s("Extension");
             rc = fft_evaluate(cfs, log_size, ev, nc, ext, t, flags, &wk);
             break;
         }
