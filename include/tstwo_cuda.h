@@ -127,6 +127,22 @@ int tstwo_fold_line(const tstwo_dptr src[4], int log_size, uint32_t coset_initia
 int tstwo_fold_circle_into_line(const tstwo_dptr dst[4], const tstwo_dptr src[4], int log_size,
                                 uint32_t half_coset_initial_index, const uint32_t alpha[4], tstwo_twiddles tw);
 int tstwo_fri_decompose(const tstwo_dptr src[4], int log_size, const tstwo_dptr g[4], uint32_t lambda[4]);
+/* FriProver.commitInnerLayers (fri.ts:676-716) in ONE call with the Fiat-Shamir transcript kept on the device: per layer
+ * MerkleProver.commit of the 4 coordinate columns (fri.ts:519-531) -> Blake2sMerkleChannel.mix_root (vcs/blake2_merkle.ts:27-32)
+ * -> channel.draw_felt (channel/blake2.ts:172-181) -> fold_line, then fold_circle_into_line of the circle column whose folded
+ * size equals the new layer's (fri.ts:704-711), with the same alpha.  Everything is enqueued back to back; the host waits once.
+ *   first[4], first_log, first_coset_init : the layer evaluation after the first circle fold and its LineDomain coset
+ *   last_log                             : stop when the layer has 2^last_log elements (config.last_layer_domain_size())
+ *   circle_cols[n_circle][4], circle_logs, circle_half_inits : the remaining circle columns, descending sizes
+ *   channel_state[19]                    : in/out  digest[8], n_challenges, n_sent, queue_len, queue[8] (Blake2sChannel state)
+ *   layer_evals[n_layers][4]             : out, evaluation columns of layers 1 .. n_layers (tstwo_malloc'ed: caller frees)
+ *   layer_trees[n_layers]                : out, Merkle tree buffer of layers 0 .. n_layers-1 (root first; caller frees)
+ *   roots[n_layers][32], alphas[n_layers][4], *n_layers : out, n_layers = first_log - last_log */
+int tstwo_fri_commit_layers(const tstwo_dptr first[4], int first_log, uint32_t first_coset_init, int last_log,
+                            const tstwo_dptr *circle_cols, const int *circle_logs, const uint32_t *circle_half_inits, int n_circle,
+                            tstwo_twiddles tw, uint32_t channel_state[19], tstwo_dptr *layer_evals, tstwo_dptr *layer_trees,
+                            uint8_t *roots, uint32_t *alphas, int *n_layers);
+
 
 /* ---- AccumulationOps / QuotientOps  (backend/cpu/accumulation.ts:38-63, backend/cpu/quotients.ts:52-178) ---- */
 int tstwo_accumulate(const tstwo_dptr dst[4], const tstwo_dptr src[4], uint64_t len);

@@ -31,7 +31,8 @@ int tstwo_debug_set_fft_tc(int mask);
 int tstwo_debug_pass_timing(int on);
 int tstwo_debug_pass_times(int max, int *tags, float *ms);
 
-/* Merkle leaf layer: 1 = bulk-copy-fed kernel where it applies (default), 0 = merkle_layer_kernel always */
+/* Merkle: bit 0 = leaf layer by the bulk-copy-fed kernel where it applies (default 1; 0 = merkle_layer_kernel always);
+ * bit 1 set = one launch per node layer instead of the fused bottom layers (merkle_tail_kernel) */
 int tstwo_debug_set_leaf_mode(int mode);
 int tstwo_debug_last_leaf_mode(void);
 

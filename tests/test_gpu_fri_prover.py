@@ -88,3 +88,36 @@ def test_fri_rejects_high_degree_and_bad_inputs(tb, orc):
     bad = tb.SecureEvaluation(tb.CanonicCoset.new(7).circleDomain(), tb.SecureColumnByCoords.from_cpu(list(rnd)))
     with pytest.raises(ValueError, match="invalid degree"):
         FriProver.commit(Blake2sChannel.create(), tb.FriConfig(0, 1, 3), [bad])
+
+
+@pytest.mark.parametrize("with_tree", [False, True])
+def test_one_call_commit_equals_layer_by_layer(tb, orc, with_tree):
+    """tstwo_fri_commit_layers (transcript on the device, one host wait) against the layer-by-layer host loop: same roots, same
+    layers, same channel state afterwards (incl. the queue of base-field draws), for mixed column sizes, with and without a tree."""
+    from tstwo_b200.channel import Blake2sChannel
+    from tstwo_b200.fri import FriProver
+    cols = [secure_column_of_degree(tb, orc, d, 1, 7 * d) for d in (11, 9, 4)]
+    dev_cols = [tb.SecureEvaluation(tb.CanonicCoset.new(log).circleDomain(), tb.SecureColumnByCoords.from_cpu(c)) for log, c in cols]
+    tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(cols[0][0]).half_coset()) if with_tree else None
+    config = tb.FriConfig(1, 1, 4)
+    res = []
+    for per_layer in (True, False):
+        ch = Blake2sChannel.create()
+        ch.mix_u64(7)
+        ch.draw_felt()                               # leaves 4 base-field draws queued: the device must continue from them
+        FriProver.per_layer_calls = per_layer
+        try:
+            pr = FriProver.commit(ch, config, dev_cols, tw)
+        finally:
+            FriProver.per_layer_calls = False
+        res.append((pr, ch))
+    (a, ca), (b, cb) = res
+    assert ca.digest() == cb.digest() and ca.getChannelTime() == cb.getChannelTime() and ca._base_queue == cb._base_queue
+    assert len(a.inner_layers) == len(b.inner_layers) > 0
+    for la, lb in zip(a.inner_layers, b.inner_layers):
+        assert la.merkle_tree.root() == lb.merkle_tree.root()
+        assert la.evaluation.domain().coset() == lb.evaluation.domain().coset()
+        assert all((x == y).all() for x, y in zip(la.evaluation.values.to_cpu(), lb.evaluation.values.to_cpu()))
+        for k in range(len(la.merkle_tree.layers)):
+            assert (la.merkle_tree.layers[k].toCpu() == lb.merkle_tree.layers[k].toCpu()).all()
+    assert a.last_layer_poly.coeffs == b.last_layer_poly.coeffs

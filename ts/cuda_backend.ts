@@ -63,6 +63,7 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   tstwo_lde_columns_sharded: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.i32, T.u32], returns: T.i32 },
   tstwo_scatter_shards: { args: [T.u64, T.i32, T.u64, T.ptr, T.i32, T.i32], returns: T.i32 },
   tstwo_scatter_join: { args: [], returns: T.i32 },
+  tstwo_fri_commit_layers: { args: [T.ptr, T.i32, T.u32, T.i32, T.ptr, T.ptr, T.ptr, T.i32, T.u64, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr], returns: T.i32 },
   tstwo_lde_commit_multi: { args: [T.ptr, T.i32, T.i32, T.i32, T.ptr, T.u32], returns: T.i32 },
   tstwo_lde_commit_multi_dev: { args: [T.ptr, T.i32, T.i32, T.i32, T.ptr, T.u32], returns: T.i32 },
 }).symbols;

@@ -64,6 +64,8 @@ SIGNATURES = {
     "tstwo_fold_line": (C.c_int, [dptrp, C.c_int, C.c_uint32, u32p, dptrp, C.c_uint64]),
     "tstwo_fold_circle_into_line": (C.c_int, [dptrp, dptrp, C.c_int, C.c_uint32, u32p, C.c_uint64]),
     "tstwo_fri_decompose": (C.c_int, [dptrp, C.c_int, dptrp, u32p]),
+    "tstwo_fri_commit_layers": (C.c_int, [dptrp, C.c_int, C.c_uint32, C.c_int, dptrp, intp, u32p, C.c_int, C.c_uint64, u32p, dptrp, dptrp,
+                                           C.POINTER(C.c_uint8), u32p, intp]),
     "tstwo_accumulate": (C.c_int, [dptrp, dptrp, C.c_uint64]),
     "tstwo_accumulate_quotients": (C.c_int, [C.c_int, C.c_uint32, dptrp, C.c_int, u32p, C.c_int, u32p, intp, intp, u32p, dptrp]),
     "tstwo_scatter_shards": (C.c_int, [C.c_uint64, C.c_int, C.c_uint64, dptrp, C.c_int, C.c_int]),

@@ -191,6 +191,32 @@ __global__ void __launch_bounds__(LEAF_ROWS, 5) merkle_leaf_tma_kernel(const __g
     out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
 }
 
+// ---- the bottom of a tree in ONE launch: node layers start_log .. 0 (no column values at those sizes), one CTA.  A layer of a
+// few hundred nodes is one compression latency of work, but as its own launch it costs ~3 us: 10 such launches per tree, 23 trees
+// per FRI commitment of config 4 (FriProver.commit 5.4 -> 5.0 ms, profiles/r02_fri_c4.txt).  Larger layers stay separate launches:
+// a single SM hashes 128 nodes per ~0.7 us, so 4096 nodes alone would take 22 us.  `tree` is the layers buffer, root first.
+constexpr int TAIL_LOG = 9;    // 512 + 256 + ... + 1 compressions: beyond that one SM is compute-bound (a 4096-node layer alone is 22 us)
+__global__ void __launch_bounds__(1024) merkle_tail_kernel(uint4 *__restrict__ tree, int start_log, uint32_t one)
+{
+    for (int log = start_log; log >= 0; log--) {
+        const uint4 *prev = tree + 2ull * ((2ull << log) - 1);
+        uint4 *dst = tree + 2ull * ((1ull << log) - 1);
+        for (uint32_t i = threadIdx.x; i < (1u << log); i += blockDim.x) {
+            uint32_t h[8], m[16];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const uint4 v = prev[4 * i + q];
+                m[4 * q] = v.x; m[4 * q + 1] = v.y; m[4 * q + 2] = v.z; m[4 * q + 3] = v.w;
+            }
+            b2s_init(h);
+            b2s_compress(h, m, 64u, true, one);
+            dst[2 * i] = make_uint4(h[0], h[1], h[2], h[3]);
+            dst[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
+        }
+        __syncthreads();                               // the next layer reads what this CTA just wrote (same block: visible)
+    }
+}
+
 // ---- proof-of-work grind (backend/cpu/grind.ts:31-42): the smallest nonce for which the channel digest after
 // mix_u64(nonce) -- BLAKE2s(digest || LE32(lo) || LE32(hi)), one 40-byte block (channel/blake2.ts:120-151) -- has at least
 // pow_bits trailing zero bits in its low 128 bits (:94-111).  Every thread tries nonces base + k * stride; a batch covers a
@@ -215,6 +241,7 @@ __global__ void __launch_bounds__(256) grind_kernel(const uint32_t *__restrict__
     }
 }
 
+static int g_tail_mode = 1;    // 1: the bottom layers of tstwo_merkle_commit in one launch (merkle_tail_kernel); 0: one launch per layer
 static int g_leaf_mode = 1;    // 1: bulk-copy-fed leaf kernel where it applies; 0: merkle_layer_kernel always (tstwo_debug_set_leaf_mode)
 static int g_last_leaf = -1;
 
@@ -301,9 +328,20 @@ int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, i
 
 using namespace tstwo;
 
+namespace tstwo {
+int merkle_tail(uint8_t *layers, int start_log)
+{
+    if (!g_tail_mode || start_log < 0) return -1;
+    if (start_log > TAIL_LOG) start_log = TAIL_LOG;
+    merkle_tail_kernel<<<1, 1024, 0, ctx().stream>>>((uint4 *)layers, start_log, 1u);
+    ctx().launches++;
+    return cudaGetLastError() == cudaSuccess ? start_log : -1;
+}
+}  // namespace tstwo
+
 extern "C" {
 
-int tstwo_debug_set_leaf_mode(int mode) { g_leaf_mode = mode; return 0; }
+int tstwo_debug_set_leaf_mode(int mode) { g_leaf_mode = mode & 1; g_tail_mode = !(mode & 2); return 0; }
 int tstwo_debug_last_leaf_mode(void) { return g_last_leaf; }
 
 int tstwo_grind(const uint8_t digest[32], uint32_t pow_bits, uint64_t *nonce)
@@ -371,7 +409,15 @@ int tstwo_merkle_commit(const tstwo_dptr *cols, const int *col_logs, int n_cols,
         }
         std::vector<tstwo_dptr> layer_cols((size_t)n_cols);
         const uint8_t *prev = nullptr;
+        int min_log = 31;
+        for (int c = 0; c < n_cols; c++) if (col_logs[c] < min_log) min_log = col_logs[c];
+        // layers below the smallest column are pure node layers: the last TAIL_LOG + 1 of them go out as one launch
+        const int tail_log = min_log - 1 < TAIL_LOG ? min_log - 1 : TAIL_LOG;
         for (int log = max_log; log >= 0; log--) {
+            if (log == tail_log && g_tail_mode) {
+                TS_LAUNCH(merkle_tail_kernel, 1, 1024, 0, (uint4 *)base, tail_log, 1u);
+                break;
+            }
             int k = 0;   // stable order among equal lengths (vcs/prover.ts:21,25)
             for (int c = 0; c < n_cols; c++) if (col_logs[c] == log) layer_cols[k++] = cols[c];
             ColSet cs;

@@ -137,6 +137,9 @@ int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int log_si
 int fft_evaluate(const ColSet &src, int poly_log, const ColSet &dst, int n_cols, int domain_log, const TwiddleTree *t,
                  uint32_t flags, const ColSet *work = nullptr, int pass_select = 0);
 int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, int n_cols, uint8_t *out);
+// node layers start_log .. 0 of the tree buffer `layers` (root first) in one launch; layer start_log + 1 must be there.
+// Returns the layer it started from (start_log clamped to what the kernel takes), or -1 when the fused form is switched off.
+int merkle_tail(uint8_t *layers, int start_log);
 // leaf layer fed in column chunks: absorbs columns [c0, c0 + nc) (given as `cols`) of leaves of total_cols words
 int merkle_leaf_absorb(int log_size, const ColSet &cols, int c0, int nc, int total_cols, uint8_t *leaf_layer);
 // tstwo_shutdown: frees the scratch and the side stream / events pipeline.cu keeps between calls

@@ -26,10 +26,13 @@ __device__ __forceinline__ uint32_t pair_itw2(const uint32_t *tab, int mode, uin
 }
 
 // fri.ts:120-152 / backend/cpu/fri.ts:23-51: out[i] = f0 + alpha f1, (f0, f1) = ibutterfly(f(x), f(-x), 1/x)
-__global__ void fold_line_kernel(CQ4 src, Q4 dst, uint64_t n_out, const uint32_t *itab, int mode, m31::QM alpha)
+// alpha_dev != nullptr: the folding coefficient is read from device memory (written by fri_channel_kernel: the transcript stays
+// on the device between the layers of tstwo_fri_commit_layers)
+__global__ void fold_line_kernel(CQ4 src, Q4 dst, uint64_t n_out, const uint32_t *itab, int mode, m31::QM alpha, const uint32_t *alpha_dev = nullptr)
 {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_out) return;
+    if (alpha_dev) alpha = { alpha_dev[0], alpha_dev[1], alpha_dev[2], alpha_dev[3] };
     uint32_t it2 = pair_itw2(itab, mode, i);
     uint32_t f0[4], f1[4];
 #pragma unroll
@@ -44,10 +47,11 @@ __global__ void fold_line_kernel(CQ4 src, Q4 dst, uint64_t n_out, const uint32_t
 
 // fri.ts:162-192 / backend/cpu/fri.ts:61-92: dst[i] = dst[i] alpha^2 + (alpha f1 + f0), twiddle 1/p.y
 __global__ void fold_circle_kernel(CQ4 src, Q4 dst, uint64_t n_out, const uint32_t *itab, int mode, m31::QM alpha,
-                                   m31::QM alpha_sq)
+                                   m31::QM alpha_sq, const uint32_t *alpha_dev = nullptr)
 {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_out) return;
+    if (alpha_dev) { alpha = { alpha_dev[0], alpha_dev[1], alpha_dev[2], alpha_dev[3] }; alpha_sq = m31::qmul(alpha, alpha); }
     uint32_t it2 = pair_itw2(itab, mode, i);
     uint32_t f0[4], f1[4];
 #pragma unroll
@@ -587,6 +591,68 @@ static int scratch(size_t bytes, uint32_t **out)
     return 0;
 }
 
+// ---- Fiat-Shamir channel on the device (channel/blake2.ts:25-224, vcs/blake2_merkle.ts:27-32), one thread: what
+// FriProver.commitInnerLayers (fri.ts:676-716) does between two layers -- mix_root(root) then draw_felt() -- without a host round
+// trip.  State layout (13 words): digest[8], n_challenges, n_sent, queue_len, then queue[8] (the base-field draws draw_felt keeps
+// between calls, blake2.ts:172-181; NOT cleared by a digest update, as in the reference).
+__device__ void b2s_hash64(const uint32_t m[16], uint32_t out[8])   // unkeyed BLAKE2s-256 of one full 64-byte block (RFC 7693)
+{
+    const uint32_t IV[8] = { 0x6A09E667u, 0xBB67AE85u, 0x3C6EF372u, 0xA54FF53Au, 0x510E527Fu, 0x9B05688Cu, 0x1F83D9ABu, 0x5BE0CD19u };
+    const uint8_t SIG[10][16] = {
+        { 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15 }, { 14, 10, 4, 8, 9, 15, 13, 6, 1, 12, 0, 2, 11, 7, 5, 3 },
+        { 11, 8, 12, 0, 5, 2, 15, 13, 10, 14, 3, 6, 7, 1, 9, 4 }, { 7, 9, 3, 1, 13, 12, 11, 14, 2, 6, 5, 10, 4, 0, 15, 8 },
+        { 9, 0, 5, 7, 2, 4, 10, 15, 14, 1, 11, 12, 6, 8, 3, 13 }, { 2, 12, 6, 10, 0, 11, 8, 3, 4, 13, 7, 5, 15, 14, 1, 9 },
+        { 12, 5, 1, 15, 14, 13, 4, 10, 0, 7, 6, 3, 9, 2, 8, 11 }, { 13, 11, 7, 14, 12, 1, 3, 9, 5, 0, 15, 4, 8, 6, 2, 10 },
+        { 6, 15, 14, 9, 11, 3, 0, 8, 12, 2, 13, 7, 1, 4, 10, 5 }, { 10, 2, 8, 4, 7, 6, 1, 5, 15, 11, 9, 14, 3, 12, 13, 0 } };
+    uint32_t h[8], v[16];
+    for (int i = 0; i < 8; i++) h[i] = IV[i];
+    h[0] ^= 0x01010020u;                               // digest length 32, fanout 1, depth 1
+    for (int i = 0; i < 8; i++) { v[i] = h[i]; v[8 + i] = IV[i]; }
+    v[12] ^= 64u;                                      // t = 64 bytes
+    v[14] = ~v[14];                                    // final block
+    auto rotr = [](uint32_t x, int r) { return (x >> r) | (x << (32 - r)); };
+    for (int r = 0; r < 10; r++) {
+        auto G = [&](int a, int b, int c, int d, int x, int y) {
+            v[a] = v[a] + v[b] + m[SIG[r][x]]; v[d] = rotr(v[d] ^ v[a], 16);
+            v[c] = v[c] + v[d];                v[b] = rotr(v[b] ^ v[c], 12);
+            v[a] = v[a] + v[b] + m[SIG[r][y]]; v[d] = rotr(v[d] ^ v[a], 8);
+            v[c] = v[c] + v[d];                v[b] = rotr(v[b] ^ v[c], 7);
+        };
+        G(0, 4, 8, 12, 0, 1); G(1, 5, 9, 13, 2, 3); G(2, 6, 10, 14, 4, 5); G(3, 7, 11, 15, 6, 7);
+        G(0, 5, 10, 15, 8, 9); G(1, 6, 11, 12, 10, 11); G(2, 7, 8, 13, 12, 13); G(3, 4, 9, 14, 14, 15);
+    }
+    for (int i = 0; i < 8; i++) out[i] = h[i] ^ v[i] ^ v[8 + i];
+}
+constexpr int CH_WORDS = 19;
+__global__ void fri_channel_kernel(uint32_t *state, const uint32_t *root, uint32_t *alpha_out, uint32_t *root_out)
+{
+    if (threadIdx.x || blockIdx.x) return;
+    uint32_t m[16], d[8];
+    for (int i = 0; i < 8; i++) { m[i] = state[i]; m[8 + i] = root[i]; root_out[i] = root[i]; }
+    b2s_hash64(m, d);                                  // Blake2sMerkleChannel.mix_root: digest = H(digest || root)
+    for (int i = 0; i < 8; i++) state[i] = d[i];
+    state[8] += 1;                                     // updateDigest: n_challenges++, n_sent = 0
+    state[9] = 0;
+    uint32_t qlen = state[10];
+    while (qlen < 4) {                                 // draw_felt -> _draw_base_felts (retry when a word is >= 2P)
+        for (;;) {
+            for (int i = 0; i < 8; i++) m[i] = state[i];
+            m[8] = state[9];
+            for (int i = 9; i < 16; i++) m[i] = 0;
+            state[9] += 1;
+            b2s_hash64(m, d);
+            bool ok = true;
+            for (int i = 0; i < 8; i++) ok = ok && d[i] < 2u * m31::P;
+            if (ok) break;
+        }
+        for (int i = 0; i < 8; i++) state[11 + qlen + i] = d[i] >= m31::P ? d[i] - m31::P : d[i];
+        qlen += 8;
+    }
+    for (int i = 0; i < 4; i++) alpha_out[i] = state[11 + i];
+    for (uint32_t i = 4; i < qlen; i++) state[11 + i - 4] = state[11 + i];
+    state[10] = qlen - 4;
+}
+
 // ---- tstwo_debug_field_op: the device field arithmetic of m31.cuh, one operation per thread, so that the reference's
 // golden vectors (test-vectors/*.json, replayed by test-equivalence/fields/*.test.ts) run on the DEVICE code one to one
 __global__ void field_op_kernel(int field, int op, const uint32_t *a, const uint32_t *b, uint32_t *out, int n)
@@ -713,6 +779,104 @@ int tstwo_fold_circle_into_line(const tstwo_dptr dst[4], const tstwo_dptr src[4]
     host::qst(a2v, a2);
     TS_LAUNCH(fold_circle_kernel, (unsigned)((n_out + 255) / 256), 256, 0, s, d, n_out, itab, mode, to_dev(alpha), to_dev(a2v));
     return 0;
+}
+
+// FriProver.commitInnerLayers (fri.ts:676-716) in ONE call, the transcript on the device: per layer  Merkle tree of the 4 coordinate
+// columns -> mix_root -> draw_felt -> fold_line (-> fold_circle_into_line of the circle column whose folded size matches), all
+// enqueued back to back; the host waits once at the end.  Same transcript, same layers as the per-layer calls.
+int tstwo_fri_commit_layers(const tstwo_dptr first[4], int first_log, uint32_t first_coset_init, int last_log,
+                            const tstwo_dptr *circle_cols, const int *circle_logs, const uint32_t *circle_half_inits, int n_circle, tstwo_twiddles tw,
+                            uint32_t channel_state[19], tstwo_dptr *layer_evals, tstwo_dptr *layer_trees, uint8_t *roots,
+                            uint32_t *alphas, int *n_layers_out)
+{
+    TS_REQUIRE_INIT();
+    if (!first || first_log < 1 || first_log > 30 || last_log < 0 || !channel_state || !layer_evals || !layer_trees || !roots || !alphas || !n_layers_out ||
+        n_circle < 0 || (n_circle && (!circle_cols || !circle_logs || !circle_half_inits)))
+        return fail(TSTWO_ERR_BAD_ARG, "bad fri_commit_layers arguments");
+    const int n_layers = first_log > last_log ? first_log - last_log : 0;
+    *n_layers_out = n_layers;
+    if (n_layers == 0) return 0;
+    Context &c = ctx();
+    uint32_t *d_state = nullptr, *d_alpha = nullptr, *d_roots = nullptr;
+    TS_CUDA(cudaMallocAsync(&d_state, CH_WORDS * 4, c.stream));
+    TS_CUDA(cudaMallocAsync(&d_alpha, (size_t)n_layers * 16, c.stream));
+    TS_CUDA(cudaMallocAsync(&d_roots, (size_t)n_layers * 32, c.stream));
+    auto cleanup = [&]() { cudaFreeAsync(d_state, c.stream); cudaFreeAsync(d_alpha, c.stream); cudaFreeAsync(d_roots, c.stream); };
+    auto body = [&]() -> int {
+        TS_CUDA(cudaMemcpyAsync(d_state, channel_state, CH_WORDS * 4, cudaMemcpyHostToDevice, c.stream));
+        tstwo_dptr cur[4] = { first[0], first[1], first[2], first[3] };
+        uint32_t coset = first_coset_init & 0x7fffffffu;
+        int pending = 0;
+        const uint32_t zero_alpha[4] = { 0, 0, 0, 0 };
+        for (int l = 0; l < n_layers; l++) {
+            const int log = first_log - l;
+            const uint64_t n = 1ull << log;
+            // Merkle tree of this layer's evaluation
+            tstwo_dptr tree;
+            int rc = tstwo_malloc(32ull * (2 * n - 1), &tree);
+            if (rc) return rc;
+            layer_trees[l] = tree;
+            int logs[4] = { log, log, log, log };
+            if ((rc = tstwo_merkle_commit(cur, logs, 4, tree, nullptr))) return rc;
+            // mix_root + draw_felt on the device
+            TS_LAUNCH(fri_channel_kernel, 1, 32, 0, d_state, (const uint32_t *)tree, d_alpha + 4 * l, d_roots + 8 * l);
+            // fold_line into fresh columns (alpha read from device memory)
+            tstwo_dptr nxt[4];
+            for (int k = 0; k < 4; k++) {
+                if ((rc = tstwo_malloc(4ull * (n / 2), &nxt[k]))) return rc;
+                layer_evals[4 * l + k] = nxt[k];
+            }
+            {
+                CQ4 s4; Q4 d4;
+                for (int k = 0; k < 4; k++) { s4.c[k] = (const uint32_t *)cur[k]; d4.c[k] = (uint32_t *)nxt[k]; }
+                TwiddleTree *t = tw ? get_tree(tw) : nullptr;
+                if (tw && !t) return fail(TSTWO_ERR_BAD_ARG, "unknown twiddle tree handle");
+                const uint32_t *itab;
+                const uint64_t n_out = n / 2;
+                if (t && is_doubling_of(coset, log, t)) itab = t->itw2 + ((1ull << t->root_log) - (1ull << log));
+                else {
+                    // every layer needs its own table while the launches are in flight: carve them from one scratch block
+                    uint32_t *tmp;
+                    if ((rc = scratch((4ull << first_log) * 4, &tmp))) return rc;
+                    tmp += (2ull << first_log) - (2ull << log);
+                    if ((rc = launch_coset_points(tmp, 0, coset, log, log - 1))) return rc;
+                    itab = tmp;
+                }
+                TS_LAUNCH(fold_line_kernel, (unsigned)((n_out + 255) / 256), 256, 0, s4, d4, n_out, itab, 0, to_dev(zero_alpha), d_alpha + 4 * l);
+            }
+            coset = (coset * 2u) & 0x7fffffffu;
+            // a circle column whose folded size equals the new layer joins it, with the same alpha (fri.ts:704-711)
+            if (pending < n_circle && circle_logs[pending] == log) {
+                const int clog = circle_logs[pending], half_log = clog - 1;
+                const uint32_t half_init = circle_half_inits[pending] & 0x7fffffffu;
+                const uint64_t n_out = 1ull << half_log;
+                CQ4 s4; Q4 d4;
+                for (int k = 0; k < 4; k++) { s4.c[k] = (const uint32_t *)circle_cols[4 * pending + k]; d4.c[k] = (uint32_t *)nxt[k]; }
+                TwiddleTree *t = tw ? get_tree(tw) : nullptr;
+                const uint32_t *itab;
+                int mode = 0;
+                if (t && half_log >= 2 && is_doubling_of(half_init, half_log, t)) { itab = t->itw2 + ((1ull << t->root_log) - (1ull << half_log)); mode = 1; }
+                else {
+                    uint32_t *tmp;
+                    if ((rc = scratch((4ull << first_log) * 4, &tmp))) return rc;
+                    tmp += (2ull << first_log) + (2ull << first_log) - (2ull << clog);     // second half of the scratch block
+                    if ((rc = launch_coset_points(tmp, 1, half_init, half_log, half_log))) return rc;
+                    itab = tmp;
+                }
+                TS_LAUNCH(fold_circle_kernel, (unsigned)((n_out + 255) / 256), 256, 0, s4, d4, n_out, itab, mode, to_dev(zero_alpha), to_dev(zero_alpha), d_alpha + 4 * l);
+                pending++;
+            }
+            for (int k = 0; k < 4; k++) cur[k] = nxt[k];
+        }
+        TS_CUDA(cudaMemcpyAsync(channel_state, d_state, CH_WORDS * 4, cudaMemcpyDeviceToHost, c.stream));
+        TS_CUDA(cudaMemcpyAsync(alphas, d_alpha, (size_t)n_layers * 16, cudaMemcpyDeviceToHost, c.stream));
+        TS_CUDA(cudaMemcpyAsync(roots, d_roots, (size_t)n_layers * 32, cudaMemcpyDeviceToHost, c.stream));
+        TS_CUDA(cudaStreamSynchronize(c.stream));
+        return 0;
+    };
+    const int rc = body();
+    cleanup();
+    return rc;
 }
 
 int tstwo_fri_decompose(const tstwo_dptr src[4], int log_size, const tstwo_dptr g[4], uint32_t lambda[4])

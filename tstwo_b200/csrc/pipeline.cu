@@ -55,6 +55,7 @@ int lde_commit_device(const uint32_t *trace, int n_cols, int log_size, int log_b
         const uint8_t *prev = nullptr;
         ColSet none = { nullptr, 0, nullptr };
         for (int log = ext; log >= 0; log--) {
+            if (log < ext && log <= 9 && merkle_tail(layers, log) == log) break;   // the bottom layers in one launch
             uint8_t *dst = layers + 32ull * ((1ull << log) - 1);
             rc = merkle_commit_layer(log, prev, log == ext ? ev : none, log == ext ? n_cols : 0, dst);
             if (rc) return rc;
@@ -326,6 +327,7 @@ int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, 
         const uint8_t *prev = (const uint8_t *)layers + 32ull * ((1ull << ext) - 1);
         ColSet none = { nullptr, 0, nullptr };
         for (int log = ext - 1; log >= 0; log--) {
+            if (log <= 9 && merkle_tail((uint8_t *)layers, log) == log) break;
             uint8_t *dst = (uint8_t *)layers + 32ull * ((1ull << log) - 1);
             rc = merkle_commit_layer(log, prev, none, 0, dst);
             if (rc) return rc;

@@ -17,7 +17,7 @@ from ._lib import check, dptr_array
 from . import _lib
 from .backend import (_L, CudaBackend, FriConfig, LineEvaluation, MerkleDecommitment, MerkleProver, SecureColumnByCoords, SecureEvaluation,
                       TwiddleTree, fold_circle_into_line, fold_line)
-from .channel import Blake2sMerkleChannel
+from .channel import Blake2sChannel, Blake2sMerkleChannel
 from .circle import Coset, LineDomain
 
 P = 2147483647
@@ -255,7 +255,13 @@ class FriProver:
     @staticmethod
     def _commit_inner_layers(channel, config, columns, twiddles):
         """fri.ts:676-716 with the channel in place of the placeholders; a circle column joins the layer whose size its
-        folded size equals and is only consumed then (Stwo's `next_if`; the TS loop drops a non-matching column)."""
+        folded size equals and is only consumed then (Stwo's `next_if`; the TS loop drops a non-matching column).
+        The circle column is folded with the alpha of the layer it joins, as the reference's text does (fri.ts:704-711,
+        a port of Stwo 0.1.1's commit_inner_layers).
+
+        The whole loop is ONE library call (tstwo_fri_commit_layers): trees, mix_root, draw_felt and folds run back to back
+        on the device with the transcript in device memory; the channel object is updated from the state that comes back.
+        FriProver.per_layer_calls = True takes the layer-by-layer form (one host round trip per layer) instead."""
         folded_size = lambda v: v.len() >> CIRCLE_TO_LINE_FOLD_STEP
         first_log = folded_size(columns[0]).bit_length() - 1
         layer_evaluation = LineEvaluation.newZero(LineDomain.new(Coset.half_odds(first_log)))
@@ -263,6 +269,8 @@ class FriProver:
         layers: List[FriInnerLayerProver] = []
         alpha = channel.draw_felt()
         fold_circle_into_line(layer_evaluation, pending.pop(0), alpha, twiddles)
+        if not FriProver.per_layer_calls and isinstance(channel, Blake2sChannel):
+            return FriProver._commit_inner_layers_device(channel, config, layer_evaluation, pending, twiddles)
         while layer_evaluation.len() > config.last_layer_domain_size():
             layer = FriInnerLayerProver.new(layer_evaluation)
             Blake2sMerkleChannel.mix_root(channel, layer.merkle_tree.root())
@@ -274,6 +282,59 @@ class FriProver:
         if pending:
             raise ValueError("columns left over after the last layer")
         return layers, layer_evaluation
+
+    per_layer_calls = False
+
+    @staticmethod
+    def _commit_inner_layers_device(channel, config, layer_evaluation, pending, twiddles):
+        import ctypes as C
+        from . import _lib
+        from .backend import CudaColumn, SecureColumnByCoords, MerkleProver
+        L = _lib.load()
+        first_log = layer_evaluation.len().bit_length() - 1
+        last_log = config.last_layer_domain_size().bit_length() - 1
+        n_layers = max(0, first_log - last_log)
+        folded_log = lambda v: v.domain.logSize() - CIRCLE_TO_LINE_FOLD_STEP
+        if any(folded_log(c) >= first_log or folded_log(c) < last_log for c in pending):
+            raise ValueError("columns left over after the last layer")
+        if n_layers == 0:
+            if pending:
+                raise ValueError("columns left over after the last layer")
+            return [], layer_evaluation
+        n_c = len(pending)
+        cptrs = _lib.dptr_array([col.ptr for c in pending for col in c.values.columns])
+        clogs = (C.c_int * max(1, n_c))(*[c.domain.logSize() for c in pending])
+        cinits = _lib.u32_array([c.domain.halfCoset.initial_index.value for c in pending])
+        st = channel._digest + channel._n_challenges.to_bytes(4, "little") + channel._n_sent.to_bytes(4, "little")
+        q = list(channel._base_queue)
+        state = (C.c_uint32 * 19)(*(list(int.from_bytes(st[4 * i:4 * i + 4], "little") for i in range(10)) + [len(q)] + q + [0] * (8 - len(q))))
+        evals = (C.c_uint64 * (4 * n_layers))()
+        trees = (C.c_uint64 * n_layers)()
+        roots = (C.c_uint8 * (32 * n_layers))()
+        alphas = (C.c_uint32 * (4 * n_layers))()
+        n_out = C.c_int()
+        dom = layer_evaluation.domain()
+        _lib.check(L.tstwo_fri_commit_layers(layer_evaluation.values.ptrs(), first_log, dom.coset().initial_index.value, last_log,
+                                             cptrs, clogs, cinits, n_c, twiddles.handle if twiddles is not None else 0, state,
+                                             evals, trees, roots, alphas, C.byref(n_out)))
+        assert n_out.value == n_layers
+        # the transcript continues from the device's state
+        channel._digest = b"".join(int(state[i]).to_bytes(4, "little") for i in range(8))
+        channel._n_challenges, channel._n_sent = int(state[8]), int(state[9])
+        channel._base_queue = [int(state[11 + i]) for i in range(int(state[10]))]
+        layers: List[FriInnerLayerProver] = []
+        cur = layer_evaluation
+        coset = dom.coset()
+        for l in range(n_layers):
+            log = first_log - l
+            buf = CudaColumn(int(trees[l]), 8 * ((2 << log) - 1))
+            tree_layers = [buf.slice(8 * ((1 << k) - 1), 8 << k) for k in range(log + 1)]
+            layers.append(FriInnerLayerProver(cur, MerkleProver(tree_layers, bytes(roots[32 * l:32 * l + 32]))))
+            coset = coset.double()
+            cols = [CudaColumn(int(evals[4 * l + k]), 1 << (log - 1)) for k in range(4)]
+            cur = LineEvaluation.new(LineDomain.new(coset), SecureColumnByCoords(cols))
+        FriProver.last_alphas = [[int(alphas[4 * l + k]) for k in range(4)] for l in range(n_layers)]
+        return layers, cur
 
     @staticmethod
     def _commit_last_layer(channel, config, evaluation: LineEvaluation) -> LinePoly:
