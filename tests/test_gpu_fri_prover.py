@@ -121,3 +121,28 @@ def test_one_call_commit_equals_layer_by_layer(tb, orc, with_tree):
         for k in range(len(la.merkle_tree.layers)):
             assert (la.merkle_tree.layers[k].toCpu() == lb.merkle_tree.layers[k].toCpu()).all()
     assert a.last_layer_poly.coeffs == b.last_layer_poly.coeffs
+
+
+@pytest.mark.parametrize("log_degrees,log_last,blow,n_queries", [((8, 6, 5), 2, 1, 6), ((9, 4), 0, 2, 5), ((7, 3), 2, 1, 4)])
+def test_device_proof_is_accepted_by_the_host_verifier(tb, orc, log_degrees, log_last, blow, n_queries):
+    """The device FriProver's proof (columns of several degrees, one joining the last layer) through oracle/fri_verify.py: the
+    transcript, every layer's Merkle decommitment, the fold arithmetic and the last-layer polynomial are consistent."""
+    from oracle.fri_verify import fri_verify
+    from tstwo_b200.channel import Blake2sChannel
+    from tstwo_b200.fri import FriProver
+    cols = [secure_column_of_degree(tb, orc, d, blow, 7 * d + blow) for d in log_degrees]
+    channel, vchannel = Blake2sChannel.create(), orc.Channel()
+    channel.mix_u64(99); vchannel.mix_u64(99)
+    dev_cols = [tb.SecureEvaluation(tb.CanonicCoset.new(log).circleDomain(), tb.SecureColumnByCoords.from_cpu(c)) for log, c in cols]
+    prover = FriProver.commit(channel, tb.FriConfig(log_last, blow, n_queries), dev_cols)
+    proof, by_log = prover.decommit(channel)
+    layers = [(l.fri_witness, (l.decommitment.hashWitness, list(l.decommitment.columnWitness)), l.commitment)
+              for l in [proof.first_layer] + proof.inner_layers]
+    max_log = cols[0][0]
+    evals = [[[int(c[p]) for c in col] for p in by_log[log]] for log, col in cols]
+    alphas = fri_verify(orc, vchannel, log_last, blow, [log for log, _ in cols], layers, proof.last_layer_poly.coeffs,
+                        by_log[max_log], evals)
+    assert len(alphas) == 1 + len(proof.inner_layers)
+    # the verifier's transcript ends where the prover's was before it drew the queries: same query positions
+    from tstwo_b200.fri import Queries
+    assert Queries.generate(vchannel, max_log, n_queries).positions == by_log[max_log]
