@@ -50,6 +50,8 @@ def parse():
                     help="N > 1: 'peer' = last FFT pass stores into the peers' leaf buffers over NVLink; 'nccl' = all-to-all")
     ap.add_argument("--overlap", default="auto", help="N > 1, --exchange peer: 'groups,peer_sms' = column groups and SMs given to the "
                     "NVLink-bound pass running beside the next group's transforms; 'off' = one group; 'auto' = per world size")
+    ap.add_argument("--fence", default="flags", choices=["flags", "nccl"],
+                    help="N > 1, --exchange peer: cross-rank ordering by release/acquire flags in peer memory (default) or NCCL collectives")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample-cols", type=int, default=0, help="columns of the CPU legs (0 = all of --cols: the whole config)")
     ap.add_argument("--no-extras", action="store_true", help="skip the config 4 (FRI) and config 5 (prove) timings")
@@ -370,13 +372,18 @@ def run_cuda(args):
             ov = OVERLAP_AUTO.get(world) if args.overlap == "auto" else None if args.overlap == "off" else tuple(int(x) for x in args.overlap.split(","))
             if args.exchange == "ce":
                 ov = None
-            sc = PeerShardedCommit(local, stream, n_cols, log, blow, overlap=ov)
+            sc = PeerShardedCommit(local, stream, n_cols, log, blow, overlap=ov, fence=args.fence)
         else:
             sc = ShardedCommit(CudaShardOps(local, stream), n_cols, log, blow)
         trace_flat = trace.view(-1)
         holder = {}
 
+        # device-resident steps are enqueued back to back (no host synchronisation inside the timed region: the ranks order
+        # themselves with flags in peer memory); the root is read once after the loop
         def step():
+            if args.exchange == "peer":
+                sc.step(trace_flat, read_root=False)
+                return
             r = sc.step_pipelined(trace_flat, args.chunks) if args.exchange == "ce" else sc.step(trace_flat)
             if r is not None:
                 holder["root"] = r
@@ -426,6 +433,8 @@ def run_cuda(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     value = n_cols * n / (ms * 1e-3)
+    if world > 1 and args.exchange == "peer" and rank == 0:
+        holder["root"] = sc.root_bytes()
     root_hex = bytes(root).hex() if world == 1 else (holder.get("root", b"").hex() if rank == 0 else "")
 
     # ---- per-rank phase breakdown (N > 1, fused peer stores): CUDA events at the phase boundaries, min / max over ranks, and
@@ -439,7 +448,7 @@ def run_cuda(args):
         for _ in range(6):
             recs.append(sc.step_phases(trace_flat))
         torch.cuda.synchronize()
-        names = ["lde_and_peer_stores", "fence_all_reduce", "leaf_layer_and_subtree", "root_gather_and_top_layers"]
+        names = ["lde_and_peer_stores", "fence", "leaf_layer_and_subtree", "root_gather_and_top_layers"]
         tot = [sum(r[i].elapsed_time(r[i + 1]) for r in recs) / len(recs) for i in range(4)]
         t = torch.tensor(tot, device=dev, dtype=torch.float64)
         mx, mn = t.clone(), t.clone()
@@ -610,6 +619,8 @@ def run_cuda(args):
                        "l2": "inputs (%.1f GiB) and outputs exceed the 126 MB L2; no flush needed" % (n_cols * n * 4 / 2**30),
                        "parallelism": "1 GPU" if world == 1 else (f"column-sharded LDE, last FFT pass stores rows to their owner over NVLink peer memory -> row-sharded Merkle x{world}"
                                                                        if args.exchange == "peer" else f"column-sharded LDE -> NCCL all-to-all -> row-sharded Merkle x{world}")},
+            **({"fence": ("release/acquire flags in peer memory (tstwo_peer_signal / _wait / _put), no collective and no host synchronisation inside a step"
+                          if args.fence == "flags" else "NCCL all-reduce + all-gather")} if world > 1 and args.exchange == "peer" else {}),
             "gpu_launches": launches, "clocks": clocks, "root": root_hex, "root_matches_oracle_checked_root": root_hex == BENCH_ROOT if (n_cols, log, blow) == (N_COLS, LOG_SIZE, LOG_BLOWUP) else None,
             "sass_patch": sass_patch,
         }

@@ -206,6 +206,18 @@ int tstwo_scatter_join(void);
 int tstwo_ipc_export(tstwo_dptr ptr, uint8_t handle[64]);
 int tstwo_ipc_import(const uint8_t handle[64], tstwo_dptr *out);
 int tstwo_ipc_close(tstwo_dptr ptr);
+/* Cross-device fences WITHOUT a collective: 32-bit flags in peer-mapped device memory (CUDA IPC or peer access over NVLink),
+ * written with st.release.sys and polled with ld.acquire.sys by one-warp kernels on the library's stream.  They replace the
+ * all-reduce / all-gather that only ordered the steps of the exchange above (vcs/prover.ts:13-30 is one tree: the ranks must agree
+ * on "all rows have arrived" and "all leaves are hashed").  Values are step counters compared in wrap-around order.
+ *   tstwo_peer_signal  once everything enqueued so far on the library's stream has completed, store `value` to the n words
+ *                      flag_addrs[i] (n <= 64; typically one word in every peer's flag block);
+ *   tstwo_peer_wait    the library's stream waits until each of the n words at `flags` (n <= 64, LOCAL device memory) has reached
+ *                      `value`; traps after timeout_ms (0 = 4000) instead of hanging the device when a peer never arrives;
+ *   tstwo_peer_put     copy n_words (<= 1024) from src to dst (a peer address), then signal flag_addr = value. */
+int tstwo_peer_signal(const tstwo_dptr *flag_addrs, int n, uint32_t value);
+int tstwo_peer_wait(tstwo_dptr flags, int n, uint32_t value, uint32_t timeout_ms);
+int tstwo_peer_put(tstwo_dptr dst, tstwo_dptr src, int n_words, tstwo_dptr flag_addr, uint32_t value);
 /* Same, but the trace lives in HOST memory (pinned or pageable): host->device copies are pipelined with the
  * kernels inside the call; only the root comes back. */
 int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,

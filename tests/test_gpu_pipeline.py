@@ -299,3 +299,34 @@ def test_shutdown_releases_side_streams_and_reinit_works():
     """ % root)
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "reinit ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_peer_flags_signal_wait_put(tb):
+    """tstwo_peer_signal / _wait / _put on one device (the flag block and the "peer" are local memory): the wait returns once
+    every flag has reached the value, in wrap-around order, and put delivers its words before its flag; twiddle trees freed and
+    asked for again come back without being rebuilt (spare list) with identical tables."""
+    from tstwo_b200 import _lib
+    L, chk = _lib.load(), _lib.check
+    blk = tb.CudaColumn.zeros(64)
+    for value in (1, 2, 0xFFFFFFFF, 3):                       # 0xFFFFFFFF -> 3 wraps: (int32)(3 - 0xFFFFFFFF) = 4 >= 0
+        chk(L.tstwo_peer_signal(_lib.dptr_array([blk.ptr + 4 * i for i in range(5)]), 5, value))
+        chk(L.tstwo_peer_wait(blk.ptr, 5, value, 2000))
+        chk(L.tstwo_sync())
+        assert list(blk.toCpu()[:6]) == [value] * 5 + [0]
+    chk(L.tstwo_peer_wait(blk.ptr, 5, 2, 2000))               # already past 2 (wrap-around order): returns at once
+    src = tb.CudaColumn.from_cpu(np.arange(100, 108, dtype=np.uint32))
+    chk(L.tstwo_peer_put(blk.ptr + 4 * 16, src.ptr, 8, blk.ptr + 4 * 40, 9))
+    chk(L.tstwo_peer_wait(blk.ptr + 4 * 40, 1, 9, 2000))
+    chk(L.tstwo_sync())
+    got = blk.toCpu()
+    assert list(got[16:24]) == list(range(100, 108)) and got[40] == 9
+    assert L.tstwo_peer_signal(None, 1, 1) != 0 and L.tstwo_peer_wait(blk.ptr, 65, 1, 0) != 0
+    # spare twiddle trees
+    coset = tb.CanonicCoset.new(12).half_coset()
+    t1 = tb.CudaBackend.precomputeTwiddles(coset)
+    a = t1.twiddles.toCpu().copy()
+    n0 = L.tstwo_launch_count()
+    del t1
+    t2 = tb.CudaBackend.precomputeTwiddles(coset)
+    assert L.tstwo_launch_count() == n0, "a freed tree of the same coset is reused, not rebuilt"
+    assert (t2.twiddles.toCpu() == a).all()

@@ -34,6 +34,9 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   tstwo_ipc_export: { args: [T.u64, T.ptr], returns: T.i32 },
   tstwo_ipc_import: { args: [T.ptr, T.ptr], returns: T.i32 },
   tstwo_ipc_close: { args: [T.u64], returns: T.i32 },
+  tstwo_peer_signal: { args: [T.ptr, T.i32, T.u32], returns: T.i32 },
+  tstwo_peer_wait: { args: [T.u64, T.i32, T.u32, T.u32], returns: T.i32 },
+  tstwo_peer_put: { args: [T.u64, T.u64, T.i32, T.u64, T.u32], returns: T.i32 },
   // decommitment witnesses, proof of work, Stwo-correct DEEP quotients (callers: MerkleProver.decommit, FriProver.decommit, prove_values)
   tstwo_gather_words: { args: [T.ptr, T.i32, T.i32, T.ptr], returns: T.i32 },
   tstwo_grind: { args: [T.ptr, T.u32, T.ptr], returns: T.i32 },

@@ -82,6 +82,9 @@ SIGNATURES = {
     "tstwo_ipc_export": (C.c_int, [dptr, C.POINTER(C.c_uint8)]),
     "tstwo_ipc_import": (C.c_int, [C.POINTER(C.c_uint8), C.POINTER(C.c_uint64)]),
     "tstwo_ipc_close": (C.c_int, [dptr]),
+    "tstwo_peer_signal": (C.c_int, [C.POINTER(C.c_uint64), C.c_int, C.c_uint32]),
+    "tstwo_peer_wait": (C.c_int, [dptr, C.c_int, C.c_uint32, C.c_uint32]),
+    "tstwo_peer_put": (C.c_int, [dptr, dptr, C.c_int, dptr, C.c_uint32]),
     "tstwo_lde_commit_host": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptr, dptr,
                                         C.POINTER(C.c_uint8), C.c_uint32]),
 }

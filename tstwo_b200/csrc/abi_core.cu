@@ -149,6 +149,22 @@ int launch_coset_points(uint32_t *out2, int which, uint32_t init, int step_log, 
 
 static std::mutex g_tree_mu;
 static std::unordered_map<uint64_t, TwiddleTree *> g_trees;
+// Freed trees are kept (at most TW_SPARE_MAX, oldest dropped first) and handed out again by tstwo_twiddles_precompute for the same
+// (device, coset): a prover that builds the tree of a domain inside every prove() (DomainEvaluationAccumulator.finalize,
+// air/accumulator.ts:189-238) then pays neither the table kernel nor the device-wide synchronisation of cudaFree each time
+// (15 ms of config 5's 35 ms prove()).  The tables are read-only, so reuse while earlier kernels still read them is safe.
+static std::vector<TwiddleTree *> g_spare_trees;
+constexpr size_t TW_SPARE_MAX = 4;
+static void drop_spare_trees_locked()
+{
+    for (TwiddleTree *t : g_spare_trees) {
+        if (g_ctxs[t->slot].ready) cudaSetDevice(g_ctxs[t->slot].device);
+        cudaFree(t->tw);
+        delete t;
+    }
+    g_spare_trees.clear();
+    if (g_ctxs[g_cur].ready) cudaSetDevice(g_ctxs[g_cur].device);
+}
 static uint64_t g_next_tree = 1;
 
 TwiddleTree *get_tree(tstwo_twiddles h)
@@ -297,6 +313,7 @@ int tstwo_shutdown(void)
             delete kv.second;
         }
         g_trees.clear();
+        drop_spare_trees_locked();
     }
     scatter_release();
     for (int i = MAX_SLOTS - 1; i >= 0; i--) shutdown_slot(i);
@@ -414,8 +431,13 @@ int tstwo_free(tstwo_dptr p)
 int tstwo_mem_trim(void)
 {
     TS_REQUIRE_INIT();
-    std::lock_guard<std::mutex> lock(g_alloc_mu);
-    release_cached_blocks();
+    {
+        std::lock_guard<std::mutex> lock(g_alloc_mu);
+        release_cached_blocks();
+    }
+    TS_CUDA(cudaStreamSynchronize(ctx().stream));
+    std::lock_guard<std::mutex> lk(g_tree_mu);
+    drop_spare_trees_locked();
     return 0;
 }
 int tstwo_memset_zero(tstwo_dptr p, uint64_t bytes)
@@ -617,6 +639,19 @@ int tstwo_twiddles_precompute(uint32_t init, int log, tstwo_twiddles *out)
 {
     TS_REQUIRE_INIT();
     if (!out || log < 0 || log > 30) return fail(TSTWO_ERR_BAD_ARG, "bad twiddle request (log %d)", log);
+    {
+        std::lock_guard<std::mutex> lk(g_tree_mu);
+        for (size_t i = 0; i < g_spare_trees.size(); i++) {
+            TwiddleTree *sp = g_spare_trees[i];
+            if (sp->slot == ctx().slot && sp->root_init == (init & 0x7fffffffu) && sp->root_log == log) {
+                g_spare_trees.erase(g_spare_trees.begin() + (long)i);
+                uint64_t h = g_next_tree++;
+                g_trees[h] = sp;
+                *out = h;
+                return 0;
+            }
+        }
+    }
     uint64_t n = 1ull << log;
     uint32_t *buf = nullptr;
     cudaError_t e = cudaMalloc(&buf, n * 4 * 4);
@@ -635,13 +670,22 @@ int tstwo_twiddles_free(tstwo_twiddles h)
     TS_REQUIRE_INIT();
     TwiddleTree *t = get_tree(h);
     if (!t) return fail(TSTWO_ERR_BAD_ARG, "unknown twiddle tree handle");
-    TS_CUDA(cudaStreamSynchronize(ctx().stream));
-    TS_CUDA(cudaFree(t->tw));
+    TwiddleTree *victim = nullptr;
     {
         std::lock_guard<std::mutex> lk(g_tree_mu);
         g_trees.erase(h);
+        g_spare_trees.push_back(t);
+        if (g_spare_trees.size() > TW_SPARE_MAX) { victim = g_spare_trees.front(); g_spare_trees.erase(g_spare_trees.begin()); }
     }
-    delete t;
+    if (victim) {
+        const int back = ctx().slot;
+        if (victim->slot != back) ctx_select(victim->slot);
+        cudaStreamSynchronize(ctx().stream);           // kernels enqueued earlier may still read the tables
+        cudaError_t e = cudaFree(victim->tw);
+        delete victim;
+        if (ctx().slot != back) ctx_select(back);
+        TS_CUDA(e);
+    }
     return 0;
 }
 int tstwo_twiddles_info(tstwo_twiddles h, uint32_t *root_init, int *root_log, tstwo_dptr *tw, tstwo_dptr *itw)

@@ -515,28 +515,55 @@ __global__ void __launch_bounds__(QM_WARPS * 32, 3) widefib_mma_kernel(int trace
     }
 }
 
-// eval_at_point (backend/cpu/circle.ts:52-69, poly/utils.ts:36-59 fold): bottom-up pairwise folding, 4 levels
-// (16 values) per thread.  Level l combines (w[2k], w[2k+1]) -> w[2k] + f_l w[2k+1]; f_0 = y, f_1 = x, f_2 = pi(x)...
+// eval_at_point (backend/cpu/circle.ts:52-69, poly/utils.ts:36-59 fold).  The reference folds bottom-up: level l combines
+// (w[2k], w[2k+1]) -> w[2k] + f_l w[2k+1] with f_0 = y, f_1 = x, f_2 = pi(x), ...  Field arithmetic is exact, so the same value is
+//     sum_k c_k B_k,   B_k = prod_{bit b of k} f_b                                    (16 coefficients per thread, B_k on the host)
+// i.e. per thread a 16 x 4 dot product of M31 coefficients with constant QM31 coordinates: 4 multiplications per coefficient
+// instead of 9 for the pairwise tree, and they accumulate in u64 (IMAD.WIDE with a 64-bit addend) -- four products of canonical
+// values plus a folded carry stay below 2^64, so a reduction is needed only every four terms.  The levels above multiply QM31
+// values by the constant f_l, which is the 4 x 4 M31 matrix of qmat(): again four products per output coordinate, one reduction.
 struct FoldFactors { m31::QM f[32]; };
+struct BaseConsts { uint32_t b[16][4]; };           // B_k, k = 0..15 (B_0 = 1 is not multiplied)
+struct QMat { uint32_t m[4][4]; };                  // y = f * x  <=>  y_r = sum_c m[r][c] x_c
+struct QMats { QMat l[4]; };
+__device__ __forceinline__ uint64_t fold31(uint64_t a) { return (a & m31::P) + (a >> 31); }   // same residue, < 2^31 + 2^33
 // blockIdx.y = polynomial of the batch; out / in of polynomial p at + p * stride words
+__global__ void __launch_bounds__(128) fold_base16_kernel(ColSet polys, uint64_t n_out, BaseConsts bc, uint32_t *out, uint64_t out_stride)
+{
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_out) return;
+    const uint32_t *c = polys.col(blockIdx.y) + t * 16;
+    uint32_t v[16];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const uint4 q = __ldcs(reinterpret_cast<const uint4 *>(c) + k);
+        v[4 * k] = q.x; v[4 * k + 1] = q.y; v[4 * k + 2] = q.z; v[4 * k + 3] = q.w;
+    }
+    uint32_t r[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        uint64_t acc = j == 0 ? v[0] : 0;
+#pragma unroll
+        for (int k = 1; k < 16; k++) {
+            acc += (uint64_t)v[k] * bc.b[k][j];
+            if ((k & 3) == 0) acc = fold31(acc);      // after 4 products (k = 1..4, 5..8, 9..12); the last 3 go straight to reduce
+        }
+        r[j] = m31::reduce(acc);
+    }
+    out += blockIdx.y * out_stride;
+    reinterpret_cast<uint4 *>(out)[t] = make_uint4(r[0], r[1], r[2], r[3]);
+}
+// the pairwise form, for polynomials with fewer than 16 coefficients
 __global__ void fold_base_kernel(ColSet polys, uint64_t n_out, int levels, FoldFactors ff, uint32_t *out, uint64_t out_stride)
 {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_out) return;
-    const int cnt = 1 << levels;   // <= 16
+    const int cnt = 1 << levels;   // < 16
     m31::QM w[8];
     const uint32_t *c = polys.col(blockIdx.y) + t * cnt;
     uint32_t v[16];
-    if (levels == 4) {
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const uint4 q = __ldcs(reinterpret_cast<const uint4 *>(c) + k);
-            v[4 * k] = q.x; v[4 * k + 1] = q.y; v[4 * k + 2] = q.z; v[4 * k + 3] = q.w;
-        }
-    } else {
-#pragma unroll
-        for (int k = 0; k < 16; k++) v[k] = k < cnt ? c[k] : 0u;
-    }
+    for (int k = 0; k < 16; k++) v[k] = k < cnt ? c[k] : 0u;
 #pragma unroll
     for (int k = 0; k < 8; k++)
         if (2 * k + 1 < cnt) w[k] = m31::qadd(m31::qfrom(v[2 * k]), m31::qmul_m(ff.f[0], v[2 * k + 1]));
@@ -550,8 +577,22 @@ __global__ void fold_base_kernel(ColSet polys, uint64_t n_out, int levels, FoldF
     out += blockIdx.y * out_stride;
     reinterpret_cast<uint4 *>(out)[t] = make_uint4(w[0].a, w[0].b, w[0].c, w[0].d);
 }
-__global__ void fold_qm_kernel(const uint32_t *in, uint64_t in_stride, uint64_t n_out, int levels, int level0, FoldFactors ff, uint32_t *out,
-                               uint64_t out_stride)
+// w_even + f * w_odd with f as its matrix: 4 products + one canonical addend < 2^64 per coordinate
+__device__ __forceinline__ m31::QM fold_pair(const m31::QM &e, const m31::QM &o, const QMat &m)
+{
+    const uint32_t x[4] = { o.a, o.b, o.c, o.d }, add[4] = { e.a, e.b, e.c, e.d };
+    uint32_t r[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        uint64_t acc = add[j];
+#pragma unroll
+        for (int c = 0; c < 4; c++) acc += (uint64_t)x[c] * m.m[j][c];
+        r[j] = m31::reduce(acc);
+    }
+    return { r[0], r[1], r[2], r[3] };
+}
+__global__ void __launch_bounds__(128) fold_qm_kernel(const uint32_t *in, uint64_t in_stride, uint64_t n_out, int levels, QMats mats, uint32_t *out,
+                                                      uint64_t out_stride)
 {
     uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_out) return;
@@ -566,10 +607,20 @@ __global__ void fold_qm_kernel(const uint32_t *in, uint64_t in_stride, uint64_t 
         if (l < levels) {
 #pragma unroll
             for (int k = 0; k < (8 >> l); k++)
-                if (k < (cnt >> (l + 1))) w[k] = m31::qadd(w[2 * k], m31::qmul(ff.f[level0 + l], w[2 * k + 1]));
+                if (k < (cnt >> (l + 1))) w[k] = fold_pair(w[2 * k], w[2 * k + 1], mats.l[l]);
         }
     out += blockIdx.y * out_stride;
     reinterpret_cast<uint4 *>(out)[t] = make_uint4(w[0].a, w[0].b, w[0].c, w[0].d);
+}
+// multiplication by the constant f = (f0 + f1 i) + (f2 + f3 i) u, u^2 = 2 + i (fields/qm31.ts:9), as a matrix over M31
+static QMat qmat(const host::QM &f)
+{
+    using namespace host;
+    const uint32_t n1 = sub(0, f.b), n3 = sub(0, f.d);
+    const uint32_t t = sub(add(f.c, f.c), f.d);                // 2 f2 - f3
+    const uint32_t s = add(f.c, add(f.d, f.d));                // f2 + 2 f3
+    QMat q = { { { f.a, n1, t, sub(0, s) }, { f.b, f.a, s, t }, { f.c, n3, f.a, n1 }, { f.d, f.c, f.b, f.a } } };
+    return q;
 }
 
 static m31::QM to_dev(const uint32_t a[4]) { return { a[0], a[1], a[2], a[3] }; }
@@ -1135,13 +1186,23 @@ int tstwo_eval_at_point_many(const tstwo_dptr *coeffs, int n_polys, int log_size
         return 0;
     }
     FoldFactors ff;
+    host::QM hf[32];
     host::QM x = host::qld(px), one = { 1, 0, 0, 0 };
-    { host::QM y = host::qld(py); ff.f[0] = { y.a, y.b, y.c, y.d }; }
+    hf[0] = host::qld(py);
     for (int i = 1; i < log_size; i++) {
-        ff.f[i] = { x.a, x.b, x.c, x.d };
+        hf[i] = x;
         host::QM sx = host::qmul(x, x);
         x = host::qsub(host::qadd(sx, sx), one);     // circle.ts:37-40 double_x
     }
+    for (int i = 0; i < log_size; i++) ff.f[i] = { hf[i].a, hf[i].b, hf[i].c, hf[i].d };
+    BaseConsts bc;
+    memset(&bc, 0, sizeof bc);
+    if (log_size >= 4)
+        for (int k = 0; k < 16; k++) {               // B_k = product of the factors of k's set bits
+            host::QM b = one;
+            for (int bit = 0; bit < 4; bit++) if (k >> bit & 1) b = host::qmul(b, hf[bit]);
+            bc.b[k][0] = b.a; bc.b[k][1] = b.b; bc.b[k][2] = b.c; bc.b[k][3] = b.d;
+        }
     const uint64_t n = 1ull << log_size;
     const int lv = log_size < 4 ? log_size : 4;
     const uint64_t cnt0 = n >> lv, per_poly = 4 * (cnt0 + (cnt0 >> 1) + 64);      // words of scratch per polynomial (two ping-pong buffers)
@@ -1159,12 +1220,16 @@ int tstwo_eval_at_point_many(const tstwo_dptr *coeffs, int n_polys, int log_size
         if ((rc = make_colset(coeffs + p0, nb, 0, &cs))) return rc;
         uint64_t cnt = cnt0;
         uint32_t *cur = buf, *nxt = buf + 4 * cnt0;
-        TS_LAUNCH(fold_base_kernel, dim3((unsigned)((cnt + 127) / 128), nb), 128, 0, cs, cnt, lv, ff, cur, per_poly);
+        if (lv == 4) TS_LAUNCH(fold_base16_kernel, dim3((unsigned)((cnt + 127) / 128), nb), 128, 0, cs, cnt, bc, cur, per_poly);
+        else TS_LAUNCH(fold_base_kernel, dim3((unsigned)((cnt + 127) / 128), nb), 128, 0, cs, cnt, lv, ff, cur, per_poly);
         int level = lv;
         while (cnt > 1) {
             const int rem = log_size - level, l = rem < 4 ? rem : 4;
             const uint64_t ncnt = cnt >> l;
-            TS_LAUNCH(fold_qm_kernel, dim3((unsigned)((ncnt + 127) / 128), nb), 128, 0, cur, per_poly, ncnt, l, level, ff, nxt, per_poly);
+            QMats mats;
+            memset(&mats, 0, sizeof mats);
+            for (int k = 0; k < l; k++) mats.l[k] = qmat(hf[level + k]);
+            TS_LAUNCH(fold_qm_kernel, dim3((unsigned)((ncnt + 127) / 128), nb), 128, 0, cur, per_poly, ncnt, l, mats, nxt, per_poly);
             uint32_t *t = cur; cur = nxt; nxt = t;
             cnt = ncnt; level += l;
         }

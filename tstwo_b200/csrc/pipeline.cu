@@ -283,6 +283,74 @@ int tstwo_ipc_close(tstwo_dptr ptr)
     return 0;
 }
 
+// ---- cross-device flags (see the header).  A kernel boundary orders the flag store after every store of the kernels before it
+// on the stream (the peer stores of the last FFT pass included); fence.sys + st.release.sys publish it to the peer, whose
+// polling kernel acquires it before the hashing kernels that follow it on ITS stream start.
+namespace {
+struct FlagAddrs { uint32_t *a[64]; };
+__global__ void peer_signal_kernel(FlagAddrs fa, int n, uint32_t value)
+{
+    if ((int)threadIdx.x < n) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(fa.a[threadIdx.x]), "r"(value) : "memory");
+    }
+}
+__global__ void peer_wait_kernel(const uint32_t *flags, int n, uint32_t value, unsigned long long timeout_ns)
+{
+    if ((int)threadIdx.x < n) {
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (;;) {
+            uint32_t v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + threadIdx.x) : "memory");
+            if ((int32_t)(v - value) >= 0) break;
+            __nanosleep(200);
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > timeout_ns) __trap();          // a peer that never arrives is an error, not a hung device
+        }
+    }
+    __syncwarp();
+    __threadfence_system();
+}
+__global__ void peer_put_kernel(uint32_t *dst, const uint32_t *src, int n_words, uint32_t *flag, uint32_t value)
+{
+    for (int i = threadIdx.x; i < n_words; i += blockDim.x) dst[i] = src[i];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+}  // namespace
+
+int tstwo_peer_signal(const tstwo_dptr *flag_addrs, int n, uint32_t value)
+{
+    TS_REQUIRE_INIT();
+    if (!flag_addrs || n < 1 || n > 64) return fail(TSTWO_ERR_BAD_ARG, "tstwo_peer_signal: 1..64 flag addresses");
+    FlagAddrs fa;
+    memset(&fa, 0, sizeof fa);
+    for (int i = 0; i < n; i++) {
+        if (!flag_addrs[i] || (flag_addrs[i] & 3)) return fail(TSTWO_ERR_BAD_ARG, "tstwo_peer_signal: flag %d null or unaligned", i);
+        fa.a[i] = (uint32_t *)flag_addrs[i];
+    }
+    TS_LAUNCH(peer_signal_kernel, 1, 64, 0, fa, n, value);
+    return 0;
+}
+int tstwo_peer_wait(tstwo_dptr flags, int n, uint32_t value, uint32_t timeout_ms)
+{
+    TS_REQUIRE_INIT();
+    if (!flags || (flags & 3) || n < 1 || n > 64) return fail(TSTWO_ERR_BAD_ARG, "tstwo_peer_wait: 1..64 aligned flags");
+    TS_LAUNCH(peer_wait_kernel, 1, 64, 0, (const uint32_t *)flags, n, value, (unsigned long long)(timeout_ms ? timeout_ms : 4000) * 1000000ull);
+    return 0;
+}
+int tstwo_peer_put(tstwo_dptr dst, tstwo_dptr src, int n_words, tstwo_dptr flag_addr, uint32_t value)
+{
+    TS_REQUIRE_INIT();
+    if (!dst || !src || !flag_addr || ((dst | src | flag_addr) & 3) || n_words < 1 || n_words > 1024)
+        return fail(TSTWO_ERR_BAD_ARG, "tstwo_peer_put: bad arguments");
+    TS_LAUNCH(peer_put_kernel, 1, 64, 0, (uint32_t *)dst, (const uint32_t *)src, n_words, (uint32_t *)flag_addr, value);
+    return 0;
+}
+
 // Host-resident trace: the columns are copied in chunks on a copy stream while the previous chunk's interpolate /
 // evaluate kernels run; the Merkle commit runs once all columns are extended.
 int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,

@@ -144,11 +144,20 @@ class PeerShardedCommit:
          is still being hashed in the next step), top log2 G layers on rank 0.
     CUDA-only (needs peer access); the protocol above the device work is the one tests/test_distributed_cpu.py covers."""
 
+    # word offsets inside the 4 KiB flag block that follows every rank's leaf buffer (same CUDA IPC mapping)
+    _ARRIVE, _HASHED, _ROOTF, _ROOTS, FLAG_BYTES = 0, 64, 128, 256, 4096
+
     def __init__(self, device_index: int, stream, n_cols: int, log_size: int, log_blowup: int, keep_coeffs: bool = False,
-                 overlap: tuple | None = None):
+                 overlap: tuple | None = None, fence: str = "flags"):
         """overlap = (col_groups, peer_sms): run the NVLink-bound last pass of each column group on a side stream on peer_sms
-        SMs while the others transform the next group (tstwo_lde_columns_to_peers_overlapped); None = one group."""
+        SMs while the others transform the next group (tstwo_lde_columns_to_peers_overlapped); None = one group.
+        fence = "flags": the ranks order a step with release/acquire flags in each other's memory (tstwo_peer_signal / _wait /
+        _put: no NCCL kernel in the step, no host synchronisation); "nccl": the 4-byte all-reduce + 32-byte all-gather of round 1."""
         from . import _lib
+        if fence not in ("flags", "nccl"):
+            raise ValueError("fence must be 'flags' or 'nccl'")
+        self.fence = fence
+        self._step = 0
         self.overlap = overlap
         self._lib_mod = _lib
         self.L = _lib.init(device_index)
@@ -177,8 +186,11 @@ class PeerShardedCommit:
         self.top: List[torch.Tensor] = []
         # leaf buffer of this rank: its own cudaMalloc (IPC exports whole allocations), exported to every peer
         p = C.c_uint64()
-        chk(self.L.tstwo_malloc(4 * n_cols * rows, C.byref(p)))
+        self.leaf_bytes = 4 * n_cols * rows
+        chk(self.L.tstwo_malloc(self.leaf_bytes + self.FLAG_BYTES, C.byref(p)))
         self.recv_ptr = p.value
+        chk(self.L.tstwo_memset_zero(self.recv_ptr + self.leaf_bytes, self.FLAG_BYTES))
+        chk(self.L.tstwo_sync())
         handle = (C.c_uint8 * 64)()
         chk(self.L.tstwo_ipc_export(self.recv_ptr, handle))
         mine = torch.tensor(list(bytes(handle)), dtype=torch.uint8, device=self.dev)
@@ -196,16 +208,47 @@ class PeerShardedCommit:
             self.bases.append(q.value)
             self._imported.append(q.value)
         self._bases_arr = _lib.dptr_array(self.bases)
-        dist.barrier()
+        # per-step argument arrays, built once (the step is a few ms: host work per step counts)
+        G, r = self.world, self.rank
+        fb = [b + self.leaf_bytes for b in self.bases]
+        self._flag_local = fb[r]
+        self._arrive_addrs = _lib.dptr_array([f + 4 * (self._ARRIVE + r) for f in fb])
+        self._hashed_addrs = _lib.dptr_array([f + 4 * (self._HASHED + r) for f in fb])
+        self._root_dst = fb[0] + 4 * (self._ROOTS + 8 * r)
+        self._root_flag = fb[0] + 4 * (self._ROOTF + r)
+        self._leaf_ptrs = _lib.dptr_array([self.recv_ptr + 4 * rows * c for c in range(self.n_cols)])
+        self._leaf_logs = (C.c_int * self.n_cols)(*([self.sub] * self.n_cols))
+        self._top = [self.ops.empty(8 << k) for k in range(G.bit_length() - 2, -1, -1)] if r == 0 else []
+        import os
+        self._timeout_ms = int(os.environ.get("TSTWO_PEER_TIMEOUT_MS", "10000"))
+        dist.barrier()                             # every rank's flags are zero and mapped before anyone signals
 
-    def step(self, trace: torch.Tensor):
+    def _before_stores(self):
+        """My stores go into every rank's leaf buffer: their hashing of the previous step must be over (flags: every rank
+        publishes hashed[rank] = step after its tree; nccl: the all-gather at the end of the previous step said so)."""
+        if self.fence == "flags" and self._step > 0:
+            self._lib_mod.check(self.L.tstwo_peer_wait(self._flag_local + 4 * self._HASHED, self.world, self._step, self._timeout_ms))
+
+    def step(self, trace: torch.Tensor, read_root: bool = True):
+        """One LDE + commit.  read_root = False leaves the root on the device (rank 0: root_bytes()), so that the host can enqueue
+        the next step while this one runs."""
         chk = self._lib_mod.check
         groups, peer_sms = self.overlap if self.overlap else (1, 0)
+        self._before_stores()
         chk(self.L.tstwo_lde_columns_to_peers_overlapped(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw,
                                                          self.coeffs.data_ptr() if self.coeffs is not None else 0,
                                                          self.work.data_ptr(), self._bases_arr, self.world, self.rank * self.lc, 0,
                                                          groups, peer_sms))
-        return self._finish()
+        return self._finish(read_root=read_root)
+
+    def root_bytes(self) -> bytes | None:
+        """The last step's root (rank 0; synchronises)."""
+        if self.rank != 0:
+            return None
+        t = self._top[-1] if self._top else None
+        if t is None:                              # one rank: the subtree root is the root
+            return self.ops.to_host_bytes(self.layers[:8])[:32]
+        return self.ops.to_host_bytes(t)[:32]
 
     def step_phases(self, trace: torch.Tensor):
         """step() with a CUDA event at every phase boundary (for bench.py's per-rank breakdown): returns the 5 events around
@@ -214,6 +257,7 @@ class PeerShardedCommit:
         st = self._stream if self._stream is not None else torch.cuda.current_stream()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
         groups, peer_sms = self.overlap if self.overlap else (1, 0)
+        self._before_stores()
         ev[0].record(st)
         chk(self.L.tstwo_lde_columns_to_peers_overlapped(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw,
                                                          self.coeffs.data_ptr() if self.coeffs is not None else 0,
@@ -223,24 +267,40 @@ class PeerShardedCommit:
         self._finish(ev, st)
         return ev
 
-    def _finish(self, ev=None, st=None):
+    def _finish(self, ev=None, st=None, read_root: bool = True):
         chk = self._lib_mod.check
-        self._order_before_collective()
-        dist.all_reduce(self.flag)                 # every rank's stores into my leaf buffer are complete after this
-        self._order_after_collective()
+        L, G = self.L, self.world
+        self._step += 1
+        s = self._step
+        if self.fence == "flags":
+            # "my stores are complete" into every rank's arrive[rank]; then wait until every rank has said so here
+            chk(L.tstwo_peer_signal(self._arrive_addrs, G, s))
+            chk(L.tstwo_peer_wait(self._flag_local + 4 * self._ARRIVE, G, s, self._timeout_ms))
+        else:
+            self._order_before_collective()
+            dist.all_reduce(self.flag)             # every rank's stores into my leaf buffer are complete after this
+            self._order_after_collective()
         if ev: ev[2].record(st)
-        rows = 1 << self.sub
-        ptrs = self._lib_mod.dptr_array([self.recv_ptr + 4 * rows * c for c in range(self.n_cols)])
-        logs = (C.c_int * self.n_cols)(*([self.sub] * self.n_cols))
-        chk(self.L.tstwo_merkle_commit(ptrs, logs, self.n_cols, self.layers.data_ptr(), None))
+        chk(L.tstwo_merkle_commit(self._leaf_ptrs, self._leaf_logs, self.n_cols, self.layers.data_ptr(), None))
         if ev: ev[3].record(st)
-        self._order_before_collective()
-        dist.all_gather_into_tensor(self.roots, self.layers[:8].contiguous())
-        self._order_after_collective()
-        out = None
-        if self.rank == 0:
-            self.top = top_layers(self.ops, self.roots, self.world)
-            out = self.ops.to_host_bytes(self.top[-1] if self.top else self.roots)[:32]
+        if self.fence == "flags":
+            chk(L.tstwo_peer_signal(self._hashed_addrs, G, s))                     # my leaf buffer may be overwritten
+            chk(L.tstwo_peer_put(self._root_dst, self.layers.data_ptr(), 8, self._root_flag, s))
+            if self.rank == 0:
+                chk(L.tstwo_peer_wait(self._flag_local + 4 * self._ROOTF, G, s, self._timeout_ms))
+                prev = self._flag_local + 4 * self._ROOTS
+                for i, k in enumerate(range(G.bit_length() - 2, -1, -1)):
+                    chk(L.tstwo_merkle_commit_layer(k, prev, None, 0, self._top[i].data_ptr()))
+                    prev = self._top[i].data_ptr()
+                self.top = self._top
+        else:
+            self._order_before_collective()
+            dist.all_gather_into_tensor(self.roots, self.layers[:8].contiguous())
+            self._order_after_collective()
+            if self.rank == 0:
+                self.top = top_layers(self.ops, self.roots, self.world)
+                self._top = self.top
+        out = self.root_bytes() if (read_root and self.rank == 0) else None
         if ev: ev[4].record(st)
         return out
 
@@ -272,6 +332,7 @@ class PeerShardedCommit:
         device-to-device copies on side streams (tstwo_scatter_shards) while the SMs transform the next group.  Only the last
         group's copies are exposed; the SMs never wait on NVLink."""
         chk = self._lib_mod.check
+        self._before_stores()
         chunks = max(1, min(chunks, self.lc))
         while self.lc % chunks:
             chunks -= 1
@@ -298,6 +359,7 @@ class PeerShardedCommit:
         while self.lc % chunks:
             chunks -= 1
         per, n = self.lc // chunks, 1 << self.log_size
+        self._before_stores()
         cs.wait_stream(main)                       # the staging buffer is free once the previous step's transforms are done
         for k in range(chunks):
             with torch.cuda.stream(cs):
