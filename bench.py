@@ -557,8 +557,18 @@ def run_cuda(args):
             e2e_step()          # synchronises inside (root is host-visible on return)
         dt = (time.perf_counter() - t0) / k
         assert bytes(root2).hex() == root_hex, "e2e root differs from device-resident root"
+        # the PCIe floor of that step: the same 4 GiB copied from the same pinned buffer with no kernel running
+        stage.copy_(host, non_blocking=True); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(k):
+            stage.copy_(host, non_blocking=True)
+        torch.cuda.synchronize()
+        dh = (time.perf_counter() - t0) / k
         e2e = {"value": n_cols * n / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "h2d_bytes_per_step": n_cols * n * 4,
-               "d2h_bytes_per_step": 32, "api": "tstwo_lde_commit_host (C ABI, pinned host trace -> root)"}
+               "d2h_bytes_per_step": 32, "api": "tstwo_lde_commit_host (C ABI, pinned host trace -> root)",
+               "h2d_only": {"ms_per_step": dh * 1e3, "gbs_per_link": n_cols * n * 4 / dh / 1e9,
+                            "note": "the same pinned buffer copied to the device with no kernel running: the PCIe floor of the e2e step"},
+               "e2e_over_floor": dt / max(dh, ms * 1e-3)}
 
     # ---- end to end at N > 1: every rank's column shard starts in pinned HOST memory and crosses its own PCIe link inside the
     # timed region (in column groups, overlapped with the transforms and the NVLink exchange); rank 0 reads the root back
@@ -587,10 +597,26 @@ def run_cuda(args):
         dt = float(dt.item())
         if rank == 0:
             assert got["root"].hex() == root_hex, "e2e root differs from device-resident root"
+        # the platform's share of that: ALL ranks copying their pinned shard to their GPU at the same time, no kernel at all
+        # (what the PCIe links + host memory deliver to N GPUs at once); e2e cannot beat max(this, the device-resident step)
+        def h2d_only():
+            stage.copy_(host, non_blocking=True)
+        h2d_only()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(k):
+            h2d_only()
+        barrier()
+        dh = torch.tensor([(time.perf_counter() - t0) / k], device=dev, dtype=torch.float64)
+        dist.all_reduce(dh, op=dist.ReduceOp.MAX)
+        dh = float(dh.item())
         e2e = {"value": n_cols * n / dt, "unit": UNIT, "ms_per_step": dt * 1e3, "h2d_bytes_per_step": n_cols * n * 4,
                "d2h_bytes_per_step": 32,
                "api": f"PeerShardedCommit.step_from_host (pinned host shard per rank -> root on rank 0), {world} PCIe links",
-               "cpu_affinity": "NUMA node of each rank's GPU (nvmlDeviceSetCpuAffinity)" if numa_bound else "unbound"}
+               "cpu_affinity": "NUMA node of each rank's GPU (nvmlDeviceSetCpuAffinity)" if numa_bound else "unbound",
+               "h2d_only": {"ms_per_step": dh * 1e3, "gbs_per_link": lc * n * 4 / dh / 1e9, "gbs_aggregate": n_cols * n * 4 / dh / 1e9,
+                            "note": "all ranks copy their pinned shard concurrently, no kernels: the PCIe / host-memory floor of the e2e step"},
+               "e2e_over_floor": dt / max(dh, ms * 1e-3)}
 
     extras = None
     if world == 1 and not args.no_extras:

@@ -27,7 +27,10 @@ def run_prove(tb, trace, log, n_cols, pow_bits, last, blow, n_queries):
     return prover.prove([comp], channel, scheme), channel, scheme
 
 
-@pytest.mark.parametrize("log,n_cols,pow_bits,last,blow,n_queries", [(5, 6, 4, 1, 1, 3), (4, 4, 3, 0, 2, 2), (9, 20, 8, 2, 1, 5)])
+# the last two are BASELINE config 5's shape (100 columns = Stwo's FIB_SEQUENCE_LENGTH, blow-up 2, 70 queries, 10 proof-of-work
+# bits) at log 16 and log 20; the log-23 size itself is covered by test_config5_log23_commitments below
+@pytest.mark.parametrize("log,n_cols,pow_bits,last,blow,n_queries", [(5, 6, 4, 1, 1, 3), (4, 4, 3, 0, 2, 2), (9, 20, 8, 2, 1, 5),
+                                                                     (16, 100, 10, 0, 1, 70), (20, 100, 10, 0, 1, 70)])
 def test_prove_matches_oracle_flow(tb, orc, log, n_cols, pow_bits, last, blow, n_queries):
     from oracle import stark
     exp = stark.prove_wide_fibonacci(log, n_cols, pow_bits, last, blow, n_queries)
@@ -77,3 +80,53 @@ def test_prove_argument_checks(tb):
         prover.prove([object()], Blake2sChannel.create(), None)
     with pytest.raises(ValueError, match="preprocessed trace not found"):
         prover.prove([object()], Blake2sChannel.create(), scheme)
+
+
+def test_config5_log23_commitments(tb, orc):
+    """BASELINE config 5 at its own size: wide-Fibonacci prove() with 100 columns of 2^23 rows, blow-up 2.  The proof's trace
+    commitment (and the empty preprocessed tree's) must equal the oracle's LDE + Merkle root of the same trace, the prover's own
+    sanity check (composition polynomial at the out-of-domain point == constraints at the sampled values) must hold, and the
+    sampled trace values must equal the oracle's eval_at_point of the oracle's coefficients for the first / last column."""
+    import torch
+    from oracle import stark
+    from tstwo_b200 import air, prover
+    from tstwo_b200.channel import Blake2sChannel
+    log, n_cols, blow = 23, 100, 1
+    n = 1 << log
+    trace = torch.empty((n_cols, n), dtype=torch.int32, device="cuda")
+    a = torch.ones(n, dtype=torch.int64, device="cuda")
+    b = torch.arange(n, dtype=torch.int64, device="cuda")
+    trace[0], trace[1] = a.to(torch.int32), b.to(torch.int32)
+    for k in range(2, n_cols):                                   # generateTestTrace (examples/fibonacci.ts:245-258)
+        a, b = b, (a * a % P + b * b % P) % P
+        trace[k] = b.to(torch.int32)
+    del a, b
+    host = trace.cpu().numpy().view(np.uint32)
+    assert (host[:, :64] == stark.fib_trace(6, n_cols)[:, :64]).all()            # same generator as the oracle's, row for row
+    tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(log + 1 + blow).half_coset())
+    dom = tb.CanonicCoset.new(log).circleDomain()
+    cols = [tb.CudaCircleEvaluation(dom, tb.CudaColumn.view(trace.data_ptr() + 4 * (c << log), n, trace)) for c in range(n_cols)]
+    channel = Blake2sChannel.create()
+    scheme = tb.CommitmentSchemeProver(tb.PcsConfig(10, tb.FriConfig(0, blow, 70)), tw)
+    bld = scheme.tree_builder(); bld.extend_evals([]); bld.commit(channel)
+    bld = scheme.tree_builder(); bld.extend_evals(cols); bld.commit(channel)
+    proof = prover.prove([air.WideFibonacciComponent(air.WideFibonacciEval.create(log, n_cols))], channel, scheme)
+    p = proof.get()
+    # oracle: the same LDE + commitment (Stwo-correct transforms, as the commitment scheme uses them)
+    hi, hl = orc.canonic_half_coset(log + blow)
+    otw, oitw = orc.precompute_twiddles(hi, hl)
+    orc.use_all_cores()
+    coeffs, _, layers = orc.lde_commit(host, blow, otw, oitw, want_coeffs=True, quirks=False)
+    assert p.commitments[0] == orc.merkle_commit([])[0][0].tobytes()
+    assert p.commitments[1] == layers[0][0].tobytes()
+    # out-of-domain samples of the first and last trace column against the oracle's coefficients at the proof's own point:
+    # replay the transcript up to the point on the oracle's channel
+    ch = orc.Channel()
+    for root in p.commitments[:2]:
+        ch.mix_root(root)
+    ch.draw_felt()                                               # the composition polynomial's random coefficient
+    ch.mix_root(p.commitments[2])
+    oods = stark.random_point(ch)
+    for c in (0, n_cols - 1):
+        assert [int(v) for v in orc.eval_at_point(coeffs[c], oods[0], oods[1])] == list(p.sampled_values[1][c][0])
+    assert len(p.fri_proof.inner_layers) == log + 1 + blow - 1 - blow and len(p.sampled_values[2]) == 4
