@@ -135,7 +135,9 @@ int tstwo_fri_decompose(const tstwo_dptr src[4], int log_size, const tstwo_dptr 
  *   last_log                             : stop when the layer has 2^last_log elements (config.last_layer_domain_size())
  *   circle_cols[n_circle][4], circle_logs, circle_half_inits : the remaining circle columns, descending sizes
  *   channel_state[19]                    : in/out  digest[8], n_challenges, n_sent, queue_len, queue[8] (Blake2sChannel state)
- *   layer_evals[n_layers][4]             : out, evaluation columns of layers 1 .. n_layers (tstwo_malloc'ed: caller frees)
+ *   layer_evals[n_layers][4]             : out, evaluation columns of layers 1 .. n_layers; the four coordinates of a layer are
+ *                                          the quarters of ONE tstwo_malloc block (evenly spaced columns take the bulk-copy leaf
+ *                                          kernel): the caller frees layer_evals[l][0] only
  *   layer_trees[n_layers]                : out, Merkle tree buffer of layers 0 .. n_layers-1 (root first; caller frees)
  *   roots[n_layers][32], alphas[n_layers][4], *n_layers : out, n_layers = first_log - last_log */
 int tstwo_fri_commit_layers(const tstwo_dptr first[4], int first_log, uint32_t first_coset_init, int last_log,

@@ -24,6 +24,10 @@ int tstwo_debug_last_fft_mode(void);
 /* top stage of the bulk-copy passes on the tensor cores (tcgen05 kind::i8, tc_stage.cuh): bit 0 = forward strided passes
  * (default), bit 1 = contiguous passes, bit 2 = inverse strided passes; 0 = integer pipes everywhere */
 int tstwo_debug_set_fft_tc(int mask);
+/* tstwo_lde_columns_to_peers_overlapped: percent of an equal share that the first and the last column group get (100 = equal
+ * groups).  Smaller edge groups shorten the two phases that have no partner (the first group's own passes, the last group's
+ * NVLink-bound storing pass); every phase then splits the SMs in proportion to the columns on its two sides. */
+int tstwo_debug_set_overlap_taper(int percent);
 
 /* CUDA events around every bulk-copy FFT pass launch from now on (on = 1; 0 stops and forgets).  tstwo_debug_pass_times
  * waits for the recorded passes and returns how many there were (<= max): tags[i] bit 0 = inverse, bit 1 = strided pass,

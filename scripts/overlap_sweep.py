@@ -21,26 +21,26 @@ trace = torch.randint(0, P, (lc, 1 << log), dtype=torch.int32, device="cuda", ge
 sc = PeerShardedCommit(local, stream, n_cols, log, blow)
 cfgs = [tuple(int(x) for x in a.split(",")) for a in sys.argv[1:]] or [(1, 0), (2, 48), (4, 48), (4, 64), (8, 64)]
 roots = {}
-for cfg in cfgs:
-    sc.overlap = None if cfg[0] <= 1 else cfg
+for cfg in cfgs:                                   # "groups,peer_sms[,taper percent]"
+    sc.overlap = None if cfg[0] <= 1 else cfg[:2]
+    _lib.check(L.tstwo_debug_set_overlap_taper(cfg[2] if len(cfg) > 2 else 100))
     for _ in range(3):
-        r = sc.step(trace)
+        sc.step(trace, read_root=False)
     torch.cuda.synchronize(); dist.barrier()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    K = 8
+    K = 10
     torch.cuda.synchronize(); dist.barrier()
     a.record(stream)
     for _ in range(K):
-        r = sc.step(trace)
-        if r is None:
-            _lib.check(L.tstwo_sync())
+        sc.step(trace, read_root=False)          # steps are enqueued back to back; the ranks order themselves with peer flags
     b.record(stream)
     torch.cuda.synchronize(); dist.barrier()
+    r = sc.root_bytes()
     t = torch.tensor([a.elapsed_time(b) / K], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:
         roots[cfg] = r.hex()
-        print(f"N={world} groups={cfg[0]:2d} peer_sms={cfg[1]:3d}  {t.item():7.3f} ms/step  root {r.hex()[:16]}", flush=True)
+        print(f"N={world} groups={cfg[0]:2d} peer_sms={cfg[1]:3d} taper={cfg[2] if len(cfg) > 2 else 100:3d}  {t.item():7.3f} ms/step  root {r.hex()[:16]}", flush=True)
 if rank == 0:
     assert len(set(roots.values())) == 1, f"roots differ: {roots}"
     print("all roots equal")

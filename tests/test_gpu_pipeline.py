@@ -154,12 +154,15 @@ def test_lde_columns_to_peers_local_bases(tb, orc, n_shards, col_offset, total):
                 assert (got[c] == 7).all(), f"shard {d} column {c} must be untouched"
 
 
-@pytest.mark.parametrize("groups,peer_sms,n_cols", [(2, 48, 5), (4, 60, 9), (3, 100, 3), (8, 16, 4)])
-def test_lde_columns_to_peers_overlapped_matches(tb, orc, groups, peer_sms, n_cols):
+@pytest.mark.parametrize("groups,peer_sms,n_cols,taper", [(2, 48, 5, 100), (4, 60, 9, 100), (3, 100, 3, 100), (8, 16, 4, 100),
+                                                          (4, 62, 16, 33), (5, 62, 13, 50), (4, 62, 5, 25), (3, 62, 3, 10)])
+def test_lde_columns_to_peers_overlapped_matches(tb, orc, groups, peer_sms, n_cols, taper):
     """tstwo_lde_columns_to_peers_overlapped (last pass of each column group on a side stream with an SM budget) writes exactly
-    what the one-group call writes, for uneven groups too; checked against the oracle's evaluations on local shard buffers."""
+    what the one-group call writes, for uneven groups too (taper < 100: smaller first / last group, per-phase SM split); checked
+    against the oracle's evaluations on local shard buffers."""
     from tstwo_b200 import _lib
     L = _lib.init(0)
+    _lib.check(L.tstwo_debug_set_overlap_taper(taper))
     log, blow, n_shards, col_offset = 15, 1, 4, 1
     ext = log + blow
     rows = (1 << ext) // n_shards
@@ -184,6 +187,7 @@ def test_lde_columns_to_peers_overlapped_matches(tb, orc, groups, peer_sms, n_co
                     assert (got[c] == evals[c - col_offset][d * rows:(d + 1) * rows]).all(), f"rep {rep} shard {d} column {c}"
                 else:
                     assert (got[c] == 7).all(), f"shard {d} column {c} must be untouched"
+    _lib.check(L.tstwo_debug_set_overlap_taper(100))
 
 
 def test_lde_columns_to_peers_overlapped_rejects_bad_budget(tb):

@@ -96,6 +96,7 @@ DEBUG_SIGNATURES = {
     "tstwo_debug_set_fft_radix": (C.c_int, [C.c_int]),
     "tstwo_debug_last_fft_mode": (C.c_int, []),
     "tstwo_debug_set_fft_tc": (C.c_int, [C.c_int]),
+    "tstwo_debug_set_overlap_taper": (C.c_int, [C.c_int]),
     "tstwo_debug_pass_timing": (C.c_int, [C.c_int]),
     "tstwo_debug_pass_times": (C.c_int, [C.c_int, intp, C.POINTER(C.c_float)]),
     "tstwo_debug_set_leaf_mode": (C.c_int, [C.c_int]),

@@ -107,6 +107,31 @@ __global__ void __launch_bounds__(256) merkle_layer_kernel(const uint4 *__restri
     out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
 }
 
+// Pure node layer (no column values at this size: every layer of a tree below its smallest column, all of a FRI layer tree but
+// its leaves): one 64-byte block per node.  Its SHAPE is chosen for ptxas: with __launch_bounds__(256, 5) (<= 51 registers) and the
+// compression inside a run-time loop (n_blocks = 1 at run time) the additions come out as IMAD R, R, UR, R -- `one` in a uniform
+// register, 1345 clk per warp-compression -- where merkle_layer_kernel's straight-line copies get the three-register form (1556 clk,
+// profiles/r01_microbench_blake2s_forms.txt).  Checked with cuobjdump at build time by tests/test_abi_cpu.py (UR form present).
+__global__ void __launch_bounds__(256, 5) merkle_node_kernel(const uint4 *__restrict__ prev, uint64_t n_nodes, uint4 *__restrict__ out,
+                                                             uint32_t n_blocks, uint32_t one)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    uint32_t h[8], m[16];
+    const uint4 *p = prev + 4 * i;   // 64 bytes = children 2i, 2i+1
+    const uint4 x0 = __ldcs(p), x1 = __ldcs(p + 1), x2 = __ldcs(p + 2), x3 = __ldcs(p + 3);
+    m[0] = x0.x; m[1] = x0.y; m[2] = x0.z; m[3] = x0.w; m[4] = x1.x; m[5] = x1.y; m[6] = x1.z; m[7] = x1.w;
+    m[8] = x2.x; m[9] = x2.y; m[10] = x2.z; m[11] = x2.w; m[12] = x3.x; m[13] = x3.y; m[14] = x3.z; m[15] = x3.w;
+    b2s_init(h);
+#pragma unroll 1
+    for (uint32_t b = 0; b < n_blocks; b++) {        // n_blocks == 1: a node is exactly one final block
+        const bool last = b + 1 == n_blocks;
+        b2s_compress(h, m, (b + 1) * 64u, last, one);
+    }
+    out[2 * i] = make_uint4(h[0], h[1], h[2], h[3]);
+    out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
+}
+
 // ---- leaf layer fed by bulk tensor copies -----------------------------------------------------------------------
 // The leaf hash of row i absorbs column words c = 0, 1, ... of that row, 16 per compression.  With uniformly spaced
 // columns the message blocks of 256 consecutive rows are boxes [16 columns x 256 rows] (16 KiB, sixteen 1 KiB runs) of
@@ -319,7 +344,8 @@ int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, i
         g_last_leaf = g_leaf_mode;
         return merkle_leaf_tma(cols, n_cols, n, out);
     }
-    if (prev) TS_LAUNCH((merkle_layer_kernel<true>), grid, block, 0, (const uint4 *)prev, cols, n_cols, n, (uint4 *)out, 1u);
+    if (prev && n_cols == 0 && g_leaf_mode) TS_LAUNCH(merkle_node_kernel, grid, block, 0, (const uint4 *)prev, n, (uint4 *)out, 1u, 1u);
+    else if (prev) TS_LAUNCH((merkle_layer_kernel<true>), grid, block, 0, (const uint4 *)prev, cols, n_cols, n, (uint4 *)out, 1u);
     else TS_LAUNCH((merkle_layer_kernel<false>), grid, block, 0, (const uint4 *)nullptr, cols, n_cols, n, (uint4 *)out, 1u);
     return 0;
 }

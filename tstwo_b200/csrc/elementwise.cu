@@ -873,8 +873,11 @@ int tstwo_fri_commit_layers(const tstwo_dptr first[4], int first_log, uint32_t f
             TS_LAUNCH(fri_channel_kernel, 1, 32, 0, d_state, (const uint32_t *)tree, d_alpha + 4 * l, d_roots + 8 * l);
             // fold_line into fresh columns (alpha read from device memory)
             tstwo_dptr nxt[4];
+            // one block, coordinate k at + k * stride words (stride = n/2, at least 4 words: every coordinate stays 16-byte aligned)
+            const uint64_t stride_words = n / 2 < 4 ? 4 : n / 2;
+            if ((rc = tstwo_malloc(4 * 4ull * stride_words, &nxt[0]))) return rc;
             for (int k = 0; k < 4; k++) {
-                if ((rc = tstwo_malloc(4ull * (n / 2), &nxt[k]))) return rc;
+                nxt[k] = nxt[0] + (uint64_t)k * 4ull * stride_words;
                 layer_evals[4 * l + k] = nxt[k];
             }
             {

@@ -2,6 +2,7 @@
 // packages/core/src/pcs/prover.ts:215-235 (interpolate -> evaluate on the blown-up canonic domain -> Merkle commit),
 // i.e. PolyOps.interpolateColumns + evaluatePolynomials (poly/circle/ops.ts:73-101) + MerkleProver.commit
 // (vcs/prover.ts:13-30) on device-resident columns.
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -142,6 +143,7 @@ int tstwo_lde_columns_sharded(tstwo_dptr trace, int n_cols, int log_size, int lo
 // exchange (7/8 of the evaluations at 8 GPUs, >= 1 ms at 900 GB/s) then overlaps ALL of the LDE's arithmetic, not just the
 // 14 layers of the pass that issues the stores.  Same bytes, same destinations: results are identical for any grouping.
 namespace {
+int g_overlap_taper = 100;     // percent of an equal share given to the first and the last column group (tstwo_debug_set_overlap_taper)
 // per device (Context): peer_stream; peer_ev[0] group ready for its last pass (main -> side), [1] side drained
 #define g_peer_stream (ctx().peer_stream)
 #define g_peer_ev (ctx().peer_ev)
@@ -170,6 +172,7 @@ int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tst
     for (int d = 0; d < n_shards; d++)
         if (!shard_bases[d] || (shard_bases[d] & 15)) return fail(TSTWO_ERR_BAD_ARG, "shard base %d null or not 16-byte aligned", d);
     if (col_groups > 1 && !g_peer_stream) {
+        if (const char *e = getenv("TSTWO_OVERLAP_TAPER")) { const int v = atoi(e); if (v >= 1 && v <= 100) g_overlap_taper = v; }
         int lo_pri = 0, hi_pri = 0;
         TS_CUDA(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
         TS_CUDA(cudaStreamCreateWithPriority(&g_peer_stream, cudaStreamNonBlocking, hi_pri));
@@ -178,17 +181,47 @@ int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tst
     cudaStream_t main_stream = c.stream;
     // per-shard bases, advanced to each group's first column, in the library's device pointer table (slot 2, 64 per group)
     uint64_t host_bases[32 * 64];
+    // Column groups.  Equal groups leave the first group's main passes and the last group's storing pass without a partner; with
+    // g_overlap_taper < 100 the first and the last group get that percentage of an equal share (the middle ones the rest), and
+    // every phase splits the SMs in proportion to the work of its two sides, so head and tail shrink while the phases stay balanced.
+    int group_cols[32];
+    {
+        int edge = col_groups >= 3 ? (int)(((long long)n_cols * g_overlap_taper + 50LL * col_groups) / (100LL * col_groups)) : 0;
+        if (col_groups >= 3 && edge < 1) edge = 1;
+        if (col_groups < 3 || g_overlap_taper >= 100 || n_cols - 2 * edge < col_groups - 2) edge = 0;
+        int left = n_cols - 2 * edge, c = 0;
+        for (int k = 0; k < col_groups; k++) {
+            if (edge && (k == 0 || k == col_groups - 1)) group_cols[k] = edge;
+            else {
+                const int mid_left = edge ? col_groups - 2 - (k - 1) : col_groups - k;
+                group_cols[k] = (left + mid_left - 1) / mid_left;
+                left -= group_cols[k];
+            }
+            c += group_cols[k];
+        }
+        if (c != n_cols) return fail(TSTWO_ERR_BAD_ARG, "internal: column groups do not add up (%d of %d)", c, n_cols);
+    }
     int c0 = 0;
     for (int k = 0; k < col_groups; k++) {
-        const int nc = (n_cols - c0 + (col_groups - k) - 1) / (col_groups - k);   // remaining columns spread evenly
+        const int nc = group_cols[k];
         for (int d = 0; d < n_shards; d++) host_bases[64 * k + d] = shard_bases[d] + (uint64_t)(col_offset + c0) * rows * 4;
         c0 += nc;
     }
+    // SMs of group k's storing pass while group k + 1's other passes run beside it: peer_sms is the storing pass's share of the
+    // LDE's integer work for EQUAL groups; for unequal neighbours the split follows their column counts
+    auto side_sms = [&](int k) -> int {
+        if (k >= col_groups - 1) return 0;
+        const double ws = (double)peer_sms * group_cols[k], wm = (double)(c.sm_count - peer_sms) * group_cols[k + 1];
+        int p = (int)(c.sm_count * ws / (ws + wm) + 0.5);
+        if (p < 8) p = 8;
+        if (p > c.sm_count - 8) p = c.sm_count - 8;
+        return p;
+    };
     uint64_t *dev_bases = c.d_ptr_table + 2 * 4096;
     TS_CUDA(cudaMemcpyAsync(dev_bases, host_bases, sizeof(uint64_t) * 64 * (size_t)col_groups, cudaMemcpyHostToDevice, main_stream));
     c0 = 0;
     for (int k = 0; k < col_groups && !rc; k++) {
-        const int nc = (n_cols - c0 + (col_groups - k) - 1) / (col_groups - k);
+        const int nc = group_cols[k];
         ColSet src = { (const uint32_t *)trace + (uint64_t)c0 * n, n, nullptr };
         ColSet cfs = { cf + (uint64_t)c0 * n, n, nullptr };
         ColSet wk = { (const uint32_t *)work + (uint64_t)c0 * ne, ne, nullptr };
@@ -203,7 +236,7 @@ int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tst
             break;
         }
         // every pass but the last on the library's stream; while an earlier group's last pass may be running they leave it peer_sms SMs
-        c.grid_limit = k > 0 ? c.sm_count - peer_sms : 0;
+        c.grid_limit = k > 0 ? c.sm_count - side_sms(k - 1) : 0;
         if (!(rc = fft_interpolate(src, cfs, nc, log_size, t, flags))) rc = fft_evaluate(cfs, log_size, ev, nc, ext, t, flags, &wk, 1);
         if (rc) break;
         cudaError_t e = cudaEventRecord(g_peer_ev[0], main_stream);
@@ -211,7 +244,7 @@ int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tst
         if (e != cudaSuccess) { rc = fail(TSTWO_ERR_CUDA, "event record/wait failed: %s", cudaGetErrorString(e)); break; }
         // the pass whose stores cross NVLink, on the side stream; the last group's has the GPU to itself
         c.stream = g_peer_stream;
-        c.grid_limit = k < col_groups - 1 ? peer_sms : 0;
+        c.grid_limit = side_sms(k);
         rc = fft_evaluate(cfs, log_size, ev, nc, ext, t, flags, &wk, 2);
         c.stream = main_stream;
         c0 += nc;
@@ -239,6 +272,12 @@ void pipeline_release()
 }  // namespace tstwo
 
 extern "C" {
+int tstwo_debug_set_overlap_taper(int percent)
+{
+    if (percent < 1 || percent > 100) return fail(TSTWO_ERR_BAD_ARG, "taper must be 1..100 percent");
+    g_overlap_taper = percent;
+    return 0;
+}
 int tstwo_lde_columns_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, tstwo_dptr coeffs,
                                tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards, int col_offset, uint32_t flags)
 {

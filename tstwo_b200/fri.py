@@ -331,7 +331,9 @@ class FriProver:
             tree_layers = [buf.slice(8 * ((1 << k) - 1), 8 << k) for k in range(log + 1)]
             layers.append(FriInnerLayerProver(cur, MerkleProver(tree_layers, bytes(roots[32 * l:32 * l + 32]))))
             coset = coset.double()
-            cols = [CudaColumn(int(evals[4 * l + k]), 1 << (log - 1)) for k in range(4)]
+            stride = max(4, 1 << (log - 1))
+            block = CudaColumn(int(evals[4 * l]), 4 * stride)              # the four coordinates are one block (owner)
+            cols = [block.slice(k * stride, 1 << (log - 1)) for k in range(4)]
             cur = LineEvaluation.new(LineDomain.new(coset), SecureColumnByCoords(cols))
         FriProver.last_alphas = [[int(alphas[4 * l + k]) for k in range(4)] for l in range(n_layers)]
         return layers, cur
