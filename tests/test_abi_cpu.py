@@ -94,3 +94,29 @@ def test_host_circle_mirror(orc):
     assert CirclePointIndex(1).to_point() == (2, 1268011823)
     with pytest.raises(ValueError):
         CanonicCoset.new(0)
+
+
+def test_blake2s_kernels_keep_the_uniform_register_imad_form():
+    """The two BLAKE2s kernels that carry the Merkle time (leaf layer, node layers) rely on ptxas emitting their additions as
+    IMAD R, R, UR, R (`one` in a uniform register: 1345 clk per warp-compression against 1556 for the three-register form,
+    profiles/r01_microbench_blake2s_forms.txt).  The choice is a ptxas heuristic (launch bounds, loop shape, even blockDim.x vs a
+    literal flip it), so the built library is disassembled here: a toolchain change that loses the form fails loudly instead of
+    costing 14 % silently."""
+    import re
+    import shutil
+    import subprocess
+    from tstwo_b200 import _lib
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    sass = subprocess.run(["cuobjdump", "-sass", _lib.SO_PATH], capture_output=True, text=True).stdout
+    for kernel in ("merkle_leaf_tma_kernel", "merkle_node_kernel"):
+        body, on = [], False
+        for line in sass.splitlines():
+            if "Function :" in line:
+                on = kernel in line
+            elif on:
+                body.append(line)
+        forms = [m.group(1) for l in body for m in [re.search(r"\bIMAD R\d+, R\d+, (UR\d+|R\d+)[.\w]*, R\d+", l)] if m]
+        ur = sum(f.startswith("UR") for f in forms)
+        assert len(forms) >= 400, f"{kernel}: expected ~480 IMAD additions per compression, found {len(forms)}"
+        assert ur >= 0.95 * len(forms), f"{kernel}: {ur} of {len(forms)} IMAD additions use the uniform-register form"

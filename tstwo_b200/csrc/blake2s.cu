@@ -111,11 +111,11 @@ __global__ void __launch_bounds__(256) merkle_layer_kernel(const uint4 *__restri
 // its leaves): one 64-byte block per node.  Its SHAPE is chosen for ptxas: with __launch_bounds__(256, 5) (<= 51 registers) and the
 // compression inside a run-time loop (n_blocks = 1 at run time) the additions come out as IMAD R, R, UR, R -- `one` in a uniform
 // register, 1345 clk per warp-compression -- where merkle_layer_kernel's straight-line copies get the three-register form (1556 clk,
-// profiles/r01_microbench_blake2s_forms.txt).  Checked with cuobjdump at build time by tests/test_abi_cpu.py (UR form present).
+// profiles/r01_microbench_blake2s_forms.txt).  tests/test_abi_cpu.py disassembles the built library and fails if the form is lost.
 __global__ void __launch_bounds__(256, 5) merkle_node_kernel(const uint4 *__restrict__ prev, uint64_t n_nodes, uint4 *__restrict__ out,
                                                              uint32_t n_blocks, uint32_t one)
 {
-    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;   // literal block size: with blockDim.x ptxas falls back to the register form
     if (i >= n_nodes) return;
     uint32_t h[8], m[16];
     const uint4 *p = prev + 4 * i;   // 64 bytes = children 2i, 2i+1
@@ -223,9 +223,12 @@ __global__ void __launch_bounds__(LEAF_ROWS, 5) merkle_leaf_tma_kernel(const __g
 constexpr int TAIL_LOG = 9;    // 512 + 256 + ... + 1 compressions: beyond that one SM is compute-bound (a 4096-node layer alone is 22 us)
 __global__ void __launch_bounds__(1024) merkle_tail_kernel(uint4 *__restrict__ tree, int start_log, uint32_t one)
 {
+    // a layer's hashes also stay in shared memory for the layer above it (ping-pong): the chain of TAIL_LOG + 1 dependent layers
+    // then pays one compression + one barrier per layer instead of a round trip through L2 as well
+    __shared__ uint4 keep[2][2 << TAIL_LOG];
     for (int log = start_log; log >= 0; log--) {
-        const uint4 *prev = tree + 2ull * ((2ull << log) - 1);
-        uint4 *dst = tree + 2ull * ((1ull << log) - 1);
+        const uint4 *prev = log == start_log ? tree + 2ull * ((2ull << log) - 1) : keep[(log + 1) & 1];
+        uint4 *dst = tree + 2ull * ((1ull << log) - 1), *mine = keep[log & 1];
         for (uint32_t i = threadIdx.x; i < (1u << log); i += blockDim.x) {
             uint32_t h[8], m[16];
 #pragma unroll
@@ -235,10 +238,11 @@ __global__ void __launch_bounds__(1024) merkle_tail_kernel(uint4 *__restrict__ t
             }
             b2s_init(h);
             b2s_compress(h, m, 64u, true, one);
-            dst[2 * i] = make_uint4(h[0], h[1], h[2], h[3]);
-            dst[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
+            const uint4 lo = make_uint4(h[0], h[1], h[2], h[3]), hi = make_uint4(h[4], h[5], h[6], h[7]);
+            dst[2 * i] = lo; dst[2 * i + 1] = hi;
+            mine[2 * i] = lo; mine[2 * i + 1] = hi;
         }
-        __syncthreads();                               // the next layer reads what this CTA just wrote (same block: visible)
+        __syncthreads();
     }
 }
 
