@@ -107,6 +107,16 @@ int tstwo_eval_at_point(tstwo_dptr coeffs, int log_size, const uint32_t px[4], c
  * out = n_polys x 4 words. */
 int tstwo_eval_at_point_many(const tstwo_dptr *coeffs, int n_polys, int log_size, const uint32_t px[4], const uint32_t py[4],
                              uint32_t *out);
+/* tstwo_eval_at_point for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same result as
+ * tstwo_eval_at_point, bit for bit, but the partial sums live in a fixed 1.5 MiB file-scope device array (held by every GPU that
+ * loads the library until exit) instead of the library's grow-on-demand scratch, and the call performs no cudaMalloc / cudaFree /
+ * allocating library routine.  Limit: log_size <= tstwo_eval_at_point_noalloc_max_log() = 20 (2^20 coefficients); larger sizes
+ * are rejected with TSTWO_ERR_BAD_ARG and a message naming the limit.  coeffs must be 16-byte aligned for log_size >= 4.
+ * All calls share the array, which keeps the last call's contents (nothing in it needs to start at zero: every word read was
+ * written earlier in the same call); calls that overlap on the GPU -- two streams, two host threads -- race on it. */
+int tstwo_eval_at_point_noalloc(tstwo_dptr coeffs, int log_size, const uint32_t px[4], const uint32_t py[4], uint32_t out[4]);
+int tstwo_eval_at_point_noalloc_max_log(void);
 
 /* ---- MerkleOps<Blake2sHash>  (vcs/ops.ts:16-26; vcs/blake2_merkle.ts:9-24; backend/cpu/blake2.ts:98-127) --- */
 /* commitOnLayer(logSize, prevLayer, columns): out_layer = 2^log_size hashes (32 B each); prev_layer = 0 or the

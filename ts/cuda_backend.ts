@@ -60,6 +60,8 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   tstwo_twiddles_info: { args: [T.u64, T.ptr, T.ptr, T.ptr, T.ptr], returns: T.i32 },
   tstwo_eval_at_point: { args: [T.u64, T.i32, T.ptr, T.ptr, T.ptr], returns: T.i32 },
   tstwo_eval_at_point_many: { args: [T.ptr, T.i32, T.i32, T.ptr, T.ptr, T.ptr], returns: T.i32 },
+  tstwo_eval_at_point_noalloc: { args: [T.u64, T.i32, T.ptr, T.ptr, T.ptr], returns: T.i32 },
+  tstwo_eval_at_point_noalloc_max_log: { args: [], returns: T.i32 },
   tstwo_fri_decompose: { args: [T.ptr, T.i32, T.ptr, T.ptr], returns: T.i32 },
   tstwo_accumulate: { args: [T.ptr, T.ptr, T.u64], returns: T.i32 },
   tstwo_accumulate_quotients: { args: [T.i32, T.u32, T.ptr, T.i32, T.ptr, T.i32, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr], returns: T.i32 },

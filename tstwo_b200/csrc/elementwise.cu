@@ -1244,3 +1244,108 @@ int tstwo_eval_at_point_many(const tstwo_dptr *coeffs, int n_polys, int log_size
 }
 
 }  // extern "C"
+
+// ---- eval_at_point WITHOUT any allocation (tstwo_eval_at_point_noalloc) -------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels and launch sequence as
+// tstwo_eval_at_point_many for one polynomial, but the two ping-pong partial buffers live in a file-scope device array instead of
+// the library's grow-on-demand scratch (scratch() above calls cudaMalloc).  2^20 coefficients need
+// 4 * (2^16 + 2^15 + 64) = 393 472 words = 1.5 MiB: that is the array, held by every GPU that loads the library until exit.
+//   * In HOST code the array's name is a host-side stand-in, not a device address: the address is resolved with
+//     cudaGetSymbolAddress, once per device slot, with that device current, and only that pointer is given to kernels.
+//   * Every call shares the array and it keeps the last call's contents.  Nothing in it has to start at zero: each launch writes
+//     the partials the next launch reads (fold_base* fills buffer 0 completely up to cnt, every fold_qm reads only what the launch
+//     before it wrote), so there is nothing to clear.  Calls that overlap on the GPU (two streams, two host threads) RACE on it.
+constexpr int NOALLOC_MAX_LOG = 20;
+constexpr uint64_t NOALLOC_WORDS = 4ull * ((1ull << (NOALLOC_MAX_LOG - 4)) + (1ull << (NOALLOC_MAX_LOG - 5)) + 64);
+static __device__ __align__(256) uint32_t g_noalloc_scratch[NOALLOC_WORDS];
+static uint32_t *g_noalloc_ptr[MAX_SLOTS];       // device address of the array on the device of each slot (nullptr = not resolved yet)
+
+static int noalloc_scratch(uint32_t **out)
+{
+    Context &c = ctx();
+    if (c.slot < 0 || c.slot >= MAX_SLOTS) return fail(TSTWO_ERR_BAD_ARG, "tstwo_eval_at_point_noalloc: bad device slot %d", c.slot);
+    if (!g_noalloc_ptr[c.slot]) {                // once per device, with that device current (ctx_select made it so)
+        int dev = -1;
+        TS_CUDA(cudaGetDevice(&dev));
+        if (dev != c.device) TS_CUDA(cudaSetDevice(c.device));
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return fail(TSTWO_ERR_CUDA, "tstwo_eval_at_point_noalloc: cudaGetSymbolAddress failed on device %d: %s", c.device, cudaGetErrorString(e));
+        }
+        g_noalloc_ptr[c.slot] = static_cast<uint32_t *>(p);
+    }
+    *out = g_noalloc_ptr[c.slot];
+    return 0;
+}
+
+extern "C" {
+
+int tstwo_eval_at_point_noalloc_max_log(void) { return NOALLOC_MAX_LOG; }
+
+int tstwo_eval_at_point_noalloc(tstwo_dptr coeffs, int log_size, const uint32_t px[4], const uint32_t py[4], uint32_t out[4])
+{
+    TS_REQUIRE_INIT();
+    if (log_size < 0 || !coeffs || !px || !py || !out) return fail(TSTWO_ERR_BAD_ARG, "bad eval_at_point_noalloc arguments");
+    if (log_size > NOALLOC_MAX_LOG)
+        return fail(TSTWO_ERR_BAD_ARG, "tstwo_eval_at_point_noalloc: log_size %d exceeds the fixed scratch (at most 2^%d coefficients; "
+                                       "use tstwo_eval_at_point for larger polynomials)", log_size, NOALLOC_MAX_LOG);
+    Context &c = ctx();
+    if (log_size == 0) {                          // a constant: its value, no kernel
+        uint32_t c0 = 0;
+        TS_CUDA(cudaMemcpyAsync(&c0, (const void *)coeffs, 4, cudaMemcpyDeviceToHost, c.stream));
+        TS_CUDA(cudaStreamSynchronize(c.stream));
+        out[0] = c0; out[1] = out[2] = out[3] = 0;
+        return 0;
+    }
+    uint32_t *buf;
+    int rc = noalloc_scratch(&buf);
+    if (rc) return rc;
+    FoldFactors ff;
+    host::QM hf[32];
+    host::QM x = host::qld(px), one = { 1, 0, 0, 0 };
+    hf[0] = host::qld(py);
+    for (int i = 1; i < log_size; i++) {
+        hf[i] = x;
+        host::QM sx = host::qmul(x, x);
+        x = host::qsub(host::qadd(sx, sx), one);     // circle.ts:37-40 double_x
+    }
+    for (int i = 0; i < log_size; i++) ff.f[i] = { hf[i].a, hf[i].b, hf[i].c, hf[i].d };
+    BaseConsts bc;
+    memset(&bc, 0, sizeof bc);
+    if (log_size >= 4)
+        for (int k = 0; k < 16; k++) {
+            host::QM b = one;
+            for (int bit = 0; bit < 4; bit++) if (k >> bit & 1) b = host::qmul(b, hf[bit]);
+            bc.b[k][0] = b.a; bc.b[k][1] = b.b; bc.b[k][2] = b.c; bc.b[k][3] = b.d;
+        }
+    const uint64_t n = 1ull << log_size;
+    const int lv = log_size < 4 ? log_size : 4;
+    const uint64_t cnt0 = n >> lv, per_poly = 4 * (cnt0 + (cnt0 >> 1) + 64);
+    if (per_poly > NOALLOC_WORDS) return fail(TSTWO_ERR_BAD_ARG, "tstwo_eval_at_point_noalloc: internal size check failed");
+    ColSet cs = { reinterpret_cast<const uint32_t *>(coeffs), 0, nullptr };      // one column, no pointer table
+    cs.aligned16 = (coeffs & 15) == 0;
+    if (lv == 4 && !cs.aligned16) return fail(TSTWO_ERR_BAD_ARG, "tstwo_eval_at_point_noalloc: coefficients must be 16-byte aligned");
+    uint64_t cnt = cnt0;
+    uint32_t *cur = buf, *nxt = buf + 4 * cnt0;
+    if (lv == 4) TS_LAUNCH(fold_base16_kernel, dim3((unsigned)((cnt + 127) / 128), 1), 128, 0, cs, cnt, bc, cur, per_poly);
+    else TS_LAUNCH(fold_base_kernel, dim3((unsigned)((cnt + 127) / 128), 1), 128, 0, cs, cnt, lv, ff, cur, per_poly);
+    int level = lv;
+    while (cnt > 1) {
+        const int rem = log_size - level, l = rem < 4 ? rem : 4;
+        const uint64_t ncnt = cnt >> l;
+        QMats mats;
+        memset(&mats, 0, sizeof mats);
+        for (int k = 0; k < l; k++) mats.l[k] = qmat(hf[level + k]);
+        TS_LAUNCH(fold_qm_kernel, dim3((unsigned)((ncnt + 127) / 128), 1), 128, 0, cur, per_poly, ncnt, l, mats, nxt, per_poly);
+        uint32_t *t = cur; cur = nxt; nxt = t;
+        cnt = ncnt; level += l;
+    }
+    TS_CUDA(cudaMemcpyAsync(out, cur, 16, cudaMemcpyDeviceToHost, c.stream));
+    TS_CUDA(cudaStreamSynchronize(c.stream));
+    return 0;
+}
+
+}  // extern "C"
