@@ -85,6 +85,16 @@ int tstwo_gather_words(const tstwo_dptr *addrs, int n, int words_each, uint32_t 
 int tstwo_merkle_decommit(tstwo_dptr tree, int max_log, const tstwo_dptr *cols, const int *col_logs, int n_cols,
                           const int *query_offsets, const uint32_t *query_positions, uint32_t *queried_values,
                           uint8_t *hash_witness, uint32_t *column_witness, uint64_t counts[3]);
+/* FriProver.decommitOnQueries' loop over the inner layers (fri.ts:769-785; FriInnerLayerProver.decommit :533-541;
+ * computeDecommitmentPositionsAndWitnessEvals :346-384 with fold step 1) in ONE call with one synchronisation.
+ *   trees[l], evals[l][4], logs[l] : layer l's tree buffer (root first), its 4 coordinate columns and their log size
+ *   queries[n_queries]            : sorted distinct positions on layer 0's domain; folded by 1 from layer to layer
+ *   fri_witness / hash_witness / column_witness : host outputs, layer after layer (capacities in evaluations of 4 words / hashes of
+ *                                   32 bytes / words); counts[3 l ..] = {FRI witness evaluations, witness hashes, column-witness
+ *                                   words} of layer l.  Too small a capacity is an error (nothing is written). */
+int tstwo_fri_decommit_layers(int n_layers, const tstwo_dptr *trees, const tstwo_dptr *evals, const int *logs, const uint32_t *queries,
+                              int n_queries, uint32_t *fri_witness, uint64_t cap_fri_witness, uint8_t *hash_witness, uint64_t cap_hashes,
+                              uint32_t *column_witness, uint64_t cap_column_witness, uint64_t *counts);
 
 /* ---- PolyOps  (poly/circle/ops.ts:20-66; impl backend/cpu/circle.ts:17-239) -------------------------------- */
 /* precomputeTwiddles(coset): backend/cpu/circle.ts:210-239.  The tree holds 2^log words of twiddles+itwiddles. */

@@ -146,3 +146,37 @@ def test_device_proof_is_accepted_by_the_host_verifier(tb, orc, log_degrees, log
     # the verifier's transcript ends where the prover's was before it drew the queries: same query positions
     from tstwo_b200.fri import Queries
     assert Queries.generate(vchannel, max_log, n_queries).positions == by_log[max_log]
+
+
+@pytest.mark.parametrize("log_degree,n_queries", [(10, 1), (12, 9), (15, 40)])
+def test_one_call_decommit_equals_layer_by_layer(tb, orc, log_degree, n_queries):
+    """tstwo_fri_decommit_layers (every inner layer's positions, witnesses and Merkle walk in one call, one synchronisation) gives
+    the proof the per-layer loop of FriInnerLayerProver.decommit gives; a capacity that is too small is an error."""
+    import ctypes as C
+    from tstwo_b200 import _lib
+    from tstwo_b200.channel import Blake2sChannel
+    from tstwo_b200.fri import FriProver, Queries
+    log, coords = secure_column_of_degree(tb, orc, log_degree, 1, 5 * log_degree)
+    col = tb.SecureEvaluation(tb.CanonicCoset.new(log).circleDomain(), tb.SecureColumnByCoords.from_cpu(coords))
+    prover = FriProver.commit(Blake2sChannel.create(), tb.FriConfig(1, 1, n_queries), [col])
+    rng = np.random.default_rng(n_queries)
+    queries = Queries.from_positions(sorted({int(v) for v in rng.integers(0, 1 << log, n_queries)}), log)
+    one = prover.decommit_on_queries(queries)
+    FriProver.per_layer_calls = True
+    try:
+        ref = prover.decommit_on_queries(queries)
+    finally:
+        FriProver.per_layer_calls = False
+    assert len(one.inner_layers) == len(ref.inner_layers) == log - 1 - 2
+    for a, b in zip(one.inner_layers, ref.inner_layers):
+        assert [list(w) for w in a.fri_witness] == [list(w) for w in b.fri_witness]
+        assert list(a.decommitment.hashWitness) == list(b.decommitment.hashWitness)
+        assert list(a.decommitment.columnWitness) == list(b.decommitment.columnWitness) and a.commitment == b.commitment
+    # capacity check
+    L = _lib.load()
+    layer = prover.inner_layers[0]
+    counts = (C.c_uint64 * 3)()
+    w = np.zeros(4, dtype=np.uint32)
+    rc = L.tstwo_fri_decommit_layers(1, _lib.dptr_array([layer.merkle_tree.layers[0].ptr]), layer.evaluation.values.ptrs(),
+                                     (C.c_int * 1)(log - 1), _lib.u32_array([5]), 1, w.ctypes.data_as(_lib.u32p), 1, None, 0, None, 0, counts)
+    assert rc != 0 and b"capacity" in L.tstwo_last_error()

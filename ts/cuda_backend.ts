@@ -41,6 +41,7 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   tstwo_gather_words: { args: [T.ptr, T.i32, T.i32, T.ptr], returns: T.i32 },
   tstwo_grind: { args: [T.ptr, T.u32, T.ptr], returns: T.i32 },
   tstwo_merkle_decommit: { args: [T.u64, T.i32, T.ptr, T.ptr, T.i32, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr], returns: T.i32 },
+  tstwo_fri_decommit_layers: { args: [T.i32, T.ptr, T.ptr, T.ptr, T.ptr, T.i32, T.ptr, T.u64, T.ptr, T.u64, T.ptr, T.u64, T.ptr], returns: T.i32 },
   tstwo_accumulate_quotients_ex: { args: [T.i32, T.u32, T.ptr, T.i32, T.ptr, T.i32, T.ptr, T.ptr, T.ptr, T.ptr, T.ptr, T.u32], returns: T.i32 },
   // wide-Fibonacci constraint quotients over the evaluation domain (ComponentProver.evaluateConstraintQuotientsOnDomain); allocator trim
   tstwo_widefib_constraints: { args: [T.i32, T.i32, T.ptr, T.i32, T.ptr, T.ptr, T.ptr], returns: T.i32 },

@@ -74,6 +74,8 @@ SIGNATURES = {
     "tstwo_eval_at_point_noalloc": (C.c_int, [dptr, C.c_int, u32p, u32p, u32p]),
     "tstwo_eval_at_point_noalloc_max_log": (C.c_int, []),
     "tstwo_merkle_decommit": (C.c_int, [C.c_uint64, C.c_int, dptrp, intp, C.c_int, intp, u32p, u32p, C.POINTER(C.c_uint8), u32p, C.POINTER(C.c_uint64)]),
+    "tstwo_fri_decommit_layers": (C.c_int, [C.c_int, dptrp, dptrp, intp, u32p, C.c_int, u32p, C.c_uint64, C.POINTER(C.c_uint8), C.c_uint64,
+                                            u32p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "tstwo_widefib_constraints": (C.c_int, [C.c_int, C.c_int, dptrp, C.c_int, u32p, u32p, dptrp]),
     "tstwo_accumulate_quotients_ex": (C.c_int, [C.c_int, C.c_uint32, dptrp, C.c_int, u32p, C.c_int, u32p, intp, intp, u32p, dptrp, C.c_uint32]),
     "tstwo_lde_commit": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptr, C.POINTER(C.c_uint8), C.c_uint32]),

@@ -550,21 +550,18 @@ int tstwo_gather_words(const tstwo_dptr *addrs, int n, int words_each, uint32_t 
     TS_CUDA(cudaStreamSynchronize(c.stream));
     return 0;
 }
-// MerkleProver.decommit (vcs/prover.ts:32-109) in one call: the walk over the query tree on the host (nextDecommitmentNode,
-// vcs/utils.ts:40-57), then one gather launch for the witness hashes and one for the column values, one synchronisation.
-int tstwo_merkle_decommit(tstwo_dptr tree, int max_log, const tstwo_dptr *cols, const int *col_logs, int n_cols, const int *query_offsets,
-                          const uint32_t *query_positions, uint32_t *queried_values, uint8_t *hash_witness, uint32_t *column_witness,
-                          uint64_t counts[3])
+// MerkleProver.decommit (vcs/prover.ts:32-109): the walk over the query tree on the host (nextDecommitmentNode,
+// vcs/utils.ts:40-57).  Appends the device address of every witness hash (in order) and of every column value in node order
+// (is_query: the value belongs to a queried node, else it is column witness).
+static int decommit_walk(tstwo_dptr tree, int max_log, const tstwo_dptr *cols, const int *col_logs, int n_cols, const int *query_offsets,
+                         const uint32_t *query_positions, std::vector<uint64_t> &hash_addrs, std::vector<uint64_t> &value_addrs,
+                         std::vector<uint8_t> &value_is_query)
 {
-    TS_REQUIRE_INIT();
-    if (!tree || max_log < 0 || max_log > 30 || n_cols < 0 || !query_offsets || !counts) return fail(TSTWO_ERR_BAD_ARG, "bad decommit arguments");
     for (int k = 0; k < n_cols; k++)
         if (col_logs[k] < 0 || col_logs[k] > max_log || !cols[k]) return fail(TSTWO_ERR_BAD_ARG, "column %d does not fit the tree", k);
     // columns by size, largest first, stable (Array.prototype.sort in the reference)
     std::vector<std::vector<int>> by_log(max_log + 1);
     for (int k = 0; k < n_cols; k++) by_log[col_logs[k]].push_back(k);
-    std::vector<uint64_t> hash_addrs, value_addrs;
-    std::vector<uint8_t> value_is_query;
     std::vector<uint32_t> last, nxt;
     for (int log = max_log; log >= 0; log--) {
         const uint32_t *direct = query_positions + query_offsets[log];
@@ -590,20 +587,19 @@ int tstwo_merkle_decommit(tstwo_dptr tree, int max_log, const tstwo_dptr *cols, 
         }
         last.swap(nxt);
     }
-    uint64_t n_q = 0;
-    for (uint8_t q : value_is_query) n_q += q;
-    counts[0] = n_q; counts[1] = hash_addrs.size(); counts[2] = value_addrs.size() - n_q;
-    if (!queried_values && !hash_witness && !column_witness) return 0;      // sizing call
-    if ((n_q && !queried_values) || (counts[1] && !hash_witness) || (counts[2] && !column_witness))
-        return fail(TSTWO_ERR_BAD_ARG, "decommit output buffer missing");
+    return 0;
+}
+// hashes (8 words each) then single words, gathered by two launches into `words` ([8 nh | nv]); one synchronisation
+static int gather_hashes_and_words(const std::vector<uint64_t> &hash_addrs, const std::vector<uint64_t> &value_addrs, std::vector<uint32_t> &words)
+{
     const size_t nh = hash_addrs.size(), nv = value_addrs.size();
+    words.assign(8 * nh + nv, 0u);
     if (nh + nv == 0) return 0;
     Context &c = ctx();
     uint64_t *d_addrs = nullptr;
     uint32_t *d_out = nullptr;
     std::vector<uint64_t> addrs(hash_addrs);
     addrs.insert(addrs.end(), value_addrs.begin(), value_addrs.end());
-    std::vector<uint32_t> words(8 * nh + nv);
     TS_CUDA(cudaMallocAsync(&d_addrs, sizeof(uint64_t) * addrs.size(), c.stream));
     TS_CUDA(cudaMallocAsync(&d_out, 4 * words.size(), c.stream));
     TS_CUDA(cudaMemcpyAsync(d_addrs, addrs.data(), sizeof(uint64_t) * addrs.size(), cudaMemcpyHostToDevice, c.stream));
@@ -613,12 +609,110 @@ int tstwo_merkle_decommit(tstwo_dptr tree, int max_log, const tstwo_dptr *cols, 
     TS_CUDA(cudaFreeAsync(d_addrs, c.stream));
     TS_CUDA(cudaFreeAsync(d_out, c.stream));
     TS_CUDA(cudaStreamSynchronize(c.stream));
+    return 0;
+}
+int tstwo_merkle_decommit(tstwo_dptr tree, int max_log, const tstwo_dptr *cols, const int *col_logs, int n_cols, const int *query_offsets,
+                          const uint32_t *query_positions, uint32_t *queried_values, uint8_t *hash_witness, uint32_t *column_witness,
+                          uint64_t counts[3])
+{
+    TS_REQUIRE_INIT();
+    if (!tree || max_log < 0 || max_log > 30 || n_cols < 0 || !query_offsets || !counts) return fail(TSTWO_ERR_BAD_ARG, "bad decommit arguments");
+    std::vector<uint64_t> hash_addrs, value_addrs;
+    std::vector<uint8_t> value_is_query;
+    int rc = decommit_walk(tree, max_log, cols, col_logs, n_cols, query_offsets, query_positions, hash_addrs, value_addrs, value_is_query);
+    if (rc) return rc;
+    uint64_t n_q = 0;
+    for (uint8_t q : value_is_query) n_q += q;
+    counts[0] = n_q; counts[1] = hash_addrs.size(); counts[2] = value_addrs.size() - n_q;
+    if (!queried_values && !hash_witness && !column_witness) return 0;      // sizing call
+    if ((n_q && !queried_values) || (counts[1] && !hash_witness) || (counts[2] && !column_witness))
+        return fail(TSTWO_ERR_BAD_ARG, "decommit output buffer missing");
+    const size_t nh = hash_addrs.size(), nv = value_addrs.size();
+    std::vector<uint32_t> words;
+    if ((rc = gather_hashes_and_words(hash_addrs, value_addrs, words))) return rc;
     if (nh) memcpy(hash_witness, words.data(), 32 * nh);
     size_t qi = 0, wi = 0;
     for (size_t k = 0; k < nv; k++) {
         if (value_is_query[k]) queried_values[qi++] = words[8 * nh + k];
         else column_witness[wi++] = words[8 * nh + k];
     }
+    return 0;
+}
+
+// FriProver.decommitOnQueries' loop over the inner layers (fri.ts:769-785 with FriInnerLayerProver.decommit :533-541) in ONE call:
+// per layer the decommitment positions and FRI witness positions of the folded queries (computeDecommitmentPositionsAndWitnessEvals,
+// fri.ts:346-384, fold step 1), the Merkle walk of that layer's tree, then ALL witness evaluations, witness hashes and column
+// values of ALL layers are fetched by two gather launches and one synchronisation (23 layers of config 4 used to be 23 x 2 calls
+// with a synchronisation each plus the host's per-layer bookkeeping).  Outputs are concatenated layer by layer; counts[l] =
+// {FRI witness evaluations (4 words each), witness hashes, column-witness words} of layer l.
+int tstwo_fri_decommit_layers(int n_layers, const tstwo_dptr *trees, const tstwo_dptr *evals, const int *logs, const uint32_t *queries,
+                              int n_queries, uint32_t *fri_witness, uint64_t cap_fri_witness, uint8_t *hash_witness, uint64_t cap_hashes,
+                              uint32_t *column_witness, uint64_t cap_column_witness, uint64_t *counts)
+{
+    TS_REQUIRE_INIT();
+    if (n_layers < 0 || n_queries < 0 || !counts || (n_layers && (!trees || !evals || !logs)) || (n_queries && !queries))
+        return fail(TSTWO_ERR_BAD_ARG, "bad fri_decommit_layers arguments");
+    std::vector<uint32_t> q(queries, queries + n_queries), pos, folded;
+    for (int k = 1; k < n_queries; k++)
+        if (q[k] <= q[k - 1]) return fail(TSTWO_ERR_BAD_ARG, "fri_decommit_layers: queries must be sorted and distinct");
+    std::vector<uint64_t> hash_addrs, value_addrs, wit_addrs;
+    std::vector<uint8_t> value_is_query;
+    std::vector<size_t> h_end((size_t)n_layers), v_end((size_t)n_layers), w_end((size_t)n_layers);
+    std::vector<int> offsets;
+    for (int l = 0; l < n_layers; l++) {
+        const int log = logs[l];
+        if (log < 1 || log > 30 || !trees[l]) return fail(TSTWO_ERR_BAD_ARG, "fri_decommit_layers: bad layer %d", l);
+        if (!q.empty() && (q.back() >> log)) return fail(TSTWO_ERR_BAD_ARG, "fri_decommit_layers: query position outside layer %d", l);
+        // every position of every folding coset (pairs) that holds a query; those that are not queries go into the FRI witness
+        pos.clear();
+        for (size_t i = 0; i < q.size();) {
+            const uint32_t coset = q[i] >> 1;
+            bool has[2] = { false, false };
+            while (i < q.size() && (q[i] >> 1) == coset) { has[q[i] & 1] = true; i++; }
+            for (uint32_t b = 0; b < 2; b++) {
+                const uint32_t p = 2 * coset + b;
+                pos.push_back(p);
+                if (!has[b]) for (int k = 0; k < 4; k++) wit_addrs.push_back(evals[4 * l + k] + 4ull * p);
+            }
+        }
+        offsets.assign((size_t)log + 2, 0);
+        offsets[(size_t)log + 1] = (int)pos.size();
+        int col_logs[4] = { log, log, log, log };
+        int rc = decommit_walk(trees[l], log, evals + 4 * l, col_logs, 4, offsets.data(), pos.data(), hash_addrs, value_addrs, value_is_query);
+        if (rc) return rc;
+        h_end[l] = hash_addrs.size(); v_end[l] = value_addrs.size(); w_end[l] = wit_addrs.size();
+        folded.clear();
+        for (uint32_t p : q) if (folded.empty() || folded.back() != (p >> 1)) folded.push_back(p >> 1);
+        q.swap(folded);
+    }
+    // counts + capacity checks before any device work
+    uint64_t tot_w = 0, tot_h = 0, tot_c = 0;
+    for (int l = 0; l < n_layers; l++) {
+        const size_t v0 = l ? v_end[l - 1] : 0;
+        uint64_t cw = 0;
+        for (size_t k = v0; k < v_end[l]; k++) cw += !value_is_query[k];
+        counts[3 * l] = (w_end[l] - (l ? w_end[l - 1] : 0)) / 4;
+        counts[3 * l + 1] = h_end[l] - (l ? h_end[l - 1] : 0);
+        counts[3 * l + 2] = cw;
+        tot_w += counts[3 * l]; tot_h += counts[3 * l + 1]; tot_c += cw;
+    }
+    if (tot_w > cap_fri_witness || tot_h > cap_hashes || tot_c > cap_column_witness)
+        return fail(TSTWO_ERR_BAD_ARG, "fri_decommit_layers: output capacity too small (need %llu evaluations, %llu hashes, %llu words)",
+                    (unsigned long long)tot_w, (unsigned long long)tot_h, (unsigned long long)tot_c);
+    if ((tot_w && !fri_witness) || (tot_h && !hash_witness) || (tot_c && !column_witness))
+        return fail(TSTWO_ERR_BAD_ARG, "fri_decommit_layers: output buffer missing");
+    // one gather: [hashes | witness evaluation words | column values]; only the column WITNESS words are kept of the last group
+    std::vector<uint64_t> word_addrs(wit_addrs);
+    std::vector<size_t> cw_index;
+    for (size_t k = 0; k < value_addrs.size(); k++)
+        if (!value_is_query[k]) { word_addrs.push_back(value_addrs[k]); cw_index.push_back(k); }
+    std::vector<uint32_t> words;
+    int rc = gather_hashes_and_words(hash_addrs, word_addrs, words);
+    if (rc) return rc;
+    const size_t nh = hash_addrs.size();
+    if (nh) memcpy(hash_witness, words.data(), 32 * nh);
+    if (!wit_addrs.empty()) memcpy(fri_witness, words.data() + 8 * nh, 4 * wit_addrs.size());
+    if (tot_c) memcpy(column_witness, words.data() + 8 * nh + wit_addrs.size(), 4 * (size_t)tot_c);
     return 0;
 }
 int tstwo_bit_reverse(tstwo_dptr col, uint64_t len)

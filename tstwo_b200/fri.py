@@ -360,9 +360,45 @@ class FriProver:
     def decommit_on_queries(self, queries: Queries) -> FriProof:
         """fri.ts:769-785."""
         first = self.first_layer.decommit(queries)
-        inner, layer_queries = [], queries.fold(CIRCLE_TO_LINE_FOLD_STEP)
-        for layer in self.inner_layers:
-            inner.append(layer.decommit(layer_queries))
-            layer_queries = layer_queries.fold(FOLD_STEP)
-        return FriProof(first, inner, self.last_layer_poly)
+        layer_queries = queries.fold(CIRCLE_TO_LINE_FOLD_STEP)
+        if FriProver.per_layer_calls or not self.inner_layers or not all(self._tree_is_one_buffer(l) for l in self.inner_layers):
+            inner = []
+            for layer in self.inner_layers:
+                inner.append(layer.decommit(layer_queries))
+                layer_queries = layer_queries.fold(FOLD_STEP)
+            return FriProof(first, inner, self.last_layer_poly)
+        return FriProof(first, self._decommit_inner_layers_device(layer_queries), self.last_layer_poly)
+
+    @staticmethod
+    def _tree_is_one_buffer(layer: "FriInnerLayerProver") -> bool:
+        ls = layer.merkle_tree.layers
+        return all(ls[k].ptr == ls[0].ptr + 32 * ((1 << k) - 1) for k in range(len(ls)))
+
+    def _decommit_inner_layers_device(self, layer_queries: Queries) -> List[FriLayerProof]:
+        """All inner layers in ONE library call (tstwo_fri_decommit_layers): positions, FRI witnesses and Merkle walks of every
+        layer on the host inside the library, two gather launches and one synchronisation for all of them."""
+        import ctypes as C
+        L = _L()
+        n = len(self.inner_layers)
+        logs = [l.evaluation.domain().logSize() for l in self.inner_layers]
+        trees = dptr_array([l.merkle_tree.layers[0].ptr for l in self.inner_layers])
+        evals = dptr_array([c.ptr for l in self.inner_layers for c in l.evaluation.values.columns])
+        q = list(layer_queries.positions)
+        nq = len(q)
+        cap_w, cap_h = max(1, nq * n), max(1, 2 * nq * sum(logs))
+        wit = np.zeros((cap_w, 4), dtype=np.uint32)
+        hashes = np.zeros((cap_h, 32), dtype=np.uint8)
+        colw = np.zeros(max(1, 8 * nq * n), dtype=np.uint32)
+        counts = (C.c_uint64 * (3 * n))()
+        check(L.tstwo_fri_decommit_layers(n, trees, evals, (C.c_int * n)(*logs), _lib.u32_array(q if q else [0]), nq,
+                                          wit.ctypes.data_as(_lib.u32p), cap_w, hashes.ctypes.data_as(C.POINTER(C.c_uint8)), cap_h,
+                                          colw.ctypes.data_as(_lib.u32p), colw.size, counts))
+        out, wi, hi, ci = [], 0, 0, 0
+        hash_bytes = hashes.tobytes()
+        for l, layer in enumerate(self.inner_layers):
+            nw, nh, nc = int(counts[3 * l]), int(counts[3 * l + 1]), int(counts[3 * l + 2])
+            dec = MerkleDecommitment([hash_bytes[32 * k:32 * k + 32] for k in range(hi, hi + nh)], colw[ci:ci + nc].copy())
+            out.append(FriLayerProof(wit[wi:wi + nw].tolist(), dec, layer.merkle_tree.root()))
+            wi, hi, ci = wi + nw, hi + nh, ci + nc
+        return out
     decommitOnQueries = decommit_on_queries
