@@ -30,7 +30,7 @@ N_COLS, LOG_SIZE, LOG_BLOWUP = 256, 22, 1
 NCU_LAUNCHES = "profiles/r02_launches.json"
 NCU_COUNTERS = "profiles/r02_fft_ncu.json"
 # (column groups, SMs of the NVLink-bound pass) per world size for --overlap auto, from the sweeps in profiles/r01_overlap.txt
-OVERLAP_AUTO = {2: (4, 62), 4: (4, 62), 8: (4, 62)}
+OVERLAP_AUTO = {2: (4, 62), 4: (4, 62), 8: (4, 66)}    # profiles/r01_overlap.txt, r02_multi.txt
 METRIC = "lde_blake2s_commit_throughput"
 UNIT = "M31 trace elements/s"
 P = 2147483647
@@ -52,6 +52,7 @@ def parse():
                     "NVLink-bound pass running beside the next group's transforms; 'off' = one group; 'auto' = per world size")
     ap.add_argument("--fence", default="flags", choices=["flags", "nccl"],
                     help="N > 1, --exchange peer: cross-rank ordering by release/acquire flags in peer memory (default) or NCCL collectives")
+    ap.add_argument("--e2e-chunks", type=int, default=4, help="N > 1 end-to-end leg: column groups per rank crossing PCIe (the last group's LDE and the Merkle tree are exposed)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample-cols", type=int, default=0, help="columns of the CPU legs (0 = all of --cols: the whole config)")
     ap.add_argument("--no-extras", action="store_true", help="skip the config 4 (FRI) and config 5 (prove) timings")
@@ -579,7 +580,7 @@ def run_cuda(args):
         got = {}
 
         def e2e_step():
-            r = sc.step_from_host(host, stage)
+            r = sc.step_from_host(host, stage, args.e2e_chunks)
             if r is not None:
                 got["root"] = r
             else:
@@ -614,6 +615,7 @@ def run_cuda(args):
                "d2h_bytes_per_step": 32,
                "api": f"PeerShardedCommit.step_from_host (pinned host shard per rank -> root on rank 0), {world} PCIe links",
                "cpu_affinity": "NUMA node of each rank's GPU (nvmlDeviceSetCpuAffinity)" if numa_bound else "unbound",
+               "column_groups_per_rank": args.e2e_chunks,
                "h2d_only": {"ms_per_step": dh * 1e3, "gbs_per_link": lc * n * 4 / dh / 1e9, "gbs_aggregate": n_cols * n * 4 / dh / 1e9,
                             "note": "all ranks copy their pinned shard concurrently, no kernels: the PCIe / host-memory floor of the e2e step"},
                "e2e_over_floor": dt / max(dh, ms * 1e-3)}

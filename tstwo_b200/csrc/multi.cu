@@ -166,7 +166,7 @@ int ensure(int n_cols, int log_size, int log_blowup, bool need_stage)
 }
 
 // column groups / SMs of the NVLink-bound pass for the overlapped exchange (profiles/r01_overlap.txt)
-void overlap_params(int G, int *groups, int *peer_sms) { *groups = G > 1 ? 4 : 1; *peer_sms = G > 1 ? 62 : 0; }
+void overlap_params(int G, int *groups, int *peer_sms) { *groups = G > 1 ? 4 : 1; *peer_sms = G >= 8 ? 66 : G > 1 ? 62 : 0; }   // profiles/r02_multi.txt
 
 int check(int n_cols, int log_size, int log_blowup)
 {
