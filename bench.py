@@ -486,9 +486,10 @@ def run_cuda(args):
             except Exception:
                 ncu_c = {}
 
-        def entry(name, ncu_names, ms, by, launches, note=None):
+        def entry(name, ncu_names, ms, by, launches, note=None, mult=None):
             tr = [ncu_l.get(k) for k in ncu_names]
-            traffic = sum(t["dram_read_bytes"] + t["dram_write_bytes"] for t in tr) if tr and all(tr) else None
+            mult = mult or [1] * len(ncu_names)            # launches of each kernel inside one step (the JSON holds per-launch means)
+            traffic = sum(m * (t["dram_read_bytes"] + t["dram_write_bytes"]) for m, t in zip(mult, tr)) if tr and all(tr) else None
             e = {"kernel": name, "bound": "hbm", "launches_per_step": launches, "algorithmic_bytes": by, "ms": ms,
                  "achieved": by / ms / 1e6, "peak": peak, "unit": "GB/s", "frac": by / ms / 1e6 / peak,
                  "traffic": traffic, "traffic_source": NCU_LAUNCHES if traffic is not None else None, "share_of_step": ms / ms_step}
@@ -517,7 +518,10 @@ def run_cuda(args):
         t_leaf, t_nodes = kernels["merkle_leaf_layer"]["ms"], kernels["merkle_node_layers"]["ms"]
         rooflines.append(entry("merkle leaf layer (merkle_leaf_tma_kernel)", ["merkle_leaf_tma_kernel"], t_leaf, (4 * n_cols + 32) * ne, 1,
                                "integer-pipe bound (int_roofline.blake2s), not HBM bound"))
-        rooflines.append(entry(f"merkle node layers ({ext} launches of merkle_layer_kernel<1>)", [], t_nodes, 96 * (ne - 1), ext))
+        n_node_launches = max(0, ext - 10)                 # layers ext-1 .. 10 one launch each; layers 9 .. 0 in merkle_tail_kernel
+        rooflines.append(entry(f"merkle node layers (in a step: {n_node_launches} launches of merkle_node_kernel + merkle_tail_kernel; timed here layer by layer)",
+                               ["merkle_node_kernel", "merkle_tail_kernel"], t_nodes, 96 * (ne - 1), n_node_launches + 1,
+                               "integer-pipe bound like the leaf layer", mult=[n_node_launches, 1]))
         roof = entry("circle FFT: interpolate + evaluate (4 launches of fft_tma_kernel)", names_int + names_ev, t_int + t_ev,
                      (8 + 4 + 4 * (1 << blow)) * el, 4,
                      "largest share of the step; HBM is the bound SURVEY 8(d) assigns, the passes are integer-pipe / issue limited "

@@ -54,6 +54,9 @@ int tstwo_init(int device);                 /* select device, create the library
  * cross-device fences).  Slot 0 is current afterwards; tstwo_set_device(slot) makes another slot the target of every
  * following call of this thread (columns, twiddles, transforms ... are per device). */
 int tstwo_init_devices(int n_devices, const int *ids);
+/* Environment: TSTWO_CUDA_DEVICES="0,1,2,3" is the device list of tstwo_init_devices(n, NULL) (n = 0: all of them);
+ * TSTWO_TRACE=1 prints one line per span ("Interpolation for commitment", "Extension", "Merkle", ...) with its host time to
+ * stderr, TSTWO_TRACE=2 drains the stream first (device time); TSTWO_FFT_TC / TSTWO_OVERLAP_TAPER: see tstwo_cuda_debug.h. */
 int tstwo_device_count(void);               /* slots initialised (1 after tstwo_init) */
 int tstwo_set_device(int slot);
 int tstwo_shutdown(void);

@@ -18,6 +18,7 @@ that fails loudly without a B200.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Sequence
 
 import numpy as np
@@ -521,7 +522,8 @@ class CudaBackend:
 
     name = "CudaBackend"
     device = 0
-    quirks = True      # reproduce CpuBackend's log_size==3 swap; False = Stwo-correct
+    # reproduce CpuBackend's log_size==3 swap; False = Stwo-correct.  Env TSTWO_QUIRKS=0 / 1 sets the default.
+    quirks = os.environ.get("TSTWO_QUIRKS", "1") not in ("0", "false", "False", "")
     merkleOps = CudaMerkleOps()
     friOps = CudaFriOps()
 

@@ -1,5 +1,8 @@
 // libtstwo_cuda.so: lifecycle, column memory, bit-reverse and twiddle-tree entry points of include/tstwo_cuda.h.
 #include <cstdarg>
+#include <cstdlib>
+#include <ctime>
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -41,6 +44,23 @@ int fail(int code, const char *fmt, ...)
 static const int PTR_SLOTS = 4;
 static const size_t PTR_SLOT_CAP = 4096;   // addresses per slot
 void scatter_release();                     // side streams of tstwo_scatter_shards (defined with them)
+
+int trace_level()
+{
+    static const int level = [] { const char *e = getenv("TSTWO_TRACE"); return e ? atoi(e) : 0; }();
+    return level;
+}
+double trace_now()
+{
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
+void trace_span_end(const char *name, double t0)
+{
+    if (trace_level() >= 2 && ctx().ready) cudaStreamSynchronize(ctx().stream);
+    fprintf(stderr, "tstwo: %-32s %9.3f ms%s\n", name, trace_now() - t0, trace_level() >= 2 ? " (stream drained)" : "");
+}
 
 int make_colset(const tstwo_dptr *cols, int n_cols, int slot, ColSet *out)
 {
@@ -266,6 +286,24 @@ int tstwo_init(int device)
 // fan-out lives inside the library).  Slot k drives device ids[k]; every pair gets peer access (NVLink).  Slot 0 is current.
 int tstwo_init_devices(int n, const int *ids)
 {
+    // ids == NULL: the devices named by the environment, TSTWO_CUDA_DEVICES="0,1,2,3" (SURVEY 5); n = 0 takes all of them, else the first n
+    int env_ids[MAX_SLOTS];
+    if (!ids) {
+        const char *e = getenv("TSTWO_CUDA_DEVICES");
+        if (!e || !*e) return fail(TSTWO_ERR_BAD_ARG, "tstwo_init_devices: no device list given and TSTWO_CUDA_DEVICES is not set");
+        int m = 0;
+        for (const char *p = e; *p;) {
+            char *end = nullptr;
+            const long v = strtol(p, &end, 10);
+            if (end == p || v < 0 || m >= MAX_SLOTS) return fail(TSTWO_ERR_BAD_ARG, "TSTWO_CUDA_DEVICES: cannot parse '%s'", e);
+            env_ids[m++] = (int)v;
+            p = (*end == ',') ? end + 1 : end;
+            if (*end && *end != ',') return fail(TSTWO_ERR_BAD_ARG, "TSTWO_CUDA_DEVICES: cannot parse '%s'", e);
+        }
+        if (n == 0) n = m;
+        if (n > m) return fail(TSTWO_ERR_BAD_ARG, "TSTWO_CUDA_DEVICES names %d devices, %d asked for", m, n);
+        ids = env_ids;
+    }
     if (n < 1 || n > MAX_SLOTS || !ids) return fail(TSTWO_ERR_BAD_ARG, "tstwo_init_devices: 1..%d devices", MAX_SLOTS);
     for (int i = 0; i < n; i++)
         for (int j = 0; j < i; j++)

@@ -57,9 +57,16 @@ int fail(int code, const char *fmt, ...);
 // NVTX range for the lifetime of the object; the names are Stwo's tracing spans (Rust text quoted in the reference at
 // packages/core/src/pcs/prover.ts:44,92-97,180,222-226): "Commitment", "Interpolation for commitment", "Extension", "Merkle",
 // "Evaluate columns out of domain", "Grind" -- so that an Nsight timeline of a TStwo host reads like Stwo's own trace
+// TSTWO_TRACE=1 (env): every span also prints "tstwo: <span> <ms>" to stderr when it closes -- host time of the call
+// (enqueue + whatever the call waits for); TSTWO_TRACE=2 drains the library's stream first, so the figure is the device's.
+int trace_level();                                  // abi_core.cu: getenv once
+void trace_span_end(const char *name, double t0);   // prints (and drains the stream for level 2)
+double trace_now();
 struct Span {
-    explicit Span(const char *name) { nvtxRangePushA(name); }
-    ~Span() { nvtxRangePop(); }
+    const char *name_;
+    double t0_;
+    explicit Span(const char *name) : name_(name), t0_(trace_level() ? trace_now() : 0.0) { nvtxRangePushA(name); }
+    ~Span() { nvtxRangePop(); if (trace_level()) trace_span_end(name_, t0_); }
 };
 
 #define TS_CUDA(expr)                                                                              \
