@@ -698,14 +698,24 @@ def config4_fri(L, torch):
     n = 1 << log
     by = 16 * n + 32 * (n // 2) + sum(16 * m + 16 * (m // 2) + 4 * (m // 2) for m in (1 << k for k in range(log - 1, 1, -1)))
     coords = [tb.CudaCirclePoly.new(rng.integers(0, P, 1 << (log - 1), dtype=np.uint32)).evaluateWithTwiddles(dom, tw).values for _ in range(4)]
-    col = tb.SecureEvaluation(dom, tb.SecureColumnByCoords(coords))
+    # a SecureColumnByCoords as the prover's own steps produce it (accumulate_quotients, fold outputs): ONE block, four quarters
+    sc = tb.SecureColumnByCoords.uninitialized(1 << log)
+    for k in range(4):
+        L.tstwo_copy(sc.columns[k].ptr, coords[k].ptr, 4 << log)
+    del coords
+    col = tb.SecureEvaluation(dom, sc)
     cfg = tb.FriConfig(0, 1, 30)
     FriProver.commit(Blake2sChannel.create(), cfg, [col], tw); L.tstwo_sync()
-    t0 = time.perf_counter(); pr = FriProver.commit(Blake2sChannel.create(), cfg, [col], tw); L.tstwo_sync()
-    t_commit = time.perf_counter() - t0
+    t_commit, t_dec = 1e9, 1e9
+    for _ in range(3):
+        t0 = time.perf_counter(); pr = FriProver.commit(Blake2sChannel.create(), cfg, [col], tw); L.tstwo_sync()
+        t_commit = min(t_commit, time.perf_counter() - t0)
+        t0 = time.perf_counter(); pr.decommit(Blake2sChannel.create()); L.tstwo_sync()
+        t_dec = min(t_dec, time.perf_counter() - t0)
     return {"workload": "one QM31 column on CanonicCoset(24): fold_circle_into_line + 22 fold_line (to 2 elements)",
             "fold_chain_ms": best * 1e3, "fold_chain_algorithmic_bytes": by, "fold_chain_gbs": by / best / 1e9,
-            "qm31_elements_per_s": n / best, "fri_commit_ms": t_commit * 1e3, "fri_inner_layers": len(pr.inner_layers),
+            "qm31_elements_per_s": n / best, "fri_commit_ms": t_commit * 1e3, "fri_decommit_30_queries_ms": t_dec * 1e3,
+            "fri_commit_compressions": 4 * n, "fri_commit_gcompress_per_s": 4 * n / t_commit / 1e9, "fri_inner_layers": len(pr.inner_layers),
             "timing": "wall clock, device sync on both sides (23 launches; includes launch latency)"}
 
 

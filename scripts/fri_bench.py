@@ -62,7 +62,10 @@ coords = []
 for k in range(4):
     c = np.zeros(1 << deg, dtype=np.uint32); c[: 1 << deg] = rng.integers(0, P, 1 << deg, dtype=np.uint32)
     coords.append(tb.CudaCirclePoly.new(c).evaluateWithTwiddles(dom, tw).values)
-col = tb.SecureEvaluation(dom, tb.SecureColumnByCoords(coords))
+sc = tb.SecureColumnByCoords.uninitialized(1 << log)      # one block, as the prover's own steps produce a secure column
+for k in range(4):
+    L.tstwo_copy(sc.columns[k].ptr, coords[k].ptr, 4 << log)
+col = tb.SecureEvaluation(dom, sc)
 cfg = tb.FriConfig(0, 1, 30)
 def commit():
     return FriProver.commit(Blake2sChannel.create(), cfg, [col], tw)

@@ -14,7 +14,10 @@ rng = np.random.default_rng(0x5EED0004)
 dom = tb.CanonicCoset.new(log).circleDomain()
 tw = tb.CudaBackend.precomputeTwiddles(dom.halfCoset)
 coords = [tb.CudaCirclePoly.new(rng.integers(0, P, 1 << (log - 1), dtype=np.uint32)).evaluateWithTwiddles(dom, tw).values for _ in range(4)]
-col = tb.SecureEvaluation(dom, tb.SecureColumnByCoords(coords))
+sc = tb.SecureColumnByCoords.uninitialized(1 << log)      # one block, as the prover's own steps produce a secure column
+for k in range(4):
+    L.tstwo_copy(sc.columns[k].ptr, coords[k].ptr, 4 << log)
+col = tb.SecureEvaluation(dom, sc)
 cfg = tb.FriConfig(0, 1, 30)
 for rep in range(3):
     L.tstwo_sync(); t0 = time.perf_counter()
