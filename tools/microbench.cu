@@ -3,6 +3,7 @@
 // Prints one line per test: name, ops per SM per clock (from clock64), and chip-wide Gops/s (from CUDA events).
 #include <cstdint>
 #include <cstdio>
+#include <cstring>
 #include <cuda_runtime.h>
 #include "../tstwo_b200/csrc/m31.cuh"
 
@@ -98,6 +99,57 @@ __device__ __forceinline__ void compress_v(uint32_t (&h)[8], const uint32_t (&m)
     RNDX(GX, 6, 15, 14, 9, 11, 3, 0, 8, 12, 2, 13, 7, 1, 4, 10, 5); RNDX(GX, 10, 2, 8, 4, 7, 6, 1, 5, 15, 11, 9, 14, 3, 12, 13, 0);
     if (VAR == 0) { ALLR(G) } else if (VAR == 1) { ALLR(G2) } else { ALLR(G3) }
     h[0] ^= v0 ^ v8; h[1] ^= v1 ^ v9; h[2] ^= v2 ^ v10; h[3] ^= v3 ^ v11; h[4] ^= v4 ^ v12; h[5] ^= v5 ^ v13; h[6] ^= v6 ^ v14; h[7] ^= v7 ^ v15;
+}
+// ---- rotations on the FMA pipe: rotr(x, r) = lo32(x * 2^(32-r)) + hi32(x * 2^(32-r)) = IMAD.HI + IMAD (the multiplier is a
+// run-time value so that ptxas cannot turn the product back into a shift).  ROTM = 0 none, 1 = rotr7 of every second G,
+// 2 = rotr7 of every G, 3 = rotr7 and rotr12 of every G, 4 = rotr7 of one G in four.
+__device__ __forceinline__ uint32_t rotm(uint32_t x, uint32_t mul) { return x * mul + __umulhi(x, mul); }
+#define G4(a, b, c, d, x, y, U7, U12) do { a = GA(GA(a, b), (x)); d = rotr16(d ^ a); c = GA(c, d); b = (U12) ? rotm(b ^ c, c20) : rotr12(b ^ c); \
+    a = GA(GA(a, b), (y)); d = rotr8(d ^ a); c = GA(c, d); b = (U7) ? rotm(b ^ c, c25) : rotr7(b ^ c); } while (0)
+#define RND4(s0, s1, s2, s3, s4, s5, s6, s7, s8, s9, s10, s11, s12, s13, s14, s15) do { \
+    G4(v0, v4, v8, v12, m[s0], m[s1], ROTM >= 1, ROTM == 3); G4(v1, v5, v9, v13, m[s2], m[s3], ROTM == 2 || ROTM == 3, ROTM == 3); \
+    G4(v2, v6, v10, v14, m[s4], m[s5], (ROTM >= 1 && ROTM <= 3), ROTM == 3); G4(v3, v7, v11, v15, m[s6], m[s7], ROTM == 2 || ROTM == 3, ROTM == 3); \
+    G4(v0, v5, v10, v15, m[s8], m[s9], (ROTM >= 1 && ROTM <= 3), ROTM == 3); G4(v1, v6, v11, v12, m[s10], m[s11], ROTM == 2 || ROTM == 3, ROTM == 3); \
+    G4(v2, v7, v8, v13, m[s12], m[s13], ROTM >= 1, ROTM == 3); G4(v3, v4, v9, v14, m[s14], m[s15], ROTM == 2 || ROTM == 3, ROTM == 3); } while (0)
+template <int ROTM>
+__device__ __forceinline__ void compress_r(uint32_t (&h)[8], const uint32_t (&m)[16], uint32_t t, uint32_t one, uint32_t c25, uint32_t c20)
+{
+    uint32_t v0 = h[0], v1 = h[1], v2 = h[2], v3 = h[3], v4 = h[4], v5 = h[5], v6 = h[6], v7 = h[7];
+    uint32_t v8 = 0x6A09E667u, v9 = 0xBB67AE85u, v10 = 0x3C6EF372u, v11 = 0xA54FF53Au, v12 = 0x510E527Fu ^ t, v13 = 0x9B05688Cu, v14 = 0x1F83D9ABu, v15 = 0x5BE0CD19u;
+    RND4(0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15); RND4(14, 10, 4, 8, 9, 15, 13, 6, 1, 12, 0, 2, 11, 7, 5, 3);
+    RND4(11, 8, 12, 0, 5, 2, 15, 13, 10, 14, 3, 6, 7, 1, 9, 4); RND4(7, 9, 3, 1, 13, 12, 11, 14, 2, 6, 5, 10, 4, 0, 15, 8);
+    RND4(9, 0, 5, 7, 2, 4, 10, 15, 14, 1, 11, 12, 6, 8, 3, 13); RND4(2, 12, 6, 10, 0, 11, 8, 3, 4, 13, 7, 5, 15, 14, 1, 9);
+    RND4(12, 5, 1, 15, 14, 13, 4, 10, 0, 7, 6, 3, 9, 2, 8, 11); RND4(13, 11, 7, 14, 12, 1, 3, 9, 5, 0, 15, 4, 8, 6, 2, 10);
+    RND4(6, 15, 14, 9, 11, 3, 0, 8, 12, 2, 13, 7, 1, 4, 10, 5); RND4(10, 2, 8, 4, 7, 6, 1, 5, 15, 11, 9, 14, 3, 12, 13, 0);
+    h[0] ^= v0 ^ v8; h[1] ^= v1 ^ v9; h[2] ^= v2 ^ v10; h[3] ^= v3 ^ v11; h[4] ^= v4 ^ v12; h[5] ^= v5 ^ v13; h[6] ^= v6 ^ v14; h[7] ^= v7 ^ v15;
+}
+template <int ROTM>
+__global__ void __launch_bounds__(256) k_blake_rot(uint32_t *out, unsigned long long n_rows, int blocks, uint32_t one, uint32_t c25, uint32_t c20)
+{
+    for (unsigned long long row0 = (unsigned long long)blockIdx.x * 256; row0 < n_rows; row0 += (unsigned long long)gridDim.x * 256) {
+        uint32_t h[8], m[16];
+        const unsigned long long i = row0 + threadIdx.x;
+        for (int k = 0; k < 8; k++) h[k] = threadIdx.x * 31 + k;
+        for (int k = 0; k < 16; k++) m[k] = threadIdx.x * 17 + k * 3 + blockIdx.x;
+        for (int b = 0; b < blocks; b++) compress_r<ROTM>(h, m, b, one, c25, c20);
+        uint32_t s = 0;
+        for (int k = 0; k < 8; k++) s ^= h[k];
+        out[i] = s;
+    }
+}
+template <int ROTM> int run_rot(const char *name, uint32_t *out, unsigned long long n_rows, int blocks, int sms, uint32_t *check)
+{
+    const int grid = (int)(n_rows / 256);
+    cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    k_blake_rot<ROTM><<<grid, 256>>>(out, n_rows, blocks, 1u, 1u << 25, 1u << 20); CK(cudaDeviceSynchronize());
+    CK(cudaEventRecord(e0)); k_blake_rot<ROTM><<<grid, 256>>>(out, n_rows, blocks, 1u, 1u << 25, 1u << 20); CK(cudaEventRecord(e1)); CK(cudaDeviceSynchronize());
+    float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+    uint32_t first[4]; CK(cudaMemcpy(first, out, 16, cudaMemcpyDeviceToHost));
+    if (ROTM == 0) memcpy(check, first, 16);
+    double comp = (double)n_rows * blocks;
+    printf("blake2s rotations on the FMA pipe: %-34s chip %7.2f Gcompress/s  => %.0f clk per warp-compress per SMSP (%.3f ms) %s\n",
+           name, comp / ms / 1e6, 1.965e9 / (comp / (ms * 1e-3) / 32 / (sms * 4)), ms, memcmp(check, first, 16) ? "RESULT DIFFERS" : "same result");
+    return 0;
 }
 template <int VAR>
 __global__ void __launch_bounds__(256) k_blake_v(uint32_t *out, int iters, uint32_t one)
@@ -233,6 +285,14 @@ int main()
         const int cols = 256;
         uint32_t *in, *o2; CK(cudaMalloc(&in, n_rows * cols * 4)); CK(cudaMalloc(&o2, n_rows * 4)); CK(cudaMemset(in, 5, n_rows * cols * 4));
         run_shape<0>("registers, one CTA per row tile", (int)(n_rows / 256), o2, in, n_rows, cols / 16, sms);
+        {
+            uint32_t chk[4];
+            run_rot<0>("none (SHF for 12 and 7)", o2, n_rows, cols / 16, sms, chk);
+            run_rot<4>("rotr7 of 1 G in 4 (20 of 320)", o2, n_rows, cols / 16, sms, chk);
+            run_rot<1>("rotr7 of every second G (40)", o2, n_rows, cols / 16, sms, chk);
+            run_rot<2>("rotr7 of every G (80)", o2, n_rows, cols / 16, sms, chk);
+            run_rot<3>("rotr7 and rotr12 of every G (160)", o2, n_rows, cols / 16, sms, chk);
+        }
         run_shape<0>("registers, persistent (4 CTAs/SM)", sms * 4, o2, in, n_rows, cols / 16, sms);
         run_shape<1>("column loads, one CTA per row tile", (int)(n_rows / 256), o2, in, n_rows, cols / 16, sms);
         run_shape<1>("column loads, persistent (4 CTAs/SM)", sms * 4, o2, in, n_rows, cols / 16, sms);
