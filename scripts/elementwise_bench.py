@@ -48,4 +48,4 @@ for log, cnt in ((20, 100), (23, 100)):
     res = (C.c_uint32 * (4 * cnt))()
     px, py = u32_array([1, 0, 478637715, 513582971]), u32_array([992285211, 649143431, 740191619, 1186584352])
     report(f"eval_at_point_many {cnt} x 2^{log} coefficients", timed(lambda: check(L.tstwo_eval_at_point_many(ptrs, cnt, log, px, py, res)), 5),
-           cnt * (5 << log))          # reads 4 B per coefficient, writes + re-reads n/16 QM31 partials
+           cnt * (4 << log))          # every coefficient read once; the partial sums are n / 2048 QM31 values
