@@ -40,7 +40,7 @@ def main():
         nice = names.get(mangled, mangled)
         if not any(p.search(nice) for p in pats):
             continue
-        short = re.sub(r"\(.*", "", nice).replace("tstwo::(anonymous namespace)::", "").replace("(anonymous namespace)::", "")
+        short = re.sub(r"\(.*", "", nice.replace("(anonymous namespace)::", ""))
         mix = collections.Counter()
         for _, text in ins:
             ops = [o for o in text.split() if not o.startswith("@")]
