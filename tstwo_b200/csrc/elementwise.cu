@@ -28,43 +28,95 @@ __device__ __forceinline__ uint32_t pair_itw2(const uint32_t *tab, int mode, uin
 // fri.ts:120-152 / backend/cpu/fri.ts:23-51: out[i] = f0 + alpha f1, (f0, f1) = ibutterfly(f(x), f(-x), 1/x)
 // alpha_dev != nullptr: the folding coefficient is read from device memory (written by fri_channel_kernel: the transcript stays
 // on the device between the layers of tstwo_fri_commit_layers)
-__global__ void fold_line_kernel(CQ4 src, Q4 dst, uint64_t n_out, const uint32_t *itab, int mode, m31::QM alpha, const uint32_t *alpha_dev = nullptr)
+// V = outputs per thread: 2 when the columns allow 16-byte loads / 8-byte stores (n_out even, aligned), else 1.
+template <int V>
+__global__ void __launch_bounds__(256) fold_line_kernel(CQ4 src, Q4 dst, uint64_t n_out, const uint32_t *itab, int mode, m31::QM alpha,
+                                                        const uint32_t *alpha_dev = nullptr)
 {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, i = V * t;
     if (i >= n_out) return;
     if (alpha_dev) alpha = { alpha_dev[0], alpha_dev[1], alpha_dev[2], alpha_dev[3] };
-    uint32_t it2 = pair_itw2(itab, mode, i);
-    uint32_t f0[4], f1[4];
+    uint32_t it2[V];
+#pragma unroll
+    for (int v = 0; v < V; v++) it2[v] = pair_itw2(itab, mode, i + v);
+    uint32_t f0[V][4], f1[V][4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        uint2 p = __ldcs(reinterpret_cast<const uint2 *>(src.c[k]) + i);
-        f0[k] = p.x; f1[k] = p.y;
-        m31::ibutterfly(f0[k], f1[k], it2);
+        if (V == 2) {
+            const uint4 p = __ldcs(reinterpret_cast<const uint4 *>(src.c[k]) + t);
+            f0[0][k] = p.x; f1[0][k] = p.y; f0[V - 1][k] = p.z; f1[V - 1][k] = p.w;
+        } else {
+            const uint2 p = __ldcs(reinterpret_cast<const uint2 *>(src.c[k]) + t);
+            f0[0][k] = p.x; f1[0][k] = p.y;
+        }
+#pragma unroll
+        for (int v = 0; v < V; v++) m31::ibutterfly(f0[v][k], f1[v][k], it2[v]);
     }
-    m31::QM r = m31::qadd({ f0[0], f0[1], f0[2], f0[3] }, m31::qmul(alpha, { f1[0], f1[1], f1[2], f1[3] }));
-    dst.c[0][i] = r.a; dst.c[1][i] = r.b; dst.c[2][i] = r.c; dst.c[3][i] = r.d;
+    m31::QM r[V];
+#pragma unroll
+    for (int v = 0; v < V; v++)
+        r[v] = m31::qadd({ f0[v][0], f0[v][1], f0[v][2], f0[v][3] }, m31::qmul(alpha, { f1[v][0], f1[v][1], f1[v][2], f1[v][3] }));
+    if (V == 2) {
+        reinterpret_cast<uint2 *>(dst.c[0])[t] = make_uint2(r[0].a, r[V - 1].a); reinterpret_cast<uint2 *>(dst.c[1])[t] = make_uint2(r[0].b, r[V - 1].b);
+        reinterpret_cast<uint2 *>(dst.c[2])[t] = make_uint2(r[0].c, r[V - 1].c); reinterpret_cast<uint2 *>(dst.c[3])[t] = make_uint2(r[0].d, r[V - 1].d);
+    } else {
+        dst.c[0][i] = r[0].a; dst.c[1][i] = r[0].b; dst.c[2][i] = r[0].c; dst.c[3][i] = r[0].d;
+    }
 }
 
 // fri.ts:162-192 / backend/cpu/fri.ts:61-92: dst[i] = dst[i] alpha^2 + (alpha f1 + f0), twiddle 1/p.y
-__global__ void fold_circle_kernel(CQ4 src, Q4 dst, uint64_t n_out, const uint32_t *itab, int mode, m31::QM alpha,
-                                   m31::QM alpha_sq, const uint32_t *alpha_dev = nullptr)
+template <int V>
+__global__ void __launch_bounds__(256) fold_circle_kernel(CQ4 src, Q4 dst, uint64_t n_out, const uint32_t *itab, int mode, m31::QM alpha,
+                                                          m31::QM alpha_sq, const uint32_t *alpha_dev = nullptr)
 {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, i = V * t;
     if (i >= n_out) return;
     if (alpha_dev) { alpha = { alpha_dev[0], alpha_dev[1], alpha_dev[2], alpha_dev[3] }; alpha_sq = m31::qmul(alpha, alpha); }
-    uint32_t it2 = pair_itw2(itab, mode, i);
-    uint32_t f0[4], f1[4];
+    uint32_t it2[V];
+#pragma unroll
+    for (int v = 0; v < V; v++) it2[v] = pair_itw2(itab, mode, i + v);
+    uint32_t f0[V][4], f1[V][4], cur[V][4];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        uint2 p = __ldcs(reinterpret_cast<const uint2 *>(src.c[k]) + i);
-        f0[k] = p.x; f1[k] = p.y;
-        m31::ibutterfly(f0[k], f1[k], it2);
+        if (V == 2) {
+            const uint4 p = __ldcs(reinterpret_cast<const uint4 *>(src.c[k]) + t);
+            f0[0][k] = p.x; f1[0][k] = p.y; f0[V - 1][k] = p.z; f1[V - 1][k] = p.w;
+            const uint2 c = reinterpret_cast<const uint2 *>(dst.c[k])[t];
+            cur[0][k] = c.x; cur[V - 1][k] = c.y;
+        } else {
+            const uint2 p = __ldcs(reinterpret_cast<const uint2 *>(src.c[k]) + t);
+            f0[0][k] = p.x; f1[0][k] = p.y;
+            cur[0][k] = dst.c[k][i];
+        }
+#pragma unroll
+        for (int v = 0; v < V; v++) m31::ibutterfly(f0[v][k], f1[v][k], it2[v]);
     }
-    m31::QM fp = m31::qadd(m31::qmul(alpha, { f1[0], f1[1], f1[2], f1[3] }), { f0[0], f0[1], f0[2], f0[3] });
-    m31::QM cur = { dst.c[0][i], dst.c[1][i], dst.c[2][i], dst.c[3][i] };
-    m31::QM r = m31::qadd(m31::qmul(cur, alpha_sq), fp);
-    dst.c[0][i] = r.a; dst.c[1][i] = r.b; dst.c[2][i] = r.c; dst.c[3][i] = r.d;
+    m31::QM r[V];
+#pragma unroll
+    for (int v = 0; v < V; v++) {
+        const m31::QM fp = m31::qadd(m31::qmul(alpha, { f1[v][0], f1[v][1], f1[v][2], f1[v][3] }), { f0[v][0], f0[v][1], f0[v][2], f0[v][3] });
+        r[v] = m31::qadd(m31::qmul({ cur[v][0], cur[v][1], cur[v][2], cur[v][3] }, alpha_sq), fp);
+    }
+    if (V == 2) {
+        reinterpret_cast<uint2 *>(dst.c[0])[t] = make_uint2(r[0].a, r[V - 1].a); reinterpret_cast<uint2 *>(dst.c[1])[t] = make_uint2(r[0].b, r[V - 1].b);
+        reinterpret_cast<uint2 *>(dst.c[2])[t] = make_uint2(r[0].c, r[V - 1].c); reinterpret_cast<uint2 *>(dst.c[3])[t] = make_uint2(r[0].d, r[V - 1].d);
+    } else {
+        dst.c[0][i] = r[0].a; dst.c[1][i] = r[0].b; dst.c[2][i] = r[0].c; dst.c[3][i] = r[0].d;
+    }
 }
+// two outputs per thread when every column allows it
+static bool fold_vec2(const CQ4 &s, const Q4 &d, uint64_t n_out)
+{
+    if (n_out < 2 || (n_out & 1)) return false;
+    for (int k = 0; k < 4; k++)
+        if ((reinterpret_cast<uintptr_t>(s.c[k]) & 15) || (reinterpret_cast<uintptr_t>(d.c[k]) & 7)) return false;
+    return true;
+}
+#define LAUNCH_FOLD(kernel, s, d, n_out, ...)                                                                          \
+    do {                                                                                                               \
+        if (fold_vec2(s, d, n_out)) TS_LAUNCH(kernel<2>, (unsigned)((n_out / 2 + 255) / 256), 256, 0, s, d, n_out, __VA_ARGS__); \
+        else TS_LAUNCH(kernel<1>, (unsigned)((n_out + 255) / 256), 256, 0, s, d, n_out, __VA_ARGS__);                 \
+    } while (0)
 
 // backend/cpu/fri.ts:97-123 decompositionCoefficient: 8 sums (4 coordinates x 2 halves) as u64
 __global__ void half_sums_kernel(CQ4 src, uint64_t n, unsigned long long *sums)
@@ -149,6 +201,17 @@ __global__ void accumulate_kernel(Q4 dst, CQ4 src, uint64_t n)
     if (i >= n) return;
 #pragma unroll
     for (int k = 0; k < 4; k++) dst.c[k][i] = m31::add(dst.c[k][i], src.c[k][i]);
+}
+__global__ void __launch_bounds__(256) accumulate_vec_kernel(Q4 dst, CQ4 src, uint64_t n4)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n4) return;
+    uint4 a[4], b[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) { a[k] = reinterpret_cast<const uint4 *>(dst.c[k])[i]; b[k] = __ldcs(reinterpret_cast<const uint4 *>(src.c[k]) + i); }
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        reinterpret_cast<uint4 *>(dst.c[k])[i] = make_uint4(m31::add(a[k].x, b[k].x), m31::add(a[k].y, b[k].y), m31::add(a[k].z, b[k].z), m31::add(a[k].w, b[k].w));
 }
 
 // backend/cpu/quotients.ts:52-116.  One thread per row.  The reference evaluates, per sampled column j of a batch,
@@ -849,7 +912,7 @@ int tstwo_fold_line(const tstwo_dptr src[4], int log_size, uint32_t coset_init, 
         if ((rc = launch_coset_points(tmp, 0, coset_init & 0x7fffffffu, log_size, log_size - 1))) return rc;
         itab = tmp;
     }
-    TS_LAUNCH(fold_line_kernel, (unsigned)((n_out + 255) / 256), 256, 0, s, d, n_out, itab, 0, to_dev(alpha));
+    LAUNCH_FOLD(fold_line_kernel, s, d, n_out, itab, 0, to_dev(alpha), (const uint32_t *)nullptr);
     return 0;
 }
 
@@ -880,7 +943,7 @@ int tstwo_fold_circle_into_line(const tstwo_dptr dst[4], const tstwo_dptr src[4]
     host::QM a = host::qld(alpha), a2 = host::qmul(a, a);
     uint32_t a2v[4];
     host::qst(a2v, a2);
-    TS_LAUNCH(fold_circle_kernel, (unsigned)((n_out + 255) / 256), 256, 0, s, d, n_out, itab, mode, to_dev(alpha), to_dev(a2v));
+    LAUNCH_FOLD(fold_circle_kernel, s, d, n_out, itab, mode, to_dev(alpha), to_dev(a2v), (const uint32_t *)nullptr);
     return 0;
 }
 
@@ -948,7 +1011,7 @@ int tstwo_fri_commit_layers(const tstwo_dptr first[4], int first_log, uint32_t f
                     if ((rc = launch_coset_points(tmp, 0, coset, log, log - 1))) return rc;
                     itab = tmp;
                 }
-                TS_LAUNCH(fold_line_kernel, (unsigned)((n_out + 255) / 256), 256, 0, s4, d4, n_out, itab, 0, to_dev(zero_alpha), d_alpha + 4 * l);
+                LAUNCH_FOLD(fold_line_kernel, s4, d4, n_out, itab, 0, to_dev(zero_alpha), (const uint32_t *)(d_alpha + 4 * l));
             }
             coset = (coset * 2u) & 0x7fffffffu;
             // a circle column whose folded size equals the new layer joins it, with the same alpha (fri.ts:704-711)
@@ -969,7 +1032,7 @@ int tstwo_fri_commit_layers(const tstwo_dptr first[4], int first_log, uint32_t f
                     if ((rc = launch_coset_points(tmp, 1, half_init, half_log, half_log))) return rc;
                     itab = tmp;
                 }
-                TS_LAUNCH(fold_circle_kernel, (unsigned)((n_out + 255) / 256), 256, 0, s4, d4, n_out, itab, mode, to_dev(zero_alpha), to_dev(zero_alpha), d_alpha + 4 * l);
+                LAUNCH_FOLD(fold_circle_kernel, s4, d4, n_out, itab, mode, to_dev(zero_alpha), to_dev(zero_alpha), (const uint32_t *)(d_alpha + 4 * l));
                 pending++;
             }
             for (int k = 0; k < 4; k++) cur[k] = nxt[k];
@@ -1026,7 +1089,10 @@ int tstwo_accumulate(const tstwo_dptr dst[4], const tstwo_dptr src[4], uint64_t 
     if (len == 0) return 0;
     CQ4 s; Q4 d;
     for (int k = 0; k < 4; k++) { s.c[k] = (const uint32_t *)src[k]; d.c[k] = (uint32_t *)dst[k]; }
-    TS_LAUNCH(accumulate_kernel, (unsigned)((len + 255) / 256), 256, 0, d, s, len);
+    bool vec = len >= 4 && (len & 3) == 0;
+    for (int k = 0; k < 4; k++) vec = vec && !((reinterpret_cast<uintptr_t>(d.c[k]) | reinterpret_cast<uintptr_t>(s.c[k])) & 15);
+    if (vec) TS_LAUNCH(accumulate_vec_kernel, (unsigned)((len / 4 + 255) / 256), 256, 0, d, s, len / 4);
+    else TS_LAUNCH(accumulate_kernel, (unsigned)((len + 255) / 256), 256, 0, d, s, len);
     return 0;
 }
 
