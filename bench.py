@@ -52,7 +52,7 @@ def parse():
                     "NVLink-bound pass running beside the next group's transforms; 'off' = one group; 'auto' = per world size")
     ap.add_argument("--fence", default="flags", choices=["flags", "nccl"],
                     help="N > 1, --exchange peer: cross-rank ordering by release/acquire flags in peer memory (default) or NCCL collectives")
-    ap.add_argument("--e2e-chunks", type=int, default=4, help="N > 1 end-to-end leg: column groups per rank crossing PCIe (the last group's LDE and the Merkle tree are exposed)")
+    ap.add_argument("--e2e-chunks", type=int, default=8, help="N > 1 end-to-end leg: column groups per rank crossing PCIe (the last group's LDE and the Merkle tree are exposed)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample-cols", type=int, default=0, help="columns of the CPU legs (0 = all of --cols: the whole config)")
     ap.add_argument("--no-extras", action="store_true", help="skip the config 4 (FRI) and config 5 (prove) timings")
@@ -460,6 +460,20 @@ def run_cuda(args):
                             "reference": "770 GB/s per direction measured peer copy (B200_PROFILING.md), 900 nominal"}
         phases["note"] = ("CUDA events on each rank's stream; a rank's fence / gather time includes waiting for the slowest peer. "
                           "single-GPU pure LDE of the same shard = kernels.passes of the N=1 line / N")
+        # the same roofline entries as the N = 1 line, per rank: the LDE phase (the four FFT passes of the rank's column shard, the
+        # last one storing into the peers) and the leaf layer + subtree of the rank's row shard, against the measured HBM peak
+        try:
+            pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs") or 6650.0
+        except Exception:
+            pk = 6650.0
+        el = lc * n
+        by_lde, by_merkle = (8 + 4 + 4 * (1 << blow)) * el, (4 * n_cols + 32 + 96) * (ne // world)
+        mk = lambda name, by, t_ms, note: {"kernel": name, "bound": "hbm", "algorithmic_bytes": by, "ms": t_ms, "achieved": by / t_ms / 1e6, "peak": pk,
+                                           "unit": "GB/s", "frac": by / t_ms / 1e6 / pk, "traffic": None, "share_of_step": t_ms / ms, "note": note}
+        phases["rooflines_per_rank"] = [
+            mk("circle FFT of the rank's column shard (4 x column groups x fft_tma_kernel, last pass stores to the peers)", by_lde, float(mx[0]),
+               "integer-pipe bound as at N = 1; at N = 8 the peer stores (573 GB/s all-to-all) bound this phase (profiles/r02_multi.txt)"),
+            mk("merkle leaf layer + subtree of the rank's row shard", by_merkle, float(mx[2]), "integer-pipe bound (BLAKE2s)")]
         barrier()
 
     # ---- per-kernel timing (1 GPU), live CUDA events: `roofline` = the phase with the largest share of the step (the four
@@ -657,7 +671,9 @@ def run_cuda(args):
             "sass_patch": sass_patch,
         }
         if extras: out["extras"] = extras
-        if phases: out["phases"] = phases
+        if phases:
+            out["phases"] = phases
+            out["roofline"] = dict(phases["rooflines_per_rank"][0], per="rank")
         if roof: out["roofline"] = roof
         if rooflines: out["rooflines"] = rooflines
         if int_roof: out["int_roofline"] = int_roof
