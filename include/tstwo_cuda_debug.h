@@ -17,6 +17,9 @@ extern "C" {
 int tstwo_debug_set_fft_stream(int mode);
 /* per-layer kernels only (the on-device cross-check of the tiled passes) */
 int tstwo_debug_force_naive_fft(int on);
+/* the 512-row (9-layer) strided pass of the bulk-copy family, planned when exactly nine layers remain above the contiguous pass
+ * (log size 23); 0 = plan an 8-layer window plus a one-layer pass as before (default 1) */
+int tstwo_debug_set_fft_rows9(int on);
 /* rows per thread of the fft.cu family: 16 (default) or 8 */
 int tstwo_debug_set_fft_radix(int rows_per_thread);
 /* what the last transform ran: bit 0 tiled, bits 1.. family */

@@ -123,3 +123,34 @@ def test_partial_top_pass_repeats_exactly(tb):
                 assert (back.values.toCpu() == vals).all()
     finally:
         L.tstwo_debug_set_fft_stream(2)
+
+
+@pytest.mark.parametrize("blow,n_cols", [(0, 1), (1, 3), (2, 2)])
+def test_nine_layer_window_log23(tb, orc, blow, n_cols):
+    """Log size 23 leaves exactly nine layers above the 14-layer contiguous pass: the bulk-copy family then runs ONE 512-row
+    strided pass (fft_tma_kernel<.., R9>) instead of an 8-layer window plus a one-layer pass.  Coefficients, evaluations (also with
+    blow-up, where the pass reads the zero-extended coefficients coset by coset) and the Merkle root must equal what the planner
+    without that pass gives (tstwo_debug_set_fft_rows9(0)), and column 0 must equal the oracle's transform."""
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    log = 23
+    ext = log + blow
+    root_coset = tb.CanonicCoset.new(ext).half_coset()
+    tw = tb.CudaBackend.precomputeTwiddles(root_coset)
+    trace = np.random.default_rng(2300 + 10 * blow + n_cols).integers(0, P, (n_cols, 1 << log), dtype=np.uint32)
+    res = {}
+    try:
+        for on in (1, 0):
+            L.tstwo_debug_set_fft_rows9(on)
+            res[on] = _lde(tb, L, 2, trace, n_cols, log, blow, tw)
+            assert res[on][3] == 2
+    finally:
+        L.tstwo_debug_set_fft_rows9(1)
+    assert res[1][2] == res[0][2], "Merkle root differs with the 512-row pass"
+    for c in range(n_cols):
+        assert (res[1][0][c] == res[0][0][c]).all(), f"coefficients differ (column {c})"
+        assert (res[1][1][c] == res[0][1][c]).all(), f"evaluations differ (column {c})"
+    otw, oitw = orc.precompute_twiddles(root_coset.initial_index.value, root_coset.log_size)
+    orc.use_all_cores()
+    coeffs, evals, _ = orc.lde_commit(trace[:1], blow, otw, oitw, want_coeffs=True, want_layers=False)
+    assert (res[1][0][0] == coeffs[0]).all() and (res[1][1][0] == evals[0]).all()

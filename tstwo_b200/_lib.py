@@ -97,6 +97,7 @@ SIGNATURES = {
 DEBUG_SIGNATURES = {
     "tstwo_debug_set_fft_stream": (C.c_int, [C.c_int]),
     "tstwo_debug_force_naive_fft": (C.c_int, [C.c_int]),
+    "tstwo_debug_set_fft_rows9": (C.c_int, [C.c_int]),
     "tstwo_debug_set_fft_radix": (C.c_int, [C.c_int]),
     "tstwo_debug_last_fft_mode": (C.c_int, []),
     "tstwo_debug_set_fft_tc": (C.c_int, [C.c_int]),

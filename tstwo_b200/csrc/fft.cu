@@ -379,19 +379,23 @@ static int ensure_smem_attr()
     return 0;
 }
 
-struct Pass { int lo, j_min; };
+struct Pass { int lo, j_min, win; };
 // passes in ascending layer order for L real layers (scripts/proto_fft.py): one contiguous 12-layer pass, then
 // strided 10-layer windows; the top window is aligned to L and skips the layers already done.
 // The TMA passes (fft_tma.cu) use a 14-layer contiguous pass and 8-layer strided windows instead.
 constexpr int W0 = Shape<false, 3>::RHO, W1 = Shape<true, 3>::RHO;
 constexpr int MAX_PASSES = 4;
+static int g_rows9 = 1;        // tstwo_debug_set_fft_rows9: 0 = never plan the 512-row pass
 static int plan_passes(int L, Pass out[MAX_PASSES], int w0, int w1)
 {
     int np = 0, done = w0;
-    out[np++] = { 0, 0 };
+    out[np++] = { 0, 0, 0 };
     if (L <= done) return np;
-    while (L - done > w1) { out[np++] = { done, 0 }; done += w1; }
-    out[np++] = { L - w1, done - (L - w1) };
+    // exactly nine layers left above the bulk-copy contiguous pass (L = 23: config 5's trace): ONE 512-row pass instead of an
+    // 8-layer window plus a pass that moves every byte again for a single layer (100 x 2^23: 13.7 -> ~10.5 ms per LDE)
+    if (g_rows9 && w0 == TMA_W0 && w1 == TMA_W1 && L - done == TMA_W9) { out[np++] = { done, 0, TMA_W9 }; return np; }
+    while (L - done > w1) { out[np++] = { done, 0, 0 }; done += w1; }
+    out[np++] = { L - w1, done - (L - w1), 0 };
     return np;
 }
 
@@ -434,7 +438,7 @@ static int pick_mode(bool inverse, const ColSet &src, const ColSet &dst, const C
     const int np = plan_passes(L, ps, TMA_W0, TMA_W1);
     for (int k = 0; k < np; k++) {
         PassParams p;
-        p.n_cols = n_cols; p.lo = ps[k].lo;
+        p.n_cols = n_cols; p.lo = ps[k].lo; p.win = ps[k].win;
         if (inverse) { p.src = (k == 0) ? src : dst; p.dst = dst; }
         else { p.src = (k == np - 1) ? src : work; p.dst = (k == 0) ? dst : work; }
         if (!tma_pass_supported(p)) return 1;
@@ -460,7 +464,7 @@ int fft_interpolate(const ColSet &src, const ColSet &dst, int n_cols, int n, con
         for (int k = 0; k < np; k++) {
             PassParams p;
             p.src = (k == 0) ? src : dst; p.dst = dst; p.n_cols = n_cols; p.n = n; p.src_mask = (uint32_t)(N - 1);
-            p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.tw2 = t->itw2; p.tree_len = tree_len;
+            p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.win = ps[k].win; p.tw2 = t->itw2; p.tree_len = tree_len;
             p.scale2 = (k == np - 1) ? inv_n2 : 0; p.zero = 0;
             rc = launch_pass(mode, true, p);
             if (rc) return rc;
@@ -509,7 +513,7 @@ int fft_evaluate(const ColSet &src, int L, const ColSet &dst, int n_cols, int n,
             const bool first = (k == np - 1);
             p.src = first ? src : work; p.dst = (k == 0) ? dst : work; p.n_cols = n_cols; p.n = n;
             p.src_mask = first ? (uint32_t)((1ull << L) - 1) : (uint32_t)(N - 1);
-            p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.tw2 = t->tw2; p.tree_len = tree_len; p.scale2 = 0; p.zero = 0;
+            p.lo = ps[k].lo; p.j_min = ps[k].j_min; p.win = ps[k].win; p.tw2 = t->tw2; p.tree_len = tree_len; p.scale2 = 0; p.zero = 0;
             rc = launch_pass(mode, false, p);
             if (rc) return rc;
         }
@@ -539,6 +543,7 @@ extern "C" {
 
 // test hook: force the per-layer kernels for every size (used by tests to cross-check the tiled passes on device)
 int tstwo_debug_force_naive_fft(int on) { g_force_naive = on != 0; return 0; }
+int tstwo_debug_set_fft_rows9(int on) { g_rows9 = on != 0; return 0; }
 // tuning hook: rows per thread of the tiled passes (8 -> 512-thread CTAs, 16 -> 256-thread CTAs)
 int tstwo_debug_set_fft_radix(int rows_per_thread) { g_dig = rows_per_thread == 8 ? 3 : 4; return 0; }
 // tuning / test hook: 2 = bulk-copy persistent passes (default), 1 = cp.async persistent passes, 0 = one CTA per tile

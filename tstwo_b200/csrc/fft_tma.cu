@@ -46,8 +46,10 @@ constexpr int CHUNK_BYTES = 4096 + 16;                 // contiguous pass: 256 u
 //   contiguous: 2 groups x 256 threads, 64 KiB tiles (padded chunks), 3 buffers -- integer-bound, the deep layer count wins
 //   strided   : 4 groups x 128 threads, 32 KiB tiles, 6 buffers -- the copies dominate: more, smaller tiles in flight and
 //               four independent instruction streams keep both the pipes and HBM busier
-template <bool STRIDED> struct Cfg {
-    static constexpr int G = STRIDED ? 4 : 2, GS = THREADS / G, NBUF = STRIDED ? 6 : 3;
+//   512-row strided (R9): 2 groups x 256 threads, 64 KiB dense tiles (512 rows x 128 bytes, two tensor boxes), 3 buffers, nine
+//               layers in three stages (4 + 4 + 1) -- for transforms that leave exactly nine layers above the contiguous pass
+template <bool STRIDED, bool R9 = false> struct Cfg {
+    static constexpr int G = (STRIDED && !R9) ? 4 : 2, GS = THREADS / G, NBUF = (STRIDED && !R9) ? 6 : 3;
     static constexpr int TILE_BYTES = GS * 16 * 16;
     static constexpr int BUF_BYTES = STRIDED ? TILE_BYTES : 16 * CHUNK_BYTES;   // 65792 = 514 * 128: buffers stay 128-byte aligned
 };
@@ -63,11 +65,12 @@ constexpr int STRIDED_HEAP_WORDS = 8 * 256;            // up to 8 coset heaps of
 constexpr int TC_MAX_W = 4;
 constexpr int TC_EXTRA_BYTES = 128 + TC_MAX_W * (int)tc::B_BYTES;
 constexpr int HEAP_L1_WORD = 1024 + 64 * 4;            // first word of heap level 1 of the contiguous pass (1088 words)
-template <bool STRIDED> constexpr int smem_bytes(bool tc_stage = false)
+template <bool STRIDED, bool R9 = false> constexpr int smem_bytes(bool tc_stage = false)
 {
-    return Cfg<STRIDED>::NBUF * Cfg<STRIDED>::BUF_BYTES + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS) * 4 + 128 +
+    return Cfg<STRIDED, R9>::NBUF * Cfg<STRIDED, R9>::BUF_BYTES + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS) * 4 + 128 +
            (tc_stage && STRIDED ? TC_EXTRA_BYTES : 0);
 }
+static_assert(smem_bytes<true, true>() <= 232448, "exceeds the 227 KiB of shared memory a CTA can opt into");
 static_assert(smem_bytes<false>() <= 232448 && smem_bytes<true>(true) <= 232448, "exceeds the 227 KiB of shared memory a CTA can opt into");
 
 struct alignas(64) TmaParams {
@@ -153,12 +156,14 @@ __device__ int g_trace_cta = 0;
 // thread owns U[0..3] itself (lowest contiguous stage; that is what the chunk pad is for).
 //   contiguous: ST0 = lanes + U[0..3] (layers 0..5), ST1 = U[4..7] (6..9), ST2 = U[8..11] (10..13)
 //   strided   : ST0 = U[3..6] (window layers 0..3), ST1 = U[7..10] (4..7)
-template <bool STRIDED, int ST> struct Stg {
-    static constexpr int SU = STRIDED ? 3 + 4 * ST : 4 * ST;
-    static constexpr int SL = STRIDED ? 4 * ST : 4 * ST;     // heap level of digit bit 0
+//   512-row  : U (12 bits) = row << 3 | (index >> 2 & 7); ST0 = U[3..6] (window layers 0..3), ST1 = U[7..10] (4..7), ST2 = U[8..11] of
+//              which only U[11] (layer 8) is applied -- rows 5..7 ride along so that a thread still owns 16 units
+template <bool STRIDED, int ST, bool R9 = false> struct Stg {
+    static constexpr int SU = R9 ? (ST == 2 ? 8 : 3 + 4 * ST) : STRIDED ? 3 + 4 * ST : 4 * ST;
     static constexpr int PAD = STRIDED ? 0 : 1;
     __device__ static __forceinline__ int u0(int tg)
     {
+        if (R9) return SU == 3 ? ((tg & 7) | ((tg >> 3) << 7)) : SU == 7 ? ((tg & 127) | ((tg >> 7) << 11)) : tg;
         if (STRIDED) return SU == 3 ? ((tg & 7) | ((tg >> 3) << 7)) : tg;
         if (SU == 0) return ((tg & 7) << 8) | (((tg >> 3) & 15) << 4) | ((tg >> 7) << 11);
         if (SU == 4) return (tg & 15) | ((tg >> 4) << 8);
@@ -168,9 +173,9 @@ template <bool STRIDED, int ST> struct Stg {
     __device__ static __forceinline__ int phys0(int tg) { const int U0 = u0(tg); return U0 + PAD * (U0 >> 8); }
 };
 
-template <bool STRIDED, int ST> __device__ __forceinline__ void tile_load(const uint4 *buf, int tg, uint32_t (&v)[16][4])
+template <bool STRIDED, int ST, bool R9 = false> __device__ __forceinline__ void tile_load(const uint4 *buf, int tg, uint32_t (&v)[16][4])
 {
-    using S = Stg<STRIDED, ST>;
+    using S = Stg<STRIDED, ST, R9>;
     const uint4 *b = buf + S::phys0(tg);
 #pragma unroll
     for (int d = 0; d < 16; d++) {
@@ -178,9 +183,9 @@ template <bool STRIDED, int ST> __device__ __forceinline__ void tile_load(const 
         v[d][0] = a.x; v[d][1] = a.y; v[d][2] = a.z; v[d][3] = a.w;
     }
 }
-template <bool STRIDED, int ST> __device__ __forceinline__ void tile_store(uint4 *buf, int tg, const uint32_t (&v)[16][4])
+template <bool STRIDED, int ST, bool R9 = false> __device__ __forceinline__ void tile_store(uint4 *buf, int tg, const uint32_t (&v)[16][4])
 {
-    using S = Stg<STRIDED, ST>;
+    using S = Stg<STRIDED, ST, R9>;
     uint4 *b = buf + S::phys0(tg);
 #pragma unroll
     for (int d = 0; d < 16; d++) b[S::unit_off(d)] = make_uint4(v[d][0], v[d][1], v[d][2], v[d][3]);
@@ -202,7 +207,7 @@ template <bool STRIDED> __device__ __forceinline__ constexpr int heap_base(int l
 // l1_global != nullptr (contiguous pass with the tensor-core TOP stage): heap level 1 is not in shared memory; entry q of it is
 // l1_global[q] (the tree itself, L2-resident), fetched at the top of the stage that needs it so that the latency hides
 // behind the other layers' butterflies.
-template <bool STRIDED, bool INV, bool FULL>
+template <bool STRIDED, bool INV, bool FULL, int SNLEV = 8>
 __device__ __forceinline__ void unit_layers(uint32_t (&v)[16][4], const uint32_t *heap, int U0, int sl, int j_min,
                                             const uint32_t *l1_global = nullptr)
 {
@@ -216,7 +221,7 @@ __device__ __forceinline__ void unit_layers(uint32_t (&v)[16][4], const uint32_t
         const int l = sl + k;
         if (!FULL && l < j_min) continue;              // uniform across the grid
         const int cnt = 8 >> k;
-        const int base = STRIDED ? (1 << (7 - l)) : (1 << (11 - l)) + (l <= 5 ? 64 * (5 - l) + padw : 0);
+        const int base = STRIDED ? (1 << (SNLEV - 1 - l)) : (1 << (11 - l)) + (l <= 5 ? 64 * (5 - l) + padw : 0);
         const uint32_t *q = heap + base + (ub >> (l + 1));
         uint32_t t[8];
         if (cnt == 8) {
@@ -296,11 +301,18 @@ template <bool STRIDED> __device__ __forceinline__ Tile decode(const TmaParams &
 }
 
 // fetch tile `tl` into the buffer at shared address `buf`; its 64 KiB complete one phase of `bar`
-template <bool STRIDED>
+template <bool STRIDED, bool R9 = false>
 __device__ __forceinline__ void tile_fetch(const TmaParams &sp, const Tile tl, uint32_t buf, uint32_t bar, int tg)
 {
     const PassParams &p = sp.p;
-    if (STRIDED) {
+    if (R9) {                                          // 512 rows = two boxes of 256 rows
+        if (tg == 0) {
+            mbar_arrive_expect_tx(bar, Cfg<true, true>::TILE_BYTES);
+            const uint32_t row0 = ((tl.hi << (p.lo + 9)) & p.src_mask) >> p.lo;
+            tensor_g2s(buf, &sp.src_map, tl.mid << 5, row0, tl.col, bar);
+            tensor_g2s(buf + 32768, &sp.src_map, tl.mid << 5, row0 + 256, tl.col, bar);
+        }
+    } else if (STRIDED) {
         if (tg == 0) {
             mbar_arrive_expect_tx(bar, Cfg<true>::TILE_BYTES);
             tensor_g2s(buf, &sp.src_map, tl.mid << 5, ((tl.hi << (p.lo + 8)) & p.src_mask) >> p.lo, tl.col, bar);
@@ -313,11 +325,17 @@ __device__ __forceinline__ void tile_fetch(const TmaParams &sp, const Tile tl, u
     }
 }
 // the transformed tile (complete in the buffer, made visible to the async proxy by the caller) leaves as bulk stores
-template <bool STRIDED>
+template <bool STRIDED, bool R9 = false>
 __device__ __forceinline__ void tile_drain(const TmaParams &sp, const Tile tl, uint32_t buf, int tg)
 {
     const PassParams &p = sp.p;
-    if (STRIDED) {
+    if (R9) {
+        if (tg == 0) {
+            tensor_s2g(&sp.dst_map, tl.mid << 5, tl.hi << 9, tl.col, buf);
+            tensor_s2g(&sp.dst_map, tl.mid << 5, (tl.hi << 9) + 256, tl.col, buf + 32768);
+            bulk_commit();
+        }
+    } else if (STRIDED) {
         if (tg == 0) { tensor_s2g(&sp.dst_map, tl.mid << 5, tl.hi << 8, tl.col, buf); bulk_commit(); }
     } else if (tg < 16) {
         uint32_t *dst = p.dst.ptr(tl.col, tl.hi << 14) + 1024 * tg;
@@ -327,10 +345,10 @@ __device__ __forceinline__ void tile_drain(const TmaParams &sp, const Tile tl, u
 }
 
 // twiddles of the run of tiles with high bits `hi` (all 512 threads; one cp.async group)
-template <bool STRIDED, bool SKIP_L1 = false>
+template <bool STRIDED, bool SKIP_L1 = false, bool R9 = false>
 __device__ __forceinline__ void stage_twiddles(uint32_t *heap, const PassParams &p, uint32_t hi, int tid)
 {
-    constexpr int NLEV = STRIDED ? 8 : 12;
+    constexpr int NLEV = R9 ? 9 : STRIDED ? 8 : 12;
     const int base_layer = STRIDED ? p.lo : 2;         // tree layer of heap level 0
     for (int e = 4 * tid; e < (1 << NLEV); e += 4 * THREADS) {
         if (e == 0) {
@@ -355,11 +373,12 @@ __device__ __forceinline__ void stage_twiddles(uint32_t *heap, const PassParams 
 
 // all stages of a tile, in place in its buffer: load -> butterflies -> store back, group barrier between stages
 struct TcTile { tc::Group gr; uint64_t bd0, bd1; int lane; const uint32_t *l1_global; };   // what the tensor-core TOP stage of a tile needs
-template <bool STRIDED, bool INV, bool FULL, bool TC, typename AtFirstBoundary>
+template <bool STRIDED, bool INV, bool FULL, bool TC, bool R9, typename AtFirstBoundary>
 __device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap, int tg, int g, int j_min, uint32_t scale2,
                                                const TcTile &tct, AtFirstBoundary at_first_boundary)
 {
-    constexpr int NST = STRIDED ? 2 : 3, TOP = NST - 1;
+    constexpr int NST = (STRIDED && !R9) ? 2 : 3, TOP = NST - 1;
+    constexpr int GS = Cfg<STRIDED, R9>::GS;
 #pragma unroll 1
     for (int s = 0; s < NST; s++) {
         const int st = INV ? s : TOP - s;
@@ -373,11 +392,13 @@ __device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap,
         } else {
             uint32_t v[16][4];
             int U0;
-            if (st == 0) { tile_load<STRIDED, 0>(buf, tg, v); U0 = Stg<STRIDED, 0>::u0(tg); }
-            else if (st == TOP) { tile_load<STRIDED, TOP>(buf, tg, v); U0 = Stg<STRIDED, TOP>::u0(tg); }
-            else { tile_load<STRIDED, 1>(buf, tg, v); U0 = Stg<STRIDED, 1>::u0(tg); }
+            if (st == 0) { tile_load<STRIDED, 0, R9>(buf, tg, v); U0 = Stg<STRIDED, 0, R9>::u0(tg); }
+            else if (st == TOP) { tile_load<STRIDED, TOP, R9>(buf, tg, v); U0 = Stg<STRIDED, TOP, R9>::u0(tg); }
+            else { tile_load<STRIDED, 1, R9>(buf, tg, v); U0 = Stg<STRIDED, 1, R9>::u0(tg); }
             if (!STRIDED && INV && st == 0) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
-            unit_layers<STRIDED, INV, FULL>(v, heap, U0, 4 * st, j_min, TC ? tct.l1_global : nullptr);
+            // 512-row pass: stage 2 owns unit bits 8..11 = rows 5..8, of which rows 5..7 (levels 5..7) were done in stage 1: level 8 only
+            if (R9) unit_layers<true, INV, false, 9>(v, heap, U0, st == 2 ? 5 : 4 * st, st == 2 ? 8 : 0);
+            else unit_layers<STRIDED, INV, FULL>(v, heap, U0, 4 * st, j_min, TC ? tct.l1_global : nullptr);
             if (!STRIDED && !INV && st == 0) lane_layers<INV>(v, heap + HEAP_WORDS, tg);
             if (INV && s == TOP && scale2) {
 #pragma unroll
@@ -385,21 +406,22 @@ __device__ __forceinline__ void transform_tile(uint4 *buf, const uint32_t *heap,
 #pragma unroll
                     for (int e = 0; e < 4; e++) v[d][e] = m31::mul2(v[d][e], scale2);
             }
-            if (st == 0) tile_store<STRIDED, 0>(buf, tg, v);
-            else if (st == TOP) tile_store<STRIDED, TOP>(buf, tg, v);
-            else tile_store<STRIDED, 1>(buf, tg, v);
+            if (st == 0) tile_store<STRIDED, 0, R9>(buf, tg, v);
+            else if (st == TOP) tile_store<STRIDED, TOP, R9>(buf, tg, v);
+            else tile_store<STRIDED, 1, R9>(buf, tg, v);
         }
         if (s == 0) at_first_boundary();
-        if (s < TOP) group_sync<Cfg<STRIDED>::GS>(g);
+        if (s < TOP) group_sync<GS>(g);
     }
 }
 
-template <bool INV, bool STRIDED, bool FULL, bool TC = false>
+template <bool INV, bool STRIDED, bool FULL, bool TC = false, bool R9 = false>
 __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_constant__ TmaParams sp)
 {
     static_assert(!TC || FULL, "the tensor-core TOP stage needs all layers of its window");
+    static_assert(!R9 || (STRIDED && FULL && !TC), "the 512-row pass is a full strided window on the integer pipes");
     extern __shared__ __align__(1024) uint8_t smem[];
-    using C = Cfg<STRIDED>;
+    using C = Cfg<STRIDED, R9>;
     constexpr int NBUF = C::NBUF, BUF_BYTES = C::BUF_BYTES, G = C::G;
     uint32_t *heap = reinterpret_cast<uint32_t *>(smem + NBUF * BUF_BYTES);
     const uint32_t bar0 = smem_u32(heap + (STRIDED ? STRIDED_HEAP_WORDS : HEAP_WORDS + T1_WORDS));
@@ -472,10 +494,10 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
 #pragma unroll
         for (int i = 0; i < NBUF; i++)
             if ((uint32_t)i < len && (i % G) == g)
-                tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar_of(i), tg);
+                tile_fetch<STRIDED, R9>(sp, decode<STRIDED>(sp, t0 + i * step, hi), buf0 + i * BUF_BYTES, bar_of(i), tg);
         if (STRIDED && sp.cosets_log) {
-            for (uint32_t c = 0; c < (1u << sp.cosets_log); c++) stage_twiddles<STRIDED>(heap + 256 * c, p, c, tid);
-        } else stage_twiddles<STRIDED, TC && !STRIDED>(heap, p, hi, tid);
+            for (uint32_t c = 0; c < (1u << sp.cosets_log); c++) stage_twiddles<STRIDED, false, R9>(heap + (R9 ? 512 : 256) * c, p, c, tid);
+        } else stage_twiddles<STRIDED, TC && !STRIDED, R9>(heap, p, hi, tid);
         __syncthreads();
         if (TC) {                                      // the run's weight tiles, one per resident heap (ends with a __syncthreads)
             const uint32_t nw = (STRIDED && sp.cosets_log) ? (1u << sp.cosets_log) : 1u;
@@ -497,29 +519,29 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
             // at once (the other seven warps are already on the next tile).  DEFER = refill at the first stage boundary
             // of the group's next tile instead, so that nobody blocks on the read-out.
             constexpr bool DEFER = false;   // measured: deferring costs the inverse contiguous pass 20 % (its first stage is the longest)
-            const uint32_t *tile_heap = (STRIDED && sp.cosets_log) ? heap + 256 * tl.hi : heap;
+            const uint32_t *tile_heap = (STRIDED && sp.cosets_log) ? heap + (R9 ? 512 : 256) * tl.hi : heap;
             if (TC) {
                 const uint32_t w = smem_u32(tc_weights) + ((STRIDED && sp.cosets_log) ? tl.hi * tc::B_BYTES : 0u);
                 tct.bd0 = tc::make_sdesc(w, tc::B_KCHUNK, tc::B_NGROUP);
                 tct.bd1 = tc::make_sdesc(w + 2 * tc::B_KCHUNK, tc::B_KCHUNK, tc::B_NGROUP);
             }
-            transform_tile<STRIDED, INV, FULL, TC>(buf, tile_heap, tg, g, p.j_min, p.scale2, tct, [&]() {
+            transform_tile<STRIDED, INV, FULL, TC, R9>(buf, tile_heap, tg, g, p.j_min, p.scale2, tct, [&]() {
                 if (DEFER && refill != 0xffffffffu) {
                     if (tg < 16) bulk_wait_read();
                     const uint32_t rb = refill % NBUF;
-                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (refill + NBUF) * step, hi), buf0 + rb * BUF_BYTES, bar_of(refill + NBUF), tg);
+                    tile_fetch<STRIDED, R9>(sp, decode<STRIDED>(sp, t0 + (refill + NBUF) * step, hi), buf0 + rb * BUF_BYTES, bar_of(refill + NBUF), tg);
                     refill = 0xffffffffu;
                 }
             });
             TRACE(2, i);
             fence_proxy_async();                       // generic-proxy stores above -> async-proxy reads below
             group_sync<C::GS>(g);
-            tile_drain<STRIDED>(sp, tl, buf0 + b * BUF_BYTES, tg);
+            tile_drain<STRIDED, R9>(sp, tl, buf0 + b * BUF_BYTES, tg);
             if (i + NBUF < len) {
                 if (DEFER) refill = i;
                 else {
                     if (tg < 16) bulk_wait_read();
-                    tile_fetch<STRIDED>(sp, decode<STRIDED>(sp, t0 + (i + NBUF) * step, hi), buf0 + b * BUF_BYTES, bar_of(i + NBUF), tg);
+                    tile_fetch<STRIDED, R9>(sp, decode<STRIDED>(sp, t0 + (i + NBUF) * step, hi), buf0 + b * BUF_BYTES, bar_of(i + NBUF), tg);
                 }
             }
             TRACE(3, i);
@@ -543,9 +565,9 @@ __global__ void __launch_bounds__(THREADS, 1) fft_tma_kernel(const __grid_consta
     TRACE_CTA(1);
 }
 
-template <bool INV, bool STRIDED, bool FULL, bool TC = false> cudaError_t set_attr()
+template <bool INV, bool STRIDED, bool FULL, bool TC = false, bool R9 = false> cudaError_t set_attr()
 {
-    return cudaFuncSetAttribute(fft_tma_kernel<INV, STRIDED, FULL, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<STRIDED>(TC));
+    return cudaFuncSetAttribute(fft_tma_kernel<INV, STRIDED, FULL, TC, R9>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<STRIDED, R9>(TC));
 }
 // tstwo_debug_set_fft_tc: bit 0 = forward strided passes, bit 1 = contiguous passes, bit 2 = inverse strided passes.
 // Default = forward strided only, the one pass where it wins (scripts/tc_ab.py, profiles/r02_tc_ab.txt: 2.98 -> 2.52 ms;
@@ -597,6 +619,7 @@ int tma_pass_init()
     TS_CUDA((set_attr<false, true, false>())); TS_CUDA((set_attr<true, true, false>()));
     TS_CUDA((set_attr<false, true, true, true>())); TS_CUDA((set_attr<true, true, true, true>()));
     TS_CUDA((set_attr<false, false, true, true>())); TS_CUDA((set_attr<true, false, true, true>()));
+    TS_CUDA((set_attr<false, true, true, false, true>())); TS_CUDA((set_attr<true, true, true, false, true>()));
     void *fn = nullptr;
     cudaDriverEntryPointQueryResult qres;
     TS_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
@@ -630,17 +653,20 @@ int tma_pass(bool inverse, const PassParams &p)
     memset(&sp, 0, sizeof sp);
     sp.p = p;
     const bool strided = p.lo != 0;
+    const bool rows9 = strided && p.win == TMA_W9;
+    const int width = rows9 ? TMA_W9 : TMA_W1;
     uint64_t n_hi, per_hi;
     if (strided) {
         if (p.src.shard_log != 31 || p.dst.shard_log != 31) return fail(TSTWO_ERR_BAD_ARG, "strided FFT pass on a row-sharded column set");
-        if (p.lo < 5 || p.lo + TMA_W1 > p.n) return fail(TSTWO_ERR_BAD_ARG, "bad strided window lo=%d n=%d", p.lo, p.n);
+        if (p.lo < 5 || p.lo + width > p.n || (rows9 && p.j_min != 0)) return fail(TSTWO_ERR_BAD_ARG, "bad strided window lo=%d n=%d", p.lo, p.n);
         int src_log = 0;
         while ((1ull << src_log) <= p.src_mask) src_log++;          // src holds 2^src_log words per column
         if ((rc = make_map(&sp.src_map, p.src, p.n_cols, src_log, p.lo))) return rc;
         if ((rc = make_map(&sp.dst_map, p.dst, p.n_cols, p.n, p.lo))) return rc;
-        n_hi = 1ull << (p.n - p.lo - TMA_W1);
+        if (rows9 && src_log < p.lo + TMA_W9) return fail(TSTWO_ERR_BAD_ARG, "512-row window above the source (lo=%d, source 2^%d)", p.lo, src_log);
+        n_hi = 1ull << (p.n - p.lo - width);
         per_hi = ((uint64_t)p.n_cols) << (p.lo - 5);
-        if (src_log < p.n && p.lo + TMA_W1 == src_log && p.n - src_log <= 3) {   // top window of a blown-up evaluation
+        if (src_log < p.n && p.lo + width == src_log && p.n - src_log <= (rows9 ? 2 : 3)) {   // top window of a blown-up evaluation
             sp.cosets_log = (uint32_t)(p.n - src_log);
             per_hi *= n_hi;                                                      // one run: every coset's heap is staged
             n_hi = 1;
@@ -655,13 +681,16 @@ int tma_pass(bool inverse, const PassParams &p)
     unsigned grid = (unsigned)ctx().sm_count;
     if (ctx().grid_limit > 0 && grid > (unsigned)ctx().grid_limit) grid = (unsigned)ctx().grid_limit;
     if (grid > sp.n_tiles) grid = sp.n_tiles;
-    const bool use_tc = strided ? ((g_use_tc & (inverse ? 4 : 1)) && p.j_min == 0 && (1u << sp.cosets_log) <= (unsigned)TC_MAX_W) : (g_use_tc & 2) != 0;
-    PassStamp st{ (inverse ? 1 : 0) | (strided ? 2 : 0) | (use_tc ? 4 : 0), nullptr, nullptr };
+    const bool use_tc = rows9 ? false : strided ? ((g_use_tc & (inverse ? 4 : 1)) && p.j_min == 0 && (1u << sp.cosets_log) <= (unsigned)TC_MAX_W) : (g_use_tc & 2) != 0;
+    PassStamp st{ (inverse ? 1 : 0) | (strided ? 2 : 0) | (use_tc ? 4 : 0) | (rows9 ? 8 : 0), nullptr, nullptr };
     if (g_timing) {
         TS_CUDA(cudaEventCreate(&st.e0)); TS_CUDA(cudaEventCreate(&st.e1));
         TS_CUDA(cudaEventRecord(st.e0, ctx().stream));
     }
-    if (!strided && use_tc) {
+    if (rows9) {
+        if (inverse) TS_LAUNCH((fft_tma_kernel<true, true, true, false, true>), grid, THREADS, (smem_bytes<true, true>()), sp);
+        else TS_LAUNCH((fft_tma_kernel<false, true, true, false, true>), grid, THREADS, (smem_bytes<true, true>()), sp);
+    } else if (!strided && use_tc) {
         if (inverse) TS_LAUNCH((fft_tma_kernel<true, false, true, true>), grid, THREADS, smem_bytes<false>(true), sp);
         else TS_LAUNCH((fft_tma_kernel<false, false, true, true>), grid, THREADS, smem_bytes<false>(true), sp);
     } else if (!strided) {
