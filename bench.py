@@ -6,10 +6,13 @@ elements, evaluate them on the blow-up-2 canonic domain (2^23 rows), Blake2s Mer
   value : trace elements / s with the trace resident in HBM (CUDA events, max over ranks)
   e2e   : the same through the C-ABI call a host makes (tstwo_lde_commit_host): trace in pinned HOST memory,
           host->device copies inside the timed region, root read back
-N > 1 : columns are sharded by column for the LDE, an NCCL all-to-all re-shards by row range, every rank
-        hashes its leaves and builds its subtree, rank 0 finishes the top log2(N) layers.
+N > 1 : columns are sharded by column for the LDE; the last FFT pass stores every row range into its owner's leaf buffer over
+        NVLink peer memory (--exchange nccl: an all-to-all instead), the ranks order the step with release/acquire flags in peer
+        memory (--fence nccl: collectives), every rank hashes its leaves and builds its subtree, rank 0 finishes the top log2(N)
+        layers.  --single-process drives the N devices from ONE host thread through tstwo_lde_commit_multi_dev.
 --impl reference : the CPU oracle (C restatement of TStwo's CpuBackend; the TypeScript reference cannot run here)
-        on all host cores, on a bounded sample of the same workload.
+        on all host cores, on the whole workload (all 256 columns; --cpu-sample-cols bounds it).
+roofline / rooflines / int_roofline / e2e.h2d_only / extras / phases: see DESIGN.md section 6.
 """
 import argparse
 import ctypes as C
