@@ -451,7 +451,8 @@ __global__ void __launch_bounds__(QM_WARPS * 32, 3) quotients_mma_kernel(int log
             else den_inv = { m31::mul(den[q].re, di[q]), m31::mul(m31::sub(0, den[q].im), di[q]) };
             m31::QM nm = { num[q][0], num[q][1], num[q][2], num[q][3] };
             nm = m31::qsub(nm, m31::qadd(m31::qmul_m(A, dp[q].y), B));
-            acc[q] = m31::qadd(m31::qmul(acc[q], bc), m31::qmul_cm(nm, den_inv));
+            const m31::QM term = m31::qmul_cm(nm, den_inv);
+            acc[q] = b == 0 ? term : m31::qadd(m31::qmul(acc[q], bc), term);     // 0 * bc + term for the first batch (uniform branch)
         }
     }
 #pragma unroll
