@@ -409,6 +409,33 @@ class MerkleProver:
         return queried[:counts[0]], MerkleDecommitment([h.tobytes() for h in hashes[:counts[1]]], witness[:counts[2]])
 
 
+class HashRows:
+    """A read-only sequence of 32-byte hashes over the rows of an (n, 32) uint8 array: what a list of `bytes` would be, without
+    materialising tens of thousands of bytes objects per proof (the inner FRI layers of a 70-query proof carry ~30 000 witness hashes)."""
+
+    def __init__(self, rows: np.ndarray):
+        self._rows = rows
+
+    def __len__(self): return self._rows.shape[0]
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return HashRows(self._rows[i])
+        return self._rows[i].tobytes()
+
+    def __iter__(self): return (r.tobytes() for r in self._rows)
+
+    def __eq__(self, other):
+        if isinstance(other, HashRows):
+            return self._rows.shape == other._rows.shape and bool((self._rows == other._rows).all())
+        try:
+            return len(other) == len(self) and all(bytes(a) == b for a, b in zip(other, self))
+        except TypeError:
+            return NotImplemented
+
+    def __repr__(self): return f"HashRows({len(self)} hashes)"
+
+
 class MerkleDecommitment:
     """vcs/verifier.ts:5-8."""
 

@@ -15,7 +15,7 @@ import numpy as np
 
 from ._lib import check, dptr_array
 from . import _lib
-from .backend import (_L, CudaBackend, FriConfig, LineEvaluation, MerkleDecommitment, MerkleProver, SecureColumnByCoords, SecureEvaluation,
+from .backend import (_L, CudaBackend, FriConfig, HashRows, LineEvaluation, MerkleDecommitment, MerkleProver, SecureColumnByCoords, SecureEvaluation,
                       TwiddleTree, fold_circle_into_line, fold_line)
 from .channel import Blake2sChannel, Blake2sMerkleChannel
 from .circle import Coset, LineDomain
@@ -394,10 +394,9 @@ class FriProver:
                                           wit.ctypes.data_as(_lib.u32p), cap_w, hashes.ctypes.data_as(C.POINTER(C.c_uint8)), cap_h,
                                           colw.ctypes.data_as(_lib.u32p), colw.size, counts))
         out, wi, hi, ci = [], 0, 0, 0
-        hash_bytes = hashes.tobytes()
         for l, layer in enumerate(self.inner_layers):
             nw, nh, nc = int(counts[3 * l]), int(counts[3 * l + 1]), int(counts[3 * l + 2])
-            dec = MerkleDecommitment([hash_bytes[32 * k:32 * k + 32] for k in range(hi, hi + nh)], colw[ci:ci + nc].copy())
+            dec = MerkleDecommitment(HashRows(hashes[hi:hi + nh]), colw[ci:ci + nc].copy())
             out.append(FriLayerProof(wit[wi:wi + nw].tolist(), dec, layer.merkle_tree.root()))
             wi, hi, ci = wi + nw, hi + nh, ci + nc
         return out
