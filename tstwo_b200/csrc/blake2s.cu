@@ -132,6 +132,34 @@ __global__ void __launch_bounds__(256, 5) merkle_node_kernel(const uint4 *__rest
     out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
 }
 
+// Node layer that also absorbs at most 16 evenly spaced columns (two blocks per node: the children, then the column values): the
+// layer at which the smaller columns of a mixed-size tree join (FRI's first-layer tree over quotient columns of two sizes).  Same
+// shape as merkle_node_kernel; the columns are addressed as cols.base + k * cols.stride on purpose -- through ColSet::col() (the pointer-table
+// branch) ptxas falls back to the three-register IMAD form.  Scattered column tables keep merkle_layer_kernel<true>.
+__global__ void __launch_bounds__(256, 5) merkle_node_cols_kernel(const uint4 *__restrict__ prev, ColSet cols, int n_cols, uint64_t n_nodes,
+                                                                  uint4 *__restrict__ out, uint32_t n_blocks, uint32_t one)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;   // literal block size (see merkle_node_kernel)
+    if (i >= n_nodes) return;
+    uint32_t h[8], m[16];
+    const uint4 *p = prev + 4 * i;
+    const uint4 x0 = __ldcs(p), x1 = __ldcs(p + 1), x2 = __ldcs(p + 2), x3 = __ldcs(p + 3);
+    m[0] = x0.x; m[1] = x0.y; m[2] = x0.z; m[3] = x0.w; m[4] = x1.x; m[5] = x1.y; m[6] = x1.z; m[7] = x1.w;
+    m[8] = x2.x; m[9] = x2.y; m[10] = x2.z; m[11] = x2.w; m[12] = x3.x; m[13] = x3.y; m[14] = x3.z; m[15] = x3.w;
+    b2s_init(h);
+#pragma unroll 1
+    for (uint32_t b = 0; b < n_blocks; b++) {        // n_blocks == 2 at run time
+        const bool last = b + 1 == n_blocks;
+        b2s_compress(h, m, last ? 64u + 4u * (uint32_t)n_cols : 64u, last, one);
+        if (!last) {
+#pragma unroll
+            for (int k = 0; k < 16; k++) m[k] = k < n_cols ? __ldcs(cols.base + (uint64_t)k * cols.stride + i) : 0u;
+        }
+    }
+    out[2 * i] = make_uint4(h[0], h[1], h[2], h[3]);
+    out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
+}
+
 // ---- leaf layer fed by bulk tensor copies -----------------------------------------------------------------------
 // The leaf hash of row i absorbs column words c = 0, 1, ... of that row, 16 per compression.  With uniformly spaced
 // columns the message blocks of 256 consecutive rows are boxes [16 columns x 256 rows] (16 KiB, sixteen 1 KiB runs) of
@@ -349,6 +377,8 @@ int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, i
         return merkle_leaf_tma(cols, n_cols, n, out);
     }
     if (prev && n_cols == 0 && g_leaf_mode) TS_LAUNCH(merkle_node_kernel, grid, block, 0, (const uint4 *)prev, n, (uint4 *)out, 1u, 1u);
+    else if (prev && n_cols >= 1 && n_cols <= 16 && g_leaf_mode && !cols.table && !cols.shard_bases && cols.shard_log == 31)
+        TS_LAUNCH(merkle_node_cols_kernel, grid, block, 0, (const uint4 *)prev, cols, n_cols, n, (uint4 *)out, 2u, 1u);
     else if (prev) TS_LAUNCH((merkle_layer_kernel<true>), grid, block, 0, (const uint4 *)prev, cols, n_cols, n, (uint4 *)out, 1u);
     else TS_LAUNCH((merkle_layer_kernel<false>), grid, block, 0, (const uint4 *)nullptr, cols, n_cols, n, (uint4 *)out, 1u);
     return 0;
