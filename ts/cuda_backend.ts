@@ -219,3 +219,42 @@ export function merkleDecommit(tree: bigint, maxLog: number, columns: CudaColumn
   const hashWitness = Array.from({ length: Number(counts[1]) }, (_, i) => hashes.slice(32 * i, 32 * i + 32));
   return { queried: queried.subarray(0, Number(counts[0])), hashWitness, columnWitness: witness.subarray(0, Number(counts[2])) };
 }
+
+// FriProver.commitInnerLayers (fri.ts:676-716) in one call with the Fiat-Shamir transcript on the device.  `state` is the
+// Blake2sChannel's state as 19 words (digest[8], n_challenges, n_sent, queue length, queued base felts[8]); it is updated in
+// place and the caller writes it back into its channel object.  Returns per layer the tree buffer, root, folding alpha and the
+// next layer's four coordinate columns (quarters of ONE device block: free evals[l][0] only).
+export function friCommitInnerLayers(first: [CudaColumn, CudaColumn, CudaColumn, CudaColumn], firstLog: number, firstCosetInit: number,
+                                     lastLog: number, circle: { coords: CudaColumn[]; log: number; halfInit: number }[], tw: bigint,
+                                     state: Uint32Array) {
+  const n = Math.max(0, firstLog - lastLog);
+  const f = BigUint64Array.from(first.map((c) => c.dptr));
+  const cc = BigUint64Array.from(circle.flatMap((c) => c.coords.map((k) => k.dptr)));
+  const clogs = Int32Array.from(circle.map((c) => c.log)), cinits = Uint32Array.from(circle.map((c) => c.halfInit));
+  const evals = new BigUint64Array(4 * Math.max(1, n)), trees = new BigUint64Array(Math.max(1, n));
+  const roots = new Uint8Array(32 * Math.max(1, n)), alphas = new Uint32Array(4 * Math.max(1, n)), nOut = new Int32Array(1);
+  check(lib.tstwo_fri_commit_layers(ptr(f), firstLog, firstCosetInit, lastLog, circle.length ? ptr(cc) : null, circle.length ? ptr(clogs) : null,
+                                    circle.length ? ptr(cinits) : null, circle.length, tw, ptr(state), ptr(evals), ptr(trees), ptr(roots),
+                                    ptr(alphas), ptr(nOut)));
+  return Array.from({ length: nOut[0] }, (_, l) => ({
+    tree: trees[l], root: roots.slice(32 * l, 32 * l + 32), alpha: alphas.slice(4 * l, 4 * l + 4), nextEvals: Array.from(evals.slice(4 * l, 4 * l + 4)) }));
+}
+
+// FriProver.decommitOnQueries' loop over the inner layers (fri.ts:769-785) in one call: `queries` are the sorted positions on the
+// first inner layer's domain.  Returns per layer { friWitness (QM31 as 4 words each), hashWitness, columnWitness }.
+export function friDecommitInnerLayers(layers: { tree: bigint; coords: CudaColumn[]; log: number }[], queries: number[]) {
+  const n = layers.length, nq = queries.length;
+  const trees = BigUint64Array.from(layers.map((l) => l.tree)), evals = BigUint64Array.from(layers.flatMap((l) => l.coords.map((c) => c.dptr)));
+  const logs = Int32Array.from(layers.map((l) => l.log)), q = Uint32Array.from(nq ? queries : [0]);
+  const capW = Math.max(1, nq * n), capH = Math.max(1, 2 * nq * layers.reduce((a, l) => a + l.log, 0)), capC = Math.max(1, 8 * nq * n);
+  const wit = new Uint32Array(4 * capW), hashes = new Uint8Array(32 * capH), colw = new Uint32Array(capC), counts = new BigUint64Array(3 * Math.max(1, n));
+  check(lib.tstwo_fri_decommit_layers(n, ptr(trees), ptr(evals), ptr(logs), ptr(q), nq, ptr(wit), capW, ptr(hashes), capH, ptr(colw), capC, ptr(counts)));
+  let wi = 0, hi = 0, ci = 0;
+  return layers.map((_, l) => {
+    const nw = Number(counts[3 * l]), nh = Number(counts[3 * l + 1]), nc = Number(counts[3 * l + 2]);
+    const out = { friWitness: wit.slice(4 * wi, 4 * (wi + nw)), hashWitness: Array.from({ length: nh }, (_, k) => hashes.slice(32 * (hi + k), 32 * (hi + k) + 32)),
+                  columnWitness: colw.slice(ci, ci + nc) };
+    wi += nw; hi += nh; ci += nc;
+    return out;
+  });
+}
