@@ -43,3 +43,13 @@ def test_oracle_fri_flow_degree_check(orc):
     pos = orc.fri_decommitment_positions([3, 17, 40], 1)[0]
     orc.merkle_verify(root, [log] * 4, {log: pos}, queried, hw, cw)
     assert len(w) == 3 and len(queried) == 4 * len(pos)
+
+
+def test_hash_rows_behaves_like_a_list_of_bytes():
+    """HashRows (the witness-hash sequence of the one-call FRI decommit) against the list of bytes objects it stands for."""
+    from tstwo_b200.backend import HashRows
+    a = np.arange(5 * 32, dtype=np.uint8).reshape(5, 32)
+    h, ref = HashRows(a), [bytes(r) for r in a]
+    assert len(h) == 5 and h[0] == ref[0] and h[4] == ref[4] and list(h) == ref
+    assert h == ref and h == HashRows(a.copy()) and not (h == ref[:4]) and not (h == [b"\x00" * 32] * 5)
+    assert list(h[1:3]) == ref[1:3] and len(HashRows(a[:0])) == 0 and HashRows(a[:0]) == []
