@@ -132,3 +132,46 @@ def prove_wide_fibonacci(log_n_rows: int, n_cols: int, pow_bits: int, log_last_l
             "composition_coeffs": comp_coeffs, "fri": fri, "fri_layers": fri_layers, "proof_of_work": nonce, "positions": positions,
             "decommitments": decommitments, "queries_by_log": by_log, "tree_logs": [t[0] for t in trees],
             "composition_at_oods": comp_at_oods, "constraints_at_oods": acc, "channel_digest": channel.digest}
+
+
+def serialize_proof(exp: dict, pow_bits: int, log_last_layer_degree_bound: int, log_blowup: int, n_queries: int) -> bytes:
+    """The oracle's proof (the dict prove_wide_fibonacci returns) in the byte format of tstwo_b200/proof_format.py, written
+    independently of it (struct.pack, value by value): config, commitments, sampled values, decommitments, queried values,
+    proof of work, FRI proof.  Tests compare these bytes with StarkProof.toBytes() of the device prover."""
+    import struct
+    out = [b"TSTWOPF1", struct.pack("<IIII", pow_bits, log_last_layer_degree_bound, log_blowup, n_queries)]
+    u32 = lambda v: struct.pack("<I", int(v))
+    def words(ws):
+        ws = [int(w) for w in ws]
+        return struct.pack(f"<{len(ws)}I", *ws)
+    def decommitment(hash_witness, column_witness):
+        return [u32(len(hash_witness)), b"".join(bytes(h) for h in hash_witness), u32(len(column_witness)), words(column_witness)]
+    out.append(u32(len(exp["commitments"])))
+    out += [bytes(c) for c in exp["commitments"]]
+    out.append(u32(len(exp["sampled_values"])))
+    for tree in exp["sampled_values"]:
+        out.append(u32(len(tree)))
+        for col in tree:
+            out.append(u32(len(col)))
+            for value in col:
+                out.append(words(value))
+    out.append(u32(len(exp["decommitments"])))
+    for queried, hw, cw in exp["decommitments"]:
+        out += decommitment(hw, cw)
+    out.append(u32(len(exp["decommitments"])))
+    for queried, hw, cw in exp["decommitments"]:
+        out += [u32(len(queried)), words(queried)]
+    out.append(struct.pack("<Q", exp["proof_of_work"]))
+    layers = exp["fri_layers"]
+    def fri_layer(layer):
+        witness, (queried, hw, cw), root = layer
+        r = [u32(len(witness))] + [words(w) for w in witness]
+        return r + decommitment(hw, cw) + [bytes(root)]
+    out += fri_layer(layers[0])
+    out.append(u32(len(layers) - 1))
+    for layer in layers[1:]:
+        out += fri_layer(layer)
+    last = exp["fri"]["last_poly"]
+    out.append(u32(len(last)))
+    out += [words(c) for c in last]
+    return b"".join(out)

@@ -54,6 +54,23 @@ def test_prove_matches_oracle_flow(tb, orc, log, n_cols, pow_bits, last, blow, n
     # tree decommitments
     for dec, qv, (queried, hw, cw) in zip(p.decommitments, p.queried_values, exp["decommitments"]):
         assert list(qv) == list(queried) and list(dec.hashWitness) == list(hw) and list(dec.columnWitness) == list(cw)
+    # the proof as BYTES: the device prover's serialisation against the oracle's own serialisation of the oracle's proof, a round
+    # trip through the parser, and the reference's size estimates (prover/index.ts:306-356, 487-540)
+    from tstwo_b200.prover import StarkProof
+    blob = proof.toBytes()
+    assert blob == stark.serialize_proof(exp, pow_bits, last, blow, n_queries), "proof bytes differ from the oracle's"
+    again = StarkProof.fromBytes(blob)
+    assert again.toBytes() == blob and again.commitments == p.commitments
+    hashes = len(p.commitments) + sum(len(d.hashWitness) for d in p.decommitments) + \
+        sum(len(l.decommitment.hashWitness) + 1 for l in [p.fri_proof.first_layer] + list(p.fri_proof.inner_layers))
+    words = sum(len(q) for q in p.queried_values) + sum(len(d.columnWitness) for d in p.decommitments) + \
+        sum(len(l.decommitment.columnWitness) for l in [p.fri_proof.first_layer] + list(p.fri_proof.inner_layers))
+    felts = sum(len(c) for t in p.sampled_values for c in t) + len(p.fri_proof.last_layer_poly.coeffs) + \
+        sum(len(l.fri_witness) for l in [p.fri_proof.first_layer] + list(p.fri_proof.inner_layers))
+    assert proof.sizeEstimate() == 32 * hashes + 4 * words + 16 * felts + 8 + 64
+    bd = proof.sizeBreakdownEstimate()
+    assert set(bd) == {"oodsS", "queriesValues", "friSamples", "friDecommitments", "traceDecommitments"}
+    assert sum(bd.values()) == proof.sizeEstimate() - 8 - 64
 
 
 def test_prove_rejects_invalid_trace(tb):

@@ -89,6 +89,32 @@ class StarkProof:
     @property
     def commitments(self): return self.commitmentSchemeProof.commitments
 
+    def sizeEstimate(self) -> int:
+        """prover/index.ts:471-476."""
+        from . import proof_format
+        if getattr(self, "_size_estimate_cache", None) is None:
+            self._size_estimate_cache = proof_format.size_estimate(self.commitmentSchemeProof)
+        return self._size_estimate_cache
+    size_estimate = sizeEstimate
+
+    def sizeBreakdownEstimate(self) -> dict:
+        """prover/index.ts:487-540: oodsS, queriesValues, friSamples, friDecommitments, traceDecommitments."""
+        from . import proof_format
+        return proof_format.size_breakdown_estimate(self.commitmentSchemeProof)
+    size_breakdown_estimate = sizeBreakdownEstimate
+
+    def toBytes(self) -> bytes:
+        """The proof as bytes (format: tstwo_b200/proof_format.py; the reference defines none)."""
+        from . import proof_format
+        return proof_format.to_bytes(self.commitmentSchemeProof)
+    to_bytes = toBytes
+
+    @staticmethod
+    def fromBytes(data: bytes) -> "StarkProof":
+        from . import proof_format
+        return StarkProof(proof_format.from_bytes(data))
+    from_bytes = fromBytes
+
     def extractCompositionOodsEval(self) -> List[int]:
         """The last tree holds the 4 coordinate polynomials of the composition polynomial, each sampled at one point."""
         cols = self.sampledValues[-1]
