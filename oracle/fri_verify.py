@@ -124,6 +124,10 @@ def fri_verify(orc, channel, log_last_layer_degree_bound: int, log_blowup: int, 
     if len(last_poly) > 1 << log_last_layer_degree_bound:
         raise ValueError("LastLayerDegreeInvalid")
     channel.mix_felts(last_poly)
+    # a whole-proof verifier draws the queries (and derives the evaluations from the trace decommitments) only now, from the
+    # transcript as it stands after the commit phase: it passes a callable instead of the positions
+    if callable(query_positions):
+        query_positions, first_layer_query_evals = query_positions(channel)
 
     # ---- first layer: sparse evaluations per column + ONE Merkle decommitment over all coordinate columns
     max_log = column_logs[0]

@@ -147,3 +147,17 @@ def test_config5_log23_commitments(tb, orc):
     for c in (0, n_cols - 1):
         assert [int(v) for v in orc.eval_at_point(coeffs[c], oods[0], oods[1])] == list(p.sampled_values[1][c][0])
     assert len(p.fri_proof.inner_layers) == log + 1 + blow - 1 - blow and len(p.sampled_values[2]) == 4
+
+
+@pytest.mark.parametrize("log,n_cols,pow_bits,last,blow,n_queries", [(5, 6, 4, 1, 1, 3), (6, 9, 6, 0, 2, 7), (12, 32, 8, 1, 1, 20), (16, 100, 10, 0, 1, 70)])
+def test_device_proof_bytes_are_accepted_by_the_whole_proof_verifier(tb, orc, log, n_cols, pow_bits, last, blow, n_queries):
+    """The device prover's proof, as bytes, through oracle/stark_verify.py: transcript, out-of-domain check, every Merkle
+    decommitment, DEEP quotients at the queries, FRI down to the last layer, proof of work.  A flipped byte is rejected."""
+    from oracle import stark
+    from oracle.stark_verify import verify_wide_fibonacci
+    proof, _, _ = run_prove(tb, stark.fib_trace(log, n_cols), log, n_cols, pow_bits, last, blow, n_queries)
+    blob = proof.toBytes()
+    verify_wide_fibonacci(blob, log, n_cols)
+    bad = bytearray(blob); bad[len(bad) // 2] ^= 4
+    with pytest.raises(ValueError):
+        verify_wide_fibonacci(bytes(bad), log, n_cols)
