@@ -334,3 +334,30 @@ def test_peer_flags_signal_wait_put(tb):
     t2 = tb.CudaBackend.precomputeTwiddles(coset)
     assert L.tstwo_launch_count() == n0, "a freed tree of the same coset is reused, not rebuilt"
     assert (t2.twiddles.toCpu() == a).all()
+
+
+def test_lde_columns_to_peers_log23_uses_the_nine_layer_pass(tb):
+    """The multi-GPU store path at log 23 (contiguous pass + the 512-row pass, the latter on the main stream, the storing pass on the
+    side stream): row shards equal the single-device evaluations of tstwo_lde_commit."""
+    import ctypes as C
+    from tstwo_b200 import _lib
+    L = _lib.init(0)
+    log, blow, n_cols, n_shards = 23, 1, 3, 4
+    ext = log + blow
+    rows = (1 << ext) // n_shards
+    rng = np.random.default_rng(23)
+    trace = rng.integers(0, P, (n_cols, 1 << log), dtype=np.uint32)
+    tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(ext).half_coset())
+    dtrace = tb.CudaColumn.from_cpu(trace.reshape(-1))
+    evals = tb.CudaColumn.uninitialized(n_cols << ext)
+    root = (C.c_uint8 * 32)()
+    _lib.check(L.tstwo_lde_commit(dtrace.ptr, n_cols, log, blow, tw.handle, 0, evals.ptr, 0, root, 0))
+    want = evals.toCpu().reshape(n_cols, 1 << ext)
+    for groups, peer_sms in ((1, 0), (3, 62)):
+        shards = [tb.CudaColumn.zeros(n_cols * rows) for _ in range(n_shards)]
+        work = tb.CudaColumn.uninitialized(n_cols << ext)
+        _lib.check(L.tstwo_lde_columns_to_peers_overlapped(dtrace.ptr, n_cols, log, blow, tw.handle, 0, work.ptr,
+                                                           _lib.dptr_array([s.ptr for s in shards]), n_shards, 0, 0, groups, peer_sms))
+        for d in range(n_shards):
+            got = shards[d].toCpu().reshape(n_cols, rows)
+            assert (got == want[:, d * rows:(d + 1) * rows]).all(), f"groups {groups} shard {d}"
