@@ -55,6 +55,9 @@ def parse():
                     "NVLink-bound pass running beside the next group's transforms; 'off' = one group; 'auto' = per world size")
     ap.add_argument("--fence", default="flags", choices=["flags", "nccl"],
                     help="N > 1, --exchange peer: cross-rank ordering by release/acquire flags in peer memory (default) or NCCL collectives")
+    ap.add_argument("--ownership", default="contiguous", choices=["contiguous", "halves"],
+                    help="N > 1, --exchange peer with flags: which trace columns a rank holds (tstwo_b200.distributed.owned_columns); "
+                         "'halves' lets the receivers hash the first half of every leaf beside the last storing pass")
     ap.add_argument("--e2e-chunks", type=int, default=8, help="N > 1 end-to-end leg: column groups per rank crossing PCIe (the last group's LDE and the Merkle tree are exposed)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-sample-cols", type=int, default=0, help="columns of the CPU legs (0 = all of --cols: the whole config)")
@@ -212,17 +215,27 @@ def run_reference(args):
 BENCH_ROOT = "6625eaa9c95ec2ba1258dc34cd187601c8eae7333050c25a7a7cb66b3cd3a53d"
 
 
-def make_trace(torch, dev, rank, world, n_cols, n):
+def make_trace(torch, dev, rank, world, n_cols, n, ownership="contiguous"):
     """This rank's column shard of the synthetic trace: uniform random canonical M31, generated on the device
-    in 8 column blocks with fixed seeds so that every world size <= 8 sees the same job (same root)."""
+    in 8 column blocks with fixed seeds (block b of the TRACE has seed 0x5EED0003 + b) so that every world size <= 8 and either
+    column ownership (tstwo_b200.distributed.owned_columns) sees the same job (same root)."""
+    from tstwo_b200.distributed import owned_columns
     nblk = 8 if n_cols % 8 == 0 else 1
     bs = n_cols // nblk
     lc = n_cols // world
-    assert lc % bs == 0
     trace = torch.empty((lc, n), dtype=torch.int32, device=dev)
-    for k in range(lc // bs):
-        g = torch.Generator(device=dev); g.manual_seed(0x5EED0003 + rank * (lc // bs) + k)
-        trace[k * bs:(k + 1) * bs] = torch.randint(0, P, (bs, n), dtype=torch.int32, device=dev, generator=g)
+    at = 0
+    for first, count in owned_columns(rank, world, n_cols, ownership):
+        c = first
+        while c < first + count:
+            b, off = divmod(c, bs)
+            take = min(bs - off, first + count - c)
+            g = torch.Generator(device=dev); g.manual_seed(0x5EED0003 + b)
+            blk = torch.randint(0, P, (bs, n), dtype=torch.int32, device=dev, generator=g)
+            trace[at:at + take] = blk[off:off + take]
+            del blk
+            at += take
+            c += take
     return trace
 
 
@@ -357,7 +370,8 @@ def run_cuda(args):
     tw = C.c_uint64()
     chk(L.tstwo_twiddles_precompute(1 << (31 - (ext - 1) - 2), ext - 1, C.byref(tw)))
 
-    trace = make_trace(torch, dev, rank, world, n_cols, n)
+    ownership = args.ownership if (world > 1 and args.exchange == "peer" and args.fence == "flags" and not args.overlap == "off") else "contiguous"
+    trace = make_trace(torch, dev, rank, world, n_cols, n, ownership)
     root = (C.c_uint8 * 32)()
     if world == 1:
         coeffs = torch.empty((lc, n), dtype=torch.int32, device=dev)
@@ -376,7 +390,8 @@ def run_cuda(args):
             ov = OVERLAP_AUTO.get(world) if args.overlap == "auto" else None if args.overlap == "off" else tuple(int(x) for x in args.overlap.split(","))
             if args.exchange == "ce":
                 ov = None
-            sc = PeerShardedCommit(local, stream, n_cols, log, blow, overlap=ov, fence=args.fence)
+            sc = PeerShardedCommit(local, stream, n_cols, log, blow, overlap=ov, fence=args.fence,
+                                   ownership=ownership if args.exchange == "peer" else "contiguous")
         else:
             sc = ShardedCommit(CudaShardOps(local, stream), n_cols, log, blow)
         trace_flat = trace.view(-1)
@@ -669,7 +684,11 @@ def run_cuda(args):
                        "parallelism": "1 GPU" if world == 1 else (f"column-sharded LDE, last FFT pass stores rows to their owner over NVLink peer memory -> row-sharded Merkle x{world}"
                                                                        if args.exchange == "peer" else f"column-sharded LDE -> NCCL all-to-all -> row-sharded Merkle x{world}")},
             **({"fence": ("release/acquire flags in peer memory (tstwo_peer_signal / _wait / _put), no collective and no host synchronisation inside a step"
-                          if args.fence == "flags" else "NCCL all-reduce + all-gather")} if world > 1 and args.exchange == "peer" else {}),
+                          if args.fence == "flags" else "NCCL all-reduce + all-gather"),
+                "column_ownership": ("halves: a rank holds its share of the trace's first half and of its second half; the receivers hash the first "
+                                     "half of every leaf beside the last storing pass (tstwo_merkle_leaf_absorb)" if ownership == "halves"
+                                     else "contiguous column ranges; leaves hashed once all columns have arrived")}
+               if world > 1 and args.exchange == "peer" else {}),
             "gpu_launches": launches, "clocks": clocks, "root": root_hex, "root_matches_oracle_checked_root": root_hex == BENCH_ROOT if (n_cols, log, blow) == (N_COLS, LOG_SIZE, LOG_BLOWUP) else None,
             "sass_patch": sass_patch,
         }

@@ -139,6 +139,16 @@ int tstwo_merkle_commit_layer(int log_size, tstwo_dptr prev_layer, const tstwo_d
 /* MerkleProver.commit (vcs/prover.ts:13-30): all layers, root first: layer k (2^k hashes) at byte offset
  * 32*(2^k-1) of `layers` ((2^(max_log+1)-1)*32 bytes).  root[32] is copied to the host (synchronises). */
 int tstwo_merkle_commit(const tstwo_dptr *cols, const int *col_logs, int n_cols, tstwo_dptr layers, uint8_t root[32]);
+/* The leaf layer of MerkleProver.commit (vcs/prover.ts:13-30, all columns of one length) hashed in COLUMN CHUNKS, for callers whose
+ * columns become available in groups (the multi-GPU exchange: the first half of the columns of a rank's rows arrives long before the
+ * last).  `layers` is the tree buffer of tstwo_merkle_commit for max_log = log_size; between chunks the BLAKE2s chaining value of
+ * row i lives in leaf slot i.  A call absorbs columns [c0, c0 + nc) of leaves of total_cols words, given as nc evenly spaced columns
+ * (column k at cols + 4 k col_stride_words); c0 and nc are multiples of 16 (one 64-byte block) except that the last chunk ends at
+ * total_cols and finalises.  Chunks must be given in order, c0 = 0 first.  Same digests as hashNode over the whole row
+ * (vcs/blake2_merkle.ts:9-24).  tstwo_merkle_commit_nodes then builds layers log_size - 1 .. 0 over the finished leaf layer;
+ * root[32] (may be NULL) is copied to the host, which synchronises. */
+int tstwo_merkle_leaf_absorb(tstwo_dptr cols, uint64_t col_stride_words, int c0, int nc, int total_cols, int log_size, tstwo_dptr layers);
+int tstwo_merkle_commit_nodes(int log_size, tstwo_dptr layers, uint8_t root[32]);
 /* GrindOps.grind (backend/cpu/grind.ts:31-42; Backend.grind, backend/index.ts): smallest nonce such that the Blake2sChannel
  * digest after mix_u64(nonce) has >= pow_bits trailing zero bits (channel/blake2.ts:94-111,139-151). */
 int tstwo_grind(const uint8_t digest[32], uint32_t pow_bits, uint64_t *nonce);
@@ -220,6 +230,20 @@ int tstwo_lde_columns_to_peers(tstwo_dptr trace, int n_cols, int log_size, int l
 int tstwo_lde_columns_to_peers_overlapped(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
                                           tstwo_dptr coeffs, tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards,
                                           int col_offset, uint32_t flags, int col_groups, int peer_sms);
+/* The overlapped call for COLUMN-INTERLEAVED ownership, which lets the receivers hash half of every leaf while the exchange is still
+ * running: the rank's first n_cols / 2 columns are columns col_offset_lo.. of the trace, the others col_offset_hi.. (rank r of G
+ * holding c columns: r c / 2 and total / 2 + r c / 2), so that once every rank's first col_groups / 2 groups have arrived the
+ * receivers hold columns [0, total / 2) of their rows -- a prefix of every leaf's message.  col_groups must be even, >= 2 and divide
+ * n_cols; peer_sms > 0.  The side stream stores `value` (as tstwo_peer_signal) to the n_flags words half_flag_addrs once the first
+ * half's stores are complete and to arrive_flag_addrs once all are.  The LAST group's storing pass also keeps to peer_sms SMs and,
+ * unlike the call above, the side stream is NOT joined on return: what the caller enqueues next on the library's stream
+ * (tstwo_peer_wait on the half flags, tstwo_merkle_leaf_absorb of columns [0, total / 2)) runs beside that pass on the other SMs.
+ * tstwo_peer_join then makes the library's stream wait for the side stream. */
+int tstwo_lde_columns_to_peers_halves(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
+                                      tstwo_dptr coeffs, tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards,
+                                      int col_offset_lo, int col_offset_hi, uint32_t flags, int col_groups, int peer_sms,
+                                      const tstwo_dptr *half_flag_addrs, const tstwo_dptr *arrive_flag_addrs, int n_flags, uint32_t value);
+int tstwo_peer_join(void);
 /* Multi-GPU, exchange on the copy engines: shard d of a tstwo_lde_columns_sharded block ([n_shards][n_cols][rows_per_shard]) is
  * copied into shard_bases[d] at column col_offset (destination layout as above) on side streams, after the work the library's
  * stream holds now and concurrently with what it is given next (the next column group's LDE).  tstwo_scatter_join makes the

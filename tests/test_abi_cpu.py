@@ -109,7 +109,7 @@ def test_blake2s_kernels_keep_the_uniform_register_imad_form():
     if not shutil.which("cuobjdump"):
         pytest.skip("cuobjdump not on PATH")
     sass = subprocess.run(["cuobjdump", "-sass", _lib.SO_PATH], capture_output=True, text=True).stdout
-    for kernel in ("merkle_leaf_tma_kernel", "merkle_node_kernel", "merkle_node_cols_kernel"):
+    for kernel in ("merkle_leaf_tma_kernel", "merkle_leaf_chunk_kernel", "merkle_node_kernel", "merkle_node_cols_kernel"):
         body, on = [], False
         for line in sass.splitlines():
             if "Function :" in line:

@@ -90,3 +90,23 @@ def test_sharded_commit_matches_single_process(orc, world):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert root == layers[0][0].tobytes()
+
+
+def test_owned_columns_partition_the_trace_and_halves_give_a_prefix():
+    """distributed.owned_columns: every column belongs to exactly one rank under both ownerships; under "halves" the first segments
+    of all ranks tile columns [0, n/2) -- the prefix of every leaf the receivers hash before the second half has arrived."""
+    from tstwo_b200.distributed import owned_columns
+    for n_cols in (32, 256):
+        for world in (1, 2, 4, 8):
+            for own in ("contiguous", "halves"):
+                segs = [owned_columns(r, world, n_cols, own) for r in range(world)]
+                cols = [c for s in segs for a, k in s for c in range(a, a + k)]
+                assert sorted(cols) == list(range(n_cols))
+                assert all(sum(k for _, k in s) == n_cols // world for s in segs)
+            first = sorted(c for r in range(world) for a, k in owned_columns(r, world, n_cols, "halves")[:1] for c in range(a, a + k))
+            assert first == list(range(n_cols // 2))
+    import pytest
+    with pytest.raises(ValueError):
+        owned_columns(0, 8, 8, "halves")          # one column per rank cannot be split
+    with pytest.raises(ValueError):
+        owned_columns(0, 2, 8, "thirds")

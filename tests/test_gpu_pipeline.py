@@ -361,3 +361,86 @@ def test_lde_columns_to_peers_log23_uses_the_nine_layer_pass(tb):
         for d in range(n_shards):
             got = shards[d].toCpu().reshape(n_cols, rows)
             assert (got == want[:, d * rows:(d + 1) * rows]).all(), f"groups {groups} shard {d}"
+
+
+@pytest.mark.parametrize("log,n_cols,cuts", [(12, 64, [32]), (10, 48, [16, 32]), (13, 40, [16]), (9, 33, [32]), (7, 64, [32]), (12, 16, []),
+                                             (16, 256, [128]), (11, 100, [64, 96])])
+def test_merkle_leaf_absorb_in_column_chunks_equals_the_one_shot_tree(tb, log, n_cols, cuts):
+    """tstwo_merkle_leaf_absorb over column chunks + tstwo_merkle_commit_nodes = tstwo_merkle_commit over all columns (every layer),
+    and the leaf layer equals hashlib's BLAKE2s of the rows; chunks of >= 256 rows take the bulk-copy kernel, smaller ones and
+    columns that are not 16-byte spaced the per-thread one (log 7; the odd stride below)."""
+    from tstwo_b200 import _lib
+    L, chk = _lib.init(0), _lib.check
+    n = 1 << log
+    rng = np.random.default_rng(1000 * log + n_cols)
+    for stride in (n, n + 4, n + 1):
+        data = rng.integers(0, P, (n_cols, stride), dtype=np.uint32)
+        block = tb.CudaColumn.from_cpu(data.reshape(-1))
+        want_layers = tb.CudaColumn.uninitialized(8 * ((2 << log) - 1))
+        ptrs = _lib.dptr_array([block.ptr + 4 * stride * c for c in range(n_cols)])
+        chk(L.tstwo_merkle_commit(ptrs, (C.c_int * n_cols)(*([log] * n_cols)), n_cols, want_layers.ptr, None))
+        layers = tb.CudaColumn.from_cpu(np.full(8 * ((2 << log) - 1), 0x2B2B2B2B, dtype=np.uint32))
+        edges = [0] + cuts + [n_cols]
+        for c0, c1 in zip(edges[:-1], edges[1:]):
+            chk(L.tstwo_merkle_leaf_absorb(block.ptr + 4 * stride * c0, stride, c0, c1 - c0, n_cols, log, layers.ptr))
+        root = (C.c_uint8 * 32)()
+        chk(L.tstwo_merkle_commit_nodes(log, layers.ptr, root))
+        got, want = layers.toCpu(), want_layers.toCpu()
+        assert (got == want).all(), f"stride {stride}"
+        assert bytes(root) == want[:8].tobytes()
+        for i in (0, 1, n // 2 + 3 if n > 8 else 0, n - 1):
+            leaf = got[8 * ((1 << log) - 1 + i): 8 * ((1 << log) + i)].tobytes()
+            assert leaf == hashlib.blake2s(data[:, i].astype("<u4").tobytes()).digest()
+    blk = tb.CudaColumn.uninitialized(n_cols * n)
+    lay = tb.CudaColumn.uninitialized(8 * ((2 << log) - 1))
+    assert L.tstwo_merkle_leaf_absorb(blk.ptr, n, 8, 8, n_cols, log, lay.ptr) != 0 and b"block aligned" in L.tstwo_last_error()
+    assert L.tstwo_merkle_leaf_absorb(blk.ptr, n, 0, n_cols + 16, n_cols, log, lay.ptr) != 0
+
+
+@pytest.mark.parametrize("groups,peer_sms,n_cols,n_shards", [(2, 62, 4, 2), (4, 66, 8, 4), (4, 40, 16, 1), (8, 62, 16, 2)])
+def test_lde_columns_to_peers_halves(tb, orc, groups, peer_sms, n_cols, n_shards):
+    """tstwo_lde_columns_to_peers_halves on local shard buffers: the first half of the rank's columns lands at col_offset_lo.., the
+    second at col_offset_hi.., nothing else is touched, both flag sets carry the value once the side stream is joined, and the call
+    leaves the side stream unjoined without losing work (repeated)."""
+    from tstwo_b200 import _lib
+    L, chk = _lib.init(0), _lib.check
+    log, blow = 15, 1
+    ext = log + blow
+    rows = (1 << ext) // n_shards
+    lo, hi, total = 1, n_cols + 3, 2 * n_cols + 4
+    rng = np.random.default_rng(100 * groups + n_cols)
+    trace = rng.integers(0, P, (n_cols, 1 << log), dtype=np.uint32)
+    tw = tb.CudaBackend.precomputeTwiddles(tb.CanonicCoset.new(ext).half_coset())
+    root_coset = tb.CanonicCoset.new(ext).half_coset()
+    otw, oitw = orc.precompute_twiddles(root_coset.initial_index.value, root_coset.log_size)
+    _, evals, _ = orc.lde_commit(trace, blow, otw, oitw, want_coeffs=True)
+    dtrace = tb.CudaColumn.from_cpu(trace.reshape(-1))
+    flags = tb.CudaColumn.zeros(64)
+    half = _lib.dptr_array([flags.ptr + 4 * i for i in range(3)])
+    arrive = _lib.dptr_array([flags.ptr + 4 * (8 + i) for i in range(3)])
+    where = {lo + c: c for c in range(n_cols // 2)}
+    where.update({hi + c: n_cols // 2 + c for c in range(n_cols // 2)})
+    for rep in range(1, 4):
+        shards = [tb.CudaColumn.from_cpu(np.full(total * rows, 7, dtype=np.uint32)) for _ in range(n_shards)]
+        work = tb.CudaColumn.uninitialized(n_cols << ext)
+        chk(L.tstwo_lde_columns_to_peers_halves(dtrace.ptr, n_cols, log, blow, tw.handle, 0, work.ptr,
+                                                _lib.dptr_array([s.ptr for s in shards]), n_shards, lo, hi, 0, groups, peer_sms,
+                                                half, arrive, 3, rep))
+        chk(L.tstwo_peer_wait(flags.ptr, 3, rep, 5000))          # half flags: on the library's stream, beside the side stream
+        chk(L.tstwo_peer_join())
+        chk(L.tstwo_sync())
+        f = flags.toCpu()
+        assert list(f[:3]) == [rep] * 3 and list(f[8:11]) == [rep] * 3 and f[3] == 0 and f[11] == 0
+        for d in range(n_shards):
+            got = shards[d].toCpu().reshape(total, rows)
+            for c in range(total):
+                if c in where:
+                    assert (got[c] == evals[where[c]][d * rows:(d + 1) * rows]).all(), f"rep {rep} shard {d} column {c}"
+                else:
+                    assert (got[c] == 7).all(), f"shard {d} column {c} must be untouched"
+    buf = tb.CudaColumn.uninitialized(4 << ext)
+    bases = _lib.dptr_array([buf.ptr])
+    for bad in ((3, 62), (1, 62), (2, 0)):                       # odd group count, one group, no side SMs
+        rc = L.tstwo_lde_columns_to_peers_halves(dtrace.ptr, 4, log, blow, tw.handle, 0, work.ptr, bases, 1, 0, 2, 0, bad[0], bad[1], half, arrive, 3, 9)
+        assert rc != 0 and b"halves" in L.tstwo_last_error(), bad
+    chk(L.tstwo_peer_join())

@@ -23,6 +23,8 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   tstwo_evaluate_columns: { args: [T.ptr, T.i32, T.ptr, T.i32, T.i32, T.u32, T.u64, T.u32], returns: T.i32 },
   tstwo_merkle_commit_layer: { args: [T.i32, T.u64, T.ptr, T.i32, T.u64], returns: T.i32 },
   tstwo_merkle_commit: { args: [T.ptr, T.ptr, T.i32, T.u64, T.ptr], returns: T.i32 },
+  tstwo_merkle_leaf_absorb: { args: [T.u64, T.u64, T.i32, T.i32, T.i32, T.i32, T.u64], returns: T.i32 },
+  tstwo_merkle_commit_nodes: { args: [T.i32, T.u64, T.ptr], returns: T.i32 },
   tstwo_fold_line: { args: [T.ptr, T.i32, T.u32, T.ptr, T.ptr, T.u64], returns: T.i32 },
   tstwo_fold_circle_into_line: { args: [T.ptr, T.ptr, T.i32, T.u32, T.ptr, T.u64], returns: T.i32 },
   tstwo_lde_commit: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.u64, T.ptr, T.u32], returns: T.i32 },
@@ -31,6 +33,8 @@ const lib = dlopen(`libtstwo_cuda.${suffix}`, {
   // through CUDA IPC.  A single Bun process uses tstwo_init_devices + tstwo_lde_commit_multi below instead.
   tstwo_lde_columns_to_peers: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.ptr, T.i32, T.i32, T.u32], returns: T.i32 },
   tstwo_lde_columns_to_peers_overlapped: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.ptr, T.i32, T.i32, T.u32, T.i32, T.i32], returns: T.i32 },
+  tstwo_lde_columns_to_peers_halves: { args: [T.u64, T.i32, T.i32, T.i32, T.u64, T.u64, T.u64, T.ptr, T.i32, T.i32, T.i32, T.u32, T.i32, T.i32, T.ptr, T.ptr, T.i32, T.u32], returns: T.i32 },
+  tstwo_peer_join: { args: [], returns: T.i32 },
   tstwo_ipc_export: { args: [T.u64, T.ptr], returns: T.i32 },
   tstwo_ipc_import: { args: [T.ptr, T.ptr], returns: T.i32 },
   tstwo_ipc_close: { args: [T.u64], returns: T.i32 },

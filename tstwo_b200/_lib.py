@@ -61,6 +61,8 @@ SIGNATURES = {
     "tstwo_eval_at_point": (C.c_int, [dptr, C.c_int, u32p, u32p, u32p]),
     "tstwo_merkle_commit_layer": (C.c_int, [C.c_int, dptr, dptrp, C.c_int, dptr]),
     "tstwo_merkle_commit": (C.c_int, [dptrp, intp, C.c_int, dptr, C.POINTER(C.c_uint8)]),
+    "tstwo_merkle_leaf_absorb": (C.c_int, [dptr, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, dptr]),
+    "tstwo_merkle_commit_nodes": (C.c_int, [C.c_int, dptr, C.POINTER(C.c_uint8)]),
     "tstwo_fold_line": (C.c_int, [dptrp, C.c_int, C.c_uint32, u32p, dptrp, C.c_uint64]),
     "tstwo_fold_circle_into_line": (C.c_int, [dptrp, dptrp, C.c_int, C.c_uint32, u32p, C.c_uint64]),
     "tstwo_fri_decompose": (C.c_int, [dptrp, C.c_int, dptrp, u32p]),
@@ -83,6 +85,9 @@ SIGNATURES = {
     "tstwo_lde_columns_to_peers": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptrp, C.c_int, C.c_int, C.c_uint32]),
     "tstwo_lde_columns_to_peers_overlapped": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptrp, C.c_int, C.c_int,
                                                          C.c_uint32, C.c_int, C.c_int]),
+    "tstwo_lde_columns_to_peers_halves": (C.c_int, [dptr, C.c_int, C.c_int, C.c_int, C.c_uint64, dptr, dptr, dptrp, C.c_int, C.c_int, C.c_int,
+                                                     C.c_uint32, C.c_int, C.c_int, dptrp, dptrp, C.c_int, C.c_uint32]),
+    "tstwo_peer_join": (C.c_int, []),
     "tstwo_ipc_export": (C.c_int, [dptr, C.POINTER(C.c_uint8)]),
     "tstwo_ipc_import": (C.c_int, [C.POINTER(C.c_uint8), C.POINTER(C.c_uint64)]),
     "tstwo_ipc_close": (C.c_int, [dptr]),

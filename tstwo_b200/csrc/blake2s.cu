@@ -244,6 +244,61 @@ __global__ void __launch_bounds__(LEAF_ROWS, 5) merkle_leaf_tma_kernel(const __g
     out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
 }
 
+// The same kernel for a leaf layer that is hashed in COLUMN CHUNKS (multi-GPU: the first half of the columns of a rank's rows has
+// arrived long before the last, tstwo_merkle_leaf_absorb): the map describes columns [c0, c0 + nc) only, the chaining value of
+// every row lives in its slot of the leaf layer between chunks (a leaf hash is 32 bytes, so is a BLAKE2s state), the byte counter
+// continues at 4 c0 and only the chunk that holds the last column finalises.  A separate kernel on purpose: merkle_leaf_tma_kernel's
+// register allocation and IMAD form (see leaf_mbar_wait) are left exactly as they are.
+__global__ void __launch_bounds__(LEAF_ROWS, 5) merkle_leaf_chunk_kernel(const __grid_constant__ CUtensorMap map, int nc, int c0, int total_cols,
+                                                                         uint4 *__restrict__ out, uint32_t one)
+{
+    extern __shared__ __align__(128) uint8_t leaf_smem[];
+    const uint32_t base = leaf_smem_u32(leaf_smem);
+    const uint32_t ctl = base + LEAF_STAGES * LEAF_STAGE_BYTES;
+    const uint32_t n_blocks = ((uint32_t)nc + 15u) / 16u;
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < LEAF_STAGES; s++) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(ctl + 8 * s), "r"(1) : "memory");
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(ctl + 32 + 4 * s), "r"(0) : "memory");
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#pragma unroll
+        for (uint32_t s = 0; s < LEAF_STAGES; s++)
+            if (s < n_blocks) leaf_fetch(base + s * LEAF_STAGE_BYTES, &map, blockIdx.x * LEAF_ROWS, 16 * s, ctl + 8 * s);
+    }
+    __syncthreads();
+    const uint64_t i = (uint64_t)blockIdx.x * LEAF_ROWS + threadIdx.x;
+    uint32_t h[8], m[16];
+    b2s_init(h);
+    if (c0 != 0) {
+        const uint4 a = out[2 * i], b = out[2 * i + 1];
+        h[0] = a.x; h[1] = a.y; h[2] = a.z; h[3] = a.w; h[4] = b.x; h[5] = b.y; h[6] = b.z; h[7] = b.w;
+    }
+    const uint32_t t0 = 4u * (uint32_t)c0;
+    const bool closes = c0 + nc == total_cols;
+    uint32_t s = 0, ph = 0;
+#pragma unroll 1
+    for (uint32_t b = 0; b < n_blocks; b++) {
+        leaf_mbar_wait(ctl + 8 * s, ph);
+#pragma unroll
+        for (int k = 0; k < 16; k++) m[k] = leaf_lds(base + s * LEAF_STAGE_BYTES + 4 * threadIdx.x + 4 * LEAF_ROWS * k);
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) {
+            uint32_t old;
+            asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(ctl + 32 + 4 * s) : "memory");
+            if ((old & (LEAF_ROWS / 32 - 1)) == LEAF_ROWS / 32 - 1 && b + LEAF_STAGES < n_blocks)
+                leaf_fetch(base + s * LEAF_STAGE_BYTES, &map, blockIdx.x * LEAF_ROWS, 16 * (b + LEAF_STAGES), ctl + 8 * s);
+        }
+        const bool last = closes && b + 1 == n_blocks;
+        b2s_compress(h, m, last ? (uint32_t)total_cols * 4u : t0 + (b + 1) * 64u, last, one);
+        if (++s == LEAF_STAGES) { s = 0; ph ^= 1; }
+    }
+    out[2 * i] = make_uint4(h[0], h[1], h[2], h[3]);
+    out[2 * i + 1] = make_uint4(h[4], h[5], h[6], h[7]);
+}
+
 // ---- the bottom of a tree in ONE launch: node layers start_log .. 0 (no column values at those sizes), one CTA.  A layer of a
 // few hundred nodes is one compression latency of work, but as its own launch it costs ~3 us: 10 such launches per tree, 23 trees
 // per FRI commitment of config 4 (FriProver.commit 5.4 -> 5.0 ms, profiles/r02_fri_c4.txt).  Larger layers stay separate launches:
@@ -366,6 +421,33 @@ int merkle_leaf_absorb(int log_size, const ColSet &cols, int c0, int nc, int tot
     return 0;
 }
 
+// The same chunk through the bulk-copy kernel where its tensor map can describe the columns (evenly spaced, 16-byte aligned,
+// >= 256 rows); otherwise the per-thread-load kernel above.  Same digests either way.
+int merkle_leaf_absorb_fast(int log_size, const ColSet &cols, int c0, int nc, int total_cols, uint8_t *leaf_layer)
+{
+    const uint64_t n = 1ull << log_size;
+    if (c0 < 0 || c0 % 16 || nc <= 0 || c0 + nc > total_cols || (nc % 16 && c0 + nc != total_cols))
+        return fail(TSTWO_ERR_BAD_ARG, "leaf chunk [%d, %d) of %d is not block aligned", c0, c0 + nc, total_cols);
+    if (!leaf_tma_applies(cols, nc, n)) return merkle_leaf_absorb(log_size, cols, c0, nc, total_cols, leaf_layer);
+    LeafEncodeFn enc = reinterpret_cast<LeafEncodeFn>(tma_encode_tiled_fn());
+    if (!enc) return TSTWO_ERR_CUDA;
+    if (!ctx().attr_leaf_chunk) {   // per device
+        TS_CUDA(cudaFuncSetAttribute(merkle_leaf_chunk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LEAF_SMEM));
+        TS_CUDA(cudaFuncSetAttribute(merkle_leaf_chunk_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        ctx().attr_leaf_chunk = true;
+    }
+    CUtensorMap map;
+    const cuuint64_t dims[2] = { n, (cuuint64_t)nc };
+    const cuuint64_t strides[1] = { nc > 1 ? cols.stride * 4 : n * 4 };
+    const cuuint32_t box[2] = { LEAF_ROWS, 16 }, estr[2] = { 1, 1 };
+    CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<uint32_t *>(cols.base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(TSTWO_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for %d leaf columns of %llu rows", (int)r, nc, (unsigned long long)n);
+    TS_LAUNCH(merkle_leaf_chunk_kernel, (unsigned)(n / LEAF_ROWS), LEAF_ROWS, LEAF_SMEM, map, nc, c0, total_cols, (uint4 *)leaf_layer, 1u);
+    return 0;
+}
+
 int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, int n_cols, uint8_t *out)
 {
     const uint64_t n = 1ull << log_size;
@@ -449,6 +531,38 @@ int tstwo_merkle_commit_layer(int log_size, tstwo_dptr prev_layer, const tstwo_d
     int rc = make_colset(cols, n_cols, 0, &cs);
     if (rc) return rc;
     return merkle_commit_layer(log_size, (const uint8_t *)prev_layer, cs, n_cols, (uint8_t *)out_layer);
+}
+
+int tstwo_merkle_leaf_absorb(tstwo_dptr cols, uint64_t col_stride_words, int c0, int nc, int total_cols, int log_size, tstwo_dptr layers)
+{
+    TS_REQUIRE_INIT();
+    if (!cols || !layers || log_size < 0 || log_size > 30 || nc < 1 || total_cols < 1 || (cols & 3))
+        return fail(TSTWO_ERR_BAD_ARG, "bad leaf_absorb arguments");
+    if (nc > 1 && col_stride_words < (1ull << log_size)) return fail(TSTWO_ERR_BAD_ARG, "column stride shorter than a column");
+    ColSet cs = { (const uint32_t *)cols, col_stride_words, nullptr };
+    cs.aligned16 = !((cols | (col_stride_words * 4)) & 15);
+    return merkle_leaf_absorb_fast(log_size, cs, c0, nc, total_cols, (uint8_t *)layers + 32ull * ((1ull << log_size) - 1));
+}
+
+int tstwo_merkle_commit_nodes(int log_size, tstwo_dptr layers, uint8_t root[32])
+{
+    TS_REQUIRE_INIT();
+    if (!layers || log_size < 0 || log_size > 30) return fail(TSTWO_ERR_BAD_ARG, "bad commit_nodes arguments");
+    uint8_t *base = (uint8_t *)layers;
+    const uint8_t *prev = base + 32ull * ((1ull << log_size) - 1);
+    ColSet none = { nullptr, 0, nullptr };
+    for (int log = log_size - 1; log >= 0; log--) {
+        if (log <= TAIL_LOG && merkle_tail(base, log) == log) break;   // the bottom layers in one launch
+        uint8_t *dst = base + 32ull * ((1ull << log) - 1);
+        int rc = merkle_commit_layer(log, prev, none, 0, dst);
+        if (rc) return rc;
+        prev = dst;
+    }
+    if (root) {
+        TS_CUDA(cudaMemcpyAsync(root, base, 32, cudaMemcpyDeviceToHost, ctx().stream));
+        TS_CUDA(cudaStreamSynchronize(ctx().stream));
+    }
+    return 0;
 }
 
 int tstwo_merkle_commit(const tstwo_dptr *cols, const int *col_logs, int n_cols, tstwo_dptr layers, uint8_t root[32])

@@ -31,7 +31,7 @@ struct Context {
     uint64_t *d_ptr_table = nullptr;
     size_t ptr_table_cap = 0;
     // per-device one-time kernel attributes (cudaFuncSetAttribute applies to the current device only)
-    bool attr_fft = false, attr_stream = false, attr_tma = false, attr_leaf = false;
+    bool attr_fft = false, attr_stream = false, attr_tma = false, attr_leaf = false, attr_leaf_chunk = false;
     // pipeline.cu: coefficient scratch, side stream + events of the overlapped peer-store path
     uint32_t *coeff_scratch = nullptr;
     size_t coeff_scratch_words = 0;
@@ -149,6 +149,8 @@ int merkle_commit_layer(int log_size, const uint8_t *prev, const ColSet &cols, i
 int merkle_tail(uint8_t *layers, int start_log);
 // leaf layer fed in column chunks: absorbs columns [c0, c0 + nc) (given as `cols`) of leaves of total_cols words
 int merkle_leaf_absorb(int log_size, const ColSet &cols, int c0, int nc, int total_cols, uint8_t *leaf_layer);
+// the same through the bulk-copy leaf kernel where its tensor map applies (evenly spaced aligned columns, >= 256 rows)
+int merkle_leaf_absorb_fast(int log_size, const ColSet &cols, int c0, int nc, int total_cols, uint8_t *leaf_layer);
 // tstwo_shutdown: frees the scratch and the side stream / events pipeline.cu keeps between calls
 void pipeline_release();
 

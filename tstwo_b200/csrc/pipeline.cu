@@ -148,9 +148,21 @@ int g_overlap_taper = 100;     // percent of an equal share given to the first a
 #define g_peer_stream (ctx().peer_stream)
 #define g_peer_ev (ctx().peer_ev)
 
+// Column-interleaved ownership (tstwo_lde_columns_to_peers_halves): the first half of the column groups goes to columns col_offset..,
+// the second half to col_offset_hi.., the side stream publishes `value` to half_flags once the first half's stores are complete and
+// to arrive_flags once all are, the last group's storing pass keeps to peer_sms SMs and the side stream is NOT joined (the caller
+// hashes the first half of the columns beside it and then calls tstwo_peer_join).
+struct Halves {
+    int col_offset_hi = -1;
+    const tstwo_dptr *half_flags = nullptr, *arrive_flags = nullptr;
+    int n_flags = 0;
+    uint32_t value = 0;
+};
+int signal_flags(const tstwo_dptr *flag_addrs, int n, uint32_t value);   // below: the kernel of tstwo_peer_signal on ctx().stream
+
 int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw, tstwo_dptr coeffs,
                  tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards, int col_offset, uint32_t flags,
-                 int col_groups, int peer_sms)
+                 int col_groups, int peer_sms, const Halves *hv = nullptr)
 {
     TwiddleTree *t;
     int rc = check_args(n_cols, log_size, log_blowup, tw, &t);
@@ -165,6 +177,10 @@ int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tst
     if (log_size < 15 || peer_sms == 0) col_groups = 1;          // a one-pass evaluation has nothing to split off
     if (col_groups > n_cols) col_groups = n_cols;
     if (col_groups > 32) col_groups = 32;
+    if (hv && (col_groups < 2 || (col_groups & 1) || n_cols % col_groups || hv->col_offset_hi < 0 || hv->n_flags < 1 || hv->n_flags > 64 ||
+               !hv->half_flags || !hv->arrive_flags))
+        return fail(TSTWO_ERR_BAD_ARG, "column halves need an even number of equal column groups on a side stream (%d columns, %d groups, %d SMs) and flags",
+                    n_cols, col_groups, peer_sms);
     const uint64_t n = 1ull << log_size, ne = 1ull << ext, rows = 1ull << (ext - sl);
     uint32_t *scr = nullptr;
     if (!coeffs && (rc = coeff_scratch((size_t)n_cols * n, &scr))) return rc;
@@ -188,7 +204,7 @@ int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tst
     {
         int edge = col_groups >= 3 ? (int)(((long long)n_cols * g_overlap_taper + 50LL * col_groups) / (100LL * col_groups)) : 0;
         if (col_groups >= 3 && edge < 1) edge = 1;
-        if (col_groups < 3 || g_overlap_taper >= 100 || n_cols - 2 * edge < col_groups - 2) edge = 0;
+        if (col_groups < 3 || g_overlap_taper >= 100 || n_cols - 2 * edge < col_groups - 2 || hv) edge = 0;
         int left = n_cols - 2 * edge, c = 0;
         for (int k = 0; k < col_groups; k++) {
             if (edge && (k == 0 || k == col_groups - 1)) group_cols[k] = edge;
@@ -204,13 +220,14 @@ int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tst
     int c0 = 0;
     for (int k = 0; k < col_groups; k++) {
         const int nc = group_cols[k];
-        for (int d = 0; d < n_shards; d++) host_bases[64 * k + d] = shard_bases[d] + (uint64_t)(col_offset + c0) * rows * 4;
+        const int dst_col = (hv && k >= col_groups / 2) ? hv->col_offset_hi + (c0 - n_cols / 2) : col_offset + c0;
+        for (int d = 0; d < n_shards; d++) host_bases[64 * k + d] = shard_bases[d] + (uint64_t)dst_col * rows * 4;
         c0 += nc;
     }
     // SMs of group k's storing pass while group k + 1's other passes run beside it: peer_sms is the storing pass's share of the
     // LDE's integer work for EQUAL groups; for unequal neighbours the split follows their column counts
     auto side_sms = [&](int k) -> int {
-        if (k >= col_groups - 1) return 0;
+        if (k >= col_groups - 1) return hv ? peer_sms : 0;          // halves: the caller hashes beside the last storing pass
         const double ws = (double)peer_sms * group_cols[k], wm = (double)(c.sm_count - peer_sms) * group_cols[k + 1];
         int p = (int)(c.sm_count * ws / (ws + wm) + 0.5);
         if (p < 8) p = 8;
@@ -246,12 +263,14 @@ int lde_to_peers(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tst
         c.stream = g_peer_stream;
         c.grid_limit = side_sms(k);
         rc = fft_evaluate(cfs, log_size, ev, nc, ext, t, flags, &wk, 2);
+        if (!rc && hv && k == col_groups / 2 - 1) rc = signal_flags(hv->half_flags, hv->n_flags, hv->value);
+        if (!rc && hv && k == col_groups - 1) rc = signal_flags(hv->arrive_flags, hv->n_flags, hv->value);
         c.stream = main_stream;
         c0 += nc;
     }
     c.stream = main_stream;
     c.grid_limit = 0;
-    if (col_groups > 1) {                                         // join, also on the error path: the side stream may hold work
+    if (col_groups > 1 && (!hv || rc)) {                          // join, also on the error path: the side stream may hold work
         cudaError_t e = cudaEventRecord(g_peer_ev[1], g_peer_stream);
         if (e == cudaSuccess) e = cudaStreamWaitEvent(main_stream, g_peer_ev[1], 0);
         if (e != cudaSuccess && !rc) rc = fail(TSTWO_ERR_CUDA, "event record/wait failed: %s", cudaGetErrorString(e));
@@ -291,6 +310,27 @@ int tstwo_lde_columns_to_peers_overlapped(tstwo_dptr trace, int n_cols, int log_
     TS_REQUIRE_INIT();
     return lde_to_peers(trace, n_cols, log_size, log_blowup, tw, coeffs, work, shard_bases, n_shards, col_offset, flags,
                         col_groups, peer_sms);
+}
+int tstwo_lde_columns_to_peers_halves(tstwo_dptr trace, int n_cols, int log_size, int log_blowup, tstwo_twiddles tw,
+                                      tstwo_dptr coeffs, tstwo_dptr work, const tstwo_dptr *shard_bases, int n_shards,
+                                      int col_offset_lo, int col_offset_hi, uint32_t flags, int col_groups, int peer_sms,
+                                      const tstwo_dptr *half_flag_addrs, const tstwo_dptr *arrive_flag_addrs, int n_flags, uint32_t value)
+{
+    TS_REQUIRE_INIT();
+    Halves hv;
+    hv.col_offset_hi = col_offset_hi;
+    hv.half_flags = half_flag_addrs; hv.arrive_flags = arrive_flag_addrs; hv.n_flags = n_flags; hv.value = value;
+    return lde_to_peers(trace, n_cols, log_size, log_blowup, tw, coeffs, work, shard_bases, n_shards, col_offset_lo, flags,
+                        col_groups, peer_sms, &hv);
+}
+int tstwo_peer_join(void)
+{
+    TS_REQUIRE_INIT();
+    Context &c = ctx();
+    if (!g_peer_stream) return 0;                                 // nothing was ever put on a side stream
+    TS_CUDA(cudaEventRecord(g_peer_ev[1], g_peer_stream));
+    TS_CUDA(cudaStreamWaitEvent(c.stream, g_peer_ev[1], 0));
+    return 0;
 }
 }
 
@@ -361,9 +401,10 @@ __global__ void peer_put_kernel(uint32_t *dst, const uint32_t *src, int n_words,
 }
 }  // namespace
 
-int tstwo_peer_signal(const tstwo_dptr *flag_addrs, int n, uint32_t value)
+extern "C++" {
+namespace {
+int signal_flags(const tstwo_dptr *flag_addrs, int n, uint32_t value)
 {
-    TS_REQUIRE_INIT();
     if (!flag_addrs || n < 1 || n > 64) return fail(TSTWO_ERR_BAD_ARG, "tstwo_peer_signal: 1..64 flag addresses");
     FlagAddrs fa;
     memset(&fa, 0, sizeof fa);
@@ -373,6 +414,13 @@ int tstwo_peer_signal(const tstwo_dptr *flag_addrs, int n, uint32_t value)
     }
     TS_LAUNCH(peer_signal_kernel, 1, 64, 0, fa, n, value);
     return 0;
+}
+}  // namespace
+}  // extern "C++"
+int tstwo_peer_signal(const tstwo_dptr *flag_addrs, int n, uint32_t value)
+{
+    TS_REQUIRE_INIT();
+    return signal_flags(flag_addrs, n, value);
 }
 int tstwo_peer_wait(tstwo_dptr flags, int n, uint32_t value, uint32_t timeout_ms)
 {

@@ -95,6 +95,22 @@ def top_layers(ops, roots: torch.Tensor, world: int) -> List[torch.Tensor]:
     return out
 
 
+def owned_columns(rank: int, world: int, n_cols: int, ownership: str = "contiguous"):
+    """The trace columns of a rank, in the order of its local block: [(first column, count), ...].
+    "contiguous": columns [rank c, (rank + 1) c), c = n_cols / world.  "halves": the first c / 2 local columns are columns
+    rank c / 2 .. of the trace's first half, the others the same range of its second half -- after half of every rank's work the
+    receivers hold columns [0, n_cols / 2) of their rows, a prefix of every leaf's message, and can start hashing it."""
+    lc = n_cols // world
+    if ownership == "contiguous":
+        return [(rank * lc, lc)]
+    if ownership != "halves":
+        raise ValueError("ownership must be 'contiguous' or 'halves'")
+    if lc % 2:
+        raise ValueError("column halves need an even number of columns per rank")
+    h = lc // 2
+    return [(rank * h, h), (n_cols // 2 + rank * h, h)]
+
+
 class ShardedCommit:
     """Buffers + one `step()` of the multi-rank pipeline.  trace: this rank's [n_cols/G][2^log_size] block."""
 
@@ -145,17 +161,28 @@ class PeerShardedCommit:
     CUDA-only (needs peer access); the protocol above the device work is the one tests/test_distributed_cpu.py covers."""
 
     # word offsets inside the 4 KiB flag block that follows every rank's leaf buffer (same CUDA IPC mapping)
-    _ARRIVE, _HASHED, _ROOTF, _ROOTS, FLAG_BYTES = 0, 64, 128, 256, 4096
+    _ARRIVE, _HASHED, _ROOTF, _HALF, _ROOTS, FLAG_BYTES = 0, 64, 128, 192, 256, 4096
 
     def __init__(self, device_index: int, stream, n_cols: int, log_size: int, log_blowup: int, keep_coeffs: bool = False,
-                 overlap: tuple | None = None, fence: str = "flags"):
+                 overlap: tuple | None = None, fence: str = "flags", ownership: str = "contiguous"):
         """overlap = (col_groups, peer_sms): run the NVLink-bound last pass of each column group on a side stream on peer_sms
         SMs while the others transform the next group (tstwo_lde_columns_to_peers_overlapped); None = one group.
         fence = "flags": the ranks order a step with release/acquire flags in each other's memory (tstwo_peer_signal / _wait /
-        _put: no NCCL kernel in the step, no host synchronisation); "nccl": the 4-byte all-reduce + 32-byte all-gather of round 1."""
+        _put: no NCCL kernel in the step, no host synchronisation); "nccl": the 4-byte all-reduce + 32-byte all-gather of round 1.
+        ownership = "halves" (owned_columns; needs fence = "flags" and an overlap with an even number of groups): `trace` holds
+        the rank's columns of the first half of the trace, then those of the second half; the receivers hash the first half of
+        every leaf (tstwo_merkle_leaf_absorb) beside the last group's storing pass instead of after it.  Same root."""
         from . import _lib
         if fence not in ("flags", "nccl"):
             raise ValueError("fence must be 'flags' or 'nccl'")
+        if ownership not in ("contiguous", "halves"):
+            raise ValueError("ownership must be 'contiguous' or 'halves'")
+        if ownership == "halves":
+            lc = n_cols // dist.get_world_size()
+            if fence != "flags" or not overlap or overlap[0] < 2 or overlap[0] % 2 or overlap[1] < 1 or lc % overlap[0] or n_cols % 32 or log_size < 15:
+                raise ValueError("column halves need fence='flags', an overlap (even number of groups dividing the rank's columns, "
+                                 "peer_sms > 0), n_cols a multiple of 32 and log_size >= 15")
+        self.ownership = ownership
         self.fence = fence
         self._step = 0
         self.overlap = overlap
@@ -214,6 +241,7 @@ class PeerShardedCommit:
         self._flag_local = fb[r]
         self._arrive_addrs = _lib.dptr_array([f + 4 * (self._ARRIVE + r) for f in fb])
         self._hashed_addrs = _lib.dptr_array([f + 4 * (self._HASHED + r) for f in fb])
+        self._half_addrs = _lib.dptr_array([f + 4 * (self._HALF + r) for f in fb])
         self._root_dst = fb[0] + 4 * (self._ROOTS + 8 * r)
         self._root_flag = fb[0] + 4 * (self._ROOTF + r)
         self._leaf_ptrs = _lib.dptr_array([self.recv_ptr + 4 * rows * c for c in range(self.n_cols)])
@@ -232,14 +260,42 @@ class PeerShardedCommit:
     def step(self, trace: torch.Tensor, read_root: bool = True):
         """One LDE + commit.  read_root = False leaves the root on the device (rank 0: root_bytes()), so that the host can enqueue
         the next step while this one runs."""
+        self._before_stores()
+        self._lde(trace)
+        return self._finish(read_root=read_root, split=self.ownership == "halves")
+
+    def _lde(self, trace: torch.Tensor):
+        """The rank's LDE with its stores into the peers' leaf buffers (halves: also the half / arrive flags, side stream left
+        unjoined -- _finish hashes beside it)."""
         chk = self._lib_mod.check
         groups, peer_sms = self.overlap if self.overlap else (1, 0)
-        self._before_stores()
-        chk(self.L.tstwo_lde_columns_to_peers_overlapped(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw,
-                                                         self.coeffs.data_ptr() if self.coeffs is not None else 0,
-                                                         self.work.data_ptr(), self._bases_arr, self.world, self.rank * self.lc, 0,
-                                                         groups, peer_sms))
-        return self._finish(read_root=read_root)
+        cf = self.coeffs.data_ptr() if self.coeffs is not None else 0
+        if self.ownership == "halves":
+            h = self.lc // 2
+            chk(self.L.tstwo_lde_columns_to_peers_halves(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw, cf,
+                                                         self.work.data_ptr(), self._bases_arr, self.world, self.rank * h,
+                                                         self.n_cols // 2 + self.rank * h, 0, groups, peer_sms,
+                                                         self._half_addrs, self._arrive_addrs, self.world, self._step + 1))
+        else:
+            chk(self.L.tstwo_lde_columns_to_peers_overlapped(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw, cf,
+                                                             self.work.data_ptr(), self._bases_arr, self.world, self.rank * self.lc, 0,
+                                                             groups, peer_sms))
+
+    def _dst_col(self, local_col: int) -> int:
+        """Trace column of local column `local_col` (owned_columns)."""
+        for first, count in owned_columns(self.rank, self.world, self.n_cols, self.ownership):
+            if local_col < count:
+                return first + local_col
+            local_col -= count
+        raise IndexError(local_col)
+
+    def _chunks(self, chunks: int) -> int:
+        """Largest chunk count <= chunks that divides the rank's columns and keeps every chunk inside one ownership segment."""
+        seg = self.lc // len(owned_columns(self.rank, self.world, self.n_cols, self.ownership))
+        chunks = max(1, min(chunks, self.lc))
+        while self.lc % chunks or seg % (self.lc // chunks):
+            chunks -= 1
+        return chunks
 
     def root_bytes(self) -> bytes | None:
         """The last step's root (rank 0; synchronises)."""
@@ -253,36 +309,47 @@ class PeerShardedCommit:
     def step_phases(self, trace: torch.Tensor):
         """step() with a CUDA event at every phase boundary (for bench.py's per-rank breakdown): returns the 5 events around
         [LDE + peer stores | fence (all-reduce) | leaves + subtree | root gather + top layers]."""
-        chk = self._lib_mod.check
         st = self._stream if self._stream is not None else torch.cuda.current_stream()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
-        groups, peer_sms = self.overlap if self.overlap else (1, 0)
         self._before_stores()
         ev[0].record(st)
-        chk(self.L.tstwo_lde_columns_to_peers_overlapped(trace.data_ptr(), self.lc, self.log_size, self.blow, self.tw,
-                                                         self.coeffs.data_ptr() if self.coeffs is not None else 0,
-                                                         self.work.data_ptr(), self._bases_arr, self.world, self.rank * self.lc, 0,
-                                                         groups, peer_sms))
-        ev[1].record(st)
-        self._finish(ev, st)
+        self._lde(trace)
+        if self.ownership != "halves":         # halves: the phase ends where the side stream is joined (inside _finish)
+            ev[1].record(st)
+        self._finish(ev, st, split=self.ownership == "halves")
         return ev
 
-    def _finish(self, ev=None, st=None, read_root: bool = True):
+    def _finish(self, ev=None, st=None, read_root: bool = True, split: bool = False):
+        """split = True: _lde ran in halves mode (flags published by its side stream, side stream not yet joined)."""
         chk = self._lib_mod.check
         L, G = self.L, self.world
         self._step += 1
         s = self._step
-        if self.fence == "flags":
-            # "my stores are complete" into every rank's arrive[rank]; then wait until every rank has said so here
-            chk(L.tstwo_peer_signal(self._arrive_addrs, G, s))
+        if split:
+            # the side stream has published half[rank] / arrive[rank] = s to every rank (and still runs my last storing pass on
+            # peer_sms SMs): the first half of every leaf is hashed beside it, the second once everything has arrived
+            rows, half = 1 << self.sub, self.n_cols // 2
+            chk(L.tstwo_peer_wait(self._flag_local + 4 * self._HALF, G, s, self._timeout_ms))
+            chk(L.tstwo_merkle_leaf_absorb(self.recv_ptr, rows, 0, half, self.n_cols, self.sub, self.layers.data_ptr()))
+            chk(L.tstwo_peer_join())
+            if ev: ev[1].record(st)
             chk(L.tstwo_peer_wait(self._flag_local + 4 * self._ARRIVE, G, s, self._timeout_ms))
+            if ev: ev[2].record(st)
+            chk(L.tstwo_merkle_leaf_absorb(self.recv_ptr + 4 * rows * half, rows, half, half, self.n_cols, self.sub, self.layers.data_ptr()))
+            chk(L.tstwo_merkle_commit_nodes(self.sub, self.layers.data_ptr(), None))
+            if ev: ev[3].record(st)
         else:
-            self._order_before_collective()
-            dist.all_reduce(self.flag)             # every rank's stores into my leaf buffer are complete after this
-            self._order_after_collective()
-        if ev: ev[2].record(st)
-        chk(L.tstwo_merkle_commit(self._leaf_ptrs, self._leaf_logs, self.n_cols, self.layers.data_ptr(), None))
-        if ev: ev[3].record(st)
+            if self.fence == "flags":
+                # "my stores are complete" into every rank's arrive[rank]; then wait until every rank has said so here
+                chk(L.tstwo_peer_signal(self._arrive_addrs, G, s))
+                chk(L.tstwo_peer_wait(self._flag_local + 4 * self._ARRIVE, G, s, self._timeout_ms))
+            else:
+                self._order_before_collective()
+                dist.all_reduce(self.flag)             # every rank's stores into my leaf buffer are complete after this
+                self._order_after_collective()
+            if ev: ev[2].record(st)
+            chk(L.tstwo_merkle_commit(self._leaf_ptrs, self._leaf_logs, self.n_cols, self.layers.data_ptr(), None))
+            if ev: ev[3].record(st)
         if self.fence == "flags":
             chk(L.tstwo_peer_signal(self._hashed_addrs, G, s))                     # my leaf buffer may be overwritten
             chk(L.tstwo_peer_put(self._root_dst, self.layers.data_ptr(), 8, self._root_flag, s))
@@ -333,16 +400,14 @@ class PeerShardedCommit:
         group's copies are exposed; the SMs never wait on NVLink."""
         chk = self._lib_mod.check
         self._before_stores()
-        chunks = max(1, min(chunks, self.lc))
-        while self.lc % chunks:
-            chunks -= 1
+        chunks = self._chunks(chunks)
         per, n, rows = self.lc // chunks, 1 << self.log_size, 1 << self.sub
         for k in range(chunks):
             work = self.work.data_ptr() + 4 * ((k * per) << self.ext)
             chk(self.L.tstwo_lde_columns_sharded(trace.data_ptr() + 4 * n * k * per, per, self.log_size, self.blow, self.tw,
                                                  self.coeffs.data_ptr() + 4 * n * k * per if self.coeffs is not None else 0,
                                                  work, self.world, 0))
-            chk(self.L.tstwo_scatter_shards(work, per, rows, self._bases_arr, self.world, self.rank * self.lc + k * per))
+            chk(self.L.tstwo_scatter_shards(work, per, rows, self._bases_arr, self.world, self._dst_col(k * per)))
         chk(self.L.tstwo_scatter_join())
         return self._finish()
 
@@ -355,9 +420,7 @@ class PeerShardedCommit:
         if not hasattr(self, "_copy_stream"):
             self._copy_stream = torch.cuda.Stream(device=self.dev)
         cs = self._copy_stream
-        chunks = max(1, min(chunks, self.lc))
-        while self.lc % chunks:
-            chunks -= 1
+        chunks = self._chunks(chunks)
         per, n = self.lc // chunks, 1 << self.log_size
         self._before_stores()
         cs.wait_stream(main)                       # the staging buffer is free once the previous step's transforms are done
@@ -370,7 +433,7 @@ class PeerShardedCommit:
             chk(self.L.tstwo_lde_columns_to_peers(staging.data_ptr() + 4 * n * k * per, per, self.log_size, self.blow, self.tw,
                                                   self.coeffs.data_ptr() + 4 * n * k * per if self.coeffs is not None else 0,
                                                   self.work.data_ptr() + 4 * ((k * per) << self.ext),
-                                                  self._bases_arr, self.world, self.rank * self.lc + k * per, 0))
+                                                  self._bases_arr, self.world, self._dst_col(k * per), 0))
         return self._finish()
 
     def close(self):
