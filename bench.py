@@ -55,7 +55,7 @@ def parse():
                     "NVLink-bound pass running beside the next group's transforms; 'off' = one group; 'auto' = per world size")
     ap.add_argument("--fence", default="flags", choices=["flags", "nccl"],
                     help="N > 1, --exchange peer: cross-rank ordering by release/acquire flags in peer memory (default) or NCCL collectives")
-    ap.add_argument("--ownership", default="contiguous", choices=["contiguous", "halves"],
+    ap.add_argument("--ownership", default="halves", choices=["contiguous", "halves"],
                     help="N > 1, --exchange peer with flags: which trace columns a rank holds (tstwo_b200.distributed.owned_columns); "
                          "'halves' lets the receivers hash the first half of every leaf beside the last storing pass")
     ap.add_argument("--e2e-chunks", type=int, default=8, help="N > 1 end-to-end leg: column groups per rank crossing PCIe (the last group's LDE and the Merkle tree are exposed)")
@@ -370,7 +370,12 @@ def run_cuda(args):
     tw = C.c_uint64()
     chk(L.tstwo_twiddles_precompute(1 << (31 - (ext - 1) - 2), ext - 1, C.byref(tw)))
 
-    ownership = args.ownership if (world > 1 and args.exchange == "peer" and args.fence == "flags" and not args.overlap == "off") else "contiguous"
+    ownership = "contiguous"
+    if world > 1 and args.exchange == "peer" and args.ownership == "halves":
+        from tstwo_b200.distributed import PeerShardedCommit as _PSC
+        _ov = OVERLAP_AUTO.get(world) if args.overlap == "auto" else None if args.overlap == "off" else tuple(int(x) for x in args.overlap.split(","))
+        if _PSC.halves_supported(world, n_cols, log, _ov, args.fence):
+            ownership = "halves"
     trace = make_trace(torch, dev, rank, world, n_cols, n, ownership)
     root = (C.c_uint8 * 32)()
     if world == 1:

@@ -2,8 +2,10 @@
 # N GPUs: PeerShardedCommit parity under torchrun (both column ownerships), then the step time of each ownership / overlap setting
 N=${1:-2}
 shift
-timeout 900 python -m pytest tests/test_gpu_peer_commit.py -x -q > gpurun_out/t_halves_n$N.log 2>&1
-echo "pytest rc $?"; tail -5 gpurun_out/t_halves_n$N.log
+if [ -z "$SKIP_PYTEST" ]; then
+  timeout 900 python -m pytest tests/test_gpu_peer_commit.py -x -q > gpurun_out/t_halves_n$N.log 2>&1
+  echo "pytest rc $?"; tail -5 gpurun_out/t_halves_n$N.log
+fi
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 port=29530
 for cfg in "contiguous auto" "halves auto" "$@"; do

@@ -177,11 +177,9 @@ class PeerShardedCommit:
             raise ValueError("fence must be 'flags' or 'nccl'")
         if ownership not in ("contiguous", "halves"):
             raise ValueError("ownership must be 'contiguous' or 'halves'")
-        if ownership == "halves":
-            lc = n_cols // dist.get_world_size()
-            if fence != "flags" or not overlap or overlap[0] < 2 or overlap[0] % 2 or overlap[1] < 1 or lc % overlap[0] or n_cols % 32 or log_size < 15:
-                raise ValueError("column halves need fence='flags', an overlap (even number of groups dividing the rank's columns, "
-                                 "peer_sms > 0), n_cols a multiple of 32 and log_size >= 15")
+        if ownership == "halves" and not self.halves_supported(dist.get_world_size(), n_cols, log_size, overlap, fence):
+            raise ValueError("column halves need fence='flags', an overlap (even number of groups dividing the rank's columns, "
+                             "peer_sms > 0), n_cols a multiple of 32 and log_size >= 15")
         self.ownership = ownership
         self.fence = fence
         self._step = 0
@@ -250,6 +248,17 @@ class PeerShardedCommit:
         import os
         self._timeout_ms = int(os.environ.get("TSTWO_PEER_TIMEOUT_MS", "10000"))
         dist.barrier()                             # every rank's flags are zero and mapped before anyone signals
+
+    @staticmethod
+    def halves_supported(world: int, n_cols: int, log_size: int, overlap, fence: str = "flags") -> bool:
+        """Whether ownership = "halves" applies to this shape: the two leaf chunks must be whole BLAKE2s blocks (n_cols / 2 a
+        multiple of 16), the rank's columns split into an even number of equal groups, and the LDE must have a storing pass to put
+        on a side stream (log_size >= 15)."""
+        if world < 1 or n_cols % world:
+            return False
+        lc = n_cols // world
+        return (fence == "flags" and bool(overlap) and overlap[0] >= 2 and overlap[0] % 2 == 0 and overlap[1] >= 1 and lc % overlap[0] == 0
+                and n_cols % 32 == 0 and log_size >= 15)
 
     def _before_stores(self):
         """My stores go into every rank's leaf buffer: their hashing of the previous step must be over (flags: every rank
