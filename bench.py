@@ -9,7 +9,9 @@ elements, evaluate them on the blow-up-2 canonic domain (2^23 rows), Blake2s Mer
 N > 1 : columns are sharded by column for the LDE; the last FFT pass stores every row range into its owner's leaf buffer over
         NVLink peer memory (--exchange nccl: an all-to-all instead), the ranks order the step with release/acquire flags in peer
         memory (--fence nccl: collectives), every rank hashes its leaves and builds its subtree, rank 0 finishes the top log2(N)
-        layers.  --single-process drives the N devices from ONE host thread through tstwo_lde_commit_multi_dev.
+        layers.  --ownership halves (default): a rank holds its share of the first half of the columns and of the second half, so
+        that the first half of every leaf is hashed while the exchange still runs (contiguous: one column range per rank, leaves
+        hashed after the exchange); the job and its root are the same.  --single-process drives the N devices from ONE host thread through tstwo_lde_commit_multi_dev.
 --impl reference : the CPU oracle (C restatement of TStwo's CpuBackend; the TypeScript reference cannot run here)
         on all host cores, on the whole workload (all 256 columns; --cpu-sample-cols bounds it).
 roofline / rooflines / int_roofline / e2e.h2d_only / extras / phases: see DESIGN.md section 6.
@@ -473,6 +475,8 @@ def run_cuda(args):
             recs.append(sc.step_phases(trace_flat))
         torch.cuda.synchronize()
         names = ["lde_and_peer_stores", "fence", "leaf_layer_and_subtree", "root_gather_and_top_layers"]
+        if ownership == "halves":                          # same boundaries; what lies between them differs
+            names = ["lde_and_peer_stores_and_first_half_of_leaves", "fence", "second_half_of_leaves_and_subtree", "root_gather_and_top_layers"]
         tot = [sum(r[i].elapsed_time(r[i + 1]) for r in recs) / len(recs) for i in range(4)]
         t = torch.tensor(tot, device=dev, dtype=torch.float64)
         mx, mn = t.clone(), t.clone()
@@ -493,10 +497,20 @@ def run_cuda(args):
         by_lde, by_merkle = (8 + 4 + 4 * (1 << blow)) * el, (4 * n_cols + 32 + 96) * (ne // world)
         mk = lambda name, by, t_ms, note: {"kernel": name, "bound": "hbm", "algorithmic_bytes": by, "ms": t_ms, "achieved": by / t_ms / 1e6, "peak": pk,
                                            "unit": "GB/s", "frac": by / t_ms / 1e6 / pk, "traffic": None, "share_of_step": t_ms / ms, "note": note}
-        phases["rooflines_per_rank"] = [
-            mk("circle FFT of the rank's column shard (4 x column groups x fft_tma_kernel, last pass stores to the peers)", by_lde, float(mx[0]),
-               "integer-pipe bound as at N = 1; at N = 8 the peer stores (573 GB/s all-to-all) bound this phase (profiles/r02_multi.txt)"),
-            mk("merkle leaf layer + subtree of the rank's row shard", by_merkle, float(mx[2]), "integer-pipe bound (BLAKE2s)")]
+        if ownership == "halves":
+            # the first phase also hashes the first half of every leaf (beside the last storing pass): its bytes move with it
+            by_half = (4 * (n_cols // 2)) * (ne // world)
+            phases["rooflines_per_rank"] = [
+                mk("circle FFT of the rank's column shard (4 x column groups x fft_tma_kernel, last pass stores to the peers) + the first half "
+                   "of every leaf (merkle_leaf_chunk_kernel beside the last storing pass)", by_lde + by_half, float(mx[0]),
+                   "integer-pipe bound as at N = 1; at N = 8 the peer stores (573 GB/s all-to-all) bound this phase (profiles/r02_multi.txt)"),
+                mk("second half of every leaf (merkle_leaf_chunk_kernel) + subtree of the rank's row shard", by_merkle - by_half, float(mx[2]),
+                   "integer-pipe bound (BLAKE2s)")]
+        else:
+            phases["rooflines_per_rank"] = [
+                mk("circle FFT of the rank's column shard (4 x column groups x fft_tma_kernel, last pass stores to the peers)", by_lde, float(mx[0]),
+                   "integer-pipe bound as at N = 1; at N = 8 the peer stores (573 GB/s all-to-all) bound this phase (profiles/r02_multi.txt)"),
+                mk("merkle leaf layer + subtree of the rank's row shard", by_merkle, float(mx[2]), "integer-pipe bound (BLAKE2s)")]
         barrier()
 
     # ---- per-kernel timing (1 GPU), live CUDA events: `roofline` = the phase with the largest share of the step (the four
