@@ -328,19 +328,29 @@ class PeerShardedCommit:
         self._finish(ev, st, split=self.ownership == "halves")
         return ev
 
-    def _finish(self, ev=None, st=None, read_root: bool = True, split: bool = False):
-        """split = True: _lde ran in halves mode (flags published by its side stream, side stream not yet joined)."""
+    def _absorb_first_half(self, s: int):
+        """Once every rank has published half[rank] = s: hash columns [0, n_cols / 2) of my rows (chaining values in the leaf slots)."""
+        chk, L = self._lib_mod.check, self.L
+        chk(L.tstwo_peer_wait(self._flag_local + 4 * self._HALF, self.world, s, self._timeout_ms))
+        chk(L.tstwo_merkle_leaf_absorb(self.recv_ptr, 1 << self.sub, 0, self.n_cols // 2, self.n_cols, self.sub, self.layers.data_ptr()))
+
+    def _finish(self, ev=None, st=None, read_root: bool = True, split=False):
+        """split = True: _lde ran in halves mode (flags published by its side stream, side stream not yet joined).
+        split = "absorbed": the caller has hashed the first half of the columns already (_absorb_first_half) and nothing runs on a
+        side stream; arrive[rank] is published here."""
         chk = self._lib_mod.check
         L, G = self.L, self.world
         self._step += 1
         s = self._step
         if split:
-            # the side stream has published half[rank] / arrive[rank] = s to every rank (and still runs my last storing pass on
-            # peer_sms SMs): the first half of every leaf is hashed beside it, the second once everything has arrived
+            # the first half of every leaf is hashed beside my last storing pass (still running on peer_sms SMs of the side stream,
+            # which has published half[rank] / arrive[rank] = s to every rank), the second once everything has arrived
             rows, half = 1 << self.sub, self.n_cols // 2
-            chk(L.tstwo_peer_wait(self._flag_local + 4 * self._HALF, G, s, self._timeout_ms))
-            chk(L.tstwo_merkle_leaf_absorb(self.recv_ptr, rows, 0, half, self.n_cols, self.sub, self.layers.data_ptr()))
-            chk(L.tstwo_peer_join())
+            if split == "absorbed":
+                chk(L.tstwo_peer_signal(self._arrive_addrs, G, s))
+            else:
+                self._absorb_first_half(s)
+                chk(L.tstwo_peer_join())
             if ev: ev[1].record(st)
             chk(L.tstwo_peer_wait(self._flag_local + 4 * self._ARRIVE, G, s, self._timeout_ms))
             if ev: ev[2].record(st)
@@ -431,6 +441,7 @@ class PeerShardedCommit:
         cs = self._copy_stream
         chunks = self._chunks(chunks)
         per, n = self.lc // chunks, 1 << self.log_size
+        early = self.ownership == "halves" and self.fence == "flags" and chunks >= 2
         self._before_stores()
         cs.wait_stream(main)                       # the staging buffer is free once the previous step's transforms are done
         for k in range(chunks):
@@ -443,7 +454,12 @@ class PeerShardedCommit:
                                                   self.coeffs.data_ptr() + 4 * n * k * per if self.coeffs is not None else 0,
                                                   self.work.data_ptr() + 4 * ((k * per) << self.ext),
                                                   self._bases_arr, self.world, self._dst_col(k * per), 0))
-        return self._finish()
+            if early and (k + 1) * per == self.lc // 2:
+                # halves: my share of the trace's first half is stored.  Once every rank's is, hash that half of every leaf -- while
+                # the second half is still crossing PCIe, where the device has nothing else to do
+                chk(self.L.tstwo_peer_signal(self._half_addrs, self.world, self._step + 1))
+                self._absorb_first_half(self._step + 1)
+        return self._finish(split="absorbed" if early else False)
 
     def close(self):
         torch.cuda.synchronize()
