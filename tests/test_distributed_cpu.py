@@ -110,3 +110,32 @@ def test_owned_columns_partition_the_trace_and_halves_give_a_prefix():
         owned_columns(0, 8, 8, "halves")          # one column per rank cannot be split
     with pytest.raises(ValueError):
         owned_columns(0, 2, 8, "thirds")
+
+
+def test_halves_ownership_reassembles_the_rows_and_hashes_in_two_chunks():
+    """The data flow of PeerShardedCommit(ownership="halves") on the host: every rank stores its two column segments at their trace
+    columns of the receivers' leaf buffers (first segments first), and a leaf hashed as BLAKE2s over columns [0, n/2) continued over
+    [n/2, n) -- what tstwo_merkle_leaf_absorb does in two calls -- is the leaf of the whole row."""
+    import hashlib
+    import numpy as np
+    from tstwo_b200.distributed import owned_columns
+    n_cols, rows, world = 64, 8, 4
+    trace = np.random.default_rng(5).integers(0, 2**31 - 1, (n_cols, rows), dtype=np.uint32)
+    leaf_buffer = np.zeros_like(trace)
+    arrived_after_first_phase = set()
+    for phase in (0, 1):
+        for r in range(world):
+            segs = owned_columns(r, world, n_cols, "halves")
+            local = np.concatenate([trace[a:a + c] for a, c in segs])            # the rank's local block, first-half share first
+            at = sum(c for _, c in segs[:phase])
+            first, count = segs[phase]
+            leaf_buffer[first:first + count] = local[at:at + count]
+        if phase == 0:
+            arrived_after_first_phase = {c for c in range(n_cols) if leaf_buffer[c].any()}
+    assert arrived_after_first_phase == set(range(n_cols // 2)), "after every rank's first segment the receivers hold a PREFIX of each row"
+    assert (leaf_buffer == trace).all()
+    for i in range(rows):
+        h = hashlib.blake2s()
+        h.update(leaf_buffer[:n_cols // 2, i].astype("<u4").tobytes())
+        h.update(leaf_buffer[n_cols // 2:, i].astype("<u4").tobytes())
+        assert h.digest() == hashlib.blake2s(trace[:, i].astype("<u4").tobytes()).digest()
