@@ -280,7 +280,9 @@ int tstwo_lde_commit_host(const uint32_t *host_trace, int n_cols, int log_size, 
  * buffers (allocated at the first call for a shape).  G = tstwo_device_count() must be a power of two dividing n_cols, and every
  * device needs >= 2^14 rows.
  *   tstwo_lde_commit_multi      host_trace = [n_cols][2^log_size] words in HOST memory (pinned for full PCIe speed): every device
- *                               pulls its shard over its own PCIe link, chunk by chunk, overlapped with the transforms;
+ *                               pulls its shard over its own PCIe link, chunk by chunk, overlapped with the transforms (which
+ *                               columns a device pulls is the library's choice: for n_cols a multiple of 32, its share of the first
+ *                               half of the columns and then of the second, so that half of every leaf is hashed during the copy);
  *   tstwo_lde_commit_multi_dev  trace_shards[d] = device address ON slot d of columns [d n_cols/G, (d+1) n_cols/G). */
 int tstwo_lde_commit_multi(const uint32_t *host_trace, int n_cols, int log_size, int log_blowup, uint8_t root[32], uint32_t flags);
 int tstwo_lde_commit_multi_dev(const tstwo_dptr *trace_shards, int n_cols, int log_size, int log_blowup, uint8_t root[32],

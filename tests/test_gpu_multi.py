@@ -78,7 +78,10 @@ print("MULTI OK", G, want.hex())
 '''
 
 
-@pytest.mark.parametrize("G,n_cols,log,blow", [(1, 6, 15, 1), (2, 12, 16, 1), (4, 16, 17, 1), (8, 32, 17, 2)])
+# n_cols a multiple of 32: the host-fed call takes the column-interleaved ownership (first half of every leaf hashed while the
+# second half of the trace is still being copied); the other shapes keep contiguous column ranges
+@pytest.mark.parametrize("G,n_cols,log,blow", [(1, 6, 15, 1), (1, 32, 15, 1), (2, 12, 16, 1), (2, 64, 16, 1), (4, 16, 17, 1), (4, 64, 16, 1),
+                                               (8, 32, 17, 2)])
 def test_lde_commit_multi_in_one_process(G, n_cols, log, blow):
     import torch
     if torch.cuda.device_count() < G:

@@ -97,7 +97,7 @@ struct Dev {
     tstwo_twiddles tw = 0;
     uint32_t *stage = nullptr, *work = nullptr, *leaf = nullptr;   // host-fed staging [lc][n], evaluations scratch [lc][ne], leaf buffer [n_cols][rows]
     uint8_t *layers = nullptr;                                     // this device's subtree, root first
-    cudaEvent_t lde_done = nullptr, sub_done = nullptr, stage_free = nullptr;
+    cudaEvent_t lde_done = nullptr, sub_done = nullptr, stage_free = nullptr, half_done = nullptr;
     std::vector<cudaEvent_t> chunk_ev;
 };
 struct Multi {
@@ -117,7 +117,7 @@ void release_all()
         cudaDeviceSynchronize();
         if (v.tw) tstwo_twiddles_free(v.tw);
         cudaFree(v.stage); cudaFree(v.work); cudaFree(v.leaf); cudaFree(v.layers);
-        for (cudaEvent_t e : { v.lde_done, v.sub_done, v.stage_free }) if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : { v.lde_done, v.sub_done, v.stage_free, v.half_done }) if (e) cudaEventDestroy(e);
         for (cudaEvent_t e : v.chunk_ev) cudaEventDestroy(e);
         if (i == 0) { cudaFree(g_m.roots); cudaFree(g_m.top); }
         v = Dev();
@@ -155,7 +155,7 @@ int ensure(int n_cols, int log_size, int log_blowup, bool need_stage)
         if ((rc = dev_alloc((void **)&v.leaf, (size_t)n_cols * rows * 4, "leaf buffer"))) return rc;
         if ((rc = dev_alloc((void **)&v.layers, 32ull * (2 * rows - 1), "subtree"))) return rc;
         if (need_stage && (rc = dev_alloc((void **)&v.stage, (size_t)lc * n * 4, "trace staging"))) return rc;
-        for (cudaEvent_t *e : { &v.lde_done, &v.sub_done, &v.stage_free }) TS_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+        for (cudaEvent_t *e : { &v.lde_done, &v.sub_done, &v.stage_free, &v.half_done }) TS_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
         if (i == 0) {
             if ((rc = dev_alloc((void **)&g_m.roots, 32ull * G, "subtree roots"))) return rc;
             if ((rc = dev_alloc((void **)&g_m.top, 32ull * (G > 1 ? G : 2), "top layers"))) return rc;
@@ -182,7 +182,7 @@ int check(int n_cols, int log_size, int log_blowup)
 }
 
 // steps 2..4 of the header comment, after every device's LDE has been enqueued and lde_done recorded
-int subtrees_and_top(uint8_t root[32])
+int subtrees_and_top(uint8_t root[32], bool first_half_absorbed = false)
 {
     const int G = g_m.n_dev, n_cols = g_m.n_cols, ext = g_m.log_size + g_m.log_blowup;
     int sl = 0;
@@ -195,8 +195,14 @@ int subtrees_and_top(uint8_t root[32])
         Context &c = ctx();
         Dev &v = g_m.d[i];
         for (int e = 0; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].lde_done, 0));
-        for (int k = 0; k < n_cols; k++) ptrs[k] = (tstwo_dptr)(v.leaf + (uint64_t)k * rows);
-        int r = tstwo_merkle_commit(ptrs.data(), logs.data(), n_cols, (tstwo_dptr)v.layers, nullptr);
+        int r;
+        if (first_half_absorbed) {                             // columns [0, n_cols / 2) are in the leaf slots' chaining values already
+            r = tstwo_merkle_leaf_absorb((tstwo_dptr)(v.leaf + (uint64_t)(n_cols / 2) * rows), rows, n_cols / 2, n_cols / 2, n_cols, ext - sl, (tstwo_dptr)v.layers);
+            if (!r) r = tstwo_merkle_commit_nodes(ext - sl, (tstwo_dptr)v.layers, nullptr);
+        } else {
+            for (int k = 0; k < n_cols; k++) ptrs[k] = (tstwo_dptr)(v.leaf + (uint64_t)k * rows);
+            r = tstwo_merkle_commit(ptrs.data(), logs.data(), n_cols, (tstwo_dptr)v.layers, nullptr);
+        }
         if (r) return r;
         TS_CUDA(cudaMemcpyPeerAsync(g_m.roots + 32 * i, ctx_at(0).device, v.layers, c.device, 32, c.stream));
         TS_CUDA(cudaEventRecord(v.sub_done, c.stream));
@@ -272,6 +278,16 @@ int tstwo_lde_commit_multi(const uint32_t *host_trace, int n_cols, int log_size,
     int chunks = lc < 4 ? lc : 4;
     while (lc % chunks) chunks--;
     const int per = lc / chunks;
+    // Column-interleaved ownership (the library picks which columns a device pulls): device i takes its share of the trace's FIRST
+    // half of the columns, then its share of the second, so that after everyone's first chunks/2 chunks every device holds columns
+    // [0, n_cols/2) of its rows and hashes that half of every leaf while the second half is still crossing PCIe (as
+    // PeerShardedCommit(ownership="halves"), tstwo_b200/distributed.py).  Needs whole BLAKE2s blocks per half and an even chunk count.
+    const bool halves = n_cols % 32 == 0 && chunks % 2 == 0;
+    auto first_col = [&](int i, int k) -> uint64_t {           // trace column of local column k * per of device i
+        if (!halves) return (uint64_t)i * lc + (uint64_t)k * per;
+        const int h = lc / 2, c = k * per;
+        return c < h ? (uint64_t)i * h + c : (uint64_t)n_cols / 2 + (uint64_t)i * h + (c - h);
+    };
     tstwo_dptr bases[MAX_SLOTS];
     for (int i = 0; i < G; i++) bases[i] = (tstwo_dptr)g_m.d[i].leaf;
     // all copies first, so that every PCIe link starts at once
@@ -282,28 +298,45 @@ int tstwo_lde_commit_multi(const uint32_t *host_trace, int n_cols, int log_size,
         while ((int)v.chunk_ev.size() < chunks) { cudaEvent_t e; TS_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); v.chunk_ev.push_back(e); }
         if (g_m.ran) TS_CUDA(cudaStreamWaitEvent(c.copy_stream, v.stage_free, 0));   // the previous step's transforms have read the staging buffer
         for (int k = 0; k < chunks; k++) {
-            TS_CUDA(cudaMemcpyAsync(v.stage + (uint64_t)k * per * n, host_trace + ((uint64_t)i * lc + (uint64_t)k * per) * n, (uint64_t)per * n * 4,
+            TS_CUDA(cudaMemcpyAsync(v.stage + (uint64_t)k * per * n, host_trace + first_col(i, k) * n, (uint64_t)per * n * 4,
                                     cudaMemcpyHostToDevice, c.copy_stream));
             TS_CUDA(cudaEventRecord(v.chunk_ev[k], c.copy_stream));
         }
     }
-    rc = g_fan.run(G, [&](int i) -> int {
-        DeviceScope sc(i);
-        Context &c = ctx();
-        Dev &v = g_m.d[i];
-        if (g_m.ran) for (int e = 0; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].sub_done, 0));
-        for (int k = 0; k < chunks; k++) {
-            TS_CUDA(cudaStreamWaitEvent(c.stream, v.chunk_ev[k], 0));
-            int r = tstwo_lde_columns_to_peers((tstwo_dptr)(v.stage + (uint64_t)k * per * n), per, log_size, log_blowup, v.tw, 0,
-                                               (tstwo_dptr)(v.work + (uint64_t)k * per * ne), bases, G, i * lc + k * per, flags);
-            if (r) return r;
-        }
-        TS_CUDA(cudaEventRecord(v.stage_free, c.stream));
-        TS_CUDA(cudaEventRecord(v.lde_done, c.stream));
-        return 0;
-    });
-    if (rc) return rc;
-    return subtrees_and_top(root);
+    // chunks [k0, k1) of every device; `after_half`: first wait for every device's first half, hash it, then go on
+    auto run_chunks = [&](int k0, int k1, bool after_half) -> int {
+        return g_fan.run(G, [&](int i) -> int {
+            DeviceScope sc(i);
+            Context &c = ctx();
+            Dev &v = g_m.d[i];
+            if (k0 == 0 && g_m.ran) for (int e = 0; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].sub_done, 0));
+            if (after_half) {
+                int sl = 0;
+                while ((1 << sl) < G) sl++;
+                const uint64_t rows = ne >> sl;
+                for (int e = 0; e < G; e++) TS_CUDA(cudaStreamWaitEvent(c.stream, g_m.d[e].half_done, 0));
+                int r = tstwo_merkle_leaf_absorb((tstwo_dptr)v.leaf, rows, 0, n_cols / 2, n_cols, log_size + log_blowup - sl, (tstwo_dptr)v.layers);
+                if (r) return r;
+            }
+            for (int k = k0; k < k1; k++) {
+                TS_CUDA(cudaStreamWaitEvent(c.stream, v.chunk_ev[k], 0));
+                int r = tstwo_lde_columns_to_peers((tstwo_dptr)(v.stage + (uint64_t)k * per * n), per, log_size, log_blowup, v.tw, 0,
+                                                   (tstwo_dptr)(v.work + (uint64_t)k * per * ne), bases, G, (int)first_col(i, k), flags);
+                if (r) return r;
+            }
+            if (k1 == chunks) {
+                TS_CUDA(cudaEventRecord(v.stage_free, c.stream));
+                TS_CUDA(cudaEventRecord(v.lde_done, c.stream));
+            } else TS_CUDA(cudaEventRecord(v.half_done, c.stream));
+            return 0;
+        });
+    };
+    // an event must be RECORDED (host side) before another device's stream is told to wait for it: one fan-out per phase
+    if (halves) {
+        if ((rc = run_chunks(0, chunks / 2, false))) return rc;
+        if ((rc = run_chunks(chunks / 2, chunks, true))) return rc;
+    } else if ((rc = run_chunks(0, chunks, false))) return rc;
+    return subtrees_and_top(root, halves);
 }
 
 }  // extern "C"
