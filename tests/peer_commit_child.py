@@ -1,6 +1,6 @@
 """PeerShardedCommit (one process per GPU, fused peer stores, flag fences) against the ORACLE's root, for both column ownerships
 and the chunked steps; run under torchrun (tests/test_gpu_peer_commit.py does, for every world size the box offers).
-usage: torchrun --nproc-per-node G scripts/peer_commit_check.py n_cols log blow groups peer_sms"""
+usage: torchrun --nproc-per-node G tests/peer_commit_child.py n_cols log blow groups peer_sms"""
 import os
 import sys
 

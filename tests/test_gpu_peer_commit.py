@@ -20,7 +20,7 @@ def test_peer_sharded_commit_both_ownerships(G, n_cols, log, blow, groups, peer_
         pytest.skip(f"needs {G} GPUs")
     port = 29600 + (os.getpid() + 7 * G + log) % 300
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={G}", "--master-addr", "127.0.0.1",
-           "--master-port", str(port), os.path.join(ROOT, "scripts", "peer_commit_check.py"),
+           "--master-port", str(port), os.path.join(ROOT, "tests", "peer_commit_child.py"),
            str(n_cols), str(log), str(blow), str(groups), str(peer_sms)]
     env = dict(os.environ, TSTWO_PEER_TIMEOUT_MS="20000")
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=env)

@@ -380,7 +380,7 @@ static int ensure_smem_attr()
 }
 
 struct Pass { int lo, j_min, win; };
-// passes in ascending layer order for L real layers (scripts/proto_fft.py): one contiguous 12-layer pass, then
+// passes in ascending layer order for L real layers (tests/proto_fft.py): one contiguous 12-layer pass, then
 // strided 10-layer windows; the top window is aligned to L and skips the layers already done.
 // The TMA passes (fft_tma.cu) use a 14-layer contiguous pass and 8-layer strided windows instead.
 constexpr int W0 = Shape<false, 3>::RHO, W1 = Shape<true, 3>::RHO;
