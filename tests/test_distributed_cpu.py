@@ -139,3 +139,29 @@ def test_halves_ownership_reassembles_the_rows_and_hashes_in_two_chunks():
         h.update(leaf_buffer[:n_cols // 2, i].astype("<u4").tobytes())
         h.update(leaf_buffer[n_cols // 2:, i].astype("<u4").tobytes())
         assert h.digest() == hashlib.blake2s(trace[:, i].astype("<u4").tobytes()).digest()
+
+
+def test_bench_make_trace_is_the_same_job_under_every_world_size_and_ownership():
+    """bench.make_trace: the shards of every world size and of both column ownerships reassemble to the SAME trace (the one whose
+    root bench.py prints and tests/test_gpu_config_sizes.py checks against the oracle) -- on the CPU generator here, which has its
+    own random stream but the same block / seed structure."""
+    import os
+    import sys
+    import torch
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    from tstwo_b200.distributed import owned_columns
+    n_cols, n = 64, 32
+    dev = torch.device("cpu")
+    whole = bench.make_trace(torch, dev, 0, 1, n_cols, n)
+    assert whole.shape == (n_cols, n) and int(whole.max()) < 2**31 - 1 and int(whole.min()) >= 0
+    for world in (2, 4, 8):
+        for own in ("contiguous", "halves"):
+            got = torch.empty_like(whole)
+            for r in range(world):
+                shard = bench.make_trace(torch, dev, r, world, n_cols, n, own)
+                at = 0
+                for first, count in owned_columns(r, world, n_cols, own):
+                    got[first:first + count] = shard[at:at + count]
+                    at += count
+            assert torch.equal(got, whole), (world, own)
