@@ -257,7 +257,7 @@ class PeerShardedCommit:
         if world < 1 or n_cols % world:
             return False
         lc = n_cols // world
-        return (fence == "flags" and bool(overlap) and overlap[0] >= 2 and overlap[0] % 2 == 0 and overlap[1] >= 1 and lc % overlap[0] == 0
+        return (fence == "flags" and bool(overlap) and 2 <= overlap[0] <= 32 and overlap[0] % 2 == 0 and overlap[1] >= 1 and lc % overlap[0] == 0
                 and n_cols % 32 == 0 and log_size >= 15)
 
     def _before_stores(self):
